@@ -1,0 +1,160 @@
+/* ubresnet_b200 -- C ABI of the sm_100a hot-path library (libubresnet_b200.so).
+ *
+ * The reference (NuTufts/ubresnet) has NO plugin/FFI boundary: its hot path sits behind the Python
+ * nn.Module API (models/ub_uresnet.py:31,88; training/pixelwise_nllloss.py:35,41) and every device
+ * op is a torch.nn library call.  The entry points below are what a binding for that path needs:
+ * one call per reference op (or per fused group of ops), taking raw DEVICE pointers, plain sizes and
+ * a cudaStream_t (as void*).  No torch types, no C++ types, no exceptions cross this boundary.
+ *
+ * Conventions
+ *   - every function returns 0 on success, <0 on error (UBR_E_*); the message is in ubr_last_error()
+ *     (thread local).  There is NO CPU fallback: a non-sm_100 device gives UBR_E_UNSUPPORTED.
+ *   - the library never allocates caller-visible memory; outputs and workspaces are caller provided
+ *     (sizes via the *_workspace_bytes helpers) and must stay valid until the stream reaches the op.
+ *   - activations are NHWC bf16 "views": a channel slice [0,c) of a pixel-major buffer with pixel
+ *     pitch `ld` elements (ld >= c, ld*2 bytes multiple of 16, ptr 16-byte aligned).  Channel slices
+ *     make torch.cat([deconv, skip], 1) (models/common_layers.py:130) a zero-copy operation.
+ *   - parameters stay fp32 in the reference layouts (OIHW, ConvTranspose IOHW); ubr_pack_weights
+ *     derives the bf16 GEMM operand copies.
+ */
+#ifndef UBRESNET_B200_H
+#define UBRESNET_B200_H
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define UBR_ABI_VERSION 1
+#define UBR_OK 0
+#define UBR_E_BADARG (-1)
+#define UBR_E_UNSUPPORTED (-2)
+#define UBR_E_CUDA (-3)
+#define UBR_E_NCCL (-4)
+
+typedef struct ubr_view {
+  void* ptr;      /* device pointer to (n=0,h=0,w=0,c=0) of the slice, bf16 */
+  int32_t n, h, w, c;
+  int32_t ld;     /* elements between consecutive pixels of the underlying buffer */
+} ubr_view;
+
+/* ---- library ------------------------------------------------------------------------------ */
+int ubr_abi_version(void);
+const char* ubr_last_error(void);
+int ubr_device_check(void);               /* 0 iff the current CUDA device is sm_100 (B200) */
+int ubr_sync_check(void* stream);         /* cudaStreamSynchronize + surface async errors */
+
+/* ---- weight packing: fp32 reference layout -> bf16 [tap][n][k] GEMM operand ---------------------
+ * replaces the implicit cuDNN filter transforms behind nn.Conv2d / nn.ConvTranspose2d.
+ *   src_layout 0: OIHW  (nn.Conv2d.weight,            models/common_layers.py:15,34; ub_uresnet.py:41,60,64)
+ *   src_layout 1: IOHW  (nn.ConvTranspose2d.weight,   models/common_layers.py:125)
+ *   n_is_out 1: n = output channel, k = input channel (forward operand)
+ *   n_is_out 0: n = input channel,  k = output channel (data-gradient operand)
+ * dst has taps = kh*kw slabs of [n_pad][k_pad] (zero padded, n_pad/k_pad multiples of 16). */
+int ubr_pack_weights(const float* src, int src_layout, int n_is_out, int out_ch, int in_ch, int kh, int kw,
+                     int n_pad, int k_pad, void* dst_bf16, void* stream);
+
+/* ---- tensor-core implicit-GEMM convolutions (tcgen05 + TMEM + TMA) ----------------------------
+ * nn.Conv2d(k in {1,3,7}, stride in {1,2}, padding=(k-1)/2)  forward:
+ *   y[n,ho,wo,:] = sum_{r,s} x[n, ho*stride+r-pad, wo*stride+s-pad, :] * W[:, :, r, s]^T  (+ bias)
+ * wpk = ubr_pack_weights(..., n_is_out=1).  bias may be NULL.
+ * If y_f32 != NULL the result is written as fp32 [pixel][y_f32_ld] (first out_ch columns) instead of y. */
+int ubr_conv2d_fwd(ubr_view x, const void* wpk, const float* bias, int out_ch, int ksize, int stride,
+                   ubr_view y, float* y_f32, int y_f32_ld, void* stream);
+/* data gradient of the same conv: dx = conv_transpose(dy, W).  wpk = pack(..., n_is_out=0). */
+int ubr_conv2d_dgrad(ubr_view dy, const void* wpk, int in_ch, int ksize, int stride, ubr_view dx, void* stream);
+/* weight gradient: dw[o,i,r,s] (+)= sum_pixels dy[.,o] * x[shifted,i]; fp32 OIHW.  accumulate: 0 overwrite, 1 add */
+int ubr_conv2d_wgrad(ubr_view x, ubr_view dy, int out_ch /* true rows of dw; dy.c may be padded */, int ksize,
+                     int stride, float* dw, int accumulate, void* workspace, uint64_t workspace_bytes, void* stream);
+/* split-K partial buffer size.  conv: grid = output (n,h,w), m_ch = padded out_ch, n_ch = in_ch, ntaps = k*k;
+ * deconv: grid = input (n,h,w), m_ch = in_ch, n_ch = out_ch, ntaps = 16 */
+uint64_t ubr_wgrad_workspace_bytes(int grid_n, int grid_h, int grid_w, int m_ch, int n_ch, int ntaps);
+
+/* nn.ConvTranspose2d(k=4, stride=2, padding=1, bias=False), output_size == 2x input (common_layers.py:125,128) */
+int ubr_deconv4s2_fwd(ubr_view x, const void* wpk, int out_ch, ubr_view y, void* stream);
+int ubr_deconv4s2_dgrad(ubr_view dy, const void* wpk, int in_ch, ubr_view dx, void* stream);
+int ubr_deconv4s2_wgrad(ubr_view x, ubr_view dy, float* dw /* IOHW */, int accumulate,
+                        void* workspace, uint64_t workspace_bytes, void* stream);
+
+/* ---- stem: nn.Conv2d(1, 16*m, 7, 1, 3, bias=True) on the fp32 NCHW input (ub_uresnet.py:41,94) -- */
+int ubr_stem_conv_fwd(const float* x /* [n,1,h,w] */, int n, int h, int w, const float* wgt /* [oc,1,7,7] */,
+                      const float* bias, int out_ch, ubr_view y, void* stream);
+int ubr_stem_conv_wgrad(const float* x, int n, int h, int w, ubr_view dy, float* dw, float* dbias,
+                        int accumulate, void* workspace, uint64_t workspace_bytes, void* stream);
+uint64_t ubr_stem_wgrad_workspace_bytes(int n, int h, int w, int out_ch);
+
+/* ---- BatchNorm2d (ub_uresnet.py:42,61; common_layers.py:24,27,35) ------------------------------
+ * training statistics over (n,h,w): deterministic two-level reduction.
+ * stats kernel writes per-block partials, finalize produces the per-channel affine
+ *   scale = gamma*invstd, shift = beta - mean*scale, and updates running stats
+ *   (momentum 0.1, unbiased variance for running_var, eps inside sqrt). */
+uint64_t ubr_bn_workspace_bytes(int c);
+int ubr_bn_stats(ubr_view y, void* workspace, void* stream);
+int ubr_bn_finalize(const void* workspace, int c, double count, const float* gamma, const float* beta,
+                    float* running_mean, float* running_var, float momentum, float eps,
+                    float* scale, float* shift, float* mean, float* invstd, void* stream);
+/* eval mode: scale/shift from running statistics */
+int ubr_bn_eval_affine(int c, const float* gamma, const float* beta, const float* running_mean,
+                       const float* running_var, float eps, float* scale, float* shift, void* stream);
+/* out = relu?(y*scale+shift) */
+int ubr_bn_act(ubr_view y, const float* scale, const float* shift, int relu, ubr_view out, void* stream);
+/* residual block tail (common_layers.py:45-56): out = relu( relu(y2*s2+b2) + (res*sr+br | res) ) */
+int ubr_block_tail(ubr_view y2, const float* s2, const float* b2, ubr_view res, const float* sr, const float* br,
+                   ubr_view out, void* stream);
+
+/* backward of out = relu(bn(y)):  given dout and y(+affine), two passes.
+ *  pass 1 (reduce): sums[0:c) = sum dz, sums[c:2c) = sum dz*xhat       (dz = dout * (bn(y)>0 or !relu))
+ *  pass 2 (apply) : dy = gamma*invstd*(dz - sum_dz/count - xhat*sum_dzx/count); dgamma=sum_dzx; dbeta=sum_dz */
+int ubr_bn_act_bwd_reduce(ubr_view dout, ubr_view y, const float* scale, const float* shift, const float* mean,
+                          const float* invstd, int relu, void* workspace, void* stream);
+int ubr_bn_act_bwd_apply(ubr_view dout, ubr_view y, const float* scale, const float* shift, const float* mean,
+                         const float* invstd, const float* gamma, int relu, const void* workspace, double count,
+                         ubr_view dy, float* dgamma, float* dbeta, int accumulate, void* stream);
+/* backward of the block tail.  du = dout*(out>0); main branch dz2 = du*(bn2(y2)>0); residual branch gets du.
+ * res_is_bn=1: residual is bnpass(bypass conv) -> dres = BN backward of du wrt `res` (pre-BN conv output)
+ * res_is_bn=0: identity residual -> dres = du */
+int ubr_block_tail_bwd_reduce(ubr_view dout, ubr_view out, ubr_view y2, const float* s2, const float* b2,
+                              const float* mean2, const float* invstd2, ubr_view res, const float* meanr,
+                              const float* invstdr, int res_is_bn, void* workspace, void* stream);
+int ubr_block_tail_bwd_apply(ubr_view dout, ubr_view out, ubr_view y2, const float* s2, const float* b2,
+                             const float* mean2, const float* invstd2, const float* gamma2,
+                             ubr_view res, const float* meanr, const float* invstdr, const float* gammar,
+                             int res_is_bn, const void* workspace, double count, ubr_view dy2, ubr_view dres,
+                             float* dgamma2, float* dbeta2, float* dgammar, float* dbetar, int accumulate,
+                             void* stream);
+
+/* ---- MaxPool2d(3, stride 2, pad 1) (ub_uresnet.py:44,97) and pointwise sums ---------------------- */
+int ubr_maxpool3s2_fwd(ubr_view x, ubr_view y, void* stream);
+int ubr_maxpool3s2_bwd(ubr_view x, ubr_view dy, ubr_view dx_accum, int accumulate, void* stream);
+/* out = a + b (+ c); b/c may have ptr == NULL */
+int ubr_add(ubr_view a, ubr_view b, ubr_view c, ubr_view out, void* stream);
+
+/* ---- LogSoftmax(dim=1) + PixelWiseNLLLoss (ub_uresnet.py:70,143; pixelwise_nllloss.py:41-61) ----
+ * logits: fp32 [pixel][ld] (first ncls columns).  logp: fp32 NCHW [n,ncls,h,w] (the model output). */
+int ubr_logsoftmax_fwd(const float* logits, int ld, int n, int ncls, int hw, float* logp, void* stream);
+/* dlogits (bf16 view, c >= ncls; pad channels zeroed) = dlogp - softmax * sum_k dlogp_k */
+int ubr_logsoftmax_bwd(const float* logp, const float* dlogp, int n, int ncls, int hw, ubr_view dlogits, void* stream);
+/* loss = mean_{pixels}( pw * cw[t] * -logp[t] ), t == ignore_index contributes 0 (stays in the mean) */
+uint64_t ubr_nll_workspace_bytes(int n, int hw);
+int ubr_pixelwise_nll_fwd(const float* logp, const int64_t* target, const float* pixw, const float* classw,
+                          int n, int ncls, int hw, int64_t ignore_index, void* workspace, float* loss, void* stream);
+/* dlogp[n,t,hw] = -gout * pw*cw[t]/(n*hw) at the target class, 0 elsewhere; gout read from device */
+int ubr_pixelwise_nll_bwd(const int64_t* target, const float* pixw, const float* classw, const float* gout,
+                          int n, int ncls, int hw, int64_t ignore_index, float* dlogp, void* stream);
+
+/* ---- whole-view tiling (deploy/run_ubresnet_wholeview.py:238-239; larcv Image2D.cxx:362-367) ------
+ * origins: int32 [ntiles][2] (row0, col0) on the device.
+ * gather : crops[t,0,:,:] = plane[row0:row0+crop, col0:col0+crop]
+ * scatter: out[:, r, c] = value from the HIGHEST-index tile covering (r,c)  (== sequential overwrite) */
+int ubr_tile_gather(const float* plane, int rows, int cols, const int32_t* origins, int ntiles, int crop,
+                    float* crops, void* stream);
+int ubr_stitch_scatter(const float* tiles /* [ntiles,c,crop,crop] */, int nch, const int32_t* origins, int ntiles,
+                       int crop, int rows, int cols, float* out /* [c,rows,cols] */, void* stream);
+
+/* ---- flat-buffer helpers for the data-parallel gradient buckets --------------------------------- */
+int ubr_scale_f32(float* buf, uint64_t count, float alpha, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,90 @@
+"""ctypes binding of libubresnet_b200.so (the C ABI in include/ubresnet_b200.h).
+
+The library is the ONLY compute path: if it is missing or the device is not a B200 every op raises.
+"""
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIBPATH = os.path.join(_HERE, "lib", "libubresnet_b200.so")
+
+
+class View(C.Structure):
+    """ubr_view: NHWC bf16 channel slice."""
+    _fields_ = [("ptr", C.c_void_p), ("n", C.c_int32), ("h", C.c_int32), ("w", C.c_int32), ("c", C.c_int32),
+                ("ld", C.c_int32)]
+
+
+_vp, _i, _u64, _i64, _f, _d = C.c_void_p, C.c_int, C.c_uint64, C.c_int64, C.c_float, C.c_double
+
+# name -> (restype, argtypes).  Mirrors include/ubresnet_b200.h one to one.
+SIGNATURES = {
+    "ubr_abi_version": (_i, []),
+    "ubr_last_error": (C.c_char_p, []),
+    "ubr_device_check": (_i, []),
+    "ubr_sync_check": (_i, [_vp]),
+    "ubr_pack_weights": (_i, [_vp, _i, _i, _i, _i, _i, _i, _i, _i, _vp, _vp]),
+    "ubr_conv2d_fwd": (_i, [View, _vp, _vp, _i, _i, _i, View, _vp, _i, _vp]),
+    "ubr_conv2d_dgrad": (_i, [View, _vp, _i, _i, _i, View, _vp]),
+    "ubr_conv2d_wgrad": (_i, [View, View, _i, _i, _i, _vp, _i, _vp, _u64, _vp]),
+    "ubr_wgrad_workspace_bytes": (_u64, [_i, _i, _i, _i, _i, _i]),
+    "ubr_deconv4s2_fwd": (_i, [View, _vp, _i, View, _vp]),
+    "ubr_deconv4s2_dgrad": (_i, [View, _vp, _i, View, _vp]),
+    "ubr_deconv4s2_wgrad": (_i, [View, View, _vp, _i, _vp, _u64, _vp]),
+    "ubr_stem_conv_fwd": (_i, [_vp, _i, _i, _i, _vp, _vp, _i, View, _vp]),
+    "ubr_stem_conv_wgrad": (_i, [_vp, _i, _i, _i, View, _vp, _vp, _i, _vp, _u64, _vp]),
+    "ubr_stem_wgrad_workspace_bytes": (_u64, [_i, _i, _i, _i]),
+    "ubr_bn_workspace_bytes": (_u64, [_i]),
+    "ubr_bn_stats": (_i, [View, _vp, _vp]),
+    "ubr_bn_finalize": (_i, [_vp, _i, _d, _vp, _vp, _vp, _vp, _f, _f, _vp, _vp, _vp, _vp, _vp]),
+    "ubr_bn_eval_affine": (_i, [_i, _vp, _vp, _vp, _vp, _f, _vp, _vp, _vp]),
+    "ubr_bn_act": (_i, [View, _vp, _vp, _i, View, _vp]),
+    "ubr_block_tail": (_i, [View, _vp, _vp, View, _vp, _vp, View, _vp]),
+    "ubr_bn_act_bwd_reduce": (_i, [View, View, _vp, _vp, _vp, _vp, _i, _vp, _vp]),
+    "ubr_bn_act_bwd_apply": (_i, [View, View, _vp, _vp, _vp, _vp, _vp, _i, _vp, _d, View, _vp, _vp, _i, _vp]),
+    "ubr_block_tail_bwd_reduce": (_i, [View, View, View, _vp, _vp, _vp, _vp, View, _vp, _vp, _i, _vp, _vp]),
+    "ubr_block_tail_bwd_apply": (_i, [View, View, View, _vp, _vp, _vp, _vp, _vp, View, _vp, _vp, _vp, _i, _vp, _d,
+                                      View, View, _vp, _vp, _vp, _vp, _i, _vp]),
+    "ubr_maxpool3s2_fwd": (_i, [View, View, _vp]),
+    "ubr_maxpool3s2_bwd": (_i, [View, View, View, _i, _vp]),
+    "ubr_add": (_i, [View, View, View, View, _vp]),
+    "ubr_logsoftmax_fwd": (_i, [_vp, _i, _i, _i, _i, _vp, _vp]),
+    "ubr_logsoftmax_bwd": (_i, [_vp, _vp, _i, _i, _i, View, _vp]),
+    "ubr_nll_workspace_bytes": (_u64, [_i, _i]),
+    "ubr_pixelwise_nll_fwd": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i64, _vp, _vp, _vp]),
+    "ubr_pixelwise_nll_bwd": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i64, _vp, _vp]),
+    "ubr_tile_gather": (_i, [_vp, _i, _i, _vp, _i, _i, _vp, _vp]),
+    "ubr_stitch_scatter": (_i, [_vp, _i, _vp, _i, _i, _i, _i, _vp, _vp]),
+    "ubr_scale_f32": (_i, [_vp, _u64, _f, _vp]),
+}
+
+_lib = None
+
+
+def load():
+    """dlopen the in-tree library; raises (never falls back) when it is absent."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.isfile(LIBPATH):
+        raise RuntimeError(
+            "ubresnet_b200: %s is missing -- run `python -c 'import __graft_entry__ as g; g.build()'` "
+            "(there is no CPU/PyTorch fallback)" % LIBPATH)
+    lib = C.CDLL(LIBPATH)
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(lib, name)          # AttributeError if the symbol is not exported
+        fn.restype = res
+        fn.argtypes = args
+    if lib.ubr_abi_version() != 1:
+        raise RuntimeError("ubresnet_b200: ABI version mismatch")
+    _lib = lib
+    return lib
+
+
+def last_error():
+    return load().ubr_last_error().decode("utf-8", "replace")
+
+
+def check(rc, what):
+    if rc != 0:
+        raise RuntimeError("ubresnet_b200.%s failed (%d): %s" % (what, rc, last_error()))

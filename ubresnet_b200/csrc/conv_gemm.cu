@@ -1,0 +1,489 @@
+// Implicit-GEMM "gather" convolution on tcgen05 tensor cores (sm_100a).
+//
+//   out[pixel, co] = sum_{tap} sum_{ci} A_view[tap.map][pixel + (tap.dh, tap.dw), ci] * Wpk[tap.slab][co][ci]
+//
+// One kernel covers every dense contraction of the forward and data-gradient passes:
+//   conv kxk stride 1 fwd/dgrad   : 1 input view, k*k taps
+//   conv kxk stride 2 fwd         : 4 parity views of the input (strided TMA maps), k*k taps
+//   conv kxk stride 2 dgrad       : 4 launches, one per output parity phase (strided TMA store map)
+//   ConvTranspose 4x4 s2 fwd      : 4 launches (sub-pixel phases, 2x2 taps each)
+//   ConvTranspose 4x4 s2 dgrad    : == 4x4 stride-2 conv of dy
+//
+// Structure (one 128-pixel x NT-channel output tile per CTA, several CTAs resident per SM):
+//   warp 0    : TMA producer.  A tile = box {KC ch, bw, bh, bn} of the NHWC activation at the tap's
+//               shifted coordinates (TMA zero-fills the halo => conv padding for free); B tile = weight slab.
+//   warp 1    : TMEM allocator + single-thread tcgen05.mma issuer (K-major A and B, fp32 accum in TMEM).
+//   warps 2-5 : epilogue.  tcgen05.ld -> (+bias) -> bf16 -> swizzled smem staging -> TMA store
+//               (channel-slice / parity-phase aware through the tensor map), or fp32 direct store (logits).
+#include "common.cuh"
+
+namespace ubr {
+
+constexpr int kMaxTaps = 49;
+constexpr int kThreads = 192;
+
+struct ConvGemmParams {
+  CUtensorMap a_map[4];
+  CUtensorMap b_map;
+  CUtensorMap o_map;
+  int ntaps, nkc, kc, nt, stages;
+  int tiles_w, tiles_h, bw, bh, bn;
+  uint32_t a_bytes, b_bytes, a_stride, b_stride;
+  uint32_t idesc, tmem_cols;
+  int out_mode;                 // 0: bf16 via TMA store, 1: fp32 direct (first out_cols columns)
+  int o_box_c;                  // channels per TMA store box
+  const float* bias;
+  float* out_f32;
+  int out_ld, out_cols, out_n, out_h, out_w;
+  int8_t dh[kMaxTaps], dw[kMaxTaps];
+  uint8_t amap[kMaxTaps], slab[kMaxTaps];
+};
+
+__global__ void __launch_bounds__(kThreads, 1) conv_gemm_kernel(const __grid_constant__ ConvGemmParams p) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  // dynamic smem base is not guaranteed 1024-aligned: align by hand (host adds 1024 slack)
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t stage_bytes = p.a_stride + p.b_stride;
+  const uint32_t staging_bytes = 128u * (uint32_t)p.nt * 2u;
+  uint32_t data_bytes = (uint32_t)p.stages * stage_bytes;
+  if (data_bytes < staging_bytes) data_bytes = staging_bytes;
+  const uint32_t bar_base = smem_base + data_bytes;        // full[stages], empty[stages], accum, tmem ptr
+  const uint32_t full0 = bar_base;
+  const uint32_t empty0 = bar_base + 8u * p.stages;
+  const uint32_t accum_bar = bar_base + 16u * p.stages;
+  const uint32_t tmem_slot = accum_bar + 8u;
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  // tile coordinates
+  const int tile = blockIdx.x;
+  const int tw = tile % p.tiles_w;
+  const int th = (tile / p.tiles_w) % p.tiles_h;
+  const int tn = tile / (p.tiles_w * p.tiles_h);
+  const int w0 = tw * p.bw, h0 = th * p.bh, n0 = tn * p.bn;
+  const int co0 = blockIdx.y * p.nt;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < p.stages; ++s) {
+      mbar_init(full0 + 8u * s, 1);
+      mbar_init(empty0 + 8u * s, 1);
+    }
+    mbar_init(accum_bar, 1);
+    fence_mbar_init();
+    prefetch_tmap(&p.a_map[0]);
+    prefetch_tmap(&p.b_map);
+    if (p.out_mode == 0) prefetch_tmap(&p.o_map);
+  }
+  if (warp == 1) {
+    tmem_alloc_dyn(tmem_slot, p.tmem_cols);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  uint32_t tmem_base;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
+
+  const int total_iters = p.ntaps * p.nkc;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      // ================= TMA producer =================
+      int it = 0;
+      for (int t = 0; t < p.ntaps; ++t) {
+        const CUtensorMap* am = &p.a_map[p.amap[t]];
+        const int cw = w0 + p.dw[t], ch = h0 + p.dh[t];
+        for (int kc = 0; kc < p.nkc; ++kc, ++it) {
+          const int s = it % p.stages;
+          const uint32_t ph = (uint32_t)(it / p.stages) & 1u;
+          mbar_wait(empty0 + 8u * s, ph ^ 1u);
+          const uint32_t a_dst = smem_base + (uint32_t)s * stage_bytes;
+          const uint32_t b_dst = a_dst + p.a_stride;
+          mbar_arrive_expect_tx(full0 + 8u * s, p.a_bytes + p.b_bytes);
+          tma_load_4d(a_dst, am, full0 + 8u * s, kc * p.kc, cw, ch, n0);
+          tma_load_3d(b_dst, &p.b_map, full0 + 8u * s, kc * p.kc, co0, (int)p.slab[t]);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      // ================= MMA issuer =================
+      const uint32_t row_bytes = (uint32_t)p.kc * 2u;
+      const uint32_t layout = swizzle_layout_code((int)row_bytes);
+      const uint32_t sbo = 8u * row_bytes;
+      const int ksteps = p.kc / 16;
+      for (int it = 0; it < total_iters; ++it) {
+        const int s = it % p.stages;
+        const uint32_t ph = (uint32_t)(it / p.stages) & 1u;
+        mbar_wait(full0 + 8u * s, ph);
+        tc_fence_after();
+        const uint32_t a_src = smem_base + (uint32_t)s * stage_bytes;
+        const uint32_t b_src = a_src + p.a_stride;
+        const uint64_t adesc = make_smem_desc(a_src, 0, sbo, layout);
+        const uint64_t bdesc = make_smem_desc(b_src, 0, sbo, layout);
+        for (int k = 0; k < ksteps; ++k) {
+          // advance 16 bf16 = 32 bytes along K inside the swizzle row: +2 in the (addr>>4) field
+          tc_mma_bf16(tmem_base, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), p.idesc,
+                      (it > 0 || k > 0) ? 1u : 0u);
+        }
+        tc_commit(empty0 + 8u * s);          // frees the smem stage when these MMAs retire
+      }
+      tc_commit(accum_bar);                  // accumulator complete
+    }
+  } else {
+    // ================= epilogue (warps 2..5) =================
+    const int quad = warp & 3;               // TMEM lane quadrant this warp may access
+    const int row = quad * 32 + lane;        // tile-local pixel
+    mbar_wait(accum_bar, 0);
+    tc_fence_after();
+    const uint32_t t_row = tmem_base + ((uint32_t)(quad * 32) << 16);
+    if (p.out_mode == 0) {
+      const int bc = p.o_box_c;                         // channels per staging block
+      const uint32_t rb = (uint32_t)bc * 2u;            // staging row bytes (32/64/128)
+      const uint32_t xr = rb == 128 ? (uint32_t)(row & 7) : (rb == 64 ? (uint32_t)((row >> 1) & 3)
+                                                                       : (uint32_t)((row >> 2) & 1));
+      for (int c = 0; c < p.nt; c += 16) {
+        uint32_t v[16];
+        tmem_ld16(t_row + (uint32_t)c, v);
+        tmem_ld_wait();
+        float f[16];
+#pragma unroll
+        for (int j = 0; j < 16; ++j) f[j] = __uint_as_float(v[j]);
+        if (p.bias) {
+#pragma unroll
+          for (int j = 0; j < 16; ++j) f[j] += __ldg(p.bias + co0 + c + j);
+        }
+        uint32_t pk[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) pk[j] = pack_bf16x2(f[2 * j], f[2 * j + 1]);
+        const int blk = c / bc;
+        const uint32_t q = (uint32_t)((c % bc) >> 3);   // 16-byte chunk index inside the row
+        const uint32_t base = smem_base + (uint32_t)blk * 128u * rb + (uint32_t)row * rb;
+        const uint32_t a0 = base + ((q ^ xr) << 4);
+        const uint32_t a1 = base + (((q + 1u) ^ xr) << 4);
+        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a0), "r"(pk[0]), "r"(pk[1]), "r"(pk[2]), "r"(pk[3]) : "memory");
+        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a1), "r"(pk[4]), "r"(pk[5]), "r"(pk[6]), "r"(pk[7]) : "memory");
+      }
+      fence_proxy_async_smem();
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      if (warp == 2 && lane == 0) {
+        const int nblk = p.nt / bc;
+        for (int b = 0; b < nblk; ++b)
+          tma_store_4d(&p.o_map, smem_base + (uint32_t)b * 128u * rb, co0 + b * bc, w0, h0, n0);
+        tma_store_commit();
+        tma_store_wait_all();
+      }
+    } else {
+      // fp32 direct store (network logits): few valid columns, pixel-major rows
+      const int mw = row % p.bw, mh = (row / p.bw) % p.bh, mn = row / (p.bw * p.bh);
+      const int pw_ = w0 + mw, ph_ = h0 + mh, pn_ = n0 + mn;
+      const bool valid = pw_ < p.out_w && ph_ < p.out_h && pn_ < p.out_n;
+      float* dst = p.out_f32 + ((size_t)((size_t)pn_ * p.out_h + ph_) * p.out_w + pw_) * (size_t)p.out_ld;
+      for (int c = 0; c < p.nt; c += 16) {
+        uint32_t v[16];
+        tmem_ld16(t_row + (uint32_t)c, v);
+        tmem_ld_wait();
+        if (valid) {
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {
+            const int col = co0 + c + j;
+            if (col < p.out_cols) dst[col] = __uint_as_float(v[j]) + (p.bias ? __ldg(p.bias + col) : 0.f);
+          }
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    __syncwarp();
+    tc_fence_after();
+    tmem_dealloc_dyn(tmem_base, p.tmem_cols);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// host side
+// ------------------------------------------------------------------------------------------------
+struct TileShape { int bw, bh, bn; };
+
+static TileShape pick_tile(int n, int h, int w) {
+  // 128 pixels per tile = bw x bh x bn (powers of two); maximise useful fraction, prefer wide rows
+  TileShape best{128, 1, 1};
+  double best_eff = -1.0;
+  for (int bw = 128; bw >= 1; bw >>= 1) {
+    for (int bh = 128 / bw; bh >= 1; bh >>= 1) {
+      const int bn = 128 / (bw * bh);
+      const double eff = ((double)w / (ceil_div(w, bw) * bw)) * ((double)h / (ceil_div(h, bh) * bh)) *
+                         ((double)n / (ceil_div(n, bn) * bn));
+      // prefer larger bw, then larger bh (fewer images per tile) on ties
+      if (eff > best_eff + 1e-9) { best_eff = eff; best = TileShape{bw, bh, bn}; }
+    }
+  }
+  return best;
+}
+
+static int check_view(const ubr_view& v, const char* name) {
+  UBR_REQUIRE(v.ptr != nullptr, "%s: null pointer", name);
+  UBR_REQUIRE(v.n > 0 && v.h > 0 && v.w > 0 && v.c > 0, "%s: bad extents n=%d h=%d w=%d c=%d", name, v.n, v.h, v.w, v.c);
+  UBR_REQUIRE(v.ld >= v.c && (v.ld % 8) == 0, "%s: ld=%d must be >= c=%d and a multiple of 8", name, v.ld, v.c);
+  UBR_REQUIRE(((uintptr_t)v.ptr & 15) == 0, "%s: pointer must be 16-byte aligned", name);
+  return 0;
+}
+
+// plain NHWC map (C, W, H, N) over a view, box {box_c, bw, bh, bn}
+static int make_act_map(CUtensorMap* m, const ubr_view& v, int box_c, TileShape t) {
+  uint64_t dims[4] = {(uint64_t)v.c, (uint64_t)v.w, (uint64_t)v.h, (uint64_t)v.n};
+  uint64_t str[4] = {2, (uint64_t)v.ld * 2, (uint64_t)v.w * v.ld * 2, (uint64_t)v.h * v.w * v.ld * 2};
+  uint32_t box[4] = {(uint32_t)box_c, (uint32_t)t.bw, (uint32_t)t.bh, (uint32_t)t.bn};
+  return make_tmap_bf16(m, v.ptr, 4, dims, str, box, box_c * 2);
+}
+// parity-phase map: pixels (2i+ph, 2j+pw) of the view, as a (C, W/2, H/2, N) tensor
+static int make_phase_map(CUtensorMap* m, const ubr_view& v, int ph, int pw, int box_c, TileShape t) {
+  uint64_t dims[4] = {(uint64_t)v.c, (uint64_t)(v.w / 2), (uint64_t)(v.h / 2), (uint64_t)v.n};
+  uint64_t str[4] = {2, (uint64_t)v.ld * 4, (uint64_t)v.w * v.ld * 4, (uint64_t)v.h * v.w * v.ld * 2};
+  uint32_t box[4] = {(uint32_t)box_c, (uint32_t)t.bw, (uint32_t)t.bh, (uint32_t)t.bn};
+  const uint8_t* base = (const uint8_t*)v.ptr + ((size_t)ph * v.w + pw) * (size_t)v.ld * 2;
+  return make_tmap_bf16(m, base, 4, dims, str, box, box_c * 2);
+}
+
+struct TapSpec { int dh, dw, amap, slab; };
+
+// generic launcher. `grid_view` = (n, h, w) of the output tile grid; a_maps built by caller.
+static int launch_conv_gemm(ConvGemmParams& p, int grid_n, int grid_h, int grid_w, TileShape t, int k_ch,
+                            int n_pad, const void* wpk, int nslabs, const TapSpec* taps, int ntaps,
+                            cudaStream_t stream) {
+  UBR_REQUIRE(ntaps >= 1 && ntaps <= kMaxTaps, "conv_gemm: ntaps=%d out of range", ntaps);
+  UBR_REQUIRE(k_ch % 16 == 0 && n_pad % 16 == 0, "conv_gemm: channels must be multiples of 16 (k=%d n=%d)", k_ch, n_pad);
+  p.kc = k_ch >= 64 ? 64 : k_ch;
+  UBR_REQUIRE(p.kc == 16 || p.kc == 32 || p.kc == 64, "conv_gemm: unsupported K chunk %d", p.kc);
+  UBR_REQUIRE(k_ch % p.kc == 0, "conv_gemm: K=%d not a multiple of chunk %d", k_ch, p.kc);
+  p.nkc = k_ch / p.kc;
+  p.nt = n_pad >= 128 ? 128 : n_pad;
+  UBR_REQUIRE(n_pad % p.nt == 0, "conv_gemm: N=%d not a multiple of tile %d", n_pad, p.nt);
+  p.ntaps = ntaps;
+  for (int i = 0; i < ntaps; ++i) {
+    p.dh[i] = (int8_t)taps[i].dh; p.dw[i] = (int8_t)taps[i].dw;
+    p.amap[i] = (uint8_t)taps[i].amap; p.slab[i] = (uint8_t)taps[i].slab;
+  }
+  p.bw = t.bw; p.bh = t.bh; p.bn = t.bn;
+  p.tiles_w = ceil_div(grid_w, t.bw);
+  p.tiles_h = ceil_div(grid_h, t.bh);
+  const int tiles_n = ceil_div(grid_n, t.bn);
+  p.a_bytes = 128u * p.kc * 2u;
+  p.b_bytes = (uint32_t)p.nt * p.kc * 2u;
+  p.a_stride = (p.a_bytes + 1023u) & ~1023u;
+  p.b_stride = (p.b_bytes + 1023u) & ~1023u;
+  const uint32_t stage = p.a_stride + p.b_stride;
+  int stages = (int)(98304u / stage);
+  if (stages > 8) stages = 8;
+  if (stages < 2) stages = 2;
+  if (stages > ntaps * p.nkc) stages = ntaps * p.nkc;
+  p.stages = stages;
+  p.idesc = make_idesc_bf16(128, p.nt, 0, 0);
+  uint32_t cols = 32;
+  while ((int)cols < p.nt) cols <<= 1;
+  p.tmem_cols = cols;
+  // weights: (K, N, slab) 3-D map, box {kc, nt, 1}
+  {
+    uint64_t dims[3] = {(uint64_t)k_ch, (uint64_t)n_pad, (uint64_t)nslabs};
+    uint64_t str[3] = {2, (uint64_t)k_ch * 2, (uint64_t)k_ch * n_pad * 2};
+    uint32_t box[3] = {(uint32_t)p.kc, (uint32_t)p.nt, 1};
+    int rc = make_tmap_bf16(&p.b_map, wpk, 3, dims, str, box, p.kc * 2);
+    if (rc) return rc;
+  }
+  uint32_t data = (uint32_t)stages * stage;
+  const uint32_t staging = 128u * p.nt * 2u;
+  if (data < staging) data = staging;
+  const uint32_t smem = data + 16u * stages + 16u + 1024u;
+  static bool attr_set = false;
+  if (!attr_set) {
+    UBR_CUDA_OK(cudaFuncSetAttribute(conv_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    attr_set = true;
+  }
+  dim3 grid((unsigned)(p.tiles_w * p.tiles_h * tiles_n), (unsigned)(n_pad / p.nt), 1);
+  conv_gemm_kernel<<<grid, kThreads, smem, stream>>>(p);
+  UBR_LAUNCH_CHECK("conv_gemm_kernel");
+  return 0;
+}
+
+static int out_box_c(int nt) { return nt >= 64 ? 64 : nt; }
+
+}  // namespace ubr
+
+using namespace ubr;
+
+extern "C" {
+
+int ubr_conv2d_fwd(ubr_view x, const void* wpk, const float* bias, int out_ch, int ksize, int stride, ubr_view y,
+                   float* y_f32, int y_f32_ld, void* stream) {
+  if (int rc = ensure_device()) return rc;
+  if (int rc = check_view(x, "conv2d_fwd.x")) return rc;
+  UBR_REQUIRE(ksize == 1 || ksize == 3 || ksize == 7, "conv2d_fwd: ksize %d unsupported", ksize);
+  UBR_REQUIRE(stride == 1 || stride == 2, "conv2d_fwd: stride %d unsupported", stride);
+  UBR_REQUIRE(x.c % 16 == 0, "conv2d_fwd: in_ch=%d must be a multiple of 16", x.c);
+  UBR_REQUIRE(wpk != nullptr, "conv2d_fwd: null weights");
+  const int pad = (ksize - 1) / 2;
+  const int n_pad = (out_ch + 15) / 16 * 16;
+  int ho, wo;
+  if (stride == 1) { ho = x.h; wo = x.w; }
+  else {
+    UBR_REQUIRE(x.h % 2 == 0 && x.w % 2 == 0, "conv2d_fwd: stride 2 needs even H,W (got %dx%d)", x.h, x.w);
+    ho = x.h / 2; wo = x.w / 2;
+  }
+  ConvGemmParams p;
+  memset(&p, 0, sizeof(p));
+  TileShape t = pick_tile(x.n, ho, wo);
+  const int kc = x.c >= 64 ? 64 : x.c;
+  TapSpec taps[kMaxTaps];
+  int nt = 0;
+  if (stride == 1) {
+    if (int rc = make_act_map(&p.a_map[0], x, kc, t)) return rc;
+    for (int r = 0; r < ksize; ++r)
+      for (int s = 0; s < ksize; ++s) taps[nt++] = TapSpec{r - pad, s - pad, 0, r * ksize + s};
+  } else {
+    for (int ph = 0; ph < 2; ++ph)
+      for (int pw = 0; pw < 2; ++pw)
+        if (int rc = make_phase_map(&p.a_map[ph * 2 + pw], x, ph, pw, kc, t)) return rc;
+    for (int r = 0; r < ksize; ++r)
+      for (int s = 0; s < ksize; ++s) {
+        const int oh = r - pad, ow = s - pad;                 // input row = 2*ho + oh
+        const int ph = oh & 1, pw = ow & 1;                   // parity (two's complement & works for -1)
+        const int dh = (oh - ph) / 2, dw = (ow - pw) / 2;     // floor division
+        taps[nt++] = TapSpec{dh, dw, ph * 2 + pw, r * ksize + s};
+      }
+  }
+  p.bias = bias;
+  if (y_f32) {
+    p.out_mode = 1; p.out_f32 = y_f32; p.out_ld = y_f32_ld; p.out_cols = out_ch;
+    p.out_n = x.n; p.out_h = ho; p.out_w = wo;
+    UBR_REQUIRE(y_f32_ld >= out_ch, "conv2d_fwd: y_f32_ld too small");
+  } else {
+    if (int rc = check_view(y, "conv2d_fwd.y")) return rc;
+    UBR_REQUIRE(y.n == x.n && y.h == ho && y.w == wo && y.c == out_ch, "conv2d_fwd: output view mismatch");
+    UBR_REQUIRE(out_ch % 16 == 0, "conv2d_fwd: bf16 output needs out_ch %% 16 == 0");
+    p.out_mode = 0;
+    p.o_box_c = out_box_c(n_pad >= 128 ? 128 : n_pad);
+    if (int rc = make_act_map(&p.o_map, y, p.o_box_c, t)) return rc;
+  }
+  return launch_conv_gemm(p, x.n, ho, wo, t, x.c, n_pad, wpk, ksize * ksize, taps, nt, (cudaStream_t)stream);
+}
+
+int ubr_conv2d_dgrad(ubr_view dy, const void* wpk, int in_ch, int ksize, int stride, ubr_view dx, void* stream) {
+  if (int rc = ensure_device()) return rc;
+  if (int rc = check_view(dy, "conv2d_dgrad.dy")) return rc;
+  if (int rc = check_view(dx, "conv2d_dgrad.dx")) return rc;
+  UBR_REQUIRE(ksize == 1 || ksize == 3 || ksize == 7, "conv2d_dgrad: ksize %d unsupported", ksize);
+  UBR_REQUIRE(stride == 1 || stride == 2, "conv2d_dgrad: stride %d unsupported", stride);
+  UBR_REQUIRE(dy.c % 16 == 0 && in_ch % 16 == 0, "conv2d_dgrad: channels must be multiples of 16");
+  UBR_REQUIRE(dx.c == in_ch && dx.n == dy.n && dx.h == dy.h * stride && dx.w == dy.w * stride,
+              "conv2d_dgrad: dx view mismatch");
+  const int pad = (ksize - 1) / 2;
+  const int kc = dy.c >= 64 ? 64 : dy.c;
+  TileShape t = pick_tile(dy.n, dy.h, dy.w);
+  if (stride == 1) {
+    ConvGemmParams p;
+    memset(&p, 0, sizeof(p));
+    if (int rc = make_act_map(&p.a_map[0], dy, kc, t)) return rc;
+    TapSpec taps[kMaxTaps];
+    int nt = 0;
+    // dx[p] = sum_{r,s} dy[p - (r-pad, s-pad)] * W[:, :, r, s]
+    for (int r = 0; r < ksize; ++r)
+      for (int s = 0; s < ksize; ++s) taps[nt++] = TapSpec{pad - r, pad - s, 0, r * ksize + s};
+    p.out_mode = 0;
+    p.o_box_c = out_box_c(in_ch >= 128 ? 128 : in_ch);
+    if (int rc = make_act_map(&p.o_map, dx, p.o_box_c, t)) return rc;
+    return launch_conv_gemm(p, dy.n, dy.h, dy.w, t, dy.c, in_ch, wpk, ksize * ksize, taps, nt, (cudaStream_t)stream);
+  }
+  // stride 2: input row x = 2*o + r - pad.  For output parity (ph,pw) only taps with (r-pad)&1 == ph contribute,
+  // from dy row o = (x - (r-pad))/2 = i + (ph - (r-pad))/2.
+  for (int ph = 0; ph < 2; ++ph)
+    for (int pw = 0; pw < 2; ++pw) {
+      ConvGemmParams p;
+      memset(&p, 0, sizeof(p));
+      if (int rc = make_act_map(&p.a_map[0], dy, kc, t)) return rc;
+      TapSpec taps[kMaxTaps];
+      int nt = 0;
+      for (int r = 0; r < ksize; ++r)
+        for (int s = 0; s < ksize; ++s) {
+          const int oh = r - pad, ow = s - pad;
+          if ((oh & 1) != ph || (ow & 1) != pw) continue;
+          taps[nt++] = TapSpec{(ph - oh) / 2, (pw - ow) / 2, 0, r * ksize + s};
+        }
+      p.out_mode = 0;
+      p.o_box_c = out_box_c(in_ch >= 128 ? 128 : in_ch);
+      if (int rc = make_phase_map(&p.o_map, dx, ph, pw, p.o_box_c, t)) return rc;
+      if (nt == 0) {
+        // no tap reaches this phase (1x1 stride 2, odd pixels): gradient is zero there.
+        // Handled by a zero weight slab: use tap 0 with slab index == ksize*ksize (caller packs +1 zero slab)
+        taps[nt++] = TapSpec{0, 0, 0, ksize * ksize};
+      }
+      if (int rc = launch_conv_gemm(p, dy.n, dy.h, dy.w, t, dy.c, in_ch, wpk, ksize * ksize + 1, taps, nt,
+                                    (cudaStream_t)stream))
+        return rc;
+    }
+  return 0;
+}
+
+int ubr_deconv4s2_fwd(ubr_view x, const void* wpk, int out_ch, ubr_view y, void* stream) {
+  if (int rc = ensure_device()) return rc;
+  if (int rc = check_view(x, "deconv_fwd.x")) return rc;
+  if (int rc = check_view(y, "deconv_fwd.y")) return rc;
+  UBR_REQUIRE(x.c % 16 == 0 && out_ch % 16 == 0, "deconv_fwd: channels must be multiples of 16");
+  UBR_REQUIRE(y.c == out_ch && y.n == x.n && y.h == 2 * x.h && y.w == 2 * x.w, "deconv_fwd: output view mismatch");
+  const int kc = x.c >= 64 ? 64 : x.c;
+  TileShape t = pick_tile(x.n, x.h, x.w);
+  // out row o = 2*i - 1 + kh  =>  for o = 2*j + ph: i = j + (ph + 1 - kh)/2, kh == (ph+1) mod 2
+  for (int ph = 0; ph < 2; ++ph)
+    for (int pw = 0; pw < 2; ++pw) {
+      ConvGemmParams p;
+      memset(&p, 0, sizeof(p));
+      if (int rc = make_act_map(&p.a_map[0], x, kc, t)) return rc;
+      TapSpec taps[4];
+      int nt = 0;
+      for (int kh = 0; kh < 4; ++kh)
+        for (int kw = 0; kw < 4; ++kw) {
+          if (((ph + 1 - kh) & 1) || ((pw + 1 - kw) & 1)) continue;
+          taps[nt++] = TapSpec{(ph + 1 - kh) / 2, (pw + 1 - kw) / 2, 0, kh * 4 + kw};
+        }
+      p.out_mode = 0;
+      p.o_box_c = out_box_c(out_ch >= 128 ? 128 : out_ch);
+      if (int rc = make_phase_map(&p.o_map, y, ph, pw, p.o_box_c, t)) return rc;
+      if (int rc = launch_conv_gemm(p, x.n, x.h, x.w, t, x.c, out_ch, wpk, 16, taps, nt, (cudaStream_t)stream))
+        return rc;
+    }
+  return 0;
+}
+
+int ubr_deconv4s2_dgrad(ubr_view dy, const void* wpk, int in_ch, ubr_view dx, void* stream) {
+  if (int rc = ensure_device()) return rc;
+  if (int rc = check_view(dy, "deconv_dgrad.dy")) return rc;
+  if (int rc = check_view(dx, "deconv_dgrad.dx")) return rc;
+  UBR_REQUIRE(dy.c % 16 == 0 && in_ch % 16 == 0, "deconv_dgrad: channels must be multiples of 16");
+  UBR_REQUIRE(dy.h % 2 == 0 && dy.w % 2 == 0, "deconv_dgrad: dy must have even H,W");
+  UBR_REQUIRE(dx.c == in_ch && dx.n == dy.n && dx.h * 2 == dy.h && dx.w * 2 == dy.w, "deconv_dgrad: dx view mismatch");
+  // dx[i] = sum_{kh,kw} dy[2*i - 1 + kh] * W[ci, co, kh, kw]   -> a 4x4 stride-2 pad-1 conv of dy
+  const int kc = dy.c >= 64 ? 64 : dy.c;
+  TileShape t = pick_tile(dx.n, dx.h, dx.w);
+  ConvGemmParams p;
+  memset(&p, 0, sizeof(p));
+  for (int ph = 0; ph < 2; ++ph)
+    for (int pw = 0; pw < 2; ++pw)
+      if (int rc = make_phase_map(&p.a_map[ph * 2 + pw], dy, ph, pw, kc, t)) return rc;
+  TapSpec taps[16];
+  int nt = 0;
+  for (int kh = 0; kh < 4; ++kh)
+    for (int kw = 0; kw < 4; ++kw) {
+      const int oh = kh - 1, ow = kw - 1;
+      const int ph = oh & 1, pw = ow & 1;
+      taps[nt++] = TapSpec{(oh - ph) / 2, (ow - pw) / 2, ph * 2 + pw, kh * 4 + kw};
+    }
+  p.out_mode = 0;
+  p.o_box_c = out_box_c(in_ch >= 128 ? 128 : in_ch);
+  if (int rc = make_act_map(&p.o_map, dx, p.o_box_c, t)) return rc;
+  return launch_conv_gemm(p, dx.n, dx.h, dx.w, t, dy.c, in_ch, wpk, 16, taps, nt, (cudaStream_t)stream);
+}
+
+}  // extern "C"

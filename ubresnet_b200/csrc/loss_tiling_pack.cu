@@ -1,0 +1,267 @@
+// LogSoftmax + PixelWiseNLLLoss (reference models/ub_uresnet.py:70,143; training/pixelwise_nllloss.py:41-61),
+// whole-view tile gather / stitch scatter (deploy/run_ubresnet_wholeview.py:238-239; larcv Image2D.cxx:362-367),
+// and weight packing.  All coalesced, fp32 math, deterministic reductions.
+#include "common.cuh"
+
+namespace ubr {
+
+constexpr int kMaxCls = 16;
+
+// logits [pixel][ld] fp32 -> logp NCHW fp32
+__global__ void __launch_bounds__(256) logsoftmax_fwd_kernel(const float* __restrict__ logits, int ld, int n, int ncls,
+                                                             int hw, float* __restrict__ logp) {
+  const long total = (long)n * hw;
+  for (long p = (long)blockIdx.x * blockDim.x + threadIdx.x; p < total; p += (long)gridDim.x * blockDim.x) {
+    const float* src = logits + p * ld;
+    float v[kMaxCls];
+    float m = -INFINITY;
+    if (ld == 4 && ncls <= 4) {
+      const float4 q = *reinterpret_cast<const float4*>(src);
+      v[0] = q.x; v[1] = q.y; v[2] = q.z; v[3] = q.w;
+    } else {
+      for (int k = 0; k < ncls; ++k) v[k] = src[k];
+    }
+    for (int k = 0; k < ncls; ++k) m = fmaxf(m, v[k]);
+    float s = 0.f;
+    for (int k = 0; k < ncls; ++k) s += expf(v[k] - m);
+    const float lse = m + logf(s);
+    const long b = p / hw, i = p % hw;
+    for (int k = 0; k < ncls; ++k) logp[(b * ncls + k) * hw + i] = v[k] - lse;
+  }
+}
+
+// dlogits[p][k] = dlogp[k] - exp(logp[k]) * sum_j dlogp[j]   (bf16, channels >= ncls zeroed)
+__global__ void __launch_bounds__(256) logsoftmax_bwd_kernel(const float* __restrict__ logp,
+                                                             const float* __restrict__ dlogp, int n, int ncls, int hw,
+                                                             __nv_bfloat16* __restrict__ dl, int dl_c, int dl_ld) {
+  const long total = (long)n * hw;
+  for (long p = (long)blockIdx.x * blockDim.x + threadIdx.x; p < total; p += (long)gridDim.x * blockDim.x) {
+    const long b = p / hw, i = p % hw;
+    float g[kMaxCls], s = 0.f;
+    for (int k = 0; k < ncls; ++k) { g[k] = dlogp[(b * ncls + k) * hw + i]; s += g[k]; }
+    for (int k = 0; k < ncls; ++k) g[k] -= expf(logp[(b * ncls + k) * hw + i]) * s;
+    __nv_bfloat16* dst = dl + p * dl_ld;
+    for (int c0 = 0; c0 < dl_c; c0 += 8) {
+      float f[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) f[j] = (c0 + j < ncls) ? g[c0 + j] : 0.f;
+      uint4 u;
+      u.x = pack_bf16x2(f[0], f[1]); u.y = pack_bf16x2(f[2], f[3]);
+      u.z = pack_bf16x2(f[4], f[5]); u.w = pack_bf16x2(f[6], f[7]);
+      *reinterpret_cast<uint4*>(dst + c0) = u;
+    }
+  }
+}
+
+constexpr int kNllBlocks = 592;
+__global__ void __launch_bounds__(256) nll_fwd_kernel(const float* __restrict__ logp, const long long* __restrict__ target,
+                                                      const float* __restrict__ pixw, const float* __restrict__ classw,
+                                                      int n, int ncls, int hw, long long ignore_index,
+                                                      float* __restrict__ partials) {
+  const long total = (long)n * hw;
+  float acc = 0.f;
+  for (long p = (long)blockIdx.x * blockDim.x + threadIdx.x; p < total; p += (long)gridDim.x * blockDim.x) {
+    const long long t = target[p];
+    if (t != ignore_index && t >= 0 && t < ncls) {
+      const long b = p / hw, i = p % hw;
+      float v = -logp[(b * ncls + t) * hw + i];
+      if (classw) v *= classw[t];
+      acc = fmaf(v, pixw[p], acc);
+    }
+  }
+  __shared__ float red[8];
+  acc = warp_sum(acc);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float s = 0.f;
+    for (int i = 0; i < 8; ++i) s += red[i];
+    partials[blockIdx.x] = s;
+  }
+}
+__global__ void nll_finalize_kernel(const float* partials, int nb, double inv_count, float* loss) {
+  if (threadIdx.x == 0 && blockIdx.x == 0) {
+    double s = 0.0;
+    for (int i = 0; i < nb; ++i) s += (double)partials[i];
+    *loss = (float)(s * inv_count);
+  }
+}
+__global__ void __launch_bounds__(256) nll_bwd_kernel(const long long* __restrict__ target, const float* __restrict__ pixw,
+                                                      const float* __restrict__ classw, const float* __restrict__ gout,
+                                                      int n, int ncls, int hw, long long ignore_index, float inv_count,
+                                                      float* __restrict__ dlogp) {
+  const long total = (long)n * hw;
+  const float go = gout ? *gout : 1.f;
+  for (long p = (long)blockIdx.x * blockDim.x + threadIdx.x; p < total; p += (long)gridDim.x * blockDim.x) {
+    const long long t = target[p];
+    const long b = p / hw, i = p % hw;
+    float g = 0.f;
+    if (t != ignore_index && t >= 0 && t < ncls) g = -go * pixw[p] * (classw ? classw[t] : 1.f) * inv_count;
+    for (int k = 0; k < ncls; ++k) dlogp[(b * ncls + k) * hw + i] = (k == t) ? g : 0.f;
+  }
+}
+
+// ------------------------------------------------------------------ tiling
+__global__ void __launch_bounds__(256) tile_gather_kernel(const float* __restrict__ plane, int rows, int cols,
+                                                          const int* __restrict__ origins, int ntiles, int crop,
+                                                          float* __restrict__ crops) {
+  const long per = (long)crop * crop;
+  const long total = per * ntiles;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+    const int t = (int)(i / per);
+    const int r = (int)((i % per) / crop), c = (int)(i % crop);
+    const int sr = origins[2 * t] + r, sc = origins[2 * t + 1] + c;
+    crops[i] = (sr >= 0 && sr < rows && sc >= 0 && sc < cols) ? plane[(long)sr * cols + sc] : 0.f;
+  }
+}
+// every output pixel takes the value of the highest-index tile that covers it (== sequential overwrite)
+__global__ void __launch_bounds__(256) stitch_scatter_kernel(const float* __restrict__ tiles, int nch,
+                                                             const int* __restrict__ origins, int ntiles, int crop,
+                                                             int rows, int cols, float* __restrict__ out) {
+  const long total = (long)rows * cols;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+    const int r = (int)(i / cols), c = (int)(i % cols);
+    int owner = -1;
+    for (int t = ntiles - 1; t >= 0; --t) {
+      const int r0 = origins[2 * t], c0 = origins[2 * t + 1];
+      if (r >= r0 && r < r0 + crop && c >= c0 && c < c0 + crop) { owner = t; break; }
+    }
+    for (int k = 0; k < nch; ++k) {
+      float v = 0.f;
+      if (owner >= 0) {
+        const int r0 = origins[2 * owner], c0 = origins[2 * owner + 1];
+        v = tiles[(((long)owner * nch + k) * crop + (r - r0)) * crop + (c - c0)];
+      }
+      out[(long)k * total + i] = v;
+    }
+  }
+}
+
+// ------------------------------------------------------------------ weight packing
+// dst[tap][n][k] (bf16, zero padded); one extra all-zero slab at index taps (used by phases no tap reaches)
+__global__ void __launch_bounds__(256) pack_weights_kernel(const float* __restrict__ src, int src_layout, int n_is_out,
+                                                           int out_ch, int in_ch, int kh, int kw, int n_pad, int k_pad,
+                                                           __nv_bfloat16* __restrict__ dst) {
+  const int taps = kh * kw;
+  const long total = (long)(taps + 1) * n_pad * k_pad;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+    const int k = (int)(i % k_pad);
+    const int nn = (int)((i / k_pad) % n_pad);
+    const int t = (int)(i / ((long)k_pad * n_pad));
+    float v = 0.f;
+    if (t < taps) {
+      const int o = n_is_out ? nn : k, ci = n_is_out ? k : nn;
+      if (o < out_ch && ci < in_ch) {
+        const long idx = src_layout == 0 ? (((long)o * in_ch + ci) * taps + t) : (((long)ci * out_ch + o) * taps + t);
+        v = src[idx];
+      }
+    }
+    dst[i] = __float2bfloat16_rn(v);
+  }
+}
+
+static inline unsigned blocks_for(long total) {
+  long nb = (total + 255) / 256;
+  const long cap = (long)sm_count() * 16;
+  if (nb > cap) nb = cap;
+  if (nb < 1) nb = 1;
+  return (unsigned)nb;
+}
+
+}  // namespace ubr
+
+using namespace ubr;
+
+extern "C" {
+
+int ubr_pack_weights(const float* src, int src_layout, int n_is_out, int out_ch, int in_ch, int kh, int kw, int n_pad,
+                     int k_pad, void* dst_bf16, void* stream) {
+  if (int rc = ensure_device()) return rc;
+  UBR_REQUIRE(src && dst_bf16, "pack_weights: null pointer");
+  UBR_REQUIRE(src_layout == 0 || src_layout == 1, "pack_weights: bad src_layout");
+  UBR_REQUIRE(n_pad % 16 == 0 && k_pad % 16 == 0, "pack_weights: pads must be multiples of 16");
+  const int nn = n_is_out ? out_ch : in_ch, kk = n_is_out ? in_ch : out_ch;
+  UBR_REQUIRE(n_pad >= nn && k_pad >= kk, "pack_weights: pads too small");
+  const long total = (long)(kh * kw + 1) * n_pad * k_pad;
+  pack_weights_kernel<<<blocks_for(total), 256, 0, (cudaStream_t)stream>>>(src, src_layout, n_is_out, out_ch, in_ch, kh,
+                                                                           kw, n_pad, k_pad, (__nv_bfloat16*)dst_bf16);
+  UBR_LAUNCH_CHECK("pack_weights_kernel");
+  return 0;
+}
+
+int ubr_logsoftmax_fwd(const float* logits, int ld, int n, int ncls, int hw, float* logp, void* stream) {
+  if (int rc = ensure_device()) return rc;
+  UBR_REQUIRE(logits && logp, "logsoftmax_fwd: null pointer");
+  UBR_REQUIRE(ncls >= 1 && ncls <= kMaxCls && ld >= ncls, "logsoftmax_fwd: ncls=%d ld=%d unsupported", ncls, ld);
+  logsoftmax_fwd_kernel<<<blocks_for((long)n * hw), 256, 0, (cudaStream_t)stream>>>(logits, ld, n, ncls, hw, logp);
+  UBR_LAUNCH_CHECK("logsoftmax_fwd_kernel");
+  return 0;
+}
+
+int ubr_logsoftmax_bwd(const float* logp, const float* dlogp, int n, int ncls, int hw, ubr_view dlogits, void* stream) {
+  if (int rc = ensure_device()) return rc;
+  UBR_REQUIRE(logp && dlogp && dlogits.ptr, "logsoftmax_bwd: null pointer");
+  UBR_REQUIRE(ncls >= 1 && ncls <= kMaxCls && dlogits.c >= ncls && dlogits.c % 8 == 0 && dlogits.ld % 8 == 0,
+              "logsoftmax_bwd: bad dlogits view");
+  UBR_REQUIRE((long)dlogits.n * dlogits.h * dlogits.w == (long)n * hw, "logsoftmax_bwd: pixel count mismatch");
+  logsoftmax_bwd_kernel<<<blocks_for((long)n * hw), 256, 0, (cudaStream_t)stream>>>(
+      logp, dlogp, n, ncls, hw, (__nv_bfloat16*)dlogits.ptr, dlogits.c, dlogits.ld);
+  UBR_LAUNCH_CHECK("logsoftmax_bwd_kernel");
+  return 0;
+}
+
+uint64_t ubr_nll_workspace_bytes(int n, int hw) {
+  (void)n; (void)hw;
+  return (uint64_t)kNllBlocks * sizeof(float);
+}
+
+int ubr_pixelwise_nll_fwd(const float* logp, const int64_t* target, const float* pixw, const float* classw, int n,
+                          int ncls, int hw, int64_t ignore_index, void* workspace, float* loss, void* stream) {
+  if (int rc = ensure_device()) return rc;
+  UBR_REQUIRE(logp && target && pixw && workspace && loss, "pixelwise_nll_fwd: null pointer");
+  UBR_REQUIRE(n > 0 && hw > 0 && ncls >= 1, "pixelwise_nll_fwd: bad sizes");
+  cudaStream_t st = (cudaStream_t)stream;
+  long nb = ((long)n * hw + 255) / 256;
+  if (nb > kNllBlocks) nb = kNllBlocks;
+  nll_fwd_kernel<<<(unsigned)nb, 256, 0, st>>>(logp, (const long long*)target, pixw, classw, n, ncls, hw,
+                                               (long long)ignore_index, (float*)workspace);
+  UBR_LAUNCH_CHECK("nll_fwd_kernel");
+  nll_finalize_kernel<<<1, 32, 0, st>>>((const float*)workspace, (int)nb, 1.0 / ((double)n * hw), loss);
+  UBR_LAUNCH_CHECK("nll_finalize_kernel");
+  return 0;
+}
+
+int ubr_pixelwise_nll_bwd(const int64_t* target, const float* pixw, const float* classw, const float* gout, int n,
+                          int ncls, int hw, int64_t ignore_index, float* dlogp, void* stream) {
+  if (int rc = ensure_device()) return rc;
+  UBR_REQUIRE(target && pixw && dlogp, "pixelwise_nll_bwd: null pointer");
+  nll_bwd_kernel<<<blocks_for((long)n * hw), 256, 0, (cudaStream_t)stream>>>(
+      (const long long*)target, pixw, classw, gout, n, ncls, hw, (long long)ignore_index,
+      (float)(1.0 / ((double)n * hw)), dlogp);
+  UBR_LAUNCH_CHECK("nll_bwd_kernel");
+  return 0;
+}
+
+int ubr_tile_gather(const float* plane, int rows, int cols, const int32_t* origins, int ntiles, int crop, float* crops,
+                    void* stream) {
+  if (int rc = ensure_device()) return rc;
+  UBR_REQUIRE(plane && origins && crops, "tile_gather: null pointer");
+  UBR_REQUIRE(rows > 0 && cols > 0 && ntiles > 0 && crop > 0, "tile_gather: bad sizes");
+  tile_gather_kernel<<<blocks_for((long)ntiles * crop * crop), 256, 0, (cudaStream_t)stream>>>(plane, rows, cols, origins,
+                                                                                               ntiles, crop, crops);
+  UBR_LAUNCH_CHECK("tile_gather_kernel");
+  return 0;
+}
+
+int ubr_stitch_scatter(const float* tiles, int nch, const int32_t* origins, int ntiles, int crop, int rows, int cols,
+                       float* out, void* stream) {
+  if (int rc = ensure_device()) return rc;
+  UBR_REQUIRE(tiles && origins && out, "stitch_scatter: null pointer");
+  UBR_REQUIRE(rows > 0 && cols > 0 && ntiles > 0 && crop > 0 && nch > 0, "stitch_scatter: bad sizes");
+  stitch_scatter_kernel<<<blocks_for((long)rows * cols), 256, 0, (cudaStream_t)stream>>>(tiles, nch, origins, ntiles,
+                                                                                         crop, rows, cols, out);
+  UBR_LAUNCH_CHECK("stitch_scatter_kernel");
+  return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,734 @@
+// Memory-bound NHWC bf16 kernels: BatchNorm statistics / affine / backward, residual block tail,
+// max-pool, pointwise sums.  All are HBM-roofline kernels: 16-byte vector accesses (8 bf16 channels per
+// thread), fp32 math, deterministic two-level reductions (per-block partials, fixed-order finalize).
+#include "common.cuh"
+
+namespace ubr {
+
+constexpr int kRedBlocks = 592;      // 4 x 148 SMs: partial rows of every reduction workspace
+constexpr int kRedThreads = 256;
+
+struct DView {
+  const __nv_bfloat16* ptr;
+  int c, ld;
+  long npix;
+};
+struct DViewW {
+  __nv_bfloat16* ptr;
+  int c, ld;
+  long npix;
+};
+
+static inline DView dv(const ubr_view& v) { return DView{(const __nv_bfloat16*)v.ptr, v.c, v.ld, (long)v.n * v.h * v.w}; }
+static inline DViewW dvw(const ubr_view& v) { return DViewW{(__nv_bfloat16*)v.ptr, v.c, v.ld, (long)v.n * v.h * v.w}; }
+
+__device__ __forceinline__ void load8(const __nv_bfloat16* p, float (&f)[8]) {
+  const uint4 u = *reinterpret_cast<const uint4*>(p);
+  float2 a = unpack_bf16x2(u.x), b = unpack_bf16x2(u.y), c = unpack_bf16x2(u.z), d = unpack_bf16x2(u.w);
+  f[0] = a.x; f[1] = a.y; f[2] = b.x; f[3] = b.y; f[4] = c.x; f[5] = c.y; f[6] = d.x; f[7] = d.y;
+}
+__device__ __forceinline__ void store8(__nv_bfloat16* p, const float (&f)[8]) {
+  uint4 u;
+  u.x = pack_bf16x2(f[0], f[1]); u.y = pack_bf16x2(f[2], f[3]);
+  u.z = pack_bf16x2(f[4], f[5]); u.w = pack_bf16x2(f[6], f[7]);
+  *reinterpret_cast<uint4*>(p) = u;
+}
+__device__ __forceinline__ void ldparam8(const float* p, int c0, float (&f)[8]) {
+  const float4 a = __ldg(reinterpret_cast<const float4*>(p + c0));
+  const float4 b = __ldg(reinterpret_cast<const float4*>(p + c0 + 4));
+  f[0] = a.x; f[1] = a.y; f[2] = a.z; f[3] = a.w; f[4] = b.x; f[5] = b.y; f[6] = b.z; f[7] = b.w;
+}
+// round an fp32 value through bf16 (what a consumer reading the stored tensor would see)
+__device__ __forceinline__ float rbf(float x) { return __bfloat162float(__float2bfloat16_rn(x)); }
+
+// ---------------------------------------------------------------------------------------------
+// block-level reduction of NS x 8 per-thread accumulators -> partials[block][NS][C]
+// thread layout: cg = tid % (C/8) (channel group), pixel lane = tid / (C/8)
+// ---------------------------------------------------------------------------------------------
+template <int NS>
+__device__ __forceinline__ void block_reduce_store(float (&acc)[NS][8], int c, float* partials) {
+  extern __shared__ float red[];            // [blockDim.x][NS*8]
+  const int cgs = c >> 3;
+  const int lanes = blockDim.x / cgs;
+  float* mine = red + (size_t)threadIdx.x * (NS * 8);
+#pragma unroll
+  for (int s = 0; s < NS; ++s)
+#pragma unroll
+    for (int j = 0; j < 8; ++j) mine[s * 8 + j] = acc[s][j];
+  __syncthreads();
+  float* out = partials + (size_t)blockIdx.x * NS * c;
+  for (int o = threadIdx.x; o < cgs * NS * 8; o += blockDim.x) {
+    const int cg = o / (NS * 8), r = o % (NS * 8);
+    float sum = 0.f;
+    for (int l = 0; l < lanes; ++l) sum += red[(size_t)(l * cgs + cg) * (NS * 8) + r];
+    const int s = r >> 3, j = r & 7;
+    out[s * c + cg * 8 + j] = sum;
+  }
+}
+
+static inline int red_blocks(long npix, int c) {
+  const int lanes = kRedThreads / (c >> 3);
+  long nb = (npix + (long)lanes * 8 - 1) / ((long)lanes * 8);
+  if (nb > kRedBlocks) nb = kRedBlocks;
+  if (nb < 1) nb = 1;
+  return (int)nb;
+}
+
+// ------------------------------------------------------------------ BN forward statistics
+__global__ void __launch_bounds__(kRedThreads) bn_stats_kernel(DView y, float* partials) {
+  const int cgs = y.c >> 3, lanes = blockDim.x / cgs;
+  const int cg = threadIdx.x % cgs, pl = threadIdx.x / cgs;
+  float acc[2][8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) { acc[0][j] = 0.f; acc[1][j] = 0.f; }
+  for (long p = (long)blockIdx.x * lanes + pl; p < y.npix; p += (long)gridDim.x * lanes) {
+    float f[8];
+    load8(y.ptr + p * y.ld + cg * 8, f);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { acc[0][j] += f[j]; acc[1][j] = fmaf(f[j], f[j], acc[1][j]); }
+  }
+  block_reduce_store<2>(acc, y.c, partials);
+}
+
+__global__ void bn_finalize_kernel(const float* partials, int nb, int c, double count, const float* gamma,
+                                   const float* beta, float* running_mean, float* running_var, float momentum,
+                                   float eps, float* scale, float* shift, float* mean_out, float* invstd_out) {
+  const int ch = blockIdx.x * blockDim.x + threadIdx.x;
+  if (ch >= c) return;
+  double s = 0.0, q = 0.0;
+  for (int b = 0; b < nb; ++b) {
+    s += (double)partials[(size_t)b * 2 * c + ch];
+    q += (double)partials[(size_t)b * 2 * c + c + ch];
+  }
+  const double mean = s / count;
+  double var = q / count - mean * mean;
+  if (var < 0.0) var = 0.0;
+  const float invstd = (float)(1.0 / sqrt(var + (double)eps));
+  const float g = gamma ? gamma[ch] : 1.f, b = beta ? beta[ch] : 0.f;
+  scale[ch] = g * invstd;
+  shift[ch] = b - (float)mean * g * invstd;
+  if (mean_out) mean_out[ch] = (float)mean;
+  if (invstd_out) invstd_out[ch] = invstd;
+  if (running_mean) running_mean[ch] = (1.f - momentum) * running_mean[ch] + momentum * (float)mean;
+  if (running_var) {
+    const double unbiased = count > 1.0 ? var * count / (count - 1.0) : var;
+    running_var[ch] = (1.f - momentum) * running_var[ch] + momentum * (float)unbiased;
+  }
+}
+
+__global__ void bn_eval_affine_kernel(int c, const float* gamma, const float* beta, const float* rm, const float* rv,
+                                      float eps, float* scale, float* shift) {
+  const int ch = blockIdx.x * blockDim.x + threadIdx.x;
+  if (ch >= c) return;
+  const float invstd = rsqrtf(rv[ch] + eps);
+  const float g = gamma ? gamma[ch] : 1.f, b = beta ? beta[ch] : 0.f;
+  scale[ch] = g * invstd;
+  shift[ch] = b - rm[ch] * g * invstd;
+}
+
+// ------------------------------------------------------------------ BN apply (+ReLU), block tail
+__global__ void __launch_bounds__(256) bn_act_kernel(DView y, const float* scale, const float* shift, int relu,
+                                                     DViewW out) {
+  const int cgs = y.c >> 3;
+  const long total = y.npix * cgs;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+    const long p = i / cgs;
+    const int cg = (int)(i % cgs);
+    float f[8], sc[8], sh[8];
+    load8(y.ptr + p * y.ld + cg * 8, f);
+    ldparam8(scale, cg * 8, sc);
+    ldparam8(shift, cg * 8, sh);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      f[j] = fmaf(f[j], sc[j], sh[j]);
+      if (relu) f[j] = fmaxf(f[j], 0.f);
+    }
+    store8(out.ptr + p * out.ld + cg * 8, f);
+  }
+}
+
+// out = relu( relu(y2*s2+b2) + (res*sr+br | res) )
+__global__ void __launch_bounds__(256) block_tail_kernel(DView y2, const float* s2, const float* b2, DView res,
+                                                         const float* sr, const float* br, DViewW out) {
+  const int cgs = y2.c >> 3;
+  const long total = y2.npix * cgs;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+    const long p = i / cgs;
+    const int cg = (int)(i % cgs);
+    float f[8], r[8], a[8], b[8];
+    load8(y2.ptr + p * y2.ld + cg * 8, f);
+    load8(res.ptr + p * res.ld + cg * 8, r);
+    ldparam8(s2, cg * 8, a);
+    ldparam8(b2, cg * 8, b);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) f[j] = fmaxf(fmaf(f[j], a[j], b[j]), 0.f);
+    if (sr) {
+      ldparam8(sr, cg * 8, a);
+      ldparam8(br, cg * 8, b);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) r[j] = fmaf(r[j], a[j], b[j]);
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) f[j] = fmaxf(f[j] + r[j], 0.f);
+    store8(out.ptr + p * out.ld + cg * 8, f);
+  }
+}
+
+// ------------------------------------------------------------------ BN(+ReLU) backward
+// reduce: sums[0] = sum dz, sums[1] = sum dz*xhat
+__global__ void __launch_bounds__(kRedThreads) bn_act_bwd_reduce_kernel(DView dout, DView y, const float* scale,
+                                                                        const float* shift, const float* mean,
+                                                                        const float* invstd, int relu, float* partials) {
+  const int cgs = y.c >> 3, lanes = blockDim.x / cgs;
+  const int cg = threadIdx.x % cgs, pl = threadIdx.x / cgs;
+  float sc[8], sh[8], mu[8], is[8];
+  ldparam8(scale, cg * 8, sc); ldparam8(shift, cg * 8, sh);
+  ldparam8(mean, cg * 8, mu); ldparam8(invstd, cg * 8, is);
+  float acc[2][8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) { acc[0][j] = 0.f; acc[1][j] = 0.f; }
+  for (long p = (long)blockIdx.x * lanes + pl; p < y.npix; p += (long)gridDim.x * lanes) {
+    float g[8], v[8];
+    load8(dout.ptr + p * dout.ld + cg * 8, g);
+    load8(y.ptr + p * y.ld + cg * 8, v);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float z = fmaf(v[j], sc[j], sh[j]);
+      const float dz = (!relu || z > 0.f) ? g[j] : 0.f;
+      acc[0][j] += dz;
+      acc[1][j] = fmaf(dz, (v[j] - mu[j]) * is[j], acc[1][j]);
+    }
+  }
+  block_reduce_store<2>(acc, y.c, partials);
+}
+
+// sums partials[nb][NS][C] -> sums[NS][C] (fixed order, double)
+__global__ void sums_finalize_kernel(const float* partials, int nb, int nsc, float* sums) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= nsc) return;
+  double s = 0.0;
+  for (int b = 0; b < nb; ++b) s += (double)partials[(size_t)b * nsc + i];
+  sums[i] = (float)s;
+}
+
+__global__ void param_grad_kernel(const float* sums, int c, int off_dz, int off_dzx, float* dgamma, float* dbeta,
+                                  int accumulate) {
+  const int ch = blockIdx.x * blockDim.x + threadIdx.x;
+  if (ch >= c) return;
+  if (dgamma) dgamma[ch] = (accumulate ? dgamma[ch] : 0.f) + sums[off_dzx * c + ch];
+  if (dbeta) dbeta[ch] = (accumulate ? dbeta[ch] : 0.f) + sums[off_dz * c + ch];
+}
+
+__global__ void __launch_bounds__(256) bn_act_bwd_apply_kernel(DView dout, DView y, const float* scale,
+                                                               const float* shift, const float* mean,
+                                                               const float* invstd, const float* gamma, int relu,
+                                                               const float* sums, float inv_count, DViewW dy) {
+  const int cgs = y.c >> 3;
+  const long total = y.npix * cgs;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+    const long p = i / cgs;
+    const int cg = (int)(i % cgs);
+    float g[8], v[8], sc[8], sh[8], mu[8], is[8], s0[8], s1[8];
+    load8(dout.ptr + p * dout.ld + cg * 8, g);
+    load8(y.ptr + p * y.ld + cg * 8, v);
+    ldparam8(scale, cg * 8, sc); ldparam8(shift, cg * 8, sh);
+    ldparam8(mean, cg * 8, mu); ldparam8(invstd, cg * 8, is);
+    ldparam8(sums, cg * 8, s0); ldparam8(sums + y.c, cg * 8, s1);
+    float o[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float z = fmaf(v[j], sc[j], sh[j]);
+      const float dz = (!relu || z > 0.f) ? g[j] : 0.f;
+      const float xh = (v[j] - mu[j]) * is[j];
+      // gamma*invstd == scale
+      o[j] = sc[j] * (dz - s0[j] * inv_count - xh * s1[j] * inv_count);
+    }
+    (void)gamma;
+    store8(dy.ptr + p * dy.ld + cg * 8, o);
+  }
+}
+
+// ------------------------------------------------------------------ block tail backward
+// du = dout*(out>0);  dz2 = du*(bn2(y2)>0)
+// sums: [0] sum dz2, [1] sum dz2*xhat2, [2] sum du, [3] sum du*xhat_r   (2,3 only if res_is_bn)
+template <bool RES_BN>
+__global__ void __launch_bounds__(kRedThreads) tail_bwd_reduce_kernel(DView dout, DView out, DView y2, const float* s2,
+                                                                      const float* b2, const float* mean2,
+                                                                      const float* invstd2, DView res,
+                                                                      const float* meanr, const float* invstdr,
+                                                                      float* partials) {
+  constexpr int NS = RES_BN ? 4 : 2;
+  const int cgs = y2.c >> 3, lanes = blockDim.x / cgs;
+  const int cg = threadIdx.x % cgs, pl = threadIdx.x / cgs;
+  float sc[8], sh[8], mu[8], is[8], mur[8], isr[8];
+  ldparam8(s2, cg * 8, sc); ldparam8(b2, cg * 8, sh);
+  ldparam8(mean2, cg * 8, mu); ldparam8(invstd2, cg * 8, is);
+  if (RES_BN) { ldparam8(meanr, cg * 8, mur); ldparam8(invstdr, cg * 8, isr); }
+  float acc[NS][8];
+#pragma unroll
+  for (int s = 0; s < NS; ++s)
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[s][j] = 0.f;
+  for (long p = (long)blockIdx.x * lanes + pl; p < y2.npix; p += (long)gridDim.x * lanes) {
+    float g[8], o[8], v[8], r[8];
+    load8(dout.ptr + p * dout.ld + cg * 8, g);
+    load8(out.ptr + p * out.ld + cg * 8, o);
+    load8(y2.ptr + p * y2.ld + cg * 8, v);
+    if (RES_BN) load8(res.ptr + p * res.ld + cg * 8, r);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float du = o[j] > 0.f ? g[j] : 0.f;
+      const float z = fmaf(v[j], sc[j], sh[j]);
+      const float dz = z > 0.f ? du : 0.f;
+      acc[0][j] += dz;
+      acc[1][j] = fmaf(dz, (v[j] - mu[j]) * is[j], acc[1][j]);
+      if (RES_BN) {
+        acc[2][j] += du;
+        acc[3][j] = fmaf(du, (r[j] - mur[j]) * isr[j], acc[3][j]);
+      }
+    }
+  }
+  block_reduce_store<NS>(acc, y2.c, partials);
+}
+
+template <bool RES_BN>
+__global__ void __launch_bounds__(256) tail_bwd_apply_kernel(DView dout, DView out, DView y2, const float* s2,
+                                                             const float* b2, const float* mean2,
+                                                             const float* invstd2, DView res, const float* meanr,
+                                                             const float* invstdr, const float* gammar,
+                                                             const float* sums, float inv_count, DViewW dy2,
+                                                             DViewW dres) {
+  const int cgs = y2.c >> 3, c = y2.c;
+  const long total = y2.npix * cgs;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+    const long p = i / cgs;
+    const int cg = (int)(i % cgs);
+    float g[8], o[8], v[8], sc[8], sh[8], mu[8], is[8], t0[8], t1[8];
+    load8(dout.ptr + p * dout.ld + cg * 8, g);
+    load8(out.ptr + p * out.ld + cg * 8, o);
+    load8(y2.ptr + p * y2.ld + cg * 8, v);
+    ldparam8(s2, cg * 8, sc); ldparam8(b2, cg * 8, sh);
+    ldparam8(mean2, cg * 8, mu); ldparam8(invstd2, cg * 8, is);
+    ldparam8(sums, cg * 8, t0); ldparam8(sums + c, cg * 8, t1);
+    float du[8], d2[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      du[j] = o[j] > 0.f ? g[j] : 0.f;
+      const float z = fmaf(v[j], sc[j], sh[j]);
+      const float dz = z > 0.f ? du[j] : 0.f;
+      const float xh = (v[j] - mu[j]) * is[j];
+      d2[j] = sc[j] * (dz - t0[j] * inv_count - xh * t1[j] * inv_count);
+    }
+    store8(dy2.ptr + p * dy2.ld + cg * 8, d2);
+    if (RES_BN) {
+      float r[8], mur[8], isr[8], gr[8], u0[8], u1[8], dr[8];
+      load8(res.ptr + p * res.ld + cg * 8, r);
+      ldparam8(meanr, cg * 8, mur); ldparam8(invstdr, cg * 8, isr); ldparam8(gammar, cg * 8, gr);
+      ldparam8(sums + 2 * c, cg * 8, u0); ldparam8(sums + 3 * c, cg * 8, u1);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float xh = (r[j] - mur[j]) * isr[j];
+        dr[j] = gr[j] * isr[j] * (du[j] - u0[j] * inv_count - xh * u1[j] * inv_count);
+      }
+      store8(dres.ptr + p * dres.ld + cg * 8, dr);
+    } else {
+      store8(dres.ptr + p * dres.ld + cg * 8, du);
+    }
+  }
+}
+
+// ------------------------------------------------------------------ pointwise sum
+__global__ void __launch_bounds__(256) add_kernel(DView a, DView b, DView c, DViewW out) {
+  const int cgs = a.c >> 3;
+  const long total = a.npix * cgs;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+    const long p = i / cgs;
+    const int cg = (int)(i % cgs);
+    float x[8], y[8];
+    load8(a.ptr + p * a.ld + cg * 8, x);
+    if (b.ptr) {
+      load8(b.ptr + p * b.ld + cg * 8, y);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) x[j] += y[j];
+    }
+    if (c.ptr) {
+      load8(c.ptr + p * c.ld + cg * 8, y);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) x[j] += y[j];
+    }
+    store8(out.ptr + p * out.ld + cg * 8, x);
+  }
+}
+
+// ------------------------------------------------------------------ MaxPool 3x3 / stride 2 / pad 1
+__global__ void __launch_bounds__(256) maxpool_fwd_kernel(const __nv_bfloat16* x, int xld, int n, int h, int w, int c,
+                                                          __nv_bfloat16* y, int yld) {
+  const int cgs = c >> 3, ho = h / 2, wo = w / 2;
+  const long total = (long)n * ho * wo * cgs;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+    const int cg = (int)(i % cgs);
+    long p = i / cgs;
+    const int ow = (int)(p % wo); p /= wo;
+    const int oh = (int)(p % ho);
+    const int b = (int)(p / ho);
+    float m[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) m[j] = -INFINITY;
+    for (int kh = 0; kh < 3; ++kh) {
+      const int ih = 2 * oh - 1 + kh;
+      if (ih < 0 || ih >= h) continue;
+      for (int kw = 0; kw < 3; ++kw) {
+        const int iw = 2 * ow - 1 + kw;
+        if (iw < 0 || iw >= w) continue;
+        float f[8];
+        load8(x + (((long)b * h + ih) * w + iw) * xld + cg * 8, f);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) m[j] = fmaxf(m[j], f[j]);
+      }
+    }
+    store8(y + (((long)b * ho + oh) * wo + ow) * yld + cg * 8, m);
+  }
+}
+
+// gather form of the backward: each input pixel re-derives the argmax (first maximum in (kh,kw) scan
+// order, as ATen's max_pool2d) of every window that covers it.  Deterministic, no atomics.
+__global__ void __launch_bounds__(256) maxpool_bwd_kernel(const __nv_bfloat16* x, int xld, int n, int h, int w, int c,
+                                                          const __nv_bfloat16* dy, int dyld, __nv_bfloat16* dx,
+                                                          int dxld, int accumulate) {
+  const int cgs = c >> 3, ho = h / 2, wo = w / 2;
+  const long total = (long)n * h * w * cgs;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+    const int cg = (int)(i % cgs);
+    long p = i / cgs;
+    const int iw = (int)(p % w); p /= w;
+    const int ih = (int)(p % h);
+    const int b = (int)(p / h);
+    float acc[8];
+    if (accumulate) load8(dx + (((long)b * h + ih) * w + iw) * dxld + cg * 8, acc);
+    else {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+    }
+    // windows oh with 2*oh-1 <= ih <= 2*oh+1
+    const int oh_lo = ih / 2, oh_hi = (ih + 1) / 2;
+    const int ow_lo = iw / 2, ow_hi = (iw + 1) / 2;
+    for (int oh = oh_lo; oh <= oh_hi; ++oh) {
+      if (oh >= ho) continue;
+      for (int ow = ow_lo; ow <= ow_hi; ++ow) {
+        if (ow >= wo) continue;
+        float best[8];
+        int arg[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) { best[j] = -INFINITY; arg[j] = -1; }
+        for (int kh = 0; kh < 3; ++kh) {
+          const int yh = 2 * oh - 1 + kh;
+          if (yh < 0 || yh >= h) continue;
+          for (int kw = 0; kw < 3; ++kw) {
+            const int yw = 2 * ow - 1 + kw;
+            if (yw < 0 || yw >= w) continue;
+            float f[8];
+            load8(x + (((long)b * h + yh) * w + yw) * xld + cg * 8, f);
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+              if (f[j] > best[j] || arg[j] < 0) { best[j] = f[j]; arg[j] = kh * 3 + kw; }
+          }
+        }
+        const int me = (ih - (2 * oh - 1)) * 3 + (iw - (2 * ow - 1));
+        float g[8];
+        load8(dy + (((long)b * ho + oh) * wo + ow) * dyld + cg * 8, g);
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          if (arg[j] == me) acc[j] += g[j];
+      }
+    }
+    store8(dx + (((long)b * h + ih) * w + iw) * dxld + cg * 8, acc);
+  }
+}
+
+__global__ void scale_f32_kernel(float* buf, unsigned long long count, float alpha) {
+  for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < count;
+       i += (unsigned long long)gridDim.x * blockDim.x)
+    buf[i] *= alpha;
+}
+
+// ------------------------------------------------------------------ host helpers
+static int chk(const ubr_view& v, const char* name) {
+  UBR_REQUIRE(v.ptr != nullptr, "%s: null pointer", name);
+  UBR_REQUIRE(v.n > 0 && v.h > 0 && v.w > 0 && v.c > 0 && v.c % 8 == 0, "%s: bad extents (c=%d)", name, v.c);
+  UBR_REQUIRE(v.ld >= v.c && v.ld % 8 == 0, "%s: bad ld=%d (c=%d)", name, v.ld, v.c);
+  UBR_REQUIRE(((uintptr_t)v.ptr & 15) == 0, "%s: pointer must be 16-byte aligned", name);
+  return 0;
+}
+static int same_shape(const ubr_view& a, const ubr_view& b, const char* what) {
+  UBR_REQUIRE(a.n == b.n && a.h == b.h && a.w == b.w && a.c == b.c, "%s: shape mismatch (%d,%d,%d,%d) vs (%d,%d,%d,%d)",
+              what, a.n, a.h, a.w, a.c, b.n, b.h, b.w, b.c);
+  return 0;
+}
+static int chk_red(const ubr_view& v, const char* name) {
+  if (int rc = chk(v, name)) return rc;
+  const int cgs = v.c >> 3;
+  UBR_REQUIRE(cgs <= kRedThreads && kRedThreads % cgs == 0, "%s: c=%d must divide %d (power-of-two multiples of 8)",
+              name, v.c, kRedThreads * 8);
+  return 0;
+}
+static inline unsigned ew_blocks(long total) {
+  long nb = (total + 255) / 256;
+  const long cap = (long)sm_count() * 16;
+  if (nb > cap) nb = cap;
+  if (nb < 1) nb = 1;
+  return (unsigned)nb;
+}
+
+}  // namespace ubr
+
+using namespace ubr;
+
+extern "C" {
+
+uint64_t ubr_bn_workspace_bytes(int c) {
+  // partial rows [kRedBlocks][4][c] + finalised sums [4][c]
+  return (uint64_t)(kRedBlocks + 1) * 4 * (uint64_t)c * sizeof(float);
+}
+
+int ubr_bn_stats(ubr_view y, void* workspace, void* stream) {
+  if (int rc = ensure_device()) return rc;
+  if (int rc = chk_red(y, "bn_stats.y")) return rc;
+  UBR_REQUIRE(workspace != nullptr, "bn_stats: null workspace");
+  DView v = dv(y);
+  const int nb = red_blocks(v.npix, v.c);
+  bn_stats_kernel<<<nb, kRedThreads, kRedThreads * 16 * sizeof(float), (cudaStream_t)stream>>>(v, (float*)workspace);
+  UBR_LAUNCH_CHECK("bn_stats_kernel");
+  return 0;
+}
+
+int ubr_bn_finalize(const void* workspace, int c, double count, const float* gamma, const float* beta,
+                    float* running_mean, float* running_var, float momentum, float eps, float* scale, float* shift,
+                    float* mean, float* invstd, void* stream) {
+  if (int rc = ensure_device()) return rc;
+  UBR_REQUIRE(workspace && scale && shift, "bn_finalize: null pointer");
+  UBR_REQUIRE(c > 0 && c % 8 == 0 && count >= 1.0, "bn_finalize: bad c/count");
+  const int nb = red_blocks((long)count, c);
+  bn_finalize_kernel<<<ceil_div(c, 128), 128, 0, (cudaStream_t)stream>>>((const float*)workspace, nb, c, count, gamma,
+                                                                         beta, running_mean, running_var, momentum,
+                                                                         eps, scale, shift, mean, invstd);
+  UBR_LAUNCH_CHECK("bn_finalize_kernel");
+  return 0;
+}
+
+int ubr_bn_eval_affine(int c, const float* gamma, const float* beta, const float* running_mean,
+                       const float* running_var, float eps, float* scale, float* shift, void* stream) {
+  if (int rc = ensure_device()) return rc;
+  UBR_REQUIRE(running_mean && running_var && scale && shift && c > 0, "bn_eval_affine: bad args");
+  bn_eval_affine_kernel<<<ceil_div(c, 128), 128, 0, (cudaStream_t)stream>>>(c, gamma, beta, running_mean, running_var,
+                                                                            eps, scale, shift);
+  UBR_LAUNCH_CHECK("bn_eval_affine_kernel");
+  return 0;
+}
+
+int ubr_bn_act(ubr_view y, const float* scale, const float* shift, int relu, ubr_view out, void* stream) {
+  if (int rc = ensure_device()) return rc;
+  if (int rc = chk(y, "bn_act.y")) return rc;
+  if (int rc = chk(out, "bn_act.out")) return rc;
+  if (int rc = same_shape(y, out, "bn_act")) return rc;
+  UBR_REQUIRE(scale && shift, "bn_act: null affine");
+  DView v = dv(y);
+  bn_act_kernel<<<ew_blocks(v.npix * (v.c >> 3)), 256, 0, (cudaStream_t)stream>>>(v, scale, shift, relu, dvw(out));
+  UBR_LAUNCH_CHECK("bn_act_kernel");
+  return 0;
+}
+
+int ubr_block_tail(ubr_view y2, const float* s2, const float* b2, ubr_view res, const float* sr, const float* br,
+                   ubr_view out, void* stream) {
+  if (int rc = ensure_device()) return rc;
+  if (int rc = chk(y2, "block_tail.y2")) return rc;
+  if (int rc = chk(res, "block_tail.res")) return rc;
+  if (int rc = chk(out, "block_tail.out")) return rc;
+  if (int rc = same_shape(y2, res, "block_tail(res)")) return rc;
+  if (int rc = same_shape(y2, out, "block_tail(out)")) return rc;
+  UBR_REQUIRE(s2 && b2 && ((sr == nullptr) == (br == nullptr)), "block_tail: bad affine pointers");
+  DView v = dv(y2);
+  block_tail_kernel<<<ew_blocks(v.npix * (v.c >> 3)), 256, 0, (cudaStream_t)stream>>>(v, s2, b2, dv(res), sr, br,
+                                                                                      dvw(out));
+  UBR_LAUNCH_CHECK("block_tail_kernel");
+  return 0;
+}
+
+int ubr_bn_act_bwd_reduce(ubr_view dout, ubr_view y, const float* scale, const float* shift, const float* mean,
+                          const float* invstd, int relu, void* workspace, void* stream) {
+  if (int rc = ensure_device()) return rc;
+  if (int rc = chk_red(y, "bn_act_bwd_reduce.y")) return rc;
+  if (int rc = chk(dout, "bn_act_bwd_reduce.dout")) return rc;
+  if (int rc = same_shape(y, dout, "bn_act_bwd_reduce")) return rc;
+  UBR_REQUIRE(scale && shift && mean && invstd && workspace, "bn_act_bwd_reduce: null pointer");
+  DView v = dv(y);
+  const int nb = red_blocks(v.npix, v.c);
+  bn_act_bwd_reduce_kernel<<<nb, kRedThreads, kRedThreads * 16 * sizeof(float), (cudaStream_t)stream>>>(
+      dv(dout), v, scale, shift, mean, invstd, relu, (float*)workspace);
+  UBR_LAUNCH_CHECK("bn_act_bwd_reduce_kernel");
+  return 0;
+}
+
+int ubr_bn_act_bwd_apply(ubr_view dout, ubr_view y, const float* scale, const float* shift, const float* mean,
+                         const float* invstd, const float* gamma, int relu, const void* workspace, double count,
+                         ubr_view dy, float* dgamma, float* dbeta, int accumulate, void* stream) {
+  if (int rc = ensure_device()) return rc;
+  if (int rc = chk_red(y, "bn_act_bwd_apply.y")) return rc;
+  if (int rc = chk(dout, "bn_act_bwd_apply.dout")) return rc;
+  if (int rc = chk(dy, "bn_act_bwd_apply.dy")) return rc;
+  if (int rc = same_shape(y, dout, "bn_act_bwd_apply(dout)")) return rc;
+  if (int rc = same_shape(y, dy, "bn_act_bwd_apply(dy)")) return rc;
+  UBR_REQUIRE(scale && shift && mean && invstd && workspace, "bn_act_bwd_apply: null pointer");
+  DView v = dv(y);
+  const int nb = red_blocks(v.npix, v.c);
+  const float* partials = (const float*)workspace;
+  float* sums = (float*)workspace + (size_t)kRedBlocks * 4 * v.c;
+  cudaStream_t st = (cudaStream_t)stream;
+  sums_finalize_kernel<<<ceil_div(2 * v.c, 128), 128, 0, st>>>(partials, nb, 2 * v.c, sums);
+  UBR_LAUNCH_CHECK("sums_finalize_kernel");
+  if (dgamma || dbeta) {
+    param_grad_kernel<<<ceil_div(v.c, 128), 128, 0, st>>>(sums, v.c, 0, 1, dgamma, dbeta, accumulate);
+    UBR_LAUNCH_CHECK("param_grad_kernel");
+  }
+  bn_act_bwd_apply_kernel<<<ew_blocks(v.npix * (v.c >> 3)), 256, 0, st>>>(dv(dout), v, scale, shift, mean, invstd,
+                                                                          gamma, relu, sums, (float)(1.0 / count),
+                                                                          dvw(dy));
+  UBR_LAUNCH_CHECK("bn_act_bwd_apply_kernel");
+  return 0;
+}
+
+int ubr_block_tail_bwd_reduce(ubr_view dout, ubr_view out, ubr_view y2, const float* s2, const float* b2,
+                              const float* mean2, const float* invstd2, ubr_view res, const float* meanr,
+                              const float* invstdr, int res_is_bn, void* workspace, void* stream) {
+  if (int rc = ensure_device()) return rc;
+  if (int rc = chk_red(y2, "block_tail_bwd_reduce.y2")) return rc;
+  if (int rc = chk(dout, "block_tail_bwd_reduce.dout")) return rc;
+  if (int rc = chk(out, "block_tail_bwd_reduce.out")) return rc;
+  if (int rc = same_shape(y2, dout, "block_tail_bwd_reduce(dout)")) return rc;
+  if (int rc = same_shape(y2, out, "block_tail_bwd_reduce(out)")) return rc;
+  UBR_REQUIRE(s2 && b2 && mean2 && invstd2 && workspace, "block_tail_bwd_reduce: null pointer");
+  DView v = dv(y2);
+  const int nb = red_blocks(v.npix, v.c);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (res_is_bn) {
+    if (int rc = chk(res, "block_tail_bwd_reduce.res")) return rc;
+    if (int rc = same_shape(y2, res, "block_tail_bwd_reduce(res)")) return rc;
+    UBR_REQUIRE(meanr && invstdr, "block_tail_bwd_reduce: null residual stats");
+    tail_bwd_reduce_kernel<true><<<nb, kRedThreads, kRedThreads * 32 * sizeof(float), st>>>(
+        dv(dout), dv(out), v, s2, b2, mean2, invstd2, dv(res), meanr, invstdr, (float*)workspace);
+  } else {
+    tail_bwd_reduce_kernel<false><<<nb, kRedThreads, kRedThreads * 16 * sizeof(float), st>>>(
+        dv(dout), dv(out), v, s2, b2, mean2, invstd2, v, nullptr, nullptr, (float*)workspace);
+  }
+  UBR_LAUNCH_CHECK("tail_bwd_reduce_kernel");
+  return 0;
+}
+
+int ubr_block_tail_bwd_apply(ubr_view dout, ubr_view out, ubr_view y2, const float* s2, const float* b2,
+                             const float* mean2, const float* invstd2, const float* gamma2, ubr_view res,
+                             const float* meanr, const float* invstdr, const float* gammar, int res_is_bn,
+                             const void* workspace, double count, ubr_view dy2, ubr_view dres, float* dgamma2,
+                             float* dbeta2, float* dgammar, float* dbetar, int accumulate, void* stream) {
+  if (int rc = ensure_device()) return rc;
+  if (int rc = chk_red(y2, "block_tail_bwd_apply.y2")) return rc;
+  if (int rc = chk(dout, "block_tail_bwd_apply.dout")) return rc;
+  if (int rc = chk(out, "block_tail_bwd_apply.out")) return rc;
+  if (int rc = chk(dy2, "block_tail_bwd_apply.dy2")) return rc;
+  if (int rc = chk(dres, "block_tail_bwd_apply.dres")) return rc;
+  if (int rc = same_shape(y2, dout, "block_tail_bwd_apply(dout)")) return rc;
+  if (int rc = same_shape(y2, out, "block_tail_bwd_apply(out)")) return rc;
+  if (int rc = same_shape(y2, dy2, "block_tail_bwd_apply(dy2)")) return rc;
+  if (int rc = same_shape(y2, dres, "block_tail_bwd_apply(dres)")) return rc;
+  UBR_REQUIRE(s2 && b2 && mean2 && invstd2 && workspace, "block_tail_bwd_apply: null pointer");
+  (void)gamma2;
+  DView v = dv(y2);
+  const int nb = red_blocks(v.npix, v.c);
+  const int ns = res_is_bn ? 4 : 2;
+  const float* partials = (const float*)workspace;
+  float* sums = (float*)workspace + (size_t)kRedBlocks * 4 * v.c;
+  cudaStream_t st = (cudaStream_t)stream;
+  sums_finalize_kernel<<<ceil_div(ns * v.c, 128), 128, 0, st>>>(partials, nb, ns * v.c, sums);
+  UBR_LAUNCH_CHECK("sums_finalize_kernel");
+  if (dgamma2 || dbeta2) {
+    param_grad_kernel<<<ceil_div(v.c, 128), 128, 0, st>>>(sums, v.c, 0, 1, dgamma2, dbeta2, accumulate);
+    UBR_LAUNCH_CHECK("param_grad_kernel");
+  }
+  const unsigned blocks = ew_blocks(v.npix * (v.c >> 3));
+  if (res_is_bn) {
+    if (int rc = chk(res, "block_tail_bwd_apply.res")) return rc;
+    UBR_REQUIRE(meanr && invstdr && gammar, "block_tail_bwd_apply: null residual stats");
+    if (dgammar || dbetar) {
+      param_grad_kernel<<<ceil_div(v.c, 128), 128, 0, st>>>(sums, v.c, 2, 3, dgammar, dbetar, accumulate);
+      UBR_LAUNCH_CHECK("param_grad_kernel");
+    }
+    tail_bwd_apply_kernel<true><<<blocks, 256, 0, st>>>(dv(dout), dv(out), v, s2, b2, mean2, invstd2, dv(res), meanr,
+                                                        invstdr, gammar, sums, (float)(1.0 / count), dvw(dy2),
+                                                        dvw(dres));
+  } else {
+    tail_bwd_apply_kernel<false><<<blocks, 256, 0, st>>>(dv(dout), dv(out), v, s2, b2, mean2, invstd2, v, nullptr,
+                                                         nullptr, nullptr, sums, (float)(1.0 / count), dvw(dy2),
+                                                         dvw(dres));
+  }
+  UBR_LAUNCH_CHECK("tail_bwd_apply_kernel");
+  return 0;
+}
+
+int ubr_maxpool3s2_fwd(ubr_view x, ubr_view y, void* stream) {
+  if (int rc = ensure_device()) return rc;
+  if (int rc = chk(x, "maxpool_fwd.x")) return rc;
+  if (int rc = chk(y, "maxpool_fwd.y")) return rc;
+  UBR_REQUIRE(x.h % 2 == 0 && x.w % 2 == 0, "maxpool_fwd: H,W must be even");
+  UBR_REQUIRE(y.n == x.n && y.c == x.c && y.h == x.h / 2 && y.w == x.w / 2, "maxpool_fwd: output view mismatch");
+  const long total = (long)y.n * y.h * y.w * (y.c >> 3);
+  maxpool_fwd_kernel<<<ew_blocks(total), 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)x.ptr, x.ld, x.n, x.h,
+                                                                         x.w, x.c, (__nv_bfloat16*)y.ptr, y.ld);
+  UBR_LAUNCH_CHECK("maxpool_fwd_kernel");
+  return 0;
+}
+
+int ubr_maxpool3s2_bwd(ubr_view x, ubr_view dy, ubr_view dx_accum, int accumulate, void* stream) {
+  if (int rc = ensure_device()) return rc;
+  if (int rc = chk(x, "maxpool_bwd.x")) return rc;
+  if (int rc = chk(dy, "maxpool_bwd.dy")) return rc;
+  if (int rc = chk(dx_accum, "maxpool_bwd.dx")) return rc;
+  if (int rc = same_shape(x, dx_accum, "maxpool_bwd(dx)")) return rc;
+  UBR_REQUIRE(dy.n == x.n && dy.c == x.c && dy.h == x.h / 2 && dy.w == x.w / 2, "maxpool_bwd: dy view mismatch");
+  const long total = (long)x.n * x.h * x.w * (x.c >> 3);
+  maxpool_bwd_kernel<<<ew_blocks(total), 256, 0, (cudaStream_t)stream>>>(
+      (const __nv_bfloat16*)x.ptr, x.ld, x.n, x.h, x.w, x.c, (const __nv_bfloat16*)dy.ptr, dy.ld,
+      (__nv_bfloat16*)dx_accum.ptr, dx_accum.ld, accumulate);
+  UBR_LAUNCH_CHECK("maxpool_bwd_kernel");
+  return 0;
+}
+
+int ubr_add(ubr_view a, ubr_view b, ubr_view c, ubr_view out, void* stream) {
+  if (int rc = ensure_device()) return rc;
+  if (int rc = chk(a, "add.a")) return rc;
+  if (int rc = chk(out, "add.out")) return rc;
+  if (int rc = same_shape(a, out, "add(out)")) return rc;
+  DView vb{nullptr, 0, 0, 0}, vc{nullptr, 0, 0, 0};
+  if (b.ptr) {
+    if (int rc = chk(b, "add.b")) return rc;
+    if (int rc = same_shape(a, b, "add(b)")) return rc;
+    vb = dv(b);
+  }
+  if (c.ptr) {
+    if (int rc = chk(c, "add.c")) return rc;
+    if (int rc = same_shape(a, c, "add(c)")) return rc;
+    vc = dv(c);
+  }
+  DView va = dv(a);
+  add_kernel<<<ew_blocks(va.npix * (va.c >> 3)), 256, 0, (cudaStream_t)stream>>>(va, vb, vc, dvw(out));
+  UBR_LAUNCH_CHECK("add_kernel");
+  return 0;
+}
+
+int ubr_scale_f32(float* buf, uint64_t count, float alpha, void* stream) {
+  if (int rc = ensure_device()) return rc;
+  UBR_REQUIRE(buf != nullptr || count == 0, "scale_f32: null buffer");
+  if (count == 0) return 0;
+  scale_f32_kernel<<<ew_blocks((long)count), 256, 0, (cudaStream_t)stream>>>(buf, (unsigned long long)count, alpha);
+  UBR_LAUNCH_CHECK("scale_f32_kernel");
+  return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,364 @@
+"""Thin torch-tensor wrappers over the C ABI.  Device memory, streams and allocation are PyTorch's;
+every byte of arithmetic happens in libubresnet_b200.so.  No fallback paths.
+"""
+import torch
+
+from . import _lib
+from ._lib import View
+
+BN_EPS = 1e-5
+BN_MOMENTUM = 0.1
+
+
+def _stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _ptr(t):
+    return 0 if t is None else t.data_ptr()
+
+
+def require_cuda(t, name):
+    if not isinstance(t, torch.Tensor) or not t.is_cuda:
+        raise RuntimeError("ubresnet_b200: %s must be a CUDA tensor (there is no CPU path)" % name)
+
+
+class Act:
+    """Channel slice [c0, c0+c) of an NHWC bf16 buffer (N,H,W,LD)."""
+    __slots__ = ("buf", "c0", "c")
+
+    def __init__(self, buf, c0=0, c=None):
+        assert buf.dtype == torch.bfloat16 and buf.dim() == 4 and buf.is_contiguous()
+        self.buf = buf
+        self.c0 = c0
+        self.c = buf.shape[3] - c0 if c is None else c
+        assert 0 <= c0 and c0 + self.c <= buf.shape[3]
+
+    @staticmethod
+    def empty(n, h, w, c, device, ld=None):
+        return Act(torch.empty((n, h, w, ld or c), dtype=torch.bfloat16, device=device), 0, c)
+
+    @staticmethod
+    def zeros(n, h, w, c, device, ld=None):
+        return Act(torch.zeros((n, h, w, ld or c), dtype=torch.bfloat16, device=device), 0, c)
+
+    @property
+    def n(self): return self.buf.shape[0]
+
+    @property
+    def h(self): return self.buf.shape[1]
+
+    @property
+    def w(self): return self.buf.shape[2]
+
+    @property
+    def npix(self): return self.buf.shape[0] * self.buf.shape[1] * self.buf.shape[2]
+
+    def slice(self, c0, c):
+        return Act(self.buf, self.c0 + c0, c)
+
+    def view(self):
+        b = self.buf
+        return View(b.data_ptr() + 2 * self.c0, b.shape[0], b.shape[1], b.shape[2], self.c, b.shape[3])
+
+    def torch(self):
+        return self.buf[..., self.c0:self.c0 + self.c]
+
+    def nchw_float(self):
+        return self.torch().permute(0, 3, 1, 2).float().contiguous()
+
+    @staticmethod
+    def from_nchw(x, ld=None, c0=0):
+        n, c, h, w = x.shape
+        a = Act.zeros(n, h, w, c, x.device, ld=ld) if ld is None else Act(
+            torch.zeros((n, h, w, ld), dtype=torch.bfloat16, device=x.device), c0, c)
+        a.torch().copy_(x.permute(0, 2, 3, 1))
+        return a
+
+
+_NULLVIEW = View(0, 0, 0, 0, 0, 0)
+
+
+# ------------------------------------------------------------------------------------------------
+def pack_weights(w, transposed, n_is_out):
+    """fp32 OIHW (conv) / IOHW (deconv) parameter -> bf16 [taps+1][n_pad][k_pad] GEMM operand."""
+    require_cuda(w, "weight")
+    lib = _lib.load()
+    w = w.detach().contiguous().float()
+    if transposed:
+        in_ch, out_ch, kh, kw = w.shape
+    else:
+        out_ch, in_ch, kh, kw = w.shape
+    nn, kk = (out_ch, in_ch) if n_is_out else (in_ch, out_ch)
+    n_pad, k_pad = (nn + 15) // 16 * 16, (kk + 15) // 16 * 16
+    dst = torch.empty((kh * kw + 1, n_pad, k_pad), dtype=torch.bfloat16, device=w.device)
+    _lib.check(lib.ubr_pack_weights(w.data_ptr(), 1 if transposed else 0, 1 if n_is_out else 0, out_ch, in_ch, kh, kw,
+                                    n_pad, k_pad, dst.data_ptr(), _stream()), "pack_weights")
+    return dst
+
+
+def conv2d_fwd(x, wpk, bias, out_ch, ksize, stride, y=None, y_f32=None):
+    lib = _lib.load()
+    if y_f32 is not None:
+        _lib.check(lib.ubr_conv2d_fwd(x.view(), wpk.data_ptr(), _ptr(bias), out_ch, ksize, stride, _NULLVIEW,
+                                      y_f32.data_ptr(), y_f32.shape[-1], _stream()), "conv2d_fwd")
+        return y_f32
+    if y is None:
+        y = Act.empty(x.n, x.h // stride, x.w // stride, out_ch, x.buf.device)
+    _lib.check(lib.ubr_conv2d_fwd(x.view(), wpk.data_ptr(), _ptr(bias), out_ch, ksize, stride, y.view(), 0, 0,
+                                  _stream()), "conv2d_fwd")
+    return y
+
+
+def conv2d_dgrad(dy, wpk, in_ch, ksize, stride, dx=None):
+    lib = _lib.load()
+    if dx is None:
+        dx = Act.empty(dy.n, dy.h * stride, dy.w * stride, in_ch, dy.buf.device)
+    _lib.check(lib.ubr_conv2d_dgrad(dy.view(), wpk.data_ptr(), in_ch, ksize, stride, dx.view(), _stream()),
+               "conv2d_dgrad")
+    return dx
+
+
+def wgrad_workspace_bytes(grid_n, grid_h, grid_w, m_ch, n_ch, ntaps):
+    return int(_lib.load().ubr_wgrad_workspace_bytes(grid_n, grid_h, grid_w, m_ch, n_ch, ntaps))
+
+
+def conv2d_wgrad(x, dy, out_ch, ksize, stride, dw, accumulate, ws):
+    lib = _lib.load()
+    assert dw.dtype == torch.float32 and dw.is_contiguous()
+    _lib.check(lib.ubr_conv2d_wgrad(x.view(), dy.view(), out_ch, ksize, stride, dw.data_ptr(), int(accumulate),
+                                    ws.data_ptr(), ws.numel() * ws.element_size(), _stream()), "conv2d_wgrad")
+    return dw
+
+
+def deconv_fwd(x, wpk, out_ch, y=None):
+    lib = _lib.load()
+    if y is None:
+        y = Act.empty(x.n, x.h * 2, x.w * 2, out_ch, x.buf.device)
+    _lib.check(lib.ubr_deconv4s2_fwd(x.view(), wpk.data_ptr(), out_ch, y.view(), _stream()), "deconv4s2_fwd")
+    return y
+
+
+def deconv_dgrad(dy, wpk, in_ch, dx=None):
+    lib = _lib.load()
+    if dx is None:
+        dx = Act.empty(dy.n, dy.h // 2, dy.w // 2, in_ch, dy.buf.device)
+    _lib.check(lib.ubr_deconv4s2_dgrad(dy.view(), wpk.data_ptr(), in_ch, dx.view(), _stream()), "deconv4s2_dgrad")
+    return dx
+
+
+def deconv_wgrad(x, dy, dw, accumulate, ws):
+    lib = _lib.load()
+    assert dw.dtype == torch.float32 and dw.is_contiguous()
+    _lib.check(lib.ubr_deconv4s2_wgrad(x.view(), dy.view(), dw.data_ptr(), int(accumulate), ws.data_ptr(),
+                                       ws.numel() * ws.element_size(), _stream()), "deconv4s2_wgrad")
+    return dw
+
+
+def stem_conv_fwd(x, w, b, y=None):
+    """x (N,1,H,W) fp32 CUDA -> NHWC bf16 (N,H,W,OC)."""
+    lib = _lib.load()
+    require_cuda(x, "input")
+    n, cin, h, wd = x.shape
+    assert cin == 1 and x.dtype == torch.float32 and x.is_contiguous()
+    oc = w.shape[0]
+    if y is None:
+        y = Act.empty(n, h, wd, oc, x.device)
+    _lib.check(lib.ubr_stem_conv_fwd(x.data_ptr(), n, h, wd, w.data_ptr(), _ptr(b), oc, y.view(), _stream()),
+               "stem_conv_fwd")
+    return y
+
+
+def stem_wgrad_workspace_bytes(n, h, w, oc):
+    return int(_lib.load().ubr_stem_wgrad_workspace_bytes(n, h, w, oc))
+
+
+def stem_conv_wgrad(x, dy, dw, db, accumulate, ws):
+    lib = _lib.load()
+    n, _, h, wd = x.shape
+    _lib.check(lib.ubr_stem_conv_wgrad(x.data_ptr(), n, h, wd, dy.view(), _ptr(dw), _ptr(db), int(accumulate),
+                                       ws.data_ptr(), ws.numel() * ws.element_size(), _stream()), "stem_conv_wgrad")
+
+
+def bn_workspace(c, device):
+    nbytes = int(_lib.load().ubr_bn_workspace_bytes(c))
+    return torch.empty(nbytes // 4, dtype=torch.float32, device=device)
+
+
+class BNState:
+    """Per-layer affine (scale, shift) plus the batch statistics the backward needs."""
+    __slots__ = ("scale", "shift", "mean", "invstd", "count")
+
+    def __init__(self, c, device):
+        buf = torch.empty((4, c), dtype=torch.float32, device=device)
+        self.scale, self.shift, self.mean, self.invstd = buf[0], buf[1], buf[2], buf[3]
+        self.count = 0.0
+
+
+def bn_train_stats(y, gamma, beta, running_mean, running_var, ws, state=None, momentum=BN_MOMENTUM, eps=BN_EPS):
+    lib = _lib.load()
+    st = state or BNState(y.c, y.buf.device)
+    st.count = float(y.npix)
+    _lib.check(lib.ubr_bn_stats(y.view(), ws.data_ptr(), _stream()), "bn_stats")
+    _lib.check(lib.ubr_bn_finalize(ws.data_ptr(), y.c, st.count, _ptr(gamma), _ptr(beta), _ptr(running_mean),
+                                   _ptr(running_var), momentum, eps, st.scale.data_ptr(), st.shift.data_ptr(),
+                                   st.mean.data_ptr(), st.invstd.data_ptr(), _stream()), "bn_finalize")
+    return st
+
+
+def bn_eval_affine(gamma, beta, running_mean, running_var, state=None, eps=BN_EPS):
+    lib = _lib.load()
+    c = running_mean.numel()
+    st = state or BNState(c, running_mean.device)
+    _lib.check(lib.ubr_bn_eval_affine(c, _ptr(gamma), _ptr(beta), running_mean.data_ptr(), running_var.data_ptr(), eps,
+                                      st.scale.data_ptr(), st.shift.data_ptr(), _stream()), "bn_eval_affine")
+    return st
+
+
+def bn_act(y, st, relu, out=None):
+    lib = _lib.load()
+    if out is None:
+        out = Act.empty(y.n, y.h, y.w, y.c, y.buf.device)
+    _lib.check(lib.ubr_bn_act(y.view(), st.scale.data_ptr(), st.shift.data_ptr(), int(relu), out.view(), _stream()),
+               "bn_act")
+    return out
+
+
+def block_tail(y2, st2, res, st_res, out=None):
+    lib = _lib.load()
+    if out is None:
+        out = Act.empty(y2.n, y2.h, y2.w, y2.c, y2.buf.device)
+    sr = st_res.scale.data_ptr() if st_res is not None else 0
+    br = st_res.shift.data_ptr() if st_res is not None else 0
+    _lib.check(lib.ubr_block_tail(y2.view(), st2.scale.data_ptr(), st2.shift.data_ptr(), res.view(), sr, br, out.view(),
+                                  _stream()), "block_tail")
+    return out
+
+
+def bn_act_bwd(dout, y, st, relu, ws, dgamma=None, dbeta=None, accumulate=False, dy=None):
+    """Backward of out = relu?(bn(y)) in training mode.  Returns dy (grad wrt the conv output y)."""
+    lib = _lib.load()
+    if dy is None:
+        dy = Act.empty(y.n, y.h, y.w, y.c, y.buf.device)
+    s = _stream()
+    _lib.check(lib.ubr_bn_act_bwd_reduce(dout.view(), y.view(), st.scale.data_ptr(), st.shift.data_ptr(),
+                                         st.mean.data_ptr(), st.invstd.data_ptr(), int(relu), ws.data_ptr(), s),
+               "bn_act_bwd_reduce")
+    _lib.check(lib.ubr_bn_act_bwd_apply(dout.view(), y.view(), st.scale.data_ptr(), st.shift.data_ptr(),
+                                        st.mean.data_ptr(), st.invstd.data_ptr(), 0, int(relu), ws.data_ptr(), st.count,
+                                        dy.view(), _ptr(dgamma), _ptr(dbeta), int(accumulate), s), "bn_act_bwd_apply")
+    return dy
+
+
+def block_tail_bwd(dout, out, y2, st2, res, st_res, gamma_res, ws, dgamma2=None, dbeta2=None, dgamma_res=None,
+                   dbeta_res=None, accumulate=False, dy2=None, dres=None):
+    """Backward of the ReLU-add-ReLU block tail.  Returns (dy2, dres)."""
+    lib = _lib.load()
+    dev = y2.buf.device
+    if dy2 is None:
+        dy2 = Act.empty(y2.n, y2.h, y2.w, y2.c, dev)
+    if dres is None:
+        dres = Act.empty(y2.n, y2.h, y2.w, y2.c, dev)
+    s = _stream()
+    res_bn = st_res is not None
+    rv = res.view() if res_bn else _NULLVIEW
+    mr = st_res.mean.data_ptr() if res_bn else 0
+    ir = st_res.invstd.data_ptr() if res_bn else 0
+    _lib.check(lib.ubr_block_tail_bwd_reduce(dout.view(), out.view(), y2.view(), st2.scale.data_ptr(),
+                                             st2.shift.data_ptr(), st2.mean.data_ptr(), st2.invstd.data_ptr(), rv, mr,
+                                             ir, int(res_bn), ws.data_ptr(), s), "block_tail_bwd_reduce")
+    _lib.check(lib.ubr_block_tail_bwd_apply(dout.view(), out.view(), y2.view(), st2.scale.data_ptr(),
+                                            st2.shift.data_ptr(), st2.mean.data_ptr(), st2.invstd.data_ptr(), 0, rv, mr,
+                                            ir, _ptr(gamma_res), int(res_bn), ws.data_ptr(), st2.count, dy2.view(),
+                                            dres.view(), _ptr(dgamma2), _ptr(dbeta2), _ptr(dgamma_res), _ptr(dbeta_res),
+                                            int(accumulate), s), "block_tail_bwd_apply")
+    return dy2, dres
+
+
+def maxpool_fwd(x, y=None):
+    lib = _lib.load()
+    if y is None:
+        y = Act.empty(x.n, x.h // 2, x.w // 2, x.c, x.buf.device)
+    _lib.check(lib.ubr_maxpool3s2_fwd(x.view(), y.view(), _stream()), "maxpool3s2_fwd")
+    return y
+
+
+def maxpool_bwd(x, dy, dx, accumulate):
+    lib = _lib.load()
+    _lib.check(lib.ubr_maxpool3s2_bwd(x.view(), dy.view(), dx.view(), int(accumulate), _stream()), "maxpool3s2_bwd")
+    return dx
+
+
+def add(a, b=None, c=None, out=None):
+    lib = _lib.load()
+    if out is None:
+        out = Act.empty(a.n, a.h, a.w, a.c, a.buf.device)
+    _lib.check(lib.ubr_add(a.view(), b.view() if b is not None else _NULLVIEW,
+                           c.view() if c is not None else _NULLVIEW, out.view(), _stream()), "add")
+    return out
+
+
+def logsoftmax_fwd(logits, n, ncls, h, w):
+    """logits fp32 (N*H*W, LD) -> log-probs fp32 NCHW."""
+    lib = _lib.load()
+    logp = torch.empty((n, ncls, h, w), dtype=torch.float32, device=logits.device)
+    _lib.check(lib.ubr_logsoftmax_fwd(logits.data_ptr(), logits.shape[-1], n, ncls, h * w, logp.data_ptr(), _stream()),
+               "logsoftmax_fwd")
+    return logp
+
+
+def logsoftmax_bwd(logp, dlogp, dl=None):
+    lib = _lib.load()
+    n, ncls, h, w = logp.shape
+    if dl is None:
+        dl = Act.empty(n, h, w, 16, logp.device)
+    dlogp = dlogp.contiguous()
+    _lib.check(lib.ubr_logsoftmax_bwd(logp.data_ptr(), dlogp.data_ptr(), n, ncls, h * w, dl.view(), _stream()),
+               "logsoftmax_bwd")
+    return dl
+
+
+def pixelwise_nll_fwd(logp, target, pixw, classw, ignore_index):
+    lib = _lib.load()
+    n, ncls, h, w = logp.shape
+    ws = torch.empty(int(lib.ubr_nll_workspace_bytes(n, h * w)) // 4, dtype=torch.float32, device=logp.device)
+    loss = torch.empty((), dtype=torch.float32, device=logp.device)
+    _lib.check(lib.ubr_pixelwise_nll_fwd(logp.data_ptr(), target.data_ptr(), pixw.data_ptr(), _ptr(classw), n, ncls,
+                                         h * w, ignore_index, ws.data_ptr(), loss.data_ptr(), _stream()),
+               "pixelwise_nll_fwd")
+    return loss
+
+
+def pixelwise_nll_bwd(target, pixw, classw, gout, n, ncls, h, w, ignore_index):
+    lib = _lib.load()
+    dlogp = torch.empty((n, ncls, h, w), dtype=torch.float32, device=target.device)
+    _lib.check(lib.ubr_pixelwise_nll_bwd(target.data_ptr(), pixw.data_ptr(), _ptr(classw), _ptr(gout), n, ncls, h * w,
+                                         ignore_index, dlogp.data_ptr(), _stream()), "pixelwise_nll_bwd")
+    return dlogp
+
+
+def tile_gather(plane, origins, crop):
+    lib = _lib.load()
+    require_cuda(plane, "plane")
+    rows, cols = plane.shape
+    nt = origins.shape[0]
+    crops = torch.empty((nt, 1, crop, crop), dtype=torch.float32, device=plane.device)
+    _lib.check(lib.ubr_tile_gather(plane.data_ptr(), rows, cols, origins.data_ptr(), nt, crop, crops.data_ptr(),
+                                   _stream()), "tile_gather")
+    return crops
+
+
+def stitch_scatter(tiles, origins, rows, cols):
+    lib = _lib.load()
+    require_cuda(tiles, "tiles")
+    nt, nch, crop, _ = tiles.shape
+    out = torch.empty((nch, rows, cols), dtype=torch.float32, device=tiles.device)
+    _lib.check(lib.ubr_stitch_scatter(tiles.data_ptr(), nch, origins.data_ptr(), nt, crop, rows, cols, out.data_ptr(),
+                                      _stream()), "stitch_scatter")
+    return out
+
+
+def scale_f32_(buf, alpha):
+    lib = _lib.load()
+    _lib.check(lib.ubr_scale_f32(buf.data_ptr(), buf.numel(), float(alpha), _stream()), "scale_f32")
+    return buf
