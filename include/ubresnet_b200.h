@@ -43,6 +43,7 @@ int ubr_abi_version(void);
 const char* ubr_last_error(void);
 int ubr_device_check(void);               /* 0 iff the current CUDA device is sm_100 (B200) */
 int ubr_sync_check(void* stream);         /* cudaStreamSynchronize + surface async errors */
+uint64_t ubr_launch_count(void);          /* kernels launched by this library so far (process wide) */
 
 /* ---- weight packing: fp32 reference layout -> bf16 [tap][n][k] GEMM operand ---------------------
  * replaces the implicit cuDNN filter transforms behind nn.Conv2d / nn.ConvTranspose2d.
@@ -50,7 +51,8 @@ int ubr_sync_check(void* stream);         /* cudaStreamSynchronize + surface asy
  *   src_layout 1: IOHW  (nn.ConvTranspose2d.weight,   models/common_layers.py:125)
  *   n_is_out 1: n = output channel, k = input channel (forward operand)
  *   n_is_out 0: n = input channel,  k = output channel (data-gradient operand)
- * dst has taps = kh*kw slabs of [n_pad][k_pad] (zero padded, n_pad/k_pad multiples of 16). */
+ * dst has kh*kw + 1 slabs of [n_pad][k_pad] (zero padded, n_pad/k_pad multiples of 16); the extra last slab is
+ * all zero (used by stride-2 data-gradient phases that no filter tap reaches). */
 int ubr_pack_weights(const float* src, int src_layout, int n_is_out, int out_ch, int in_ch, int kh, int kw,
                      int n_pad, int k_pad, void* dst_bf16, void* stream);
 

@@ -1,0 +1,77 @@
+"""TEST INFRASTRUCTURE -- generates tests/golden/*.pt FROM THE UNMODIFIED REFERENCE (via reference_shim).
+
+Run inside the build container only (needs /root/reference):  python -m oracle.make_golden
+The fixtures travel to the GPU box, the reference does not.
+"""
+import os
+import sys
+from collections import OrderedDict
+
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+from oracle import reference_shim as shim  # noqa: E402
+from ubresnet_b200 import synthetic  # noqa: E402
+
+GOLD = os.path.join(ROOT, "tests", "golden")
+GRAD_KEYS = ["conv1.weight", "conv1.bias", "bn1.weight", "bn1.bias", "enc_layer1.res1.conv1.weight",
+             "enc_layer1.res1.bypass.weight", "enc_layer2.res1.bnpass.weight", "enc_layer3.res2.bn2.bias",
+             "enc_layer5.res2.bn1.weight", "dec_layer1.deconv.weight", "dec_layer2.res.res1.bn1.weight",
+             "dec_layer1.res.res2.conv2.weight", "conv10.weight", "conv10.bias", "bn10.weight", "conv11.weight",
+             "conv11.bias"]
+
+
+def uresnet_fixture(seed=20180721, batch=2, size=128):
+    torch.manual_seed(seed)
+    model = shim.make_reference_model(3, 1, 16)
+    chk = sum(float(v.double().abs().sum()) for v in model.state_dict().values() if v.is_floating_point())
+    img, lab, wgt = synthetic.make_batch(batch, size, size)
+    model.train()
+    crit = shim.make_reference_criterion()
+    logp = model(img)
+    loss = shim.reference_loss(crit, logp, lab, wgt)
+    loss.backward()
+    params = dict(model.named_parameters())
+    grads = OrderedDict((k, params[k].grad.clone()) for k in GRAD_KEYS)
+    gnorm = OrderedDict((k, float(p.grad.abs().max())) for k, p in params.items())
+    sd = model.state_dict()
+    running = OrderedDict((k, sd[k].clone()) for k in ("bn1.running_mean", "bn1.running_var",
+                                                        "enc_layer5.res2.bn2.running_var", "bn10.running_mean"))
+    model.eval()
+    with torch.no_grad():
+        logp_eval = model(img)
+    return dict(seed=seed, image=img, label=lab, weight=wgt, logp=logp.detach(), loss=float(loss), grads=grads,
+                grad_absmax=gnorm, weight_abs_sum=chk, running=running, logp_eval=logp_eval,
+                note="generated from /root/reference (commit 3491bf2) through oracle/reference_shim.py")
+
+
+def loss_fixture(seed=7):
+    g = torch.Generator().manual_seed(seed)
+    logits = torch.randn(2, 3, 24, 40, generator=g) * 2
+    logp = torch.log_softmax(logits, 1).requires_grad_(True)
+    tgt = torch.randint(0, 3, (2, 24, 40), generator=g)
+    tgt[1, 3, :7] = -100
+    pw = torch.rand(2, 24, 40, generator=g) * 50 + 1
+    out = {}
+    for tag, cw in (("plain", None), ("classw", torch.tensor([0.3, 1.0, 2.5]))):
+        crit = shim.make_reference_criterion(weight=cw)
+        if logp.grad is not None:
+            logp.grad = None
+        loss = shim.reference_loss(crit, logp, tgt, pw)
+        loss.backward()
+        out[tag] = dict(loss=float(loss), dlogp=logp.grad.clone(), classw=cw)
+    return dict(logp=logp.detach(), target=tgt, pixelweights=pw, cases=out)
+
+
+def main():
+    os.makedirs(GOLD, exist_ok=True)
+    torch.save(uresnet_fixture(), os.path.join(GOLD, "uresnet_b2_128.pt"))
+    torch.save(loss_fixture(), os.path.join(GOLD, "pixelwise_nll.pt"))
+    for f in sorted(os.listdir(GOLD)):
+        print(f, os.path.getsize(os.path.join(GOLD, f)))
+
+
+if __name__ == "__main__":
+    main()

@@ -63,9 +63,34 @@ def inventory(num_classes=3, input_channels=1, inplanes=16, final_conv_kernels=1
     return ents
 
 
+class _RoundBF16(torch.autograd.Function):
+    """bf16 storage emulation: round the value forward and the gradient backward (used only by the
+    `quant=True` diagnostic mode that mimics where the CUDA pipeline stores bf16)."""
+
+    @staticmethod
+    def forward(ctx, t):
+        return t.to(torch.bfloat16).to(torch.float32)
+
+    @staticmethod
+    def backward(ctx, g):
+        return g.to(torch.bfloat16).to(torch.float32)
+
+
+_QUANT = [False]
+
+
+def _q(t):
+    return _RoundBF16.apply(t) if _QUANT[0] else t
+
+
 def _bn(x, sd, name, training):
     return F.batch_norm(x, sd[name + ".running_mean"], sd[name + ".running_var"],
                         sd[name + ".weight"], sd[name + ".bias"], training, BN_MOMENTUM, BN_EPS)
+
+
+def _qw(w):
+    """weights are used as bf16 GEMM operands by the CUDA path (no gradient rounding: wgrad is fp32)"""
+    return (w + (w.detach().to(torch.bfloat16).to(torch.float32) - w.detach())) if _QUANT[0] else w
 
 
 def _bump(sd, name, training):
@@ -75,16 +100,16 @@ def _bump(sd, name, training):
 
 def _res_block(x, sd, pre, stride, training, taps):
     # common_layers.py:39-58 -- note relu2 BEFORE the add, and a second ReLU after it
-    y = F.conv2d(x, sd[pre + "conv1.weight"], None, stride, 1)
-    y = F.relu(_bn(y, sd, pre + "bn1", training)); _bump(sd, pre + "bn1", training)
-    y = F.conv2d(y, sd[pre + "conv2.weight"], None, 1, 1)
+    y = _q(F.conv2d(x, _qw(sd[pre + "conv1.weight"]), None, stride, 1))
+    y = _q(F.relu(_bn(y, sd, pre + "bn1", training))); _bump(sd, pre + "bn1", training)
+    y = _q(F.conv2d(y, _qw(sd[pre + "conv2.weight"]), None, 1, 1))
     y = F.relu(_bn(y, sd, pre + "bn2", training)); _bump(sd, pre + "bn2", training)
     if (pre + "bypass.weight") in sd:
-        s = F.conv2d(x, sd[pre + "bypass.weight"], None, stride, 0)
+        s = _q(F.conv2d(x, _qw(sd[pre + "bypass.weight"]), None, stride, 0))
         s = _bn(s, sd, pre + "bnpass", training); _bump(sd, pre + "bnpass", training)
     else:
         s = x
-    out = F.relu(y + s)
+    out = _q(F.relu(y + s))
     if taps is not None:
         taps[pre[:-1]] = out
     return out
@@ -95,14 +120,22 @@ def _double(x, sd, pre, stride, training, taps):
     return _res_block(x, sd, pre + "res2.", 1, training, taps)
 
 
-def forward(sd, x, training=True, taps=None, return_logits=False):
+def forward(sd, x, training=True, taps=None, return_logits=False, quant=False):
+    _QUANT[0] = bool(quant)
+    try:
+        return _forward(sd, x, training, taps, return_logits)
+    finally:
+        _QUANT[0] = False
+
+
+def _forward(sd, x, training=True, taps=None, return_logits=False):
     """log-probabilities (B,C,H,W) exactly as UResNet.forward (ub_uresnet.py:88-147).
 
     `sd` maps reference state_dict names to tensors; BN running buffers are updated in place
     when `training`.  `taps` (optional dict) receives intermediate activations by name.
     """
-    y = F.conv2d(x, sd["conv1.weight"], sd["conv1.bias"], 1, 3)
-    x0 = F.relu(_bn(y, sd, "bn1", training)); _bump(sd, "bn1", training)
+    y = _q(F.conv2d(x, sd["conv1.weight"], sd["conv1.bias"], 1, 3))
+    x0 = _q(F.relu(_bn(y, sd, "bn1", training))); _bump(sd, "bn1", training)
     h = F.max_pool2d(x0, 3, 2, 1)
     if taps is not None:
         taps["x0"] = x0
@@ -113,13 +146,13 @@ def forward(sd, x, training=True, taps=None, return_logits=False):
     for i in (5, 4, 3, 2, 1):
         skip = skips[i - 1]
         # ConvTranspose2d(k4,s2,p1) with output_size == skip size -> output_padding 0 (common_layers.py:128)
-        up = F.conv_transpose2d(h, sd["dec_layer%d.deconv.weight" % i], None, 2, 1)
+        up = _q(F.conv_transpose2d(h, _qw(sd["dec_layer%d.deconv.weight" % i]), None, 2, 1))
         assert up.shape[-2:] == skip.shape[-2:]
         h = torch.cat([up, skip], 1)                           # [deconv, skip]  (common_layers.py:130)
         h = _double(h, sd, "dec_layer%d.res." % i, 1, training, taps)
-    h = F.conv2d(h, sd["conv10.weight"], sd["conv10.bias"], 1, 3)
-    h = F.relu(_bn(h, sd, "bn10", training)); _bump(sd, "bn10", training)
-    logits = F.conv2d(h, sd["conv11.weight"], sd["conv11.bias"], 1, 3)
+    h = _q(F.conv2d(h, _qw(sd["conv10.weight"]), sd["conv10.bias"], 1, 3))
+    h = _q(F.relu(_bn(h, sd, "bn10", training))); _bump(sd, "bn10", training)
+    logits = F.conv2d(h, _qw(sd["conv11.weight"]), sd["conv11.bias"], 1, 3)
     if taps is not None:
         taps["logits"] = logits
     logp = F.log_softmax(logits, dim=1)
@@ -176,10 +209,11 @@ def clone_state_dict(sd, requires_grad=False):
     return out
 
 
-def train_step_grads(sd, x, target, pixelweights, class_weight=None):
-    """fwd + loss + bwd; returns (loss, logp, grads dict, updated-buffer state_dict)."""
+def train_step_grads(sd, x, target, pixelweights, class_weight=None, quant=False):
+    """fwd + loss + bwd; returns (loss, logp, grads dict, updated-buffer state_dict).
+    quant=True: diagnostic bf16-storage emulation (NOT the parity oracle)."""
     work = clone_state_dict(sd, requires_grad=True)
-    logp = forward(work, x, training=True)
+    logp = forward(work, x, training=True, quant=quant)
     loss = pixelwise_nll(logp, target, pixelweights, class_weight)
     loss.backward()
     grads = OrderedDict((k, v.grad.detach()) for k, v in work.items() if v.requires_grad)

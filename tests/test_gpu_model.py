@@ -1,0 +1,56 @@
+"""-m gpu: whole-network parity (forward, loss, backward, BN buffers) through the public nn.Module API."""
+import pytest
+import torch
+
+from tests import model_checks
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("name", list(model_checks.CHECKS))
+def test_model(name):
+    results, _ = model_checks.CHECKS[name]()
+    bad = [(lbl, err, tol) for lbl, err, tol in results if not err <= tol]
+    assert not bad, "parity failures: %s" % bad
+
+
+def test_cpu_input_raises():
+    from ubresnet_b200.models import UResNet
+    m = UResNet(3, 1, 16).cuda()
+    with pytest.raises(RuntimeError):
+        m(torch.zeros(1, 1, 64, 64))
+
+
+def test_checkpoint_roundtrip_and_deploy_loader(tmp_path):
+    """reference checkpoint dict layout (train_ubresnet2018_wlarcv2.py:260-266) incl. DataParallel `module.` prefix"""
+    from collections import OrderedDict
+    from ubresnet_b200.deploy.ubresnet_funcs import load_cosmic_retrain_model
+    from ubresnet_b200.models import UResNet
+    torch.manual_seed(3)
+    m = UResNet(num_classes=4, input_channels=1, inplanes=16)
+    sd = OrderedDict(("module." + k, v) for k, v in m.state_dict().items())
+    path = str(tmp_path / "checkpoint.0th.tar")
+    torch.save({"iter": 0, "epoch": 0, "state_dict": sd, "best_prec1": 0.0, "optimizer": {}}, path)
+    m2 = load_cosmic_retrain_model(path, device="cuda:0").to("cuda:0").eval()
+    x = torch.randn(1, 1, 64, 64, device="cuda:0")
+    with torch.no_grad():
+        a = m.to("cuda:0").eval()(x)
+        b = m2(x)
+    assert a.shape == (1, 4, 64, 64)
+    assert torch.equal(a, b)
+    assert torch.allclose(a.exp().sum(1), torch.ones_like(a[:, 0]), atol=1e-4)
+
+
+def test_wholeview_deploy_bitexact_tiling():
+    from oracle import uresnet_port as port
+    from ubresnet_b200 import synthetic
+    from ubresnet_b200.deploy import wholeview
+    ev = synthetic.make_wholeview(rows=256, cols=448, planes=1)
+    plan = wholeview.tile_plan(256, 448, 128)
+    assert plan == [(r, c) for r in port.tile_starts(256, 128) for c in port.tile_starts(448, 128)]
+    crops = wholeview.gather(ev[0].cuda(), plan, 128)
+    ref = port.tile_gather_np(ev[0].numpy(), plan, 128)
+    assert (crops[:, 0].cpu().numpy() == ref).all()
+    tiles = torch.randn(len(plan), 3, 128, 128)
+    st = wholeview.stitch(tiles.cuda(), plan, 256, 448)
+    assert (st.cpu().numpy() == port.stitch_scatter_np(tiles.numpy(), plan, 256, 448)).all()

@@ -23,6 +23,7 @@ SIGNATURES = {
     "ubr_last_error": (C.c_char_p, []),
     "ubr_device_check": (_i, []),
     "ubr_sync_check": (_i, [_vp]),
+    "ubr_launch_count": (_u64, []),
     "ubr_pack_weights": (_i, [_vp, _i, _i, _i, _i, _i, _i, _i, _i, _vp, _vp]),
     "ubr_conv2d_fwd": (_i, [View, _vp, _vp, _i, _i, _i, View, _vp, _i, _vp]),
     "ubr_conv2d_dgrad": (_i, [View, _vp, _i, _i, _i, View, _vp]),
@@ -79,6 +80,54 @@ def load():
         raise RuntimeError("ubresnet_b200: ABI version mismatch")
     _lib = lib
     return lib
+
+
+class TimedLib:
+    """Profiling proxy: brackets every C-ABI call with CUDA events on the launching (current) stream.
+    Used by bench.py for the live per-kernel-class timings behind the `roofline` object."""
+
+    def __init__(self, lib):
+        self._lib = lib
+        self.records = []          # (function name, start event, end event)
+
+    def __getattr__(self, name):
+        fn = getattr(self._lib, name)
+        if not name.startswith("ubr_") or name in ("ubr_last_error", "ubr_abi_version", "ubr_launch_count") \
+                or name.endswith("_bytes"):
+            return fn
+        import torch
+
+        def timed(*args):
+            e0 = torch.cuda.Event(enable_timing=True)
+            e1 = torch.cuda.Event(enable_timing=True)
+            e0.record()
+            rc = fn(*args)
+            e1.record()
+            self.records.append((name, e0, e1))
+            return rc
+        return timed
+
+    def summary(self):
+        """{function name: (calls, total ms)} -- call after torch.cuda.synchronize()."""
+        out = {}
+        for name, e0, e1 in self.records:
+            c, t = out.get(name, (0, 0.0))
+            out[name] = (c + 1, t + e0.elapsed_time(e1))
+        return out
+
+
+def enable_profiling():
+    global _lib
+    lib = load()
+    if not isinstance(lib, TimedLib):
+        _lib = TimedLib(lib)
+    return _lib
+
+
+def disable_profiling():
+    global _lib
+    if isinstance(_lib, TimedLib):
+        _lib = _lib._lib
 
 
 def last_error():

@@ -1,6 +1,7 @@
 // Library plumbing: error reporting, device gating, TMA descriptor encoding.
 #include <stdarg.h>
 #include <string.h>
+#include <atomic>
 #include <mutex>
 #include "common.cuh"
 
@@ -19,6 +20,9 @@ int cuda_fail(cudaError_t e, const char* what) {
   set_error("CUDA error %d (%s) at %s", (int)e, cudaGetErrorString(e), what);
   return UBR_E_CUDA;
 }
+
+static std::atomic<unsigned long long> g_launches{0};
+void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
 
 static int g_dev_ok[64];       // 0 unknown, 1 ok, -1 unsupported
 static int g_sm_count[64];
@@ -101,6 +105,8 @@ extern "C" {
 int ubr_abi_version(void) { return UBR_ABI_VERSION; }
 const char* ubr_last_error(void) { return ubr::g_err; }
 int ubr_device_check(void) { return ubr::ensure_device(); }
+
+uint64_t ubr_launch_count(void) { return (uint64_t)ubr::g_launches.load(); }
 
 int ubr_sync_check(void* stream) {
   cudaError_t e = cudaStreamSynchronize((cudaStream_t)stream);

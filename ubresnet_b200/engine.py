@@ -1,0 +1,369 @@
+"""Whole-network kernel schedule for the U-ResNet (forward, backward) on top of the C-ABI ops.
+
+The reference runs 58 convolutions, 52 BatchNorms, 62 ReLUs, 5 concats, ... as separate torch.nn library calls
+under autograd (models/ub_uresnet.py:88-147, models/common_layers.py:39-58,127-132).  Here the whole network is
+ONE autograd node: `Engine.forward` launches the sm_100a kernels in order and records the few tensors the
+hand-written backward needs; `Engine.backward` replays the network in reverse (dgrad / wgrad GEMMs, fused
+BN+ReLU backward, block-tail backward) and hands PyTorch one gradient per parameter.
+
+Data layout: activations NHWC bf16; `torch.cat([deconv, skip], 1)` is zero-copy -- encoder outputs and deconv
+outputs are written directly into channel slices of the decoder's concat buffer.  Parameters stay fp32 in the
+reference layouts (state_dict compatibility); bf16 GEMM operand copies are re-derived when a parameter changes.
+"""
+import torch
+
+from . import ops
+from .ops import Act
+
+
+class _ConvW:
+    """bf16 packed operands of one conv / deconv parameter, refreshed when the parameter changes."""
+    __slots__ = ("param", "transposed", "fwd", "dgrad", "_key")
+
+    def __init__(self, param, transposed=False):
+        self.param = param
+        self.transposed = transposed
+        self.fwd = None
+        self.dgrad = None
+        self._key = None
+
+    def refresh(self, need_dgrad):
+        key = (self.param.data_ptr(), self.param._version)
+        if key != self._key:
+            self.fwd = ops.pack_weights(self.param, self.transposed, True)
+            self.dgrad = None
+            self._key = key
+        if need_dgrad and self.dgrad is None:
+            self.dgrad = ops.pack_weights(self.param, self.transposed, False)
+
+
+class _BlockRec:
+    __slots__ = ("x", "y1", "st1", "a1", "y2", "st2", "yb", "stb", "out")
+
+
+class Engine:
+    def __init__(self, model):
+        self.model = model
+        self._packs = {}
+        self._ws = None
+        self._ws_key = None
+        self.grad_sink = None      # optional data-parallel gradient sink (ubresnet_b200.parallel.GradBuckets)
+
+    # ------------------------------------------------------------------ helpers
+    def _pack(self, conv, need_dgrad, transposed=False):
+        ent = self._packs.get(id(conv))
+        if ent is None or ent.param is not conv.weight:
+            ent = _ConvW(conv.weight, transposed)
+            self._packs[id(conv)] = ent
+        ent.refresh(need_dgrad)
+        return ent
+
+    def _workspaces(self, n, h, w, device):
+        """(bn workspace, wgrad workspace, stem workspace) sized for the largest layer."""
+        m = self.model
+        key = (n, h, w, str(device), m.inplanes)
+        if self._ws_key == key:
+            return self._ws
+        p = m.inplanes
+        cmax = 32 * p
+        bn_ws = ops.bn_workspace(max(cmax, 16), device)
+        need = 0
+        # (grid_n, grid_h, grid_w, m_ch, n_ch, taps) for every wgrad GEMM in the net
+        pad16 = lambda v: (v + 15) // 16 * 16
+        shapes = [(n, h, w, pad16(m.nkernels), p, 49), (n, h, w, 16, pad16(m.nkernels), 49)]
+        for i in range(1, 6):                      # encoder stage i works at H/2^i
+            ci, co = p * 2 ** (i - 1), p * 2 ** i
+            hi, wi = h // 2 ** i, w // 2 ** i
+            shapes += [(n, hi, wi, co, ci, 9), (n, hi, wi, co, co, 9), (n, hi, wi, co, ci, 1)]
+        for i in (5, 4, 3, 2, 1):                  # decoder stage i: deconv input at H/2^i, blocks at H/2^(i-1)
+            ci, cd = p * 2 ** i, p * 2 ** (i - 1)
+            hin, win = h // 2 ** i, w // 2 ** i
+            shapes += [(n, hin, win, ci, cd, 16), (n, 2 * hin, 2 * win, cd, 2 * cd, 9), (n, 2 * hin, 2 * win, cd, cd, 9),
+                       (n, 2 * hin, 2 * win, cd, 2 * cd, 1)]
+        for s_ in shapes:
+            need = max(need, ops.wgrad_workspace_bytes(*s_))
+        wg_ws = torch.empty(need // 4 + 64, dtype=torch.float32, device=device)
+        stem_ws = torch.empty(ops.stem_wgrad_workspace_bytes(n, h, w, p) // 4 + 16, dtype=torch.float32, device=device)
+        self._ws = (bn_ws, wg_ws, stem_ws)
+        self._ws_key = key
+        return self._ws
+
+    @staticmethod
+    def _bn(y, bn, training, bn_ws):
+        if training:
+            st = ops.bn_train_stats(y, bn.weight, bn.bias, bn.running_mean, bn.running_var, bn_ws,
+                                    momentum=bn.momentum if bn.momentum is not None else 0.1, eps=bn.eps)
+        else:
+            st = ops.bn_eval_affine(bn.weight, bn.bias, bn.running_mean, bn.running_var, eps=bn.eps)
+            st.count = float(y.npix)
+        return st
+
+    # ------------------------------------------------------------------ forward pieces
+    def _block_fwd(self, blk, x, out, training, need_grad, bn_ws):
+        rec = _BlockRec()
+        cout = blk.conv1.out_channels
+        s = blk.stride
+        w1 = self._pack(blk.conv1, need_grad)
+        w2 = self._pack(blk.conv2, need_grad)
+        y1 = ops.conv2d_fwd(x, w1.fwd, None, cout, 3, s)
+        st1 = self._bn(y1, blk.bn1, training, bn_ws)
+        a1 = ops.bn_act(y1, st1, True)
+        y2 = ops.conv2d_fwd(a1, w2.fwd, None, cout, 3, 1)
+        st2 = self._bn(y2, blk.bn2, training, bn_ws)
+        if blk.bypass is not None:
+            wb = self._pack(blk.bypass, need_grad)
+            yb = ops.conv2d_fwd(x, wb.fwd, None, cout, 1, s)
+            stb = self._bn(yb, blk.bnpass, training, bn_ws)
+            out = ops.block_tail(y2, st2, yb, stb, out)
+        else:
+            yb, stb = None, None
+            out = ops.block_tail(y2, st2, x, None, out)
+        if need_grad:
+            rec.x, rec.y1, rec.st1, rec.a1, rec.y2, rec.st2, rec.yb, rec.stb, rec.out = x, y1, st1, a1, y2, st2, yb, stb, out
+        return out, rec
+
+    def _double_fwd(self, dbl, x, out, training, need_grad, bn_ws):
+        mid, r1 = self._block_fwd(dbl.res1, x, None, training, need_grad, bn_ws)
+        o, r2 = self._block_fwd(dbl.res2, mid, out, training, need_grad, bn_ws)
+        return o, (r1, r2)
+
+    def forward(self, x):
+        m = self.model
+        ops.require_cuda(x, "UResNet input")
+        if x.dim() != 4 or x.shape[1] != m.conv1.in_channels:
+            raise RuntimeError("UResNet: expected input (B,%d,H,W), got %s" % (m.conv1.in_channels, tuple(x.shape)))
+        if m.conv1.in_channels != 1:
+            raise RuntimeError("ubresnet_b200: only input_channels=1 (wire-plane crops) is implemented")
+        if m.inplanes % 16 != 0:
+            raise RuntimeError("ubresnet_b200: inplanes must be a multiple of 16 (tensor-core tile width)")
+        if x.shape[2] % 32 or x.shape[3] % 32:
+            raise RuntimeError("UResNet: H and W must be multiples of 32 (5 stride-2 stages), got %dx%d" % tuple(x.shape[2:]))
+        if m.conv1.weight.device != x.device:
+            raise RuntimeError("UResNet: parameters on %s but input on %s" % (m.conv1.weight.device, x.device))
+        need_grad = torch.is_grad_enabled() and m.training and any(p.requires_grad for p in m.parameters())
+        with torch.cuda.device(x.device):
+            if need_grad:
+                params = [p for p in m.parameters()]
+                return _UResNetFn.apply(self, x, *params)
+            with torch.no_grad():
+                logp, _ = self._forward_impl(x.detach(), m.training, False)
+            return logp
+
+    def _forward_impl(self, x, training, need_grad):
+        m = self.model
+        x = x.contiguous().float()
+        n, _, h, w = x.shape
+        dev = x.device
+        p = m.inplanes
+        bn_ws, _, _ = self._workspaces(n, h, w, dev)
+        saved = {}
+        # concat buffers: cat[i] feeds dec_layer{i}; channels [0,Cd) deconv output, [Cd,2Cd) skip x_{i-1}
+        cat = {}
+        for i in (1, 2, 3, 4, 5):
+            cd = p * 2 ** (i - 1)
+            hh, ww = (h, w) if i == 1 else (h // 2 ** (i - 1), w // 2 ** (i - 1))
+            cat[i] = torch.empty((n, hh, ww, 2 * cd), dtype=torch.bfloat16, device=dev)
+        # ---- stem (ub_uresnet.py:94-97)
+        y0 = ops.stem_conv_fwd(x, m.conv1.weight, m.conv1.bias)
+        st0 = self._bn(y0, m.bn1, training, bn_ws)
+        x0 = ops.bn_act(y0, st0, True, out=Act(cat[1], p, p))
+        h0 = ops.maxpool_fwd(x0)
+        # ---- encoder (:103-107)
+        recs = {}
+        cur = h0
+        for i in range(1, 6):
+            co = p * 2 ** i
+            out = Act(cat[i + 1], co, co) if i < 5 else None
+            cur, recs["enc%d" % i] = self._double_fwd(getattr(m, "enc_layer%d" % i), cur, out, training, need_grad, bn_ws)
+        # ---- decoder (:116-133; common_layers.py:127-132)
+        dec_in = {}
+        for i in (5, 4, 3, 2, 1):
+            layer = getattr(m, "dec_layer%d" % i)
+            cd = p * 2 ** (i - 1)
+            wd = self._pack(layer.deconv, need_grad, transposed=True)
+            ops.deconv_fwd(cur, wd.fwd, cd, y=Act(cat[i], 0, cd))
+            dec_in[i] = cur
+            cur, recs["dec%d" % i] = self._double_fwd(layer.res, Act(cat[i]), None, training, need_grad, bn_ws)
+        # ---- head (:137-143)
+        w10 = self._pack(m.conv10, need_grad)
+        y10 = ops.conv2d_fwd(cur, w10.fwd, m.conv10.bias, m.nkernels, 7, 1)
+        st10 = self._bn(y10, m.bn10, training, bn_ws)
+        a10 = ops.bn_act(y10, st10, True)
+        w11 = self._pack(m.conv11, need_grad)
+        ncls = m.conv11.out_channels
+        ld = 4 if ncls <= 4 else 16
+        logits = torch.empty((n * h * w, ld), dtype=torch.float32, device=dev)
+        ops.conv2d_fwd(a10, w11.fwd, m.conv11.bias, ncls, 7, 1, y_f32=logits)
+        logp = ops.logsoftmax_fwd(logits, n, ncls, h, w)
+        if training:
+            with torch.no_grad():
+                bns = [mod.num_batches_tracked for mod in m.modules()
+                       if isinstance(mod, torch.nn.BatchNorm2d) and mod.num_batches_tracked is not None]
+                if bns:
+                    torch._foreach_add_(bns, 1)
+        if need_grad:
+            saved.update(x=x, y0=y0, st0=st0, x0=x0, h0=h0, recs=recs, dec_in=dec_in, d1=cur, y10=y10, st10=st10,
+                         a10=a10, logp=logp, shape=(n, h, w))
+        return logp, saved
+
+    # ------------------------------------------------------------------ backward pieces
+    def _block_bwd(self, blk, rec, dout, grads, bn_ws, wg_ws, extra=None, need_dx=True):
+        """Returns grad wrt the block input (optionally + `extra`, a same-shape Act)."""
+        cout = blk.conv1.out_channels
+        cin = blk.conv1.in_channels
+        s = blk.stride
+        g = grads
+        has_bp = blk.bypass is not None
+        dy2, dres = ops.block_tail_bwd(
+            dout, rec.out, rec.y2, rec.st2, rec.yb if has_bp else None, rec.stb, blk.bnpass.weight if has_bp else None,
+            bn_ws, g[blk.bn2.weight], g[blk.bn2.bias], g[blk.bnpass.weight] if has_bp else None,
+            g[blk.bnpass.bias] if has_bp else None)
+        w2 = self._pack(blk.conv2, True)
+        ops.conv2d_wgrad(rec.a1, dy2, cout, 3, 1, g[blk.conv2.weight], False, wg_ws)
+        da1 = ops.conv2d_dgrad(dy2, w2.dgrad, cout, 3, 1)
+        del dy2
+        dy1 = ops.bn_act_bwd(da1, rec.y1, rec.st1, True, bn_ws, g[blk.bn1.weight], g[blk.bn1.bias])
+        del da1
+        ops.conv2d_wgrad(rec.x, dy1, cout, 3, s, g[blk.conv1.weight], False, wg_ws)
+        if has_bp:
+            ops.conv2d_wgrad(rec.x, dres, cout, 1, s, g[blk.bypass.weight], False, wg_ws)
+        if not need_dx:
+            return None
+        w1 = self._pack(blk.conv1, True)
+        dx1 = ops.conv2d_dgrad(dy1, w1.dgrad, cin, 3, s)
+        if has_bp:
+            wb = self._pack(blk.bypass, True)
+            dxb = ops.conv2d_dgrad(dres, wb.dgrad, cin, 1, s)
+            return ops.add(dx1, dxb, extra, out=dx1)
+        return ops.add(dx1, dres, extra, out=dx1)
+
+    def _double_bwd(self, dbl, recs, dout, grads, bn_ws, wg_ws, extra=None):
+        r1, r2 = recs
+        dmid = self._block_bwd(dbl.res2, r2, dout, grads, bn_ws, wg_ws)
+        return self._block_bwd(dbl.res1, r1, dmid, grads, bn_ws, wg_ws, extra=extra)
+
+    def backward(self, saved, dlogp):
+        """dlogp: (B,C,H,W) fp32 grad wrt the log-probabilities.  Returns {param: fp32 grad}."""
+        m = self.model
+        n, h, w = saved["shape"]
+        dev = dlogp.device
+        p = m.inplanes
+        bn_ws, wg_ws, stem_ws = self._workspaces(n, h, w, dev)
+        sink = self.grad_sink
+        if sink is not None:
+            grads = {prm: sink.grad_buffer(prm) for prm in m.parameters()}
+        else:
+            grads = {prm: torch.empty_like(prm, dtype=torch.float32) for prm in m.parameters()}
+        done = sink.stage_done if sink is not None else (lambda name: None)
+        ncls = m.conv11.out_channels
+        # ---- head
+        dl = ops.logsoftmax_bwd(saved["logp"], dlogp.float())
+        ops.conv2d_wgrad(saved["a10"], dl, ncls, 7, 1, grads[m.conv11.weight], False, wg_ws)
+        grads[m.conv11.bias].copy_(_channel_sum(dl, ncls))
+        w11 = self._pack(m.conv11, True)
+        da10 = ops.conv2d_dgrad(dl, w11.dgrad, m.nkernels, 7, 1)
+        del dl
+        dy10 = ops.bn_act_bwd(da10, saved["y10"], saved["st10"], True, bn_ws, grads[m.bn10.weight], grads[m.bn10.bias])
+        del da10
+        ops.conv2d_wgrad(saved["d1"], dy10, m.nkernels, 7, 1, grads[m.conv10.weight], False, wg_ws)
+        grads[m.conv10.bias].copy_(_channel_sum(dy10, m.nkernels))
+        w10 = self._pack(m.conv10, True)
+        dcur = ops.conv2d_dgrad(dy10, w10.dgrad, p, 7, 1)
+        del dy10
+        done("head")
+        # ---- decoder, shallow to deep
+        recs = saved["recs"]
+        dskip = {}
+        for i in (1, 2, 3, 4, 5):
+            layer = getattr(m, "dec_layer%d" % i)
+            cd = p * 2 ** (i - 1)
+            dcat = self._double_bwd(layer.res, recs["dec%d" % i], dcur, grads, bn_ws, wg_ws)
+            ddec = dcat.slice(0, cd)
+            dskip[i - 1] = dcat.slice(cd, cd)                      # grad wrt x_{i-1}
+            xin = saved["dec_in"][i]
+            ops.deconv_wgrad(xin, ddec, grads[layer.deconv.weight], False, wg_ws)
+            wd = self._pack(layer.deconv, True, transposed=True)
+            dcur = ops.deconv_dgrad(ddec, wd.dgrad, p * 2 ** i)
+            done("dec%d" % i)
+        # ---- encoder, deep to shallow: grad(x_i) = (from enc_{i+1} | dec5 deconv) + skip grad
+        for i in (5, 4, 3, 2, 1):
+            extra = dskip[i - 1] if i > 1 else None
+            dcur = self._double_bwd(getattr(m, "enc_layer%d" % i), recs["enc%d" % i], dcur, grads, bn_ws, wg_ws,
+                                    extra=extra)
+            done("enc%d" % i)
+        # ---- stem: x0 gets the pool gradient plus the dec1 skip gradient (accumulated in place)
+        dx0 = dskip[0]
+        ops.maxpool_bwd(saved["x0"], dcur, dx0, True)
+        dy0 = ops.bn_act_bwd(dx0, saved["y0"], saved["st0"], True, bn_ws, grads[m.bn1.weight], grads[m.bn1.bias])
+        ops.stem_conv_wgrad(saved["x"], dy0, grads[m.conv1.weight], grads[m.conv1.bias], False, stem_ws)
+        done("stem")
+        if sink is not None:
+            sink.finish()
+        return grads
+
+
+def _channel_sum(a, nvalid):
+    """per-channel sum over pixels of an Act (bias gradients): tiny, done with the BN statistics kernels."""
+    dev = a.buf.device
+    ws = ops.bn_workspace(a.c, dev)
+    st = ops.BNState(a.c, dev)
+    lib = ops._lib.load()
+    ops._lib.check(lib.ubr_bn_stats(a.view(), ws.data_ptr(), ops._stream()), "bn_stats")
+    # finalize with gamma = beta = NULL: mean = sum / count
+    ops._lib.check(lib.ubr_bn_finalize(ws.data_ptr(), a.c, float(a.npix), 0, 0, 0, 0, 0.0, 1e-5, st.scale.data_ptr(),
+                                       st.shift.data_ptr(), st.mean.data_ptr(), st.invstd.data_ptr(), ops._stream()),
+                   "bn_finalize")
+    return (st.mean * float(a.npix))[:nvalid]
+
+
+class _UResNetFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, engine, x, *params):
+        logp, saved = engine._forward_impl(x.detach(), True, True)
+        ctx.engine = engine
+        ctx.saved = saved
+        ctx.nparams = len(params)
+        return logp
+
+    @staticmethod
+    def backward(ctx, dlogp):
+        engine = ctx.engine
+        saved = ctx.saved
+        ctx.saved = None
+        with torch.cuda.device(dlogp.device):
+            grads = engine.backward(saved, dlogp.contiguous())
+        out = [grads[p] if p.requires_grad else None for p in engine.model.parameters()]
+        return (None, None) + tuple(out)
+
+
+# ------------------------------------------------------------------------------------------------
+# stand-alone sub-module execution (BasicBlock / DoubleResNet / ConvTransposeLayer called directly).
+# Inference-style (no autograd through the block): the reference scripts never call blocks on their own.
+# ------------------------------------------------------------------------------------------------
+def run_submodule(module, *inputs):
+    from .models.common_layers import BasicBlock, ConvTransposeLayer, DoubleResNet
+    x = inputs[0]
+    ops.require_cuda(x, type(module).__name__ + " input")
+    if torch.is_grad_enabled() and module.training and any(p.requires_grad for p in module.parameters()):
+        raise RuntimeError("ubresnet_b200: autograd through a stand-alone %s is not supported; call the whole "
+                           "UResNet (one fused autograd node)" % type(module).__name__)
+    eng = Engine(module)
+    with torch.no_grad(), torch.cuda.device(x.device):
+        bn_ws = ops.bn_workspace(4096, x.device)
+        xa = Act.from_nchw(x.float())
+        if isinstance(module, BasicBlock):
+            out, _ = eng._block_fwd(module, xa, None, module.training, False, bn_ws)
+        elif isinstance(module, DoubleResNet):
+            out, _ = eng._double_fwd(module, xa, None, module.training, False, bn_ws)
+        elif isinstance(module, ConvTransposeLayer):
+            skip = inputs[1]
+            cd = module.deconv.out_channels
+            n, _, hh, ww = skip.shape
+            catbuf = torch.empty((n, hh, ww, cd + skip.shape[1]), dtype=torch.bfloat16, device=x.device)
+            Act(catbuf, cd, skip.shape[1]).torch().copy_(skip.permute(0, 2, 3, 1))
+            wd = eng._pack(module.deconv, False, transposed=True)
+            ops.deconv_fwd(xa, wd.fwd, cd, y=Act(catbuf, 0, cd))
+            out, _ = eng._double_fwd(module.res, Act(catbuf), None, module.training, False, bn_ws)
+        else:
+            raise RuntimeError("unsupported sub-module %s" % type(module).__name__)
+        return out.nchw_float()
