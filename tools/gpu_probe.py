@@ -20,8 +20,8 @@ def main():
         for nm in names:
             t0 = time.time()
             try:
-                r = subprocess.run(["timeout", "-k", "5", "150", sys.executable, "-m", "tests.gpu_checks", nm], cwd=ROOT,
-                                   env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=200)
+                r = subprocess.run(["timeout", "-k", "5", "70", sys.executable, "-m", "tests.gpu_checks", nm], cwd=ROOT,
+                                   env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=100)
                 rc, out = r.returncode, r.stdout
             except subprocess.TimeoutExpired as e:
                 rc, out = -999, (e.stdout or "") + "\nTIMEOUT"
