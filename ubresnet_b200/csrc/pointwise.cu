@@ -90,16 +90,31 @@ __global__ void __launch_bounds__(kRedThreads) bn_stats_kernel(DView y, float* p
   block_reduce_store<2>(acc, y.c, partials);
 }
 
+// column sums of partials[nb][stride] for 32 consecutive columns starting at col0, by a (32 x 8) thread block:
+// threadIdx.x = column, threadIdx.y = row lane (coalesced 128-byte row reads, fixed summation order).
+__device__ __forceinline__ double col_sum_32x8(const float* partials, int nb, int stride, int col, bool active) {
+  __shared__ double sred[8][33];
+  double s = 0.0;
+  if (active)
+    for (int b = threadIdx.y; b < nb; b += 8) s += (double)partials[(size_t)b * stride + col];
+  sred[threadIdx.y][threadIdx.x] = s;
+  __syncthreads();
+  double t = 0.0;
+#pragma unroll
+  for (int l = 0; l < 8; ++l) t += sred[l][threadIdx.x];
+  __syncthreads();
+  return t;
+}
+
+// grid = ceil(c/32), block = (32, 8)
 __global__ void bn_finalize_kernel(const float* partials, int nb, int c, double count, const float* gamma,
                                    const float* beta, float* running_mean, float* running_var, float momentum,
                                    float eps, float* scale, float* shift, float* mean_out, float* invstd_out) {
-  const int ch = blockIdx.x * blockDim.x + threadIdx.x;
-  if (ch >= c) return;
-  double s = 0.0, q = 0.0;
-  for (int b = 0; b < nb; ++b) {
-    s += (double)partials[(size_t)b * 2 * c + ch];
-    q += (double)partials[(size_t)b * 2 * c + c + ch];
-  }
+  const int ch = blockIdx.x * 32 + threadIdx.x;
+  const bool act = ch < c;
+  const double s = col_sum_32x8(partials, nb, 2 * c, ch, act);
+  const double q = col_sum_32x8(partials, nb, 2 * c, c + ch, act);
+  if (!act || threadIdx.y != 0) return;
   const double mean = s / count;
   double var = q / count - mean * mean;
   if (var < 0.0) var = 0.0;
@@ -202,13 +217,11 @@ __global__ void __launch_bounds__(kRedThreads) bn_act_bwd_reduce_kernel(DView do
   block_reduce_store<2>(acc, y.c, partials);
 }
 
-// sums partials[nb][NS][C] -> sums[NS][C] (fixed order, double)
+// sums partials[nb][NS][C] -> sums[NS][C] (fixed order, double); grid = ceil(nsc/32), block = (32, 8)
 __global__ void sums_finalize_kernel(const float* partials, int nb, int nsc, float* sums) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= nsc) return;
-  double s = 0.0;
-  for (int b = 0; b < nb; ++b) s += (double)partials[(size_t)b * nsc + i];
-  sums[i] = (float)s;
+  const int i = blockIdx.x * 32 + threadIdx.x;
+  const double s = col_sum_32x8(partials, nb, nsc, i, i < nsc);
+  if (i < nsc && threadIdx.y == 0) sums[i] = (float)s;
 }
 
 __global__ void param_grad_kernel(const float* sums, int c, int off_dz, int off_dzx, float* dgamma, float* dbeta,
@@ -508,7 +521,7 @@ int ubr_bn_finalize(const void* workspace, int c, double count, const float* gam
   UBR_REQUIRE(workspace && scale && shift, "bn_finalize: null pointer");
   UBR_REQUIRE(c > 0 && c % 8 == 0 && count >= 1.0, "bn_finalize: bad c/count");
   const int nb = red_blocks((long)count, c);
-  bn_finalize_kernel<<<ceil_div(c, 128), 128, 0, (cudaStream_t)stream>>>((const float*)workspace, nb, c, count, gamma,
+  bn_finalize_kernel<<<ceil_div(c, 32), dim3(32, 8), 0, (cudaStream_t)stream>>>((const float*)workspace, nb, c, count, gamma,
                                                                          beta, running_mean, running_var, momentum,
                                                                          eps, scale, shift, mean, invstd);
   UBR_LAUNCH_CHECK("bn_finalize_kernel");
@@ -583,7 +596,7 @@ int ubr_bn_act_bwd_apply(ubr_view dout, ubr_view y, const float* scale, const fl
   const float* partials = (const float*)workspace;
   float* sums = (float*)workspace + (size_t)kRedBlocks * 4 * v.c;
   cudaStream_t st = (cudaStream_t)stream;
-  sums_finalize_kernel<<<ceil_div(2 * v.c, 128), 128, 0, st>>>(partials, nb, 2 * v.c, sums);
+  sums_finalize_kernel<<<ceil_div(2 * v.c, 32), dim3(32, 8), 0, st>>>(partials, nb, 2 * v.c, sums);
   UBR_LAUNCH_CHECK("sums_finalize_kernel");
   if (dgamma || dbeta) {
     param_grad_kernel<<<ceil_div(v.c, 128), 128, 0, st>>>(sums, v.c, 0, 1, dgamma, dbeta, accumulate);
@@ -646,7 +659,7 @@ int ubr_block_tail_bwd_apply(ubr_view dout, ubr_view out, ubr_view y2, const flo
   const float* partials = (const float*)workspace;
   float* sums = (float*)workspace + (size_t)kRedBlocks * 4 * v.c;
   cudaStream_t st = (cudaStream_t)stream;
-  sums_finalize_kernel<<<ceil_div(ns * v.c, 128), 128, 0, st>>>(partials, nb, ns * v.c, sums);
+  sums_finalize_kernel<<<ceil_div(ns * v.c, 32), dim3(32, 8), 0, st>>>(partials, nb, ns * v.c, sums);
   UBR_LAUNCH_CHECK("sums_finalize_kernel");
   if (dgamma2 || dbeta2) {
     param_grad_kernel<<<ceil_div(v.c, 128), 128, 0, st>>>(sums, v.c, 0, 1, dgamma2, dbeta2, accumulate);
