@@ -404,6 +404,21 @@ CHECKS = {
     "conv_wgrad_big": lambda: check_conv_wgrad(128, 256, 3, 1, 4, 8, 8, seed=4) + check_conv_wgrad(256, 128, 1, 1, 4, 8, 8, seed=5),
     "conv_wgrad_s2": lambda: check_conv_wgrad(32, 64, 3, 2, 2, 32, 32, seed=6) + check_conv_wgrad(64, 128, 1, 2, 2, 16, 16, seed=7),
     "conv_wgrad_7x7": lambda: check_conv_wgrad(16, 16, 7, 1, 2, 32, 32, seed=8) + check_conv_wgrad(16, 3, 7, 1, 2, 32, 32, seed=9, cout_pad=16),
+    # halo-resident kernels (W % 128 == 0, C <= 64, stride 1): every swizzle span, tap set, output mode
+    "halo_fwd_c16": lambda: check_conv_fwd(16, 16, 3, 1, 2, 64, 128, seed=21) + check_conv_fwd(16, 32, 3, 1, 1, 32, 256, seed=22),
+    "halo_fwd_c32": lambda: check_conv_fwd(32, 32, 3, 1, 2, 32, 128, seed=23) + check_conv_fwd(32, 16, 1, 1, 2, 40, 128, seed=24),
+    "halo_fwd_c64": lambda: check_conv_fwd(64, 64, 3, 1, 1, 32, 128, seed=25) + check_conv_fwd(64, 32, 1, 1, 1, 16, 256, seed=26),
+    "halo_fwd_7x7": lambda: (check_conv_fwd(16, 16, 7, 1, 1, 64, 128, seed=27, bias=True)
+                             + check_conv_fwd(16, 3, 7, 1, 1, 32, 256, seed=28, bias=True, f32=True)),
+    "halo_fwd_slices": lambda: check_conv_fwd(32, 16, 3, 1, 2, 32, 128, in_ld=64, out_ld=32, seed=29),
+    "halo_dgrad": lambda: (check_conv_dgrad(16, 32, 3, 1, 2, 64, 128, seed=31) + check_conv_dgrad(128, 64, 3, 1, 1, 32, 128, seed=32)
+                           + check_conv_dgrad(16, 16, 7, 1, 1, 32, 256, seed=33) + check_conv_dgrad(64, 32, 1, 1, 1, 32, 128, seed=34)),
+    "halo_wgrad_3x3": lambda: (check_conv_wgrad(16, 16, 3, 1, 2, 64, 128, seed=41) + check_conv_wgrad(32, 32, 3, 1, 1, 32, 256, seed=42)
+                               + check_conv_wgrad(64, 64, 3, 1, 1, 32, 128, seed=43) + check_conv_wgrad(16, 32, 3, 1, 1, 32, 128, seed=44)
+                               + check_conv_wgrad(64, 32, 3, 1, 1, 32, 128, seed=45)),
+    "halo_wgrad_1x1": lambda: check_conv_wgrad(32, 16, 1, 1, 2, 32, 128, seed=46) + check_conv_wgrad(64, 32, 1, 1, 1, 32, 128, seed=47),
+    "halo_wgrad_7x7": lambda: (check_conv_wgrad(16, 16, 7, 1, 1, 64, 128, seed=48)
+                               + check_conv_wgrad(16, 3, 7, 1, 1, 32, 256, seed=49, cout_pad=16)),
 }
 
 

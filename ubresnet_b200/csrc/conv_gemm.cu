@@ -16,6 +16,7 @@
 //   warps 2-5 : epilogue.  tcgen05.ld -> (+bias) -> bf16 -> swizzled smem staging -> TMA store
 //               (channel-slice / parity-phase aware through the tensor map), or fp32 direct store (logits).
 #include "common.cuh"
+#include "conv_internal.cuh"
 
 namespace ubr {
 
@@ -249,8 +250,6 @@ static int make_phase_map(CUtensorMap* m, const ubr_view& v, int ph, int pw, int
   return make_tmap_bf16(m, base, 4, dims, str, box, box_c * 2);
 }
 
-struct TapSpec { int dh, dw, amap, slab; };
-
 // generic launcher. `grid_view` = (n, h, w) of the output tile grid; a_maps built by caller.
 static int launch_conv_gemm(ConvGemmParams& p, int grid_n, int grid_h, int grid_w, TileShape t, int k_ch,
                             int n_pad, const void* wpk, int nslabs, const TapSpec* taps, int ntaps,
@@ -355,6 +354,18 @@ int ubr_conv2d_fwd(ubr_view x, const void* wpk, const float* bias, int out_ch, i
         taps[nt++] = TapSpec{dh, dw, ph * 2 + pw, r * ksize + s};
       }
   }
+  if (stride == 1) {
+    if (!y_f32) {
+      if (int rc = check_view(y, "conv2d_fwd.y")) return rc;
+      UBR_REQUIRE(y.n == x.n && y.h == ho && y.w == wo && y.c == out_ch, "conv2d_fwd: output view mismatch");
+      UBR_REQUIRE(out_ch % 16 == 0, "conv2d_fwd: bf16 output needs out_ch %% 16 == 0");
+    } else {
+      UBR_REQUIRE(y_f32_ld >= out_ch, "conv2d_fwd: y_f32_ld too small");
+    }
+    const int hrc = conv_halo_try(x, wpk, ksize * ksize, n_pad, taps, nt, bias, y_f32 ? nullptr : &y, y_f32, y_f32_ld,
+                                  out_ch, (cudaStream_t)stream);
+    if (hrc <= 0) return hrc;
+  }
   p.bias = bias;
   if (y_f32) {
     p.out_mode = 1; p.out_f32 = y_f32; p.out_ld = y_f32_ld; p.out_cols = out_ch;
@@ -392,6 +403,11 @@ int ubr_conv2d_dgrad(ubr_view dy, const void* wpk, int in_ch, int ksize, int str
     // dx[p] = sum_{r,s} dy[p - (r-pad, s-pad)] * W[:, :, r, s]
     for (int r = 0; r < ksize; ++r)
       for (int s = 0; s < ksize; ++s) taps[nt++] = TapSpec{pad - r, pad - s, 0, r * ksize + s};
+    {
+      const int hrc = conv_halo_try(dy, wpk, ksize * ksize, in_ch, taps, nt, nullptr, &dx, nullptr, 0, in_ch,
+                                    (cudaStream_t)stream);
+      if (hrc <= 0) return hrc;
+    }
     p.out_mode = 0;
     p.o_box_c = out_box_c(in_ch >= 128 ? 128 : in_ch);
     if (int rc = make_act_map(&p.o_map, dx, p.o_box_c, t)) return rc;

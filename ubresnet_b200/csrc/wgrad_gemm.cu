@@ -10,6 +10,7 @@
 // Split-K over pixel chunks: each CTA writes an fp32 partial [m][tap][n]; a second kernel sums the
 // partials in a FIXED order (deterministic, no atomics) into the fp32 parameter-gradient layout.
 #include "common.cuh"
+#include "conv_internal.cuh"
 
 namespace ubr {
 
@@ -340,7 +341,14 @@ extern "C" {
 uint64_t ubr_wgrad_workspace_bytes(int grid_n, int grid_h, int grid_w, int m_ch, int n_ch, int ntaps) {
   if (grid_n <= 0 || grid_h <= 0 || grid_w <= 0 || m_ch <= 0 || n_ch <= 0 || ntaps <= 0) return 0;
   WPlan pl = plan_wgrad(grid_n, grid_h, grid_w, m_ch, n_ch, ntaps);
-  return plan_ws_bytes(pl, m_ch, n_ch, ntaps);
+  uint64_t need = plan_ws_bytes(pl, m_ch, n_ch, ntaps);
+  // the halo-resident kernel (stride-1 convs, <= 64 channels) keeps one partial per persistent CTA
+  if (m_ch <= 64 && n_ch <= 64 && (ntaps == 1 || ntaps == 9 || ntaps == 49)) {
+    const int k = ntaps == 1 ? 1 : (ntaps == 9 ? 3 : 7);
+    const uint64_t h = wgrad_halo_workspace_bytes(n_ch, m_ch, k);
+    if (h > need) need = h;
+  }
+  return need;
 }
 
 int ubr_conv2d_wgrad(ubr_view x, ubr_view dy, int out_ch, int ksize, int stride, float* dw, int accumulate,
@@ -365,6 +373,10 @@ int ubr_conv2d_wgrad(ubr_view x, ubr_view dy, int out_ch, int ksize, int stride,
       }
     }
   UBR_REQUIRE(out_ch >= 1 && out_ch <= dy.c, "conv2d_wgrad: out_ch=%d vs dy.c=%d", out_ch, dy.c);
+  if (stride == 1) {
+    const int hrc = wgrad_halo_try(x, dy, out_ch, ksize, dw, accumulate, workspace, workspace_bytes, (cudaStream_t)stream);
+    if (hrc <= 0) return hrc;
+  }
   // dw is OIHW with the TRUE out_ch rows; dy.c may be padded (logits): rows >= out_ch are skipped
   return run_wgrad(dy, x, stride == 2, taps, nt, out_ch, x.c, (long)x.c * T, 1, (long)T, dw, accumulate, workspace,
                    workspace_bytes, (cudaStream_t)stream);
