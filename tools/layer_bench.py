@@ -45,13 +45,14 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--batch", type=int, default=32)
     ap.add_argument("--only", type=int, default=0)
+    ap.add_argument("--name", default="", help="substring filter on the layer name")
     args = ap.parse_args()
     B = args.batch
     # a big scratch write between runs is unnecessary: every tensor here is >> L2 at the high resolutions
     print("%-18s %4s %4s k s  res |  fwd ms   GB/s   TF/s | dgrad ms   GB/s | wgrad ms   GB/s" % ("layer", "cin", "cout"))
     tot = [0.0, 0.0, 0.0]
     for name, cin, cout, k, s, res in LAYERS:
-        if args.only and res != args.only:
+        if (args.only and res != args.only) or (args.name and args.name not in name):
             continue
         ro = res // s
         cop = (cout + 15) // 16 * 16

@@ -101,17 +101,20 @@ struct T2Params {
   uint32_t b_lbo, b_sbo, b_layout, b_kadv;
   uint32_t a_stage_bytes, b_stage_bytes, nstage;
   uint32_t idesc;
+  int commit_every;
 };
 __global__ void __launch_bounds__(128, 1) t2_kernel(const T2Params p, unsigned long long* cycles) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   __shared__ uint32_t tmem_slot;
   __shared__ __align__(8) unsigned long long bar;
+  __shared__ __align__(8) unsigned long long bar2[2];
   const uint32_t bar_a = smem_u32(&bar);
+  const uint32_t bar_b = smem_u32(&bar2[0]);
   // fill smem with small finite bf16 values
   for (uint32_t i = threadIdx.x; i < (p.a_stage_bytes + p.b_stage_bytes) * p.nstage / 4; i += blockDim.x)
     asm volatile("st.shared.b32 [%0], %1;" ::"r"(base + i * 4), "r"(0x3c003c00u));
-  if (threadIdx.x == 0) { mbar_init(bar_a, 1); fence_mbar_init(); }
+  if (threadIdx.x == 0) { mbar_init(bar_a, 1); mbar_init(bar_b, 1); mbar_init(bar_b + 8, 1); fence_mbar_init(); }
   if (threadIdx.x < 32) { tmem_alloc_dyn(smem_u32(&tmem_slot), 512); tmem_relinquish(); }
   fence_proxy_async_smem();
   tc_fence_before();
@@ -138,7 +141,11 @@ __global__ void __launch_bounds__(128, 1) t2_kernel(const T2Params p, unsigned l
       for (int k = 0; k < 8; ++k) {
         tc_mma_bf16(tmem + g * gstep, ad[k], bd[k], idesc, 1u);
         g = (g + 1u) & gmask;
+        if (p.commit_every == 1) { tc_commit(bar_b); }
       }
+      if (p.commit_every == 8) { tc_commit(bar_b); }
+      if (p.commit_every == 82) { tc_commit(bar_b); tc_commit(bar_b + 8); }
+      if (p.commit_every == 16 && (it & 1)) { tc_commit(bar_b); }
     }
     tc_commit(bar_a);
     mbar_wait(bar_a, 0);
@@ -149,6 +156,7 @@ __global__ void __launch_bounds__(128, 1) t2_kernel(const T2Params p, unsigned l
   if (threadIdx.x < 32) { tc_fence_after(); tmem_dealloc_dyn(tmem, 512); }
 }
 
+static int g_commit_every = 0;
 static void run_t2(const char* name, int n, int row_bytes_a, int row_bytes_b, bool mn_major, int m_blocks, int n_blocks, int groups = 1) {
   T2Params p;
   memset(&p, 0, sizeof(p));
@@ -175,6 +183,7 @@ static void run_t2(const char* name, int n, int row_bytes_a, int row_bytes_b, bo
     p.idesc = make_idesc_bf16(128, n, 1, 1);
   }
   p.nstage = (p.a_stage_bytes + p.b_stage_bytes) > 49152 ? 2 : 4;
+  p.commit_every = g_commit_every;
   unsigned long long* cyc;
   CK(cudaMalloc(&cyc, 148 * 8));
   const int smem = (p.a_stage_bytes + p.b_stage_bytes) * p.nstage + 2048;
@@ -190,6 +199,39 @@ static void run_t2(const char* name, int n, int row_bytes_a, int row_bytes_b, bo
   const double macs = 128.0 * n * 16;
   printf("T2 %-34s G=%d N=%3d : %7.1f cyc/MMA  (%6.0f MAC/cyc/SM = %5.1f%% of 4096; floor %d cyc)\n", name, groups, n, per, macs / per,
          100.0 * macs / per / 4096.0, n / 2);
+  CK(cudaFree(cyc));
+}
+
+// T2w: the stacked-tap weight-gradient MMA (wgrad_halo.cu): A MN-major with overlapping atoms (LBO = 1 pixel),
+// B MN-major with one atom per dy row (LBO = row pitch), N = ks*cout
+static void run_t2w(int cin, int cout, int ks, int groups = 1) {
+  T2Params p;
+  memset(&p, 0, sizeof(p));
+  const int ra = cin * 2, rbb = cout * 2;
+  p.n = ks * cout;
+  p.groups = groups;
+  p.iters = 512;
+  p.ksteps = 8;
+  p.a_lbo = ra; p.a_sbo = 8 * ra; p.a_layout = swizzle_layout_code(ra); p.a_kadv = 16 * ra;
+  p.b_lbo = 128 * rbb; p.b_sbo = 8 * rbb; p.b_layout = swizzle_layout_code(rbb); p.b_kadv = 16 * rbb;
+  p.a_stage_bytes = ((160 * ra) + 1023) & ~1023;
+  p.b_stage_bytes = ks * 128 * rbb;
+  p.idesc = make_idesc_bf16(128, p.n, 1, 1);
+  p.nstage = 1;
+  unsigned long long* cyc;
+  CK(cudaMalloc(&cyc, 148 * 8));
+  const int smem = (p.a_stage_bytes + p.b_stage_bytes) * p.nstage + 2048;
+  CK(cudaFuncSetAttribute(t2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
+  t2_kernel<<<148, 128, smem>>>(p, cyc);
+  CK(cudaDeviceSynchronize());
+  unsigned long long h[148];
+  CK(cudaMemcpy(h, cyc, sizeof(h), cudaMemcpyDeviceToHost));
+  double avg = 0;
+  for (int i = 0; i < 148; ++i) avg += (double)h[i];
+  avg /= 148;
+  const double per = avg / ((double)(p.iters * p.ksteps / 8) * 8);
+  printf("T2w stacked wgrad MMA cin=%2d cout=%2d ks=%d (M=128 overlap LBO=%dB, N=%3d) G=%d : %7.1f cyc/MMA\n", cin, cout, ks, ra,
+         p.n, groups, per);
   CK(cudaFree(cyc));
 }
 
@@ -314,6 +356,21 @@ int main(int argc, char** argv) {
     run_t2("MN-major A C=128,     B C=64", 64, 128, 128, true, 2, 1, 4);
     run_t2("MN-major A C=128,     B C=128", 128, 128, 128, true, 2, 2, 1);
     run_t2("MN-major A C=128,     B C=128", 128, 128, 128, true, 2, 2, 4);
+  }
+  if (!strcmp(which, "t2c")) {
+    // cost of tcgen05.commit in the MMA stream: none / one per 16 / one per 8 / two per 8 / one per MMA
+    for (int ce : {0, 16, 8, 82, 1}) {
+      g_commit_every = ce;
+      printf("commit_every=%d: ", ce);
+      run_t2("K-major SW32  (C=16 rows)", 16, 32, 32, false, 1, 1, 1);
+    }
+    g_commit_every = 0;
+  }
+  if (!strcmp(which, "t2w")) {
+    for (int g : {1, 2}) {
+      run_t2w(16, 16, 1, g); run_t2w(16, 16, 3, g); run_t2w(16, 16, 7, g);
+      run_t2w(32, 32, 3, g); run_t2w(64, 64, 3, g); run_t2w(64, 32, 1, g);
+    }
   }
   if (!strcmp(which, "t2b")) {
     // swapped orientation: A = weights (M rows, wide SW128 rows), B = pixels (N rows of C*2 bytes)

@@ -12,35 +12,36 @@
 //     absolute smem address, so any span-aligned start is legal (profiles/r01_ubench_tma_mma_desc.txt, T3).
 //   * TMA zero-fills out-of-image pixels => conv padding for free; every input byte is read from L2/HBM once per
 //     row band (+ halo rows), every output byte written once.
-//   * persistent CTAs (<= 2 per SM) walk (image, 128-column block, 32-row band) tiles; TMEM holds two
-//     accumulators so the epilogue of row i overlaps the MMAs of row i+1; all filter taps stay resident in smem.
+//   * persistent CTAs (<= 2 per SM) walk (image, 128-column block, 32-row band) tiles; TMEM holds FOUR
+//     accumulators so the MMA issuer runs two rows ahead of the epilogue; all filter taps stay resident in smem.
 //
-// Warp roles: warp 0 TMA producer (weights once, then one row segment per ring slot), warp 1 TMEM owner +
-// single-thread tcgen05.mma issuer, warps 2-5 epilogue (tcgen05.ld -> +bias -> bf16 -> swizzled staging ->
-// TMA store; or fp32 direct store for the logits).
+// Warp roles (320 threads): warp 0 TMA producer (weights once, then one row segment per ring slot), warp 1 TMEM
+// owner + single-thread tcgen05.mma issuer (fully unrolled per filter size: descriptor = one integer add per MMA),
+// warps 2-5 / 6-9 two independent epilogue groups taking alternate output rows
+// (tcgen05.ld -> +bias -> bf16 -> direct 16-byte global stores when Cout <= 32, else swizzled staging + TMA store;
+// fp32 direct store for the logits).
 #include "common.cuh"
 #include "conv_internal.cuh"
 
 namespace ubr {
 
-constexpr int kHThreads = 192;
-constexpr int kHMaxTaps = 49;
+constexpr int kHThreads = 320;
 
 struct HaloParams {
   CUtensorMap a_map;            // input view (C, W, H, N), box {cin, 128+2p, 1, 1}
   CUtensorMap w_map;            // packed weights (K, N, slab), box {cin, nt, 1}
-  CUtensorMap o_map;            // output view, box {o_box_c, 128, 1, 1}
-  int ntaps, pad, ksteps, nt;
+  CUtensorMap o_map;            // output view, box {o_box_c, 128, 1, 1}  (out_mode 0 only)
+  int ksize, pad, nt, flip;     // flip: data-gradient tap order (dh = p-r, dw = p-s)
   int bands, cblocks, bh, ntiles;
   int nslots;
   uint32_t span, row_bytes, slot_bytes, w_tap_bytes, w_region, stage_bytes;
-  uint32_t idesc;
-  int out_mode, o_box_c;
+  uint32_t idesc, tmem_cols, acc_stride;
+  int out_mode;                 // 0: bf16 staging + TMA store, 1: fp32 direct (logits), 2: bf16 direct stores
+  int o_box_c;
   const float* bias;
   float* out_f32;
+  __nv_bfloat16* out_bf16;
   int out_ld, out_cols, out_h, out_w;
-  int8_t dh[kHMaxTaps], dw[kHMaxTaps];
-  uint8_t slab[kHMaxTaps];
 };
 
 template <int N>
@@ -48,6 +49,30 @@ __device__ __forceinline__ void tma_store_wait_read_n() {
   asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
 }
 
+// D[tmem] (+)= A * B with descriptors given as (lo, hi) 32-bit halves; ACC is a compile-time flag
+template <bool ACC>
+__device__ __forceinline__ void mma_lohi(uint32_t d_tmem, uint32_t alo, uint32_t ahi, uint32_t blo, uint32_t bhi,
+                                         uint32_t idesc) {
+  if (ACC) {
+    asm volatile(
+        "{\n\t.reg .b64 da, db;\n\t.reg .pred p;\n\t"
+        "mov.b64 da, {%1, %2};\n\tmov.b64 db, {%3, %4};\n\t"
+        "setp.ne.b32 p, 1, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %5, p;\n\t}\n"
+        ::"r"(d_tmem), "r"(alo), "r"(ahi), "r"(blo), "r"(bhi), "r"(idesc)
+        : "memory");
+  } else {
+    asm volatile(
+        "{\n\t.reg .b64 da, db;\n\t.reg .pred p;\n\t"
+        "mov.b64 da, {%1, %2};\n\tmov.b64 db, {%3, %4};\n\t"
+        "setp.ne.b32 p, 0, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %5, p;\n\t}\n"
+        ::"r"(d_tmem), "r"(alo), "r"(ahi), "r"(blo), "r"(bhi), "r"(idesc)
+        : "memory");
+  }
+}
+
+template <int KS, int KSTEPS>
 __global__ void __launch_bounds__(kHThreads, 1) conv_halo_kernel(const __grid_constant__ HaloParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -58,33 +83,35 @@ __global__ void __launch_bounds__(kHThreads, 1) conv_halo_kernel(const __grid_co
   const uint32_t full0 = bar_base;
   const uint32_t empty0 = full0 + 8u * p.nslots;
   const uint32_t wbar = empty0 + 8u * p.nslots;
-  const uint32_t accf0 = wbar + 8u;         // [2]
-  const uint32_t acce0 = accf0 + 16u;       // [2]
-  const uint32_t tmem_slot = acce0 + 16u;
+  const uint32_t accf0 = wbar + 8u;         // [4]
+  const uint32_t acce0 = accf0 + 32u;       // [4]
+  const uint32_t tmem_slot = acce0 + 32u;
 
+  constexpr int PAD = (KS - 1) / 2;
+  constexpr int ROWS_EXTRA = 2 * PAD;
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   const int co0 = blockIdx.y * p.nt;
-  const int S = p.nslots;
-  const int rows_in = p.bh + 2 * p.pad;
+  const uint32_t S = (uint32_t)p.nslots;
+  const int rows_in = p.bh + ROWS_EXTRA;
 
   if (threadIdx.x == 0) {
-    for (int s = 0; s < S; ++s) {
+    for (uint32_t s = 0; s < S; ++s) {
       mbar_init(full0 + 8u * s, 1);
       mbar_init(empty0 + 8u * s, 1);
     }
     mbar_init(wbar, 1);
-    mbar_init(accf0, 1);
-    mbar_init(accf0 + 8u, 1);
-    mbar_init(acce0, 4);
-    mbar_init(acce0 + 8u, 4);
+    for (uint32_t b = 0; b < 4; ++b) {
+      mbar_init(accf0 + 8u * b, 1);
+      mbar_init(acce0 + 8u * b, 4);
+    }
     fence_mbar_init();
     prefetch_tmap(&p.a_map);
     prefetch_tmap(&p.w_map);
     if (p.out_mode == 0) prefetch_tmap(&p.o_map);
   }
   if (warp == 1) {
-    tmem_alloc_dyn(tmem_slot, 256);
+    tmem_alloc_dyn(tmem_slot, p.tmem_cols);
     tmem_relinquish();
   }
   tc_fence_before();
@@ -94,91 +121,150 @@ __global__ void __launch_bounds__(kHThreads, 1) conv_halo_kernel(const __grid_co
   asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
 
   if (warp == 0) {
-    if (lane == 0) {
-      // ================= TMA producer =================
-      mbar_arrive_expect_tx(wbar, (uint32_t)p.ntaps * p.w_tap_bytes);
-      for (int t = 0; t < p.ntaps; ++t)
-        tma_load_3d(w_base + (uint32_t)t * p.w_tap_bytes, &p.w_map, wbar, 0, co0, (int)p.slab[t]);
-      uint32_t g = 0;
-      for (int tile = blockIdx.x; tile < p.ntiles; tile += gridDim.x) {
-        const int band = tile % p.bands;
-        const int cb = (tile / p.bands) % p.cblocks;
-        const int n = tile / (p.bands * p.cblocks);
-        const int h0 = band * p.bh - p.pad, c0 = cb * 128 - p.pad;
-        for (int j = 0; j < rows_in; ++j, ++g) {
-          const uint32_t s = g % (uint32_t)S;
-          const uint32_t ph = (g / (uint32_t)S) & 1u;
-          mbar_wait(empty0 + 8u * s, ph ^ 1u);
-          mbar_arrive_expect_tx(full0 + 8u * s, p.row_bytes);
-          tma_load_4d(ring_base + s * p.slot_bytes, &p.a_map, full0 + 8u * s, 0, c0, h0 + j, n);
-        }
-      }
+    // ================= TMA producer (whole warp walks the loop, one elected lane issues) =================
+    if (elect_one()) {
+      mbar_arrive_expect_tx(wbar, (uint32_t)(KS * KS) * p.w_tap_bytes);
+      for (int t = 0; t < KS * KS; ++t)
+        tma_load_3d(w_base + (uint32_t)t * p.w_tap_bytes, &p.w_map, wbar, 0, co0, t);
     }
-  } else if (warp == 1) {
-    if (lane == 0) {
-      // ================= MMA issuer =================
-      const uint32_t layout = swizzle_layout_code((int)p.span);
-      const uint32_t sbo = 8u * p.span;
-      mbar_wait(wbar, 0);
-      uint32_t g0 = 0, r = 0;
-      for (int tile = blockIdx.x; tile < p.ntiles; tile += gridDim.x) {
-        for (int i = 0; i < p.bh; ++i, ++r) {
-          // rows g0+i .. g0+i+2p must have landed
-          const int jfirst = (i == 0) ? 0 : 2 * p.pad;
-          for (int j = jfirst; j <= 2 * p.pad; ++j) {
-            const uint32_t gi = g0 + (uint32_t)(i + j);
-            mbar_wait(full0 + 8u * (gi % (uint32_t)S), (gi / (uint32_t)S) & 1u);
-          }
-          const uint32_t b = r & 1u;
-          mbar_wait(acce0 + 8u * b, ((r >> 1) & 1u) ^ 1u);
-          tc_fence_after();
-          const uint32_t d_tmem = tmem_base + b * 128u;
-          for (int t = 0; t < p.ntaps; ++t) {
-            const uint32_t gi = g0 + (uint32_t)(i + p.dh[t] + p.pad);
-            const uint32_t a_src = ring_base + (gi % (uint32_t)S) * p.slot_bytes + (uint32_t)(p.dw[t] + p.pad) * p.span;
-            const uint64_t adesc = make_smem_desc(a_src, 0, sbo, layout);
-            const uint64_t bdesc = make_smem_desc(w_base + (uint32_t)t * p.w_tap_bytes, 0, sbo, layout);
-            for (int k = 0; k < p.ksteps; ++k)
-              tc_mma_bf16(d_tmem, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), p.idesc, (t > 0 || k > 0) ? 1u : 0u);
-          }
-          tc_commit(accf0 + 8u * b);
-          {
-            const uint32_t gi = g0 + (uint32_t)i;                       // oldest row: no later output row needs it
-            tc_commit(empty0 + 8u * (gi % (uint32_t)S));
-          }
-          if (i == p.bh - 1)
-            for (int j = 1; j <= 2 * p.pad; ++j) {
-              const uint32_t gi = g0 + (uint32_t)(i + j);
-              tc_commit(empty0 + 8u * (gi % (uint32_t)S));
-            }
-        }
-        g0 += (uint32_t)rows_in;
-      }
-    }
-  } else {
-    // ================= epilogue (warps 2..5) =================
-    const int quad = warp & 3;                 // TMEM lane quadrant this warp may access
-    const int row = quad * 32 + lane;          // tile-local pixel (column inside the 128-wide block)
-    const bool leader = (warp == 2 && lane == 0);
-    const int bc = p.o_box_c;
-    const uint32_t rb = (uint32_t)bc * 2u;
-    const uint32_t xr = rb == 128 ? (uint32_t)(row & 7) : (rb == 64 ? (uint32_t)((row >> 1) & 3) : (uint32_t)((row >> 2) & 1));
-    uint32_t r = 0;
+    __syncwarp();
+    uint32_t s = 0, ph = 0;
     for (int tile = blockIdx.x; tile < p.ntiles; tile += gridDim.x) {
       const int band = tile % p.bands;
       const int cb = (tile / p.bands) % p.cblocks;
       const int n = tile / (p.bands * p.cblocks);
-      const int c0 = cb * 128;
+      const int h0 = band * p.bh - PAD, c0 = cb * 128 - PAD;
+      for (int j = 0; j < rows_in; ++j) {
+        mbar_wait(empty0 + 8u * s, ph ^ 1u);
+        if (elect_one()) {
+          mbar_arrive_expect_tx(full0 + 8u * s, p.row_bytes);
+          tma_load_4d(ring_base + s * p.slot_bytes, &p.a_map, full0 + 8u * s, 0, c0, h0 + j, n);
+        }
+        __syncwarp();
+        if (++s == S) { s = 0; ph ^= 1u; }
+      }
+    }
+  } else if (warp == 1) {
+    // ================= MMA issuer =================
+    // The WHOLE warp walks the loop with warp-uniform values (descriptors live in uniform registers); only the
+    // tcgen05.mma / tcgen05.commit instructions are issued by one elected lane.  (Issuing from inside an
+    // `if (lane == 0)` region makes ptxas wrap every UTCHMMA in a per-thread waterfall loop: ~10 SASS
+    // instructions per MMA at ~6 cycles each on a lone warp -- measured, profiles/r01c_*.)
+    const uint32_t layout = swizzle_layout_code((int)p.span);
+    const uint32_t desc_hi = (uint32_t)((make_smem_desc(0, 0, 8u * p.span, layout)) >> 32);
+    const uint32_t span16 = p.span >> 4, slot16 = p.slot_bytes >> 4, wtap16 = p.w_tap_bytes >> 4;
+    const uint32_t ring16 = ring_base >> 4;
+    // weight descriptor of tap index t' = r'*KS + s' (row/col OFFSET order): forward slab t', data-gradient
+    // slab KS*KS-1-t' (180-degree rotated filter)
+    const uint32_t b_first = (w_base >> 4) + (p.flip ? (uint32_t)(KS * KS - 1) * wtap16 : 0u);
+    const uint32_t b_step = p.flip ? (0u - wtap16) : wtap16;
+    const uint32_t idesc = p.idesc;
+    const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem_base, 0);
+    mbar_wait(wbar, 0);
+    uint32_t s_first = 0, ph_first = 0;       // ring slot / phase of the first input row of the current output row
+    uint32_t r = 0;
+    for (int tile = blockIdx.x; tile < p.ntiles; tile += gridDim.x) {
       for (int i = 0; i < p.bh; ++i, ++r) {
-        const int h = band * p.bh + i;
-        const uint32_t b = r & 1u;
-        mbar_wait(accf0 + 8u * b, (r >> 1) & 1u);
+        // rows s_first .. s_first+2*PAD must have landed (all but the newest were waited for earlier)
+        {
+          uint32_t s = s_first, ph = ph_first;
+#pragma unroll
+          for (int j = 0; j <= ROWS_EXTRA; ++j) {
+            if (i == 0 || j == ROWS_EXTRA) mbar_wait(full0 + 8u * s, ph);
+            if (++s == S) { s = 0; ph ^= 1u; }
+          }
+        }
+        const uint32_t b = r & 3u;
+        mbar_wait(acce0 + 8u * b, ((r >> 2) & 1u) ^ 1u);
         tc_fence_after();
-        const uint32_t t_row = tmem_base + b * 128u + ((uint32_t)(quad * 32) << 16);
-        if (p.out_mode == 0) {
-          const uint32_t sbase = stage_base + b * p.stage_bytes;
-          if (leader) tma_store_wait_read_n<1>();          // the store that last read this staging buffer is done
-          asm volatile("bar.sync 1, 128;" ::: "memory");
+        const uint32_t d_tmem = tmem_u + b * p.acc_stride;
+        const bool last = (i == p.bh - 1);
+        if (elect_one()) {
+          uint32_t srow = s_first;
+#pragma unroll
+          for (int rr = 0; rr < KS; ++rr) {
+            const uint32_t a_row = ring16 + srow * slot16;
+#pragma unroll
+            for (int ss = 0; ss < KS; ++ss) {
+              const uint32_t a_t = a_row + (uint32_t)ss * span16;
+              const uint32_t b_t = b_first + (uint32_t)(rr * KS + ss) * b_step;
+#pragma unroll
+              for (int k = 0; k < KSTEPS; ++k) {
+                if (rr == 0 && ss == 0 && k == 0) mma_lohi<false>(d_tmem, a_t, desc_hi, b_t, desc_hi, idesc);
+                else mma_lohi<true>(d_tmem, a_t + 2u * k, desc_hi, b_t + 2u * k, desc_hi, idesc);
+              }
+            }
+            if (++srow == S) srow = 0;
+          }
+          tc_commit(accf0 + 8u * b);
+          tc_commit(empty0 + 8u * s_first);      // oldest row: no later output row of this tile needs it
+          if (last) {
+            uint32_t s = s_first;
+#pragma unroll
+            for (int j = 0; j < ROWS_EXTRA; ++j) {
+              if (++s == S) s = 0;
+              tc_commit(empty0 + 8u * s);
+            }
+          }
+        }
+        __syncwarp();
+        const uint32_t adv = last ? (uint32_t)(1 + ROWS_EXTRA) : 1u;
+        for (uint32_t j = 0; j < adv; ++j)
+          if (++s_first == S) { s_first = 0; ph_first ^= 1u; }
+      }
+    }
+  } else {
+    // ================= epilogue: group 0 = warps 2..5 (even rows), group 1 = warps 6..9 (odd rows) ============
+    const int grp = (warp - 2) >> 2;
+    const int quad = warp & 3;                 // TMEM lane quadrant this warp may access
+    const int row = quad * 32 + lane;          // pixel inside the 128-wide column block
+    const bool leader = (((warp - 2) & 3) == 0 && lane == 0);
+    const int bc = p.o_box_c;
+    const uint32_t rb = (uint32_t)bc * 2u;
+    const uint32_t xr = rb == 128 ? (uint32_t)(row & 7) : (rb == 64 ? (uint32_t)((row >> 1) & 3) : (uint32_t)((row >> 2) & 1));
+    const uint32_t sbase = stage_base + (uint32_t)grp * p.stage_bytes;
+    const int bar_id = 1 + grp;
+    uint32_t r0 = 0;                           // global output-row counter at the start of the tile
+    for (int tile = blockIdx.x; tile < p.ntiles; tile += gridDim.x, r0 += (uint32_t)p.bh) {
+      const int band = tile % p.bands;
+      const int cb = (tile / p.bands) % p.cblocks;
+      const int n = tile / (p.bands * p.cblocks);
+      const int c0 = cb * 128;
+      for (int i = grp; i < p.bh; i += 2) {
+        const uint32_t r = r0 + (uint32_t)i;
+        const int h = band * p.bh + i;
+        const uint32_t b = r & 3u;
+        mbar_wait(accf0 + 8u * b, (r >> 2) & 1u);
+        tc_fence_after();
+        const uint32_t t_row = tmem_base + b * p.acc_stride + ((uint32_t)(quad * 32) << 16);
+        if (p.out_mode == 2) {
+          // bf16 direct stores: one pixel (nt <= 32 channels) per thread, 16-byte vectors
+          __nv_bfloat16* dst = p.out_bf16 + ((size_t)((size_t)n * p.out_h + h) * p.out_w + (c0 + row)) * (size_t)p.out_ld + co0;
+          for (int c = 0; c < p.nt; c += 16) {
+            uint32_t v[16];
+            tmem_ld16(t_row + (uint32_t)c, v);
+            tmem_ld_wait();
+            float f[16];
+#pragma unroll
+            for (int j = 0; j < 16; ++j) f[j] = __uint_as_float(v[j]);
+            if (p.bias) {
+#pragma unroll
+              for (int j = 0; j < 16; ++j) f[j] += __ldg(p.bias + co0 + c + j);
+            }
+            uint4 u0, u1;
+            u0.x = pack_bf16x2(f[0], f[1]); u0.y = pack_bf16x2(f[2], f[3]);
+            u0.z = pack_bf16x2(f[4], f[5]); u0.w = pack_bf16x2(f[6], f[7]);
+            u1.x = pack_bf16x2(f[8], f[9]); u1.y = pack_bf16x2(f[10], f[11]);
+            u1.z = pack_bf16x2(f[12], f[13]); u1.w = pack_bf16x2(f[14], f[15]);
+            *reinterpret_cast<uint4*>(dst + c) = u0;
+            *reinterpret_cast<uint4*>(dst + c + 8) = u1;
+          }
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(acce0 + 8u * b);
+        } else if (p.out_mode == 0) {
+          if (leader) tma_store_wait_read_n<0>();          // this group's previous store has read the staging tile
+          asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");
           for (int c = 0; c < p.nt; c += 16) {
             uint32_t v[16];
             tmem_ld16(t_row + (uint32_t)c, v);
@@ -203,9 +289,9 @@ __global__ void __launch_bounds__(kHThreads, 1) conv_halo_kernel(const __grid_co
           }
           tc_fence_before();
           __syncwarp();
-          if (lane == 0) mbar_arrive(acce0 + 8u * b);      // accumulator drained: MMA may overwrite it
+          if (lane == 0) mbar_arrive(acce0 + 8u * b);      // accumulator drained: the issuer may overwrite it
           fence_proxy_async_smem();
-          asm volatile("bar.sync 1, 128;" ::: "memory");
+          asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");
           if (leader) {
             const int nblk = p.nt / bc;
             for (int k = 0; k < nblk; ++k)
@@ -221,13 +307,10 @@ __global__ void __launch_bounds__(kHThreads, 1) conv_halo_kernel(const __grid_co
             tmem_ld_wait();
             if (p.out_ld == 4 && c == 0 && co0 == 0) {
               float4 o;
-              o.x = __uint_as_float(v[0]) + ((p.bias && 0 < p.out_cols) ? __ldg(p.bias + 0) : 0.f);
-              o.y = __uint_as_float(v[1]) + ((p.bias && 1 < p.out_cols) ? __ldg(p.bias + 1) : 0.f);
-              o.z = __uint_as_float(v[2]) + ((p.bias && 2 < p.out_cols) ? __ldg(p.bias + 2) : 0.f);
-              o.w = __uint_as_float(v[3]) + ((p.bias && 3 < p.out_cols) ? __ldg(p.bias + 3) : 0.f);
-              if (p.out_cols < 4) o.w = 0.f;
-              if (p.out_cols < 3) o.z = 0.f;
-              if (p.out_cols < 2) o.y = 0.f;
+              o.x = (0 < p.out_cols) ? __uint_as_float(v[0]) + (p.bias ? __ldg(p.bias + 0) : 0.f) : 0.f;
+              o.y = (1 < p.out_cols) ? __uint_as_float(v[1]) + (p.bias ? __ldg(p.bias + 1) : 0.f) : 0.f;
+              o.z = (2 < p.out_cols) ? __uint_as_float(v[2]) + (p.bias ? __ldg(p.bias + 2) : 0.f) : 0.f;
+              o.w = (3 < p.out_cols) ? __uint_as_float(v[3]) + (p.bias ? __ldg(p.bias + 3) : 0.f) : 0.f;
               *reinterpret_cast<float4*>(dst) = o;
             } else {
 #pragma unroll
@@ -251,7 +334,7 @@ __global__ void __launch_bounds__(kHThreads, 1) conv_halo_kernel(const __grid_co
   if (warp == 1) {
     __syncwarp();
     tc_fence_after();
-    tmem_dealloc_dyn(tmem_base, 256);
+    tmem_dealloc_dyn(tmem_base, p.tmem_cols);
   }
 }
 
@@ -264,6 +347,21 @@ static bool halo_disabled() {
   return v == 1;
 }
 
+typedef void (*halo_kernel_t)(const HaloParams);
+static halo_kernel_t pick_halo_kernel(int ks, int ksteps) {
+  switch (ks * 10 + ksteps) {
+    case 11: return conv_halo_kernel<1, 1>;
+    case 12: return conv_halo_kernel<1, 2>;
+    case 14: return conv_halo_kernel<1, 4>;
+    case 31: return conv_halo_kernel<3, 1>;
+    case 32: return conv_halo_kernel<3, 2>;
+    case 34: return conv_halo_kernel<3, 4>;
+    case 71: return conv_halo_kernel<7, 1>;
+    case 72: return conv_halo_kernel<7, 2>;
+    default: return nullptr;
+  }
+}
+
 int conv_halo_try(const ubr_view& x, const void* wpk, int nslabs, int n_pad, const TapSpec* taps, int ntaps,
                   const float* bias, const ubr_view* y, float* y_f32, int y_f32_ld, int out_cols,
                   cudaStream_t stream) {
@@ -271,13 +369,23 @@ int conv_halo_try(const ubr_view& x, const void* wpk, int nslabs, int n_pad, con
   const int cin = x.c;
   if (!(cin == 16 || cin == 32 || cin == 64)) return 1;
   if (x.w % 128 != 0 || x.w < 128) return 1;
-  if (ntaps < 1 || ntaps > kHMaxTaps) return 1;
-  int pad = 0;
-  for (int i = 0; i < ntaps; ++i) {
-    if (taps[i].amap != 0) return 1;
-    pad = max(pad, max(abs(taps[i].dh), abs(taps[i].dw)));
+  int ks = 0;
+  if (ntaps == 1) ks = 1; else if (ntaps == 9) ks = 3; else if (ntaps == 49) ks = 7; else return 1;
+  const int pad = (ks - 1) / 2;
+  // regular tap grid only: forward (dh = r-p, dw = s-p) or data gradient (dh = p-r, dw = p-s), slab = r*ks+s
+  int flip = -1;
+  for (int sgn = 1; sgn >= -1 && flip < 0; sgn -= 2) {
+    bool ok = true;
+    for (int r = 0; r < ks && ok; ++r)
+      for (int s = 0; s < ks && ok; ++s) {
+        const TapSpec& t = taps[r * ks + s];
+        ok = t.amap == 0 && t.slab == r * ks + s && t.dh == sgn * (r - pad) && t.dw == sgn * (s - pad);
+      }
+    if (ok) flip = sgn > 0 ? 0 : 1;
   }
-  if (pad > 3) return 1;
+  if (flip < 0) return 1;
+  halo_kernel_t kern = pick_halo_kernel(ks, cin / 16);
+  if (!kern) return 1;
   int bh = 32;
   while (bh > 1 && x.h % bh != 0) bh >>= 1;
   if (bh < 8) return 1;
@@ -286,16 +394,17 @@ int conv_halo_try(const ubr_view& x, const void* wpk, int nslabs, int n_pad, con
   const uint32_t slot_bytes = (row_bytes + 1023u) & ~1023u;
   // N tile: largest divisor tile whose resident weights + ring + staging fit
   const uint32_t budget = 225u * 1024u - 1024u - 512u;
-  int nt = 0, nslots = 0;
+  int nt = 0, nslots = 0, out_mode = 0;
   uint32_t w_region = 0, stage_bytes = 0;
   for (int cand = n_pad > 128 ? 128 : n_pad; cand >= 16; cand -= 16) {
     if (n_pad % cand) continue;
     const uint32_t wr = ((uint32_t)ntaps * cand * span + 1023u) & ~1023u;
-    const uint32_t st = y_f32 ? 0u : 128u * (uint32_t)cand * 2u;
+    const int mode = y_f32 ? 1 : (cand <= 32 ? 2 : 0);
+    const uint32_t st = mode == 0 ? 128u * (uint32_t)cand * 2u : 0u;
     if (wr + 2u * st + (uint32_t)(2 * pad + 2) * slot_bytes > budget) continue;
     int s = (int)((budget - wr - 2u * st) / slot_bytes);
     if (s > 16) s = 16;
-    nt = cand; nslots = s; w_region = wr; stage_bytes = st;
+    nt = cand; nslots = s; w_region = wr; stage_bytes = st; out_mode = mode;
     break;
   }
   if (nt == 0) return 1;
@@ -314,41 +423,39 @@ int conv_halo_try(const ubr_view& x, const void* wpk, int nslabs, int n_pad, con
     uint32_t box[3] = {(uint32_t)cin, (uint32_t)nt, 1};
     if (int rc = make_tmap_bf16(&p.w_map, wpk, 3, dims, str, box, (int)span)) return rc;
   }
-  if (y_f32) {
-    p.out_mode = 1; p.out_f32 = y_f32; p.out_ld = y_f32_ld; p.out_cols = out_cols;
-    p.out_h = x.h; p.out_w = x.w;
+  p.out_mode = out_mode;
+  p.out_h = x.h; p.out_w = x.w;
+  if (out_mode == 1) {
+    p.out_f32 = y_f32; p.out_ld = y_f32_ld; p.out_cols = out_cols;
+  } else if (out_mode == 2) {
+    p.out_bf16 = (__nv_bfloat16*)y->ptr; p.out_ld = y->ld; p.out_cols = out_cols;
   } else {
-    p.out_mode = 0;
     p.o_box_c = nt >= 64 ? 64 : nt;
     uint64_t dims[4] = {(uint64_t)y->c, (uint64_t)y->w, (uint64_t)y->h, (uint64_t)y->n};
     uint64_t str[4] = {2, (uint64_t)y->ld * 2, (uint64_t)y->w * y->ld * 2, (uint64_t)y->h * y->w * y->ld * 2};
     uint32_t box[4] = {(uint32_t)p.o_box_c, 128, 1, 1};
     if (int rc = make_tmap_bf16(&p.o_map, y->ptr, 4, dims, str, box, p.o_box_c * 2)) return rc;
   }
-  p.ntaps = ntaps; p.pad = pad; p.ksteps = cin / 16; p.nt = nt;
+  if (p.o_box_c == 0) p.o_box_c = 16;
+  p.ksize = ks; p.pad = pad; p.nt = nt; p.flip = flip;
   p.bh = bh; p.bands = x.h / bh; p.cblocks = x.w / 128; p.ntiles = p.bands * p.cblocks * x.n;
   p.nslots = nslots;
   p.span = span; p.row_bytes = row_bytes; p.slot_bytes = slot_bytes;
   p.w_tap_bytes = (uint32_t)nt * span; p.w_region = w_region; p.stage_bytes = stage_bytes;
   p.idesc = make_idesc_bf16(128, nt, 0, 0);
+  p.acc_stride = nt <= 64 ? 64u : 128u;
+  p.tmem_cols = 4u * p.acc_stride;
   p.bias = bias;
-  for (int i = 0; i < ntaps; ++i) {
-    p.dh[i] = (int8_t)taps[i].dh; p.dw[i] = (int8_t)taps[i].dw; p.slab[i] = (uint8_t)taps[i].slab;
-  }
-  const uint32_t smem = w_region + (uint32_t)nslots * slot_bytes + 2u * stage_bytes + 16u * nslots + 64u + 1024u;
-  static bool attr_set = false;
-  if (!attr_set) {
-    UBR_CUDA_OK(cudaFuncSetAttribute(conv_halo_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-    attr_set = true;
-  }
+  const uint32_t smem = w_region + (uint32_t)nslots * slot_bytes + 2u * stage_bytes + 16u * nslots + 128u + 1024u;
+  UBR_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
   const int n_tiles = n_pad / nt;
-  int per_sm = (smem <= 110u * 1024u) ? 2 : 1;
+  int per_sm = (smem <= 110u * 1024u && p.tmem_cols <= 256u) ? 2 : 1;
   int ctas = per_sm * sm_count() / n_tiles;
   if (const char* e = getenv("UBR_HALO_MAX_CTAS")) { const int v = atoi(e); if (v > 0 && ctas > v) ctas = v; }
   if (ctas < 1) ctas = 1;
   if (ctas > p.ntiles) ctas = p.ntiles;
   dim3 grid((unsigned)ctas, (unsigned)n_tiles, 1);
-  conv_halo_kernel<<<grid, kHThreads, smem, stream>>>(p);
+  kern<<<grid, kHThreads, smem, stream>>>(p);
   UBR_LAUNCH_CHECK("conv_halo_kernel");
   return 0;
 }

@@ -36,6 +36,18 @@ struct WgradHaloParams {
   float* partials;              // [cta][r][s][cout][cin]
 };
 
+template <bool ACC>
+__device__ __forceinline__ void mma_wg(uint32_t d_tmem, uint32_t alo, uint32_t ahi, uint32_t blo, uint32_t bhi,
+                                       uint32_t idesc) {
+  asm volatile(
+      "{\n\t.reg .b64 da, db;\n\t.reg .pred p;\n\t"
+      "mov.b64 da, {%1, %2};\n\tmov.b64 db, {%3, %4};\n\t"
+      "setp.ne.b32 p, %6, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %5, p;\n\t}\n"
+      ::"r"(d_tmem), "r"(alo), "r"(ahi), "r"(blo), "r"(bhi), "r"(idesc), "n"(ACC ? 1 : 0)
+      : "memory");
+}
+
 __global__ void __launch_bounds__(kWHThreads, 1) wgrad_halo_kernel(const __grid_constant__ WgradHaloParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -74,84 +86,104 @@ __global__ void __launch_bounds__(kWHThreads, 1) wgrad_halo_kernel(const __grid_
   asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
 
   if (warp == 0) {
-    if (lane == 0) {
-      // ================= TMA producer =================
-      uint32_t gx = 0, gy = 0;
-      for (int tile = blockIdx.x; tile < p.ntiles; tile += gridDim.x) {
-        const int band = tile % p.bands;
-        const int cb = (tile / p.bands) % p.cblocks;
-        const int n = tile / (p.bands * p.cblocks);
-        const int h0 = band * p.bh, c0 = cb * 128;
-        for (int j = 0; j < rows_y; ++j) {
-          {
-            const uint32_t s = gy % SY, ph = (gy / SY) & 1u;
-            mbar_wait(yempty0 + 8u * s, ph ^ 1u);
-            const bool mirror = (int)s < P2;
-            mbar_arrive_expect_tx(yfull0 + 8u * s, mirror ? 2u * p.yrow_bytes : p.yrow_bytes);
-            tma_load_4d(yr_base + s * p.yslot_bytes, &p.y_map, yfull0 + 8u * s, 0, c0, h0 - p.pad + j, n);
-            if (mirror)
-              tma_load_4d(yr_base + (SY + s) * p.yslot_bytes, &p.y_map, yfull0 + 8u * s, 0, c0, h0 - p.pad + j, n);
-            ++gy;
-          }
+    // ================= TMA producer (whole warp walks the loop, one elected lane issues) =================
+    uint32_t sx = 0, phx = 0, sy = 0, phy = 0;
+    for (int tile = blockIdx.x; tile < p.ntiles; tile += gridDim.x) {
+      const int band = tile % p.bands;
+      const int cb = (tile / p.bands) % p.cblocks;
+      const int n = tile / (p.bands * p.cblocks);
+      const int h0 = band * p.bh, c0 = cb * 128;
+      for (int j = 0; j < rows_y; ++j) {
+        mbar_wait(yempty0 + 8u * sy, phy ^ 1u);
+        if (j >= P2) mbar_wait(xempty0 + 8u * sx, phx ^ 1u);
+        if (elect_one()) {
+          const bool mirror = (int)sy < P2;
+          const uint32_t fb = yfull0 + 8u * sy;
+          mbar_arrive_expect_tx(fb, mirror ? 2u * p.yrow_bytes : p.yrow_bytes);
+          tma_load_4d(yr_base + sy * p.yslot_bytes, &p.y_map, fb, 0, c0, h0 - p.pad + j, n);
+          if (mirror) tma_load_4d(yr_base + (SY + sy) * p.yslot_bytes, &p.y_map, fb, 0, c0, h0 - p.pad + j, n);
           if (j >= P2) {
-            const uint32_t s = gx % SX, ph = (gx / SX) & 1u;
-            mbar_wait(xempty0 + 8u * s, ph ^ 1u);
-            mbar_arrive_expect_tx(xfull0 + 8u * s, p.xrow_bytes);
-            tma_load_4d(xr_base + s * p.xslot_bytes, &p.x_map, xfull0 + 8u * s, 0, c0 - p.pad, h0 + (j - P2), n);
-            ++gx;
+            const uint32_t fx = xfull0 + 8u * sx;
+            mbar_arrive_expect_tx(fx, p.xrow_bytes);
+            tma_load_4d(xr_base + sx * p.xslot_bytes, &p.x_map, fx, 0, c0 - p.pad, h0 + (j - P2), n);
           }
         }
+        __syncwarp();
+        if (++sy == SY) { sy = 0; phy ^= 1u; }
+        if (j >= P2) { if (++sx == SX) { sx = 0; phx ^= 1u; } }
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
-      // ================= MMA issuer =================
-      const uint32_t lay_x = swizzle_layout_code((int)p.span_x);
-      const uint32_t lay_y = swizzle_layout_code((int)p.span_y);
-      uint32_t gx = 0, gy0 = 0, first = 1;
-      for (int tile = blockIdx.x; tile < p.ntiles; tile += gridDim.x) {
-        for (int i = 0; i < p.bh; ++i, ++gx) {
-          const int jfirst = (i == 0) ? 0 : P2;
-          for (int j = jfirst; j <= P2; ++j) {
-            const uint32_t g = gy0 + (uint32_t)(i + j);
-            mbar_wait(yfull0 + 8u * (g % SY), (g / SY) & 1u);
+    // ================= MMA issuer =================
+    // whole warp, warp-uniform control flow; one elected lane issues tcgen05.mma / tcgen05.commit
+    // descriptors are (lo, hi) pairs; per MMA only the 14-bit start-address field of lo changes (one add)
+    const uint64_t dx0 = make_smem_desc(0, p.span_x, 8u * p.span_x, swizzle_layout_code((int)p.span_x));
+    const uint64_t dy0 = make_smem_desc(0, p.yslot_bytes, 8u * p.span_y, swizzle_layout_code((int)p.span_y));
+    const uint32_t x_hi = (uint32_t)(dx0 >> 32), x_lo0 = (uint32_t)dx0 + (xr_base >> 4);
+    const uint32_t y_hi = (uint32_t)(dy0 >> 32), y_lo0 = (uint32_t)dy0 + (yr_base >> 4);
+    const uint32_t xs16 = p.xslot_bytes >> 4, ys16 = p.yslot_bytes >> 4;
+    const uint32_t xk16 = p.span_x, yk16 = p.span_y;            // 16 pixels * span / 16
+    const uint32_t xm16 = ((uint32_t)p.natoms * p.span_x) >> 4; // second MMA: M atoms shifted by natoms pixels
+    const uint32_t idesc = p.idesc, nN = (uint32_t)p.nN;
+    const bool two = p.nmma > 1;
+    const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem_base, 0);
+    uint32_t sx = 0, phx = 0, sy = 0, phy = 0;                  // x slot / dy slot of the current row (+ phases)
+    bool first = true;
+    for (int tile = blockIdx.x; tile < p.ntiles; tile += gridDim.x) {
+      for (int i = 0; i < p.bh; ++i) {
+        {
+          uint32_t s = sy, ph = phy;
+          for (int j = 0; j <= P2; ++j) {
+            if (i == 0 || j == P2) mbar_wait(yfull0 + 8u * s, ph);
+            if (++s == SY) { s = 0; ph ^= 1u; }
           }
-          const uint32_t sxi = gx % SX;
-          mbar_wait(xfull0 + 8u * sxi, (gx / SX) & 1u);
-          tc_fence_after();
-          const uint32_t x_src = xr_base + sxi * p.xslot_bytes;
-          const uint32_t y_src = yr_base + ((gy0 + (uint32_t)i) % SY) * p.yslot_bytes;
-#pragma unroll 1
-          for (int ks = 0; ks < 8; ++ks) {
-            const uint64_t bdesc = make_smem_desc(y_src + (uint32_t)ks * 16u * p.span_y, p.yslot_bytes, 8u * p.span_y, lay_y);
-            for (int m = 0; m < p.nmma; ++m) {
-              const uint64_t adesc = make_smem_desc(x_src + (uint32_t)(ks * 16 + m * p.natoms) * p.span_x, p.span_x,
-                                                    8u * p.span_x, lay_x);
-              tc_mma_bf16(tmem_base + (uint32_t)(m * p.nN), adesc, bdesc, p.idesc, (first && ks == 0) ? 0u : 1u);
-            }
-          }
-          first = 0;
-          tc_commit(xempty0 + 8u * sxi);
-          {
-            const uint32_t g = gy0 + (uint32_t)i;
-            tc_commit(yempty0 + 8u * (g % SY));
-          }
-          if (i == p.bh - 1)
-            for (int j = 1; j <= P2; ++j) {
-              const uint32_t g = gy0 + (uint32_t)(i + j);
-              tc_commit(yempty0 + 8u * (g % SY));
-            }
         }
-        gy0 += (uint32_t)rows_y;
+        mbar_wait(xfull0 + 8u * sx, phx);
+        tc_fence_after();
+        const uint32_t a0 = x_lo0 + sx * xs16;
+        const uint32_t b0 = y_lo0 + sy * ys16;
+        const bool last = (i == p.bh - 1);
+        if (elect_one()) {
+          if (first) {
+            mma_wg<false>(tmem_u, a0, x_hi, b0, y_hi, idesc);
+            if (two) mma_wg<false>(tmem_u + nN, a0 + xm16, x_hi, b0, y_hi, idesc);
+          } else {
+            mma_wg<true>(tmem_u, a0, x_hi, b0, y_hi, idesc);
+            if (two) mma_wg<true>(tmem_u + nN, a0 + xm16, x_hi, b0, y_hi, idesc);
+          }
+#pragma unroll
+          for (int ks = 1; ks < 8; ++ks) {
+            mma_wg<true>(tmem_u, a0 + ks * xk16, x_hi, b0 + ks * yk16, y_hi, idesc);
+            if (two) mma_wg<true>(tmem_u + nN, a0 + ks * xk16 + xm16, x_hi, b0 + ks * yk16, y_hi, idesc);
+          }
+          tc_commit(xempty0 + 8u * sx);
+          tc_commit(yempty0 + 8u * sy);
+          if (last) {
+            uint32_t s = sy;
+            for (int j = 0; j < P2; ++j) {
+              if (++s == SY) s = 0;
+              tc_commit(yempty0 + 8u * s);
+            }
+          }
+        }
+        __syncwarp();
+        first = false;
+        if (++sx == SX) { sx = 0; phx ^= 1u; }
+        const int adv = last ? 1 + P2 : 1;
+        for (int j = 0; j < adv; ++j)
+          if (++sy == SY) { sy = 0; phy ^= 1u; }
       }
-      tc_commit(accum_bar);
     }
+    if (elect_one()) tc_commit(accum_bar);
+    __syncwarp();
+    mbar_wait(accum_bar, 0);                       // the epilogue warps sleep on a named barrier, not on a spin loop
+    asm volatile("bar.sync 1, 160;" ::: "memory");
   } else {
     // ================= epilogue: TMEM -> fp32 partial [r][s][co][ci] =================
     const int quad = warp & 3;
     const int m = quad * 32 + lane;
     const int a_loc = m / p.cin, ci = m % p.cin;
-    mbar_wait(accum_bar, 0);
+    asm volatile("bar.sync 1, 160;" ::: "memory");
     tc_fence_after();
     const uint32_t t_row = tmem_base + ((uint32_t)(quad * 32) << 16);
     float* base = p.partials + (size_t)blockIdx.x * p.ksize * p.ksize * p.cout * p.cin;
@@ -243,12 +275,19 @@ int wgrad_halo_try(const ubr_view& x, const ubr_view& dy, int out_ch, int ksize,
   const uint32_t yrow = 128u * span_y;
   const uint32_t yslot = yrow;                                  // 4096 / 8192 / 16384: 1024-aligned
   const uint32_t budget = 225u * 1024u - 2048u;
+  // deep, balanced rings: ~1.5 us of HBM latency at 23 B/cycle/SM needs >= 64 KB in flight per SM
   int sy = 0, sx = 0;
-  for (int cand_sx = 4; cand_sx >= 2 && sy == 0; --cand_sx) {
-    const uint32_t left = budget - (uint32_t)cand_sx * xslot;
-    int s = (int)(left / yslot) - 2 * pad;
+  {
+    int s = (int)((budget - (uint32_t)(2 * pad) * yslot) / (xslot + yslot));
     if (s > 16) s = 16;
-    if (s >= 2 * pad + 2) { sy = s; sx = cand_sx; }
+    if (s >= 2 * pad + 2) { sx = s; sy = s; }
+    else {
+      // not enough room for equal depth: give dy its minimum window + 1 and x the rest
+      sy = 2 * pad + 2;
+      const uint32_t used = (uint32_t)(sy + 2 * pad) * yslot;
+      if (used + 2u * xslot <= budget) { sx = (int)((budget - used) / xslot); if (sx > 16) sx = 16; }
+      else sy = 0;
+    }
   }
   if (sy == 0) return 1;
   const int ntiles = (x.h / bh) * (x.w / 128) * x.n;
