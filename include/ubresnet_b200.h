@@ -56,6 +56,11 @@ uint64_t ubr_launch_count(void);          /* kernels launched by this library so
 int ubr_pack_weights(const float* src, int src_layout, int n_is_out, int out_ch, int in_ch, int kh, int kw,
                      int n_pad, int k_pad, void* dst_bf16, void* stream);
 
+/* batched form: `jobs_device` is a DEVICE array of njobs records of 10 int64:
+ * {src ptr, dst ptr, src_layout, n_is_out, out_ch, in_ch, kh, kw, n_pad, k_pad}; one launch repacks every conv of
+ * the network after an optimizer step. */
+int ubr_pack_weights_batch(const int64_t* jobs_device, int njobs, void* stream);
+
 /* ---- tensor-core implicit-GEMM convolutions (tcgen05 + TMEM + TMA) ----------------------------
  * nn.Conv2d(k in {1,3,7}, stride in {1,2}, padding=(k-1)/2)  forward:
  *   y[n,ho,wo,:] = sum_{r,s} x[n, ho*stride+r-pad, wo*stride+s-pad, :] * W[:, :, r, s]^T  (+ bias)
@@ -128,6 +133,10 @@ int ubr_block_tail_bwd_apply(ubr_view dout, ubr_view out, ubr_view y2, const flo
 /* ---- MaxPool2d(3, stride 2, pad 1) (ub_uresnet.py:44,97) and pointwise sums ---------------------- */
 int ubr_maxpool3s2_fwd(ubr_view x, ubr_view y, void* stream);
 int ubr_maxpool3s2_bwd(ubr_view x, ubr_view dy, ubr_view dx_accum, int accumulate, void* stream);
+/* same pooling, recording the argmax tap (kh*3+kw, first maximum in scan order) per output element in
+ * idx[n][h/2][w/2][c] (uint8) so the backward is a pure gather (what ATen/cuDNN keep as `indices`) */
+int ubr_maxpool3s2_fwd_idx(ubr_view x, ubr_view y, uint8_t* idx, void* stream);
+int ubr_maxpool3s2_bwd_idx(const uint8_t* idx, ubr_view dy, ubr_view dx_accum, int accumulate, void* stream);
 /* out = a + b (+ c); b/c may have ptr == NULL */
 int ubr_add(ubr_view a, ubr_view b, ubr_view c, ubr_view out, void* stream);
 

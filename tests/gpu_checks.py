@@ -299,6 +299,13 @@ def check_maxpool(c, n, h, w, seed=0):
     ops.maxpool_bwd(xa, act_from(dy), dx, False)
     torch.cuda.synchronize()
     res = [(name + "_fwd", relerr(ya.nchw_float(), ref), 0.0), (name + "_bwd", relerr(dx.nchw_float(), xg.grad), 8e-3)]
+    # recorded-argmax variant (what the engine uses): identical results
+    yb, idx = ops.maxpool_fwd_idx(xa)
+    dx2 = act_out(n, h, w, c)
+    ops.maxpool_bwd_idx(idx, act_from(dy), dx2, False)
+    torch.cuda.synchronize()
+    res += [(name + "_fwd_idx", relerr(yb.nchw_float(), ref), 0.0),
+            (name + "_bwd_idx", (dx2.nchw_float() - dx.nchw_float()).abs().max().item(), 0.0)]
     return res
 
 

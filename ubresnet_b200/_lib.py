@@ -25,6 +25,7 @@ SIGNATURES = {
     "ubr_sync_check": (_i, [_vp]),
     "ubr_launch_count": (_u64, []),
     "ubr_pack_weights": (_i, [_vp, _i, _i, _i, _i, _i, _i, _i, _i, _vp, _vp]),
+    "ubr_pack_weights_batch": (_i, [_vp, _i, _vp]),
     "ubr_conv2d_fwd": (_i, [View, _vp, _vp, _i, _i, _i, View, _vp, _i, _vp]),
     "ubr_conv2d_dgrad": (_i, [View, _vp, _i, _i, _i, View, _vp]),
     "ubr_conv2d_wgrad": (_i, [View, View, _i, _i, _i, _vp, _i, _vp, _u64, _vp]),
@@ -48,6 +49,8 @@ SIGNATURES = {
                                       View, View, _vp, _vp, _vp, _vp, _i, _vp]),
     "ubr_maxpool3s2_fwd": (_i, [View, View, _vp]),
     "ubr_maxpool3s2_bwd": (_i, [View, View, View, _i, _vp]),
+    "ubr_maxpool3s2_fwd_idx": (_i, [View, View, _vp, _vp]),
+    "ubr_maxpool3s2_bwd_idx": (_i, [_vp, View, View, _i, _vp]),
     "ubr_add": (_i, [View, View, View, View, _vp]),
     "ubr_logsoftmax_fwd": (_i, [_vp, _i, _i, _i, _i, _vp, _vp]),
     "ubr_logsoftmax_bwd": (_i, [_vp, _vp, _i, _i, _i, View, _vp]),

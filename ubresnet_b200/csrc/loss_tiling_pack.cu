@@ -160,6 +160,30 @@ __global__ void __launch_bounds__(256) pack_weights_kernel(const float* __restri
   }
 }
 
+// batched variant: one launch packs every job of a device-resident table (blockIdx.y = job)
+__global__ void __launch_bounds__(256) pack_weights_batch_kernel(const long long* __restrict__ jobs) {
+  const long long* j = jobs + (size_t)blockIdx.y * 10;
+  const float* src = reinterpret_cast<const float*>(j[0]);
+  __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(j[1]);
+  const int src_layout = (int)j[2], n_is_out = (int)j[3], out_ch = (int)j[4], in_ch = (int)j[5];
+  const int taps = (int)(j[6] * j[7]), n_pad = (int)j[8], k_pad = (int)j[9];
+  const long total = (long)(taps + 1) * n_pad * k_pad;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+    const int k = (int)(i % k_pad);
+    const int nn = (int)((i / k_pad) % n_pad);
+    const int t = (int)(i / ((long)k_pad * n_pad));
+    float v = 0.f;
+    if (t < taps) {
+      const int o = n_is_out ? nn : k, ci = n_is_out ? k : nn;
+      if (o < out_ch && ci < in_ch) {
+        const long idx = src_layout == 0 ? (((long)o * in_ch + ci) * taps + t) : (((long)ci * out_ch + o) * taps + t);
+        v = src[idx];
+      }
+    }
+    dst[i] = __float2bfloat16_rn(v);
+  }
+}
+
 static inline unsigned blocks_for(long total) {
   long nb = (total + 255) / 256;
   const long cap = (long)sm_count() * 16;
@@ -186,6 +210,14 @@ int ubr_pack_weights(const float* src, int src_layout, int n_is_out, int out_ch,
   pack_weights_kernel<<<blocks_for(total), 256, 0, (cudaStream_t)stream>>>(src, src_layout, n_is_out, out_ch, in_ch, kh,
                                                                            kw, n_pad, k_pad, (__nv_bfloat16*)dst_bf16);
   UBR_LAUNCH_CHECK("pack_weights_kernel");
+  return 0;
+}
+
+int ubr_pack_weights_batch(const int64_t* jobs_device, int njobs, void* stream) {
+  if (int rc = ensure_device()) return rc;
+  UBR_REQUIRE(jobs_device != nullptr && njobs >= 1 && njobs <= 65535, "pack_weights_batch: bad job table");
+  pack_weights_batch_kernel<<<dim3(48, (unsigned)njobs), 256, 0, (cudaStream_t)stream>>>((const long long*)jobs_device);
+  UBR_LAUNCH_CHECK("pack_weights_batch_kernel");
   return 0;
 }
 

@@ -90,18 +90,29 @@ __global__ void __launch_bounds__(kRedThreads) bn_stats_kernel(DView y, float* p
   block_reduce_store<2>(acc, y.c, partials);
 }
 
-// column sums of partials[nb][stride] for 32 consecutive columns starting at col0, by a (32 x 8) thread block:
-// threadIdx.x = column, threadIdx.y = row lane (coalesced 128-byte row reads, fixed summation order).
+// column sums of partials[nb][stride] for 32 consecutive columns starting at col0, by a (32 x 32) thread block:
+// threadIdx.x = column, threadIdx.y = row lane (coalesced 128-byte row reads, fixed summation order; the <= 19
+// loads of a thread are independent, so the kernel costs a few memory latencies instead of nb/8 of them).
+constexpr int kColLanes = 32;
 __device__ __forceinline__ double col_sum_32x8(const float* partials, int nb, int stride, int col, bool active) {
-  __shared__ double sred[8][33];
+  __shared__ double sred[kColLanes][33];
   double s = 0.0;
-  if (active)
-    for (int b = threadIdx.y; b < nb; b += 8) s += (double)partials[(size_t)b * stride + col];
+  if (active) {
+    float v[20];
+#pragma unroll
+    for (int i = 0; i < 20; ++i) {
+      const int b = threadIdx.y + i * kColLanes;
+      v[i] = b < nb ? partials[(size_t)b * stride + col] : 0.f;
+    }
+#pragma unroll
+    for (int i = 0; i < 20; ++i) s += (double)v[i];
+    for (int b = threadIdx.y + 20 * kColLanes; b < nb; b += kColLanes) s += (double)partials[(size_t)b * stride + col];
+  }
   sred[threadIdx.y][threadIdx.x] = s;
   __syncthreads();
   double t = 0.0;
 #pragma unroll
-  for (int l = 0; l < 8; ++l) t += sred[l][threadIdx.x];
+  for (int l = 0; l < kColLanes; ++l) t += sred[l][threadIdx.x];
   __syncthreads();
   return t;
 }
@@ -403,6 +414,86 @@ __global__ void __launch_bounds__(256) maxpool_fwd_kernel(const __nv_bfloat16* x
   }
 }
 
+// forward that also records the argmax tap (kh*3+kw of the FIRST maximum in scan order, as ATen) per element
+__global__ void __launch_bounds__(256) maxpool_fwd_idx_kernel(const __nv_bfloat16* x, int xld, int n, int h, int w, int c,
+                                                              __nv_bfloat16* y, int yld, uint8_t* __restrict__ idx) {
+  const int cgs = c >> 3, ho = h / 2, wo = w / 2;
+  const long total = (long)n * ho * wo * cgs;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+    const int cg = (int)(i % cgs);
+    long p = i / cgs;
+    const int ow = (int)(p % wo); p /= wo;
+    const int oh = (int)(p % ho);
+    const int b = (int)(p / ho);
+    float m[8];
+    uint32_t arg[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { m[j] = -INFINITY; arg[j] = 255u; }
+    for (int kh = 0; kh < 3; ++kh) {
+      const int ih = 2 * oh - 1 + kh;
+      if (ih < 0 || ih >= h) continue;
+      for (int kw = 0; kw < 3; ++kw) {
+        const int iw = 2 * ow - 1 + kw;
+        if (iw < 0 || iw >= w) continue;
+        float f[8];
+        load8(x + (((long)b * h + ih) * w + iw) * xld + cg * 8, f);
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          if (f[j] > m[j] || arg[j] == 255u) { m[j] = f[j]; arg[j] = (uint32_t)(kh * 3 + kw); }
+      }
+    }
+    store8(y + (((long)b * ho + oh) * wo + ow) * yld + cg * 8, m);
+    uint2 u;
+    u.x = arg[0] | (arg[1] << 8) | (arg[2] << 16) | (arg[3] << 24);
+    u.y = arg[4] | (arg[5] << 8) | (arg[6] << 16) | (arg[7] << 24);
+    *reinterpret_cast<uint2*>(idx + i * 8) = u;          // idx layout [n][ho][wo][c], c contiguous
+  }
+}
+
+// backward from the recorded argmax: each input pixel gathers from the <= 4 windows covering it (no atomics)
+__global__ void __launch_bounds__(256) maxpool_bwd_idx_kernel(const uint8_t* __restrict__ idx, int n, int h, int w, int c,
+                                                              const __nv_bfloat16* dy, int dyld, __nv_bfloat16* dx,
+                                                              int dxld, int accumulate) {
+  const int cgs = c >> 3, ho = h / 2, wo = w / 2;
+  const long total = (long)n * h * w * cgs;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+    const int cg = (int)(i % cgs);
+    long p = i / cgs;
+    const int iw = (int)(p % w); p /= w;
+    const int ih = (int)(p % h);
+    const int b = (int)(p / h);
+    float acc[8];
+    if (accumulate) load8(dx + (((long)b * h + ih) * w + iw) * dxld + cg * 8, acc);
+    else {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+    }
+    const int oh_lo = ih / 2, oh_hi = (ih + 1) / 2;
+    const int ow_lo = iw / 2, ow_hi = (iw + 1) / 2;
+    for (int oh = oh_lo; oh <= oh_hi; ++oh) {
+      if (oh >= ho) continue;
+      for (int ow = ow_lo; ow <= ow_hi; ++ow) {
+        if (ow >= wo) continue;
+        const long q = ((long)b * ho + oh) * wo + ow;
+        const uint2 u = *reinterpret_cast<const uint2*>(idx + (q * cgs + cg) * 8);
+        const uint32_t me = (uint32_t)((ih - (2 * oh - 1)) * 3 + (iw - (2 * ow - 1)));
+        const uint32_t m4 = me * 0x01010101u;
+        const uint32_t e0 = u.x ^ m4, e1 = u.y ^ m4;       // a zero byte <=> this input is that channel's argmax
+        if (((e0 - 0x01010101u) & ~e0 & 0x80808080u) | ((e1 - 0x01010101u) & ~e1 & 0x80808080u)) {
+          float g[8];
+          load8(dy + q * dyld + cg * 8, g);
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            if (((e0 >> (8 * j)) & 0xffu) == 0u) acc[j] += g[j];
+            if (((e1 >> (8 * j)) & 0xffu) == 0u) acc[4 + j] += g[4 + j];
+          }
+        }
+      }
+    }
+    store8(dx + (((long)b * h + ih) * w + iw) * dxld + cg * 8, acc);
+  }
+}
+
 // gather form of the backward: each input pixel re-derives the argmax (first maximum in (kh,kw) scan
 // order, as ATen's max_pool2d) of every window that covers it.  Deterministic, no atomics.
 __global__ void __launch_bounds__(256) maxpool_bwd_kernel(const __nv_bfloat16* x, int xld, int n, int h, int w, int c,
@@ -521,7 +612,7 @@ int ubr_bn_finalize(const void* workspace, int c, double count, const float* gam
   UBR_REQUIRE(workspace && scale && shift, "bn_finalize: null pointer");
   UBR_REQUIRE(c > 0 && c % 8 == 0 && count >= 1.0, "bn_finalize: bad c/count");
   const int nb = red_blocks((long)count, c);
-  bn_finalize_kernel<<<ceil_div(c, 32), dim3(32, 8), 0, (cudaStream_t)stream>>>((const float*)workspace, nb, c, count, gamma,
+  bn_finalize_kernel<<<ceil_div(c, 32), dim3(32, kColLanes), 0, (cudaStream_t)stream>>>((const float*)workspace, nb, c, count, gamma,
                                                                          beta, running_mean, running_var, momentum,
                                                                          eps, scale, shift, mean, invstd);
   UBR_LAUNCH_CHECK("bn_finalize_kernel");
@@ -596,7 +687,7 @@ int ubr_bn_act_bwd_apply(ubr_view dout, ubr_view y, const float* scale, const fl
   const float* partials = (const float*)workspace;
   float* sums = (float*)workspace + (size_t)kRedBlocks * 4 * v.c;
   cudaStream_t st = (cudaStream_t)stream;
-  sums_finalize_kernel<<<ceil_div(2 * v.c, 32), dim3(32, 8), 0, st>>>(partials, nb, 2 * v.c, sums);
+  sums_finalize_kernel<<<ceil_div(2 * v.c, 32), dim3(32, kColLanes), 0, st>>>(partials, nb, 2 * v.c, sums);
   UBR_LAUNCH_CHECK("sums_finalize_kernel");
   if (dgamma || dbeta) {
     param_grad_kernel<<<ceil_div(v.c, 128), 128, 0, st>>>(sums, v.c, 0, 1, dgamma, dbeta, accumulate);
@@ -659,7 +750,7 @@ int ubr_block_tail_bwd_apply(ubr_view dout, ubr_view out, ubr_view y2, const flo
   const float* partials = (const float*)workspace;
   float* sums = (float*)workspace + (size_t)kRedBlocks * 4 * v.c;
   cudaStream_t st = (cudaStream_t)stream;
-  sums_finalize_kernel<<<ceil_div(ns * v.c, 32), dim3(32, 8), 0, st>>>(partials, nb, ns * v.c, sums);
+  sums_finalize_kernel<<<ceil_div(ns * v.c, 32), dim3(32, kColLanes), 0, st>>>(partials, nb, ns * v.c, sums);
   UBR_LAUNCH_CHECK("sums_finalize_kernel");
   if (dgamma2 || dbeta2) {
     param_grad_kernel<<<ceil_div(v.c, 128), 128, 0, st>>>(sums, v.c, 0, 1, dgamma2, dbeta2, accumulate);
@@ -710,6 +801,36 @@ int ubr_maxpool3s2_bwd(ubr_view x, ubr_view dy, ubr_view dx_accum, int accumulat
       (const __nv_bfloat16*)x.ptr, x.ld, x.n, x.h, x.w, x.c, (const __nv_bfloat16*)dy.ptr, dy.ld,
       (__nv_bfloat16*)dx_accum.ptr, dx_accum.ld, accumulate);
   UBR_LAUNCH_CHECK("maxpool_bwd_kernel");
+  return 0;
+}
+
+int ubr_maxpool3s2_fwd_idx(ubr_view x, ubr_view y, uint8_t* idx, void* stream) {
+  if (int rc = ensure_device()) return rc;
+  if (int rc = chk(x, "maxpool_fwd_idx.x")) return rc;
+  if (int rc = chk(y, "maxpool_fwd_idx.y")) return rc;
+  UBR_REQUIRE(idx != nullptr && ((uintptr_t)idx & 7) == 0, "maxpool_fwd_idx: idx must be a non-null 8-byte aligned pointer");
+  UBR_REQUIRE(x.h % 2 == 0 && x.w % 2 == 0 && y.n == x.n && y.h == x.h / 2 && y.w == x.w / 2 && y.c == x.c,
+              "maxpool_fwd_idx: shape mismatch");
+  const long total = (long)y.n * y.h * y.w * (x.c >> 3);
+  maxpool_fwd_idx_kernel<<<ew_blocks(total), 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)x.ptr, x.ld, x.n, x.h, x.w,
+                                                                             x.c, (__nv_bfloat16*)y.ptr, y.ld, idx);
+  UBR_LAUNCH_CHECK("maxpool_fwd_idx_kernel");
+  return 0;
+}
+
+int ubr_maxpool3s2_bwd_idx(const uint8_t* idx, ubr_view dy, ubr_view dx_accum, int accumulate, void* stream) {
+  if (int rc = ensure_device()) return rc;
+  if (int rc = chk(dy, "maxpool_bwd_idx.dy")) return rc;
+  if (int rc = chk(dx_accum, "maxpool_bwd_idx.dx")) return rc;
+  UBR_REQUIRE(idx != nullptr, "maxpool_bwd_idx: null idx");
+  UBR_REQUIRE(dx_accum.n == dy.n && dx_accum.h == 2 * dy.h && dx_accum.w == 2 * dy.w && dx_accum.c == dy.c,
+              "maxpool_bwd_idx: shape mismatch");
+  const long total = (long)dx_accum.n * dx_accum.h * dx_accum.w * (dy.c >> 3);
+  maxpool_bwd_idx_kernel<<<ew_blocks(total), 256, 0, (cudaStream_t)stream>>>(idx, dx_accum.n, dx_accum.h, dx_accum.w, dy.c,
+                                                                             (const __nv_bfloat16*)dy.ptr, dy.ld,
+                                                                             (__nv_bfloat16*)dx_accum.ptr, dx_accum.ld,
+                                                                             accumulate);
+  UBR_LAUNCH_CHECK("maxpool_bwd_idx_kernel");
   return 0;
 }
 

@@ -18,7 +18,7 @@ from .ops import Act
 
 class _ConvW:
     """bf16 packed operands of one conv / deconv parameter, refreshed when the parameter changes."""
-    __slots__ = ("param", "transposed", "fwd", "dgrad", "_key")
+    __slots__ = ("param", "transposed", "fwd", "dgrad", "_key", "_dgrad_stale")
 
     def __init__(self, param, transposed=False):
         self.param = param
@@ -26,6 +26,7 @@ class _ConvW:
         self.fwd = None
         self.dgrad = None
         self._key = None
+        self._dgrad_stale = False
 
     def refresh(self, need_dgrad):
         key = (self.param.data_ptr(), self.param._version)
@@ -33,8 +34,39 @@ class _ConvW:
             self.fwd = ops.pack_weights(self.param, self.transposed, True)
             self.dgrad = None
             self._key = key
-        if need_dgrad and self.dgrad is None:
+        if need_dgrad and (self.dgrad is None or self._dgrad_stale):
             self.dgrad = ops.pack_weights(self.param, self.transposed, False)
+            self._dgrad_stale = False
+
+    # ---- batched refresh (one launch for the whole network, Engine._refresh_packs)
+    def dims(self):
+        w = self.param
+        if self.transposed:
+            in_ch, out_ch, kh, kw = w.shape
+        else:
+            out_ch, in_ch, kh, kw = w.shape
+        return out_ch, in_ch, kh, kw
+
+    def jobs(self, need_dgrad):
+        """[(n_is_out, dst)] that must be (re)packed; allocates destination buffers on first use."""
+        key = (self.param.data_ptr(), self.param._version)
+        changed = key != self._key
+        out_ch, in_ch, kh, kw = self.dims()
+        pad = lambda v: (v + 15) // 16 * 16
+        res = []
+        if changed or self.fwd is None:
+            if self.fwd is None or self.fwd.device != self.param.device:
+                self.fwd = torch.empty((kh * kw + 1, pad(out_ch), pad(in_ch)), dtype=torch.bfloat16, device=self.param.device)
+            res.append((1, self.fwd))
+        if need_dgrad and (changed or self.dgrad is None or self._dgrad_stale):
+            if self.dgrad is None or self.dgrad.device != self.param.device:
+                self.dgrad = torch.empty((kh * kw + 1, pad(in_ch), pad(out_ch)), dtype=torch.bfloat16, device=self.param.device)
+            res.append((0, self.dgrad))
+            self._dgrad_stale = False
+        elif changed:
+            self._dgrad_stale = True
+        self._key = key
+        return res
 
 
 class _BlockRec:
@@ -57,6 +89,37 @@ class Engine:
             self._packs[id(conv)] = ent
         ent.refresh(need_dgrad)
         return ent
+
+    def _refresh_packs(self, need_dgrad):
+        """Re-derive the bf16 GEMM operands of every conv whose fp32 parameter changed (optimizer step,
+        load_state_dict) with ONE kernel launch; the device job table is cached while pointers are stable."""
+        m = self.model
+        convs = []
+        for mod in m.modules():
+            if mod is m.conv1:
+                continue
+            if isinstance(mod, torch.nn.ConvTranspose2d):
+                convs.append((mod, True))
+            elif isinstance(mod, torch.nn.Conv2d):
+                convs.append((mod, False))
+        jobs = []
+        for conv, transposed in convs:
+            ent = self._packs.get(id(conv))
+            if ent is None or ent.param is not conv.weight:
+                ent = _ConvW(conv.weight, transposed)
+                self._packs[id(conv)] = ent
+            for n_is_out, dst in ent.jobs(need_dgrad):
+                out_ch, in_ch, kh, kw = ent.dims()
+                jobs.append((ent.param.data_ptr(), dst.data_ptr(), 1 if transposed else 0, n_is_out, out_ch, in_ch, kh, kw,
+                             dst.shape[1], dst.shape[2]))
+        if not jobs:
+            return
+        key = tuple(jobs)
+        cache = getattr(self, "_job_cache", None)
+        if cache is None or cache[0] != key:
+            table = torch.tensor(jobs, dtype=torch.int64).to(m.conv1.weight.device)
+            self._job_cache = cache = (key, table)
+        ops.pack_weights_batch(cache[1], len(jobs))
 
     def _workspaces(self, n, h, w, device):
         """(bn workspace, wgrad workspace, stem workspace) sized for the largest layer."""
@@ -156,6 +219,7 @@ class Engine:
         dev = x.device
         p = m.inplanes
         bn_ws, _, _ = self._workspaces(n, h, w, dev)
+        self._refresh_packs(need_grad)
         saved = {}
         # concat buffers: cat[i] feeds dec_layer{i}; channels [0,Cd) deconv output, [Cd,2Cd) skip x_{i-1}
         cat = {}
@@ -167,7 +231,10 @@ class Engine:
         y0 = ops.stem_conv_fwd(x, m.conv1.weight, m.conv1.bias)
         st0 = self._bn(y0, m.bn1, training, bn_ws)
         x0 = ops.bn_act(y0, st0, True, out=Act(cat[1], p, p))
-        h0 = ops.maxpool_fwd(x0)
+        if need_grad:
+            h0, pool_idx = ops.maxpool_fwd_idx(x0)
+        else:
+            h0, pool_idx = ops.maxpool_fwd(x0), None
         # ---- encoder (:103-107)
         recs = {}
         cur = h0
@@ -202,7 +269,7 @@ class Engine:
                 if bns:
                     torch._foreach_add_(bns, 1)
         if need_grad:
-            saved.update(x=x, y0=y0, st0=st0, x0=x0, h0=h0, recs=recs, dec_in=dec_in, d1=cur, y10=y10, st10=st10,
+            saved.update(x=x, y0=y0, st0=st0, x0=x0, h0=h0, pool_idx=pool_idx, recs=recs, dec_in=dec_in, d1=cur, y10=y10, st10=st10,
                          a10=a10, logp=logp, shape=(n, h, w))
         return logp, saved
 
@@ -293,7 +360,7 @@ class Engine:
             done("enc%d" % i)
         # ---- stem: x0 gets the pool gradient plus the dec1 skip gradient (accumulated in place)
         dx0 = dskip[0]
-        ops.maxpool_bwd(saved["x0"], dcur, dx0, True)
+        ops.maxpool_bwd_idx(saved["pool_idx"], dcur, dx0, True)
         dy0 = ops.bn_act_bwd(dx0, saved["y0"], saved["st0"], True, bn_ws, grads[m.bn1.weight], grads[m.bn1.bias])
         ops.stem_conv_wgrad(saved["x"], dy0, grads[m.conv1.weight], grads[m.conv1.bias], False, stem_ws)
         done("stem")

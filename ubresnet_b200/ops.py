@@ -97,6 +97,12 @@ def pack_weights(w, transposed, n_is_out):
     return dst
 
 
+def pack_weights_batch(table, njobs):
+    """table: device int64 [njobs, 10] job records (see ubr_pack_weights_batch)."""
+    lib = _lib.load()
+    _lib.check(lib.ubr_pack_weights_batch(table.data_ptr(), int(njobs), _stream()), "pack_weights_batch")
+
+
 def conv2d_fwd(x, wpk, bias, out_ch, ksize, stride, y=None, y_f32=None):
     lib = _lib.load()
     if y_f32 is not None:
@@ -286,6 +292,23 @@ def maxpool_fwd(x, y=None):
 def maxpool_bwd(x, dy, dx, accumulate):
     lib = _lib.load()
     _lib.check(lib.ubr_maxpool3s2_bwd(x.view(), dy.view(), dx.view(), int(accumulate), _stream()), "maxpool3s2_bwd")
+    return dx
+
+
+def maxpool_fwd_idx(x, y=None):
+    """MaxPool2d(3,2,1) that also returns the argmax taps (uint8, NHWC) for the gather backward."""
+    lib = _lib.load()
+    if y is None:
+        y = Act.empty(x.n, x.h // 2, x.w // 2, x.c, x.buf.device)
+    idx = torch.empty((x.n, x.h // 2, x.w // 2, x.c), dtype=torch.uint8, device=x.buf.device)
+    _lib.check(lib.ubr_maxpool3s2_fwd_idx(x.view(), y.view(), idx.data_ptr(), _stream()), "maxpool3s2_fwd_idx")
+    return y, idx
+
+
+def maxpool_bwd_idx(idx, dy, dx, accumulate):
+    lib = _lib.load()
+    _lib.check(lib.ubr_maxpool3s2_bwd_idx(idx.data_ptr(), dy.view(), dx.view(), int(accumulate), _stream()),
+               "maxpool3s2_bwd_idx")
     return dx
 
 
