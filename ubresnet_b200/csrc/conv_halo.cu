@@ -36,6 +36,7 @@ struct HaloParams {
   int nslots;
   uint32_t span, row_bytes, slot_bytes, w_tap_bytes, w_region, stage_bytes;
   uint32_t idesc, tmem_cols, acc_stride;
+  int nb;                       // TMEM ring: nb output-row accumulators of nt columns (power of two)
   int out_mode;                 // 0: bf16 staging + TMA store, 1: fp32 direct (logits), 2: bf16 direct stores
   int o_box_c;
   const float* bias;
@@ -83,9 +84,9 @@ __global__ void __launch_bounds__(kHThreads, 1) conv_halo_kernel(const __grid_co
   const uint32_t full0 = bar_base;
   const uint32_t empty0 = full0 + 8u * p.nslots;
   const uint32_t wbar = empty0 + 8u * p.nslots;
-  const uint32_t accf0 = wbar + 8u;         // [4]
-  const uint32_t acce0 = accf0 + 32u;       // [4]
-  const uint32_t tmem_slot = acce0 + 32u;
+  const uint32_t accf0 = wbar + 8u;         // [32]
+  const uint32_t acce0 = accf0 + 256u;      // [32]
+  const uint32_t tmem_slot = acce0 + 256u;
 
   constexpr int PAD = (KS - 1) / 2;
   constexpr int ROWS_EXTRA = 2 * PAD;
@@ -101,7 +102,7 @@ __global__ void __launch_bounds__(kHThreads, 1) conv_halo_kernel(const __grid_co
       mbar_init(empty0 + 8u * s, 1);
     }
     mbar_init(wbar, 1);
-    for (uint32_t b = 0; b < 4; ++b) {
+    for (uint32_t b = 0; b < (uint32_t)p.nb; ++b) {
       mbar_init(accf0 + 8u * b, 1);
       mbar_init(acce0 + 8u * b, 4);
     }
@@ -119,13 +120,26 @@ __global__ void __launch_bounds__(kHThreads, 1) conv_halo_kernel(const __grid_co
   tc_fence_after();
   uint32_t tmem_base;
   asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
+  // every accumulator of the TMEM ring starts at zero: all MMAs accumulate (see the issuer)
+  if (warp >= 2 && warp < 6) {
+    const uint32_t t_q = tmem_base + ((uint32_t)((warp & 3) * 32) << 16);
+    for (uint32_t c = 0; c < p.tmem_cols; c += 16) tmem_st16_zero(t_q + c);
+    tmem_st_wait();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
 
   if (warp == 0) {
     // ================= TMA producer (whole warp walks the loop, one elected lane issues) =================
     if (elect_one()) {
       mbar_arrive_expect_tx(wbar, (uint32_t)(KS * KS) * p.w_tap_bytes);
-      for (int t = 0; t < KS * KS; ++t)
-        tma_load_3d(w_base + (uint32_t)t * p.w_tap_bytes, &p.w_map, wbar, 0, co0, t);
+      // smem weight order [s'][j]: s' = column offset index (dw = s'-PAD), j = accumulator-ring order (dh = PAD-j)
+      for (int sp = 0; sp < KS; ++sp)
+        for (int j = 0; j < KS; ++j) {
+          const int slab = p.flip ? (j * KS + (KS - 1 - sp)) : ((KS - 1 - j) * KS + sp);
+          tma_load_3d(w_base + (uint32_t)(sp * KS + j) * p.w_tap_bytes, &p.w_map, wbar, 0, co0, slab);
+        }
     }
     __syncwarp();
     uint32_t s = 0, ph = 0;
@@ -145,72 +159,56 @@ __global__ void __launch_bounds__(kHThreads, 1) conv_halo_kernel(const __grid_co
       }
     }
   } else if (warp == 1) {
-    // ================= MMA issuer =================
-    // The WHOLE warp walks the loop with warp-uniform values (descriptors live in uniform registers); only the
-    // tcgen05.mma / tcgen05.commit instructions are issued by one elected lane.  (Issuing from inside an
-    // `if (lane == 0)` region makes ptxas wrap every UTCHMMA in a per-thread waterfall loop: ~10 SASS
-    // instructions per MMA at ~6 cycles each on a lone warp -- measured, profiles/r01c_*.)
+    // ================= MMA issuer (row-stationary, taps stacked along N) =================
+    // Input row R contributes to the KS output rows R-PAD..R+PAD.  Their accumulators are CONSECUTIVE column
+    // blocks of a TMEM ring, so ONE tcgen05.mma per (column offset s', K step) with N = (#rows x nt) updates all
+    // of them:  D[pixel][(j, co)] += A[row R shifted by s'][pixel][ci] * W[s'][j][co][ci].   KS x fewer MMA
+    // instructions than tap-by-tap issue (each costs >= ~52 cycles at small N, profiles/r01_ubench T2).
+    // The WHOLE warp walks the loop with warp-uniform values; one elected lane issues MMAs / commits.
     const uint32_t layout = swizzle_layout_code((int)p.span);
     const uint32_t desc_hi = (uint32_t)((make_smem_desc(0, 0, 8u * p.span, layout)) >> 32);
     const uint32_t span16 = p.span >> 4, slot16 = p.slot_bytes >> 4, wtap16 = p.w_tap_bytes >> 4;
-    const uint32_t ring16 = ring_base >> 4;
-    // weight descriptor of tap index t' = r'*KS + s' (row/col OFFSET order): forward slab t', data-gradient
-    // slab KS*KS-1-t' (180-degree rotated filter)
-    const uint32_t b_first = (w_base >> 4) + (p.flip ? (uint32_t)(KS * KS - 1) * wtap16 : 0u);
-    const uint32_t b_step = p.flip ? (0u - wtap16) : wtap16;
-    const uint32_t idesc = p.idesc;
+    const uint32_t ring16 = ring_base >> 4, w16 = w_base >> 4;
+    const uint32_t idesc0 = p.idesc;                       // N field cleared; N = rows * nt added per MMA
+    const uint32_t nunit = ((uint32_t)p.nt >> 3) << 17;
+    const uint32_t NBm = (uint32_t)p.nb - 1u, nbsh = (uint32_t)__ffs(p.nb) - 1u;
     const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem_base, 0);
     mbar_wait(wbar, 0);
-    uint32_t s_first = 0, ph_first = 0;       // ring slot / phase of the first input row of the current output row
-    uint32_t r = 0;
-    for (int tile = blockIdx.x; tile < p.ntiles; tile += gridDim.x) {
-      for (int i = 0; i < p.bh; ++i, ++r) {
-        // rows s_first .. s_first+2*PAD must have landed (all but the newest were waited for earlier)
-        {
-          uint32_t s = s_first, ph = ph_first;
-#pragma unroll
-          for (int j = 0; j <= ROWS_EXTRA; ++j) {
-            if (i == 0 || j == ROWS_EXTRA) mbar_wait(full0 + 8u * s, ph);
-            if (++s == S) { s = 0; ph ^= 1u; }
-          }
+    uint32_t s = 0, ph = 0;                  // ring slot / phase of the current input row
+    uint32_t q0 = 0;                         // CTA-wide output row counter at the start of the tile
+    for (int tile = blockIdx.x; tile < p.ntiles; tile += gridDim.x, q0 += (uint32_t)p.bh) {
+      for (int j = 0; j < rows_in; ++j) {
+        mbar_wait(full0 + 8u * s, ph);
+        const int olo = j > ROWS_EXTRA ? j - ROWS_EXTRA : 0;
+        const int ohi = j < p.bh ? j : p.bh - 1;
+        if (j < p.bh) {                      // first touch of output row j's accumulator: drained + zeroed?
+          const uint32_t q = q0 + (uint32_t)j;
+          mbar_wait(acce0 + 8u * (q & NBm), ((q >> nbsh) & 1u) ^ 1u);
         }
-        const uint32_t b = r & 3u;
-        mbar_wait(acce0 + 8u * b, ((r >> 2) & 1u) ^ 1u);
         tc_fence_after();
-        const uint32_t d_tmem = tmem_u + b * p.acc_stride;
-        const bool last = (i == p.bh - 1);
+        const uint32_t blo = (q0 + (uint32_t)olo) & NBm;
+        const uint32_t nrows = (uint32_t)(ohi - olo + 1);
+        const uint32_t n1 = min(nrows, (uint32_t)p.nb - blo), n2 = nrows - n1;
+        const uint32_t jb0 = (uint32_t)(olo - j + ROWS_EXTRA);     // first W block (ring order) this row touches
         if (elect_one()) {
-          uint32_t srow = s_first;
+          const uint32_t a_row = ring16 + s * slot16;
+          const uint32_t d1 = tmem_u + blo * (uint32_t)p.nt;
+          const uint32_t id1 = idesc0 + n1 * nunit, id2 = idesc0 + n2 * nunit;
 #pragma unroll
-          for (int rr = 0; rr < KS; ++rr) {
-            const uint32_t a_row = ring16 + srow * slot16;
+          for (int sp = 0; sp < KS; ++sp) {
+            const uint32_t a_t = a_row + (uint32_t)sp * span16;
+            const uint32_t b_t = w16 + ((uint32_t)(sp * KS) + jb0) * wtap16;
 #pragma unroll
-            for (int ss = 0; ss < KS; ++ss) {
-              const uint32_t a_t = a_row + (uint32_t)ss * span16;
-              const uint32_t b_t = b_first + (uint32_t)(rr * KS + ss) * b_step;
-#pragma unroll
-              for (int k = 0; k < KSTEPS; ++k) {
-                if (rr == 0 && ss == 0 && k == 0) mma_lohi<false>(d_tmem, a_t, desc_hi, b_t, desc_hi, idesc);
-                else mma_lohi<true>(d_tmem, a_t + 2u * k, desc_hi, b_t + 2u * k, desc_hi, idesc);
-              }
-            }
-            if (++srow == S) srow = 0;
-          }
-          tc_commit(accf0 + 8u * b);
-          tc_commit(empty0 + 8u * s_first);      // oldest row: no later output row of this tile needs it
-          if (last) {
-            uint32_t s = s_first;
-#pragma unroll
-            for (int j = 0; j < ROWS_EXTRA; ++j) {
-              if (++s == S) s = 0;
-              tc_commit(empty0 + 8u * s);
+            for (int k = 0; k < KSTEPS; ++k) {
+              mma_lohi<true>(d1, a_t + 2u * k, desc_hi, b_t + 2u * k, desc_hi, id1);
+              if (n2) mma_lohi<true>(tmem_u, a_t + 2u * k, desc_hi, b_t + n1 * wtap16 + 2u * k, desc_hi, id2);
             }
           }
+          tc_commit(empty0 + 8u * s);                            // the row is consumed exactly once
+          if (j >= ROWS_EXTRA) tc_commit(accf0 + 8u * ((q0 + (uint32_t)(j - ROWS_EXTRA)) & NBm));
         }
         __syncwarp();
-        const uint32_t adv = last ? (uint32_t)(1 + ROWS_EXTRA) : 1u;
-        for (uint32_t j = 0; j < adv; ++j)
-          if (++s_first == S) { s_first = 0; ph_first ^= 1u; }
+        if (++s == S) { s = 0; ph ^= 1u; }
       }
     }
   } else {
@@ -233,10 +231,10 @@ __global__ void __launch_bounds__(kHThreads, 1) conv_halo_kernel(const __grid_co
       for (int i = grp; i < p.bh; i += 2) {
         const uint32_t r = r0 + (uint32_t)i;
         const int h = band * p.bh + i;
-        const uint32_t b = r & 3u;
-        mbar_wait(accf0 + 8u * b, (r >> 2) & 1u);
+        const uint32_t b = r & ((uint32_t)p.nb - 1u);
+        mbar_wait(accf0 + 8u * b, (r >> ((uint32_t)__ffs(p.nb) - 1u)) & 1u);
         tc_fence_after();
-        const uint32_t t_row = tmem_base + b * p.acc_stride + ((uint32_t)(quad * 32) << 16);
+        const uint32_t t_row = tmem_base + b * (uint32_t)p.nt + ((uint32_t)(quad * 32) << 16);
         if (p.out_mode == 2) {
           // bf16 direct stores: one pixel (nt <= 32 channels) per thread, 16-byte vectors
           __nv_bfloat16* dst = p.out_bf16 + ((size_t)((size_t)n * p.out_h + h) * p.out_w + (c0 + row)) * (size_t)p.out_ld + co0;
@@ -244,6 +242,7 @@ __global__ void __launch_bounds__(kHThreads, 1) conv_halo_kernel(const __grid_co
             uint32_t v[16];
             tmem_ld16(t_row + (uint32_t)c, v);
             tmem_ld_wait();
+            tmem_st16_zero(t_row + (uint32_t)c);             // hand the accumulator back zeroed
             float f[16];
 #pragma unroll
             for (int j = 0; j < 16; ++j) f[j] = __uint_as_float(v[j]);
@@ -259,6 +258,7 @@ __global__ void __launch_bounds__(kHThreads, 1) conv_halo_kernel(const __grid_co
             *reinterpret_cast<uint4*>(dst + c) = u0;
             *reinterpret_cast<uint4*>(dst + c + 8) = u1;
           }
+          tmem_st_wait();
           tc_fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive(acce0 + 8u * b);
@@ -269,6 +269,7 @@ __global__ void __launch_bounds__(kHThreads, 1) conv_halo_kernel(const __grid_co
             uint32_t v[16];
             tmem_ld16(t_row + (uint32_t)c, v);
             tmem_ld_wait();
+            tmem_st16_zero(t_row + (uint32_t)c);             // hand the accumulator back zeroed
             float f[16];
 #pragma unroll
             for (int j = 0; j < 16; ++j) f[j] = __uint_as_float(v[j]);
@@ -287,6 +288,7 @@ __global__ void __launch_bounds__(kHThreads, 1) conv_halo_kernel(const __grid_co
             asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a0), "r"(pk[0]), "r"(pk[1]), "r"(pk[2]), "r"(pk[3]) : "memory");
             asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a1), "r"(pk[4]), "r"(pk[5]), "r"(pk[6]), "r"(pk[7]) : "memory");
           }
+          tmem_st_wait();
           tc_fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive(acce0 + 8u * b);      // accumulator drained: the issuer may overwrite it
@@ -305,6 +307,7 @@ __global__ void __launch_bounds__(kHThreads, 1) conv_halo_kernel(const __grid_co
             uint32_t v[16];
             tmem_ld16(t_row + (uint32_t)c, v);
             tmem_ld_wait();
+            tmem_st16_zero(t_row + (uint32_t)c);             // hand the accumulator back zeroed
             if (p.out_ld == 4 && c == 0 && co0 == 0) {
               float4 o;
               o.x = (0 < p.out_cols) ? __uint_as_float(v[0]) + (p.bias ? __ldg(p.bias + 0) : 0.f) : 0.f;
@@ -320,6 +323,7 @@ __global__ void __launch_bounds__(kHThreads, 1) conv_halo_kernel(const __grid_co
               }
             }
           }
+          tmem_st_wait();
           tc_fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive(acce0 + 8u * b);
@@ -396,14 +400,23 @@ int conv_halo_try(const ubr_view& x, const void* wpk, int nslabs, int n_pad, con
   const uint32_t budget = 225u * 1024u - 1024u - 512u;
   int nt = 0, nslots = 0, out_mode = 0;
   uint32_t w_region = 0, stage_bytes = 0;
-  for (int cand = n_pad > 128 ? 128 : n_pad; cand >= 16; cand -= 16) {
+  const int nt_max = ks == 1 ? 128 : (ks == 3 ? 64 : 32);     // stacked MMA: ks * nt <= 256 columns
+  for (int cand = n_pad > nt_max ? nt_max : n_pad; cand >= 16; cand -= 16) {
     if (n_pad % cand) continue;
     const uint32_t wr = ((uint32_t)ntaps * cand * span + 1023u) & ~1023u;
     const int mode = y_f32 ? 1 : (cand <= 32 ? 2 : 0);
     const uint32_t st = mode == 0 ? 128u * (uint32_t)cand * 2u : 0u;
-    if (wr + 2u * st + (uint32_t)(2 * pad + 2) * slot_bytes > budget) continue;
+    if (wr + 2u * st + 4u * slot_bytes > budget) continue;
     int s = (int)((budget - wr - 2u * st) / slot_bytes);
     if (s > 16) s = 16;
+    // two CTAs per SM (two issuing threads) beat one deep ring: shrink the ring if that makes a second CTA fit
+    {
+      const uint32_t half = 110u * 1024u - 1024u - 1024u;
+      if (wr + 2u * st + 6u * slot_bytes <= half && (ks + 3 <= 8 ? 8 : 16) * cand <= 256) {
+        const int s2 = (int)((half - wr - 2u * st) / slot_bytes);
+        if (s2 < s) s = s2;
+      }
+    }
     nt = cand; nslots = s; w_region = wr; stage_bytes = st; out_mode = mode;
     break;
   }
@@ -442,11 +455,20 @@ int conv_halo_try(const ubr_view& x, const void* wpk, int nslabs, int n_pad, con
   p.nslots = nslots;
   p.span = span; p.row_bytes = row_bytes; p.slot_bytes = slot_bytes;
   p.w_tap_bytes = (uint32_t)nt * span; p.w_region = w_region; p.stage_bytes = stage_bytes;
-  p.idesc = make_idesc_bf16(128, nt, 0, 0);
-  p.acc_stride = nt <= 64 ? 64u : 128u;
-  p.tmem_cols = 4u * p.acc_stride;
+  p.idesc = make_idesc_bf16(128, 0, 0, 0);                   // N = (#stacked rows * nt) is added per MMA
+  {
+    int nb = 4;
+    while (nb < ks + 3) nb <<= 1;                            // rows in flight (ks) + slack for the epilogue
+    while (nb * nt > 512 && nb > 1) nb >>= 1;
+    if (nb < ks + 1) return 1;
+    p.nb = nb;
+    uint32_t cols = 32;
+    while ((int)cols < nb * nt) cols <<= 1;
+    p.tmem_cols = cols;
+    p.acc_stride = (uint32_t)nt;
+  }
   p.bias = bias;
-  const uint32_t smem = w_region + (uint32_t)nslots * slot_bytes + 2u * stage_bytes + 16u * nslots + 128u + 1024u;
+  const uint32_t smem = w_region + (uint32_t)nslots * slot_bytes + 2u * stage_bytes + 16u * nslots + 640u + 1024u;
   UBR_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
   const int n_tiles = n_pad / nt;
   int per_sm = (smem <= 110u * 1024u && p.tmem_cols <= 256u) ? 2 : 1;

@@ -252,7 +252,7 @@ static bool wg_halo_shape_ok(int cin, int cout, int ksize, int h, int w) {
 }
 
 uint64_t wgrad_halo_workspace_bytes(int in_ch, int out_ch_pad, int ksize) {
-  return (uint64_t)148 * ksize * ksize * out_ch_pad * in_ch * sizeof(float);
+  return (uint64_t)296 * ksize * ksize * out_ch_pad * in_ch * sizeof(float);
 }
 
 int wgrad_halo_try(const ubr_view& x, const ubr_view& dy, int out_ch, int ksize, float* dw, int accumulate,
@@ -275,24 +275,35 @@ int wgrad_halo_try(const ubr_view& x, const ubr_view& dy, int out_ch, int ksize,
   const uint32_t yrow = 128u * span_y;
   const uint32_t yslot = yrow;                                  // 4096 / 8192 / 16384: 1024-aligned
   const uint32_t budget = 225u * 1024u - 2048u;
-  // deep, balanced rings: ~1.5 us of HBM latency at 23 B/cycle/SM needs >= 64 KB in flight per SM
-  int sy = 0, sx = 0;
+  // deep, balanced rings: ~1.5 us of HBM latency at 23 B/cycle/SM needs >= 64 KB in flight per SM.  The single
+  // issuing thread is the other limiter, so prefer TWO CTAs per SM (half-depth rings each) whenever smem/TMEM allow.
+  uint32_t cols = 32;
+  while ((int)cols < nmma * nN) cols <<= 1;
+  int sy = 0, sx = 0, per_sm = 1;
   {
-    int s = (int)((budget - (uint32_t)(2 * pad) * yslot) / (xslot + yslot));
-    if (s > 16) s = 16;
-    if (s >= 2 * pad + 2) { sx = s; sy = s; }
-    else {
-      // not enough room for equal depth: give dy its minimum window + 1 and x the rest
-      sy = 2 * pad + 2;
-      const uint32_t used = (uint32_t)(sy + 2 * pad) * yslot;
-      if (used + 2u * xslot <= budget) { sx = (int)((budget - used) / xslot); if (sx > 16) sx = 16; }
-      else sy = 0;
+    const uint32_t half = 110u * 1024u - 2048u;
+    int s2 = (int)((half - (uint32_t)(2 * pad) * yslot) / (xslot + yslot));
+    if (cols <= 256 && s2 >= 2 * pad + 3 && s2 >= 4) {
+      if (s2 > 12) s2 = 12;
+      sx = sy = s2; per_sm = 2;
+    } else {
+      int s = (int)((budget - (uint32_t)(2 * pad) * yslot) / (xslot + yslot));
+      if (s > 16) s = 16;
+      if (s >= 2 * pad + 2) { sx = s; sy = s; }
+      else {
+        // not enough room for equal depth: give dy its minimum window + 1 and x the rest
+        sy = 2 * pad + 2;
+        const uint32_t used = (uint32_t)(sy + 2 * pad) * yslot;
+        if (used + 2u * xslot <= budget) { sx = (int)((budget - used) / xslot); if (sx > 16) sx = 16; }
+        else sy = 0;
+      }
     }
   }
   if (sy == 0) return 1;
   const int ntiles = (x.h / bh) * (x.w / 128) * x.n;
   int ctas = sm_count();
   if (ctas > 148) ctas = 148;
+  ctas *= per_sm;
   if (const char* e = getenv("UBR_HALO_MAX_CTAS")) { const int v = atoi(e); if (v > 0 && ctas > v) ctas = v; }
   if (ctas > ntiles) ctas = ntiles;
   const uint64_t need = (uint64_t)ctas * ksize * ksize * cout * cin * sizeof(float);
@@ -321,8 +332,6 @@ int wgrad_halo_try(const ubr_view& x, const ubr_view& dy, int out_ch, int ksize,
   p.span_x = span_x; p.span_y = span_y; p.xrow_bytes = xrow; p.xslot_bytes = xslot;
   p.yrow_bytes = yrow; p.yslot_bytes = yslot;
   p.idesc = make_idesc_bf16(128, nN, 1, 1);
-  uint32_t cols = 32;
-  while ((int)cols < nmma * nN) cols <<= 1;
   p.tmem_cols = cols;
   p.partials = (float*)workspace;
   const uint32_t smem = (uint32_t)sx * xslot + (uint32_t)(sy + 2 * pad) * yslot + 16u * (sx + sy) + 32u + 1024u;
