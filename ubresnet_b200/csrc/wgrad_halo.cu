@@ -48,28 +48,28 @@ __device__ __forceinline__ void mma_wg(uint32_t d_tmem, uint32_t alo, uint32_t a
       : "memory");
 }
 
+template <int KS, int NMMA>
 __global__ void __launch_bounds__(kWHThreads, 1) wgrad_halo_kernel(const __grid_constant__ WgradHaloParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
+  constexpr int P2 = KS - 1;
+  constexpr int PAD = (KS - 1) / 2;
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
-  const uint32_t xr_base = smem_base;
-  const uint32_t yr_base = xr_base + (uint32_t)p.sx * p.xslot_bytes;
-  const uint32_t bar_base = yr_base + (uint32_t)(p.sy + 2 * p.pad) * p.yslot_bytes;
-  const uint32_t xfull0 = bar_base;
-  const uint32_t xempty0 = xfull0 + 8u * p.sx;
-  const uint32_t yfull0 = xempty0 + 8u * p.sx;
-  const uint32_t yempty0 = yfull0 + 8u * p.sy;
-  const uint32_t accum_bar = yempty0 + 8u * p.sy;
+  // unified ring: slot = [dy row (128 px) | x row (128+2p px, padded)]; the last P2 slots mirror slots 0..P2-1 (dy part)
+  const uint32_t ring = smem_base;
+  const uint32_t slot_bytes = p.yslot_bytes + p.xslot_bytes;
+  const uint32_t bar_base = ring + (uint32_t)(p.sy + P2) * slot_bytes;
+  const uint32_t full0 = bar_base;
+  const uint32_t empty0 = full0 + 8u * p.sy;
+  const uint32_t accum_bar = empty0 + 8u * p.sy;
   const uint32_t tmem_slot = accum_bar + 8u;
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-  const uint32_t SX = (uint32_t)p.sx, SY = (uint32_t)p.sy;
-  const int P2 = 2 * p.pad;
+  const uint32_t SY = (uint32_t)p.sy;
   const int rows_y = p.bh + P2;
 
   if (threadIdx.x == 0) {
-    for (int s = 0; s < p.sx; ++s) { mbar_init(xfull0 + 8u * s, 1); mbar_init(xempty0 + 8u * s, 1); }
-    for (int s = 0; s < p.sy; ++s) { mbar_init(yfull0 + 8u * s, 1); mbar_init(yempty0 + 8u * s, 1); }
+    for (int s = 0; s < p.sy; ++s) { mbar_init(full0 + 8u * s, 1); mbar_init(empty0 + 8u * s, 1); }
     mbar_init(accum_bar, 1);
     fence_mbar_init();
     prefetch_tmap(&p.x_map);
@@ -84,94 +84,86 @@ __global__ void __launch_bounds__(kWHThreads, 1) wgrad_halo_kernel(const __grid_
   tc_fence_after();
   uint32_t tmem_base;
   asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
+  if (warp >= 2) {                                   // accumulators start at zero: every MMA accumulates
+    const uint32_t t_q = tmem_base + ((uint32_t)((warp & 3) * 32) << 16);
+    for (uint32_t c = 0; c < p.tmem_cols; c += 16) tmem_st16_zero(t_q + c);
+    tmem_st_wait();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
 
   if (warp == 0) {
     // ================= TMA producer (whole warp walks the loop, one elected lane issues) =================
-    uint32_t sx = 0, phx = 0, sy = 0, phy = 0;
+    uint32_t s = 0, ph = 0;
     for (int tile = blockIdx.x; tile < p.ntiles; tile += gridDim.x) {
       const int band = tile % p.bands;
       const int cb = (tile / p.bands) % p.cblocks;
       const int n = tile / (p.bands * p.cblocks);
       const int h0 = band * p.bh, c0 = cb * 128;
       for (int j = 0; j < rows_y; ++j) {
-        mbar_wait(yempty0 + 8u * sy, phy ^ 1u);
-        if (j >= P2) mbar_wait(xempty0 + 8u * sx, phx ^ 1u);
+        mbar_wait(empty0 + 8u * s, ph ^ 1u);
         if (elect_one()) {
-          const bool mirror = (int)sy < P2;
-          const uint32_t fb = yfull0 + 8u * sy;
-          mbar_arrive_expect_tx(fb, mirror ? 2u * p.yrow_bytes : p.yrow_bytes);
-          tma_load_4d(yr_base + sy * p.yslot_bytes, &p.y_map, fb, 0, c0, h0 - p.pad + j, n);
-          if (mirror) tma_load_4d(yr_base + (SY + sy) * p.yslot_bytes, &p.y_map, fb, 0, c0, h0 - p.pad + j, n);
-          if (j >= P2) {
-            const uint32_t fx = xfull0 + 8u * sx;
-            mbar_arrive_expect_tx(fx, p.xrow_bytes);
-            tma_load_4d(xr_base + sx * p.xslot_bytes, &p.x_map, fx, 0, c0 - p.pad, h0 + (j - P2), n);
-          }
+          const bool mirror = (int)s < P2;
+          const bool has_x = j < p.bh;
+          const uint32_t fb = full0 + 8u * s;
+          mbar_arrive_expect_tx(fb, (mirror ? 2u * p.yrow_bytes : p.yrow_bytes) + (has_x ? p.xrow_bytes : 0u));
+          tma_load_4d(ring + s * slot_bytes, &p.y_map, fb, 0, c0, h0 - PAD + j, n);
+          if (mirror) tma_load_4d(ring + (SY + s) * slot_bytes, &p.y_map, fb, 0, c0, h0 - PAD + j, n);
+          if (has_x) tma_load_4d(ring + s * slot_bytes + p.yslot_bytes, &p.x_map, fb, 0, c0 - PAD, h0 + j, n);
         }
         __syncwarp();
-        if (++sy == SY) { sy = 0; phy ^= 1u; }
-        if (j >= P2) { if (++sx == SX) { sx = 0; phx ^= 1u; } }
+        if (++s == SY) { s = 0; ph ^= 1u; }
       }
     }
   } else if (warp == 1) {
     // ================= MMA issuer =================
-    // whole warp, warp-uniform control flow; one elected lane issues tcgen05.mma / tcgen05.commit
-    // descriptors are (lo, hi) pairs; per MMA only the 14-bit start-address field of lo changes (one add)
+    // whole warp, warp-uniform control flow; one elected lane issues tcgen05.mma / tcgen05.commit.
+    // Per row: ONE barrier wait (the newest dy row), 8*NMMA MMAs (one integer add each), ONE commit.
     const uint64_t dx0 = make_smem_desc(0, p.span_x, 8u * p.span_x, swizzle_layout_code((int)p.span_x));
-    const uint64_t dy0 = make_smem_desc(0, p.yslot_bytes, 8u * p.span_y, swizzle_layout_code((int)p.span_y));
-    const uint32_t x_hi = (uint32_t)(dx0 >> 32), x_lo0 = (uint32_t)dx0 + (xr_base >> 4);
-    const uint32_t y_hi = (uint32_t)(dy0 >> 32), y_lo0 = (uint32_t)dy0 + (yr_base >> 4);
-    const uint32_t xs16 = p.xslot_bytes >> 4, ys16 = p.yslot_bytes >> 4;
+    const uint64_t dy0 = make_smem_desc(0, slot_bytes, 8u * p.span_y, swizzle_layout_code((int)p.span_y));
+    const uint32_t x_hi = (uint32_t)(dx0 >> 32), x_lo0 = (uint32_t)dx0 + ((ring + p.yslot_bytes) >> 4);
+    const uint32_t y_hi = (uint32_t)(dy0 >> 32), y_lo0 = (uint32_t)dy0 + (ring >> 4);
+    const uint32_t s16 = slot_bytes >> 4;
     const uint32_t xk16 = p.span_x, yk16 = p.span_y;            // 16 pixels * span / 16
     const uint32_t xm16 = ((uint32_t)p.natoms * p.span_x) >> 4; // second MMA: M atoms shifted by natoms pixels
     const uint32_t idesc = p.idesc, nN = (uint32_t)p.nN;
-    const bool two = p.nmma > 1;
     const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem_base, 0);
-    uint32_t sx = 0, phx = 0, sy = 0, phy = 0;                  // x slot / dy slot of the current row (+ phases)
-    bool first = true;
+    uint32_t s = 0, ph = 0;                                     // slot / phase of the current x row
     for (int tile = blockIdx.x; tile < p.ntiles; tile += gridDim.x) {
       for (int i = 0; i < p.bh; ++i) {
         {
-          uint32_t s = sy, ph = phy;
+          uint32_t sw = s, pw = ph;
+#pragma unroll
           for (int j = 0; j <= P2; ++j) {
-            if (i == 0 || j == P2) mbar_wait(yfull0 + 8u * s, ph);
-            if (++s == SY) { s = 0; ph ^= 1u; }
+            if (i == 0 || j == P2) mbar_wait(full0 + 8u * sw, pw);
+            if (++sw == SY) { sw = 0; pw ^= 1u; }
           }
         }
-        mbar_wait(xfull0 + 8u * sx, phx);
         tc_fence_after();
-        const uint32_t a0 = x_lo0 + sx * xs16;
-        const uint32_t b0 = y_lo0 + sy * ys16;
+        const uint32_t a0 = x_lo0 + s * s16;
+        const uint32_t b0 = y_lo0 + s * s16;
         const bool last = (i == p.bh - 1);
         if (elect_one()) {
-          if (first) {
-            mma_wg<false>(tmem_u, a0, x_hi, b0, y_hi, idesc);
-            if (two) mma_wg<false>(tmem_u + nN, a0 + xm16, x_hi, b0, y_hi, idesc);
-          } else {
-            mma_wg<true>(tmem_u, a0, x_hi, b0, y_hi, idesc);
-            if (two) mma_wg<true>(tmem_u + nN, a0 + xm16, x_hi, b0, y_hi, idesc);
-          }
 #pragma unroll
-          for (int ks = 1; ks < 8; ++ks) {
+          for (int ks = 0; ks < 8; ++ks) {
             mma_wg<true>(tmem_u, a0 + ks * xk16, x_hi, b0 + ks * yk16, y_hi, idesc);
-            if (two) mma_wg<true>(tmem_u + nN, a0 + ks * xk16 + xm16, x_hi, b0 + ks * yk16, y_hi, idesc);
+            if (NMMA > 1) mma_wg<true>(tmem_u + nN, a0 + ks * xk16 + xm16, x_hi, b0 + ks * yk16, y_hi, idesc);
           }
-          tc_commit(xempty0 + 8u * sx);
-          tc_commit(yempty0 + 8u * sy);
+          tc_commit(empty0 + 8u * s);
           if (last) {
-            uint32_t s = sy;
+            uint32_t sw = s;
+#pragma unroll
             for (int j = 0; j < P2; ++j) {
-              if (++s == SY) s = 0;
-              tc_commit(yempty0 + 8u * s);
+              if (++sw == SY) sw = 0;
+              tc_commit(empty0 + 8u * sw);
             }
           }
         }
         __syncwarp();
-        first = false;
-        if (++sx == SX) { sx = 0; phx ^= 1u; }
         const int adv = last ? 1 + P2 : 1;
         for (int j = 0; j < adv; ++j)
-          if (++sy == SY) { sy = 0; phy ^= 1u; }
+          if (++s == SY) { s = 0; ph ^= 1u; }
       }
     }
     if (elect_one()) tc_commit(accum_bar);
@@ -186,18 +178,18 @@ __global__ void __launch_bounds__(kWHThreads, 1) wgrad_halo_kernel(const __grid_
     asm volatile("bar.sync 1, 160;" ::: "memory");
     tc_fence_after();
     const uint32_t t_row = tmem_base + ((uint32_t)(quad * 32) << 16);
-    float* base = p.partials + (size_t)blockIdx.x * p.ksize * p.ksize * p.cout * p.cin;
-    for (int mm = 0; mm < p.nmma; ++mm) {
+    float* base = p.partials + (size_t)blockIdx.x * KS * KS * p.cout * p.cin;
+    for (int mm = 0; mm < NMMA; ++mm) {
       const int a = mm * p.natoms + a_loc;                 // horizontal tap s
-      const bool valid = a < p.ksize;
+      const bool valid = a < KS;
       for (int c = 0; c < p.nN; c += 16) {
         uint32_t v[16];
         tmem_ld16(t_row + (uint32_t)(mm * p.nN + c), v);
         tmem_ld_wait();
         if (valid) {
           const int b = c / p.cout, co0 = c % p.cout;      // cout is a multiple of 16: a 16-column group has one b
-          const int r = p.ksize - 1 - b;
-          float* dst = base + ((size_t)(r * p.ksize + a) * p.cout + co0) * p.cin + ci;
+          const int r = KS - 1 - b;
+          float* dst = base + ((size_t)(r * KS + a) * p.cout + co0) * p.cin + ci;
 #pragma unroll
           for (int j = 0; j < 16; ++j) dst[(size_t)j * p.cin] = __uint_as_float(v[j]);
         }
@@ -281,23 +273,19 @@ int wgrad_halo_try(const ubr_view& x, const ubr_view& dy, int out_ch, int ksize,
   while ((int)cols < nmma * nN) cols <<= 1;
   int sy = 0, sx = 0, per_sm = 1;
   {
+    // unified ring: every slot holds one dy row and one x row; 2p extra (mirror) slots
+    const uint32_t slot = xslot + yslot;
     const uint32_t half = 110u * 1024u - 2048u;
-    int s2 = (int)((half - (uint32_t)(2 * pad) * yslot) / (xslot + yslot));
+    int s2 = (int)(half / slot) - 2 * pad;
     if (cols <= 256 && s2 >= 2 * pad + 3 && s2 >= 4) {
       if (s2 > 12) s2 = 12;
-      sx = sy = s2; per_sm = 2;
+      sy = s2; per_sm = 2;
     } else {
-      int s = (int)((budget - (uint32_t)(2 * pad) * yslot) / (xslot + yslot));
+      int s = (int)(budget / slot) - 2 * pad;
       if (s > 16) s = 16;
-      if (s >= 2 * pad + 2) { sx = s; sy = s; }
-      else {
-        // not enough room for equal depth: give dy its minimum window + 1 and x the rest
-        sy = 2 * pad + 2;
-        const uint32_t used = (uint32_t)(sy + 2 * pad) * yslot;
-        if (used + 2u * xslot <= budget) { sx = (int)((budget - used) / xslot); if (sx > 16) sx = 16; }
-        else sy = 0;
-      }
+      if (s >= 2 * pad + 2) sy = s;
     }
+    sx = sy;
   }
   if (sy == 0) return 1;
   const int ntiles = (x.h / bh) * (x.w / 128) * x.n;
@@ -334,14 +322,20 @@ int wgrad_halo_try(const ubr_view& x, const ubr_view& dy, int out_ch, int ksize,
   p.idesc = make_idesc_bf16(128, nN, 1, 1);
   p.tmem_cols = cols;
   p.partials = (float*)workspace;
-  const uint32_t smem = (uint32_t)sx * xslot + (uint32_t)(sy + 2 * pad) * yslot + 16u * (sx + sy) + 32u + 1024u;
-  static bool attr_set = false;
-  if (!attr_set) {
-    UBR_CUDA_OK(cudaFuncSetAttribute(wgrad_halo_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-    attr_set = true;
+  const uint32_t smem = (uint32_t)(sy + 2 * pad) * (xslot + yslot) + 16u * sy + 32u + 1024u;
+  typedef void (*wg_kernel_t)(const WgradHaloParams);
+  wg_kernel_t kern = nullptr;
+  switch (ksize * 10 + nmma) {
+    case 11: kern = wgrad_halo_kernel<1, 1>; break;
+    case 31: kern = wgrad_halo_kernel<3, 1>; break;
+    case 32: kern = wgrad_halo_kernel<3, 2>; break;
+    case 71: kern = wgrad_halo_kernel<7, 1>; break;
+    case 72: kern = wgrad_halo_kernel<7, 2>; break;
+    default: return 1;
   }
+  UBR_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
   UBR_REQUIRE(smem <= 227u * 1024u, "wgrad(halo): smem plan %u too large", smem);
-  wgrad_halo_kernel<<<ctas, kWHThreads, smem, stream>>>(p);
+  kern<<<ctas, kWHThreads, smem, stream>>>(p);
   UBR_LAUNCH_CHECK("wgrad_halo_kernel");
   const int total = ksize * ksize * cout * cin;
   wgrad_halo_reduce_kernel<<<(total + 255) / 256, 256, 0, stream>>>(p.partials, ctas, ksize, cout, cin, out_ch, dw,
