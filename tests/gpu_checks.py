@@ -108,6 +108,26 @@ def check_conv_dgrad(cin, cout, k, stride, n, h, w, seed=0):
     return [(name, e, 1e-2)]
 
 
+def check_conv_dgrad_acc(cin, cout, k, n, h, w, seed=0, expect_fused=True):
+    """dx += dgrad(dy) fused in the epilogue (ubr_conv2d_dgrad_acc); falls back (returns False) on unfused shapes."""
+    name = "conv_dgrad_acc_ci%d_co%d_k%d_n%d_%dx%d" % (cin, cout, k, n, h, w)
+    dy = bf(gen(n, cout, h, w, seed=seed))
+    wt = bf(gen(cout, cin, k, k, seed=seed + 1, scale=(2.0 / (k * k * cout)) ** 0.5))
+    base = bf(gen(n, cin, h, w, seed=seed + 2))
+    ref = torch.nn.grad.conv2d_input((n, cin, h, w), wt, dy, 1, (k - 1) // 2) + base
+    dxa = act_from(base, 2 * cin, cin)
+    wpk = ops.pack_weights(wt.to(DEV), False, False)
+    fused = ops.conv2d_dgrad_acc(act_from(dy), wpk, cin, k, 1, dxa)
+    torch.cuda.synchronize()
+    res = [(name + "_fused_path", 0.0 if fused == expect_fused else 1.0, 0.0)]
+    if fused:
+        res.append((name, relerr(dxa.nchw_float(), ref), 1e-2))
+        res.append((name + "_slice_untouched", (dxa.buf[..., :cin].float() - 7.0).abs().max().item(), 0.0))
+    else:
+        res.append((name + "_untouched", relerr(dxa.nchw_float(), base), 0.0))
+    return res
+
+
 def check_conv_wgrad(cin, cout, k, stride, n, h, w, seed=0, cout_pad=None):
     name = "conv_wgrad_ci%d_co%d_k%d_s%d_n%d_%dx%d" % (cin, cout, k, stride, n, h, w)
     ho, wo = h // stride, w // stride
@@ -420,6 +440,9 @@ CHECKS = {
     "halo_fwd_slices": lambda: check_conv_fwd(32, 16, 3, 1, 2, 32, 128, in_ld=64, out_ld=32, seed=29),
     "halo_dgrad": lambda: (check_conv_dgrad(16, 32, 3, 1, 2, 64, 128, seed=31) + check_conv_dgrad(128, 64, 3, 1, 1, 32, 128, seed=32)
                            + check_conv_dgrad(16, 16, 7, 1, 1, 32, 256, seed=33) + check_conv_dgrad(64, 32, 1, 1, 1, 32, 128, seed=34)),
+    "halo_dgrad_acc": lambda: (check_conv_dgrad_acc(16, 16, 3, 2, 64, 128, seed=51) + check_conv_dgrad_acc(32, 16, 3, 1, 32, 256, seed=52)
+                               + check_conv_dgrad_acc(64, 64, 3, 1, 32, 128, seed=53, expect_fused=False)
+                               + check_conv_dgrad_acc(16, 16, 3, 1, 32, 32, seed=54, expect_fused=False)),
     "halo_wgrad_3x3": lambda: (check_conv_wgrad(16, 16, 3, 1, 2, 64, 128, seed=41) + check_conv_wgrad(32, 32, 3, 1, 1, 32, 256, seed=42)
                                + check_conv_wgrad(64, 64, 3, 1, 1, 32, 128, seed=43) + check_conv_wgrad(16, 32, 3, 1, 1, 32, 128, seed=44)
                                + check_conv_wgrad(64, 32, 3, 1, 1, 32, 128, seed=45)),

@@ -28,6 +28,7 @@ SIGNATURES = {
     "ubr_pack_weights_batch": (_i, [_vp, _i, _vp]),
     "ubr_conv2d_fwd": (_i, [View, _vp, _vp, _i, _i, _i, View, _vp, _i, _vp]),
     "ubr_conv2d_dgrad": (_i, [View, _vp, _i, _i, _i, View, _vp]),
+    "ubr_conv2d_dgrad_acc": (_i, [View, _vp, _i, _i, _i, View, _vp]),
     "ubr_conv2d_wgrad": (_i, [View, View, _i, _i, _i, _vp, _i, _vp, _u64, _vp]),
     "ubr_wgrad_workspace_bytes": (_u64, [_i, _i, _i, _i, _i, _i]),
     "ubr_deconv4s2_fwd": (_i, [View, _vp, _i, View, _vp]),

@@ -382,7 +382,19 @@ int ubr_conv2d_fwd(ubr_view x, const void* wpk, const float* bias, int out_ch, i
   return launch_conv_gemm(p, x.n, ho, wo, t, x.c, n_pad, wpk, ksize * ksize, taps, nt, (cudaStream_t)stream);
 }
 
+static int conv2d_dgrad_impl(ubr_view dy, const void* wpk, int in_ch, int ksize, int stride, ubr_view dx, int accumulate,
+                             void* stream);
+
 int ubr_conv2d_dgrad(ubr_view dy, const void* wpk, int in_ch, int ksize, int stride, ubr_view dx, void* stream) {
+  return conv2d_dgrad_impl(dy, wpk, in_ch, ksize, stride, dx, 0, stream);
+}
+
+int ubr_conv2d_dgrad_acc(ubr_view dy, const void* wpk, int in_ch, int ksize, int stride, ubr_view dx, void* stream) {
+  return conv2d_dgrad_impl(dy, wpk, in_ch, ksize, stride, dx, 1, stream);
+}
+
+static int conv2d_dgrad_impl(ubr_view dy, const void* wpk, int in_ch, int ksize, int stride, ubr_view dx, int accumulate,
+                             void* stream) {
   if (int rc = ensure_device()) return rc;
   if (int rc = check_view(dy, "conv2d_dgrad.dy")) return rc;
   if (int rc = check_view(dx, "conv2d_dgrad.dx")) return rc;
@@ -405,14 +417,16 @@ int ubr_conv2d_dgrad(ubr_view dy, const void* wpk, int in_ch, int ksize, int str
       for (int s = 0; s < ksize; ++s) taps[nt++] = TapSpec{pad - r, pad - s, 0, r * ksize + s};
     {
       const int hrc = conv_halo_try(dy, wpk, ksize * ksize, in_ch, taps, nt, nullptr, &dx, nullptr, 0, in_ch,
-                                    (cudaStream_t)stream);
+                                    (cudaStream_t)stream, accumulate);
       if (hrc <= 0) return hrc;
     }
+    if (accumulate) return 1;      // not fused for this shape: caller adds separately
     p.out_mode = 0;
     p.o_box_c = out_box_c(in_ch >= 128 ? 128 : in_ch);
     if (int rc = make_act_map(&p.o_map, dx, p.o_box_c, t)) return rc;
     return launch_conv_gemm(p, dy.n, dy.h, dy.w, t, dy.c, in_ch, wpk, ksize * ksize, taps, nt, (cudaStream_t)stream);
   }
+  if (accumulate) return 1;
   // stride 2: input row x = 2*o + r - pad.  For output parity (ph,pw) only taps with (r-pad)&1 == ph contribute,
   // from dy row o = (x - (r-pad))/2 = i + (ph - (r-pad))/2.
   for (int ph = 0; ph < 2; ++ph)

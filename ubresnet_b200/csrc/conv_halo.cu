@@ -43,6 +43,7 @@ struct HaloParams {
   float* out_f32;
   __nv_bfloat16* out_bf16;
   int out_ld, out_cols, out_h, out_w;
+  int accumulate;               // out_mode 2 only: out += result (fp32 add of the stored bf16 value, one rounding)
 };
 
 template <int N>
@@ -250,6 +251,16 @@ __global__ void __launch_bounds__(kHThreads, 1) conv_halo_kernel(const __grid_co
 #pragma unroll
               for (int j = 0; j < 16; ++j) f[j] += __ldg(p.bias + co0 + c + j);
             }
+            if (p.accumulate) {
+              const uint4 o0 = *reinterpret_cast<const uint4*>(dst + c);
+              const uint4 o1 = *reinterpret_cast<const uint4*>(dst + c + 8);
+              const uint32_t ow[8] = {o0.x, o0.y, o0.z, o0.w, o1.x, o1.y, o1.z, o1.w};
+#pragma unroll
+              for (int j = 0; j < 8; ++j) {
+                const float2 t = unpack_bf16x2(ow[j]);
+                f[2 * j] += t.x; f[2 * j + 1] += t.y;
+              }
+            }
             uint4 u0, u1;
             u0.x = pack_bf16x2(f[0], f[1]); u0.y = pack_bf16x2(f[2], f[3]);
             u0.z = pack_bf16x2(f[4], f[5]); u0.w = pack_bf16x2(f[6], f[7]);
@@ -368,7 +379,7 @@ static halo_kernel_t pick_halo_kernel(int ks, int ksteps) {
 
 int conv_halo_try(const ubr_view& x, const void* wpk, int nslabs, int n_pad, const TapSpec* taps, int ntaps,
                   const float* bias, const ubr_view* y, float* y_f32, int y_f32_ld, int out_cols,
-                  cudaStream_t stream) {
+                  cudaStream_t stream, int accumulate) {
   if (halo_disabled()) return 1;
   const int cin = x.c;
   if (!(cin == 16 || cin == 32 || cin == 64)) return 1;
@@ -421,6 +432,7 @@ int conv_halo_try(const ubr_view& x, const void* wpk, int nslabs, int n_pad, con
     break;
   }
   if (nt == 0) return 1;
+  if (accumulate && out_mode != 2) return 1;                 // in-epilogue accumulation: direct-store path only
 
   HaloParams p;
   memset(&p, 0, sizeof(p));
@@ -468,6 +480,7 @@ int conv_halo_try(const ubr_view& x, const void* wpk, int nslabs, int n_pad, con
     p.acc_stride = (uint32_t)nt;
   }
   p.bias = bias;
+  p.accumulate = accumulate;
   const uint32_t smem = w_region + (uint32_t)nslots * slot_bytes + 2u * stage_bytes + 16u * nslots + 640u + 1024u;
   UBR_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
   const int n_tiles = n_pad / nt;

@@ -297,12 +297,17 @@ class Engine:
         if not need_dx:
             return None
         w1 = self._pack(blk.conv1, True)
-        dx1 = ops.conv2d_dgrad(dy1, w1.dgrad, cin, 3, s)
+        # grad wrt the block input = dgrad(conv1) + residual-branch grad (+ skip grad): the residual term is
+        # produced first and the 3x3 data gradient accumulates onto it inside its epilogue where a fused path exists
         if has_bp:
             wb = self._pack(blk.bypass, True)
-            dxb = ops.conv2d_dgrad(dres, wb.dgrad, cin, 1, s)
-            return ops.add(dx1, dxb, extra, out=dx1)
-        return ops.add(dx1, dres, extra, out=dx1)
+            base = ops.conv2d_dgrad(dres, wb.dgrad, cin, 1, s)
+        else:
+            base = dres
+        if ops.conv2d_dgrad_acc(dy1, w1.dgrad, cin, 3, s, base):
+            return ops.add(base, extra, None, out=base) if extra is not None else base
+        dx1 = ops.conv2d_dgrad(dy1, w1.dgrad, cin, 3, s)
+        return ops.add(dx1, base, extra, out=dx1)
 
     def _double_bwd(self, dbl, recs, dout, grads, bn_ws, wg_ws, extra=None):
         r1, r2 = recs

@@ -125,6 +125,16 @@ def conv2d_dgrad(dy, wpk, in_ch, ksize, stride, dx=None):
     return dx
 
 
+def conv2d_dgrad_acc(dy, wpk, in_ch, ksize, stride, dx):
+    """dx += dgrad(dy) fused in the conv epilogue.  Returns False (nothing done) if the shape has no fused path."""
+    lib = _lib.load()
+    rc = lib.ubr_conv2d_dgrad_acc(dy.view(), wpk.data_ptr(), in_ch, ksize, stride, dx.view(), _stream())
+    if rc == 1:
+        return False
+    _lib.check(rc, "conv2d_dgrad_acc")
+    return True
+
+
 def wgrad_workspace_bytes(grid_n, grid_h, grid_w, m_ch, n_ch, ntaps):
     return int(_lib.load().ubr_wgrad_workspace_bytes(grid_n, grid_h, grid_w, m_ch, n_ch, ntaps))
 
