@@ -79,6 +79,28 @@ def main():
               flush=True)
         tot[0] += t_f; tot[1] += t_d; tot[2] += t_w
         del x, dy, y, dx, ws
+    # ConvTranspose2d(k4,s2,p1) layers: (name, cin, cout, input res)
+    for name, cin, cout, res in [("dec1.deconv", 32, 16, 256), ("dec2.deconv", 64, 32, 128), ("dec3.deconv", 128, 64, 64),
+                                 ("dec4.deconv", 256, 128, 32), ("dec5.deconv", 512, 256, 16)]:
+        if (args.only and res != args.only) or (args.name and args.name not in name):
+            continue
+        x = Act(torch.randn(B, res, res, cin, device=DEV).to(torch.bfloat16))
+        dy = Act(torch.randn(B, 2 * res, 2 * res, cout, device=DEV).to(torch.bfloat16))
+        w = torch.randn(cin, cout, 4, 4, device=DEV) * 0.05
+        wf = ops.pack_weights(w, True, True)
+        wd = ops.pack_weights(w, True, False)
+        y = Act.empty(B, 2 * res, 2 * res, cout, DEV)
+        dx = Act.empty(B, res, res, cin, DEV)
+        dw = torch.empty_like(w)
+        ws = torch.empty(ops.wgrad_workspace_bytes(B, res, res, cin, cout, 16) // 4 + 64, dtype=torch.float32, device=DEV)
+        t_f = timeit(lambda: ops.deconv_fwd(x, wf, cout, y=y))
+        t_d = timeit(lambda: ops.deconv_dgrad(dy, wd, cin, dx=dx))
+        t_w = timeit(lambda: ops.deconv_wgrad(x, dy, dw, False, ws))
+        byt = 2.0 * B * (res * res * cin + 4 * res * res * cout)
+        fl = 2.0 * B * res * res * cout * cin * 16
+        print("%-18s %4d %4d 4 T %4d | %7.3f %6.0f %6.1f | %7.3f %6.0f | %7.3f %6.0f" %
+              (name, cin, cout, res, t_f, byt / t_f / 1e6, fl / t_f / 1e9, t_d, byt / t_d / 1e6, t_w, byt / t_w / 1e6), flush=True)
+        del x, dy, y, dx, ws
     print("sum (one of each listed layer): fwd %.3f dgrad %.3f wgrad %.3f ms" % tuple(tot))
 
 
