@@ -68,6 +68,11 @@ int ubr_pack_weights_batch(const int64_t* jobs_device, int njobs, void* stream);
  * If y_f32 != NULL the result is written as fp32 [pixel][y_f32_ld] (first out_ch columns) instead of y. */
 int ubr_conv2d_fwd(ubr_view x, const void* wpk, const float* bias, int out_ch, int ksize, int stride,
                    ubr_view y, float* y_f32, int y_f32_ld, void* stream);
+/* forward conv that also emits the BatchNorm statistics partials of its (bf16-stored) output from the epilogue:
+ * bn_workspace receives *stats_rows rows of [2][out_ch] (sum, sum of squares) -- feed them to ubr_bn_finalize_rows.
+ * Returns 1 (and does nothing) when the shape has no fused path: run ubr_conv2d_fwd + ubr_bn_stats instead. */
+int ubr_conv2d_fwd_stats(ubr_view x, const void* wpk, const float* bias, int out_ch, int ksize, int stride, ubr_view y,
+                         void* bn_workspace, int* stats_rows, void* stream);
 /* data gradient of the same conv: dx = conv_transpose(dy, W).  wpk = pack(..., n_is_out=0). */
 int ubr_conv2d_dgrad(ubr_view dy, const void* wpk, int in_ch, int ksize, int stride, ubr_view dx, void* stream);
 /* dx += conv_transpose(dy, W), fused into the epilogue (fp32 add of the stored bf16 value, one rounding).
@@ -103,6 +108,10 @@ int ubr_bn_stats(ubr_view y, void* workspace, void* stream);
 int ubr_bn_finalize(const void* workspace, int c, double count, const float* gamma, const float* beta,
                     float* running_mean, float* running_var, float momentum, float eps,
                     float* scale, float* shift, float* mean, float* invstd, void* stream);
+/* same, for `rows` partial rows written by a fused producer (ubr_conv2d_fwd_stats) */
+int ubr_bn_finalize_rows(const void* workspace, int rows, int c, double count, const float* gamma, const float* beta,
+                         float* running_mean, float* running_var, float momentum, float eps,
+                         float* scale, float* shift, float* mean, float* invstd, void* stream);
 /* eval mode: scale/shift from running statistics */
 int ubr_bn_eval_affine(int c, const float* gamma, const float* beta, const float* running_mean,
                        const float* running_var, float eps, float* scale, float* shift, void* stream);

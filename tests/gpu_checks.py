@@ -89,6 +89,29 @@ def check_conv_fwd(cin, cout, k, stride, n, h, w, in_ld=None, out_ld=None, seed=
     return res
 
 
+def check_conv_fwd_bn(cin, cout, k, n, h, w, seed=0, bias=False, expect_rows=True):
+    """conv + fused BatchNorm statistics (ubr_conv2d_fwd_stats) against F.conv2d + batch statistics."""
+    name = "conv_fwd_bn_ci%d_co%d_k%d_n%d_%dx%d" % (cin, cout, k, n, h, w)
+    x = bf(gen(n, cin, h, w, seed=seed))
+    wt = bf(gen(cout, cin, k, k, seed=seed + 1, scale=(2.0 / (k * k * cin)) ** 0.5))
+    b = gen(cout, seed=seed + 2) if bias else None
+    ref = bf(F.conv2d(x, wt, b, 1, (k - 1) // 2))             # statistics are taken over the stored bf16 values
+    gamma, beta = gen(cout, seed=seed + 3).abs() + 0.5, gen(cout, seed=seed + 4)
+    rm, rv = torch.zeros(cout, device=DEV), torch.ones(cout, device=DEV)
+    ws = ops.bn_workspace(cout, DEV)
+    ws.fill_(float("nan"))
+    wpk = ops.pack_weights(wt.to(DEV), False, True)
+    y, st = ops.conv2d_fwd_bn(act_from(x), wpk, b.to(DEV) if bias else None, cout, k, 1, gamma.to(DEV), beta.to(DEV), rm, rv, ws)
+    torch.cuda.synchronize()
+    mean = ref.mean((0, 2, 3))
+    var = ref.var((0, 2, 3), unbiased=False)
+    cnt = n * h * w
+    return [(name + "_y", relerr(y.nchw_float(), ref), 1e-2),
+            (name + "_mean", (st.mean.cpu() - mean).abs().max().item() / max(ref.abs().max().item(), 1e-6), 2e-3),
+            (name + "_invstd", relerr(st.invstd, 1.0 / torch.sqrt(var + 1e-5)), 5e-3),
+            (name + "_running_var", relerr(rv, 0.9 + 0.1 * var * cnt / (cnt - 1)), 5e-3)]
+
+
 def check_conv_dgrad(cin, cout, k, stride, n, h, w, seed=0):
     """h, w are the INPUT sizes of the conv (dx size)."""
     name = "conv_dgrad_ci%d_co%d_k%d_s%d_n%d_%dx%d" % (cin, cout, k, stride, n, h, w)
@@ -440,6 +463,9 @@ CHECKS = {
     "halo_fwd_slices": lambda: check_conv_fwd(32, 16, 3, 1, 2, 32, 128, in_ld=64, out_ld=32, seed=29),
     "halo_dgrad": lambda: (check_conv_dgrad(16, 32, 3, 1, 2, 64, 128, seed=31) + check_conv_dgrad(128, 64, 3, 1, 1, 32, 128, seed=32)
                            + check_conv_dgrad(16, 16, 7, 1, 1, 32, 256, seed=33) + check_conv_dgrad(64, 32, 1, 1, 1, 32, 128, seed=34)),
+    "halo_fwd_bn": lambda: (check_conv_fwd_bn(16, 16, 3, 2, 64, 128, seed=61) + check_conv_fwd_bn(32, 32, 3, 1, 32, 256, seed=62)
+                            + check_conv_fwd_bn(16, 16, 7, 1, 32, 128, seed=63, bias=True) + check_conv_fwd_bn(64, 32, 1, 1, 32, 128, seed=64)
+                            + check_conv_fwd_bn(64, 64, 3, 1, 32, 128, seed=65) + check_conv_fwd_bn(16, 32, 3, 2, 32, 32, seed=66)),
     "halo_dgrad_acc": lambda: (check_conv_dgrad_acc(16, 16, 3, 2, 64, 128, seed=51) + check_conv_dgrad_acc(32, 16, 3, 1, 32, 256, seed=52)
                                + check_conv_dgrad_acc(64, 64, 3, 1, 32, 128, seed=53, expect_fused=False)
                                + check_conv_dgrad_acc(16, 16, 3, 1, 32, 32, seed=54, expect_fused=False)),

@@ -27,6 +27,7 @@ SIGNATURES = {
     "ubr_pack_weights": (_i, [_vp, _i, _i, _i, _i, _i, _i, _i, _i, _vp, _vp]),
     "ubr_pack_weights_batch": (_i, [_vp, _i, _vp]),
     "ubr_conv2d_fwd": (_i, [View, _vp, _vp, _i, _i, _i, View, _vp, _i, _vp]),
+    "ubr_conv2d_fwd_stats": (_i, [View, _vp, _vp, _i, _i, _i, View, _vp, _vp, _vp]),
     "ubr_conv2d_dgrad": (_i, [View, _vp, _i, _i, _i, View, _vp]),
     "ubr_conv2d_dgrad_acc": (_i, [View, _vp, _i, _i, _i, View, _vp]),
     "ubr_conv2d_wgrad": (_i, [View, View, _i, _i, _i, _vp, _i, _vp, _u64, _vp]),
@@ -40,6 +41,7 @@ SIGNATURES = {
     "ubr_bn_workspace_bytes": (_u64, [_i]),
     "ubr_bn_stats": (_i, [View, _vp, _vp]),
     "ubr_bn_finalize": (_i, [_vp, _i, _d, _vp, _vp, _vp, _vp, _f, _f, _vp, _vp, _vp, _vp, _vp]),
+    "ubr_bn_finalize_rows": (_i, [_vp, _i, _i, _d, _vp, _vp, _vp, _vp, _f, _f, _vp, _vp, _vp, _vp, _vp]),
     "ubr_bn_eval_affine": (_i, [_i, _vp, _vp, _vp, _vp, _f, _vp, _vp, _vp]),
     "ubr_bn_act": (_i, [View, _vp, _vp, _i, View, _vp]),
     "ubr_block_tail": (_i, [View, _vp, _vp, View, _vp, _vp, View, _vp]),

@@ -316,8 +316,22 @@ using namespace ubr;
 
 extern "C" {
 
+static int conv2d_fwd_impl(ubr_view x, const void* wpk, const float* bias, int out_ch, int ksize, int stride, ubr_view y,
+                           float* y_f32, int y_f32_ld, void* stream, float* stats, int* stats_rows);
+
 int ubr_conv2d_fwd(ubr_view x, const void* wpk, const float* bias, int out_ch, int ksize, int stride, ubr_view y,
                    float* y_f32, int y_f32_ld, void* stream) {
+  return conv2d_fwd_impl(x, wpk, bias, out_ch, ksize, stride, y, y_f32, y_f32_ld, stream, nullptr, nullptr);
+}
+
+int ubr_conv2d_fwd_stats(ubr_view x, const void* wpk, const float* bias, int out_ch, int ksize, int stride, ubr_view y,
+                         void* bn_workspace, int* stats_rows, void* stream) {
+  UBR_REQUIRE(bn_workspace != nullptr && stats_rows != nullptr, "conv2d_fwd_stats: null workspace / rows pointer");
+  return conv2d_fwd_impl(x, wpk, bias, out_ch, ksize, stride, y, nullptr, 0, stream, (float*)bn_workspace, stats_rows);
+}
+
+static int conv2d_fwd_impl(ubr_view x, const void* wpk, const float* bias, int out_ch, int ksize, int stride, ubr_view y,
+                           float* y_f32, int y_f32_ld, void* stream, float* stats, int* stats_rows) {
   if (int rc = ensure_device()) return rc;
   if (int rc = check_view(x, "conv2d_fwd.x")) return rc;
   UBR_REQUIRE(ksize == 1 || ksize == 3 || ksize == 7, "conv2d_fwd: ksize %d unsupported", ksize);
@@ -363,9 +377,10 @@ int ubr_conv2d_fwd(ubr_view x, const void* wpk, const float* bias, int out_ch, i
       UBR_REQUIRE(y_f32_ld >= out_ch, "conv2d_fwd: y_f32_ld too small");
     }
     const int hrc = conv_halo_try(x, wpk, ksize * ksize, n_pad, taps, nt, bias, y_f32 ? nullptr : &y, y_f32, y_f32_ld,
-                                  out_ch, (cudaStream_t)stream);
+                                  out_ch, (cudaStream_t)stream, 0, stats, stats_rows);
     if (hrc <= 0) return hrc;
   }
+  if (stats) return 1;             // no fused-statistics path for this shape: caller runs conv + bn_stats
   p.bias = bias;
   if (y_f32) {
     p.out_mode = 1; p.out_f32 = y_f32; p.out_ld = y_f32_ld; p.out_cols = out_ch;

@@ -43,6 +43,8 @@ struct HaloParams {
   float* out_f32;
   __nv_bfloat16* out_bf16;
   int out_ld, out_cols, out_h, out_w;
+  float* stats;                 // out_mode 2 only: per-CTA BN partials [row][2][stats_c] (sum, sum of squares), or null
+  int stats_c, stats_rows;
   int accumulate;               // out_mode 2 only: out += result (fp32 add of the stored bf16 value, one rounding)
 };
 
@@ -72,6 +74,22 @@ __device__ __forceinline__ void mma_lohi(uint32_t d_tmem, uint32_t alo, uint32_t
         ::"r"(d_tmem), "r"(alo), "r"(ahi), "r"(blo), "r"(bhi), "r"(idesc)
         : "memory");
   }
+}
+
+// Warp reduce-scatter of 16 per-lane values over the 32 lanes: 16 shuffles instead of 80.  On return lane l holds
+// in the result the warp total of channel (l >> 1) & 15 (both lanes of a pair hold the same total).
+__device__ __forceinline__ float warp_reduce_scatter16(float (&v)[16], int lane) {
+#pragma unroll
+  for (int h = 8, m = 16; h >= 1; h >>= 1, m >>= 1) {
+    const bool up = (lane & m) != 0;
+#pragma unroll
+    for (int i = 0; i < h; ++i) {
+      const float send = up ? v[i] : v[i + h];
+      const float keep = up ? v[i + h] : v[i];
+      v[i] = keep + __shfl_xor_sync(0xffffffffu, send, m);
+    }
+  }
+  return v[0] + __shfl_xor_sync(0xffffffffu, v[0], 1);
 }
 
 template <int KS, int KSTEPS>
@@ -223,6 +241,7 @@ __global__ void __launch_bounds__(kHThreads, 1) conv_halo_kernel(const __grid_co
     const uint32_t xr = rb == 128 ? (uint32_t)(row & 7) : (rb == 64 ? (uint32_t)((row >> 1) & 3) : (uint32_t)((row >> 2) & 1));
     const uint32_t sbase = stage_base + (uint32_t)grp * p.stage_bytes;
     const int bar_id = 1 + grp;
+    float st_sum0 = 0.f, st_sq0 = 0.f, st_sum1 = 0.f, st_sq1 = 0.f;   // fused BN statistics: this lane's channel, per 16-channel chunk
     uint32_t r0 = 0;                           // global output-row counter at the start of the tile
     for (int tile = blockIdx.x; tile < p.ntiles; tile += gridDim.x, r0 += (uint32_t)p.bh) {
       const int band = tile % p.bands;
@@ -268,6 +287,19 @@ __global__ void __launch_bounds__(kHThreads, 1) conv_halo_kernel(const __grid_co
             u1.z = pack_bf16x2(f[12], f[13]); u1.w = pack_bf16x2(f[14], f[15]);
             *reinterpret_cast<uint4*>(dst + c) = u0;
             *reinterpret_cast<uint4*>(dst + c + 8) = u1;
+            if (p.stats) {
+              // statistics of the STORED (bf16-rounded) values, like the stand-alone bn_stats kernel
+              const uint32_t uw[8] = {u0.x, u0.y, u0.z, u0.w, u1.x, u1.y, u1.z, u1.w};
+              float g[16], q[16];
+#pragma unroll
+              for (int j = 0; j < 8; ++j) {
+                const float2 t = unpack_bf16x2(uw[j]);
+                g[2 * j] = t.x; g[2 * j + 1] = t.y;
+                q[2 * j] = t.x * t.x; q[2 * j + 1] = t.y * t.y;
+              }
+              const float rs = warp_reduce_scatter16(g, lane), rq = warp_reduce_scatter16(q, lane);
+              if (c == 0) { st_sum0 += rs; st_sq0 += rq; } else { st_sum1 += rs; st_sq1 += rq; }
+            }
           }
           tmem_st_wait();
           tc_fence_before();
@@ -342,6 +374,26 @@ __global__ void __launch_bounds__(kHThreads, 1) conv_halo_kernel(const __grid_co
       }
     }
     if (p.out_mode == 0 && leader) tma_store_wait_all();
+    if (p.out_mode == 2 && p.stats) {
+      // combine the 8 epilogue warps in a fixed order (deterministic) and publish this CTA's partial row
+      float* scr = reinterpret_cast<float*>(smem_raw + (tmem_slot + 16u - smem_u32(smem_raw)));   // [8 warps][32 lanes][4]
+      const int we = warp - 2;
+      float* mine = scr + (we * 32 + lane) * 4;
+      mine[0] = st_sum0; mine[1] = st_sq0; mine[2] = st_sum1; mine[3] = st_sq1;
+      asm volatile("bar.sync 3, 256;" ::: "memory");
+      if (we == 0 && (lane & 1) == 0) {
+        const int ch = (lane >> 1) & 15;
+        float tot[4] = {0.f, 0.f, 0.f, 0.f};
+        for (int k = 0; k < 8; ++k)
+#pragma unroll
+          for (int j = 0; j < 4; ++j) tot[j] += scr[(k * 32 + lane) * 4 + j];
+        float* rowp = p.stats + (size_t)blockIdx.x * 2 * p.stats_c;
+        for (int cc = 0; cc < p.nt; cc += 16) {
+          rowp[co0 + cc + ch] = tot[(cc >> 4) * 2];
+          rowp[p.stats_c + co0 + cc + ch] = tot[(cc >> 4) * 2 + 1];
+        }
+      }
+    }
   }
 
   tc_fence_before();
@@ -379,7 +431,7 @@ static halo_kernel_t pick_halo_kernel(int ks, int ksteps) {
 
 int conv_halo_try(const ubr_view& x, const void* wpk, int nslabs, int n_pad, const TapSpec* taps, int ntaps,
                   const float* bias, const ubr_view* y, float* y_f32, int y_f32_ld, int out_cols,
-                  cudaStream_t stream, int accumulate) {
+                  cudaStream_t stream, int accumulate, float* stats, int* stats_rows) {
   if (halo_disabled()) return 1;
   const int cin = x.c;
   if (!(cin == 16 || cin == 32 || cin == 64)) return 1;
@@ -408,7 +460,7 @@ int conv_halo_try(const ubr_view& x, const void* wpk, int nslabs, int n_pad, con
   const uint32_t row_bytes = (uint32_t)(128 + 2 * pad) * span;
   const uint32_t slot_bytes = (row_bytes + 1023u) & ~1023u;
   // N tile: largest divisor tile whose resident weights + ring + staging fit
-  const uint32_t budget = 225u * 1024u - 1024u - 512u;
+  const uint32_t budget = 225u * 1024u - 1024u - 512u - 4096u - 512u;
   int nt = 0, nslots = 0, out_mode = 0;
   uint32_t w_region = 0, stage_bytes = 0;
   const int nt_max = ks == 1 ? 128 : (ks == 3 ? 64 : 32);     // stacked MMA: ks * nt <= 256 columns
@@ -422,7 +474,7 @@ int conv_halo_try(const ubr_view& x, const void* wpk, int nslabs, int n_pad, con
     if (s > 16) s = 16;
     // two CTAs per SM (two issuing threads) beat one deep ring: shrink the ring if that makes a second CTA fit
     {
-      const uint32_t half = 110u * 1024u - 1024u - 1024u;
+      const uint32_t half = 110u * 1024u - 1024u - 1024u - 4096u;
       if (wr + 2u * st + 6u * slot_bytes <= half && (ks + 3 <= 8 ? 8 : 16) * cand <= 256) {
         const int s2 = (int)((half - wr - 2u * st) / slot_bytes);
         if (s2 < s) s = s2;
@@ -433,6 +485,7 @@ int conv_halo_try(const ubr_view& x, const void* wpk, int nslabs, int n_pad, con
   }
   if (nt == 0) return 1;
   if (accumulate && out_mode != 2) return 1;                 // in-epilogue accumulation: direct-store path only
+  if (stats && out_mode != 2) return 1;                      // fused BN statistics: direct-store path only
 
   HaloParams p;
   memset(&p, 0, sizeof(p));
@@ -481,7 +534,8 @@ int conv_halo_try(const ubr_view& x, const void* wpk, int nslabs, int n_pad, con
   }
   p.bias = bias;
   p.accumulate = accumulate;
-  const uint32_t smem = w_region + (uint32_t)nslots * slot_bytes + 2u * stage_bytes + 16u * nslots + 640u + 1024u;
+  p.stats = stats; p.stats_c = n_pad;
+  const uint32_t smem = w_region + (uint32_t)nslots * slot_bytes + 2u * stage_bytes + 16u * nslots + 640u + 4096u + 1024u;
   UBR_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
   const int n_tiles = n_pad / nt;
   int per_sm = (smem <= 110u * 1024u && p.tmem_cols <= 256u) ? 2 : 1;
@@ -489,6 +543,8 @@ int conv_halo_try(const ubr_view& x, const void* wpk, int nslabs, int n_pad, con
   if (const char* e = getenv("UBR_HALO_MAX_CTAS")) { const int v = atoi(e); if (v > 0 && ctas > v) ctas = v; }
   if (ctas < 1) ctas = 1;
   if (ctas > p.ntiles) ctas = p.ntiles;
+  p.stats_rows = ctas;
+  if (stats_rows) *stats_rows = ctas;
   dim3 grid((unsigned)ctas, (unsigned)n_tiles, 1);
   kern<<<grid, kHThreads, smem, stream>>>(p);
   UBR_LAUNCH_CHECK("conv_halo_kernel");

@@ -10,7 +10,8 @@ struct TapSpec { int dh, dw, amap, slab; };
 // tap-by-tap kernel), <0 = error.  `y` (bf16 view) or `y_f32` (fp32 [pixel][ld]) selects the output mode.
 int conv_halo_try(const ubr_view& x, const void* wpk, int nslabs, int n_pad, const TapSpec* taps, int ntaps,
                   const float* bias, const ubr_view* y, float* y_f32, int y_f32_ld, int out_cols,
-                  cudaStream_t stream, int accumulate = 0);
+                  cudaStream_t stream, int accumulate = 0, float* stats = nullptr,
+                  int* stats_rows = nullptr);
 
 // Halo-resident weight gradient (wgrad_halo.cu).  Same return convention.
 int wgrad_halo_try(const ubr_view& x, const ubr_view& dy, int out_ch, int ksize, float* dw, int accumulate,

@@ -619,6 +619,19 @@ int ubr_bn_finalize(const void* workspace, int c, double count, const float* gam
   return 0;
 }
 
+int ubr_bn_finalize_rows(const void* workspace, int rows, int c, double count, const float* gamma, const float* beta,
+                         float* running_mean, float* running_var, float momentum, float eps, float* scale, float* shift,
+                         float* mean, float* invstd, void* stream) {
+  if (int rc = ensure_device()) return rc;
+  UBR_REQUIRE(workspace && scale && shift, "bn_finalize_rows: null pointer");
+  UBR_REQUIRE(c > 0 && c % 8 == 0 && count >= 1.0 && rows >= 1 && rows <= kRedBlocks, "bn_finalize_rows: bad c/count/rows");
+  bn_finalize_kernel<<<ceil_div(c, 32), dim3(32, kColLanes), 0, (cudaStream_t)stream>>>((const float*)workspace, rows, c, count,
+                                                                                      gamma, beta, running_mean, running_var,
+                                                                                      momentum, eps, scale, shift, mean, invstd);
+  UBR_LAUNCH_CHECK("bn_finalize_kernel");
+  return 0;
+}
+
 int ubr_bn_eval_affine(int c, const float* gamma, const float* beta, const float* running_mean,
                        const float* running_var, float eps, float* scale, float* shift, void* stream) {
   if (int rc = ensure_device()) return rc;

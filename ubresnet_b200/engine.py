@@ -161,6 +161,15 @@ class Engine:
             st.count = float(y.npix)
         return st
 
+    def _conv_bn(self, x, wpk, bias, out_ch, k, stride, bn, training, bn_ws):
+        """conv -> BatchNorm statistics/affine.  In training the statistics come out of the conv epilogue where the
+        kernel supports it (ops.conv2d_fwd_bn), otherwise from the stand-alone bn_stats pass."""
+        if training:
+            return ops.conv2d_fwd_bn(x, wpk, bias, out_ch, k, stride, bn.weight, bn.bias, bn.running_mean, bn.running_var,
+                                     bn_ws, momentum=bn.momentum if bn.momentum is not None else 0.1, eps=bn.eps)
+        y = ops.conv2d_fwd(x, wpk, bias, out_ch, k, stride)
+        return y, self._bn(y, bn, False, bn_ws)
+
     # ------------------------------------------------------------------ forward pieces
     def _block_fwd(self, blk, x, out, training, need_grad, bn_ws):
         rec = _BlockRec()
@@ -168,15 +177,12 @@ class Engine:
         s = blk.stride
         w1 = self._pack(blk.conv1, need_grad)
         w2 = self._pack(blk.conv2, need_grad)
-        y1 = ops.conv2d_fwd(x, w1.fwd, None, cout, 3, s)
-        st1 = self._bn(y1, blk.bn1, training, bn_ws)
+        y1, st1 = self._conv_bn(x, w1.fwd, None, cout, 3, s, blk.bn1, training, bn_ws)
         a1 = ops.bn_act(y1, st1, True)
-        y2 = ops.conv2d_fwd(a1, w2.fwd, None, cout, 3, 1)
-        st2 = self._bn(y2, blk.bn2, training, bn_ws)
+        y2, st2 = self._conv_bn(a1, w2.fwd, None, cout, 3, 1, blk.bn2, training, bn_ws)
         if blk.bypass is not None:
             wb = self._pack(blk.bypass, need_grad)
-            yb = ops.conv2d_fwd(x, wb.fwd, None, cout, 1, s)
-            stb = self._bn(yb, blk.bnpass, training, bn_ws)
+            yb, stb = self._conv_bn(x, wb.fwd, None, cout, 1, s, blk.bnpass, training, bn_ws)
             out = ops.block_tail(y2, st2, yb, stb, out)
         else:
             yb, stb = None, None
@@ -253,8 +259,7 @@ class Engine:
             cur, recs["dec%d" % i] = self._double_fwd(layer.res, Act(cat[i]), None, training, need_grad, bn_ws)
         # ---- head (:137-143)
         w10 = self._pack(m.conv10, need_grad)
-        y10 = ops.conv2d_fwd(cur, w10.fwd, m.conv10.bias, m.nkernels, 7, 1)
-        st10 = self._bn(y10, m.bn10, training, bn_ws)
+        y10, st10 = self._conv_bn(cur, w10.fwd, m.conv10.bias, m.nkernels, 7, 1, m.bn10, training, bn_ws)
         a10 = ops.bn_act(y10, st10, True)
         w11 = self._pack(m.conv11, need_grad)
         ncls = m.conv11.out_channels

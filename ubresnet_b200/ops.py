@@ -116,6 +116,30 @@ def conv2d_fwd(x, wpk, bias, out_ch, ksize, stride, y=None, y_f32=None):
     return y
 
 
+def conv2d_fwd_bn(x, wpk, bias, out_ch, ksize, stride, gamma, beta, running_mean, running_var, ws, y=None,
+                  momentum=BN_MOMENTUM, eps=BN_EPS):
+    """conv forward + training-mode BatchNorm statistics.  Where the conv kernel has a fused-statistics epilogue the
+    stand-alone bn_stats pass over y is skipped.  Returns (y, BNState)."""
+    import ctypes
+    lib = _lib.load()
+    if y is None:
+        y = Act.empty(x.n, x.h // stride, x.w // stride, out_ch, x.buf.device)
+    rows = ctypes.c_int(0)
+    rc = lib.ubr_conv2d_fwd_stats(x.view(), wpk.data_ptr(), _ptr(bias), out_ch, ksize, stride, y.view(), ws.data_ptr(),
+                                  ctypes.addressof(rows), _stream())
+    if rc == 1:
+        conv2d_fwd(x, wpk, bias, out_ch, ksize, stride, y=y)
+        return y, bn_train_stats(y, gamma, beta, running_mean, running_var, ws, momentum=momentum, eps=eps)
+    _lib.check(rc, "conv2d_fwd_stats")
+    st = BNState(y.c, y.buf.device)
+    st.count = float(y.npix)
+    _lib.check(lib.ubr_bn_finalize_rows(ws.data_ptr(), rows.value, y.c, st.count, _ptr(gamma), _ptr(beta),
+                                        _ptr(running_mean), _ptr(running_var), momentum, eps, st.scale.data_ptr(),
+                                        st.shift.data_ptr(), st.mean.data_ptr(), st.invstd.data_ptr(), _stream()),
+               "bn_finalize_rows")
+    return y, st
+
+
 def conv2d_dgrad(dy, wpk, in_ch, ksize, stride, dx=None):
     lib = _lib.load()
     if dx is None:
