@@ -49,6 +49,9 @@ uint64_t ubr_launch_count(void);          /* kernels launched by this library so
  * replaces the implicit cuDNN filter transforms behind nn.Conv2d / nn.ConvTranspose2d.
  *   src_layout 0: OIHW  (nn.Conv2d.weight,            models/common_layers.py:15,34; ub_uresnet.py:41,60,64)
  *   src_layout 1: IOHW  (nn.ConvTranspose2d.weight,   models/common_layers.py:125)
+ *   src_layout 2: IOHW ConvTranspose2d(k4,s2,p1) as a 3x3 stride-1 "sub-pixel" conv over the INPUT grid with 4*out_ch
+ *                 phase channels ((ph*2+pw)*out_ch + co <-> output pixel (2i+ph, 2j+pw)); call with kh = kw = 3.
+ *                 n_is_out 1: forward operand (n = phase channel, k = in channel); 0: data-gradient operand
  *   n_is_out 1: n = output channel, k = input channel (forward operand)
  *   n_is_out 0: n = input channel,  k = output channel (data-gradient operand)
  * dst has kh*kw + 1 slabs of [n_pad][k_pad] (zero padded, n_pad/k_pad multiples of 16); the extra last slab is
@@ -87,6 +90,10 @@ uint64_t ubr_wgrad_workspace_bytes(int grid_n, int grid_h, int grid_w, int m_ch,
 
 /* nn.ConvTranspose2d(k=4, stride=2, padding=1, bias=False), output_size == 2x input (common_layers.py:125,128) */
 int ubr_deconv4s2_fwd(ubr_view x, const void* wpk, int out_ch, ubr_view y, void* stream);
+/* same forward as a 3x3 "sub-pixel" conv over the input grid with a pixel-shuffle epilogue (halo-resident kernel);
+ * wpk3 = ubr_pack_weights(src_layout=2, n_is_out=1, kh=kw=3, n_pad=4*out_ch).  Returns 1 when the shape has no such
+ * path (in_ch > 64 or W %% 128 != 0): use ubr_deconv4s2_fwd. */
+int ubr_deconv4s2_fwd_subpixel(ubr_view x, const void* wpk3, int out_ch, ubr_view y, void* stream);
 int ubr_deconv4s2_dgrad(ubr_view dy, const void* wpk, int in_ch, ubr_view dx, void* stream);
 int ubr_deconv4s2_wgrad(ubr_view x, ubr_view dy, float* dw /* IOHW */, int accumulate,
                         void* workspace, uint64_t workspace_bytes, void* stream);

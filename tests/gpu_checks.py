@@ -192,6 +192,15 @@ def check_deconv(cin, cout, n, h, w, out_ld=None, seed=0):
     res = [(name + "_fwd", relerr(out, ref), 1e-2)]
     if res[0][1] > 1e-2:
         _dump(name + "_fwd", out=out, ref=ref, x=x, w=wt)
+    # sub-pixel path (3x3 conv over the input grid + pixel shuffle), where the shape supports it
+    yb = act_out(n, 2 * h, 2 * w, cout, out_ld, 0)
+    if ops.deconv_fwd_subpixel(xa, ops.pack_weights_subpixel(wt.to(DEV), True), cout, yb):
+        torch.cuda.synchronize()
+        res.append((name + "_fwd_subpixel", relerr(yb.nchw_float(), ref), 1e-2))
+        if out_ld and out_ld != cout:
+            res.append((name + "_fwd_subpixel_slice_untouched", (yb.buf[..., cout:].float() - 3.0).abs().max().item(), 0.0))
+    elif w % 128 == 0 and cin <= 64:
+        res.append((name + "_fwd_subpixel_missing", 1.0, 0.0))
     # dgrad: dx = conv2d(dy, W viewed as OIHW with O=cin), stride 2, pad 1
     dy = bf(gen(n, cout, 2 * h, 2 * w, seed=seed + 2))
     ref_dx = F.conv2d(dy, wt, None, 2, 1)
@@ -449,6 +458,8 @@ CHECKS = {
     "conv_dgrad_s2": lambda: (check_conv_dgrad(32, 64, 3, 2, 2, 32, 32, seed=5)
                               + check_conv_dgrad(64, 128, 1, 2, 2, 16, 16, seed=6)),
     "deconv": lambda: check_deconv(32, 16, 2, 16, 16) + check_deconv(512, 256, 2, 4, 4, out_ld=512, seed=3),
+    "deconv_subpixel": lambda: (check_deconv(32, 16, 2, 32, 128, out_ld=32, seed=71) + check_deconv(64, 32, 1, 32, 128, seed=72)
+                                + check_deconv(16, 16, 1, 16, 256, seed=73)),
     "conv_wgrad_c64": lambda: check_conv_wgrad(64, 64, 3, 1, 2, 16, 16),
     "conv_wgrad_c16": lambda: check_conv_wgrad(16, 32, 3, 1, 2, 32, 32, seed=2) + check_conv_wgrad(32, 16, 3, 1, 2, 32, 32, seed=3),
     "conv_wgrad_big": lambda: check_conv_wgrad(128, 256, 3, 1, 4, 8, 8, seed=4) + check_conv_wgrad(256, 128, 1, 1, 4, 8, 8, seed=5),

@@ -93,7 +93,8 @@ def main():
         dx = Act.empty(B, res, res, cin, DEV)
         dw = torch.empty_like(w)
         ws = torch.empty(ops.wgrad_workspace_bytes(B, res, res, cin, cout, 16) // 4 + 64, dtype=torch.float32, device=DEV)
-        t_f = timeit(lambda: ops.deconv_fwd(x, wf, cout, y=y))
+        w3 = ops.pack_weights_subpixel(w, True)
+        t_f = timeit(lambda: ops.deconv_fwd_subpixel(x, w3, cout, y) or ops.deconv_fwd(x, wf, cout, y=y))
         t_d = timeit(lambda: ops.deconv_dgrad(dy, wd, cin, dx=dx))
         t_w = timeit(lambda: ops.deconv_wgrad(x, dy, dw, False, ws))
         byt = 2.0 * B * (res * res * cin + 4 * res * res * cout)

@@ -502,6 +502,21 @@ int ubr_deconv4s2_fwd(ubr_view x, const void* wpk, int out_ch, ubr_view y, void*
   return 0;
 }
 
+int ubr_deconv4s2_fwd_subpixel(ubr_view x, const void* wpk3, int out_ch, ubr_view y, void* stream) {
+  if (int rc = ensure_device()) return rc;
+  if (int rc = check_view(x, "deconv_fwd_subpixel.x")) return rc;
+  if (int rc = check_view(y, "deconv_fwd_subpixel.y")) return rc;
+  UBR_REQUIRE(x.c % 16 == 0 && out_ch % 16 == 0, "deconv_fwd_subpixel: channels must be multiples of 16");
+  UBR_REQUIRE(y.c == out_ch && y.n == x.n && y.h == 2 * x.h && y.w == 2 * x.w, "deconv_fwd_subpixel: output view mismatch");
+  UBR_REQUIRE(wpk3 != nullptr, "deconv_fwd_subpixel: null weights");
+  TapSpec taps[9];
+  int nt = 0;
+  for (int r = 0; r < 3; ++r)
+    for (int s = 0; s < 3; ++s) taps[nt++] = TapSpec{r - 1, s - 1, 0, r * 3 + s};
+  return conv_halo_try(x, wpk3, 9, 4 * out_ch, taps, 9, nullptr, &y, nullptr, 0, 4 * out_ch, (cudaStream_t)stream, 0, nullptr,
+                       nullptr, out_ch);
+}
+
 int ubr_deconv4s2_dgrad(ubr_view dy, const void* wpk, int in_ch, ubr_view dx, void* stream) {
   if (int rc = ensure_device()) return rc;
   if (int rc = check_view(dy, "deconv_dgrad.dy")) return rc;

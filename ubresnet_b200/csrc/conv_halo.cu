@@ -37,7 +37,9 @@ struct HaloParams {
   uint32_t span, row_bytes, slot_bytes, w_tap_bytes, w_region, stage_bytes;
   uint32_t idesc, tmem_cols, acc_stride;
   int nb;                       // TMEM ring: nb output-row accumulators of nt columns (power of two)
-  int out_mode;                 // 0: bf16 staging + TMA store, 1: fp32 direct (logits), 2: bf16 direct stores
+  int out_mode;                 // 0: bf16 staging + TMA store, 1: fp32 direct (logits), 2: bf16 direct stores,
+                                // 3: bf16 pixel-shuffle stores (sub-pixel ConvTranspose: channel (ph,pw,co) -> pixel (2h+ph,2w+pw))
+  int ps_cout;                  // mode 3: channels per output pixel
   int o_box_c;
   const float* bias;
   float* out_f32;
@@ -305,6 +307,33 @@ __global__ void __launch_bounds__(kHThreads, 1) conv_halo_kernel(const __grid_co
           tc_fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive(acce0 + 8u * b);
+        } else if (p.out_mode == 3) {
+          // sub-pixel ConvTranspose: this thread's input-grid pixel (h, c0+row) owns 4 output pixels
+          for (int c = 0; c < p.nt; c += 16) {
+            uint32_t v[16];
+            tmem_ld16(t_row + (uint32_t)c, v);
+            tmem_ld_wait();
+            tmem_st16_zero(t_row + (uint32_t)c);
+            const int cc = co0 + c;
+            const int ph = cc / (2 * p.ps_cout), pw = (cc / p.ps_cout) & 1, co = cc % p.ps_cout;
+            __nv_bfloat16* dst = p.out_bf16 + ((size_t)((size_t)n * (2 * p.out_h) + (2 * h + ph)) * (2 * p.out_w) +
+                                               (size_t)(2 * (c0 + row) + pw)) * (size_t)p.out_ld + co;
+            uint4 u0, u1;
+            u0.x = pack_bf16x2(__uint_as_float(v[0]), __uint_as_float(v[1]));
+            u0.y = pack_bf16x2(__uint_as_float(v[2]), __uint_as_float(v[3]));
+            u0.z = pack_bf16x2(__uint_as_float(v[4]), __uint_as_float(v[5]));
+            u0.w = pack_bf16x2(__uint_as_float(v[6]), __uint_as_float(v[7]));
+            u1.x = pack_bf16x2(__uint_as_float(v[8]), __uint_as_float(v[9]));
+            u1.y = pack_bf16x2(__uint_as_float(v[10]), __uint_as_float(v[11]));
+            u1.z = pack_bf16x2(__uint_as_float(v[12]), __uint_as_float(v[13]));
+            u1.w = pack_bf16x2(__uint_as_float(v[14]), __uint_as_float(v[15]));
+            *reinterpret_cast<uint4*>(dst) = u0;
+            *reinterpret_cast<uint4*>(dst + 8) = u1;
+          }
+          tmem_st_wait();
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(acce0 + 8u * b);
         } else if (p.out_mode == 0) {
           if (leader) tma_store_wait_read_n<0>();          // this group's previous store has read the staging tile
           asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");
@@ -431,7 +460,7 @@ static halo_kernel_t pick_halo_kernel(int ks, int ksteps) {
 
 int conv_halo_try(const ubr_view& x, const void* wpk, int nslabs, int n_pad, const TapSpec* taps, int ntaps,
                   const float* bias, const ubr_view* y, float* y_f32, int y_f32_ld, int out_cols,
-                  cudaStream_t stream, int accumulate, float* stats, int* stats_rows) {
+                  cudaStream_t stream, int accumulate, float* stats, int* stats_rows, int shuffle_cout) {
   if (halo_disabled()) return 1;
   const int cin = x.c;
   if (!(cin == 16 || cin == 32 || cin == 64)) return 1;
@@ -463,11 +492,12 @@ int conv_halo_try(const ubr_view& x, const void* wpk, int nslabs, int n_pad, con
   const uint32_t budget = 225u * 1024u - 1024u - 512u - 4096u - 512u;
   int nt = 0, nslots = 0, out_mode = 0;
   uint32_t w_region = 0, stage_bytes = 0;
-  const int nt_max = ks == 1 ? 128 : (ks == 3 ? 64 : 32);     // stacked MMA: ks * nt <= 256 columns
+  int nt_max = ks == 1 ? 128 : (ks == 3 ? 64 : 32);           // stacked MMA: ks * nt <= 256 columns
+  if (shuffle_cout && nt_max > 64) nt_max = 64;
   for (int cand = n_pad > nt_max ? nt_max : n_pad; cand >= 16; cand -= 16) {
     if (n_pad % cand) continue;
     const uint32_t wr = ((uint32_t)ntaps * cand * span + 1023u) & ~1023u;
-    const int mode = y_f32 ? 1 : (cand <= 32 ? 2 : 0);
+    const int mode = y_f32 ? 1 : (shuffle_cout ? 3 : (cand <= 32 ? 2 : 0));
     const uint32_t st = mode == 0 ? 128u * (uint32_t)cand * 2u : 0u;
     if (wr + 2u * st + 4u * slot_bytes > budget) continue;
     int s = (int)((budget - wr - 2u * st) / slot_bytes);
@@ -505,8 +535,8 @@ int conv_halo_try(const ubr_view& x, const void* wpk, int nslabs, int n_pad, con
   p.out_h = x.h; p.out_w = x.w;
   if (out_mode == 1) {
     p.out_f32 = y_f32; p.out_ld = y_f32_ld; p.out_cols = out_cols;
-  } else if (out_mode == 2) {
-    p.out_bf16 = (__nv_bfloat16*)y->ptr; p.out_ld = y->ld; p.out_cols = out_cols;
+  } else if (out_mode == 2 || out_mode == 3) {
+    p.out_bf16 = (__nv_bfloat16*)y->ptr; p.out_ld = y->ld; p.out_cols = out_cols; p.ps_cout = shuffle_cout;
   } else {
     p.o_box_c = nt >= 64 ? 64 : nt;
     uint64_t dims[4] = {(uint64_t)y->c, (uint64_t)y->w, (uint64_t)y->h, (uint64_t)y->n};

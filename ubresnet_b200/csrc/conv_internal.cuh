@@ -11,7 +11,7 @@ struct TapSpec { int dh, dw, amap, slab; };
 int conv_halo_try(const ubr_view& x, const void* wpk, int nslabs, int n_pad, const TapSpec* taps, int ntaps,
                   const float* bias, const ubr_view* y, float* y_f32, int y_f32_ld, int out_cols,
                   cudaStream_t stream, int accumulate = 0, float* stats = nullptr,
-                  int* stats_rows = nullptr);
+                  int* stats_rows = nullptr, int shuffle_cout = 0);
 
 // Halo-resident weight gradient (wgrad_halo.cu).  Same return convention.
 int wgrad_halo_try(const ubr_view& x, const ubr_view& dy, int out_ch, int ksize, float* dw, int accumulate,

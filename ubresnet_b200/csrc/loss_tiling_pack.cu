@@ -139,6 +139,28 @@ __global__ void __launch_bounds__(256) stitch_scatter_kernel(const float* __rest
 
 // ------------------------------------------------------------------ weight packing
 // dst[tap][n][k] (bf16, zero padded); one extra all-zero slab at index taps (used by phases no tap reaches)
+// one element of the packed operand.  src_layout 0: OIHW conv, 1: IOHW deconv (16 taps),
+// 2: IOHW ConvTranspose(k4,s2,p1) re-expressed as a 3x3 stride-1 "sub-pixel" conv with 4*out_ch phase channels
+//    (phase channel = (ph*2+pw)*out_ch + co): n_is_out=1 forward  (y4 = conv3x3(x)),  n_is_out=0 data gradient
+//    (dx = conv3x3(dy4)); taps that a phase does not use are zero.
+__device__ __forceinline__ float pack_value(const float* __restrict__ src, int src_layout, int n_is_out, int out_ch,
+                                            int in_ch, int taps, int t, int nn, int k) {
+  if (src_layout == 2) {
+    const int pc = n_is_out ? nn : k, ci = n_is_out ? k : nn;
+    if (pc >= 4 * out_ch || ci >= in_ch) return 0.f;
+    const int ph = pc / (2 * out_ch), pw = (pc / out_ch) & 1, co = pc % out_ch;
+    const int dh = t / 3 - 1, dw = t % 3 - 1;
+    const int kh4 = n_is_out ? (ph + 1 - 2 * dh) : (2 * dh + ph + 1);
+    const int kw4 = n_is_out ? (pw + 1 - 2 * dw) : (2 * dw + pw + 1);
+    if (kh4 < 0 || kh4 > 3 || kw4 < 0 || kw4 > 3) return 0.f;
+    return src[(((long)ci * out_ch + co) * 4 + kh4) * 4 + kw4];
+  }
+  const int o = n_is_out ? nn : k, ci = n_is_out ? k : nn;
+  if (o >= out_ch || ci >= in_ch) return 0.f;
+  const long idx = src_layout == 0 ? (((long)o * in_ch + ci) * taps + t) : (((long)ci * out_ch + o) * taps + t);
+  return src[idx];
+}
+
 __global__ void __launch_bounds__(256) pack_weights_kernel(const float* __restrict__ src, int src_layout, int n_is_out,
                                                            int out_ch, int in_ch, int kh, int kw, int n_pad, int k_pad,
                                                            __nv_bfloat16* __restrict__ dst) {
@@ -148,14 +170,7 @@ __global__ void __launch_bounds__(256) pack_weights_kernel(const float* __restri
     const int k = (int)(i % k_pad);
     const int nn = (int)((i / k_pad) % n_pad);
     const int t = (int)(i / ((long)k_pad * n_pad));
-    float v = 0.f;
-    if (t < taps) {
-      const int o = n_is_out ? nn : k, ci = n_is_out ? k : nn;
-      if (o < out_ch && ci < in_ch) {
-        const long idx = src_layout == 0 ? (((long)o * in_ch + ci) * taps + t) : (((long)ci * out_ch + o) * taps + t);
-        v = src[idx];
-      }
-    }
+    const float v = t < taps ? pack_value(src, src_layout, n_is_out, out_ch, in_ch, taps, t, nn, k) : 0.f;
     dst[i] = __float2bfloat16_rn(v);
   }
 }
@@ -172,14 +187,7 @@ __global__ void __launch_bounds__(256) pack_weights_batch_kernel(const long long
     const int k = (int)(i % k_pad);
     const int nn = (int)((i / k_pad) % n_pad);
     const int t = (int)(i / ((long)k_pad * n_pad));
-    float v = 0.f;
-    if (t < taps) {
-      const int o = n_is_out ? nn : k, ci = n_is_out ? k : nn;
-      if (o < out_ch && ci < in_ch) {
-        const long idx = src_layout == 0 ? (((long)o * in_ch + ci) * taps + t) : (((long)ci * out_ch + o) * taps + t);
-        v = src[idx];
-      }
-    }
+    const float v = t < taps ? pack_value(src, src_layout, n_is_out, out_ch, in_ch, taps, t, nn, k) : 0.f;
     dst[i] = __float2bfloat16_rn(v);
   }
 }
@@ -202,10 +210,12 @@ int ubr_pack_weights(const float* src, int src_layout, int n_is_out, int out_ch,
                      int k_pad, void* dst_bf16, void* stream) {
   if (int rc = ensure_device()) return rc;
   UBR_REQUIRE(src && dst_bf16, "pack_weights: null pointer");
-  UBR_REQUIRE(src_layout == 0 || src_layout == 1, "pack_weights: bad src_layout");
+  UBR_REQUIRE(src_layout >= 0 && src_layout <= 2, "pack_weights: bad src_layout");
   UBR_REQUIRE(n_pad % 16 == 0 && k_pad % 16 == 0, "pack_weights: pads must be multiples of 16");
-  const int nn = n_is_out ? out_ch : in_ch, kk = n_is_out ? in_ch : out_ch;
+  const int oc_eff = src_layout == 2 ? 4 * out_ch : out_ch;
+  const int nn = n_is_out ? oc_eff : in_ch, kk = n_is_out ? in_ch : oc_eff;
   UBR_REQUIRE(n_pad >= nn && k_pad >= kk, "pack_weights: pads too small");
+  UBR_REQUIRE(src_layout != 2 || (kh == 3 && kw == 3), "pack_weights: sub-pixel deconv pack is 3x3");
   const long total = (long)(kh * kw + 1) * n_pad * k_pad;
   pack_weights_kernel<<<blocks_for(total), 256, 0, (cudaStream_t)stream>>>(src, src_layout, n_is_out, out_ch, in_ch, kh,
                                                                            kw, n_pad, k_pad, (__nv_bfloat16*)dst_bf16);

@@ -18,13 +18,14 @@ from .ops import Act
 
 class _ConvW:
     """bf16 packed operands of one conv / deconv parameter, refreshed when the parameter changes."""
-    __slots__ = ("param", "transposed", "fwd", "dgrad", "_key", "_dgrad_stale")
+    __slots__ = ("param", "transposed", "fwd", "dgrad", "fwd3", "_key", "_dgrad_stale")
 
     def __init__(self, param, transposed=False):
         self.param = param
         self.transposed = transposed
         self.fwd = None
         self.dgrad = None
+        self.fwd3 = None            # ConvTranspose only: 3x3 sub-pixel forward operand (ops.pack_weights_subpixel)
         self._key = None
         self._dgrad_stale = False
 
@@ -32,6 +33,7 @@ class _ConvW:
         key = (self.param.data_ptr(), self.param._version)
         if key != self._key:
             self.fwd = ops.pack_weights(self.param, self.transposed, True)
+            self.fwd3 = ops.pack_weights_subpixel(self.param, True) if self.transposed else None
             self.dgrad = None
             self._key = key
         if need_dgrad and (self.dgrad is None or self._dgrad_stale):
@@ -54,14 +56,19 @@ class _ConvW:
         out_ch, in_ch, kh, kw = self.dims()
         pad = lambda v: (v + 15) // 16 * 16
         res = []
+        lay = 1 if self.transposed else 0
         if changed or self.fwd is None:
             if self.fwd is None or self.fwd.device != self.param.device:
                 self.fwd = torch.empty((kh * kw + 1, pad(out_ch), pad(in_ch)), dtype=torch.bfloat16, device=self.param.device)
-            res.append((1, self.fwd))
+            res.append((lay, 1, kh, kw, self.fwd))
+            if self.transposed:
+                if self.fwd3 is None or self.fwd3.device != self.param.device:
+                    self.fwd3 = torch.empty((10, pad(4 * out_ch), pad(in_ch)), dtype=torch.bfloat16, device=self.param.device)
+                res.append((2, 1, 3, 3, self.fwd3))
         if need_dgrad and (changed or self.dgrad is None or self._dgrad_stale):
             if self.dgrad is None or self.dgrad.device != self.param.device:
                 self.dgrad = torch.empty((kh * kw + 1, pad(in_ch), pad(out_ch)), dtype=torch.bfloat16, device=self.param.device)
-            res.append((0, self.dgrad))
+            res.append((lay, 0, kh, kw, self.dgrad))
             self._dgrad_stale = False
         elif changed:
             self._dgrad_stale = True
@@ -108,9 +115,9 @@ class Engine:
             if ent is None or ent.param is not conv.weight:
                 ent = _ConvW(conv.weight, transposed)
                 self._packs[id(conv)] = ent
-            for n_is_out, dst in ent.jobs(need_dgrad):
-                out_ch, in_ch, kh, kw = ent.dims()
-                jobs.append((ent.param.data_ptr(), dst.data_ptr(), 1 if transposed else 0, n_is_out, out_ch, in_ch, kh, kw,
+            for lay, n_is_out, kh, kw, dst in ent.jobs(need_dgrad):
+                out_ch, in_ch = ent.dims()[:2]
+                jobs.append((ent.param.data_ptr(), dst.data_ptr(), lay, n_is_out, out_ch, in_ch, kh, kw,
                              dst.shape[1], dst.shape[2]))
         if not jobs:
             return
@@ -254,7 +261,8 @@ class Engine:
             layer = getattr(m, "dec_layer%d" % i)
             cd = p * 2 ** (i - 1)
             wd = self._pack(layer.deconv, need_grad, transposed=True)
-            ops.deconv_fwd(cur, wd.fwd, cd, y=Act(cat[i], 0, cd))
+            if not ops.deconv_fwd_subpixel(cur, wd.fwd3, cd, Act(cat[i], 0, cd)):
+                ops.deconv_fwd(cur, wd.fwd, cd, y=Act(cat[i], 0, cd))
             dec_in[i] = cur
             cur, recs["dec%d" % i] = self._double_fwd(layer.res, Act(cat[i]), None, training, need_grad, bn_ws)
         # ---- head (:137-143)
@@ -439,7 +447,8 @@ def run_submodule(module, *inputs):
             catbuf = torch.empty((n, hh, ww, cd + skip.shape[1]), dtype=torch.bfloat16, device=x.device)
             Act(catbuf, cd, skip.shape[1]).torch().copy_(skip.permute(0, 2, 3, 1))
             wd = eng._pack(module.deconv, False, transposed=True)
-            ops.deconv_fwd(xa, wd.fwd, cd, y=Act(catbuf, 0, cd))
+            if not ops.deconv_fwd_subpixel(xa, wd.fwd3, cd, Act(catbuf, 0, cd)):
+                ops.deconv_fwd(xa, wd.fwd, cd, y=Act(catbuf, 0, cd))
             out, _ = eng._double_fwd(module.res, Act(catbuf), None, module.training, False, bn_ws)
         else:
             raise RuntimeError("unsupported sub-module %s" % type(module).__name__)

@@ -179,6 +179,31 @@ def deconv_fwd(x, wpk, out_ch, y=None):
     return y
 
 
+def pack_weights_subpixel(w, n_is_out):
+    """ConvTranspose2d(k4,s2,p1) IOHW parameter -> bf16 [9+1][n][k] operand of the equivalent 3x3 sub-pixel conv."""
+    require_cuda(w, "weight")
+    lib = _lib.load()
+    w = w.detach().contiguous().float()
+    in_ch, out_ch, kh, kw = w.shape
+    assert kh == 4 and kw == 4
+    pad = lambda v: (v + 15) // 16 * 16
+    n_pad, k_pad = (pad(4 * out_ch), pad(in_ch)) if n_is_out else (pad(in_ch), pad(4 * out_ch))
+    dst = torch.empty((10, n_pad, k_pad), dtype=torch.bfloat16, device=w.device)
+    _lib.check(lib.ubr_pack_weights(w.data_ptr(), 2, 1 if n_is_out else 0, out_ch, in_ch, 3, 3, n_pad, k_pad,
+                                    dst.data_ptr(), _stream()), "pack_weights(subpixel)")
+    return dst
+
+
+def deconv_fwd_subpixel(x, wpk3, out_ch, y):
+    """Returns False (nothing done) when the shape has no sub-pixel path."""
+    lib = _lib.load()
+    rc = lib.ubr_deconv4s2_fwd_subpixel(x.view(), wpk3.data_ptr(), out_ch, y.view(), _stream())
+    if rc == 1:
+        return False
+    _lib.check(rc, "deconv4s2_fwd_subpixel")
+    return True
+
+
 def deconv_dgrad(dy, wpk, in_ch, dx=None):
     lib = _lib.load()
     if dx is None:
