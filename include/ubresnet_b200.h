@@ -88,6 +88,15 @@ int ubr_conv2d_wgrad(ubr_view x, ubr_view dy, int out_ch /* true rows of dw; dy.
  * deconv: grid = input (n,h,w), m_ch = in_ch, n_ch = out_ch, ntaps = 16 */
 uint64_t ubr_wgrad_workspace_bytes(int grid_n, int grid_h, int grid_w, int m_ch, int n_ch, int ntaps);
 
+/* nn.Conv2d(k=3, stride=1, padding=d, dilation=d): the atrous branches B2/B3/B4 of ASPP (reference
+ * models/ASPP_ResNet.py:203-214; d = 1, 3, 5).  Same packed operands as ubr_conv2d_{fwd,dgrad,wgrad} with ksize 3.
+ * The wgrad workspace is sized with ubr_wgrad_workspace_bytes(n, h, w, pad16(out_ch), in_ch, 9). */
+int ubr_conv2d_dilated_fwd(ubr_view x, const void* wpk, const float* bias, int out_ch, int dilation, ubr_view y,
+                           void* stream);
+int ubr_conv2d_dilated_dgrad(ubr_view dy, const void* wpk, int in_ch, int dilation, ubr_view dx, void* stream);
+int ubr_conv2d_dilated_wgrad(ubr_view x, ubr_view dy, int out_ch, int dilation, float* dw, int accumulate,
+                             void* workspace, uint64_t workspace_bytes, void* stream);
+
 /* nn.ConvTranspose2d(k=4, stride=2, padding=1, bias=False), output_size == 2x input (common_layers.py:125,128) */
 int ubr_deconv4s2_fwd(ubr_view x, const void* wpk, int out_ch, ubr_view y, void* stream);
 /* same forward as a 3x3 "sub-pixel" conv over the input grid with a pixel-shuffle epilogue (halo-resident kernel);
@@ -156,6 +165,10 @@ int ubr_maxpool3s2_bwd(ubr_view x, ubr_view dy, ubr_view dx_accum, int accumulat
  * idx[n][h/2][w/2][c] (uint8) so the backward is a pure gather (what ATen/cuDNN keep as `indices`) */
 int ubr_maxpool3s2_fwd_idx(ubr_view x, ubr_view y, uint8_t* idx, void* stream);
 int ubr_maxpool3s2_bwd_idx(const uint8_t* idx, ubr_view dy, ubr_view dx_accum, int accumulate, void* stream);
+/* nn.MaxPool2d(3, stride=1, padding=1): ASPP block 5 (models/ASPP_ResNet.py:217-219).  idx (optional, uint8
+ * [n][h][w][c]) records the argmax tap for ubr_maxpool3s1_bwd_idx (dx (+)= gathered dy). */
+int ubr_maxpool3s1_fwd(ubr_view x, ubr_view y, uint8_t* idx, void* stream);
+int ubr_maxpool3s1_bwd_idx(const uint8_t* idx, ubr_view dy, ubr_view dx_accum, int accumulate, void* stream);
 /* out = a + b (+ c); b/c may have ptr == NULL */
 int ubr_add(ubr_view a, ubr_view b, ubr_view c, ubr_view out, void* stream);
 

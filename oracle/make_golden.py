@@ -47,6 +47,40 @@ def uresnet_fixture(seed=20180721, batch=2, size=128):
                 note="generated from /root/reference (commit 3491bf2) through oracle/reference_shim.py")
 
 
+ASPP_GRAD_KEYS = ["conv1.weight", "ASPP_layer_enc3.B1_conv.weight", "ASPP_layer_enc3.B3_conv.weight",
+                  "ASPP_layer_enc3.B3_conv.bias", "ASPP_layer_enc4.B2_conv.weight", "ASPP_layer_enc4.B4_bn.weight",
+                  "ASPP_layer_enc5.B4_conv.weight", "ASPP_layer_enc5.B1_bn.bias", "ASPP_combine_enc3.ASPP_conv.weight",
+                  "ASPP_combine_enc4.ASPP_bn.weight", "ASPP_combine_enc5.ASPP_conv.bias", "enc_layer3.res2.bn2.weight",
+                  "enc_layer5.res2.bn2.bias", "dec_layer4.res.res1.bn1.weight", "dec_layer5.res.res1.bnpass.weight",
+                  "dec_layer2.deconv.weight", "conv10.weight", "conv11.weight", "conv11.bias"]
+
+
+def aspp_fixture(seed=20180722, batch=2, size=128):
+    """ASPP_ResNet(3,1,16) (reference models/ASPP_ResNet.py) train step + eval forward on seeded synthetic crops."""
+    torch.manual_seed(seed)
+    model = shim.make_reference_aspp_model(3, 1, 16)
+    chk = sum(float(v.double().abs().sum()) for v in model.state_dict().values() if v.is_floating_point())
+    img, lab, wgt = synthetic.make_batch(batch, size, size)
+    model.train()
+    crit = shim.make_reference_criterion()
+    logp = model(img)
+    loss = shim.reference_loss(crit, logp, lab, wgt)
+    loss.backward()
+    params = dict(model.named_parameters())
+    grads = OrderedDict((k, params[k].grad.clone()) for k in ASPP_GRAD_KEYS)
+    gnorm = OrderedDict((k, float(p.grad.abs().max())) for k, p in params.items())
+    sd = model.state_dict()
+    running = OrderedDict((k, sd[k].clone()) for k in ("bn1.running_mean", "ASPP_layer_enc3.B3_bn.running_var",
+                                                        "ASPP_combine_enc5.ASPP_bn.running_mean", "bn10.running_var"))
+    model.eval()
+    with torch.no_grad():
+        logp_eval = model(img)
+    return dict(seed=seed, image=img, label=lab, weight=wgt, logp=logp.detach(), loss=float(loss), grads=grads,
+                grad_absmax=gnorm, weight_abs_sum=chk, running=running, logp_eval=logp_eval, n_state=len(sd),
+                note="generated from /root/reference models/ASPP_ResNet.py (commit 3491bf2) through "
+                     "oracle/reference_shim.load_reference_aspp")
+
+
 def loss_fixture(seed=7):
     g = torch.Generator().manual_seed(seed)
     logits = torch.randn(2, 3, 24, 40, generator=g) * 2
@@ -69,6 +103,7 @@ def main():
     os.makedirs(GOLD, exist_ok=True)
     torch.save(uresnet_fixture(), os.path.join(GOLD, "uresnet_b2_128.pt"))
     torch.save(loss_fixture(), os.path.join(GOLD, "pixelwise_nll.pt"))
+    torch.save(aspp_fixture(), os.path.join(GOLD, "aspp_b2_128.pt"))
     for f in sorted(os.listdir(GOLD)):
         print(f, os.path.getsize(os.path.join(GOLD, f)))
 

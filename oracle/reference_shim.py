@@ -92,3 +92,32 @@ def reference_loss(crit, logp, target, pixelweights):
     with warnings.catch_warnings():
         warnings.simplefilter("ignore")
         return crit(logp, target, pixelweights)
+
+
+def load_reference_aspp():
+    """The unmodified reference `models/ASPP_ResNet.py` module.  It imports ROOT, larcv and the py2-only `commands`
+    module at file scope (:22,31-32) without using them in the model: empty stub modules satisfy those imports."""
+    if "aspp" in _cache:
+        return _cache["aspp"]
+    if not available():
+        raise RuntimeError("reference tree not present at %s" % REFERENCE_ROOT)
+    stubs = {}
+    for name in ("ROOT", "larcv", "commands"):
+        if name not in sys.modules:
+            stubs[name] = types.ModuleType(name)
+    stubs.get("larcv", sys.modules.get("larcv")).larcv = types.SimpleNamespace()
+    sys.modules.update(stubs)
+    try:
+        with warnings.catch_warnings():
+            warnings.simplefilter("ignore")
+            mod = _load("ASPP_ResNet", "models/ASPP_ResNet.py")
+    finally:
+        for name in stubs:
+            sys.modules.pop(name, None)
+    _cache["aspp"] = mod
+    return mod
+
+
+def make_reference_aspp_model(num_classes=3, in_channels=1, inplanes=16):
+    return load_reference_aspp().ASPP_ResNet(num_classes=num_classes, in_channels=in_channels, inplanes=inplanes,
+                                             showsizes=False)

@@ -361,6 +361,48 @@ def check_maxpool(c, n, h, w, seed=0):
     return res
 
 
+def check_dilated(cin, cout, dil, n, h, w, in_ld=None, seed=0):
+    """3x3 stride-1 conv with padding == dilation (ASPP branches): fwd (+bias), dgrad, wgrad against torch."""
+    name = "dilated_ci%d_co%d_d%d_n%d_%dx%d" % (cin, cout, dil, n, h, w)
+    x = bf(gen(n, cin, h, w, seed=seed))
+    wt = bf(gen(cout, cin, 3, 3, seed=seed + 1, scale=(2.0 / (9 * cin)) ** 0.5))
+    b = gen(cout, seed=seed + 2)
+    dy = bf(gen(n, cout, h, w, seed=seed + 3))
+    xa = act_from(x, in_ld, 0 if not in_ld else (in_ld - cin))
+    ya = act_out(n, h, w, cout, 2 * cout, cout)
+    ops.conv2d_dilated_fwd(xa, ops.pack_weights(wt.to(DEV), False, True), b.to(DEV), cout, dil, y=ya)
+    dxa = act_out(n, h, w, cin)
+    ops.conv2d_dilated_dgrad(act_from(dy), ops.pack_weights(wt.to(DEV), False, False), cin, dil, dx=dxa)
+    ws = torch.empty(ops.wgrad_workspace_bytes(n, h, w, cout, cin, 9) // 4 + 4, dtype=torch.float32, device=DEV)
+    dw = torch.full((cout, cin, 3, 3), 9.0, dtype=torch.float32, device=DEV)
+    ops.conv2d_dilated_wgrad(xa, act_from(dy), cout, dil, dw, False, ws)
+    torch.cuda.synchronize()
+    return [(name + "_fwd", relerr(ya.nchw_float(), F.conv2d(x, wt, b, 1, dil, dil)), 1e-2),
+            (name + "_fwd_slice_untouched", (ya.buf[..., :cout].float() - 3.0).abs().max().item(), 0.0),
+            (name + "_dgrad", relerr(dxa.nchw_float(), torch.nn.grad.conv2d_input((n, cin, h, w), wt, dy, 1, dil, dil)), 1e-2),
+            (name + "_wgrad", relerr(dw, torch.nn.grad.conv2d_weight(x, (cout, cin, 3, 3), dy, 1, dil, dil)), 2e-3)]
+
+
+def check_maxpool_s1(c, n, h, w, seed=0):
+    """MaxPool2d(3, 1, 1) (ASPP block 5): bit-exact forward into a channel slice, gather backward with accumulate."""
+    name = "maxpool_s1_c%d_n%d_%dx%d" % (c, n, h, w)
+    x = F.relu(bf(gen(n, c, h, w, seed=seed)))          # post-ReLU input: many exact ties at 0
+    xg = x.clone().requires_grad_(True)
+    ref = F.max_pool2d(xg, 3, 1, 1)
+    dy = bf(gen(n, c, h, w, seed=seed + 1))
+    ref.backward(dy)
+    base = bf(gen(n, c, h, w, seed=seed + 2))
+    xa = act_from(x, 2 * c, c)
+    ya, idx = ops.maxpool3s1_fwd(xa, y=act_out(n, h, w, c, c + 64, 64), want_idx=True)
+    yb, none = ops.maxpool3s1_fwd(xa)
+    dx = act_from(base, 2 * c, 0)
+    ops.maxpool3s1_bwd_idx(idx, act_from(dy, c + 16, 16), dx, True)
+    torch.cuda.synchronize()
+    return [(name + "_fwd", relerr(ya.nchw_float(), ref), 0.0), (name + "_fwd_noidx", relerr(yb.nchw_float(), ref), 0.0),
+            (name + "_noidx_is_none", 0.0 if none is None else 1.0, 0.0),
+            (name + "_bwd_acc", relerr(dx.nchw_float(), bf(xg.grad + base)), 8e-3)]
+
+
 def check_add(c, n, h, w, seed=0):
     a, b, d = (bf(gen(n, c, h, w, seed=seed + i)) for i in range(3))
     out = ops.add(act_from(a), act_from(b, 2 * c, c), act_from(d))
@@ -487,6 +529,25 @@ CHECKS = {
     "halo_wgrad_7x7": lambda: (check_conv_wgrad(16, 16, 7, 1, 1, 64, 128, seed=48)
                                + check_conv_wgrad(16, 3, 7, 1, 1, 32, 256, seed=49, cout_pad=16)),
 }
+
+
+# ASPP_ResNet operators (reference models/ASPP_ResNet.py:188-286): dilated branches, stride-1 max-pool, and the
+# 192/320/576/384/768-channel concat operands (64-wide N tiles in conv_gemm / wgrad_gemm)
+CHECKS.update({
+    "aspp_dilated_d3": lambda: check_dilated(128, 16, 3, 2, 16, 16, seed=81) + check_dilated(256, 16, 3, 1, 8, 8, in_ld=512, seed=82),
+    "aspp_dilated_d5": lambda: check_dilated(128, 16, 5, 2, 16, 16, seed=83) + check_dilated(512, 16, 5, 3, 4, 4, seed=84),
+    "aspp_dilated_d1": lambda: check_dilated(64, 32, 1, 1, 16, 24, seed=85),
+    "aspp_maxpool_s1": lambda: check_maxpool_s1(128, 2, 16, 16, seed=86) + check_maxpool_s1(16, 1, 5, 9, seed=87),
+    "aspp_combine_1x1": lambda: (check_conv_fwd(192, 128, 1, 1, 2, 16, 16, seed=88, bias=True)
+                                 + check_conv_dgrad(192, 128, 1, 1, 2, 16, 16, seed=89)
+                                 + check_conv_wgrad(192, 128, 1, 1, 2, 16, 16, seed=90)
+                                 + check_conv_dgrad(320, 256, 1, 1, 2, 8, 8, seed=91)
+                                 + check_conv_wgrad(576, 512, 1, 1, 4, 4, 4, seed=92)),
+    "aspp_decoder_convs": lambda: (check_conv_fwd(384, 256, 3, 1, 1, 16, 16, seed=93) + check_conv_dgrad(384, 256, 3, 1, 1, 16, 16, seed=94)
+                                   + check_conv_wgrad(384, 256, 3, 1, 1, 16, 16, seed=95)
+                                   + check_conv_wgrad(768, 512, 1, 1, 2, 8, 8, seed=96)
+                                   + check_deconv(1024, 256, 1, 4, 4, out_ld=768, seed=97)),
+})
 
 
 def run(name):

@@ -29,9 +29,10 @@ import torch
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 
+from oracle import aspp_port  # noqa: E402
 from oracle import uresnet_port as port  # noqa: E402
 from ubresnet_b200 import synthetic  # noqa: E402
-from ubresnet_b200.models import UResNet  # noqa: E402
+from ubresnet_b200.models import ASPP_ResNet, UResNet  # noqa: E402
 from ubresnet_b200.training.pixelwise_nllloss import PixelWiseNLLLoss  # noqa: E402
 
 DEV = "cuda:0"
@@ -45,6 +46,11 @@ SLACK = 1.6          # allowed multiple of the emulated-bf16 oracle's own error
 GRAD_RATIO_MEDIAN = 1.25
 GRAD_RATIO_MAX = 3.0
 NEAR_ZERO_BIASES = ("conv1.bias", "conv10.bias")   # conv bias followed by train-mode BN: true gradient == 0
+
+
+def _near_zero_bias(name):
+    """conv biases that feed a train-mode BatchNorm (every biased conv except conv11): true gradient == 0."""
+    return name in NEAR_ZERO_BIASES or name.endswith(("_conv.bias",))
 
 
 def _rel(a, b):
@@ -61,11 +67,14 @@ def _argmax_disagree(lp, ref, mask=None):
     return 1.0 - am.float().mean().item()
 
 
-def build_pair(num_classes=3, inplanes=16, seed=1234, warm_bn=True):
+def build_pair(num_classes=3, inplanes=16, seed=1234, warm_bn=True, arch="uresnet"):
     """(CUDA model, oracle state_dict) with identical weights; BN affine params perturbed so that gamma/beta
     gradients and the affine path are exercised (the reference init gamma=1, beta=0 hides errors)."""
     torch.manual_seed(seed)
-    model = UResNet(num_classes=num_classes, input_channels=1, inplanes=inplanes)
+    if arch == "aspp":
+        model = ASPP_ResNet(num_classes=num_classes, in_channels=1, inplanes=inplanes, showsizes=False)
+    else:
+        model = UResNet(num_classes=num_classes, input_channels=1, inplanes=inplanes)
     g = torch.Generator().manual_seed(seed + 1)
     if warm_bn:
         with torch.no_grad():
@@ -79,15 +88,16 @@ def build_pair(num_classes=3, inplanes=16, seed=1234, warm_bn=True):
     return model.to(DEV), sd
 
 
-def train_parity(batch=2, size=128, num_classes=3, dense=False, seed=1234):
-    model, sd = build_pair(num_classes=num_classes, seed=seed)
+def train_parity(batch=2, size=128, num_classes=3, dense=False, seed=1234, arch="uresnet"):
+    model, sd = build_pair(num_classes=num_classes, seed=seed, arch=arch)
+    port = aspp_port if arch == "aspp" else globals()["port"]
     img, lab, wgt = synthetic.make_batch(batch, size, size, dense=dense)
     if num_classes > 3:
         lab = lab.clone()
         lab[:, :4, :4] = num_classes - 1
     # fp32 oracle, and the same oracle with bf16 storage emulation (the inherent-error yardstick)
     loss_ref, logp_ref, grads_ref, sd_after = port.train_step_grads(sd, img, lab, wgt)
-    loss_emu, logp_emu, grads_emu, _ = port.train_step_grads(sd, img, lab, wgt, quant=True)
+    loss_emu, logp_emu, grads_emu, sd_emu = port.train_step_grads(sd, img, lab, wgt, quant=True)
     # device
     model.train()
     crit = PixelWiseNLLLoss()
@@ -112,7 +122,7 @@ def train_parity(batch=2, size=128, num_classes=3, dense=False, seed=1234):
     head_worst, head_emu = 0.0, 0.0
     detail = {}
     for name, prm in params.items():
-        if name in NEAR_ZERO_BIASES:
+        if _near_zero_bias(name):
             wname = name.replace("bias", "weight")
             scale = grads_ref[wname].abs().max().item()
             e = prm.grad.detach().abs().max().item() / scale
@@ -135,18 +145,20 @@ def train_parity(batch=2, size=128, num_classes=3, dense=False, seed=1234):
     res.append(("grad_ratio_max[%s: err %.2e]" % (worst_name, detail[worst_name][0]), ratios[worst_name],
                 GRAD_RATIO_MAX))
     msd = model.state_dict()
-    wrs = 0.0
+    wrs, wrs_emu = 0.0, 0.0
     for k, v in sd_after.items():
         if "running_" in k:
             wrs = max(wrs, _rel(msd[k], v))
-    res.append(("running_stats_rel", wrs, TOL_RUNSTAT))
+            wrs_emu = max(wrs_emu, _rel(sd_emu[k], v))
+    res.append(("running_stats_rel (emulated: %.2e)" % wrs_emu, wrs, max(TOL_RUNSTAT, SLACK * wrs_emu)))
     nbt = all(int(msd[k].item()) == int(v.item()) for k, v in sd_after.items() if k.endswith("num_batches_tracked"))
     res.append(("num_batches_tracked_mismatch", 0.0 if nbt else 1.0, 0.0))
     return res, detail
 
 
-def eval_parity(batch=2, size=128, num_classes=3, seed=77):
-    model, sd = build_pair(num_classes=num_classes, seed=seed)
+def eval_parity(batch=2, size=128, num_classes=3, seed=77, arch="uresnet"):
+    model, sd = build_pair(num_classes=num_classes, seed=seed, arch=arch)
+    port = aspp_port if arch == "aspp" else globals()["port"]
     img, _, _ = synthetic.make_batch(batch, size, size)
     with torch.no_grad():
         logp_ref = port.forward(port.clone_state_dict(sd), img, training=False)
@@ -162,16 +174,21 @@ def eval_parity(batch=2, size=128, num_classes=3, seed=77):
              max(1.0 - TOL_ARGMAX, SLACK * a_emu))], {}
 
 
-def golden_parity(path=None):
+def golden_parity(path=None, arch="uresnet"):
     """CUDA path vs the committed fixture generated FROM the reference (oracle/make_golden.py)."""
-    path = path or os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "uresnet_b2_128.pt")
+    fname = "aspp_b2_128.pt" if arch == "aspp" else "uresnet_b2_128.pt"
+    path = path or os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", fname)
+    port = aspp_port if arch == "aspp" else globals()["port"]
     gold = torch.load(path, weights_only=False)
     torch.manual_seed(gold["seed"])
-    model = UResNet(num_classes=3, input_channels=1, inplanes=16)
+    if arch == "aspp":
+        model = ASPP_ResNet(num_classes=3, in_channels=1, inplanes=16, showsizes=False)
+    else:
+        model = UResNet(num_classes=3, input_channels=1, inplanes=16)
     sd = OrderedDict((k, v.detach().clone()) for k, v in model.state_dict().items())
     chk = sum(float(v.double().abs().sum()) for k, v in model.state_dict().items() if v.is_floating_point())
     res = [("golden_weight_checksum", abs(chk - gold["weight_abs_sum"]) / gold["weight_abs_sum"], 1e-9)]
-    _, logp_emu, grads_emu, _ = port.train_step_grads(sd, gold["image"], gold["label"], gold["weight"], quant=True)
+    loss_emu, logp_emu, grads_emu, _ = port.train_step_grads(sd, gold["image"], gold["label"], gold["weight"], quant=True)
     model = model.to(DEV).train()
     logp = model(gold["image"].to(DEV))
     loss = PixelWiseNLLLoss()(logp, gold["label"].to(DEV), gold["weight"].to(DEV))
@@ -180,11 +197,13 @@ def golden_parity(path=None):
     e_emu = _rel(logp_emu, gold["logp"])
     res.append(("golden_logp_rel (emulated-bf16 oracle: %.2e)" % e_emu, _rel(logp, gold["logp"]),
                 max(TOL_LOGP, SLACK * e_emu)))
-    res.append(("golden_loss_rel", abs(loss.item() - gold["loss"]) / abs(gold["loss"]), 2e-3))
+    l_emu = abs(loss_emu.item() - gold["loss"]) / abs(gold["loss"])
+    res.append(("golden_loss_rel (emulated: %.2e)" % l_emu, abs(loss.item() - gold["loss"]) / abs(gold["loss"]),
+                max(2e-3, SLACK * l_emu)))
     params = dict(model.named_parameters())
     ratios = []
     for name, gref in gold["grads"].items():
-        if name in NEAR_ZERO_BIASES:
+        if _near_zero_bias(name):
             continue
         emu = _rel(grads_emu[name], gref)
         e = _rel(params[name].grad, gref)
@@ -204,6 +223,11 @@ CHECKS = {
     "train_256_c4": lambda: train_parity(1, 256, num_classes=4, seed=5),
     "eval_128": lambda: eval_parity(2, 128),
     "golden": lambda: golden_parity(),
+    # ASPP_ResNet (BASELINE.json configs[4]; reference models/ASPP_ResNet.py)
+    "aspp_train_256": lambda: train_parity(2, 256, arch="aspp", seed=321),
+    "aspp_train_dense_256": lambda: train_parity(1, 256, arch="aspp", dense=True, seed=17),
+    "aspp_eval_128": lambda: eval_parity(2, 128, arch="aspp"),
+    "aspp_golden": lambda: golden_parity(arch="aspp"),
 }
 
 

@@ -129,3 +129,71 @@ def test_stitch_is_highest_index_wins():
     tiles = np.stack([np.full((1, 4, 4), i + 1.0, dtype=np.float32) for i in range(4)])
     out = port.stitch_scatter_np(tiles, plan, 6, 6)[0]
     assert out[0, 0] == 1 and out[0, 3] == 2 and out[3, 0] == 3 and out[3, 3] == 4 and out[2, 2] == 4
+
+
+# ------------------------------------------------------------------------------------------------
+# ASPP_ResNet (BASELINE.json configs[4]; reference models/ASPP_ResNet.py)
+# ------------------------------------------------------------------------------------------------
+@needs_ref
+def test_aspp_port_matches_reference_forward_backward():
+    from oracle import aspp_port
+    torch.manual_seed(13)
+    ref = shim.make_reference_aspp_model(3, 1, 16)
+    sd = OrderedDict((k, v.detach().clone()) for k, v in ref.state_dict().items())
+    img, lab, wgt = synthetic.make_batch(2, 64, 64)
+    ref.train()
+    crit = shim.make_reference_criterion()
+    logp_ref = ref(img)
+    loss_ref = shim.reference_loss(crit, logp_ref, lab, wgt)
+    loss_ref.backward()
+    loss, logp, grads, after = aspp_port.train_step_grads(sd, img, lab, wgt)
+    assert _rel(logp, logp_ref.detach()) < 1e-5
+    assert abs(loss.item() - loss_ref.item()) / abs(loss_ref.item()) < 1e-6
+    for name, p in ref.named_parameters():
+        if name.endswith("_conv.bias") or name in ("conv1.bias", "conv10.bias"):
+            continue            # bias in front of a train-mode BN: exact zero in theory, round-off on both sides
+        assert _rel(grads[name], p.grad) < 2e-4, name
+    rsd = ref.state_dict()
+    for k, v in after.items():
+        if "running_" in k:
+            assert _rel(v.detach(), rsd[k]) < 1e-5, k
+        if k.endswith("num_batches_tracked"):
+            assert int(v) == int(rsd[k])
+
+
+@needs_ref
+def test_aspp_module_init_is_bit_identical_to_reference():
+    from ubresnet_b200.models import ASPP_ResNet
+    torch.manual_seed(6)
+    mine = ASPP_ResNet(3, 1, 16, showsizes=False).state_dict()
+    torch.manual_seed(6)
+    ref = shim.make_reference_aspp_model(3, 1, 16).state_dict()
+    assert list(mine.keys()) == list(ref.keys())
+    assert len(mine) == 426
+    for k in mine:
+        assert torch.equal(mine[k], ref[k]), k
+
+
+def test_aspp_port_matches_golden():
+    from oracle import aspp_port
+    from ubresnet_b200.models import ASPP_ResNet
+    gold = torch.load(os.path.join(GOLD, "aspp_b2_128.pt"), weights_only=False)
+    torch.manual_seed(gold["seed"])
+    model = ASPP_ResNet(3, 1, 16, showsizes=False)
+    sd = OrderedDict((k, v.detach().clone()) for k, v in model.state_dict().items())
+    assert len(sd) == gold["n_state"] == 426
+    assert sum(p.numel() for p in model.parameters()) == 31575683
+    chk = sum(float(v.double().abs().sum()) for v in sd.values() if v.is_floating_point())
+    assert abs(chk - gold["weight_abs_sum"]) <= 1e-9 * gold["weight_abs_sum"]
+    loss, logp, grads, after = aspp_port.train_step_grads(sd, gold["image"], gold["label"], gold["weight"])
+    assert _rel(logp, gold["logp"]) < 1e-4
+    assert abs(loss.item() - gold["loss"]) / abs(gold["loss"]) < 1e-5
+    for name, g in gold["grads"].items():
+        if name.endswith("_conv.bias"):
+            continue
+        assert _rel(grads[name], g) < 1e-3, name
+    for k, v in gold["running"].items():
+        assert _rel(after[k].detach(), v) < 1e-4, k
+    with torch.no_grad():
+        le = aspp_port.forward(after, gold["image"], training=False)
+    assert _rel(le, gold["logp_eval"]) < 1e-3

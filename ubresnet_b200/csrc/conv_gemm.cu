@@ -209,6 +209,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_gemm_kernel(const __grid_con
 // host side
 // ------------------------------------------------------------------------------------------------
 struct TileShape { int bw, bh, bn; };
+static int out_box_c(int nt) { return nt >= 64 ? 64 : nt; }
 
 static TileShape pick_tile(int n, int h, int w) {
   // 128 pixels per tile = bw x bh x bn (powers of two); maximise useful fraction, prefer wide rows
@@ -250,6 +251,9 @@ static int make_phase_map(CUtensorMap* m, const ubr_view& v, int ph, int pw, int
   return make_tmap_bf16(m, base, 4, dims, str, box, box_c * 2);
 }
 
+// output-channel tile: 128 where it divides N, else 64 (192/320/576-channel ASPP concat gradients), else all of N
+static int pick_nt(int n_pad) { return (n_pad % 128 == 0) ? 128 : ((n_pad % 64 == 0) ? 64 : n_pad); }
+
 // generic launcher. `grid_view` = (n, h, w) of the output tile grid; a_maps built by caller.
 static int launch_conv_gemm(ConvGemmParams& p, int grid_n, int grid_h, int grid_w, TileShape t, int k_ch,
                             int n_pad, const void* wpk, int nslabs, const TapSpec* taps, int ntaps,
@@ -260,8 +264,8 @@ static int launch_conv_gemm(ConvGemmParams& p, int grid_n, int grid_h, int grid_
   UBR_REQUIRE(p.kc == 16 || p.kc == 32 || p.kc == 64, "conv_gemm: unsupported K chunk %d", p.kc);
   UBR_REQUIRE(k_ch % p.kc == 0, "conv_gemm: K=%d not a multiple of chunk %d", k_ch, p.kc);
   p.nkc = k_ch / p.kc;
-  p.nt = n_pad >= 128 ? 128 : n_pad;
-  UBR_REQUIRE(n_pad % p.nt == 0, "conv_gemm: N=%d not a multiple of tile %d", n_pad, p.nt);
+  p.nt = pick_nt(n_pad);
+  UBR_REQUIRE(p.nt <= 128 && n_pad % p.nt == 0, "conv_gemm: N=%d not a multiple of tile %d", n_pad, p.nt);
   p.ntaps = ntaps;
   for (int i = 0; i < ntaps; ++i) {
     p.dh[i] = (int8_t)taps[i].dh; p.dw[i] = (int8_t)taps[i].dw;
@@ -308,7 +312,6 @@ static int launch_conv_gemm(ConvGemmParams& p, int grid_n, int grid_h, int grid_
   return 0;
 }
 
-static int out_box_c(int nt) { return nt >= 64 ? 64 : nt; }
 
 }  // namespace ubr
 
@@ -391,7 +394,7 @@ static int conv2d_fwd_impl(ubr_view x, const void* wpk, const float* bias, int o
     UBR_REQUIRE(y.n == x.n && y.h == ho && y.w == wo && y.c == out_ch, "conv2d_fwd: output view mismatch");
     UBR_REQUIRE(out_ch % 16 == 0, "conv2d_fwd: bf16 output needs out_ch %% 16 == 0");
     p.out_mode = 0;
-    p.o_box_c = out_box_c(n_pad >= 128 ? 128 : n_pad);
+    p.o_box_c = out_box_c(pick_nt(n_pad));
     if (int rc = make_act_map(&p.o_map, y, p.o_box_c, t)) return rc;
   }
   return launch_conv_gemm(p, x.n, ho, wo, t, x.c, n_pad, wpk, ksize * ksize, taps, nt, (cudaStream_t)stream);
@@ -437,7 +440,7 @@ static int conv2d_dgrad_impl(ubr_view dy, const void* wpk, int in_ch, int ksize,
     }
     if (accumulate) return 1;      // not fused for this shape: caller adds separately
     p.out_mode = 0;
-    p.o_box_c = out_box_c(in_ch >= 128 ? 128 : in_ch);
+    p.o_box_c = out_box_c(pick_nt(in_ch));
     if (int rc = make_act_map(&p.o_map, dx, p.o_box_c, t)) return rc;
     return launch_conv_gemm(p, dy.n, dy.h, dy.w, t, dy.c, in_ch, wpk, ksize * ksize, taps, nt, (cudaStream_t)stream);
   }
@@ -458,7 +461,7 @@ static int conv2d_dgrad_impl(ubr_view dy, const void* wpk, int in_ch, int ksize,
           taps[nt++] = TapSpec{(ph - oh) / 2, (pw - ow) / 2, 0, r * ksize + s};
         }
       p.out_mode = 0;
-      p.o_box_c = out_box_c(in_ch >= 128 ? 128 : in_ch);
+      p.o_box_c = out_box_c(pick_nt(in_ch));
       if (int rc = make_phase_map(&p.o_map, dx, ph, pw, p.o_box_c, t)) return rc;
       if (nt == 0) {
         // no tap reaches this phase (1x1 stride 2, odd pixels): gradient is zero there.
@@ -470,6 +473,56 @@ static int conv2d_dgrad_impl(ubr_view dy, const void* wpk, int in_ch, int ksize,
         return rc;
     }
   return 0;
+}
+
+// 3x3 stride-1 DILATED conv (padding == dilation): the ASPP branches of models/ASPP_ResNet.py:207-214.  Taps are the
+// dense 3x3 taps scaled by the dilation; the TMA zero-fill provides the (dilation-wide) padding.
+int ubr_conv2d_dilated_fwd(ubr_view x, const void* wpk, const float* bias, int out_ch, int dilation, ubr_view y,
+                           void* stream) {
+  if (int rc = ensure_device()) return rc;
+  if (int rc = check_view(x, "conv2d_dilated_fwd.x")) return rc;
+  if (int rc = check_view(y, "conv2d_dilated_fwd.y")) return rc;
+  UBR_REQUIRE(dilation >= 1 && dilation <= 16, "conv2d_dilated_fwd: dilation %d unsupported", dilation);
+  UBR_REQUIRE(x.c % 16 == 0 && out_ch % 16 == 0, "conv2d_dilated_fwd: channels must be multiples of 16");
+  UBR_REQUIRE(wpk != nullptr, "conv2d_dilated_fwd: null weights");
+  UBR_REQUIRE(y.n == x.n && y.h == x.h && y.w == x.w && y.c == out_ch, "conv2d_dilated_fwd: output view mismatch");
+  ConvGemmParams p;
+  memset(&p, 0, sizeof(p));
+  TileShape t = pick_tile(x.n, x.h, x.w);
+  const int kc = x.c >= 64 ? 64 : x.c;
+  if (int rc = make_act_map(&p.a_map[0], x, kc, t)) return rc;
+  TapSpec taps[9];
+  int nt = 0;
+  for (int r = 0; r < 3; ++r)
+    for (int s = 0; s < 3; ++s) taps[nt++] = TapSpec{(r - 1) * dilation, (s - 1) * dilation, 0, r * 3 + s};
+  p.bias = bias;
+  p.out_mode = 0;
+  p.o_box_c = out_box_c(pick_nt(out_ch));
+  if (int rc = make_act_map(&p.o_map, y, p.o_box_c, t)) return rc;
+  return launch_conv_gemm(p, x.n, x.h, x.w, t, x.c, out_ch, wpk, 9, taps, nt, (cudaStream_t)stream);
+}
+
+int ubr_conv2d_dilated_dgrad(ubr_view dy, const void* wpk, int in_ch, int dilation, ubr_view dx, void* stream) {
+  if (int rc = ensure_device()) return rc;
+  if (int rc = check_view(dy, "conv2d_dilated_dgrad.dy")) return rc;
+  if (int rc = check_view(dx, "conv2d_dilated_dgrad.dx")) return rc;
+  UBR_REQUIRE(dilation >= 1 && dilation <= 16, "conv2d_dilated_dgrad: dilation %d unsupported", dilation);
+  UBR_REQUIRE(dy.c % 16 == 0 && in_ch % 16 == 0, "conv2d_dilated_dgrad: channels must be multiples of 16");
+  UBR_REQUIRE(dx.c == in_ch && dx.n == dy.n && dx.h == dy.h && dx.w == dy.w, "conv2d_dilated_dgrad: dx view mismatch");
+  ConvGemmParams p;
+  memset(&p, 0, sizeof(p));
+  TileShape t = pick_tile(dy.n, dy.h, dy.w);
+  const int kc = dy.c >= 64 ? 64 : dy.c;
+  if (int rc = make_act_map(&p.a_map[0], dy, kc, t)) return rc;
+  TapSpec taps[9];
+  int nt = 0;
+  // dx[p] = sum_{r,s} dy[p - d*(r-1, s-1)] * W[:, :, r, s]
+  for (int r = 0; r < 3; ++r)
+    for (int s = 0; s < 3; ++s) taps[nt++] = TapSpec{(1 - r) * dilation, (1 - s) * dilation, 0, r * 3 + s};
+  p.out_mode = 0;
+  p.o_box_c = out_box_c(pick_nt(in_ch));
+  if (int rc = make_act_map(&p.o_map, dx, p.o_box_c, t)) return rc;
+  return launch_conv_gemm(p, dy.n, dy.h, dy.w, t, dy.c, in_ch, wpk, 9, taps, nt, (cudaStream_t)stream);
 }
 
 int ubr_deconv4s2_fwd(ubr_view x, const void* wpk, int out_ch, ubr_view y, void* stream) {
@@ -494,7 +547,7 @@ int ubr_deconv4s2_fwd(ubr_view x, const void* wpk, int out_ch, ubr_view y, void*
           taps[nt++] = TapSpec{(ph + 1 - kh) / 2, (pw + 1 - kw) / 2, 0, kh * 4 + kw};
         }
       p.out_mode = 0;
-      p.o_box_c = out_box_c(out_ch >= 128 ? 128 : out_ch);
+      p.o_box_c = out_box_c(pick_nt(out_ch));
       if (int rc = make_phase_map(&p.o_map, y, ph, pw, p.o_box_c, t)) return rc;
       if (int rc = launch_conv_gemm(p, x.n, x.h, x.w, t, x.c, out_ch, wpk, 16, taps, nt, (cudaStream_t)stream))
         return rc;
@@ -541,7 +594,7 @@ int ubr_deconv4s2_dgrad(ubr_view dy, const void* wpk, int in_ch, ubr_view dx, vo
       taps[nt++] = TapSpec{(oh - ph) / 2, (ow - pw) / 2, ph * 2 + pw, kh * 4 + kw};
     }
   p.out_mode = 0;
-  p.o_box_c = out_box_c(in_ch >= 128 ? 128 : in_ch);
+  p.o_box_c = out_box_c(pick_nt(in_ch));
   if (int rc = make_act_map(&p.o_map, dx, p.o_box_c, t)) return rc;
   return launch_conv_gemm(p, dx.n, dx.h, dx.w, t, dy.c, in_ch, wpk, 16, taps, nt, (cudaStream_t)stream);
 }

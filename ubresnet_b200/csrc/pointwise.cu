@@ -494,6 +494,87 @@ __global__ void __launch_bounds__(256) maxpool_bwd_idx_kernel(const uint8_t* __r
   }
 }
 
+// ------------------------------------------------------------------ MaxPool 3x3 / stride 1 / pad 1
+// ASPP block 5 (reference models/ASPP_ResNet.py:217-219, 239).  idx (optional) records the argmax tap like the
+// stride-2 kernel so the backward is a gather over the <= 9 windows that cover an input pixel.
+__global__ void __launch_bounds__(256) maxpool3s1_fwd_kernel(const __nv_bfloat16* x, int xld, int n, int h, int w, int c,
+                                                             __nv_bfloat16* y, int yld, uint8_t* __restrict__ idx) {
+  const int cgs = c >> 3;
+  const long total = (long)n * h * w * cgs;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+    const int cg = (int)(i % cgs);
+    long p = i / cgs;
+    const int ow = (int)(p % w); p /= w;
+    const int oh = (int)(p % h);
+    const int b = (int)(p / h);
+    float m[8];
+    uint32_t arg[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { m[j] = -INFINITY; arg[j] = 255u; }
+    for (int kh = 0; kh < 3; ++kh) {
+      const int ih = oh - 1 + kh;
+      if (ih < 0 || ih >= h) continue;
+      for (int kw = 0; kw < 3; ++kw) {
+        const int iw = ow - 1 + kw;
+        if (iw < 0 || iw >= w) continue;
+        float f[8];
+        load8(x + (((long)b * h + ih) * w + iw) * xld + cg * 8, f);
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          if (f[j] > m[j] || arg[j] == 255u) { m[j] = f[j]; arg[j] = (uint32_t)(kh * 3 + kw); }
+      }
+    }
+    store8(y + (((long)b * h + oh) * w + ow) * yld + cg * 8, m);
+    if (idx) {
+      uint2 u;
+      u.x = arg[0] | (arg[1] << 8) | (arg[2] << 16) | (arg[3] << 24);
+      u.y = arg[4] | (arg[5] << 8) | (arg[6] << 16) | (arg[7] << 24);
+      *reinterpret_cast<uint2*>(idx + i * 8) = u;          // idx layout [n][h][w][c], c contiguous
+    }
+  }
+}
+
+__global__ void __launch_bounds__(256) maxpool3s1_bwd_idx_kernel(const uint8_t* __restrict__ idx, int n, int h, int w, int c,
+                                                                 const __nv_bfloat16* dy, int dyld, __nv_bfloat16* dx,
+                                                                 int dxld, int accumulate) {
+  const int cgs = c >> 3;
+  const long total = (long)n * h * w * cgs;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+    const int cg = (int)(i % cgs);
+    long p = i / cgs;
+    const int iw = (int)(p % w); p /= w;
+    const int ih = (int)(p % h);
+    const int b = (int)(p / h);
+    float acc[8];
+    if (accumulate) load8(dx + (((long)b * h + ih) * w + iw) * dxld + cg * 8, acc);
+    else {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+    }
+    for (int oh = ih - 1; oh <= ih + 1; ++oh) {
+      if (oh < 0 || oh >= h) continue;
+      for (int ow = iw - 1; ow <= iw + 1; ++ow) {
+        if (ow < 0 || ow >= w) continue;
+        const long q = ((long)b * h + oh) * w + ow;
+        const uint2 u = *reinterpret_cast<const uint2*>(idx + (q * cgs + cg) * 8);
+        const uint32_t me = (uint32_t)((ih - oh + 1) * 3 + (iw - ow + 1));
+        const uint32_t m4 = me * 0x01010101u;
+        const uint32_t e0 = u.x ^ m4, e1 = u.y ^ m4;       // a zero byte <=> this input is that channel's argmax
+        if (((e0 - 0x01010101u) & ~e0 & 0x80808080u) | ((e1 - 0x01010101u) & ~e1 & 0x80808080u)) {
+          float g[8];
+          load8(dy + q * dyld + cg * 8, g);
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            if (((e0 >> (8 * j)) & 0xffu) == 0u) acc[j] += g[j];
+            if (((e1 >> (8 * j)) & 0xffu) == 0u) acc[4 + j] += g[4 + j];
+          }
+        }
+      }
+    }
+    store8(dx + (((long)b * h + ih) * w + iw) * dxld + cg * 8, acc);
+  }
+}
+
 // gather form of the backward: each input pixel re-derives the argmax (first maximum in (kh,kw) scan
 // order, as ATen's max_pool2d) of every window that covers it.  Deterministic, no atomics.
 __global__ void __launch_bounds__(256) maxpool_bwd_kernel(const __nv_bfloat16* x, int xld, int n, int h, int w, int c,
@@ -814,6 +895,32 @@ int ubr_maxpool3s2_bwd(ubr_view x, ubr_view dy, ubr_view dx_accum, int accumulat
       (const __nv_bfloat16*)x.ptr, x.ld, x.n, x.h, x.w, x.c, (const __nv_bfloat16*)dy.ptr, dy.ld,
       (__nv_bfloat16*)dx_accum.ptr, dx_accum.ld, accumulate);
   UBR_LAUNCH_CHECK("maxpool_bwd_kernel");
+  return 0;
+}
+
+int ubr_maxpool3s1_fwd(ubr_view x, ubr_view y, uint8_t* idx, void* stream) {
+  if (int rc = ensure_device()) return rc;
+  if (int rc = chk(x, "maxpool3s1_fwd.x")) return rc;
+  if (int rc = chk(y, "maxpool3s1_fwd.y")) return rc;
+  UBR_REQUIRE(idx == nullptr || ((uintptr_t)idx & 7) == 0, "maxpool3s1_fwd: idx must be 8-byte aligned");
+  if (int rc = same_shape(x, y, "maxpool3s1_fwd(y)")) return rc;
+  const long total = (long)x.n * x.h * x.w * (x.c / 8);
+  maxpool3s1_fwd_kernel<<<ew_blocks(total), 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)x.ptr, x.ld, x.n, x.h, x.w,
+                                                                            x.c, (__nv_bfloat16*)y.ptr, y.ld, idx);
+  UBR_LAUNCH_CHECK("maxpool3s1_fwd_kernel");
+  return 0;
+}
+
+int ubr_maxpool3s1_bwd_idx(const uint8_t* idx, ubr_view dy, ubr_view dx_accum, int accumulate, void* stream) {
+  if (int rc = ensure_device()) return rc;
+  if (int rc = chk(dy, "maxpool3s1_bwd_idx.dy")) return rc;
+  if (int rc = chk(dx_accum, "maxpool3s1_bwd_idx.dx")) return rc;
+  UBR_REQUIRE(idx != nullptr, "maxpool3s1_bwd_idx: null idx");
+  if (int rc = same_shape(dy, dx_accum, "maxpool3s1_bwd_idx(dx)")) return rc;
+  const long total = (long)dy.n * dy.h * dy.w * (dy.c / 8);
+  maxpool3s1_bwd_idx_kernel<<<ew_blocks(total), 256, 0, (cudaStream_t)stream>>>(
+      idx, dy.n, dy.h, dy.w, dy.c, (const __nv_bfloat16*)dy.ptr, dy.ld, (__nv_bfloat16*)dx_accum.ptr, dx_accum.ld, accumulate);
+  UBR_LAUNCH_CHECK("maxpool3s1_bwd_idx_kernel");
   return 0;
 }
 

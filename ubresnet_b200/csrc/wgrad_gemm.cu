@@ -217,7 +217,8 @@ static WPlan plan_wgrad(int grid_n, int grid_h, int grid_w, int m_ch, int n_ch, 
   pl.m_blocks = m_tile_ch / pl.mbox_c;
   pl.m_tiles = ceil_div(m_ch, 128);
   pl.nbox_c = n_ch >= 64 ? 64 : n_ch;
-  pl.nt = n_ch >= 128 ? 128 : n_ch;
+  // N tile: 128 channels where they divide the operand, else 64 (192/320/576-channel ASPP concat inputs)
+  pl.nt = (n_ch % 128 == 0) ? 128 : ((n_ch % 64 == 0) ? 64 : n_ch);
   pl.n_blocks = pl.nt / pl.nbox_c;
   pl.n_tiles = n_ch / pl.nt;
   pl.m_bytes = (uint32_t)pl.m_blocks * 128u * pl.mbox_c * 2u;
@@ -287,6 +288,8 @@ static int run_wgrad(const ubr_view& ms, const ubr_view& ns, bool n_strided, con
                      int n_valid, long sm, long st, long sn, float* dw, int accumulate, void* workspace,
                      uint64_t workspace_bytes, cudaStream_t stream) {
   UBR_REQUIRE(ntaps >= 1 && ntaps <= kWMaxTaps, "wgrad: ntaps=%d out of range", ntaps);
+  UBR_REQUIRE(ms.c <= 128 || ms.c % 128 == 0, "wgrad: M-side channels %d must be <= 128 or a multiple of 128", ms.c);
+  UBR_REQUIRE(ns.c <= 128 || ns.c % 64 == 0, "wgrad: N-side channels %d must be <= 128 or a multiple of 64", ns.c);
   WPlan pl = plan_wgrad(ms.n, ms.h, ms.w, ms.c, ns.c, ntaps);
   const uint64_t need = plan_ws_bytes(pl, ms.c, ns.c, ntaps);
   UBR_REQUIRE(workspace != nullptr && workspace_bytes >= need, "wgrad: workspace too small (%llu < %llu)",
@@ -380,6 +383,24 @@ int ubr_conv2d_wgrad(ubr_view x, ubr_view dy, int out_ch, int ksize, int stride,
   // dw is OIHW with the TRUE out_ch rows; dy.c may be padded (logits): rows >= out_ch are skipped
   return run_wgrad(dy, x, stride == 2, taps, nt, out_ch, x.c, (long)x.c * T, 1, (long)T, dw, accumulate, workspace,
                    workspace_bytes, (cudaStream_t)stream);
+}
+
+int ubr_conv2d_dilated_wgrad(ubr_view x, ubr_view dy, int out_ch, int dilation, float* dw, int accumulate,
+                             void* workspace, uint64_t workspace_bytes, void* stream) {
+  if (int rc = ensure_device()) return rc;
+  if (int rc = check_view_w(x, "conv2d_dilated_wgrad.x")) return rc;
+  if (int rc = check_view_w(dy, "conv2d_dilated_wgrad.dy")) return rc;
+  UBR_REQUIRE(dilation >= 1 && dilation <= 16, "conv2d_dilated_wgrad: dilation %d unsupported", dilation);
+  UBR_REQUIRE(dy.n == x.n && dy.h == x.h && dy.w == x.w, "conv2d_dilated_wgrad: shape mismatch");
+  UBR_REQUIRE(dw != nullptr, "conv2d_dilated_wgrad: null dw");
+  UBR_REQUIRE(out_ch >= 1 && out_ch <= dy.c, "conv2d_dilated_wgrad: out_ch=%d vs dy.c=%d", out_ch, dy.c);
+  // dw[co,ci,r,s] = sum_p dy[p,co] * x[p + d*(r-1, s-1), ci]   (3x3, stride 1, padding == dilation)
+  WTap taps[9];
+  int nt = 0;
+  for (int r = 0; r < 3; ++r)
+    for (int s = 0; s < 3; ++s) taps[nt++] = WTap{(r - 1) * dilation, (s - 1) * dilation, 0};
+  return run_wgrad(dy, x, false, taps, nt, out_ch, x.c, (long)x.c * 9, 1, 9L, dw, accumulate, workspace, workspace_bytes,
+                   (cudaStream_t)stream);
 }
 
 int ubr_deconv4s2_wgrad(ubr_view x, ubr_view dy, float* dw, int accumulate, void* workspace, uint64_t workspace_bytes,

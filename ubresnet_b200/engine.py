@@ -138,7 +138,19 @@ class Engine:
         cmax = 32 * p
         bn_ws = ops.bn_workspace(max(cmax, 16), device)
         need = 0
-        # (grid_n, grid_h, grid_w, m_ch, n_ch, taps) for every wgrad GEMM in the net
+        shapes = self._wgrad_shapes(n, h, w)
+        for s_ in shapes:
+            need = max(need, ops.wgrad_workspace_bytes(*s_))
+        wg_ws = torch.empty(need // 4 + 64, dtype=torch.float32, device=device)
+        stem_ws = torch.empty(ops.stem_wgrad_workspace_bytes(n, h, w, p) // 4 + 16, dtype=torch.float32, device=device)
+        self._ws = (bn_ws, wg_ws, stem_ws)
+        self._ws_key = key
+        return self._ws
+
+    def _wgrad_shapes(self, n, h, w):
+        """(grid_n, grid_h, grid_w, m_ch, n_ch, taps) for every weight-gradient GEMM in the net."""
+        m = self.model
+        p = m.inplanes
         pad16 = lambda v: (v + 15) // 16 * 16
         shapes = [(n, h, w, pad16(m.nkernels), p, 49), (n, h, w, 16, pad16(m.nkernels), 49)]
         for i in range(1, 6):                      # encoder stage i works at H/2^i
@@ -150,13 +162,7 @@ class Engine:
             hin, win = h // 2 ** i, w // 2 ** i
             shapes += [(n, hin, win, ci, cd, 16), (n, 2 * hin, 2 * win, cd, 2 * cd, 9), (n, 2 * hin, 2 * win, cd, cd, 9),
                        (n, 2 * hin, 2 * win, cd, 2 * cd, 1)]
-        for s_ in shapes:
-            need = max(need, ops.wgrad_workspace_bytes(*s_))
-        wg_ws = torch.empty(need // 4 + 64, dtype=torch.float32, device=device)
-        stem_ws = torch.empty(ops.stem_wgrad_workspace_bytes(n, h, w, p) // 4 + 16, dtype=torch.float32, device=device)
-        self._ws = (bn_ws, wg_ws, stem_ws)
-        self._ws_key = key
-        return self._ws
+        return shapes
 
     @staticmethod
     def _bn(y, bn, training, bn_ws):
@@ -176,6 +182,65 @@ class Engine:
                                      bn_ws, momentum=bn.momentum if bn.momentum is not None else 0.1, eps=bn.eps)
         y = ops.conv2d_fwd(x, wpk, bias, out_ch, k, stride)
         return y, self._bn(y, bn, False, bn_ws)
+
+    # ------------------------------------------------------------------ stem / head (shared with engine_aspp)
+    def _stem_fwd(self, x, x0_out, training, need_grad, bn_ws):
+        """conv1 -> bn1 -> relu1 -> pool1 (ub_uresnet.py:94-97); x0 lands in `x0_out` (the dec1 skip slice)."""
+        m = self.model
+        y0 = ops.stem_conv_fwd(x, m.conv1.weight, m.conv1.bias)
+        st0 = self._bn(y0, m.bn1, training, bn_ws)
+        x0 = ops.bn_act(y0, st0, True, out=x0_out)
+        if need_grad:
+            h0, pool_idx = ops.maxpool_fwd_idx(x0)
+        else:
+            h0, pool_idx = ops.maxpool_fwd(x0), None
+        return y0, st0, x0, h0, pool_idx
+
+    def _head_fwd(self, cur, training, need_grad, bn_ws):
+        """conv10 -> bn10 -> relu10 -> conv11 -> log-softmax (ub_uresnet.py:137-143); bumps num_batches_tracked."""
+        m = self.model
+        n, h, w = cur.n, cur.h, cur.w
+        w10 = self._pack(m.conv10, need_grad)
+        y10, st10 = self._conv_bn(cur, w10.fwd, m.conv10.bias, m.nkernels, 7, 1, m.bn10, training, bn_ws)
+        a10 = ops.bn_act(y10, st10, True)
+        w11 = self._pack(m.conv11, need_grad)
+        ncls = m.conv11.out_channels
+        ld = 4 if ncls <= 4 else 16
+        logits = torch.empty((n * h * w, ld), dtype=torch.float32, device=cur.buf.device)
+        ops.conv2d_fwd(a10, w11.fwd, m.conv11.bias, ncls, 7, 1, y_f32=logits)
+        logp = ops.logsoftmax_fwd(logits, n, ncls, h, w)
+        if training:
+            with torch.no_grad():
+                bns = [mod.num_batches_tracked for mod in m.modules()
+                       if isinstance(mod, torch.nn.BatchNorm2d) and mod.num_batches_tracked is not None]
+                if bns:
+                    torch._foreach_add_(bns, 1)
+        return y10, st10, a10, logp
+
+    def _head_bwd(self, saved, dlogp, grads, bn_ws, wg_ws):
+        """backward of the head; returns the gradient wrt the last decoder output."""
+        m = self.model
+        p = m.inplanes
+        ncls = m.conv11.out_channels
+        dl = ops.logsoftmax_bwd(saved["logp"], dlogp.float())
+        ops.conv2d_wgrad(saved["a10"], dl, ncls, 7, 1, grads[m.conv11.weight], False, wg_ws)
+        grads[m.conv11.bias].copy_(_channel_sum(dl, ncls))
+        w11 = self._pack(m.conv11, True)
+        da10 = ops.conv2d_dgrad(dl, w11.dgrad, m.nkernels, 7, 1)
+        del dl
+        dy10 = ops.bn_act_bwd(da10, saved["y10"], saved["st10"], True, bn_ws, grads[m.bn10.weight], grads[m.bn10.bias])
+        del da10
+        ops.conv2d_wgrad(saved["d1"], dy10, m.nkernels, 7, 1, grads[m.conv10.weight], False, wg_ws)
+        grads[m.conv10.bias].copy_(_channel_sum(dy10, m.nkernels))
+        w10 = self._pack(m.conv10, True)
+        return ops.conv2d_dgrad(dy10, w10.dgrad, p, 7, 1)
+
+    def _stem_bwd(self, saved, dcur, dx0, grads, bn_ws, stem_ws):
+        """x0 gets the pool gradient plus the dec1 skip gradient `dx0` (accumulated in place), then bn1 / conv1."""
+        m = self.model
+        ops.maxpool_bwd_idx(saved["pool_idx"], dcur, dx0, True)
+        dy0 = ops.bn_act_bwd(dx0, saved["y0"], saved["st0"], True, bn_ws, grads[m.bn1.weight], grads[m.bn1.bias])
+        ops.stem_conv_wgrad(saved["x"], dy0, grads[m.conv1.weight], grads[m.conv1.bias], False, stem_ws)
 
     # ------------------------------------------------------------------ forward pieces
     def _block_fwd(self, blk, x, out, training, need_grad, bn_ws):
@@ -241,13 +306,7 @@ class Engine:
             hh, ww = (h, w) if i == 1 else (h // 2 ** (i - 1), w // 2 ** (i - 1))
             cat[i] = torch.empty((n, hh, ww, 2 * cd), dtype=torch.bfloat16, device=dev)
         # ---- stem (ub_uresnet.py:94-97)
-        y0 = ops.stem_conv_fwd(x, m.conv1.weight, m.conv1.bias)
-        st0 = self._bn(y0, m.bn1, training, bn_ws)
-        x0 = ops.bn_act(y0, st0, True, out=Act(cat[1], p, p))
-        if need_grad:
-            h0, pool_idx = ops.maxpool_fwd_idx(x0)
-        else:
-            h0, pool_idx = ops.maxpool_fwd(x0), None
+        y0, st0, x0, h0, pool_idx = self._stem_fwd(x, Act(cat[1], p, p), training, need_grad, bn_ws)
         # ---- encoder (:103-107)
         recs = {}
         cur = h0
@@ -266,21 +325,7 @@ class Engine:
             dec_in[i] = cur
             cur, recs["dec%d" % i] = self._double_fwd(layer.res, Act(cat[i]), None, training, need_grad, bn_ws)
         # ---- head (:137-143)
-        w10 = self._pack(m.conv10, need_grad)
-        y10, st10 = self._conv_bn(cur, w10.fwd, m.conv10.bias, m.nkernels, 7, 1, m.bn10, training, bn_ws)
-        a10 = ops.bn_act(y10, st10, True)
-        w11 = self._pack(m.conv11, need_grad)
-        ncls = m.conv11.out_channels
-        ld = 4 if ncls <= 4 else 16
-        logits = torch.empty((n * h * w, ld), dtype=torch.float32, device=dev)
-        ops.conv2d_fwd(a10, w11.fwd, m.conv11.bias, ncls, 7, 1, y_f32=logits)
-        logp = ops.logsoftmax_fwd(logits, n, ncls, h, w)
-        if training:
-            with torch.no_grad():
-                bns = [mod.num_batches_tracked for mod in m.modules()
-                       if isinstance(mod, torch.nn.BatchNorm2d) and mod.num_batches_tracked is not None]
-                if bns:
-                    torch._foreach_add_(bns, 1)
+        y10, st10, a10, logp = self._head_fwd(cur, training, need_grad, bn_ws)
         if need_grad:
             saved.update(x=x, y0=y0, st0=st0, x0=x0, h0=h0, pool_idx=pool_idx, recs=recs, dec_in=dec_in, d1=cur, y10=y10, st10=st10,
                          a10=a10, logp=logp, shape=(n, h, w))
@@ -340,21 +385,8 @@ class Engine:
         else:
             grads = {prm: torch.empty_like(prm, dtype=torch.float32) for prm in m.parameters()}
         done = sink.stage_done if sink is not None else (lambda name: None)
-        ncls = m.conv11.out_channels
         # ---- head
-        dl = ops.logsoftmax_bwd(saved["logp"], dlogp.float())
-        ops.conv2d_wgrad(saved["a10"], dl, ncls, 7, 1, grads[m.conv11.weight], False, wg_ws)
-        grads[m.conv11.bias].copy_(_channel_sum(dl, ncls))
-        w11 = self._pack(m.conv11, True)
-        da10 = ops.conv2d_dgrad(dl, w11.dgrad, m.nkernels, 7, 1)
-        del dl
-        dy10 = ops.bn_act_bwd(da10, saved["y10"], saved["st10"], True, bn_ws, grads[m.bn10.weight], grads[m.bn10.bias])
-        del da10
-        ops.conv2d_wgrad(saved["d1"], dy10, m.nkernels, 7, 1, grads[m.conv10.weight], False, wg_ws)
-        grads[m.conv10.bias].copy_(_channel_sum(dy10, m.nkernels))
-        w10 = self._pack(m.conv10, True)
-        dcur = ops.conv2d_dgrad(dy10, w10.dgrad, p, 7, 1)
-        del dy10
+        dcur = self._head_bwd(saved, dlogp, grads, bn_ws, wg_ws)
         done("head")
         # ---- decoder, shallow to deep
         recs = saved["recs"]
@@ -377,10 +409,7 @@ class Engine:
                                     extra=extra)
             done("enc%d" % i)
         # ---- stem: x0 gets the pool gradient plus the dec1 skip gradient (accumulated in place)
-        dx0 = dskip[0]
-        ops.maxpool_bwd_idx(saved["pool_idx"], dcur, dx0, True)
-        dy0 = ops.bn_act_bwd(dx0, saved["y0"], saved["st0"], True, bn_ws, grads[m.bn1.weight], grads[m.bn1.bias])
-        ops.stem_conv_wgrad(saved["x"], dy0, grads[m.conv1.weight], grads[m.conv1.bias], False, stem_ws)
+        self._stem_bwd(saved, dcur, dskip[0], grads, bn_ws, stem_ws)
         done("stem")
         if sink is not None:
             sink.finish()

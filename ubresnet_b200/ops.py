@@ -171,6 +171,34 @@ def conv2d_wgrad(x, dy, out_ch, ksize, stride, dw, accumulate, ws):
     return dw
 
 
+def conv2d_dilated_fwd(x, wpk, bias, out_ch, dilation, y=None):
+    """3x3 stride-1 conv with padding == dilation (ASPP branches, reference models/ASPP_ResNet.py:203-214)."""
+    lib = _lib.load()
+    if y is None:
+        y = Act.empty(x.n, x.h, x.w, out_ch, x.buf.device)
+    _lib.check(lib.ubr_conv2d_dilated_fwd(x.view(), wpk.data_ptr(), _ptr(bias), out_ch, dilation, y.view(), _stream()),
+               "conv2d_dilated_fwd")
+    return y
+
+
+def conv2d_dilated_dgrad(dy, wpk, in_ch, dilation, dx=None):
+    lib = _lib.load()
+    if dx is None:
+        dx = Act.empty(dy.n, dy.h, dy.w, in_ch, dy.buf.device)
+    _lib.check(lib.ubr_conv2d_dilated_dgrad(dy.view(), wpk.data_ptr(), in_ch, dilation, dx.view(), _stream()),
+               "conv2d_dilated_dgrad")
+    return dx
+
+
+def conv2d_dilated_wgrad(x, dy, out_ch, dilation, dw, accumulate, ws):
+    lib = _lib.load()
+    assert dw.dtype == torch.float32 and dw.is_contiguous()
+    _lib.check(lib.ubr_conv2d_dilated_wgrad(x.view(), dy.view(), out_ch, dilation, dw.data_ptr(), int(accumulate),
+                                            ws.data_ptr(), ws.numel() * ws.element_size(), _stream()),
+               "conv2d_dilated_wgrad")
+    return dw
+
+
 def deconv_fwd(x, wpk, out_ch, y=None):
     lib = _lib.load()
     if y is None:
@@ -368,6 +396,23 @@ def maxpool_bwd_idx(idx, dy, dx, accumulate):
     lib = _lib.load()
     _lib.check(lib.ubr_maxpool3s2_bwd_idx(idx.data_ptr(), dy.view(), dx.view(), int(accumulate), _stream()),
                "maxpool3s2_bwd_idx")
+    return dx
+
+
+def maxpool3s1_fwd(x, y=None, want_idx=False):
+    """MaxPool2d(3, stride=1, padding=1) (ASPP block 5); returns (y, idx|None)."""
+    lib = _lib.load()
+    if y is None:
+        y = Act.empty(x.n, x.h, x.w, x.c, x.buf.device)
+    idx = torch.empty((x.n, x.h, x.w, x.c), dtype=torch.uint8, device=x.buf.device) if want_idx else None
+    _lib.check(lib.ubr_maxpool3s1_fwd(x.view(), y.view(), _ptr(idx), _stream()), "maxpool3s1_fwd")
+    return y, idx
+
+
+def maxpool3s1_bwd_idx(idx, dy, dx, accumulate):
+    lib = _lib.load()
+    _lib.check(lib.ubr_maxpool3s1_bwd_idx(idx.data_ptr(), dy.view(), dx.view(), int(accumulate), _stream()),
+               "maxpool3s1_bwd_idx")
     return dx
 
 
