@@ -128,6 +128,107 @@ def run_reference(args, rank):
 
 
 # ------------------------------------------------------------------------------------------------
+# per-kernel roofline from the profiled C-ABI calls
+# ------------------------------------------------------------------------------------------------
+def _conv_call_work(fn, a):
+    """(algorithmic FLOPs, algorithmic HBM bytes) of one conv C-ABI call from its raw arguments (Views are (n,h,w,c)).
+    FLOPs = 2*M*N*K of the contraction; bytes = each operand / result tensor once (bf16), the DESIGN.md figure."""
+    npx = lambda v: v[0] * v[1] * v[2]
+    if fn in ("ubr_conv2d_fwd", "ubr_conv2d_fwd_stats"):
+        x, out_ch, k, st = a[0], a[3], a[4], a[5]
+        m = npx(x) // (st * st)
+        return 2.0 * m * x[3] * out_ch * k * k, 2.0 * (npx(x) * x[3] + m * max(out_ch, 16))
+    if fn in ("ubr_conv2d_dgrad", "ubr_conv2d_dgrad_acc"):
+        dy, in_ch, k, st = a[0], a[2], a[3], a[4]
+        b = 2.0 * (npx(dy) * dy[3] + npx(dy) * st * st * in_ch * (2 if fn.endswith("_acc") else 1))
+        return 2.0 * npx(dy) * dy[3] * in_ch * k * k, b
+    if fn == "ubr_conv2d_wgrad":
+        x, dy, out_ch, k = a[0], a[1], a[2], a[3]
+        return 2.0 * npx(dy) * x[3] * out_ch * k * k, 2.0 * (npx(x) * x[3] + npx(dy) * dy[3])
+    if fn in ("ubr_deconv4s2_fwd", "ubr_deconv4s2_fwd_subpixel"):
+        x, out_ch = a[0], a[2]
+        return 2.0 * npx(x) * x[3] * out_ch * 16, 2.0 * (npx(x) * x[3] + 4 * npx(x) * out_ch)
+    if fn == "ubr_deconv4s2_dgrad":
+        dy, in_ch = a[0], a[2]
+        return 2.0 * (npx(dy) // 4) * dy[3] * in_ch * 16, 2.0 * (npx(dy) * dy[3] + (npx(dy) // 4) * in_ch)
+    if fn == "ubr_deconv4s2_wgrad":
+        x, dy = a[0], a[1]
+        return 2.0 * npx(x) * x[3] * dy[3] * 16, 2.0 * (npx(x) * x[3] + npx(dy) * dy[3])
+    return None
+
+
+def conv_kernel_classes(groups, nsteps):
+    """{primary kernel: per-step launches / ms / algorithmic GFLOP and GB} from TimedLib.by_kernel()."""
+    out = {}
+    for kern, calls in groups.items():
+        names = kern.split("+") if kern else []
+        if not names or names[0] not in ("conv_halo_kernel", "conv_gemm_kernel", "wgrad_halo_kernel", "wgrad_gemm_kernel"):
+            continue
+        ent = out.setdefault(names[0], {"calls": 0.0, "launches": 0.0, "ms": 0.0, "gflop": 0.0, "gbytes": 0.0})
+        for fn, a, ms in calls:
+            work = _conv_call_work(fn, a)
+            if work is None:
+                continue
+            ent["calls"] += 1.0 / nsteps
+            ent["launches"] += sum(1 for nm in names if nm == names[0]) / nsteps
+            ent["ms"] += ms / nsteps
+            ent["gflop"] += work[0] / 1e9 / nsteps
+            ent["gbytes"] += work[1] / 1e9 / nsteps
+    for ent in out.values():
+        ent["tflops"] = ent["gflop"] / ent["ms"] if ent["ms"] else None
+        ent["gbs"] = ent["gbytes"] / ent["ms"] * 1e3 if ent["ms"] else None
+    return out
+
+
+def load_traffic():
+    """per-launch DRAM traffic of the conv kernels from the committed `ncu --set full` capture (profiles/)."""
+    path = os.path.join(ROOT, "profiles", "ncu_traffic.json")
+    if os.path.isfile(path):
+        with open(path) as fh:
+            return json.load(fh)
+    return {}
+
+
+def make_roofline(klass, peaks, step_ms):
+    """`roofline` of the dominant conv kernel (largest share of the step) + the same figures for the other three."""
+    if not klass:
+        return None
+    traffic = load_traffic()
+    hbm_bound = {"conv_halo_kernel": True, "wgrad_halo_kernel": True, "conv_gemm_kernel": False, "wgrad_gemm_kernel": False}
+    desc = {"conv_halo_kernel": "halo-resident tcgen05 conv fwd/dgrad, stride 1, C<=64 at 512^2..128^2 (AI below the ridge)",
+            "wgrad_halo_kernel": "halo-resident stacked-tap tcgen05 weight gradient, stride 1, C<=64",
+            "conv_gemm_kernel": "tcgen05 implicit-GEMM conv fwd/dgrad + deconv, C>=128 and strided layers",
+            "wgrad_gemm_kernel": "tcgen05 split-K weight-gradient GEMM, C>=128 and strided layers"}
+
+    def one(name):
+        e = klass[name]
+        per_launch_ms = e["ms"] / max(e["launches"], 1.0)
+        t = traffic.get(name)
+        if hbm_bound[name]:
+            r = {"bound": "hbm", "achieved": e["gbs"], "peak": peaks["hbm_gbs"], "unit": "GB/s",
+                 "frac": e["gbs"] / peaks["hbm_gbs"], "algorithmic_bytes_per_launch": e["gbytes"] * 1e9 / max(e["launches"], 1.0)}
+        else:
+            r = {"bound": "tensor", "achieved": e["tflops"], "peak": peaks["tf_sustained"], "unit": "TFLOP/s",
+                 "frac": e["tflops"] / peaks["tf_sustained"],
+                 "algorithmic_flops_per_launch": e["gflop"] * 1e9 / max(e["launches"], 1.0)}
+        r.update(kernel="%s (%s)" % (name, desc[name]), launches_per_step=e["launches"], avg_launch_ms=per_launch_ms,
+                 share_of_step=e["ms"] / step_ms if step_ms else None,
+                 traffic=t.get("dram_bytes_per_launch") if t else None,
+                 traffic_source=t.get("source") if t else None,
+                 peak_source=peaks["source"] + (" (HBM copy bandwidth)" if hbm_bound[name] else " (bf16 sustained)"))
+        return r
+
+    order = sorted(klass, key=lambda k: -klass[k]["ms"])
+    roof = one(order[0])
+    roof["others"] = [one(k) for k in order[1:]]
+    tot_ms = sum(e["ms"] for e in klass.values())
+    tot_gf = sum(e["gflop"] for e in klass.values())
+    roof["all_conv_kernels_tflops"] = tot_gf / tot_ms if tot_ms else None
+    roof["all_conv_kernels_share_of_step"] = tot_ms / step_ms if step_ms else None
+    return roof
+
+
+# ------------------------------------------------------------------------------------------------
 # CUDA arm
 # ------------------------------------------------------------------------------------------------
 def run_own(args, rank, world, local_rank):
@@ -211,10 +312,11 @@ def run_own(args, rank, world, local_rank):
     value = world * B * args.steps / (ms * 1e-3)
     e2e = world * B * args.steps / (ms_e2e * 1e-3)
 
-    # ---- live per-kernel-class timing (CUDA events around every C-ABI call, separate short pass)
+    # ---- live per-kernel timing: CUDA events around every C-ABI call on the launching stream (separate short pass);
+    # every rank runs the extra steps (they contain the gradient all-reduce), only rank 0 records events
     roof = None
     kernels = None
-    # every rank runs the extra steps (they contain the gradient all-reduce); only rank 0 records events
+    klass = None
     nprof = 2
     prof = None
     if rank == 0:
@@ -225,31 +327,53 @@ def run_own(args, rank, world, local_rank):
     barrier()
     if rank == 0:
         summ = prof.summary()
+        groups = prof.by_kernel()
         _lib.disable_profiling()
         tot = sum(t for _, t in summ.values())
-        gemm_fns = ("ubr_conv2d_fwd", "ubr_conv2d_dgrad", "ubr_deconv4s2_fwd", "ubr_deconv4s2_dgrad")
-        wg_fns = ("ubr_conv2d_wgrad", "ubr_deconv4s2_wgrad")
-        t_fd = sum(summ[f][1] for f in gemm_fns if f in summ) / nprof
-        t_wg = sum(summ[f][1] for f in wg_fns if f in summ) / nprof
-        t_gemm = t_fd + t_wg
-        n_gemm = sum(summ[f][0] for f in gemm_fns + wg_fns if f in summ) / nprof
         peaks = load_peaks()
-        # algorithmic conv FLOPs of one step: fwd + dgrad + wgrad of every tensor-core conv (stem runs on CUDA cores)
-        gf_gemm = 3.0 * (GF_FWD - GF_STEM) * B
-        gf_wg = (GF_FWD - GF_STEM) * B
-        ach = gf_gemm / t_gemm                               # GFLOP / ms = TFLOP/s
-        roof = {"bound": "tensor",
-                "kernel": "tcgen05 conv kernels: conv_halo_kernel / conv_gemm_kernel (fwd, dgrad) + wgrad_halo_kernel / "
-                          "wgrad_gemm_kernel, %d C-ABI conv calls per step" % n_gemm,
-                "achieved": ach, "peak": peaks["tf_sustained"], "unit": "TFLOP/s", "frac": ach / peaks["tf_sustained"],
-                "traffic": None, "peak_source": peaks["source"] + " (bf16 sustained)",
-                "share_of_step": t_gemm * nprof / tot if tot else None,
-                "note": "41% of these FLOPs sit in C<=32 layers (AI 72-144 FLOP/B < ridge 213) and are HBM-bound; "
-                        "see profiles/ per-layer tables for their GB/s against the measured HBM peak",
-                "fwd_dgrad_tflops": 2.0 * (GF_FWD - GF_STEM) * B / t_fd if t_fd else None}
+        klass = conv_kernel_classes(groups, nprof)
+        roof = make_roofline(klass, peaks, tot / nprof)
         kernels = {k: {"calls_per_step": c / nprof, "ms_per_step": t / nprof} for k, (c, t) in
                    sorted(summ.items(), key=lambda kv: -kv[1][1])}
-        kernels["_wgrad_gemm_tflops"] = gf_wg / t_wg if t_wg else None
+
+    # ---- inference (eval-mode forward; BASELINE metric is "train+infer") and whole-view deploy (configs[3])
+    infer = None
+    wholeview = None
+    if not args.no_infer:
+        model.eval()
+
+        def infer_resident(i):
+            with torch.no_grad():
+                return model(resident[i % nbuf][0])
+
+        def infer_e2e(i):
+            with torch.no_grad():
+                out = model(host[i % nbuf][0].to(dev, non_blocking=True))
+                return out.argmax(1).to(torch.uint8).cpu()          # class map back on the host, every step
+
+        ms_i, l_i = timed(infer_resident, args.steps, args.warmup)
+        ms_ie, _ = timed(infer_e2e, max(2, args.steps // 2), 1)
+        infer = {"metric": "infer_crops_per_sec_512x512", "value": world * B * args.steps / (ms_i * 1e-3), "unit": UNIT,
+                 "ms_per_step": ms_i / args.steps, "gpu_launches": int(l_i),
+                 "e2e": {"value": world * B * max(2, args.steps // 2) / (ms_ie * 1e-3), "unit": UNIT,
+                         "h2d_bytes_per_step": host[0][0].numel() * 4 * world, "d2h_bytes_per_step": B * S * S * world},
+                 "conv_tflops": GF_FWD * B * args.steps / (ms_i * 1e-3) / 1e3}
+        if S == 512:
+            from ubresnet_b200.deploy import wholeview as wv
+            planes = synthetic.make_wholeview(seed=synthetic.BASE_SEED + rank, rows=1008, cols=3456, planes=3).pin_memory()
+            nev = max(2, args.steps // 2)
+
+            def event(i):
+                out = wv.run_event(model, planes, crop=512, batch=14)
+                return out.argmax(1).to(torch.uint8).cpu()           # stitched class maps (3, 1008, 3456) to the host
+
+            ms_w, l_w = timed(event, nev, 1)
+            wholeview = {"metric": "wholeview_events_per_sec", "value": world * nev / (ms_w * 1e-3), "unit": "events/s",
+                         "crops_per_sec": world * nev * 42 / (ms_w * 1e-3), "ms_per_event": ms_w / nev,
+                         "workload": "3 planes 1008x3456 -> 42 overlapping 512x512 crops -> eval forward -> stitch; "
+                                     "events sharded round-robin over ranks (no collective); host planes in, host "
+                                     "class maps out", "gpu_launches_per_event": int(l_w / nev)}
+        model.train()
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
@@ -278,6 +402,12 @@ def run_own(args, rank, world, local_rank):
             line["roofline"] = roof
         if cpu:
             line["cpu_baseline"] = cpu
+        if infer:
+            line["infer"] = infer
+        if wholeview:
+            line["wholeview"] = wholeview
+        if klass:
+            line["conv_kernels"] = klass
         if kernels and args.verbose:
             line["kernels"] = kernels
         print(json.dumps(line), flush=True)
@@ -296,6 +426,7 @@ def main():
     ap.add_argument("--size", type=int, default=512)
     ap.add_argument("--cpu-batch", type=int, default=4, help="crops per CPU step (bounded sample)")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-infer", action="store_true", help="skip the eval-forward and whole-view measurements")
     ap.add_argument("--verbose", action="store_true")
     ap.add_argument("--kernel-log", default="")
     args = ap.parse_args()

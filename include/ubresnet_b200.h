@@ -44,6 +44,10 @@ const char* ubr_last_error(void);
 int ubr_device_check(void);               /* 0 iff the current CUDA device is sm_100 (B200) */
 int ubr_sync_check(void* stream);         /* cudaStreamSynchronize + surface async errors */
 uint64_t ubr_launch_count(void);          /* kernels launched by this library so far (process wide) */
+/* profiling aid (bench.py): when enabled, ubr_take_kernel_names() returns "k1+k2" = the kernels the calling thread
+ * launched since the previous take (thread-local buffer, valid until the next take) */
+void ubr_trace_kernels(int enable);
+const char* ubr_take_kernel_names(void);
 
 /* ---- weight packing: fp32 reference layout -> bf16 [tap][n][k] GEMM operand ---------------------
  * replaces the implicit cuDNN filter transforms behind nn.Conv2d / nn.ConvTranspose2d.
@@ -193,6 +197,12 @@ int ubr_tile_gather(const float* plane, int rows, int cols, const int32_t* origi
                     float* crops, void* stream);
 int ubr_stitch_scatter(const float* tiles /* [ntiles,c,crop,crop] */, int nch, const int32_t* origins, int ntiles,
                        int crop, int rows, int cols, float* out /* [c,rows,cols] */, void* stream);
+
+/* ---- accuracy counters: replaces the 2*C `.item()` reductions of `accuracy()` (reference
+ * training/train_ubresnet2018_wlarcv2.py:509-566).  pred = argmax over classes of logp (NCHW fp32, first maximum);
+ * counts[c] = #pixels with target == c, counts[ncls + c] = #of those predicted correctly.  counts (2*ncls uint64,
+ * device) is zeroed by the call.  Targets outside [0, ncls) are not counted. */
+int ubr_accuracy_counts(const float* logp, const int64_t* target, int n, int ncls, int hw, uint64_t* counts, void* stream);
 
 /* ---- flat-buffer helpers for the data-parallel gradient buckets --------------------------------- */
 int ubr_scale_f32(float* buf, uint64_t count, float alpha, void* stream);

@@ -121,3 +121,21 @@ def load_reference_aspp():
 def make_reference_aspp_model(num_classes=3, in_channels=1, inplanes=16):
     return load_reference_aspp().ASPP_ResNet(num_classes=num_classes, in_channels=in_channels, inplanes=inplanes,
                                              showsizes=False)
+
+
+def load_reference_accuracy(script="training/train_ubresnet2018_wlarcv2.py"):
+    """The reference `accuracy()` function, cut out of the (un-importable: ROOT, larcv, py2) training script TEXT
+    (train_ubresnet2018_wlarcv2.py:509-566 / train_ubresnet2018_wlarcv1.py:528-586) and exec'd with the print shim."""
+    key = "acc:" + script
+    if key in _cache:
+        return _cache[key]
+    import time
+    import torch
+    with open(os.path.join(REFERENCE_ROOT, script), "r") as fh:
+        text = fh.read()
+    m = re.search(r"^def accuracy\(.*?(?=^def )", text, re.S | re.M)
+    body = _PRINT_RE.sub(r"\1print(\2)", m.group(0))
+    ns = {"torch": torch, "time": time}
+    exec(compile(body, os.path.join(REFERENCE_ROOT, script), "exec"), ns)
+    _cache[key] = ns["accuracy"]
+    return _cache[key]

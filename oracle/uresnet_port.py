@@ -220,6 +220,30 @@ def train_step_grads(sd, x, target, pixelweights, class_weight=None, quant=False
     return loss.detach(), logp.detach(), grads, work
 
 
+def accuracy_counts(output, target):
+    """[pixels per class | correct pixels per class] (2*C ints) behind `accuracy()`
+    (training/train_ubresnet2018_wlarcv2.py:519-547: pred = output.max(1), correct = pred.eq(target), per-class sums)."""
+    pred = output.max(1)[1]
+    tgt = target.reshape(pred.shape)
+    ncls = output.size(1)
+    num = [int((tgt == c).sum()) for c in range(ncls)]
+    corr = [int(((pred == tgt) & (tgt == c)).sum()) for c in range(ncls)]
+    return num + corr
+
+
+def accuracy(output, target, nonzero=False):
+    """percent accuracies: per class (0.0 if absent), total (:552-561); nonzero adds the track+shower value of
+    training/train_ubresnet2018_wlarcv1.py:583."""
+    ncls = output.size(1)
+    cnt = accuracy_counts(output, target)
+    num, corr = cnt[:ncls], cnt[ncls:]
+    res = [100.0 * corr[c] / num[c] if num[c] > 0 else 0.0 for c in range(ncls)]
+    res.append(100.0 * float(sum(corr)) / sum(num))
+    if nonzero:
+        res.append(100.0 * float(corr[1] + corr[2]) / (num[1] + num[2]))
+    return res
+
+
 # ----------------------------------------------------------------------------------------------
 # whole-view tiling (numpy restatement; SURVEY.md 8c: builder-defined plan, slice + overwrite)
 # ----------------------------------------------------------------------------------------------

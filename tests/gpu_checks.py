@@ -438,6 +438,23 @@ def check_loss(n, ncls, h, w, seed=0, classw=False):
             (name + "_dlogits_pad", dl_nchw[:, ncls:].abs().max().item(), 0.0)]
 
 
+def check_accuracy(n, ncls, h, w, seed=0):
+    """fused argmax + per-class counters (ubr_accuracy_counts) against the oracle restatement: integer exact."""
+    from oracle import uresnet_port as port
+    from ubresnet_b200.training.accuracy import accuracy
+    name = "accuracy_n%d_c%d_%dx%d" % (n, ncls, h, w)
+    g = torch.Generator().manual_seed(seed)
+    logp = torch.log_softmax(bf(torch.randn(n, ncls, h, w, generator=g)), 1)      # bf16-rounded: exact ties occur
+    tgt = torch.randint(0, ncls, (n, h, w), generator=g)
+    tgt[0, :2, :5] = -100
+    cnt = ops.accuracy_counts(logp.to(DEV), tgt.to(DEV)).cpu().tolist()
+    ref = port.accuracy_counts(logp, tgt)
+    acc = accuracy(logp.to(DEV), tgt.to(DEV), nonzero=True)
+    acc_ref = port.accuracy(logp, tgt, nonzero=True)
+    return [(name + "_counts", float(sum(abs(a - b) for a, b in zip(cnt, ref))), 0.0),
+            (name + "_percent", max(abs(a - b) for a, b in zip(acc, acc_ref)), 1e-9)]
+
+
 def check_tiling(rows=208, cols=400, crop=64, seed=0):
     import numpy as np
     from oracle import uresnet_port as port
@@ -484,6 +501,7 @@ CHECKS = {
     "stem": lambda: check_stem(2, 64, 64) + check_stem(1, 40, 72, oc=32, seed=4),
     "loss": lambda: check_loss(2, 3, 32, 32) + check_loss(2, 4, 16, 48, seed=3, classw=True),
     "tiling": lambda: check_tiling(),
+    "accuracy": lambda: check_accuracy(2, 3, 64, 96) + check_accuracy(3, 4, 33, 17, seed=5),
     # tensor-core forward: each swizzle mode / K-chunk count / N-tile count / stride / kernel size
     "conv_fwd_c64": lambda: check_conv_fwd(64, 64, 3, 1, 2, 16, 16),
     "conv_fwd_c16": lambda: check_conv_fwd(16, 32, 3, 1, 2, 32, 32),

@@ -197,3 +197,22 @@ def test_aspp_port_matches_golden():
     with torch.no_grad():
         le = aspp_port.forward(after, gold["image"], training=False)
     assert _rel(le, gold["logp_eval"]) < 1e-3
+
+
+@needs_ref
+@pytest.mark.parametrize("script,nonzero", [("training/train_ubresnet2018_wlarcv2.py", False),
+                                            ("training/train_ubresnet2018_wlarcv1.py", True)])
+def test_accuracy_port_matches_reference(script, nonzero):
+    ref_acc = shim.load_reference_accuracy(script)
+    g = torch.Generator().manual_seed(21)
+    out = torch.log_softmax(torch.randn(2, 3, 24, 40, generator=g), 1)
+    tgt = torch.randint(0, 3, (2, 24, 40), generator=g)
+    a = ref_acc(out, tgt.clone(), None) if nonzero else ref_acc(out, tgt.clone())
+    b = port.accuracy(out, tgt, nonzero=nonzero)
+    assert len(a) == len(b) == (5 if nonzero else 4)
+    for x, y in zip(a, b):
+        assert abs(float(x) - y) < 1e-4, (a, b)
+    # absent class -> 0.0 (reference :553-556)
+    tgt2 = tgt.clamp(max=1)
+    a2 = ref_acc(out, tgt2.clone(), None) if nonzero else ref_acc(out, tgt2.clone())
+    assert float(a2[2]) == port.accuracy(out, tgt2, nonzero=nonzero)[2] == 0.0

@@ -1,0 +1,21 @@
+#!/bin/bash
+# ncu evidence for one training step of bench.py (run on the GPU box, after the plain bench has exited 0):
+#   1. launch list (gpu__time_duration) of the whole short run
+#   2. DRAM traffic + tensor-pipe activity of EVERY conv kernel launch (metrics-only pass, same counters as --set full)
+#   3. --set full capture of a few launches of each tcgen05 conv kernel (source-level detail), exported as CSV
+# usage: tools/profile_step.sh <tag>      (outputs under gpurun_out/<tag>_*)
+set -u
+TAG=${1:-prof}
+OUT=gpurun_out
+CMD="python bench.py --steps 1 --warmup 1 --no-cpu --no-infer"
+mkdir -p $OUT
+timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 6000 --csv --log-file $OUT/${TAG}_launches.csv $CMD > $OUT/${TAG}_ncu_list.log 2>&1
+echo "launch list rc=$?"
+M=gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum,sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active,sm__throughput.avg.pct_of_peak_sustained_elapsed,gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed,lts__t_sector_hit_rate.pct
+timeout 900 ncu --metrics $M --clock-control none -k regex:"conv_gemm_kernel|wgrad_gemm_kernel|halo_kernel" -c 2000 --csv --log-file $OUT/${TAG}_conv_traffic.csv $CMD > $OUT/${TAG}_ncu_traffic.log 2>&1
+echo "traffic pass rc=$?"
+timeout 600 ncu --set full --clock-control none --import-source on -k regex:"conv_gemm_kernel|wgrad_gemm_kernel" --launch-skip 290 -c 10 -o /tmp/${TAG}_gemm_full $CMD > $OUT/${TAG}_ncu_full.log 2>&1
+echo "set full rc=$?"
+ncu -i /tmp/${TAG}_gemm_full.ncu-rep --page raw --csv > $OUT/${TAG}_gemm_full_raw.csv 2>/dev/null
+ncu -i /tmp/${TAG}_gemm_full.ncu-rep --page details --csv > $OUT/${TAG}_gemm_full_details.csv 2>/dev/null
+ls -la $OUT

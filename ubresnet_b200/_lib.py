@@ -24,6 +24,8 @@ SIGNATURES = {
     "ubr_device_check": (_i, []),
     "ubr_sync_check": (_i, [_vp]),
     "ubr_launch_count": (_u64, []),
+    "ubr_trace_kernels": (None, [_i]),
+    "ubr_take_kernel_names": (C.c_char_p, []),
     "ubr_pack_weights": (_i, [_vp, _i, _i, _i, _i, _i, _i, _i, _i, _vp, _vp]),
     "ubr_pack_weights_batch": (_i, [_vp, _i, _vp]),
     "ubr_conv2d_fwd": (_i, [View, _vp, _vp, _i, _i, _i, View, _vp, _i, _vp]),
@@ -68,6 +70,7 @@ SIGNATURES = {
     "ubr_pixelwise_nll_bwd": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i64, _vp, _vp]),
     "ubr_tile_gather": (_i, [_vp, _i, _i, _vp, _i, _i, _vp, _vp]),
     "ubr_stitch_scatter": (_i, [_vp, _i, _vp, _i, _i, _i, _i, _vp, _vp]),
+    "ubr_accuracy_counts": (_i, [_vp, _vp, _i, _i, _i, _vp, _vp]),
     "ubr_scale_f32": (_i, [_vp, _u64, _f, _vp]),
 }
 
@@ -95,36 +98,50 @@ def load():
 
 
 class TimedLib:
-    """Profiling proxy: brackets every C-ABI call with CUDA events on the launching (current) stream.
-    Used by bench.py for the live per-kernel-class timings behind the `roofline` object."""
+    """Profiling proxy: brackets every C-ABI call with CUDA events on the launching (current) stream and notes which
+    kernels the call launched (ubr_take_kernel_names) plus its View / integer arguments.
+    Used by bench.py for the live per-kernel timings behind the `roofline` object."""
+
+    _SKIP = ("ubr_last_error", "ubr_abi_version", "ubr_launch_count", "ubr_trace_kernels", "ubr_take_kernel_names")
 
     def __init__(self, lib):
         self._lib = lib
-        self.records = []          # (function name, start event, end event)
+        self.records = []          # (function name, start event, end event, kernel names, args summary)
+        lib.ubr_trace_kernels(1)
 
     def __getattr__(self, name):
         fn = getattr(self._lib, name)
-        if not name.startswith("ubr_") or name in ("ubr_last_error", "ubr_abi_version", "ubr_launch_count") \
-                or name.endswith("_bytes"):
+        if not name.startswith("ubr_") or name in self._SKIP or name.endswith("_bytes"):
             return fn
         import torch
+        take = self._lib.ubr_take_kernel_names
 
         def timed(*args):
             e0 = torch.cuda.Event(enable_timing=True)
             e1 = torch.cuda.Event(enable_timing=True)
+            take()
             e0.record()
             rc = fn(*args)
             e1.record()
-            self.records.append((name, e0, e1))
+            kern = take().decode("ascii", "replace")
+            summ = tuple((a.n, a.h, a.w, a.c) if isinstance(a, View) else a for a in args)      # positional, raw
+            self.records.append((name, e0, e1, kern, summ))
             return rc
         return timed
 
     def summary(self):
         """{function name: (calls, total ms)} -- call after torch.cuda.synchronize()."""
         out = {}
-        for name, e0, e1 in self.records:
+        for name, e0, e1, _, _ in self.records:
             c, t = out.get(name, (0, 0.0))
             out[name] = (c + 1, t + e0.elapsed_time(e1))
+        return out
+
+    def by_kernel(self):
+        """{kernel names launched by one call ("a+b"): [(function, args summary, ms), ...]}."""
+        out = {}
+        for name, e0, e1, kern, summ in self.records:
+            out.setdefault(kern, []).append((name, summ, e0.elapsed_time(e1)))
         return out
 
 
@@ -139,6 +156,7 @@ def enable_profiling():
 def disable_profiling():
     global _lib
     if isinstance(_lib, TimedLib):
+        _lib._lib.ubr_trace_kernels(0)
         _lib = _lib._lib
 
 

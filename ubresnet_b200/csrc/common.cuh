@@ -18,9 +18,9 @@ int cuda_fail(cudaError_t e, const char* what);      // records + returns UBR_E_
 #define UBR_REQUIRE(cond, ...)                                         \
   do { if (!(cond)) { ::ubr::set_error(__VA_ARGS__); return UBR_E_BADARG; } } while (0)
 #define UBR_LAUNCH_CHECK(name)                                         \
-  do { ::ubr::count_launch(); cudaError_t _e = cudaGetLastError();     \
+  do { ::ubr::count_launch(name); cudaError_t _e = cudaGetLastError();     \
        if (_e != cudaSuccess) return ::ubr::cuda_fail(_e, name); } while (0)
-void count_launch();            // every kernel launch of this library is counted (ubr_launch_count)
+void count_launch(const char* name);          // every kernel launch of this library is counted (ubr_launch_count)
 
 int ensure_device();            // 0 if current device is sm_100; else UBR_E_UNSUPPORTED
 int sm_count();

@@ -200,6 +200,36 @@ static inline unsigned blocks_for(long total) {
   return (unsigned)nb;
 }
 
+// ------------------------------------------------------------------ accuracy counters
+// pred = argmax_c logp[b,c,pixel] (first maximum, as torch.max); counts[c] += (target == c),
+// counts[ncls + c] += (target == c && pred == c).  Integer counters: exact and order independent.
+constexpr int kAccMaxCls = 16;
+__global__ void __launch_bounds__(256) accuracy_counts_kernel(const float* __restrict__ logp,
+                                                              const long long* __restrict__ target, int n, int ncls,
+                                                              int hw, unsigned long long* __restrict__ counts) {
+  __shared__ unsigned int s_cnt[2 * kAccMaxCls];
+  if (threadIdx.x < 2 * kAccMaxCls) s_cnt[threadIdx.x] = 0u;
+  __syncthreads();
+  const long total = (long)n * hw;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+    const long b = i / hw, px = i % hw;
+    const float* lp = logp + b * (long)ncls * hw + px;
+    float best = lp[0];
+    int arg = 0;
+    for (int c = 1; c < ncls; ++c) {
+      const float v = lp[(long)c * hw];
+      if (v > best) { best = v; arg = c; }
+    }
+    const long long t = target[i];
+    if (t >= 0 && t < ncls) {
+      atomicAdd(&s_cnt[(int)t], 1u);
+      if (arg == (int)t) atomicAdd(&s_cnt[ncls + (int)t], 1u);
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x < 2 * ncls && s_cnt[threadIdx.x]) atomicAdd(&counts[threadIdx.x], (unsigned long long)s_cnt[threadIdx.x]);
+}
+
 }  // namespace ubr
 
 using namespace ubr;
@@ -303,6 +333,20 @@ int ubr_stitch_scatter(const float* tiles, int nch, const int32_t* origins, int 
   stitch_scatter_kernel<<<blocks_for((long)rows * cols), 256, 0, (cudaStream_t)stream>>>(tiles, nch, origins, ntiles,
                                                                                          crop, rows, cols, out);
   UBR_LAUNCH_CHECK("stitch_scatter_kernel");
+  return 0;
+}
+
+int ubr_accuracy_counts(const float* logp, const int64_t* target, int n, int ncls, int hw, uint64_t* counts, void* stream) {
+  if (int rc = ensure_device()) return rc;
+  UBR_REQUIRE(logp != nullptr && target != nullptr && counts != nullptr, "accuracy_counts: null pointer");
+  UBR_REQUIRE(n > 0 && hw > 0 && ncls >= 1 && ncls <= kAccMaxCls, "accuracy_counts: bad extents n=%d ncls=%d hw=%d", n, ncls, hw);
+  UBR_CUDA_OK(cudaMemsetAsync(counts, 0, 2 * (size_t)ncls * sizeof(uint64_t), (cudaStream_t)stream));
+  const long total = (long)n * hw;
+  long nb = (total + 255) / 256;
+  if (nb > 148 * 8) nb = 148 * 8;
+  accuracy_counts_kernel<<<(unsigned)nb, 256, 0, (cudaStream_t)stream>>>(logp, (const long long*)target, n, ncls, hw,
+                                                                       (unsigned long long*)counts);
+  UBR_LAUNCH_CHECK("accuracy_counts_kernel");
   return 0;
 }
 

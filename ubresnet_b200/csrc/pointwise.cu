@@ -7,6 +7,7 @@ namespace ubr {
 
 constexpr int kRedBlocks = 592;      // 4 x 148 SMs: partial rows of every reduction workspace
 constexpr int kRedThreads = 256;
+constexpr int kBwdRedBlocks = 296;   // 2 x 148: the backward reduce kernels keep 2 CTAs (x4 / x2 pixels in flight) per SM
 
 struct DView {
   const __nv_bfloat16* ptr;
@@ -24,6 +25,12 @@ static inline DViewW dvw(const ubr_view& v) { return DViewW{(__nv_bfloat16*)v.pt
 
 __device__ __forceinline__ void load8(const __nv_bfloat16* p, float (&f)[8]) {
   const uint4 u = *reinterpret_cast<const uint4*>(p);
+  float2 a = unpack_bf16x2(u.x), b = unpack_bf16x2(u.y), c = unpack_bf16x2(u.z), d = unpack_bf16x2(u.w);
+  f[0] = a.x; f[1] = a.y; f[2] = b.x; f[3] = b.y; f[4] = c.x; f[5] = c.y; f[6] = d.x; f[7] = d.y;
+}
+// raw 16-byte load kept packed while in flight (4 registers instead of 8), unpacked at the point of use
+__device__ __forceinline__ uint4 ldraw(const __nv_bfloat16* p) { return *reinterpret_cast<const uint4*>(p); }
+__device__ __forceinline__ void unpack8(const uint4& u, float (&f)[8]) {
   float2 a = unpack_bf16x2(u.x), b = unpack_bf16x2(u.y), c = unpack_bf16x2(u.z), d = unpack_bf16x2(u.w);
   f[0] = a.x; f[1] = a.y; f[2] = b.x; f[3] = b.y; f[4] = c.x; f[5] = c.y; f[6] = d.x; f[7] = d.y;
 }
@@ -66,10 +73,21 @@ __device__ __forceinline__ void block_reduce_store(float (&acc)[NS][8], int c, f
   }
 }
 
-static inline int red_blocks(long npix, int c) {
+// Streaming kernels: a thread owns ONE channel group (8 channels; per-channel parameters live in registers) and walks
+// pixels p0, p0 + ps, ... with U independent 16-byte loads per tensor in flight.  HBM latency under load is ~1.5 us
+// (profiles/r01_ubench_tma_mma_desc.txt T1), so ~64 KB must be in flight per SM to reach the copy bandwidth; the grid
+// is sized so that (threads x cgs) tiles evenly (gridDim * blockDim is a multiple of cgs).
+struct EwIdx { int cg; long p0, ps; };
+__device__ __forceinline__ EwIdx ew_index(int cgs) {
+  const long g = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  const long t = (long)gridDim.x * blockDim.x;
+  return EwIdx{(int)(g % cgs), g / cgs, t / cgs};
+}
+
+static inline int red_blocks(long npix, int c, int cap = kRedBlocks) {
   const int lanes = kRedThreads / (c >> 3);
   long nb = (npix + (long)lanes * 8 - 1) / ((long)lanes * 8);
-  if (nb > kRedBlocks) nb = kRedBlocks;
+  if (nb > cap) nb = cap;
   if (nb < 1) nb = 1;
   return (int)nb;
 }
@@ -78,14 +96,24 @@ static inline int red_blocks(long npix, int c) {
 __global__ void __launch_bounds__(kRedThreads) bn_stats_kernel(DView y, float* partials) {
   const int cgs = y.c >> 3, lanes = blockDim.x / cgs;
   const int cg = threadIdx.x % cgs, pl = threadIdx.x / cgs;
+  const long ps = (long)gridDim.x * lanes;
   float acc[2][8];
 #pragma unroll
   for (int j = 0; j < 8; ++j) { acc[0][j] = 0.f; acc[1][j] = 0.f; }
-  for (long p = (long)blockIdx.x * lanes + pl; p < y.npix; p += (long)gridDim.x * lanes) {
-    float f[8];
-    load8(y.ptr + p * y.ld + cg * 8, f);
+  for (long p = (long)blockIdx.x * lanes + pl; p < y.npix; p += 4 * ps) {
+    uint4 rf[4];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) { acc[0][j] += f[j]; acc[1][j] = fmaf(f[j], f[j], acc[1][j]); }
+    for (int u = 0; u < 4; ++u) {
+      const long q = p + u * ps;
+      rf[u] = q < y.npix ? ldraw(y.ptr + q * y.ld + cg * 8) : make_uint4(0u, 0u, 0u, 0u);
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      float f[8];
+      unpack8(rf[u], f);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) { acc[0][j] += f[j]; acc[1][j] = fmaf(f[j], f[j], acc[1][j]); }
+    }
   }
   block_reduce_store<2>(acc, y.c, partials);
 }
@@ -153,76 +181,114 @@ __global__ void bn_eval_affine_kernel(int c, const float* gamma, const float* be
 }
 
 // ------------------------------------------------------------------ BN apply (+ReLU), block tail
-__global__ void __launch_bounds__(256) bn_act_kernel(DView y, const float* scale, const float* shift, int relu,
-                                                     DViewW out) {
-  const int cgs = y.c >> 3;
-  const long total = y.npix * cgs;
-  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
-    const long p = i / cgs;
-    const int cg = (int)(i % cgs);
-    float f[8], sc[8], sh[8];
-    load8(y.ptr + p * y.ld + cg * 8, f);
-    ldparam8(scale, cg * 8, sc);
-    ldparam8(shift, cg * 8, sh);
+__global__ void __launch_bounds__(256, 2) bn_act_kernel(DView y, const float* scale, const float* shift, int relu,
+                                                        DViewW out) {
+  const EwIdx ix = ew_index(y.c >> 3);
+  float sc[8], sh[8];
+  ldparam8(scale, ix.cg * 8, sc);
+  ldparam8(shift, ix.cg * 8, sh);
+  const float lo = relu ? 0.f : -INFINITY;
+  for (long p = ix.p0; p < y.npix; p += 4 * ix.ps) {
+    uint4 rf[4];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      f[j] = fmaf(f[j], sc[j], sh[j]);
-      if (relu) f[j] = fmaxf(f[j], 0.f);
+    for (int u = 0; u < 4; ++u) {
+      const long q = p + u * ix.ps;
+      if (q < y.npix) rf[u] = ldraw(y.ptr + q * y.ld + ix.cg * 8);
     }
-    store8(out.ptr + p * out.ld + cg * 8, f);
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const long q = p + u * ix.ps;
+      if (q < y.npix) {
+        float f[8];
+        unpack8(rf[u], f);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) f[j] = fmaxf(fmaf(f[j], sc[j], sh[j]), lo);
+        store8(out.ptr + q * out.ld + ix.cg * 8, f);
+      }
+    }
   }
 }
 
 // out = relu( relu(y2*s2+b2) + (res*sr+br | res) )
-__global__ void __launch_bounds__(256) block_tail_kernel(DView y2, const float* s2, const float* b2, DView res,
-                                                         const float* sr, const float* br, DViewW out) {
-  const int cgs = y2.c >> 3;
-  const long total = y2.npix * cgs;
-  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
-    const long p = i / cgs;
-    const int cg = (int)(i % cgs);
-    float f[8], r[8], a[8], b[8];
-    load8(y2.ptr + p * y2.ld + cg * 8, f);
-    load8(res.ptr + p * res.ld + cg * 8, r);
-    ldparam8(s2, cg * 8, a);
-    ldparam8(b2, cg * 8, b);
+__global__ void __launch_bounds__(256, 2) block_tail_kernel(DView y2, const float* s2, const float* b2, DView res,
+                                                            const float* sr, const float* br, DViewW out) {
+  const EwIdx ix = ew_index(y2.c >> 3);
+  float a2[8], c2[8], ar[8], cr[8];
+  ldparam8(s2, ix.cg * 8, a2);
+  ldparam8(b2, ix.cg * 8, c2);
+  if (sr) { ldparam8(sr, ix.cg * 8, ar); ldparam8(br, ix.cg * 8, cr); }
+  else {
 #pragma unroll
-    for (int j = 0; j < 8; ++j) f[j] = fmaxf(fmaf(f[j], a[j], b[j]), 0.f);
-    if (sr) {
-      ldparam8(sr, cg * 8, a);
-      ldparam8(br, cg * 8, b);
+    for (int j = 0; j < 8; ++j) { ar[j] = 1.f; cr[j] = 0.f; }
+  }
+  for (long p = ix.p0; p < y2.npix; p += 4 * ix.ps) {
+    uint4 rf[4], rr4[4];
 #pragma unroll
-      for (int j = 0; j < 8; ++j) r[j] = fmaf(r[j], a[j], b[j]);
+    for (int u = 0; u < 4; ++u) {
+      const long q = p + u * ix.ps;
+      if (q < y2.npix) {
+        rf[u] = ldraw(y2.ptr + q * y2.ld + ix.cg * 8);
+        rr4[u] = ldraw(res.ptr + q * res.ld + ix.cg * 8);
+      }
     }
 #pragma unroll
-    for (int j = 0; j < 8; ++j) f[j] = fmaxf(f[j] + r[j], 0.f);
-    store8(out.ptr + p * out.ld + cg * 8, f);
+    for (int u = 0; u < 4; ++u) {
+      const long q = p + u * ix.ps;
+      if (q < y2.npix) {
+        float f[8], r[8];
+        unpack8(rf[u], f);
+        unpack8(rr4[u], r);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float z = fmaxf(fmaf(f[j], a2[j], c2[j]), 0.f);
+          const float rr = sr ? fmaf(r[j], ar[j], cr[j]) : r[j];
+          f[j] = fmaxf(z + rr, 0.f);
+        }
+        store8(out.ptr + q * out.ld + ix.cg * 8, f);
+      }
+    }
   }
 }
 
 // ------------------------------------------------------------------ BN(+ReLU) backward
 // reduce: sums[0] = sum dz, sums[1] = sum dz*xhat
-__global__ void __launch_bounds__(kRedThreads) bn_act_bwd_reduce_kernel(DView dout, DView y, const float* scale,
-                                                                        const float* shift, const float* mean,
-                                                                        const float* invstd, int relu, float* partials) {
+__global__ void __launch_bounds__(kRedThreads, 2) bn_act_bwd_reduce_kernel(DView dout, DView y, const float* scale,
+                                                                           const float* shift, const float* mean,
+                                                                           const float* invstd, int relu, float* partials) {
   const int cgs = y.c >> 3, lanes = blockDim.x / cgs;
   const int cg = threadIdx.x % cgs, pl = threadIdx.x / cgs;
+  const long ps = (long)gridDim.x * lanes;
   float sc[8], sh[8], mu[8], is[8];
   ldparam8(scale, cg * 8, sc); ldparam8(shift, cg * 8, sh);
   ldparam8(mean, cg * 8, mu); ldparam8(invstd, cg * 8, is);
   float acc[2][8];
 #pragma unroll
   for (int j = 0; j < 8; ++j) { acc[0][j] = 0.f; acc[1][j] = 0.f; }
-  for (long p = (long)blockIdx.x * lanes + pl; p < y.npix; p += (long)gridDim.x * lanes) {
-    float g[8], v[8];
-    load8(dout.ptr + p * dout.ld + cg * 8, g);
-    load8(y.ptr + p * y.ld + cg * 8, v);
+  for (long p = (long)blockIdx.x * lanes + pl; p < y.npix; p += 4 * ps) {
+    uint4 rg[4], rv[4];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      const float z = fmaf(v[j], sc[j], sh[j]);
-      const float dz = (!relu || z > 0.f) ? g[j] : 0.f;
-      acc[0][j] += dz;
-      acc[1][j] = fmaf(dz, (v[j] - mu[j]) * is[j], acc[1][j]);
+    for (int u = 0; u < 4; ++u) {
+      const long q = p + u * ps;
+      if (q < y.npix) {
+        rg[u] = ldraw(dout.ptr + q * dout.ld + cg * 8);
+        rv[u] = ldraw(y.ptr + q * y.ld + cg * 8);
+      } else {
+        rg[u] = make_uint4(0u, 0u, 0u, 0u);
+        rv[u] = make_uint4(0u, 0u, 0u, 0u);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      float g[8], v[8];
+      unpack8(rg[u], g);
+      unpack8(rv[u], v);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float z = fmaf(v[j], sc[j], sh[j]);
+        const float dz = (!relu || z > 0.f) ? g[j] : 0.f;
+        acc[0][j] += dz;
+        acc[1][j] = fmaf(dz, (v[j] - mu[j]) * is[j], acc[1][j]);
+      }
     }
   }
   block_reduce_store<2>(acc, y.c, partials);
@@ -243,32 +309,52 @@ __global__ void param_grad_kernel(const float* sums, int c, int off_dz, int off_
   if (dbeta) dbeta[ch] = (accumulate ? dbeta[ch] : 0.f) + sums[off_dz * c + ch];
 }
 
-__global__ void __launch_bounds__(256) bn_act_bwd_apply_kernel(DView dout, DView y, const float* scale,
-                                                               const float* shift, const float* mean,
-                                                               const float* invstd, const float* gamma, int relu,
-                                                               const float* sums, float inv_count, DViewW dy) {
-  const int cgs = y.c >> 3;
-  const long total = y.npix * cgs;
-  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
-    const long p = i / cgs;
-    const int cg = (int)(i % cgs);
-    float g[8], v[8], sc[8], sh[8], mu[8], is[8], s0[8], s1[8];
-    load8(dout.ptr + p * dout.ld + cg * 8, g);
-    load8(y.ptr + p * y.ld + cg * 8, v);
-    ldparam8(scale, cg * 8, sc); ldparam8(shift, cg * 8, sh);
-    ldparam8(mean, cg * 8, mu); ldparam8(invstd, cg * 8, is);
-    ldparam8(sums, cg * 8, s0); ldparam8(sums + y.c, cg * 8, s1);
-    float o[8];
+// dy = scale * (dz - S0/N - xhat * S1/N) with xhat = (y - mean) * invstd, regrouped per channel as
+// dy = scale * dz + A * y + B,  A = -scale * invstd * S1/N,  B = -scale * S0/N - A * mean   (gamma*invstd == scale)
+__global__ void __launch_bounds__(256, 2) bn_act_bwd_apply_kernel(DView dout, DView y, const float* scale,
+                                                                  const float* shift, const float* mean,
+                                                                  const float* invstd, const float* gamma, int relu,
+                                                                  const float* sums, float inv_count, DViewW dy) {
+  const EwIdx ix = ew_index(y.c >> 3);
+  float sc[8], sh[8], ca[8], cb[8];
+  {
+    float mu[8], is[8], s0[8], s1[8];
+    ldparam8(scale, ix.cg * 8, sc); ldparam8(shift, ix.cg * 8, sh);
+    ldparam8(mean, ix.cg * 8, mu); ldparam8(invstd, ix.cg * 8, is);
+    ldparam8(sums, ix.cg * 8, s0); ldparam8(sums + y.c, ix.cg * 8, s1);
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-      const float z = fmaf(v[j], sc[j], sh[j]);
-      const float dz = (!relu || z > 0.f) ? g[j] : 0.f;
-      const float xh = (v[j] - mu[j]) * is[j];
-      // gamma*invstd == scale
-      o[j] = sc[j] * (dz - s0[j] * inv_count - xh * s1[j] * inv_count);
+      ca[j] = -sc[j] * is[j] * s1[j] * inv_count;
+      cb[j] = -sc[j] * s0[j] * inv_count - ca[j] * mu[j];
     }
-    (void)gamma;
-    store8(dy.ptr + p * dy.ld + cg * 8, o);
+  }
+  (void)gamma;
+  for (long p = ix.p0; p < y.npix; p += 4 * ix.ps) {
+    uint4 rg[4], rv[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const long q = p + u * ix.ps;
+      if (q < y.npix) {
+        rg[u] = ldraw(dout.ptr + q * dout.ld + ix.cg * 8);
+        rv[u] = ldraw(y.ptr + q * y.ld + ix.cg * 8);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const long q = p + u * ix.ps;
+      if (q < y.npix) {
+        float o[8], g[8], v[8];
+        unpack8(rg[u], g);
+        unpack8(rv[u], v);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float z = fmaf(v[j], sc[j], sh[j]);
+          const float dz = (!relu || z > 0.f) ? g[j] : 0.f;
+          o[j] = fmaf(sc[j], dz, fmaf(ca[j], v[j], cb[j]));
+        }
+        store8(dy.ptr + q * dy.ld + ix.cg * 8, o);
+      }
+    }
   }
 }
 
@@ -276,7 +362,7 @@ __global__ void __launch_bounds__(256) bn_act_bwd_apply_kernel(DView dout, DView
 // du = dout*(out>0);  dz2 = du*(bn2(y2)>0)
 // sums: [0] sum dz2, [1] sum dz2*xhat2, [2] sum du, [3] sum du*xhat_r   (2,3 only if res_is_bn)
 template <bool RES_BN>
-__global__ void __launch_bounds__(kRedThreads) tail_bwd_reduce_kernel(DView dout, DView out, DView y2, const float* s2,
+__global__ void __launch_bounds__(kRedThreads, 2) tail_bwd_reduce_kernel(DView dout, DView out, DView y2, const float* s2,
                                                                       const float* b2, const float* mean2,
                                                                       const float* invstd2, DView res,
                                                                       const float* meanr, const float* invstdr,
@@ -293,94 +379,151 @@ __global__ void __launch_bounds__(kRedThreads) tail_bwd_reduce_kernel(DView dout
   for (int s = 0; s < NS; ++s)
 #pragma unroll
     for (int j = 0; j < 8; ++j) acc[s][j] = 0.f;
-  for (long p = (long)blockIdx.x * lanes + pl; p < y2.npix; p += (long)gridDim.x * lanes) {
-    float g[8], o[8], v[8], r[8];
-    load8(dout.ptr + p * dout.ld + cg * 8, g);
-    load8(out.ptr + p * out.ld + cg * 8, o);
-    load8(y2.ptr + p * y2.ld + cg * 8, v);
-    if (RES_BN) load8(res.ptr + p * res.ld + cg * 8, r);
+  const long ps = (long)gridDim.x * lanes;
+  for (long p = (long)blockIdx.x * lanes + pl; p < y2.npix; p += 2 * ps) {
+    uint4 rg[2], ro[2], rv[2], rr4[2];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      const float du = o[j] > 0.f ? g[j] : 0.f;
-      const float z = fmaf(v[j], sc[j], sh[j]);
-      const float dz = z > 0.f ? du : 0.f;
-      acc[0][j] += dz;
-      acc[1][j] = fmaf(dz, (v[j] - mu[j]) * is[j], acc[1][j]);
-      if (RES_BN) {
-        acc[2][j] += du;
-        acc[3][j] = fmaf(du, (r[j] - mur[j]) * isr[j], acc[3][j]);
+    for (int u = 0; u < 2; ++u) {
+      const long q = p + u * ps;
+      if (q < y2.npix) {
+        rg[u] = ldraw(dout.ptr + q * dout.ld + cg * 8);
+        ro[u] = ldraw(out.ptr + q * out.ld + cg * 8);
+        rv[u] = ldraw(y2.ptr + q * y2.ld + cg * 8);
+        rr4[u] = RES_BN ? ldraw(res.ptr + q * res.ld + cg * 8) : make_uint4(0u, 0u, 0u, 0u);
+      } else {
+        rg[u] = make_uint4(0u, 0u, 0u, 0u); ro[u] = make_uint4(0u, 0u, 0u, 0u); rv[u] = make_uint4(0u, 0u, 0u, 0u); rr4[u] = make_uint4(0u, 0u, 0u, 0u);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      float g[8], o[8], v[8], r[8];
+      unpack8(rg[u], g);
+      unpack8(ro[u], o);
+      unpack8(rv[u], v);
+      unpack8(rr4[u], r);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float du = o[j] > 0.f ? g[j] : 0.f;
+        const float z = fmaf(v[j], sc[j], sh[j]);
+        const float dz = z > 0.f ? du : 0.f;
+        acc[0][j] += dz;
+        acc[1][j] = fmaf(dz, (v[j] - mu[j]) * is[j], acc[1][j]);
+        if (RES_BN) {
+          acc[2][j] += du;
+          acc[3][j] = fmaf(du, (r[j] - mur[j]) * isr[j], acc[3][j]);
+        }
       }
     }
   }
   block_reduce_store<NS>(acc, y2.c, partials);
 }
 
+// dy2 = s2 * dz2 + A2 * y2 + B2 (see bn_act_bwd_apply_kernel);  dres = du | Gr * du + Ar * res + Br with
+// Gr = gamma_r * invstd_r, Ar = -Gr * invstd_r * S3/N, Br = -Gr * S2/N - Ar * mean_r
 template <bool RES_BN>
-__global__ void __launch_bounds__(256) tail_bwd_apply_kernel(DView dout, DView out, DView y2, const float* s2,
-                                                             const float* b2, const float* mean2,
-                                                             const float* invstd2, DView res, const float* meanr,
-                                                             const float* invstdr, const float* gammar,
-                                                             const float* sums, float inv_count, DViewW dy2,
-                                                             DViewW dres) {
-  const int cgs = y2.c >> 3, c = y2.c;
-  const long total = y2.npix * cgs;
-  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
-    const long p = i / cgs;
-    const int cg = (int)(i % cgs);
-    float g[8], o[8], v[8], sc[8], sh[8], mu[8], is[8], t0[8], t1[8];
-    load8(dout.ptr + p * dout.ld + cg * 8, g);
-    load8(out.ptr + p * out.ld + cg * 8, o);
-    load8(y2.ptr + p * y2.ld + cg * 8, v);
-    ldparam8(s2, cg * 8, sc); ldparam8(b2, cg * 8, sh);
-    ldparam8(mean2, cg * 8, mu); ldparam8(invstd2, cg * 8, is);
-    ldparam8(sums, cg * 8, t0); ldparam8(sums + c, cg * 8, t1);
-    float du[8], d2[8];
+__global__ void __launch_bounds__(256, 2) tail_bwd_apply_kernel(DView dout, DView out, DView y2, const float* s2,
+                                                                const float* b2, const float* mean2,
+                                                                const float* invstd2, DView res, const float* meanr,
+                                                                const float* invstdr, const float* gammar,
+                                                                const float* sums, float inv_count, DViewW dy2,
+                                                                DViewW dres) {
+  const int c = y2.c;
+  const EwIdx ix = ew_index(c >> 3);
+  float sc[8], sh[8], ca[8], cb[8], gr[8], ra[8], rb[8];
+  {
+    float mu[8], is[8], t0[8], t1[8];
+    ldparam8(s2, ix.cg * 8, sc); ldparam8(b2, ix.cg * 8, sh);
+    ldparam8(mean2, ix.cg * 8, mu); ldparam8(invstd2, ix.cg * 8, is);
+    ldparam8(sums, ix.cg * 8, t0); ldparam8(sums + c, ix.cg * 8, t1);
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-      du[j] = o[j] > 0.f ? g[j] : 0.f;
-      const float z = fmaf(v[j], sc[j], sh[j]);
-      const float dz = z > 0.f ? du[j] : 0.f;
-      const float xh = (v[j] - mu[j]) * is[j];
-      d2[j] = sc[j] * (dz - t0[j] * inv_count - xh * t1[j] * inv_count);
+      ca[j] = -sc[j] * is[j] * t1[j] * inv_count;
+      cb[j] = -sc[j] * t0[j] * inv_count - ca[j] * mu[j];
     }
-    store8(dy2.ptr + p * dy2.ld + cg * 8, d2);
     if (RES_BN) {
-      float r[8], mur[8], isr[8], gr[8], u0[8], u1[8], dr[8];
-      load8(res.ptr + p * res.ld + cg * 8, r);
-      ldparam8(meanr, cg * 8, mur); ldparam8(invstdr, cg * 8, isr); ldparam8(gammar, cg * 8, gr);
-      ldparam8(sums + 2 * c, cg * 8, u0); ldparam8(sums + 3 * c, cg * 8, u1);
+      ldparam8(meanr, ix.cg * 8, mu); ldparam8(invstdr, ix.cg * 8, is); ldparam8(gammar, ix.cg * 8, gr);
+      ldparam8(sums + 2 * c, ix.cg * 8, t0); ldparam8(sums + 3 * c, ix.cg * 8, t1);
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
-        const float xh = (r[j] - mur[j]) * isr[j];
-        dr[j] = gr[j] * isr[j] * (du[j] - u0[j] * inv_count - xh * u1[j] * inv_count);
+        gr[j] *= is[j];
+        ra[j] = -gr[j] * is[j] * t1[j] * inv_count;
+        rb[j] = -gr[j] * t0[j] * inv_count - ra[j] * mu[j];
       }
-      store8(dres.ptr + p * dres.ld + cg * 8, dr);
-    } else {
-      store8(dres.ptr + p * dres.ld + cg * 8, du);
+    }
+  }
+  for (long p = ix.p0; p < y2.npix; p += 2 * ix.ps) {
+    uint4 rg[2], ro[2], rv[2], rr4[2];
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      const long q = p + u * ix.ps;
+      if (q < y2.npix) {
+        rg[u] = ldraw(dout.ptr + q * dout.ld + ix.cg * 8);
+        ro[u] = ldraw(out.ptr + q * out.ld + ix.cg * 8);
+        rv[u] = ldraw(y2.ptr + q * y2.ld + ix.cg * 8);
+        if (RES_BN) rr4[u] = ldraw(res.ptr + q * res.ld + ix.cg * 8);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      const long q = p + u * ix.ps;
+      if (q < y2.npix) {
+        float du[8], d2[8], g[8], o[8], v[8];
+        unpack8(rg[u], g);
+        unpack8(ro[u], o);
+        unpack8(rv[u], v);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          du[j] = o[j] > 0.f ? g[j] : 0.f;
+          const float z = fmaf(v[j], sc[j], sh[j]);
+          const float dz = z > 0.f ? du[j] : 0.f;
+          d2[j] = fmaf(sc[j], dz, fmaf(ca[j], v[j], cb[j]));
+        }
+        store8(dy2.ptr + q * dy2.ld + ix.cg * 8, d2);
+        if (RES_BN) {
+          float r[8];
+          unpack8(rr4[u], r);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) du[j] = fmaf(gr[j], du[j], fmaf(ra[j], r[j], rb[j]));
+        }
+        store8(dres.ptr + q * dres.ld + ix.cg * 8, du);
+      }
     }
   }
 }
 
 // ------------------------------------------------------------------ pointwise sum
-__global__ void __launch_bounds__(256) add_kernel(DView a, DView b, DView c, DViewW out) {
-  const int cgs = a.c >> 3;
-  const long total = a.npix * cgs;
-  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
-    const long p = i / cgs;
-    const int cg = (int)(i % cgs);
-    float x[8], y[8];
-    load8(a.ptr + p * a.ld + cg * 8, x);
-    if (b.ptr) {
-      load8(b.ptr + p * b.ld + cg * 8, y);
+__global__ void __launch_bounds__(256, 2) add_kernel(DView a, DView b, DView c, DViewW out) {
+  const EwIdx ix = ew_index(a.c >> 3);
+  for (long p = ix.p0; p < a.npix; p += 4 * ix.ps) {
+    uint4 rx[4], ry[4], rz[4];
 #pragma unroll
-      for (int j = 0; j < 8; ++j) x[j] += y[j];
+    for (int u = 0; u < 4; ++u) {
+      const long q = p + u * ix.ps;
+      if (q < a.npix) {
+        rx[u] = ldraw(a.ptr + q * a.ld + ix.cg * 8);
+        if (b.ptr) ry[u] = ldraw(b.ptr + q * b.ld + ix.cg * 8);
+        if (c.ptr) rz[u] = ldraw(c.ptr + q * c.ld + ix.cg * 8);
+      }
     }
-    if (c.ptr) {
-      load8(c.ptr + p * c.ld + cg * 8, y);
 #pragma unroll
-      for (int j = 0; j < 8; ++j) x[j] += y[j];
+    for (int u = 0; u < 4; ++u) {
+      const long q = p + u * ix.ps;
+      if (q < a.npix) {
+        float x[8], y[8];
+        unpack8(rx[u], x);
+        if (b.ptr) {
+          unpack8(ry[u], y);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) x[j] += y[j];
+        }
+        if (c.ptr) {
+          unpack8(rz[u], y);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) x[j] += y[j];
+        }
+        store8(out.ptr + q * out.ld + ix.cg * 8, x);
+      }
     }
-    store8(out.ptr + p * out.ld + cg * 8, x);
   }
 }
 
@@ -656,6 +799,19 @@ static int chk_red(const ubr_view& v, const char* name) {
               name, v.c, kRedThreads * 8);
   return 0;
 }
+// grid of the fixed-channel-group streaming kernels (ew_index): `unroll` pixels per thread per trip, at most 4 CTAs
+// per SM, and gridDim * 256 a multiple of cgs so that every thread keeps one channel group
+static inline unsigned ew_grid(long npix, int cgs, int unroll) {
+  long nb = (npix * cgs + 256L * unroll - 1) / (256L * unroll);
+  const long cap = (long)sm_count() * 4;
+  if (nb > cap) nb = cap;
+  if (nb < 1) nb = 1;
+  int g = cgs, r = 256;
+  while (r) { const int t = g % r; g = r; r = t; }          // g = gcd(cgs, 256)
+  const long m = cgs / g;
+  nb = (nb + m - 1) / m * m;
+  return (unsigned)nb;
+}
 static inline unsigned ew_blocks(long total) {
   long nb = (total + 255) / 256;
   const long cap = (long)sm_count() * 16;
@@ -730,7 +886,7 @@ int ubr_bn_act(ubr_view y, const float* scale, const float* shift, int relu, ubr
   if (int rc = same_shape(y, out, "bn_act")) return rc;
   UBR_REQUIRE(scale && shift, "bn_act: null affine");
   DView v = dv(y);
-  bn_act_kernel<<<ew_blocks(v.npix * (v.c >> 3)), 256, 0, (cudaStream_t)stream>>>(v, scale, shift, relu, dvw(out));
+  bn_act_kernel<<<ew_grid(v.npix, v.c >> 3, 4), 256, 0, (cudaStream_t)stream>>>(v, scale, shift, relu, dvw(out));
   UBR_LAUNCH_CHECK("bn_act_kernel");
   return 0;
 }
@@ -745,7 +901,7 @@ int ubr_block_tail(ubr_view y2, const float* s2, const float* b2, ubr_view res, 
   if (int rc = same_shape(y2, out, "block_tail(out)")) return rc;
   UBR_REQUIRE(s2 && b2 && ((sr == nullptr) == (br == nullptr)), "block_tail: bad affine pointers");
   DView v = dv(y2);
-  block_tail_kernel<<<ew_blocks(v.npix * (v.c >> 3)), 256, 0, (cudaStream_t)stream>>>(v, s2, b2, dv(res), sr, br,
+  block_tail_kernel<<<ew_grid(v.npix, v.c >> 3, 4), 256, 0, (cudaStream_t)stream>>>(v, s2, b2, dv(res), sr, br,
                                                                                       dvw(out));
   UBR_LAUNCH_CHECK("block_tail_kernel");
   return 0;
@@ -759,7 +915,7 @@ int ubr_bn_act_bwd_reduce(ubr_view dout, ubr_view y, const float* scale, const f
   if (int rc = same_shape(y, dout, "bn_act_bwd_reduce")) return rc;
   UBR_REQUIRE(scale && shift && mean && invstd && workspace, "bn_act_bwd_reduce: null pointer");
   DView v = dv(y);
-  const int nb = red_blocks(v.npix, v.c);
+  const int nb = red_blocks(v.npix, v.c, kBwdRedBlocks);
   bn_act_bwd_reduce_kernel<<<nb, kRedThreads, kRedThreads * 16 * sizeof(float), (cudaStream_t)stream>>>(
       dv(dout), v, scale, shift, mean, invstd, relu, (float*)workspace);
   UBR_LAUNCH_CHECK("bn_act_bwd_reduce_kernel");
@@ -777,7 +933,7 @@ int ubr_bn_act_bwd_apply(ubr_view dout, ubr_view y, const float* scale, const fl
   if (int rc = same_shape(y, dy, "bn_act_bwd_apply(dy)")) return rc;
   UBR_REQUIRE(scale && shift && mean && invstd && workspace, "bn_act_bwd_apply: null pointer");
   DView v = dv(y);
-  const int nb = red_blocks(v.npix, v.c);
+  const int nb = red_blocks(v.npix, v.c, kBwdRedBlocks);
   const float* partials = (const float*)workspace;
   float* sums = (float*)workspace + (size_t)kRedBlocks * 4 * v.c;
   cudaStream_t st = (cudaStream_t)stream;
@@ -787,7 +943,7 @@ int ubr_bn_act_bwd_apply(ubr_view dout, ubr_view y, const float* scale, const fl
     param_grad_kernel<<<ceil_div(v.c, 128), 128, 0, st>>>(sums, v.c, 0, 1, dgamma, dbeta, accumulate);
     UBR_LAUNCH_CHECK("param_grad_kernel");
   }
-  bn_act_bwd_apply_kernel<<<ew_blocks(v.npix * (v.c >> 3)), 256, 0, st>>>(dv(dout), v, scale, shift, mean, invstd,
+  bn_act_bwd_apply_kernel<<<ew_grid(v.npix, v.c >> 3, 4), 256, 0, st>>>(dv(dout), v, scale, shift, mean, invstd,
                                                                           gamma, relu, sums, (float)(1.0 / count),
                                                                           dvw(dy));
   UBR_LAUNCH_CHECK("bn_act_bwd_apply_kernel");
@@ -805,7 +961,7 @@ int ubr_block_tail_bwd_reduce(ubr_view dout, ubr_view out, ubr_view y2, const fl
   if (int rc = same_shape(y2, out, "block_tail_bwd_reduce(out)")) return rc;
   UBR_REQUIRE(s2 && b2 && mean2 && invstd2 && workspace, "block_tail_bwd_reduce: null pointer");
   DView v = dv(y2);
-  const int nb = red_blocks(v.npix, v.c);
+  const int nb = red_blocks(v.npix, v.c, kBwdRedBlocks);
   cudaStream_t st = (cudaStream_t)stream;
   if (res_is_bn) {
     if (int rc = chk(res, "block_tail_bwd_reduce.res")) return rc;
@@ -839,7 +995,7 @@ int ubr_block_tail_bwd_apply(ubr_view dout, ubr_view out, ubr_view y2, const flo
   UBR_REQUIRE(s2 && b2 && mean2 && invstd2 && workspace, "block_tail_bwd_apply: null pointer");
   (void)gamma2;
   DView v = dv(y2);
-  const int nb = red_blocks(v.npix, v.c);
+  const int nb = red_blocks(v.npix, v.c, kBwdRedBlocks);
   const int ns = res_is_bn ? 4 : 2;
   const float* partials = (const float*)workspace;
   float* sums = (float*)workspace + (size_t)kRedBlocks * 4 * v.c;
@@ -850,7 +1006,7 @@ int ubr_block_tail_bwd_apply(ubr_view dout, ubr_view out, ubr_view y2, const flo
     param_grad_kernel<<<ceil_div(v.c, 128), 128, 0, st>>>(sums, v.c, 0, 1, dgamma2, dbeta2, accumulate);
     UBR_LAUNCH_CHECK("param_grad_kernel");
   }
-  const unsigned blocks = ew_blocks(v.npix * (v.c >> 3));
+  const unsigned blocks = ew_grid(v.npix, v.c >> 3, 2);
   if (res_is_bn) {
     if (int rc = chk(res, "block_tail_bwd_apply.res")) return rc;
     UBR_REQUIRE(meanr && invstdr && gammar, "block_tail_bwd_apply: null residual stats");
@@ -971,7 +1127,7 @@ int ubr_add(ubr_view a, ubr_view b, ubr_view c, ubr_view out, void* stream) {
     vc = dv(c);
   }
   DView va = dv(a);
-  add_kernel<<<ew_blocks(va.npix * (va.c >> 3)), 256, 0, (cudaStream_t)stream>>>(va, vb, vc, dvw(out));
+  add_kernel<<<ew_grid(va.npix, va.c >> 3, 4), 256, 0, (cudaStream_t)stream>>>(va, vb, vc, dvw(out));
   UBR_LAUNCH_CHECK("add_kernel");
   return 0;
 }

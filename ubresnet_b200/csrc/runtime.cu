@@ -22,7 +22,23 @@ int cuda_fail(cudaError_t e, const char* what) {
 }
 
 static std::atomic<unsigned long long> g_launches{0};
-void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
+static std::atomic<int> g_trace{0};
+static thread_local char g_names[512];
+static thread_local char g_names_out[512];
+static thread_local unsigned g_names_len = 0;
+void count_launch(const char* name) {
+  g_launches.fetch_add(1, std::memory_order_relaxed);
+  if (g_trace.load(std::memory_order_relaxed) && name) {
+    // kernel-name trace for the bench profiler: "a+b" = the kernels this thread launched since the last take
+    const size_t n = strlen(name);
+    if (g_names_len + n + 2 < sizeof(g_names)) {
+      if (g_names_len) g_names[g_names_len++] = '+';
+      memcpy(g_names + g_names_len, name, n);
+      g_names_len += (unsigned)n;
+      g_names[g_names_len] = 0;
+    }
+  }
+}
 
 static int g_dev_ok[64];       // 0 unknown, 1 ok, -1 unsupported
 static int g_sm_count[64];
@@ -107,6 +123,14 @@ const char* ubr_last_error(void) { return ubr::g_err; }
 int ubr_device_check(void) { return ubr::ensure_device(); }
 
 uint64_t ubr_launch_count(void) { return (uint64_t)ubr::g_launches.load(); }
+void ubr_trace_kernels(int enable) { ubr::g_trace.store(enable ? 1 : 0); ubr::g_names_len = 0; ubr::g_names[0] = 0; }
+const char* ubr_take_kernel_names(void) {
+  memcpy(ubr::g_names_out, ubr::g_names, ubr::g_names_len + 1);
+  ubr::g_names_out[ubr::g_names_len] = 0;
+  ubr::g_names_len = 0;
+  ubr::g_names[0] = 0;
+  return ubr::g_names_out;
+}
 
 int ubr_sync_check(void* stream) {
   cudaError_t e = cudaStreamSynchronize((cudaStream_t)stream);

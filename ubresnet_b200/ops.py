@@ -464,6 +464,19 @@ def pixelwise_nll_bwd(target, pixw, classw, gout, n, ncls, h, w, ignore_index):
     return dlogp
 
 
+def accuracy_counts(logp, target):
+    """(2*C,) int64 device tensor: [pixels per class | correctly predicted pixels per class]."""
+    lib = _lib.load()
+    require_cuda(logp, "output")
+    require_cuda(target, "target")
+    n, ncls, h, w = logp.shape
+    assert logp.dtype == torch.float32 and target.dtype == torch.int64 and target.numel() == n * h * w
+    counts = torch.empty(2 * ncls, dtype=torch.int64, device=logp.device)
+    _lib.check(lib.ubr_accuracy_counts(logp.contiguous().data_ptr(), target.contiguous().data_ptr(), n, ncls, h * w,
+                                       counts.data_ptr(), _stream()), "accuracy_counts")
+    return counts
+
+
 def tile_gather(plane, origins, crop):
     lib = _lib.load()
     require_cuda(plane, "plane")
