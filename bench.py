@@ -107,6 +107,52 @@ def cpu_train_rate(batch, size, steps, warmup, threads=None):
     return batch / mean, mean * 1e3, torch.get_num_threads()
 
 
+def library_train_rate(batch, size, steps, warmup, mode, dev):
+    """The oracle port (plain torch.nn.functional ops == what the reference's nn.Modules call) on the GPU through
+    PyTorch/cuDNN: the "library" comparison of SURVEY.md 8d cfg-2.  mode: "fp32" (TF32 off), "tf32", "bf16" (autocast +
+    channels_last).  Baseline leg only -- never part of the product path."""
+    from oracle import uresnet_port as port
+    from ubresnet_b200 import synthetic
+    torch.backends.cudnn.benchmark = True
+    tf32 = mode != "fp32"
+    torch.backends.cuda.matmul.allow_tf32 = tf32
+    torch.backends.cudnn.allow_tf32 = tf32
+    sd = port.init_state_dict(3, 1, 16, seed=1)
+    params = port.clone_state_dict(sd, requires_grad=True)
+    params = type(params)((k, v.detach().to(dev).requires_grad_(v.requires_grad)) for k, v in params.items())
+    if mode == "bf16":
+        for k, v in params.items():
+            if v.dim() == 4:
+                v.data = v.data.contiguous(memory_format=torch.channels_last)
+    leaves = [v for v in params.values() if v.requires_grad]
+    opt = torch.optim.SGD(leaves, lr=1e-4, momentum=0.9, weight_decay=1e-3, foreach=True)
+    img, lab, wgt = (t.to(dev) for t in synthetic.make_batch(batch, size, size))
+    if mode == "bf16":
+        img = img.contiguous(memory_format=torch.channels_last)
+
+    def step():
+        opt.zero_grad(set_to_none=True)
+        with torch.autocast("cuda", dtype=torch.bfloat16, enabled=(mode == "bf16")):
+            logp = port.forward(params, img, training=True)
+        loss = port.pixelwise_nll(logp.float(), lab, wgt)
+        loss.backward()
+        opt.step()
+
+    for _ in range(warmup):
+        step()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        step()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / steps
+    return {"value": batch / (ms * 1e-3), "unit": UNIT, "ms_per_step": ms, "mode": mode,
+            "what": "oracle/uresnet_port.py (torch.nn.functional -> cuDNN/ATen, torch %s) train step on the same GPU, "
+                    "batch %d" % (torch.__version__, batch)}
+
+
 def run_reference(args, rank):
     if rank != 0:
         return
@@ -268,11 +314,22 @@ def run_own(args, rank, world, local_rank):
         opt.step()
         return loss
 
+    # e2e: every step's batch is copied host -> device from pinned memory inside the timed region; the copy of batch
+    # i+1 runs on the prefetcher's side stream while step i computes (ubresnet_b200/prefetch.py)
+    from ubresnet_b200.prefetch import DevicePrefetcher
+
+    def host_batches():
+        i = 0
+        while True:
+            yield host[i % nbuf]
+            i += 1
+
+    feed = {}
+
     def step_e2e(i):
-        img, lab, wgt = host[i % nbuf]
-        img = img.to(dev, non_blocking=True)
-        lab = lab.to(dev, non_blocking=True)
-        wgt = wgt.to(dev, non_blocking=True)
+        if "it" not in feed:
+            feed["it"] = DevicePrefetcher(host_batches(), dev)
+        img, lab, wgt = next(feed["it"])
         opt.zero_grad(set_to_none=True)
         loss = crit(net(img), lab, wgt)
         loss.backward()
@@ -382,6 +439,18 @@ def run_own(args, rank, world, local_rank):
                "sample": "oracle/uresnet_port.py train step, batch %d of %dx%d crops, best-effort mean of 2 steps after 1 "
                          "warm-up (%.0f ms/step)" % (args.cpu_batch, S, S, cms)}
 
+    library = None
+    if rank == 0 and world == 1 and args.library_baseline:
+        resident.clear()
+        torch.cuda.empty_cache()
+        library = []
+        for mode in ("bf16", "tf32", "fp32"):
+            try:
+                library.append(library_train_rate(B, S, 5, 3, mode, dev))
+            except Exception as exc:                               # e.g. out of memory in fp32
+                library.append({"mode": mode, "error": str(exc)[:200]})
+            torch.cuda.empty_cache()
+
     if rank == 0:
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
@@ -402,6 +471,8 @@ def run_own(args, rank, world, local_rank):
             line["roofline"] = roof
         if cpu:
             line["cpu_baseline"] = cpu
+        if library:
+            line["library_baseline"] = library
         if infer:
             line["infer"] = infer
         if wholeview:
@@ -426,6 +497,8 @@ def main():
     ap.add_argument("--size", type=int, default=512)
     ap.add_argument("--cpu-batch", type=int, default=4, help="crops per CPU step (bounded sample)")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--library-baseline", action="store_true",
+                    help="also time the oracle port through PyTorch/cuDNN on the same GPU (bf16 autocast, tf32, fp32)")
     ap.add_argument("--no-infer", action="store_true", help="skip the eval-forward and whole-view measurements")
     ap.add_argument("--verbose", action="store_true")
     ap.add_argument("--kernel-log", default="")

@@ -368,6 +368,7 @@ __global__ void __launch_bounds__(kRedThreads, 2) tail_bwd_reduce_kernel(DView d
                                                                       const float* meanr, const float* invstdr,
                                                                       float* partials) {
   constexpr int NS = RES_BN ? 4 : 2;
+  constexpr int U = RES_BN ? 1 : 2;      // 4 tensors in flight per pixel group with the residual BN: no unroll (registers)
   const int cgs = y2.c >> 3, lanes = blockDim.x / cgs;
   const int cg = threadIdx.x % cgs, pl = threadIdx.x / cgs;
   float sc[8], sh[8], mu[8], is[8], mur[8], isr[8];
@@ -380,10 +381,10 @@ __global__ void __launch_bounds__(kRedThreads, 2) tail_bwd_reduce_kernel(DView d
 #pragma unroll
     for (int j = 0; j < 8; ++j) acc[s][j] = 0.f;
   const long ps = (long)gridDim.x * lanes;
-  for (long p = (long)blockIdx.x * lanes + pl; p < y2.npix; p += 2 * ps) {
-    uint4 rg[2], ro[2], rv[2], rr4[2];
+  for (long p = (long)blockIdx.x * lanes + pl; p < y2.npix; p += U * ps) {
+    uint4 rg[U], ro[U], rv[U], rr4[U];
 #pragma unroll
-    for (int u = 0; u < 2; ++u) {
+    for (int u = 0; u < U; ++u) {
       const long q = p + u * ps;
       if (q < y2.npix) {
         rg[u] = ldraw(dout.ptr + q * dout.ld + cg * 8);
@@ -395,7 +396,7 @@ __global__ void __launch_bounds__(kRedThreads, 2) tail_bwd_reduce_kernel(DView d
       }
     }
 #pragma unroll
-    for (int u = 0; u < 2; ++u) {
+    for (int u = 0; u < U; ++u) {
       float g[8], o[8], v[8], r[8];
       unpack8(rg[u], g);
       unpack8(ro[u], o);
