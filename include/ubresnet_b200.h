@@ -108,6 +108,13 @@ int ubr_deconv4s2_fwd(ubr_view x, const void* wpk, int out_ch, ubr_view y, void*
  * path (in_ch > 64 or W %% 128 != 0): use ubr_deconv4s2_fwd. */
 int ubr_deconv4s2_fwd_subpixel(ubr_view x, const void* wpk3, int out_ch, ubr_view y, void* stream);
 int ubr_deconv4s2_dgrad(ubr_view dy, const void* wpk, int in_ch, ubr_view dx, void* stream);
+/* backward of the same layer on the sub-pixel formulation (high-resolution decoder stages, 4*out_ch <= 64):
+ *   dy4 = ubr_pixel_unshuffle2(dy)                      [n, h, w, 4*out_ch] on the input grid
+ *   dx  = ubr_conv2d_fwd(dy4, wpk3d, NULL, in_ch, 3, 1) wpk3d = ubr_pack_weights(src_layout=2, n_is_out=0, 3, 3)
+ *   dw3 = ubr_conv2d_wgrad(x, dy4, 4*out_ch, 3, 1)      fp32 [4*out_ch][in_ch][3][3]
+ *   dw  = ubr_deconv4s2_wgrad_gather(dw3)               IOHW [in_ch][out_ch][4][4] */
+int ubr_pixel_unshuffle2(ubr_view y, ubr_view y4, void* stream);
+int ubr_deconv4s2_wgrad_gather(const float* dw3, int in_ch, int out_ch, float* dw, int accumulate, void* stream);
 int ubr_deconv4s2_wgrad(ubr_view x, ubr_view dy, float* dw /* IOHW */, int accumulate,
                         void* workspace, uint64_t workspace_bytes, void* stream);
 

@@ -226,6 +226,23 @@ def check_deconv(cin, cout, n, h, w, out_ld=None, seed=0):
     res.append((name + "_wgrad", relerr(dw, ref_dw), 2e-3))
     if res[-1][1] > 2e-3:
         _dump(name + "_wgrad", out=dw, ref=ref_dw, x=x, dy=dy)
+    # sub-pixel backward (pixel-unshuffle + 3x3 conv / 3x3 wgrad on the input grid), as Engine._deconv_bwd runs it
+    if 4 * cout <= 64 and cin <= 64:
+        dy4 = ops.pixel_unshuffle2(dya)
+        ref4 = torch.cat([dy[:, :, ph::2, pw::2] for ph in (0, 1) for pw in (0, 1)], 1)
+        res.append((name + "_unshuffle", relerr(dy4.nchw_float(), ref4), 0.0))
+        dx3 = ops.conv2d_fwd(dy4, ops.pack_weights_subpixel(wt.to(DEV), False), None, cin, 3, 1)
+        ws3 = torch.empty(ops.wgrad_workspace_bytes(n, h, w, 4 * cout, cin, 9) // 4 + 4, dtype=torch.float32, device=DEV)
+        dw3 = torch.empty((4 * cout, cin, 3, 3), dtype=torch.float32, device=DEV)
+        ops.conv2d_wgrad(xa, dy4, 4 * cout, 3, 1, dw3, False, ws3)
+        dwb = torch.full((cin, cout, 4, 4), 9.0, dtype=torch.float32, device=DEV)
+        ops.deconv_wgrad_gather(dw3, dwb)
+        torch.cuda.synchronize()
+        res.append((name + "_dgrad_subpixel", relerr(dx3.nchw_float(), ref_dx), 1e-2))
+        res.append((name + "_wgrad_subpixel", relerr(dwb, ref_dw), 2e-3))
+        ops.deconv_wgrad_gather(dw3, dwb, accumulate=True)
+        torch.cuda.synchronize()
+        res.append((name + "_wgrad_subpixel_accum", relerr(dwb, 2 * ref_dw), 2e-3))
     return res
 
 

@@ -40,6 +40,8 @@ SIGNATURES = {
     "ubr_conv2d_dilated_wgrad": (_i, [View, View, _i, _i, _vp, _i, _vp, _u64, _vp]),
     "ubr_maxpool3s1_fwd": (_i, [View, View, _vp, _vp]),
     "ubr_maxpool3s1_bwd_idx": (_i, [_vp, View, View, _i, _vp]),
+    "ubr_pixel_unshuffle2": (_i, [View, View, _vp]),
+    "ubr_deconv4s2_wgrad_gather": (_i, [_vp, _i, _i, _vp, _i, _vp]),
     "ubr_deconv4s2_fwd_subpixel": (_i, [View, _vp, _i, View, _vp]),
     "ubr_deconv4s2_dgrad": (_i, [View, _vp, _i, View, _vp]),
     "ubr_deconv4s2_wgrad": (_i, [View, View, _vp, _i, _vp, _u64, _vp]),

@@ -295,18 +295,16 @@ __global__ void __launch_bounds__(kRedThreads, 2) bn_act_bwd_reduce_kernel(DView
 }
 
 // sums partials[nb][NS][C] -> sums[NS][C] (fixed order, double); grid = ceil(nsc/32), block = (32, 8)
-__global__ void sums_finalize_kernel(const float* partials, int nb, int nsc, float* sums) {
+struct ParamGradOut { float* p[4]; };    // per sum row: optional fp32 parameter-gradient vector of c entries (dbeta / dgamma)
+__global__ void sums_finalize_kernel(const float* partials, int nb, int nsc, float* sums, int c, ParamGradOut out,
+                                     int accumulate) {
   const int i = blockIdx.x * 32 + threadIdx.x;
   const double s = col_sum_32x8(partials, nb, nsc, i, i < nsc);
-  if (i < nsc && threadIdx.y == 0) sums[i] = (float)s;
-}
-
-__global__ void param_grad_kernel(const float* sums, int c, int off_dz, int off_dzx, float* dgamma, float* dbeta,
-                                  int accumulate) {
-  const int ch = blockIdx.x * blockDim.x + threadIdx.x;
-  if (ch >= c) return;
-  if (dgamma) dgamma[ch] = (accumulate ? dgamma[ch] : 0.f) + sums[off_dzx * c + ch];
-  if (dbeta) dbeta[ch] = (accumulate ? dbeta[ch] : 0.f) + sums[off_dz * c + ch];
+  if (i < nsc && threadIdx.y == 0) {
+    sums[i] = (float)s;
+    float* dst = out.p[i / c];
+    if (dst) dst[i % c] = (accumulate ? dst[i % c] : 0.f) + (float)s;
+  }
 }
 
 // dy = scale * (dz - S0/N - xhat * S1/N) with xhat = (y - mean) * invstd, regrouped per channel as
@@ -719,6 +717,39 @@ __global__ void __launch_bounds__(256) maxpool3s1_bwd_idx_kernel(const uint8_t* 
   }
 }
 
+// ------------------------------------------------------------------ pixel unshuffle (ConvTranspose backward)
+// y4[n, h, w, (ph*2+pw)*c + co] = y[n, 2h+ph, 2w+pw, co]: the gradient of a ConvTranspose2d(k4,s2,p1) output regrouped
+// on the INPUT grid, so that its data / weight gradients become a 3x3 stride-1 conv / wgrad with 4*c channels
+// (the transpose of the sub-pixel forward, ubr_deconv4s2_fwd_subpixel).
+__global__ void __launch_bounds__(256) pixel_unshuffle2_kernel(const __nv_bfloat16* __restrict__ y, int yld, int n, int h,
+                                                               int w, int c, __nv_bfloat16* __restrict__ y4, int y4ld) {
+  const int cgs = c >> 3;                       // 16-byte groups per source pixel
+  const long total = (long)n * (2 * h) * (2 * w) * cgs;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+    const int cg = (int)(i % cgs);
+    long p = i / cgs;
+    const int ow = (int)(p % (2 * w)); p /= (2 * w);
+    const int oh = (int)(p % (2 * h));
+    const int b = (int)(p / (2 * h));
+    const uint4 v = *reinterpret_cast<const uint4*>(y + (((long)b * 2 * h + oh) * (2 * w) + ow) * yld + cg * 8);
+    const int ph = oh & 1, pw = ow & 1;
+    *reinterpret_cast<uint4*>(y4 + (((long)b * h + (oh >> 1)) * w + (ow >> 1)) * y4ld + (ph * 2 + pw) * c + cg * 8) = v;
+  }
+}
+
+// dw[ci][co][kh][kw] (+)= dw3[(ph*2+pw)*out_ch + co][ci][r][s] with kh = ph + 1 - 2*(r-1), kw = pw + 1 - 2*(s-1)
+// (the inverse of pack src_layout 2: every 4x4 tap is exactly one (phase, 3x3 tap) pair)
+__global__ void deconv_wgrad_gather_kernel(const float* __restrict__ dw3, int in_ch, int out_ch, float* __restrict__ dw,
+                                           int accumulate) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= in_ch * out_ch * 16) return;
+  const int kw = i & 3, kh = (i >> 2) & 3, co = (i >> 4) % out_ch, ci = (i >> 4) / out_ch;
+  const int ph = (kh + 1) & 1, pw = (kw + 1) & 1;
+  const int r = (ph + 1 - kh) / 2 + 1, s = (pw + 1 - kw) / 2 + 1;
+  const float v = dw3[(((long)((ph * 2 + pw) * out_ch + co) * in_ch + ci) * 3 + r) * 3 + s];
+  dw[i] = accumulate ? dw[i] + v : v;
+}
+
 // gather form of the backward: each input pixel re-derives the argmax (first maximum in (kh,kw) scan
 // order, as ATen's max_pool2d) of every window that covers it.  Deterministic, no atomics.
 __global__ void __launch_bounds__(256) maxpool_bwd_kernel(const __nv_bfloat16* x, int xld, int n, int h, int w, int c,
@@ -938,12 +969,10 @@ int ubr_bn_act_bwd_apply(ubr_view dout, ubr_view y, const float* scale, const fl
   const float* partials = (const float*)workspace;
   float* sums = (float*)workspace + (size_t)kRedBlocks * 4 * v.c;
   cudaStream_t st = (cudaStream_t)stream;
-  sums_finalize_kernel<<<ceil_div(2 * v.c, 32), dim3(32, kColLanes), 0, st>>>(partials, nb, 2 * v.c, sums);
+  // sums row 0 = sum dz (-> dbeta), row 1 = sum dz*xhat (-> dgamma): parameter gradients written by the finalize
+  sums_finalize_kernel<<<ceil_div(2 * v.c, 32), dim3(32, kColLanes), 0, st>>>(
+      partials, nb, 2 * v.c, sums, v.c, ParamGradOut{{dbeta, dgamma, nullptr, nullptr}}, accumulate);
   UBR_LAUNCH_CHECK("sums_finalize_kernel");
-  if (dgamma || dbeta) {
-    param_grad_kernel<<<ceil_div(v.c, 128), 128, 0, st>>>(sums, v.c, 0, 1, dgamma, dbeta, accumulate);
-    UBR_LAUNCH_CHECK("param_grad_kernel");
-  }
   bn_act_bwd_apply_kernel<<<ew_grid(v.npix, v.c >> 3, 4), 256, 0, st>>>(dv(dout), v, scale, shift, mean, invstd,
                                                                           gamma, relu, sums, (float)(1.0 / count),
                                                                           dvw(dy));
@@ -1001,20 +1030,14 @@ int ubr_block_tail_bwd_apply(ubr_view dout, ubr_view out, ubr_view y2, const flo
   const float* partials = (const float*)workspace;
   float* sums = (float*)workspace + (size_t)kRedBlocks * 4 * v.c;
   cudaStream_t st = (cudaStream_t)stream;
-  sums_finalize_kernel<<<ceil_div(ns * v.c, 32), dim3(32, kColLanes), 0, st>>>(partials, nb, ns * v.c, sums);
+  sums_finalize_kernel<<<ceil_div(ns * v.c, 32), dim3(32, kColLanes), 0, st>>>(
+      partials, nb, ns * v.c, sums, v.c,
+      ParamGradOut{{dbeta2, dgamma2, res_is_bn ? dbetar : nullptr, res_is_bn ? dgammar : nullptr}}, accumulate);
   UBR_LAUNCH_CHECK("sums_finalize_kernel");
-  if (dgamma2 || dbeta2) {
-    param_grad_kernel<<<ceil_div(v.c, 128), 128, 0, st>>>(sums, v.c, 0, 1, dgamma2, dbeta2, accumulate);
-    UBR_LAUNCH_CHECK("param_grad_kernel");
-  }
   const unsigned blocks = ew_grid(v.npix, v.c >> 3, 2);
   if (res_is_bn) {
     if (int rc = chk(res, "block_tail_bwd_apply.res")) return rc;
     UBR_REQUIRE(meanr && invstdr && gammar, "block_tail_bwd_apply: null residual stats");
-    if (dgammar || dbetar) {
-      param_grad_kernel<<<ceil_div(v.c, 128), 128, 0, st>>>(sums, v.c, 2, 3, dgammar, dbetar, accumulate);
-      UBR_LAUNCH_CHECK("param_grad_kernel");
-    }
     tail_bwd_apply_kernel<true><<<blocks, 256, 0, st>>>(dv(dout), dv(out), v, s2, b2, mean2, invstd2, dv(res), meanr,
                                                         invstdr, gammar, sums, (float)(1.0 / count), dvw(dy2),
                                                         dvw(dres));
@@ -1078,6 +1101,28 @@ int ubr_maxpool3s1_bwd_idx(const uint8_t* idx, ubr_view dy, ubr_view dx_accum, i
   maxpool3s1_bwd_idx_kernel<<<ew_blocks(total), 256, 0, (cudaStream_t)stream>>>(
       idx, dy.n, dy.h, dy.w, dy.c, (const __nv_bfloat16*)dy.ptr, dy.ld, (__nv_bfloat16*)dx_accum.ptr, dx_accum.ld, accumulate);
   UBR_LAUNCH_CHECK("maxpool3s1_bwd_idx_kernel");
+  return 0;
+}
+
+int ubr_pixel_unshuffle2(ubr_view y, ubr_view y4, void* stream) {
+  if (int rc = ensure_device()) return rc;
+  if (int rc = chk(y, "pixel_unshuffle2.y")) return rc;
+  if (int rc = chk(y4, "pixel_unshuffle2.y4")) return rc;
+  UBR_REQUIRE(y.h % 2 == 0 && y.w % 2 == 0 && y4.n == y.n && y4.h * 2 == y.h && y4.w * 2 == y.w && y4.c == 4 * y.c,
+              "pixel_unshuffle2: shape mismatch");
+  const long total = (long)y.n * y.h * y.w * (y.c / 8);
+  pixel_unshuffle2_kernel<<<ew_blocks(total), 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)y.ptr, y.ld, y4.n, y4.h,
+                                                                              y4.w, y.c, (__nv_bfloat16*)y4.ptr, y4.ld);
+  UBR_LAUNCH_CHECK("pixel_unshuffle2_kernel");
+  return 0;
+}
+
+int ubr_deconv4s2_wgrad_gather(const float* dw3, int in_ch, int out_ch, float* dw, int accumulate, void* stream) {
+  if (int rc = ensure_device()) return rc;
+  UBR_REQUIRE(dw3 != nullptr && dw != nullptr && in_ch > 0 && out_ch > 0, "deconv4s2_wgrad_gather: bad arguments");
+  const int total = in_ch * out_ch * 16;
+  deconv_wgrad_gather_kernel<<<(total + 255) / 256, 256, 0, (cudaStream_t)stream>>>(dw3, in_ch, out_ch, dw, accumulate);
+  UBR_LAUNCH_CHECK("deconv_wgrad_gather_kernel");
   return 0;
 }
 

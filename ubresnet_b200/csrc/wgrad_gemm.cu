@@ -244,14 +244,29 @@ static WPlan plan_wgrad(int grid_n, int grid_h, int grid_w, int m_ch, int n_ch, 
   pl.tiles_h = ceil_div(grid_h, pl.t.bh);
   pl.tiles_n = ceil_div(grid_n, pl.t.bn);
   pl.total_chunks = pl.tiles_w * pl.tiles_h * pl.tiles_n;
+  // split-K over pixel chunks.  One CTA per SM is resident (up to 192 KB of operand stages), so the grid runs in
+  // waves of 148 CTAs: pick the split count that minimises  waves x (chunks per CTA x t_chunk + fixed CTA cost)
+  // + the cost of writing and re-reading one fp32 partial per split (measured shape: profiles/r01f, wgrad_gemm at
+  // 21 % of the tensor peak with 7 splits = 336 CTAs = 2.3 waves on the 16^2 layers).
   const int base = pl.m_tiles * pl.ngroups * pl.n_tiles;
-  int target = ceil_div(2 * 148, base);
-  if (target < 1) target = 1;
-  int cps = ceil_div(pl.total_chunks, target);
-  if (cps < 4) cps = 4;
-  if (cps > pl.total_chunks) cps = pl.total_chunks;
-  pl.chunks_per_split = cps;
-  pl.splits = ceil_div(pl.total_chunks, cps);
+  const double t_chunk = pl.G * 8.0 * (pl.nt / 2 > 52 ? pl.nt / 2 : 52) / 1900.0;            // us of MMA issue per chunk
+  const double t_split = (double)m_ch * ntaps * n_ch * 8.0 / 5.0e6;                            // us: partial write + read
+  int best_s = 1;
+  double best_cost = 1e30;
+  const int max_s = pl.total_chunks < 296 ? pl.total_chunks : 296;
+  const uint32_t smem_cta = (uint32_t)pl.stages * pl.stage_bytes + 2048u;
+  int resident = (int)(232448u / smem_cta);                            // CTAs per SM by shared memory (TMEM: <= 512 columns)
+  if (resident * (int)pl.tmem_cols > 512) resident = 512 / (int)pl.tmem_cols;
+  if (resident < 1) resident = 1;
+  for (int s = 1; s <= max_s; ++s) {
+    const int cps = ceil_div(pl.total_chunks, s);
+    if (ceil_div(pl.total_chunks, cps) != s) continue;                 // not a distinct split count
+    const int waves = ceil_div(base * s, 148 * resident);
+    const double cost = waves * (cps * t_chunk + 3.0) + t_split * s;
+    if (cost < best_cost - 1e-9) { best_cost = cost; best_s = s; }
+  }
+  pl.chunks_per_split = ceil_div(pl.total_chunks, best_s);
+  pl.splits = ceil_div(pl.total_chunks, pl.chunks_per_split);
   return pl;
 }
 

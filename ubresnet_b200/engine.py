@@ -18,7 +18,7 @@ from .ops import Act
 
 class _ConvW:
     """bf16 packed operands of one conv / deconv parameter, refreshed when the parameter changes."""
-    __slots__ = ("param", "transposed", "fwd", "dgrad", "fwd3", "_key", "_dgrad_stale")
+    __slots__ = ("param", "transposed", "fwd", "dgrad", "fwd3", "dgrad3", "_key", "_dgrad_stale")
 
     def __init__(self, param, transposed=False):
         self.param = param
@@ -26,6 +26,7 @@ class _ConvW:
         self.fwd = None
         self.dgrad = None
         self.fwd3 = None            # ConvTranspose only: 3x3 sub-pixel forward operand (ops.pack_weights_subpixel)
+        self.dgrad3 = None          # ConvTranspose only: 3x3 sub-pixel data-gradient operand (4*out_ch <= 64)
         self._key = None
         self._dgrad_stale = False
 
@@ -33,12 +34,22 @@ class _ConvW:
         key = (self.param.data_ptr(), self.param._version)
         if key != self._key:
             self.fwd = ops.pack_weights(self.param, self.transposed, True)
-            self.fwd3 = ops.pack_weights_subpixel(self.param, True) if self.transposed else None
+            self.fwd3 = ops.pack_weights_subpixel(self.param, True) if self.sub_fwd() else None
             self.dgrad = None
+            self.dgrad3 = None
             self._key = key
         if need_dgrad and (self.dgrad is None or self._dgrad_stale):
             self.dgrad = ops.pack_weights(self.param, self.transposed, False)
+            self.dgrad3 = ops.pack_weights_subpixel(self.param, False) if self.sub_bwd() else None
             self._dgrad_stale = False
+
+    # sub-pixel (3x3 on the input grid) formulations of the ConvTranspose run on the halo-resident kernels, which
+    # take <= 64 input channels: forward needs in_ch <= 64, backward needs 4*out_ch <= 64 (and in_ch <= 64 for wgrad)
+    def sub_fwd(self):
+        return self.transposed and self.param.shape[0] <= 64
+
+    def sub_bwd(self):
+        return self.transposed and 4 * self.param.shape[1] <= 64 and self.param.shape[0] <= 64
 
     # ---- batched refresh (one launch for the whole network, Engine._refresh_packs)
     def dims(self):
@@ -61,7 +72,7 @@ class _ConvW:
             if self.fwd is None or self.fwd.device != self.param.device:
                 self.fwd = torch.empty((kh * kw + 1, pad(out_ch), pad(in_ch)), dtype=torch.bfloat16, device=self.param.device)
             res.append((lay, 1, kh, kw, self.fwd))
-            if self.transposed:
+            if self.sub_fwd():
                 if self.fwd3 is None or self.fwd3.device != self.param.device:
                     self.fwd3 = torch.empty((10, pad(4 * out_ch), pad(in_ch)), dtype=torch.bfloat16, device=self.param.device)
                 res.append((2, 1, 3, 3, self.fwd3))
@@ -69,6 +80,11 @@ class _ConvW:
             if self.dgrad is None or self.dgrad.device != self.param.device:
                 self.dgrad = torch.empty((kh * kw + 1, pad(in_ch), pad(out_ch)), dtype=torch.bfloat16, device=self.param.device)
             res.append((lay, 0, kh, kw, self.dgrad))
+            if self.sub_bwd():
+                if self.dgrad3 is None or self.dgrad3.device != self.param.device:
+                    self.dgrad3 = torch.empty((10, pad(in_ch), pad(4 * out_ch)), dtype=torch.bfloat16,
+                                              device=self.param.device)
+                res.append((2, 0, 3, 3, self.dgrad3))
             self._dgrad_stale = False
         elif changed:
             self._dgrad_stale = True
@@ -162,6 +178,8 @@ class Engine:
             hin, win = h // 2 ** i, w // 2 ** i
             shapes += [(n, hin, win, ci, cd, 16), (n, 2 * hin, 2 * win, cd, 2 * cd, 9), (n, 2 * hin, 2 * win, cd, cd, 9),
                        (n, 2 * hin, 2 * win, cd, 2 * cd, 1)]
+            if 4 * cd <= 64:
+                shapes.append((n, hin, win, 4 * cd, ci, 9))       # sub-pixel ConvTranspose weight gradient
         return shapes
 
     @staticmethod
@@ -242,6 +260,28 @@ class Engine:
         dy0 = ops.bn_act_bwd(dx0, saved["y0"], saved["st0"], True, bn_ws, grads[m.bn1.weight], grads[m.bn1.bias])
         ops.stem_conv_wgrad(saved["x"], dy0, grads[m.conv1.weight], grads[m.conv1.bias], False, stem_ws)
 
+    # ------------------------------------------------------------------ ConvTranspose (common_layers.py:125-128)
+    @staticmethod
+    def _deconv_fwd(x, wd, out_ch, y):
+        if wd.fwd3 is not None and ops.deconv_fwd_subpixel(x, wd.fwd3, out_ch, y):
+            return y
+        return ops.deconv_fwd(x, wd.fwd, out_ch, y=y)
+
+    @staticmethod
+    def _deconv_bwd(x, dy, wd, dw, wg_ws):
+        """weight gradient into `dw` (IOHW fp32); returns the data gradient.  High-resolution stages (4*out_ch <= 64,
+        W % 128 == 0) use the sub-pixel formulation on the halo-resident kernels: one pixel-unshuffle pass, then a 3x3
+        conv (data gradient) and a 3x3 weight gradient on the input grid."""
+        in_ch, out_ch = wd.param.shape[0], wd.param.shape[1]
+        if wd.dgrad3 is not None and x.w % 128 == 0:
+            dy4 = ops.pixel_unshuffle2(dy)
+            dw3 = torch.empty((4 * out_ch, in_ch, 3, 3), dtype=torch.float32, device=dw.device)
+            ops.conv2d_wgrad(x, dy4, 4 * out_ch, 3, 1, dw3, False, wg_ws)
+            ops.deconv_wgrad_gather(dw3, dw)
+            return ops.conv2d_fwd(dy4, wd.dgrad3, None, in_ch, 3, 1)
+        ops.deconv_wgrad(x, dy, dw, False, wg_ws)
+        return ops.deconv_dgrad(dy, wd.dgrad, in_ch)
+
     # ------------------------------------------------------------------ forward pieces
     def _block_fwd(self, blk, x, out, training, need_grad, bn_ws):
         rec = _BlockRec()
@@ -320,8 +360,7 @@ class Engine:
             layer = getattr(m, "dec_layer%d" % i)
             cd = p * 2 ** (i - 1)
             wd = self._pack(layer.deconv, need_grad, transposed=True)
-            if not ops.deconv_fwd_subpixel(cur, wd.fwd3, cd, Act(cat[i], 0, cd)):
-                ops.deconv_fwd(cur, wd.fwd, cd, y=Act(cat[i], 0, cd))
+            self._deconv_fwd(cur, wd, cd, Act(cat[i], 0, cd))
             dec_in[i] = cur
             cur, recs["dec%d" % i] = self._double_fwd(layer.res, Act(cat[i]), None, training, need_grad, bn_ws)
         # ---- head (:137-143)
@@ -398,9 +437,8 @@ class Engine:
             ddec = dcat.slice(0, cd)
             dskip[i - 1] = dcat.slice(cd, cd)                      # grad wrt x_{i-1}
             xin = saved["dec_in"][i]
-            ops.deconv_wgrad(xin, ddec, grads[layer.deconv.weight], False, wg_ws)
             wd = self._pack(layer.deconv, True, transposed=True)
-            dcur = ops.deconv_dgrad(ddec, wd.dgrad, p * 2 ** i)
+            dcur = self._deconv_bwd(xin, ddec, wd, grads[layer.deconv.weight], wg_ws)
             done("dec%d" % i)
         # ---- encoder, deep to shallow: grad(x_i) = (from enc_{i+1} | dec5 deconv) + skip grad
         for i in (5, 4, 3, 2, 1):
@@ -476,8 +514,7 @@ def run_submodule(module, *inputs):
             catbuf = torch.empty((n, hh, ww, cd + skip.shape[1]), dtype=torch.bfloat16, device=x.device)
             Act(catbuf, cd, skip.shape[1]).torch().copy_(skip.permute(0, 2, 3, 1))
             wd = eng._pack(module.deconv, False, transposed=True)
-            if not ops.deconv_fwd_subpixel(xa, wd.fwd3, cd, Act(catbuf, 0, cd)):
-                ops.deconv_fwd(xa, wd.fwd, cd, y=Act(catbuf, 0, cd))
+            eng._deconv_fwd(xa, wd, cd, Act(catbuf, 0, cd))
             out, _ = eng._double_fwd(module.res, Act(catbuf), None, module.training, False, bn_ws)
         else:
             raise RuntimeError("unsupported sub-module %s" % type(module).__name__)

@@ -49,6 +49,8 @@ class ASPPEngine(Engine):
             hin, win = h // 2 ** i, w // 2 ** i
             shapes += [(n, hin, win, ci, cd, 16), (n, 2 * hin, 2 * win, cr, cr_in, 9), (n, 2 * hin, 2 * win, cr, cr, 9),
                        (n, 2 * hin, 2 * win, cr, cr_in, 1)]
+            if 4 * cd <= 64:
+                shapes.append((n, hin, win, 4 * cd, ci, 9))
         return shapes
 
     # ------------------------------------------------------------------ ASPP forward / backward
@@ -145,8 +147,7 @@ class ASPPEngine(Engine):
             layer = getattr(m, "dec_layer%d" % i)
             cd = layer.deconv.out_channels
             wd = self._pack(layer.deconv, need_grad, transposed=True)
-            if not ops.deconv_fwd_subpixel(cur, wd.fwd3, cd, Act(cat[i], 0, cd)):
-                ops.deconv_fwd(cur, wd.fwd, cd, y=Act(cat[i], 0, cd))
+            self._deconv_fwd(cur, wd, cd, Act(cat[i], 0, cd))
             dec_in[i] = cur
             cur, recs["dec%d" % i] = self._double_fwd(layer.res, Act(cat[i]), None, training, need_grad, bn_ws)
         y10, st10, a10, logp = self._head_fwd(cur, training, need_grad, bn_ws)
@@ -174,9 +175,8 @@ class ASPPEngine(Engine):
             dcat = self._double_bwd(layer.res, recs["dec%d" % i], dcur, grads, bn_ws, wg_ws)
             ddec = dcat.slice(0, cd)
             dskip[i] = dcat.slice(cd, dcat.c - cd)
-            ops.deconv_wgrad(saved["dec_in"][i], ddec, grads[layer.deconv.weight], False, wg_ws)
             wd = self._pack(layer.deconv, True, transposed=True)
-            dcur = ops.deconv_dgrad(ddec, wd.dgrad, layer.deconv.in_channels)
+            dcur = self._deconv_bwd(saved["dec_in"][i], ddec, wd, grads[layer.deconv.weight], wg_ws)
         # dcur = grad wrt cat[aspp5, e5]; dskip[5] = grad wrt cat[aspp4, e4]; dskip[4] = grad wrt cat[aspp3, e3]
         d_as = {5: dcur.slice(0, 32 * p), 4: dskip[5].slice(0, 16 * p), 3: dskip[4].slice(0, 8 * p)}
         d_e = {5: dcur.slice(32 * p, 32 * p), 4: dskip[5].slice(16 * p, 16 * p), 3: dskip[4].slice(8 * p, 8 * p),

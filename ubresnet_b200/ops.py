@@ -232,6 +232,24 @@ def deconv_fwd_subpixel(x, wpk3, out_ch, y):
     return True
 
 
+def pixel_unshuffle2(y):
+    """(n, 2h, 2w, c) -> (n, h, w, 4c), channel (ph*2+pw)*c + co: ConvTranspose output gradient on the input grid."""
+    lib = _lib.load()
+    y4 = Act.empty(y.n, y.h // 2, y.w // 2, 4 * y.c, y.buf.device)
+    _lib.check(lib.ubr_pixel_unshuffle2(y.view(), y4.view(), _stream()), "pixel_unshuffle2")
+    return y4
+
+
+def deconv_wgrad_gather(dw3, dw, accumulate=False):
+    """dw3 fp32 [4*out_ch][in_ch][3][3] (sub-pixel weight gradient) -> ConvTranspose dw [in_ch][out_ch][4][4]."""
+    lib = _lib.load()
+    in_ch, out_ch = dw.shape[0], dw.shape[1]
+    assert dw3.shape == (4 * out_ch, in_ch, 3, 3) and dw3.is_contiguous() and dw.is_contiguous()
+    _lib.check(lib.ubr_deconv4s2_wgrad_gather(dw3.data_ptr(), in_ch, out_ch, dw.data_ptr(), int(accumulate), _stream()),
+               "deconv4s2_wgrad_gather")
+    return dw
+
+
 def deconv_dgrad(dy, wpk, in_ch, dx=None):
     lib = _lib.load()
     if dx is None:
