@@ -10,10 +10,16 @@ Data layout: activations NHWC bf16; `torch.cat([deconv, skip], 1)` is zero-copy 
 outputs are written directly into channel slices of the decoder's concat buffer.  Parameters stay fp32 in the
 reference layouts (state_dict compatibility); bf16 GEMM operand copies are re-derived when a parameter changes.
 """
+import os
+
 import torch
 
 from . import ops
 from .ops import Act
+
+# Weight gradients have no consumer inside the backward pass, so they run on a side stream concurrently with the
+# dgrad -> BN-backward chain of the main stream (deep 16^2..64^2 layers launch far fewer CTAs than the GPU has SMs).
+WGRAD_SIDE_STREAM = os.environ.get("UBR_WGRAD_STREAM", "1") != "0"
 
 
 class _ConvW:
@@ -102,7 +108,9 @@ class Engine:
         self._packs = {}
         self._ws = None
         self._ws_key = None
+        self._w_on = False
         self.grad_sink = None      # optional data-parallel gradient sink (ubresnet_b200.parallel.GradBuckets)
+        self._wstream = None       # side stream of the weight-gradient kernels (backward only)
 
     # ------------------------------------------------------------------ helpers
     def _pack(self, conv, need_dgrad, transposed=False):
@@ -201,6 +209,48 @@ class Engine:
         y = ops.conv2d_fwd(x, wpk, bias, out_ch, k, stride)
         return y, self._bn(y, bn, False, bn_ws)
 
+    # ------------------------------------------------------------------ weight gradients on a side stream
+    def _wgrad_begin(self, device):
+        if WGRAD_SIDE_STREAM and self._wstream is None:
+            self._wstream = torch.cuda.Stream(device=device)
+        self._w_on = WGRAD_SIDE_STREAM
+        self._w_keep = []          # inputs of side-stream kernels queued in the current stage (kept alive, see below)
+        self._w_prev = None        # (side-stream event, inputs) of the previous stage
+
+    def _wgrad(self, fn, *acts):
+        """Run `fn` (weight-gradient launches) on the side stream once the main stream has produced its inputs.
+        `acts` are inputs the main stream would otherwise release before the side kernels ran: they are kept alive
+        until the main stream has waited for the side stream (`_wgrad_stage`), which keeps the caching allocator's
+        reuse pattern deterministic (tensor.record_stream would make it depend on kernel timing)."""
+        if not self._w_on:
+            fn()
+            return
+        ev = torch.cuda.Event()
+        ev.record()
+        self._wstream.wait_event(ev)
+        with torch.cuda.stream(self._wstream):
+            fn()
+        self._w_keep.extend(acts)
+
+    def _wgrad_stage(self):
+        """Stage boundary: the main stream waits for the side stream's work of the PREVIOUS stage (already finished or
+        nearly so) and releases that stage's kept inputs."""
+        if not self._w_on:
+            return
+        ev = torch.cuda.Event()
+        ev.record(self._wstream)
+        if self._w_prev is not None:
+            torch.cuda.current_stream().wait_event(self._w_prev[0])
+        self._w_prev = (ev, self._w_keep)
+        self._w_keep = []
+
+    def _wgrad_join(self):
+        """main stream waits for every weight gradient queued so far (before a gradient bucket is reduced / returned)"""
+        if self._w_on:
+            torch.cuda.current_stream().wait_stream(self._wstream)
+            self._w_prev = None
+            self._w_keep = []
+
     # ------------------------------------------------------------------ stem / head (shared with engine_aspp)
     def _stem_fwd(self, x, x0_out, training, need_grad, bn_ws):
         """conv1 -> bn1 -> relu1 -> pool1 (ub_uresnet.py:94-97); x0 lands in `x0_out` (the dec1 skip slice)."""
@@ -241,14 +291,15 @@ class Engine:
         p = m.inplanes
         ncls = m.conv11.out_channels
         dl = ops.logsoftmax_bwd(saved["logp"], dlogp.float())
-        ops.conv2d_wgrad(saved["a10"], dl, ncls, 7, 1, grads[m.conv11.weight], False, wg_ws)
+        self._wgrad(lambda: ops.conv2d_wgrad(saved["a10"], dl, ncls, 7, 1, grads[m.conv11.weight], False, wg_ws), dl)
         grads[m.conv11.bias].copy_(_channel_sum(dl, ncls))
         w11 = self._pack(m.conv11, True)
         da10 = ops.conv2d_dgrad(dl, w11.dgrad, m.nkernels, 7, 1)
         del dl
         dy10 = ops.bn_act_bwd(da10, saved["y10"], saved["st10"], True, bn_ws, grads[m.bn10.weight], grads[m.bn10.bias])
         del da10
-        ops.conv2d_wgrad(saved["d1"], dy10, m.nkernels, 7, 1, grads[m.conv10.weight], False, wg_ws)
+        self._wgrad(lambda: ops.conv2d_wgrad(saved["d1"], dy10, m.nkernels, 7, 1, grads[m.conv10.weight], False, wg_ws),
+                    dy10)
         grads[m.conv10.bias].copy_(_channel_sum(dy10, m.nkernels))
         w10 = self._pack(m.conv10, True)
         return ops.conv2d_dgrad(dy10, w10.dgrad, p, 7, 1)
@@ -267,8 +318,7 @@ class Engine:
             return y
         return ops.deconv_fwd(x, wd.fwd, out_ch, y=y)
 
-    @staticmethod
-    def _deconv_bwd(x, dy, wd, dw, wg_ws):
+    def _deconv_bwd(self, x, dy, wd, dw, wg_ws):
         """weight gradient into `dw` (IOHW fp32); returns the data gradient.  High-resolution stages (4*out_ch <= 64,
         W % 128 == 0) use the sub-pixel formulation on the halo-resident kernels: one pixel-unshuffle pass, then a 3x3
         conv (data gradient) and a 3x3 weight gradient on the input grid."""
@@ -276,10 +326,13 @@ class Engine:
         if wd.dgrad3 is not None and x.w % 128 == 0:
             dy4 = ops.pixel_unshuffle2(dy)
             dw3 = torch.empty((4 * out_ch, in_ch, 3, 3), dtype=torch.float32, device=dw.device)
-            ops.conv2d_wgrad(x, dy4, 4 * out_ch, 3, 1, dw3, False, wg_ws)
-            ops.deconv_wgrad_gather(dw3, dw)
+
+            def wg():
+                ops.conv2d_wgrad(x, dy4, 4 * out_ch, 3, 1, dw3, False, wg_ws)
+                ops.deconv_wgrad_gather(dw3, dw)
+            self._wgrad(wg, dy4, dw3)
             return ops.conv2d_fwd(dy4, wd.dgrad3, None, in_ch, 3, 1)
-        ops.deconv_wgrad(x, dy, dw, False, wg_ws)
+        self._wgrad(lambda: ops.deconv_wgrad(x, dy, dw, False, wg_ws), dy)
         return ops.deconv_dgrad(dy, wd.dgrad, in_ch)
 
     # ------------------------------------------------------------------ forward pieces
@@ -383,14 +436,16 @@ class Engine:
             bn_ws, g[blk.bn2.weight], g[blk.bn2.bias], g[blk.bnpass.weight] if has_bp else None,
             g[blk.bnpass.bias] if has_bp else None)
         w2 = self._pack(blk.conv2, True)
-        ops.conv2d_wgrad(rec.a1, dy2, cout, 3, 1, g[blk.conv2.weight], False, wg_ws)
+        self._wgrad(lambda: ops.conv2d_wgrad(rec.a1, dy2, cout, 3, 1, g[blk.conv2.weight], False, wg_ws), dy2)
         da1 = ops.conv2d_dgrad(dy2, w2.dgrad, cout, 3, 1)
         del dy2
         dy1 = ops.bn_act_bwd(da1, rec.y1, rec.st1, True, bn_ws, g[blk.bn1.weight], g[blk.bn1.bias])
         del da1
-        ops.conv2d_wgrad(rec.x, dy1, cout, 3, s, g[blk.conv1.weight], False, wg_ws)
-        if has_bp:
-            ops.conv2d_wgrad(rec.x, dres, cout, 1, s, g[blk.bypass.weight], False, wg_ws)
+        def wg1():
+            ops.conv2d_wgrad(rec.x, dy1, cout, 3, s, g[blk.conv1.weight], False, wg_ws)
+            if has_bp:
+                ops.conv2d_wgrad(rec.x, dres, cout, 1, s, g[blk.bypass.weight], False, wg_ws)
+        self._wgrad(wg1, dy1, dres)
         if not need_dx:
             return None
         w1 = self._pack(blk.conv1, True)
@@ -423,7 +478,14 @@ class Engine:
             grads = {prm: sink.grad_buffer(prm) for prm in m.parameters()}
         else:
             grads = {prm: torch.empty_like(prm, dtype=torch.float32) for prm in m.parameters()}
-        done = sink.stage_done if sink is not None else (lambda name: None)
+        self._wgrad_begin(dev)
+
+        def done(name):
+            if sink is not None and sink.wants(name):
+                self._wgrad_join()             # the bucket's weight gradients must be complete before its all-reduce
+                sink.stage_done(name)
+            else:
+                self._wgrad_stage()
         # ---- head
         dcur = self._head_bwd(saved, dlogp, grads, bn_ws, wg_ws)
         done("head")
@@ -449,6 +511,7 @@ class Engine:
         # ---- stem: x0 gets the pool gradient plus the dec1 skip gradient (accumulated in place)
         self._stem_bwd(saved, dcur, dskip[0], grads, bn_ws, stem_ws)
         done("stem")
+        self._wgrad_join()
         if sink is not None:
             sink.finish()
         return grads

@@ -165,6 +165,7 @@ class ASPPEngine(Engine):
         if self.grad_sink is not None:
             raise RuntimeError("ASPP_ResNet: the data-parallel gradient buckets are only wired for UResNet")
         grads = {prm: torch.empty_like(prm, dtype=torch.float32) for prm in m.parameters()}
+        self._w_on = False         # all weight gradients in stream order (the ASPP ones share the wgrad workspace)
         recs = saved["recs"]
         dcur = self._head_bwd(saved, dlogp, grads, bn_ws, wg_ws)
         # ---- decoder, shallow to deep; dcat splits into [ddeconv | dskip]

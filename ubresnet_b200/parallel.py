@@ -68,6 +68,11 @@ class GradBuckets:
     def grad_buffer(self, param):
         return self.views[param]
 
+    def wants(self, stage):
+        """True when `stage` closes a bucket (its all-reduce is launched by stage_done)."""
+        b = BUCKET_OF_STAGE[stage]
+        return LAST_STAGE_OF_BUCKET[b] == stage and b in self.flat
+
     def stage_done(self, stage):
         b = BUCKET_OF_STAGE[stage]
         if LAST_STAGE_OF_BUCKET[b] != stage or b not in self.flat:
