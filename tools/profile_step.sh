@@ -7,12 +7,21 @@
 set -u
 TAG=${1:-prof}
 OUT=gpurun_out
-CMD="python bench.py --steps 1 --warmup 1 --no-cpu --no-infer"
+CMD="env UBR_WGRAD_STREAM=0 python bench.py --steps 1 --warmup 1 --no-cpu --no-infer"
 mkdir -p $OUT
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 6000 --csv --log-file $OUT/${TAG}_launches.csv $CMD > $OUT/${TAG}_ncu_list.log 2>&1
 echo "launch list rc=$?"
 M=gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum,sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active,sm__throughput.avg.pct_of_peak_sustained_elapsed,gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed,lts__t_sector_hit_rate.pct
-timeout 900 ncu --metrics $M --clock-control none -k regex:"conv_gemm_kernel|wgrad_gemm_kernel|halo_kernel" -c 2000 --csv --log-file $OUT/${TAG}_conv_traffic.csv $CMD > $OUT/${TAG}_ncu_traffic.log 2>&1
+# conv kernels per step: count them from the launch list, skip two steps, profile exactly one
+PER=$(python - <<PY
+import csv,re
+rows=[l for l in open("$OUT/${TAG}_launches.csv") if l.startswith('"')]
+n=sum(1 for r in csv.DictReader(rows) if re.search(r"conv_gemm_kernel|wgrad_gemm_kernel|halo_kernel", r["Kernel Name"]))
+print(n//6)
+PY
+)
+echo "conv kernel launches per step: $PER"
+timeout 900 ncu --metrics $M --clock-control none -k regex:"conv_gemm_kernel|wgrad_gemm_kernel|halo_kernel" --launch-skip $((2*PER)) -c $PER --csv --log-file $OUT/${TAG}_conv_traffic.csv $CMD > $OUT/${TAG}_ncu_traffic.log 2>&1
 echo "traffic pass rc=$?"
 timeout 600 ncu --set full --clock-control none --import-source on -k regex:"conv_gemm_kernel|wgrad_gemm_kernel" --launch-skip 290 -c 10 -o /tmp/${TAG}_gemm_full $CMD > $OUT/${TAG}_ncu_full.log 2>&1
 echo "set full rc=$?"
