@@ -554,6 +554,9 @@ CHECKS = {
     "halo_fwd_bn": lambda: (check_conv_fwd_bn(16, 16, 3, 2, 64, 128, seed=61) + check_conv_fwd_bn(32, 32, 3, 1, 32, 256, seed=62)
                             + check_conv_fwd_bn(16, 16, 7, 1, 32, 128, seed=63, bias=True) + check_conv_fwd_bn(64, 32, 1, 1, 32, 128, seed=64)
                             + check_conv_fwd_bn(64, 64, 3, 1, 32, 128, seed=65) + check_conv_fwd_bn(16, 32, 3, 2, 32, 32, seed=66)),
+    # statistics fused in the implicit-GEMM epilogue (C >= 128 / narrow layers): one partial row per 128-pixel tile
+    "gemm_fwd_bn": lambda: (check_conv_fwd_bn(128, 256, 3, 2, 16, 16, seed=67) + check_conv_fwd_bn(512, 512, 1, 4, 8, 8, seed=68, bias=True)
+                            + check_conv_fwd_bn(64, 128, 3, 8, 32, 32, seed=69) + check_conv_fwd_bn(256, 16, 3, 1, 24, 40, seed=70)),
     "halo_dgrad_acc": lambda: (check_conv_dgrad_acc(16, 16, 3, 2, 64, 128, seed=51) + check_conv_dgrad_acc(32, 16, 3, 1, 32, 256, seed=52)
                                + check_conv_dgrad_acc(64, 64, 3, 1, 32, 128, seed=53, expect_fused=False)
                                + check_conv_dgrad_acc(16, 16, 3, 1, 32, 32, seed=54, expect_fused=False)),

@@ -35,6 +35,8 @@ struct ConvGemmParams {
   int o_box_c;                  // channels per TMA store box
   const float* bias;
   float* out_f32;
+  float* stats;                 // out_mode 0: per-tile BN partials [tile][2][stats_c] (sum, sum of squares), or null
+  int stats_c;
   int out_ld, out_cols, out_n, out_h, out_w;
   int8_t dh[kMaxTaps], dw[kMaxTaps];
   uint8_t amap[kMaxTaps], slab[kMaxTaps];
@@ -53,6 +55,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_gemm_kernel(const __grid_con
   const uint32_t empty0 = bar_base + 8u * p.stages;
   const uint32_t accum_bar = bar_base + 16u * p.stages;
   const uint32_t tmem_slot = accum_bar + 8u;
+  float* s_part = reinterpret_cast<float*>(smem_raw + (tmem_slot + 8u - smem_u32(smem_raw)));   // [4 warps][2][nt]
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -165,9 +168,34 @@ __global__ void __launch_bounds__(kThreads, 1) conv_gemm_kernel(const __grid_con
         const uint32_t a1 = base + (((q + 1u) ^ xr) << 4);
         asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a0), "r"(pk[0]), "r"(pk[1]), "r"(pk[2]), "r"(pk[3]) : "memory");
         asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a1), "r"(pk[4]), "r"(pk[5]), "r"(pk[6]), "r"(pk[7]) : "memory");
+        if (p.stats) {
+          // BatchNorm statistics of the STORED (bf16-rounded) values, like the stand-alone bn_stats kernel
+          float g[16], q[16];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const float2 t = unpack_bf16x2(pk[j]);
+            g[2 * j] = t.x; g[2 * j + 1] = t.y;
+            q[2 * j] = t.x * t.x; q[2 * j + 1] = t.y * t.y;
+          }
+          const float rs = warp_reduce_scatter16(g, lane), rq = warp_reduce_scatter16(q, lane);
+          if ((lane & 1) == 0) {
+            s_part[(quad * 2 + 0) * p.nt + c + (lane >> 1)] = rs;
+            s_part[(quad * 2 + 1) * p.nt + c + (lane >> 1)] = rq;
+          }
+        }
       }
       fence_proxy_async_smem();
       asm volatile("bar.sync 1, 128;" ::: "memory");
+      if (p.stats) {
+        // fixed-order sum over the four epilogue warps -> one partial row per tile (deterministic)
+        const int e = (int)threadIdx.x - 64;
+        for (int i = e; i < 2 * p.nt; i += 128) {
+          const int k = i / p.nt, ch = i % p.nt;
+          const float v = s_part[(0 * 2 + k) * p.nt + ch] + s_part[(1 * 2 + k) * p.nt + ch] +
+                          s_part[(2 * 2 + k) * p.nt + ch] + s_part[(3 * 2 + k) * p.nt + ch];
+          p.stats[((size_t)blockIdx.x * 2 + k) * (size_t)p.stats_c + co0 + ch] = v;
+        }
+      }
       if (warp == 2 && lane == 0) {
         const int nblk = p.nt / bc;
         for (int b = 0; b < nblk; ++b)
@@ -300,7 +328,7 @@ static int launch_conv_gemm(ConvGemmParams& p, int grid_n, int grid_h, int grid_
   uint32_t data = (uint32_t)stages * stage;
   const uint32_t staging = 128u * p.nt * 2u;
   if (data < staging) data = staging;
-  const uint32_t smem = data + 16u * stages + 16u + 1024u;
+  const uint32_t smem = data + 16u * stages + 16u + 1024u + 4096u + 16u;      // + [4][2][nt] fp32 statistics scratch
   static bool attr_set = false;
   if (!attr_set) {
     UBR_CUDA_OK(cudaFuncSetAttribute(conv_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
@@ -383,7 +411,14 @@ static int conv2d_fwd_impl(ubr_view x, const void* wpk, const float* bias, int o
                                   out_ch, (cudaStream_t)stream, 0, stats, stats_rows);
     if (hrc <= 0) return hrc;
   }
-  if (stats) return 1;             // no fused-statistics path for this shape: caller runs conv + bn_stats
+  if (stats) {
+    // fused statistics in the implicit-GEMM epilogue: full tiles only (a zero-filled pixel would still add the bias)
+    const int tiles = ceil_div(wo, t.bw) * ceil_div(ho, t.bh) * ceil_div(x.n, t.bn);
+    if (y_f32 || wo % t.bw || ho % t.bh || x.n % t.bn || tiles > kMaxStatsRows || out_ch % 16) return 1;
+    p.stats = stats;
+    p.stats_c = out_ch;
+    *stats_rows = tiles;
+  }
   p.bias = bias;
   if (y_f32) {
     p.out_mode = 1; p.out_f32 = y_f32; p.out_ld = y_f32_ld; p.out_cols = out_ch;

@@ -78,22 +78,6 @@ __device__ __forceinline__ void mma_lohi(uint32_t d_tmem, uint32_t alo, uint32_t
   }
 }
 
-// Warp reduce-scatter of 16 per-lane values over the 32 lanes: 16 shuffles instead of 80.  On return lane l holds
-// in the result the warp total of channel (l >> 1) & 15 (both lanes of a pair hold the same total).
-__device__ __forceinline__ float warp_reduce_scatter16(float (&v)[16], int lane) {
-#pragma unroll
-  for (int h = 8, m = 16; h >= 1; h >>= 1, m >>= 1) {
-    const bool up = (lane & m) != 0;
-#pragma unroll
-    for (int i = 0; i < h; ++i) {
-      const float send = up ? v[i] : v[i + h];
-      const float keep = up ? v[i + h] : v[i];
-      v[i] = keep + __shfl_xor_sync(0xffffffffu, send, m);
-    }
-  }
-  return v[0] + __shfl_xor_sync(0xffffffffu, v[0], 1);
-}
-
 template <int KS, int KSTEPS>
 __global__ void __launch_bounds__(kHThreads, 1) conv_halo_kernel(const __grid_constant__ HaloParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];

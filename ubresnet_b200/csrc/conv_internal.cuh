@@ -6,6 +6,27 @@ namespace ubr {
 
 struct TapSpec { int dh, dw, amap, slab; };
 
+#ifdef __CUDACC__
+// Warp reduce-scatter of 16 per-lane values over the 32 lanes: 16 shuffles instead of 80.  On return lane l holds
+// in the result the warp total of channel (l >> 1) & 15 (both lanes of a pair hold the same total).
+__device__ __forceinline__ float warp_reduce_scatter16(float (&v)[16], int lane) {
+#pragma unroll
+  for (int h = 8, m = 16; h >= 1; h >>= 1, m >>= 1) {
+    const bool up = (lane & m) != 0;
+#pragma unroll
+    for (int i = 0; i < h; ++i) {
+      const float send = up ? v[i] : v[i + h];
+      const float keep = up ? v[i + h] : v[i];
+      v[i] = keep + __shfl_xor_sync(0xffffffffu, send, m);
+    }
+  }
+  return v[0] + __shfl_xor_sync(0xffffffffu, v[0], 1);
+}
+#endif
+
+// fused BatchNorm statistics: a conv launch may emit at most this many partial rows [2][c] into the bn workspace
+constexpr int kMaxStatsRows = 1184;
+
 // Halo-resident kernel (conv_halo.cu).  Returns 0 = launched, 1 = shape not eligible (caller falls back to the
 // tap-by-tap kernel), <0 = error.  `y` (bf16 view) or `y_f32` (fp32 [pixel][ld]) selects the output mode.
 int conv_halo_try(const ubr_view& x, const void* wpk, int nslabs, int n_pad, const TapSpec* taps, int ntaps,

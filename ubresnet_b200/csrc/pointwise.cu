@@ -893,7 +893,7 @@ int ubr_bn_finalize_rows(const void* workspace, int rows, int c, double count, c
                          float* mean, float* invstd, void* stream) {
   if (int rc = ensure_device()) return rc;
   UBR_REQUIRE(workspace && scale && shift, "bn_finalize_rows: null pointer");
-  UBR_REQUIRE(c > 0 && c % 8 == 0 && count >= 1.0 && rows >= 1 && rows <= kRedBlocks, "bn_finalize_rows: bad c/count/rows");
+  UBR_REQUIRE(c > 0 && c % 8 == 0 && count >= 1.0 && rows >= 1 && rows <= 2 * kRedBlocks, "bn_finalize_rows: bad c/count/rows");
   bn_finalize_kernel<<<ceil_div(c, 32), dim3(32, kColLanes), 0, (cudaStream_t)stream>>>((const float*)workspace, rows, c, count,
                                                                                       gamma, beta, running_mean, running_var,
                                                                                       momentum, eps, scale, shift, mean, invstd);
