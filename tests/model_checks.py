@@ -88,10 +88,11 @@ def build_pair(num_classes=3, inplanes=16, seed=1234, warm_bn=True, arch="uresne
     return model.to(DEV), sd
 
 
-def train_parity(batch=2, size=128, num_classes=3, dense=False, seed=1234, arch="uresnet"):
-    model, sd = build_pair(num_classes=num_classes, seed=seed, arch=arch)
+def train_parity(batch=2, size=128, num_classes=3, dense=False, seed=1234, arch="uresnet", inplanes=16):
+    model, sd = build_pair(num_classes=num_classes, inplanes=inplanes, seed=seed, arch=arch)
     port = aspp_port if arch == "aspp" else globals()["port"]
-    img, lab, wgt = synthetic.make_batch(batch, size, size, dense=dense)
+    hh, ww = size if isinstance(size, tuple) else (size, size)
+    img, lab, wgt = synthetic.make_batch(batch, hh, ww, dense=dense)
     if num_classes > 3:
         lab = lab.clone()
         lab[:, :4, :4] = num_classes - 1
@@ -221,6 +222,8 @@ CHECKS = {
     "train_128": lambda: train_parity(2, 128),
     "train_dense_64": lambda: train_parity(4, 64, dense=True, seed=99),
     "train_256_c4": lambda: train_parity(1, 256, num_classes=4, seed=5),
+    "train_odd_3x96x160": lambda: train_parity(3, (96, 160), dense=True, seed=31),      # partial tiles, odd batch
+    "train_inplanes32_128": lambda: train_parity(2, 128, inplanes=32, seed=41),   # train_ubresnet2018_wlarcv2.py:88
     "eval_128": lambda: eval_parity(2, 128),
     "golden": lambda: golden_parity(),
     # ASPP_ResNet (BASELINE.json configs[4]; reference models/ASPP_ResNet.py)
