@@ -27,6 +27,14 @@ __device__ __forceinline__ float warp_reduce_scatter16(float (&v)[16], int lane)
 // fused BatchNorm statistics: a conv launch may emit at most this many partial rows [2][c] into the bn workspace
 constexpr int kMaxStatsRows = 1184;
 
+// Tensor-core stem (stem_tc.cu): 1 -> 16 channels, 7x7, for w % 128 == 0 and h % 8 == 0; stem.cu keeps the other shapes.
+constexpr int kStemTcMaxBlocks = 592;          // persistent CTAs (4 per SM); the weight gradient keeps one partial each
+bool stem_tc_eligible(int n, int h, int w, int out_ch);
+int stem_tc_fwd(const float* x, int n, int h, int w, const float* wgt, const float* bias, __nv_bfloat16* y, int yld,
+                cudaStream_t stream);
+int stem_tc_wgrad(const float* x, int n, int h, int w, const __nv_bfloat16* dy, int dyld, float* dw, float* dbias,
+                  int accumulate, float* workspace, cudaStream_t stream);
+
 // Halo-resident kernel (conv_halo.cu).  Returns 0 = launched, 1 = shape not eligible (caller falls back to the
 // tap-by-tap kernel), <0 = error.  `y` (bf16 view) or `y_f32` (fp32 [pixel][ld]) selects the output mode.
 int conv_halo_try(const ubr_view& x, const void* wpk, int nslabs, int n_pad, const TapSpec* taps, int ntaps,

@@ -2,6 +2,7 @@
 // (reference models/ub_uresnet.py:41,94).  Cin = 1 means K = 49: not a tensor-core GEMM.  Direct
 // CUDA-core kernels; forward is bounded by the bf16 NHWC write (32 B/pixel for OC = 16).
 #include "common.cuh"
+#include "conv_internal.cuh"
 
 namespace ubr {
 
@@ -214,6 +215,8 @@ int ubr_stem_conv_fwd(const float* x, int n, int h, int w, const float* wgt, con
   UBR_REQUIRE(out_ch > 0 && out_ch % 16 == 0, "stem_conv_fwd: out_ch=%d must be a multiple of 16", out_ch);
   UBR_REQUIRE(y.n == n && y.h == h && y.w == w && y.c == out_ch && y.ld >= out_ch && y.ld % 8 == 0,
               "stem_conv_fwd: output view mismatch");
+  if (stem_tc_eligible(n, h, w, out_ch))
+    return stem_tc_fwd(x, n, h, w, wgt, bias, (__nv_bfloat16*)y.ptr, y.ld, (cudaStream_t)stream);
   dim3 grid(ceil_div(w, kFTW), ceil_div(h, kFTH), n * (out_ch / 16));
   stem_fwd_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(x, n, h, w, wgt, bias, out_ch, (__nv_bfloat16*)y.ptr, y.ld);
   UBR_LAUNCH_CHECK("stem_fwd_kernel");
@@ -222,7 +225,9 @@ int ubr_stem_conv_fwd(const float* x, int n, int h, int w, const float* wgt, con
 
 uint64_t ubr_stem_wgrad_workspace_bytes(int n, int h, int w, int out_ch) {
   (void)n; (void)h; (void)w;
-  return (uint64_t)kWgBlocks * (out_ch / 16) * 800 * sizeof(float);
+  const uint64_t cc = (uint64_t)kWgBlocks * (out_ch / 16) * 800 * sizeof(float);
+  const uint64_t tc = (uint64_t)kStemTcMaxBlocks * 128 * 16 * sizeof(float);
+  return cc > tc ? cc : tc;
 }
 
 int ubr_stem_conv_wgrad(const float* x, int n, int h, int w, ubr_view dy, float* dw, float* dbias, int accumulate,
@@ -232,6 +237,8 @@ int ubr_stem_conv_wgrad(const float* x, int n, int h, int w, ubr_view dy, float*
   UBR_REQUIRE(dy.c % 16 == 0 && dy.n == n && dy.h == h && dy.w == w, "stem_conv_wgrad: dy view mismatch");
   UBR_REQUIRE(workspace_bytes >= ubr_stem_wgrad_workspace_bytes(n, h, w, dy.c), "stem_conv_wgrad: workspace too small");
   cudaStream_t st = (cudaStream_t)stream;
+  if (stem_tc_eligible(n, h, w, dy.c) && dy.ld % 8 == 0)
+    return stem_tc_wgrad(x, n, h, w, (const __nv_bfloat16*)dy.ptr, dy.ld, dw, dbias, accumulate, (float*)workspace, st);
   stem_wgrad_kernel<<<kWgBlocks, 256, 0, st>>>(x, n, h, w, (const __nv_bfloat16*)dy.ptr, dy.ld, dy.c, (float*)workspace);
   UBR_LAUNCH_CHECK("stem_wgrad_kernel");
   const int total = (dy.c / 16) * 800;
