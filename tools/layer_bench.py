@@ -102,6 +102,22 @@ def main():
         print("%-18s %4d %4d 4 T %4d | %7.3f %6.0f %6.1f | %7.3f %6.0f | %7.3f %6.0f" %
               (name, cin, cout, res, t_f, byt / t_f / 1e6, fl / t_f / 1e9, t_d, byt / t_d / 1e6, t_w, byt / t_w / 1e6), flush=True)
         del x, dy, y, dx, ws
+    if not args.name or args.name in "conv1.stem":
+        # stem: fp32 1-channel input -> 16 bf16 channels (7x7); bytes = read x (4 B/px) + write y or read dy (32 B/px)
+        res = 512
+        x = torch.randn(B, 1, res, res, device=DEV) * 30
+        w = torch.randn(16, 1, 7, 7, device=DEV) * 0.05
+        b = torch.zeros(16, device=DEV)
+        y = Act(torch.empty(B, res, res, 16, device=DEV, dtype=torch.bfloat16))
+        dy = Act(torch.randn(B, res, res, 16, device=DEV).to(torch.bfloat16))
+        dw, db = torch.empty_like(w), torch.empty_like(b)
+        ws = torch.empty(ops.stem_wgrad_workspace_bytes(B, res, res, 16) // 4, dtype=torch.float32, device=DEV)
+        t_f = timeit(lambda: ops.stem_conv_fwd(x, w, b, y=y))
+        t_w = timeit(lambda: ops.stem_conv_wgrad(x, dy, dw, db, False, ws))
+        byt = 36.0 * B * res * res
+        print("%-18s %4d %4d 7 1 %4d | %7.3f %6.0f %6.1f |       -      - | %7.3f %6.0f" %
+              ("conv1.stem", 1, 16, res, t_f, byt / t_f / 1e6, 2.0 * B * res * res * 16 * 49 / t_f / 1e9, t_w,
+               byt / t_w / 1e6), flush=True)
     print("sum (one of each listed layer): fwd %.3f dgrad %.3f wgrad %.3f ms" % tuple(tot))
 
 

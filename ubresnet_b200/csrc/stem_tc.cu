@@ -21,8 +21,11 @@
 namespace ubr {
 
 constexpr int kSTThreads = 256;
-constexpr int kXsCols = 144;                 // staged input columns per row (136 used), bf16
-constexpr uint32_t kXsBytes = 8u * kXsCols * 2u;   // one staging array: ring of 8 rows
+// staged input row: 136 bf16 columns (w0-3 .. w0+132).  The 272-byte pitch puts the 8 ring rows 4 banks apart, so the
+// 8 lanes of a quarter-warp that read 16 bytes of 8 different rows touch all 32 banks once.
+constexpr int kXsCols = 136;
+constexpr uint32_t kXsPitch = kXsCols * 2u;
+constexpr uint32_t kXsBytes = 8u * kXsPitch;        // one staging array: ring of 8 rows
 
 struct StemTcParams {
   const float* x;                            // [n][h][w] fp32
@@ -40,7 +43,7 @@ struct StemTcParams {
 // shared memory (offsets from a 1024-byte aligned base)
 //   [0, 16K)      P_hi    [16K, 32K)  P_lo          im2col tiles, 128 rows x 128 B, SW128
 //   [32K, 40K)    fwd: W_hi (2 KB) at +0, W_lo at +2048;   wgrad: dy tile (4 KB, SW32)
-//   [40K, ...)    4 staging arrays: {hi, lo} x {xs0[i] = x(i), xs1[i] = x(i+1)}, each a ring of 8 rows
+//   [40K, ...)    2 staging arrays (hi, lo terms of x), each a ring of 8 rows
 struct StemSmem {
   uint32_t a_hi, a_lo, aux, xs, bar, tslot;
 };
@@ -50,19 +53,17 @@ __device__ __forceinline__ StemSmem stem_smem_layout(uint32_t base) {
   s.a_lo = base + 16384u;
   s.aux = base + 32768u;
   s.xs = s.aux + 8192u;
-  s.bar = s.xs + 4u * kXsBytes;
+  s.bar = s.xs + 2u * kXsBytes;
   s.tslot = s.bar + 16u;
   return s;
 }
-constexpr uint32_t kStemSmemBytes = 32768u + 8192u + 4u * kXsBytes + 32u + 1024u;
+constexpr uint32_t kStemSmemBytes = 32768u + 8192u + 2u * kXsBytes + 32u + 1024u;
 
 __device__ __forceinline__ void sts128(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
   asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
 }
-__device__ __forceinline__ uint32_t lds32(uint32_t addr) {
-  uint32_t v;
-  asm volatile("ld.shared.b32 %0, [%1];" : "=r"(v) : "r"(addr));
-  return v;
+__device__ __forceinline__ void lds128(uint32_t addr, uint32_t& a, uint32_t& b, uint32_t& c, uint32_t& d) {
+  asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(a), "=r"(b), "=r"(c), "=r"(d) : "r"(addr));
 }
 __device__ __forceinline__ void sts16(uint32_t addr, uint16_t v) {
   asm volatile("st.shared.b16 [%0], %1;" ::"r"(addr), "h"(v) : "memory");
@@ -88,37 +89,41 @@ __device__ __forceinline__ void stem_put_row(const StemSmem& s, int hh, float v)
   if (i < 136u) {
     uint16_t hi, lo;
     split_bf16(v, hi, lo);
-    const uint32_t e = (slot * kXsCols + i) * 2u;
+    const uint32_t e = slot * kXsPitch + i * 2u;
     sts16(s.xs + e, hi);
-    sts16(s.xs + 2u * kXsBytes + e, lo);
-    if (i >= 1u) {
-      sts16(s.xs + kXsBytes + e - 2u, hi);
-      sts16(s.xs + 3u * kXsBytes + e - 2u, lo);
-    }
+    sts16(s.xs + kXsBytes + e, lo);
   }
 }
 
-// im2col tiles (hi and lo) of the 128 pixels (h, w0 .. w0+127): thread <-> (pixel, 4 of the 8 chunks)
+// im2col tiles of the 128 pixels (h, w0 .. w0+127).  Warps 0-3 build P_hi, warps 4-7 P_lo; within a warp the lane is
+// (filter row r = lane & 7, run = lane >> 3): the thread loads the 16 staged inputs under a run of 8 consecutive
+// pixels of its filter row (2 x 16 bytes) and writes the 8 pixels' chunks, each the 8-input window starting one
+// element further (odd starts by funnel shift).  A quarter-warp = the 8 chunks of ONE pixel row of the tile = 128
+// contiguous bytes (swizzled order): loads and stores are bank-conflict free.  r = 7 is the constant chunk.
 __device__ __forceinline__ void stem_build_tiles(const StemSmem& s, int h) {
-  const int px = threadIdx.x & 127;
-  const int r0 = (threadIdx.x >> 7) * 4;
-  // element px of the staged row starts a 4-byte word in xs0 (px even) or xs1 (px odd)
-  const uint32_t src = s.xs + ((px & 1) ? kXsBytes : 0u) + (uint32_t)(px >> 1) * 4u;
-  const uint32_t row = (uint32_t)px * 128u;
+  const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+  const uint32_t r = lane & 7u;
+  const uint32_t q = (lane >> 3) + 4u * (warp & 3u);                     // run of pixels 8q .. 8q+7
+  const bool lo = warp >= 4u;
+  const uint32_t tile = (lo ? s.a_lo : s.a_hi) + q * 1024u;
+  uint32_t w[8];
+  {
+    const uint32_t slot = (uint32_t)(h + (int)r - 3 + 8) & 7u;           // (r = 7 reads a valid but unused row)
+    const uint32_t src = s.xs + (lo ? kXsBytes : 0u) + slot * kXsPitch + q * 16u;
+    lds128(src, w[0], w[1], w[2], w[3]);
+    lds128(src + 16u, w[4], w[5], w[6], w[7]);
+  }
+  const bool konst = r == 7u;
+  const uint32_t one = lo ? 0u : 0x00003F80u;                            // k = 56: constant 1 (bias-gradient row)
 #pragma unroll
-  for (int j = 0; j < 4; ++j) {
-    const int r = r0 + j;
-    const uint32_t dst = row + (((uint32_t)r ^ ((uint32_t)px & 7u)) << 4);
-    if (r < 7) {
-      const uint32_t slot = (uint32_t)(h + r - 3 + 8) & 7u;
-      const uint32_t q = src + slot * (kXsCols * 2u);
-      sts128(s.a_hi + dst, lds32(q), lds32(q + 4u), lds32(q + 8u), lds32(q + 12u));
-      const uint32_t ql = q + 2u * kXsBytes;
-      sts128(s.a_lo + dst, lds32(ql), lds32(ql + 4u), lds32(ql + 8u), lds32(ql + 12u));
-    } else {
-      sts128(s.a_hi + dst, 0x00003F80u, 0u, 0u, 0u);         // k = 56: constant 1 (bias-gradient row), k > 56: 0
-      sts128(s.a_lo + dst, 0u, 0u, 0u, 0u);
-    }
+  for (int i = 0; i < 8; ++i) {
+    uint32_t c[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+      c[j] = (i & 1) ? __funnelshift_r(w[(i >> 1) + j], w[(i >> 1) + j + 1 < 8 ? (i >> 1) + j + 1 : 7], 16)
+                     : w[(i >> 1) + j];
+    if (konst) { c[0] = one; c[1] = 0u; c[2] = 0u; c[3] = 0u; }
+    sts128(tile + (uint32_t)i * 128u + ((r ^ (uint32_t)i) << 4), c[0], c[1], c[2], c[3]);
   }
 }
 
@@ -134,22 +139,25 @@ __device__ __forceinline__ StemStrip stem_strip(const StemTcParams& p, int strip
 }
 
 // ------------------------------------------------------------------------------------------------ forward
+// accumulator columns 0..15 = P_hi W_hi + P_lo W_hi, 16..31 = P_hi W_lo
 __device__ __forceinline__ void stem_fwd_store(const StemTcParams& p, uint32_t taddr, const float (&bias_r)[16],
                                                size_t pixel) {
-  uint32_t v[16];
+  uint32_t v[16], u[16];
   tmem_ld16(taddr, v);
+  tmem_ld16(taddr + 16u, u);
   tmem_ld_wait();
   tc_fence_before();
   uint32_t pk[8];
 #pragma unroll
   for (int j = 0; j < 8; ++j)
-    pk[j] = pack_bf16x2(__uint_as_float(v[2 * j]) + bias_r[2 * j], __uint_as_float(v[2 * j + 1]) + bias_r[2 * j + 1]);
+    pk[j] = pack_bf16x2(__uint_as_float(v[2 * j]) + __uint_as_float(u[2 * j]) + bias_r[2 * j],
+                        __uint_as_float(v[2 * j + 1]) + __uint_as_float(u[2 * j + 1]) + bias_r[2 * j + 1]);
   __nv_bfloat16* dst = p.y + pixel * (size_t)p.yld;
   *reinterpret_cast<uint4*>(dst) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
   *reinterpret_cast<uint4*>(dst + 8) = make_uint4(pk[4], pk[5], pk[6], pk[7]);
 }
 
-__global__ void __launch_bounds__(kSTThreads) stem_tc_fwd_kernel(const StemTcParams p) {
+__global__ void __launch_bounds__(kSTThreads, 4) stem_tc_fwd_kernel(const StemTcParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const StemSmem s = stem_smem_layout(base);
@@ -160,7 +168,7 @@ __global__ void __launch_bounds__(kSTThreads) stem_tc_fwd_kernel(const StemTcPar
     fence_mbar_init();
   }
   if (warp == 0) {
-    tmem_alloc_dyn(s.tslot, 32);
+    tmem_alloc_dyn(s.tslot, 64);
     tmem_relinquish();
   }
   // weight tiles W_hi / W_lo [16 co][64 k], K-major SW128 (slot 7 of every filter row and k >= 56 are zero)
@@ -188,44 +196,52 @@ __global__ void __launch_bounds__(kSTThreads) stem_tc_fwd_kernel(const StemTcPar
   uint32_t tmem_base;
   asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(s.tslot));
 
-  const uint32_t idesc = make_idesc_bf16(128, 16, 0, 0);
+  // B operands: [W_hi ; W_lo] as one 32-row tile (N = 32) for P_hi, its first 16 rows (N = 16) for P_lo
+  const uint32_t idesc32 = make_idesc_bf16(128, 32, 0, 0), idesc16 = make_idesc_bf16(128, 16, 0, 0);
   float bias_r[16];
 #pragma unroll
   for (int j = 0; j < 16; ++j) bias_r[j] = p.bias ? __ldg(p.bias + j) : 0.f;
   const uint32_t lane_off = (uint32_t)((warp & 3) * 32) << 16;
 
-  uint32_t t = 0;                    // tiles issued by this CTA; tile t accumulates in TMEM columns (t & 1) * 16
+  uint32_t t = 0;                    // tiles issued by this CTA; tile t accumulates in TMEM columns (t & 1) * 32
   size_t prev_pix = 0;               // first output pixel of tile t-1
   for (int strip = blockIdx.x; strip < p.nstrips; strip += gridDim.x) {
     const StemStrip st = stem_strip(p, strip);
-    __syncthreads();                 // every thread is done with the previous strip's staged rows
-    for (int hh = st.h0 - 3; hh <= st.h0 + 3; ++hh) stem_put_row(s, hh, stem_fetch_row(p, st.n, hh, st.w0));
+    {                                // (the previous strip's last tile was built before its MMA-issue barrier)
+      float v[7];
+#pragma unroll
+      for (int i = 0; i < 7; ++i) v[i] = stem_fetch_row(p, st.n, st.h0 - 3 + i, st.w0);
+#pragma unroll
+      for (int i = 0; i < 7; ++i) stem_put_row(s, st.h0 - 3 + i, v[i]);
+    }
+    __syncthreads();                 // the strip's first rows are staged
+    float pend = stem_fetch_row(p, st.n, st.h0 + 4, st.w0);             // rows are fetched two tiles ahead of their use
     for (int h = st.h0; h < st.h0 + p.bh; ++h, ++t) {
-      const float nxt = stem_fetch_row(p, st.n, h + 4, st.w0);          // in flight while this tile is built
-      if (t >= 1) mbar_wait(s.bar, (t - 1u) & 1u);                      // MMA(t-1) has consumed the tile buffers
-      __syncthreads();
+      const float nxt = stem_fetch_row(p, st.n, h + 5, st.w0);
+      // MMA(t-1) has consumed the tile buffers.  No CTA barrier here: staged rows, TMEM reuse and the ring slot
+      // written below are all ordered by the barrier that precedes each MMA issue.
+      if (t >= 1) mbar_wait(s.bar, (t - 1u) & 1u);
       stem_build_tiles(s, h);
-      stem_put_row(s, h + 4, nxt);                                      // ring slot of row h-4: not part of this tile
+      stem_put_row(s, h + 4, pend);                                     // ring slot of row h-4: not part of this tile
+      pend = nxt;
       fence_proxy_async_smem();
       tc_fence_before();
       __syncthreads();
       if (threadIdx.x == 0) {
         tc_fence_after();
         const uint64_t a_hi = make_smem_desc(s.a_hi, 0, 1024u, 2u), a_lo = make_smem_desc(s.a_lo, 0, 1024u, 2u);
-        const uint64_t w_hi = make_smem_desc(s.aux, 0, 1024u, 2u), w_lo = make_smem_desc(s.aux + 2048u, 0, 1024u, 2u);
-        const uint32_t d = tmem_base + (t & 1u) * 16u;
+        const uint64_t wdesc = make_smem_desc(s.aux, 0, 1024u, 2u);
+        const uint32_t d = tmem_base + (t & 1u) * 32u;
 #pragma unroll
-        for (int k = 0; k < 4; ++k) tc_mma_bf16(d, a_lo + (uint64_t)(2 * k), w_hi + (uint64_t)(2 * k), idesc, k > 0 ? 1u : 0u);
+        for (int k = 0; k < 4; ++k) tc_mma_bf16(d, a_hi + (uint64_t)(2 * k), wdesc + (uint64_t)(2 * k), idesc32, k > 0 ? 1u : 0u);
 #pragma unroll
-        for (int k = 0; k < 4; ++k) tc_mma_bf16(d, a_hi + (uint64_t)(2 * k), w_lo + (uint64_t)(2 * k), idesc, 1u);
-#pragma unroll
-        for (int k = 0; k < 4; ++k) tc_mma_bf16(d, a_hi + (uint64_t)(2 * k), w_hi + (uint64_t)(2 * k), idesc, 1u);
+        for (int k = 0; k < 4; ++k) tc_mma_bf16(d, a_lo + (uint64_t)(2 * k), wdesc + (uint64_t)(2 * k), idesc16, 1u);
         tc_commit(s.bar);
       }
       // epilogue of tile t-1 (its MMAs were waited for above): overlaps MMA(t) and the other warps' next fetch
       if (t >= 1 && warp < 4) {
         tc_fence_after();
-        stem_fwd_store(p, tmem_base + ((t - 1u) & 1u) * 16u + lane_off, bias_r, prev_pix + (size_t)(warp * 32 + lane));
+        stem_fwd_store(p, tmem_base + ((t - 1u) & 1u) * 32u + lane_off, bias_r, prev_pix + (size_t)(warp * 32 + lane));
       }
       prev_pix = ((size_t)st.n * p.h + h) * (size_t)p.w + st.w0;
     }
@@ -233,13 +249,13 @@ __global__ void __launch_bounds__(kSTThreads) stem_tc_fwd_kernel(const StemTcPar
   if (t >= 1 && warp < 4) {
     mbar_wait(s.bar, (t - 1u) & 1u);
     tc_fence_after();
-    stem_fwd_store(p, tmem_base + ((t - 1u) & 1u) * 16u + lane_off, bias_r, prev_pix + (size_t)(warp * 32 + lane));
+    stem_fwd_store(p, tmem_base + ((t - 1u) & 1u) * 32u + lane_off, bias_r, prev_pix + (size_t)(warp * 32 + lane));
   }
   tc_fence_before();
   __syncthreads();
   if (warp == 0) {
     tc_fence_after();
-    tmem_dealloc_dyn(tmem_base, 32);
+    tmem_dealloc_dyn(tmem_base, 64);
   }
 }
 
@@ -247,7 +263,7 @@ __global__ void __launch_bounds__(kSTThreads) stem_tc_fwd_kernel(const StemTcPar
 // D[m][co] += sum over the tile's 128 pixels P[px][m] * dy[px][co], m = 0..63 the hi taps, 64..127 the lo taps (the
 // two im2col tiles are the two 64-channel blocks of one MN-major A operand, LBO = 16 KB apart).  One fp32
 // accumulator [128][16] per CTA lives in TMEM over all its tiles; hi + lo rows are added by the reduce kernel.
-__global__ void __launch_bounds__(kSTThreads) stem_tc_wgrad_kernel(const StemTcParams p) {
+__global__ void __launch_bounds__(kSTThreads, 4) stem_tc_wgrad_kernel(const StemTcParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const StemSmem s = stem_smem_layout(base);
@@ -274,17 +290,28 @@ __global__ void __launch_bounds__(kSTThreads) stem_tc_wgrad_kernel(const StemTcP
   uint32_t t = 0;
   for (int strip = blockIdx.x; strip < p.nstrips; strip += gridDim.x) {
     const StemStrip st = stem_strip(p, strip);
-    __syncthreads();
-    for (int hh = st.h0 - 3; hh <= st.h0 + 3; ++hh) stem_put_row(s, hh, stem_fetch_row(p, st.n, hh, st.w0));
+    {
+      float v[7];
+#pragma unroll
+      for (int i = 0; i < 7; ++i) v[i] = stem_fetch_row(p, st.n, st.h0 - 3 + i, st.w0);
+#pragma unroll
+      for (int i = 0; i < 7; ++i) stem_put_row(s, st.h0 - 3 + i, v[i]);
+    }
+    __syncthreads();                 // the strip's first rows are staged
+    float pend = stem_fetch_row(p, st.n, st.h0 + 4, st.w0);               // x rows and dy tiles are fetched ahead
+    const __nv_bfloat16* dyp = p.dy + (((size_t)st.n * p.h + st.h0) * (size_t)p.w + st.w0 + dpx) * (size_t)p.dyld + dj * 8;
+    const size_t dy_row = (size_t)p.w * (size_t)p.dyld;
+    uint4 dv = __ldg(reinterpret_cast<const uint4*>(dyp));
     for (int h = st.h0; h < st.h0 + p.bh; ++h, ++t) {
-      const float nxt = stem_fetch_row(p, st.n, h + 4, st.w0);
-      const size_t pix = ((size_t)st.n * p.h + h) * (size_t)p.w + st.w0 + dpx;
-      const uint4 dv = __ldg(reinterpret_cast<const uint4*>(p.dy + pix * (size_t)p.dyld + dj * 8));
+      const float nxt = stem_fetch_row(p, st.n, h + 5, st.w0);
+      uint4 dn = dv;
+      if (h + 1 < st.h0 + p.bh) dn = __ldg(reinterpret_cast<const uint4*>(dyp + (size_t)(h + 1 - st.h0) * dy_row));
       if (t >= 1) mbar_wait(s.bar, (t - 1u) & 1u);                        // MMA(t-1) has consumed the tile buffers
-      __syncthreads();
       stem_build_tiles(s, h);
       sts128(s.aux + dy_off, dv.x, dv.y, dv.z, dv.w);
-      stem_put_row(s, h + 4, nxt);
+      stem_put_row(s, h + 4, pend);
+      pend = nxt;
+      dv = dn;
       fence_proxy_async_smem();
       tc_fence_before();
       __syncthreads();
@@ -327,23 +354,30 @@ __global__ void __launch_bounds__(kSTThreads) stem_tc_wgrad_kernel(const StemTcP
 }
 
 // partials [nblocks][128 m][16 co] -> dw[co][r*7+s] = sum_b part[b][k][co] + part[b][64+k][co]  (k = r*8+s, s < 7),
-// dbias[co] = the same for k = 56; fixed summation order
-__global__ void stem_tc_wgrad_reduce_kernel(const float* __restrict__ partials, int nblocks, float* dw, float* db,
-                                            int accumulate) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;      // over 64 k x 16 co
-  if (i >= 64 * 16) return;
-  const int k = i >> 4, co = i & 15, r = k >> 3, sl = k & 7;
+// dbias[co] = the same for k = 56.  One block per k; 16 slices of the CTA partials per output, combined in fixed order.
+__global__ void __launch_bounds__(256) stem_tc_wgrad_reduce_kernel(const float* __restrict__ partials, int nblocks,
+                                                                   float* dw, float* db, int accumulate) {
+  __shared__ double red[16][16];
+  const int k = blockIdx.x, r = k >> 3, sl = k & 7;
   const bool is_w = r < 7 && sl < 7, is_b = k == 56;
   if (!is_w && !is_b) return;
+  const int co = threadIdx.x & 15, slice = threadIdx.x >> 4;
   double acc = 0.0;
-  for (int b = 0; b < nblocks; ++b) {
+  for (int b = slice; b < nblocks; b += 16) {
     const float* pb = partials + (size_t)b * 2048;
     acc += (double)pb[k * 16 + co] + (double)pb[(64 + k) * 16 + co];
   }
-  if (is_w) {
-    if (dw) dw[co * 49 + r * 7 + sl] = (accumulate ? dw[co * 49 + r * 7 + sl] : 0.f) + (float)acc;
-  } else if (db) {
-    db[co] = (accumulate ? db[co] : 0.f) + (float)acc;
+  red[slice][co] = acc;
+  __syncthreads();
+  if (threadIdx.x < 16) {
+    double t = 0.0;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) t += red[i][co];
+    if (is_w) {
+      if (dw) dw[co * 49 + r * 7 + sl] = (accumulate ? dw[co * 49 + r * 7 + sl] : 0.f) + (float)t;
+    } else if (db) {
+      db[co] = (accumulate ? db[co] : 0.f) + (float)t;
+    }
   }
 }
 
@@ -351,9 +385,13 @@ __global__ void stem_tc_wgrad_reduce_kernel(const float* __restrict__ partials, 
 static bool stem_tc_plan(int n, int h, int w, StemTcParams& p) {
   if (w % 128 != 0 || h % 8 != 0) return false;
   p.n = n; p.h = h; p.w = w;
-  p.bh = h % 64 == 0 ? 64 : (h % 32 == 0 ? 32 : (h % 16 == 0 ? 16 : 8));
-  p.bands = h / p.bh;
   p.wblocks = w / 128;
+  // strip height: as tall as possible (6 halo rows are re-staged per strip) while the persistent CTAs still get
+  // >= 3 strips each, so that the round-robin tail stays small
+  p.bh = 8;
+  for (int bh = 64; bh > 8; bh >>= 1)
+    if (h % bh == 0 && (long)n * (h / bh) * p.wblocks >= 3L * kStemTcMaxBlocks) { p.bh = bh; break; }
+  p.bands = h / p.bh;
   p.nstrips = n * p.bands * p.wblocks;
   return true;
 }
@@ -384,7 +422,7 @@ int stem_tc_wgrad(const float* x, int n, int h, int w, const __nv_bfloat16* dy, 
   const int grid = p.nstrips < kStemTcMaxBlocks ? p.nstrips : kStemTcMaxBlocks;
   stem_tc_wgrad_kernel<<<grid, kSTThreads, kStemSmemBytes, st>>>(p);
   UBR_LAUNCH_CHECK("stem_tc_wgrad_kernel");
-  stem_tc_wgrad_reduce_kernel<<<8, 128, 0, st>>>(workspace, grid, dw, dbias, accumulate);
+  stem_tc_wgrad_reduce_kernel<<<64, 256, 0, st>>>(workspace, grid, dw, dbias, accumulate);
   UBR_LAUNCH_CHECK("stem_tc_wgrad_reduce_kernel");
   return 0;
 }
