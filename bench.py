@@ -295,7 +295,8 @@ def run_own(args, rank, world, local_rank):
     model = UResNet(num_classes=3, input_channels=1, inplanes=16).to(dev).train()
     net = DistributedUResNet(model) if world > 1 else model
     crit = PixelWiseNLLLoss()
-    opt = torch.optim.SGD(model.parameters(), lr=1e-4, momentum=0.9, weight_decay=1e-3, foreach=True)
+    from ubresnet_b200.training.optim import SGD
+    opt = SGD(model.parameters(), lr=1e-4, momentum=0.9, weight_decay=1e-3)     # one multi-tensor launch per step
 
     B, S = args.batch, args.size
     nbuf = 2

@@ -211,6 +211,33 @@ int ubr_stitch_scatter(const float* tiles /* [ntiles,c,crop,crop] */, int nch, c
  * device) is zeroed by the call.  Targets outside [0, ncls) are not counted. */
 int ubr_accuracy_counts(const float* logp, const int64_t* target, int n, int ncls, int hw, uint64_t* counts, void* stream);
 
+/* ---- multi-tensor optimizer step (train_ubresnet2018_wlarcv1.py:127-129 SGD,
+ * train_ubresnet2018_wlarcv2.py:155-157 Adam).  One launch updates every parameter: `slots` (device) describes the
+ * tensors, `chunks` (device) cuts them into ubr_opt_chunk_elems()-element pieces, one CTA each.  Arithmetic is
+ * torch.optim's: g' = g + wd*p;  SGD: buf = first_step ? g' : m*buf + (1-dampening)*g', p -= lr*(nesterov ? g' + m*buf
+ * : buf) (state1 = momentum_buffer, NULL when momentum == 0);  Adam: exp_avg (state1), exp_avg_sq (state2), bias
+ * correction for `step` >= 1, no amsgrad. */
+typedef struct {
+  float* param;
+  const float* grad;
+  float* state1;
+  float* state2;
+  int64_t numel;
+  int32_t vec_ok;            /* all four pointers 16-byte aligned */
+  int32_t pad_;
+} ubr_opt_slot;
+typedef struct {
+  int32_t slot;
+  int32_t pad_;
+  int64_t offset;            /* first element of the chunk inside its tensor */
+} ubr_opt_chunk;
+int ubr_opt_chunk_elems(void);
+int ubr_sgd_step(const ubr_opt_slot* slots, const ubr_opt_chunk* chunks, int nchunks, float lr, float momentum,
+                 float dampening, float weight_decay, int nesterov, int first_step, void* stream);
+/* Adam hyper-parameters are doubles: torch derives 1-beta and lr/(1-beta1^t) in double before rounding to fp32 */
+int ubr_adam_step(const ubr_opt_slot* slots, const ubr_opt_chunk* chunks, int nchunks, double lr, double beta1,
+                  double beta2, double eps, double weight_decay, int step, void* stream);
+
 /* ---- flat-buffer helpers for the data-parallel gradient buckets --------------------------------- */
 int ubr_scale_f32(float* buf, uint64_t count, float alpha, void* stream);
 

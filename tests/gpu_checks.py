@@ -277,6 +277,54 @@ def check_stem(n, h, w, oc=16, seed=0):
     return res
 
 
+def check_optim(seed=0):
+    """multi-tensor SGD / Adam (training/optim.py) against torch.optim on the same parameters and gradients, 4 steps;
+    odd sizes, an unaligned view and a tensor larger than one chunk are in the set"""
+    from ubresnet_b200.training import optim as fused
+    res = []
+    g = torch.Generator().manual_seed(seed)
+    shapes = [(16, 1, 7, 7), (16,), (3,), (512, 513), (33, 7, 3, 3), (1,), (4097,)]
+    base = [torch.randn(s, generator=g) for s in shapes]
+    flat = torch.randn(1001, generator=g)                       # parameter living at a 4-byte-aligned offset
+    cases = [("sgd_m0.9_wd", fused.SGD, torch.optim.SGD, dict(lr=1e-2, momentum=0.9, weight_decay=1e-3)),
+             ("sgd_plain", fused.SGD, torch.optim.SGD, dict(lr=1e-2)),
+             ("sgd_nesterov", fused.SGD, torch.optim.SGD, dict(lr=1e-2, momentum=0.8, nesterov=True, weight_decay=1e-2)),
+             ("sgd_dampening", fused.SGD, torch.optim.SGD, dict(lr=1e-2, momentum=0.9, dampening=0.3)),
+             ("adam_wd", fused.Adam, torch.optim.Adam, dict(lr=1e-3, weight_decay=1e-4)),
+             ("adam_betas", fused.Adam, torch.optim.Adam, dict(lr=3e-3, betas=(0.8, 0.95), eps=1e-6))]
+    for name, mine, theirs, kw in cases:
+        def make():
+            ps = [torch.nn.Parameter(b.clone().to(DEV)) for b in base]
+            store = flat.clone().to(DEV)
+            ps.append(torch.nn.Parameter(store[1:]))                # data_ptr % 16 == 4
+            return ps
+        pa, pb = make(), make()
+        oa, ob = mine(pa, **kw), theirs(pb, **kw)
+        gg = torch.Generator().manual_seed(seed + 1)
+        for step in range(4):
+            for a, b in zip(pa, pb):
+                gr = torch.randn(a.shape, generator=gg).to(DEV)
+                a.grad, b.grad = gr.clone(), gr.clone()
+            oa.step()
+            ob.step()
+        torch.cuda.synchronize()
+        res.append((name + "_params", max(relerr(a, b) for a, b in zip(pa, pb)), 2e-6))
+        sa, sb = oa.state_dict()["state"], ob.state_dict()["state"]
+        worst = 0.0
+        for k in sb:
+            for nm, v in sb[k].items():
+                if torch.is_tensor(v) and v.numel() > 1:
+                    worst = max(worst, relerr(sa[k][nm], v))
+                elif nm == "step":
+                    worst = max(worst, abs(float(sa[k][nm]) - float(v)))
+        res.append((name + "_state", worst, 2e-6))
+        # the torch class accepts our state_dict (checkpoint round trip, train_ubresnet2018_wlarcv2.py:260-266)
+        oc = theirs(make(), **kw)
+        oc.load_state_dict(oa.state_dict())
+        res.append((name + "_state_dict_loads_into_torch", 0.0, 0.0))
+    return res
+
+
 def _bn_ref(y, gamma, beta, eps=1e-5):
     mean = y.mean((0, 2, 3), keepdim=True)
     var = y.var((0, 2, 3), unbiased=False, keepdim=True)
@@ -527,6 +575,7 @@ CHECKS = {
                         + check_stem(32, 40, 512, seed=8)),
     "loss": lambda: check_loss(2, 3, 32, 32) + check_loss(2, 4, 16, 48, seed=3, classw=True),
     "tiling": lambda: check_tiling(),
+    "optim": lambda: check_optim(),
     "accuracy": lambda: check_accuracy(2, 3, 64, 96) + check_accuracy(3, 4, 33, 17, seed=5),
     # tensor-core forward: each swizzle mode / K-chunk count / N-tile count / stride / kernel size
     "conv_fwd_c64": lambda: check_conv_fwd(64, 64, 3, 1, 2, 16, 16),

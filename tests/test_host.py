@@ -95,3 +95,16 @@ def test_stage_map_covers_every_parameter():
     m = UResNet(3, 1, 16)
     stages = {parallel.stage_of_param(n) for n, _ in m.named_parameters()}
     assert stages == set(parallel.STAGE_ORDER)
+
+
+def test_fused_optimizers_refuse_cpu_parameters():
+    """training/optim.py has no CPU path: a CPU parameter with a gradient raises instead of falling back"""
+    import torch
+    from ubresnet_b200.training import optim
+    for cls in (optim.SGD, optim.Adam):
+        p = torch.nn.Parameter(torch.zeros(4))
+        p.grad = torch.ones(4)
+        opt = cls([p], lr=0.1)
+        with pytest.raises(RuntimeError):
+            opt.step()
+        assert isinstance(opt, torch.optim.Optimizer) and opt.state_dict()["param_groups"][0]["lr"] == 0.1

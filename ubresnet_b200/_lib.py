@@ -74,6 +74,9 @@ SIGNATURES = {
     "ubr_stitch_scatter": (_i, [_vp, _i, _vp, _i, _i, _i, _i, _vp, _vp]),
     "ubr_accuracy_counts": (_i, [_vp, _vp, _i, _i, _i, _vp, _vp]),
     "ubr_scale_f32": (_i, [_vp, _u64, _f, _vp]),
+    "ubr_opt_chunk_elems": (_i, []),
+    "ubr_sgd_step": (_i, [_vp, _vp, _i, _f, _f, _f, _f, _i, _i, _vp]),
+    "ubr_adam_step": (_i, [_vp, _vp, _i, _d, _d, _d, _d, _d, _i, _vp]),
 }
 
 _lib = None
