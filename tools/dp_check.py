@@ -2,7 +2,7 @@
 the bucketed, overlapped NCCL all-reduce of DistributedUResNet must equal the average of the ranks' stand-alone
 gradients (same kernels, BatchNorm statistics per rank like the reference's nn.DataParallel replicas).
 
-  python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 tools/dp_check.py
+  python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 tools/dp_check.py [aspp]
 """
 import os
 import sys
@@ -24,7 +24,12 @@ def main():
     dev = torch.device("cuda", local)
     dist.init_process_group("nccl", device_id=dev)
     torch.manual_seed(99)
-    model = UResNet(3, 1, 16).to(dev).train()
+    arch = sys.argv[1] if len(sys.argv) > 1 else "uresnet"
+    if arch == "aspp":
+        from ubresnet_b200.models.ASPP_ResNet import ASPP_ResNet
+        model = ASPP_ResNet(3, 1, 16, showsizes=False).to(dev).train()
+    else:
+        model = UResNet(3, 1, 16).to(dev).train()
     img, lab, wgt = (t.to(dev) for t in synthetic.make_batch(4, 256, 256, rank=rank))
     crit = PixelWiseNLLLoss()
     worst = 0.0
@@ -49,7 +54,7 @@ def main():
     t = torch.tensor([worst], device=dev)
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
     if rank == 0:
-        print("dp_check world=%d worst relative gradient difference %.3e %s" % (world, t.item(), "OK" if t.item() < 1e-5 else "FAIL"))
+        print("dp_check %s world=%d worst relative gradient difference %.3e %s" % (arch, world, t.item(), "OK" if t.item() < 1e-5 else "FAIL"))
     dist.destroy_process_group()
     sys.exit(0 if t.item() < 1e-5 else 1)
 

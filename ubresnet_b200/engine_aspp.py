@@ -162,12 +162,19 @@ class ASPPEngine(Engine):
         n, h, w = saved["shape"]
         p = m.inplanes
         bn_ws, wg_ws, stem_ws = self._workspaces(n, h, w, dlogp.device)
-        if self.grad_sink is not None:
-            raise RuntimeError("ASPP_ResNet: the data-parallel gradient buckets are only wired for UResNet")
-        grads = {prm: torch.empty_like(prm, dtype=torch.float32) for prm in m.parameters()}
+        sink = self.grad_sink
+        if sink is not None:       # data-parallel: gradients land in the flat all-reduce buckets (parallel.py)
+            grads = {prm: sink.grad_buffer(prm) for prm in m.parameters()}
+        else:
+            grads = {prm: torch.empty_like(prm, dtype=torch.float32) for prm in m.parameters()}
         self._w_on = False         # all weight gradients in stream order (the ASPP ones share the wgrad workspace)
+
+        def done(name):
+            if sink is not None:
+                sink.stage_done(name)
         recs = saved["recs"]
         dcur = self._head_bwd(saved, dlogp, grads, bn_ws, wg_ws)
+        done("head")
         # ---- decoder, shallow to deep; dcat splits into [ddeconv | dskip]
         dskip = {}
         for i in (1, 2, 3, 4, 5):
@@ -178,6 +185,7 @@ class ASPPEngine(Engine):
             dskip[i] = dcat.slice(cd, dcat.c - cd)
             wd = self._pack(layer.deconv, True, transposed=True)
             dcur = self._deconv_bwd(saved["dec_in"][i], ddec, wd, grads[layer.deconv.weight], wg_ws)
+            done("dec%d" % i)
         # dcur = grad wrt cat[aspp5, e5]; dskip[5] = grad wrt cat[aspp4, e4]; dskip[4] = grad wrt cat[aspp3, e3]
         d_as = {5: dcur.slice(0, 32 * p), 4: dskip[5].slice(0, 16 * p), 3: dskip[4].slice(0, 8 * p)}
         d_e = {5: dcur.slice(32 * p, 32 * p), 4: dskip[5].slice(16 * p, 16 * p), 3: dskip[4].slice(8 * p, 8 * p),
@@ -190,7 +198,11 @@ class ASPPEngine(Engine):
         for i in (5, 4, 3, 2, 1):
             extra = d_e[i - 1] if i > 1 else None
             dcur = self._double_bwd(getattr(m, "enc_layer%d" % i), recs["enc%d" % i], dcur, grads, bn_ws, wg_ws, extra=extra)
+            done("enc%d" % i)
         self._stem_bwd(saved, dcur, dskip[1], grads, bn_ws, stem_ws)
+        done("stem")
+        if sink is not None:
+            sink.finish()
         return grads
 
 

@@ -17,8 +17,11 @@ import torch
 import torch.distributed as dist
 
 STAGE_ORDER = ["head", "dec1", "dec2", "dec3", "dec4", "dec5", "enc5", "enc4", "enc3", "enc2", "enc1", "stem"]
-BUCKET_OF_STAGE = {"head": 0, "dec1": 0, "dec2": 0, "dec3": 0, "dec4": 1, "dec5": 1, "enc5": 2, "enc4": 3, "enc3": 3,
-                   "enc2": 3, "enc1": 3, "stem": 3}
+ASPP_STAGE_ORDER = STAGE_ORDER[:6] + ["aspp"] + STAGE_ORDER[6:]          # backward order of engine_aspp.ASPPEngine
+# "aspp" (ASPP_ResNet only): the three ASPP skip layers run their backward between dec5 and enc5, so they share
+# enc5's bucket
+BUCKET_OF_STAGE = {"head": 0, "dec1": 0, "dec2": 0, "dec3": 0, "dec4": 1, "dec5": 1, "aspp": 2, "enc5": 2, "enc4": 3,
+                   "enc3": 3, "enc2": 3, "enc1": 3, "stem": 3}
 LAST_STAGE_OF_BUCKET = {0: "dec3", 1: "dec5", 2: "enc5", 3: "stem"}
 
 
@@ -33,6 +36,8 @@ def stage_of_param(name):
         return "enc" + head[len("enc_layer"):]
     if head.startswith("dec_layer"):
         return "dec" + head[len("dec_layer"):]
+    if head.startswith("ASPP_layer_enc") or head.startswith("ASPP_combine_enc"):
+        return "aspp"
     raise KeyError(name)
 
 
@@ -122,7 +127,8 @@ def broadcast_module(module, src=0, process_group=None):
 
 class DistributedUResNet(torch.nn.Module):
     """`model = DistributedUResNet(UResNet(...).cuda())` -- takes nn.DataParallel's place in the training
-    scripts (checkpoints keep the `module.` prefix that deploy/ubresnet_funcs.py:52-64 strips)."""
+    scripts (checkpoints keep the `module.` prefix that deploy/ubresnet_funcs.py:52-64 strips).  Wraps `UResNet`
+    and `ASPP_ResNet` alike."""
 
     def __init__(self, module, process_group=None):
         super().__init__()
