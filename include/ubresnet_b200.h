@@ -80,6 +80,11 @@ int ubr_conv2d_fwd(ubr_view x, const void* wpk, const float* bias, int out_ch, i
  * Returns 1 (and does nothing) when the shape has no fused path: run ubr_conv2d_fwd + ubr_bn_stats instead. */
 int ubr_conv2d_fwd_stats(ubr_view x, const void* wpk, const float* bias, int out_ch, int ksize, int stride, ubr_view y,
                          void* bn_workspace, int* stats_rows, void* stream);
+/* Inference form of a residual-block conv with BatchNorm folded into (wpk, bias) by the caller (SURVEY 8f N1;
+ * common_layers.py:39-58 in eval mode):  y = relu_post?( relu_pre?(conv(x) + bias) + res ).  `res` (ptr NULL = none)
+ * is a bf16 view on the output grid.  bf16 output only. */
+int ubr_conv2d_fwd_fused(ubr_view x, const void* wpk, const float* bias, int out_ch, int ksize, int stride, int relu_pre,
+                         ubr_view res, int relu_post, ubr_view y, void* stream);
 /* data gradient of the same conv: dx = conv_transpose(dy, W).  wpk = pack(..., n_is_out=0). */
 int ubr_conv2d_dgrad(ubr_view dy, const void* wpk, int in_ch, int ksize, int stride, ubr_view dx, void* stream);
 /* dx += conv_transpose(dy, W), fused into the epilogue (fp32 add of the stored bf16 value, one rounding).

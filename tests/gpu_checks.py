@@ -89,6 +89,36 @@ def check_conv_fwd(cin, cout, k, stride, n, h, w, in_ld=None, out_ld=None, seed=
     return res
 
 
+def check_conv_fwd_fused(cin, cout, k, stride, n, h, w, relu_pre=True, with_res=True, relu_post=True, res_ld=None,
+                         out_ld=None, seed=0):
+    """inference epilogue (ubr_conv2d_fwd_fused): relu_post(relu_pre(conv(x) + b) + res) against torch"""
+    name = "conv_fused_ci%d_co%d_k%d_s%d_n%d_%dx%d_%d%d%d" % (cin, cout, k, stride, n, h, w, relu_pre, with_res, relu_post)
+    ho, wo = h // stride, w // stride
+    x = bf(gen(n, cin, h, w, seed=seed))
+    wt = bf(gen(cout, cin, k, k, seed=seed + 1, scale=(2.0 / (k * k * cin)) ** 0.5))
+    b = gen(cout, seed=seed + 2, scale=0.3)
+    r = bf(gen(n, cout, ho, wo, seed=seed + 3)) if with_res else None
+    ref = F.conv2d(x, wt, b, stride, (k - 1) // 2)
+    if relu_pre:
+        ref = F.relu(ref)
+    if with_res:
+        ref = ref + r
+    if relu_post:
+        ref = F.relu(ref)
+    wpk = ops.pack_weights(wt.to(DEV), False, True)
+    ra = act_from(r, res_ld, 0 if not res_ld else (res_ld - cout)) if with_res else None
+    ya = act_out(n, ho, wo, cout, out_ld, 0)
+    ops.conv2d_fwd_fused(act_from(x), wpk, b.to(DEV), cout, k, stride, relu_pre, ra, relu_post, y=ya)
+    torch.cuda.synchronize()
+    out = ya.nchw_float()
+    res = [(name, relerr(out, ref), 1e-2)]
+    if relu_post:
+        res.append((name + "_nonneg", float((out < 0).any().item()), 0.0))
+    if out_ld and out_ld != cout:
+        res.append((name + "_slice_untouched", (ya.buf[..., cout:].float() - 3.0).abs().max().item(), 0.0))
+    return res
+
+
 def check_conv_fwd_bn(cin, cout, k, n, h, w, seed=0, bias=False, expect_rows=True):
     """conv + fused BatchNorm statistics (ubr_conv2d_fwd_stats) against F.conv2d + batch statistics."""
     name = "conv_fwd_bn_ci%d_co%d_k%d_n%d_%dx%d" % (cin, cout, k, n, h, w)
@@ -576,6 +606,21 @@ CHECKS = {
     "loss": lambda: check_loss(2, 3, 32, 32) + check_loss(2, 4, 16, 48, seed=3, classw=True),
     "tiling": lambda: check_tiling(),
     "optim": lambda: check_optim(),
+    # inference epilogue on each output path: halo direct stores (Cout <= 32), halo TMA-store (Cout 64), implicit GEMM
+    # (C >= 128, stride 2, partial tiles), residual / output living in channel slices of wider buffers
+    "conv_fused_halo_direct": lambda: (check_conv_fwd_fused(16, 16, 3, 1, 2, 32, 128)
+                                       + check_conv_fwd_fused(32, 32, 3, 1, 1, 16, 256, res_ld=64, out_ld=64, seed=3)
+                                       + check_conv_fwd_fused(16, 16, 7, 1, 1, 16, 128, with_res=False, relu_post=False, seed=5)),
+    "conv_fused_halo_tma": lambda: (check_conv_fwd_fused(64, 64, 3, 1, 2, 16, 128, seed=7)
+                                    + check_conv_fwd_fused(32, 64, 1, 1, 1, 8, 128, relu_pre=False, with_res=False,
+                                                           relu_post=False, seed=9)
+                                    + check_conv_fwd_fused(64, 64, 3, 1, 1, 8, 128, res_ld=128, out_ld=128, seed=11)),
+    "conv_fused_gemm": lambda: (check_conv_fwd_fused(128, 128, 3, 1, 2, 16, 16, seed=13)
+                                + check_conv_fwd_fused(64, 128, 3, 2, 2, 32, 32, with_res=False, relu_post=False, seed=15)
+                                + check_conv_fwd_fused(128, 256, 1, 2, 1, 24, 40, relu_pre=False, with_res=False,
+                                                       relu_post=False, seed=17)
+                                + check_conv_fwd_fused(256, 256, 3, 1, 3, 12, 20, res_ld=512, seed=19)
+                                + check_conv_fwd_fused(32, 32, 3, 1, 2, 24, 40, seed=21)),
     "accuracy": lambda: check_accuracy(2, 3, 64, 96) + check_accuracy(3, 4, 33, 17, seed=5),
     # tensor-core forward: each swizzle mode / K-chunk count / N-tile count / stride / kernel size
     "conv_fwd_c64": lambda: check_conv_fwd(64, 64, 3, 1, 2, 16, 16),

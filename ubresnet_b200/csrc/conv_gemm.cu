@@ -38,6 +38,9 @@ struct ConvGemmParams {
   float* stats;                 // out_mode 0: per-tile BN partials [tile][2][stats_c] (sum, sum of squares), or null
   int stats_c;
   int out_ld, out_cols, out_n, out_h, out_w;
+  int fused, relu_pre, relu_post;   // out_mode 0: fused inference epilogue (FusedEpi); needs out_n/out_h/out_w
+  const __nv_bfloat16* res;
+  int res_ld;
   int8_t dh[kMaxTaps], dw[kMaxTaps];
   uint8_t amap[kMaxTaps], slab[kMaxTaps];
 };
@@ -147,6 +150,13 @@ __global__ void __launch_bounds__(kThreads, 1) conv_gemm_kernel(const __grid_con
       const uint32_t rb = (uint32_t)bc * 2u;            // staging row bytes (32/64/128)
       const uint32_t xr = rb == 128 ? (uint32_t)(row & 7) : (rb == 64 ? (uint32_t)((row >> 1) & 3)
                                                                        : (uint32_t)((row >> 2) & 1));
+      const __nv_bfloat16* res_row = nullptr;           // fused epilogue: this thread's pixel of the residual
+      if (p.fused && p.res) {
+        const int mw = row % p.bw, mh = (row / p.bw) % p.bh, mn = row / (p.bw * p.bh);
+        const int pw_ = w0 + mw, ph_ = h0 + mh, pn_ = n0 + mn;
+        if (pw_ < p.out_w && ph_ < p.out_h && pn_ < p.out_n)
+          res_row = p.res + ((size_t)((size_t)pn_ * p.out_h + ph_) * p.out_w + pw_) * (size_t)p.res_ld + co0;
+      }
       for (int c = 0; c < p.nt; c += 16) {
         uint32_t v[16];
         tmem_ld16(t_row + (uint32_t)c, v);
@@ -158,6 +168,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_gemm_kernel(const __grid_con
 #pragma unroll
           for (int j = 0; j < 16; ++j) f[j] += __ldg(p.bias + co0 + c + j);
         }
+        if (p.fused) fused_epi16(f, p.relu_pre, res_row ? res_row + c : nullptr, p.relu_post);
         uint32_t pk[8];
 #pragma unroll
         for (int j = 0; j < 8; ++j) pk[j] = pack_bf16x2(f[2 * j], f[2 * j + 1]);
@@ -348,7 +359,19 @@ using namespace ubr;
 extern "C" {
 
 static int conv2d_fwd_impl(ubr_view x, const void* wpk, const float* bias, int out_ch, int ksize, int stride, ubr_view y,
-                           float* y_f32, int y_f32_ld, void* stream, float* stats, int* stats_rows);
+                           float* y_f32, int y_f32_ld, void* stream, float* stats, int* stats_rows,
+                           const FusedEpi* epi = nullptr);
+
+int ubr_conv2d_fwd_fused(ubr_view x, const void* wpk, const float* bias, int out_ch, int ksize, int stride, int relu_pre,
+                         ubr_view res, int relu_post, ubr_view y, void* stream) {
+  FusedEpi e{relu_pre, relu_post, res.ptr, res.ld};
+  if (res.ptr) {
+    UBR_REQUIRE(res.n == y.n && res.h == y.h && res.w == y.w && res.c == out_ch && res.ld % 8 == 0 &&
+                    ((uintptr_t)res.ptr & 15) == 0,
+                "conv2d_fwd_fused: residual view must match the output (n,h,w,c) with 16-byte aligned rows");
+  }
+  return conv2d_fwd_impl(x, wpk, bias, out_ch, ksize, stride, y, nullptr, 0, stream, nullptr, nullptr, &e);
+}
 
 int ubr_conv2d_fwd(ubr_view x, const void* wpk, const float* bias, int out_ch, int ksize, int stride, ubr_view y,
                    float* y_f32, int y_f32_ld, void* stream) {
@@ -362,8 +385,9 @@ int ubr_conv2d_fwd_stats(ubr_view x, const void* wpk, const float* bias, int out
 }
 
 static int conv2d_fwd_impl(ubr_view x, const void* wpk, const float* bias, int out_ch, int ksize, int stride, ubr_view y,
-                           float* y_f32, int y_f32_ld, void* stream, float* stats, int* stats_rows) {
+                           float* y_f32, int y_f32_ld, void* stream, float* stats, int* stats_rows, const FusedEpi* epi) {
   if (int rc = ensure_device()) return rc;
+  UBR_REQUIRE(!(epi && (y_f32 || stats)), "conv2d_fwd: the fused epilogue writes bf16 and emits no statistics");
   if (int rc = check_view(x, "conv2d_fwd.x")) return rc;
   UBR_REQUIRE(ksize == 1 || ksize == 3 || ksize == 7, "conv2d_fwd: ksize %d unsupported", ksize);
   UBR_REQUIRE(stride == 1 || stride == 2, "conv2d_fwd: stride %d unsupported", stride);
@@ -408,7 +432,7 @@ static int conv2d_fwd_impl(ubr_view x, const void* wpk, const float* bias, int o
       UBR_REQUIRE(y_f32_ld >= out_ch, "conv2d_fwd: y_f32_ld too small");
     }
     const int hrc = conv_halo_try(x, wpk, ksize * ksize, n_pad, taps, nt, bias, y_f32 ? nullptr : &y, y_f32, y_f32_ld,
-                                  out_ch, (cudaStream_t)stream, 0, stats, stats_rows);
+                                  out_ch, (cudaStream_t)stream, 0, stats, stats_rows, 0, epi);
     if (hrc <= 0) return hrc;
   }
   if (stats) {
@@ -431,6 +455,11 @@ static int conv2d_fwd_impl(ubr_view x, const void* wpk, const float* bias, int o
     p.out_mode = 0;
     p.o_box_c = out_box_c(pick_nt(n_pad));
     if (int rc = make_act_map(&p.o_map, y, p.o_box_c, t)) return rc;
+    if (epi) {
+      p.fused = 1; p.relu_pre = epi->relu_pre; p.relu_post = epi->relu_post;
+      p.res = (const __nv_bfloat16*)epi->res; p.res_ld = epi->res_ld;
+      p.out_n = x.n; p.out_h = ho; p.out_w = wo;
+    }
   }
   return launch_conv_gemm(p, x.n, ho, wo, t, x.c, n_pad, wpk, ksize * ksize, taps, nt, (cudaStream_t)stream);
 }

@@ -48,6 +48,9 @@ struct HaloParams {
   float* stats;                 // out_mode 2 only: per-CTA BN partials [row][2][stats_c] (sum, sum of squares), or null
   int stats_c, stats_rows;
   int accumulate;               // out_mode 2 only: out += result (fp32 add of the stored bf16 value, one rounding)
+  int fused, relu_pre, relu_post;   // out_mode 0 / 2: fused inference epilogue (FusedEpi)
+  const __nv_bfloat16* res;
+  int res_ld;
 };
 
 template <int N>
@@ -241,6 +244,7 @@ __global__ void __launch_bounds__(kHThreads, 1) conv_halo_kernel(const __grid_co
         mbar_wait(accf0 + 8u * b, (r >> ((uint32_t)__ffs(p.nb) - 1u)) & 1u);
         tc_fence_after();
         const uint32_t t_row = tmem_base + b * (uint32_t)p.nt + ((uint32_t)(quad * 32) << 16);
+        const size_t pix = (size_t)((size_t)n * p.out_h + h) * p.out_w + (c0 + row);      // this thread's output pixel
         if (p.out_mode == 2) {
           // bf16 direct stores: one pixel (nt <= 32 channels) per thread, 16-byte vectors
           __nv_bfloat16* dst = p.out_bf16 + ((size_t)((size_t)n * p.out_h + h) * p.out_w + (c0 + row)) * (size_t)p.out_ld + co0;
@@ -256,6 +260,8 @@ __global__ void __launch_bounds__(kHThreads, 1) conv_halo_kernel(const __grid_co
 #pragma unroll
               for (int j = 0; j < 16; ++j) f[j] += __ldg(p.bias + co0 + c + j);
             }
+            if (p.fused)
+              fused_epi16(f, p.relu_pre, p.res ? p.res + pix * (size_t)p.res_ld + co0 + c : nullptr, p.relu_post);
             if (p.accumulate) {
               const uint4 o0 = *reinterpret_cast<const uint4*>(dst + c);
               const uint4 o1 = *reinterpret_cast<const uint4*>(dst + c + 8);
@@ -333,6 +339,8 @@ __global__ void __launch_bounds__(kHThreads, 1) conv_halo_kernel(const __grid_co
 #pragma unroll
               for (int j = 0; j < 16; ++j) f[j] += __ldg(p.bias + co0 + c + j);
             }
+            if (p.fused)
+              fused_epi16(f, p.relu_pre, p.res ? p.res + pix * (size_t)p.res_ld + co0 + c : nullptr, p.relu_post);
             uint32_t pk[8];
 #pragma unroll
             for (int j = 0; j < 8; ++j) pk[j] = pack_bf16x2(f[2 * j], f[2 * j + 1]);
@@ -444,7 +452,8 @@ static halo_kernel_t pick_halo_kernel(int ks, int ksteps) {
 
 int conv_halo_try(const ubr_view& x, const void* wpk, int nslabs, int n_pad, const TapSpec* taps, int ntaps,
                   const float* bias, const ubr_view* y, float* y_f32, int y_f32_ld, int out_cols,
-                  cudaStream_t stream, int accumulate, float* stats, int* stats_rows, int shuffle_cout) {
+                  cudaStream_t stream, int accumulate, float* stats, int* stats_rows, int shuffle_cout,
+                  const FusedEpi* epi) {
   if (halo_disabled()) return 1;
   const int cin = x.c;
   if (!(cin == 16 || cin == 32 || cin == 64)) return 1;
@@ -549,6 +558,11 @@ int conv_halo_try(const ubr_view& x, const void* wpk, int nslabs, int n_pad, con
   p.bias = bias;
   p.accumulate = accumulate;
   p.stats = stats; p.stats_c = n_pad;
+  if (epi) {
+    UBR_REQUIRE(p.out_mode == 0 || p.out_mode == 2, "conv_halo: the fused epilogue needs a bf16 output");
+    p.fused = 1; p.relu_pre = epi->relu_pre; p.relu_post = epi->relu_post;
+    p.res = (const __nv_bfloat16*)epi->res; p.res_ld = epi->res_ld;
+  }
   const uint32_t smem = w_region + (uint32_t)nslots * slot_bytes + 2u * stage_bytes + 16u * nslots + 640u + 4096u + 1024u;
   UBR_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
   const int n_tiles = n_pad / nt;

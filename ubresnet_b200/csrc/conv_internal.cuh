@@ -6,6 +6,14 @@ namespace ubr {
 
 struct TapSpec { int dh, dw, amap, slab; };
 
+// Fused inference epilogue (eval-mode residual block with BatchNorm folded into weights and bias):
+//   v = acc + bias;  if (relu_pre) v = max(v, 0);  if (res) v += res[pixel][channel];  if (relu_post) v = max(v, 0)
+struct FusedEpi {
+  int relu_pre, relu_post;
+  const void* res;              // bf16 NHWC on the output grid (same n, h, w), or null
+  int res_ld;
+};
+
 #ifdef __CUDACC__
 // Warp reduce-scatter of 16 per-lane values over the 32 lanes: 16 shuffles instead of 80.  On return lane l holds
 // in the result the warp total of channel (l >> 1) & 15 (both lanes of a pair hold the same total).
@@ -21,6 +29,27 @@ __device__ __forceinline__ float warp_reduce_scatter16(float (&v)[16], int lane)
     }
   }
   return v[0] + __shfl_xor_sync(0xffffffffu, v[0], 1);
+}
+// FusedEpi on 16 consecutive channels of one pixel; res_px = &res[pixel][first channel] (16-byte aligned) or null
+__device__ __forceinline__ void fused_epi16(float (&f)[16], int relu_pre, const __nv_bfloat16* res_px, int relu_post) {
+  if (relu_pre) {
+#pragma unroll
+    for (int j = 0; j < 16; ++j) f[j] = fmaxf(f[j], 0.f);
+  }
+  if (res_px) {
+    const uint4 r0 = __ldg(reinterpret_cast<const uint4*>(res_px));
+    const uint4 r1 = __ldg(reinterpret_cast<const uint4*>(res_px + 8));
+    const uint32_t rw[8] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w};
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float2 t = unpack_bf16x2(rw[j]);
+      f[2 * j] += t.x; f[2 * j + 1] += t.y;
+    }
+  }
+  if (relu_post) {
+#pragma unroll
+    for (int j = 0; j < 16; ++j) f[j] = fmaxf(f[j], 0.f);
+  }
 }
 #endif
 
@@ -40,7 +69,7 @@ int stem_tc_wgrad(const float* x, int n, int h, int w, const __nv_bfloat16* dy, 
 int conv_halo_try(const ubr_view& x, const void* wpk, int nslabs, int n_pad, const TapSpec* taps, int ntaps,
                   const float* bias, const ubr_view* y, float* y_f32, int y_f32_ld, int out_cols,
                   cudaStream_t stream, int accumulate = 0, float* stats = nullptr,
-                  int* stats_rows = nullptr, int shuffle_cout = 0);
+                  int* stats_rows = nullptr, int shuffle_cout = 0, const FusedEpi* epi = nullptr);
 
 // Halo-resident weight gradient (wgrad_halo.cu).  Same return convention.
 int wgrad_halo_try(const ubr_view& x, const ubr_view& dy, int out_ch, int ksize, float* dw, int accumulate,

@@ -22,6 +22,37 @@ from .ops import Act
 WGRAD_SIDE_STREAM = os.environ.get("UBR_WGRAD_STREAM", "1") != "0"
 
 
+class _FoldedConv:
+    """Inference operands of conv -> BatchNorm(eval): W' = W * gamma/sqrt(var+eps) per output channel (packed bf16),
+    b' = beta - mean*scale (+ conv bias*scale), fp32.  Re-derived when any of the six tensors changes."""
+    __slots__ = ("w", "b", "_key")
+
+    def __init__(self):
+        self.w = self.b = self._key = None
+
+    def refresh(self, conv, bn):
+        srcs = [conv.weight, conv.bias, bn.weight, bn.bias, bn.running_mean, bn.running_var]
+        key = tuple((t.data_ptr(), t._version) if t is not None else None for t in srcs) + (bn.eps,)
+        if key == self._key:
+            return self
+        with torch.no_grad():
+            scale = torch.rsqrt(bn.running_var.float() + bn.eps)
+            if bn.weight is not None:
+                scale = scale * bn.weight.float()
+            shift = -bn.running_mean.float() * scale
+            if bn.bias is not None:
+                shift = shift + bn.bias.float()
+            if conv.bias is not None:
+                shift = shift + conv.bias.float() * scale
+            self.w = ops.pack_weights((conv.weight.float() * scale.view(-1, 1, 1, 1)).contiguous(), False, True)
+            self.b = shift.contiguous()
+        self._key = key
+        return self
+
+
+FOLD_EVAL_BN = os.environ.get("UBR_FOLD_EVAL_BN", "1") != "0"
+
+
 class _ConvW:
     """bf16 packed operands of one conv / deconv parameter, refreshed when the parameter changes."""
     __slots__ = ("param", "transposed", "fwd", "dgrad", "fwd3", "dgrad3", "_key", "_dgrad_stale")
@@ -106,6 +137,7 @@ class Engine:
     def __init__(self, model):
         self.model = model
         self._packs = {}
+        self._folds = {}           # id(conv) -> _FoldedConv (eval-mode conv+BN operands)
         self._ws = None
         self._ws_key = None
         self._w_on = False
@@ -268,9 +300,14 @@ class Engine:
         """conv10 -> bn10 -> relu10 -> conv11 -> log-softmax (ub_uresnet.py:137-143); bumps num_batches_tracked."""
         m = self.model
         n, h, w = cur.n, cur.h, cur.w
-        w10 = self._pack(m.conv10, need_grad)
-        y10, st10 = self._conv_bn(cur, w10.fwd, m.conv10.bias, m.nkernels, 7, 1, m.bn10, training, bn_ws)
-        a10 = ops.bn_act(y10, st10, True)
+        if FOLD_EVAL_BN and not training and not need_grad:
+            f10 = self._folded(m.conv10, m.bn10)
+            y10 = st10 = None
+            a10 = ops.conv2d_fwd_fused(cur, f10.w, f10.b, m.nkernels, 7, 1, True)
+        else:
+            w10 = self._pack(m.conv10, need_grad)
+            y10, st10 = self._conv_bn(cur, w10.fwd, m.conv10.bias, m.nkernels, 7, 1, m.bn10, training, bn_ws)
+            a10 = ops.bn_act(y10, st10, True)
         w11 = self._pack(m.conv11, need_grad)
         ncls = m.conv11.out_channels
         ld = 4 if ncls <= 4 else 16
@@ -336,7 +373,30 @@ class Engine:
         return ops.deconv_dgrad(dy, wd.dgrad, in_ch)
 
     # ------------------------------------------------------------------ forward pieces
+    def _folded(self, conv, bn):
+        ent = self._folds.get(id(conv))
+        if ent is None:
+            ent = self._folds[id(conv)] = _FoldedConv()
+        return ent.refresh(conv, bn)
+
+    def _block_fwd_folded(self, blk, x, out):
+        """eval-mode BasicBlock (common_layers.py:39-58) in three launches: BatchNorm folded into the conv operands,
+        ReLU / residual add / ReLU in the conv epilogues -- no stand-alone pointwise pass."""
+        cout = blk.conv1.out_channels
+        s = blk.stride
+        f1 = self._folded(blk.conv1, blk.bn1)
+        a1 = ops.conv2d_fwd_fused(x, f1.w, f1.b, cout, 3, s, True)
+        if blk.bypass is not None:
+            fb = self._folded(blk.bypass, blk.bnpass)
+            res = ops.conv2d_fwd_fused(x, fb.w, fb.b, cout, 1, s, False)
+        else:
+            res = x
+        f2 = self._folded(blk.conv2, blk.bn2)
+        return ops.conv2d_fwd_fused(a1, f2.w, f2.b, cout, 3, 1, True, res, True, y=out)
+
     def _block_fwd(self, blk, x, out, training, need_grad, bn_ws):
+        if FOLD_EVAL_BN and not training and not need_grad:
+            return self._block_fwd_folded(blk, x, out), None
         rec = _BlockRec()
         cout = blk.conv1.out_channels
         s = blk.stride

@@ -116,6 +116,17 @@ def conv2d_fwd(x, wpk, bias, out_ch, ksize, stride, y=None, y_f32=None):
     return y
 
 
+def conv2d_fwd_fused(x, wpk, bias, out_ch, ksize, stride, relu_pre, res=None, relu_post=False, y=None):
+    """inference conv with BatchNorm folded into (wpk, bias): y = relu_post?(relu_pre?(conv(x) + bias) + res)"""
+    lib = _lib.load()
+    if y is None:
+        y = Act.empty(x.n, x.h // stride, x.w // stride, out_ch, x.buf.device)
+    _lib.check(lib.ubr_conv2d_fwd_fused(x.view(), wpk.data_ptr(), _ptr(bias), out_ch, ksize, stride, int(bool(relu_pre)),
+                                        res.view() if res is not None else _NULLVIEW, int(bool(relu_post)), y.view(),
+                                        _stream()), "conv2d_fwd_fused")
+    return y
+
+
 def conv2d_fwd_bn(x, wpk, bias, out_ch, ksize, stride, gamma, beta, running_mean, running_var, ws, y=None,
                   momentum=BN_MOMENTUM, eps=BN_EPS):
     """conv forward + training-mode BatchNorm statistics.  Where the conv kernel has a fused-statistics epilogue the
