@@ -126,6 +126,10 @@ int ubr_deconv4s2_wgrad(ubr_view x, ubr_view dy, float* dw /* IOHW */, int accum
 /* ---- stem: nn.Conv2d(1, 16*m, 7, 1, 3, bias=True) on the fp32 NCHW input (ub_uresnet.py:41,94) -- */
 int ubr_stem_conv_fwd(const float* x /* [n,1,h,w] */, int n, int h, int w, const float* wgt /* [oc,1,7,7] */,
                       const float* bias, int out_ch, ubr_view y, void* stream);
+/* y = relu(conv(x) + bias): the inference form with bn1 folded into (wgt, bias) by the caller (ub_uresnet.py:94-96).
+ * Returns 1 (nothing launched) for shapes without a fused path: the caller runs ubr_stem_conv_fwd + ubr_bn_act. */
+int ubr_stem_conv_fwd_relu(const float* x, int n, int h, int w, const float* wgt, const float* bias, int out_ch,
+                           ubr_view y, void* stream);
 int ubr_stem_conv_wgrad(const float* x, int n, int h, int w, ubr_view dy, float* dw, float* dbias,
                         int accumulate, void* workspace, uint64_t workspace_bytes, void* stream);
 uint64_t ubr_stem_wgrad_workspace_bytes(int n, int h, int w, int out_ch);

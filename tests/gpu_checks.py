@@ -289,6 +289,15 @@ def check_stem(n, h, w, oc=16, seed=0):
            # the stem accumulates fp32-accurate products (stem_tc.cu splits x and W into two bf16 terms each), so
            # nearly every output equals the bf16 rounding of the fp32 reference; plain bf16 operands would not
            (name + "_fwd_not_bf16_of_fp32_ref", 1.0 - (ya.nchw_float().cpu() == bf(ref)).float().mean().item(), 0.05)]
+    # inference form relu(conv + b) into a channel slice (the dec1 skip half of the concat buffer); None = no fused path
+    yr = act_out(n, h, w, oc, 2 * oc, oc)
+    got = ops.stem_conv_fwd_relu(x.to(DEV), wt.to(DEV), b.to(DEV), y=yr)
+    torch.cuda.synchronize()
+    if oc == 16 and w % 128 == 0 and h % 8 == 0:
+        res.append((name + "_fwd_relu", relerr(yr.nchw_float(), F.relu(ref)) if got is not None else 1.0, 6e-3))
+        res.append((name + "_fwd_relu_slice_untouched", (yr.buf[..., :oc].float() - 3.0).abs().max().item(), 0.0))
+    else:
+        res.append((name + "_fwd_relu_declined", 0.0 if got is None else 1.0, 0.0))
     dy = bf(gen(n, oc, h, w, seed=seed + 3))
     ref_dw = torch.nn.grad.conv2d_weight(x, (oc, 1, 7, 7), dy, 1, 3)
     ref_db = dy.sum((0, 2, 3))

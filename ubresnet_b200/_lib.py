@@ -47,6 +47,7 @@ SIGNATURES = {
     "ubr_deconv4s2_dgrad": (_i, [View, _vp, _i, View, _vp]),
     "ubr_deconv4s2_wgrad": (_i, [View, View, _vp, _i, _vp, _u64, _vp]),
     "ubr_stem_conv_fwd": (_i, [_vp, _i, _i, _i, _vp, _vp, _i, View, _vp]),
+    "ubr_stem_conv_fwd_relu": (_i, [_vp, _i, _i, _i, _vp, _vp, _i, View, _vp]),
     "ubr_stem_conv_wgrad": (_i, [_vp, _i, _i, _i, View, _vp, _vp, _i, _vp, _u64, _vp]),
     "ubr_stem_wgrad_workspace_bytes": (_u64, [_i, _i, _i, _i]),
     "ubr_bn_workspace_bytes": (_u64, [_i]),

@@ -60,7 +60,7 @@ constexpr int kMaxStatsRows = 1184;
 constexpr int kStemTcMaxBlocks = 592;          // persistent CTAs (4 per SM); the weight gradient keeps one partial each
 bool stem_tc_eligible(int n, int h, int w, int out_ch);
 int stem_tc_fwd(const float* x, int n, int h, int w, const float* wgt, const float* bias, __nv_bfloat16* y, int yld,
-                cudaStream_t stream);
+                cudaStream_t stream, int relu = 0);
 int stem_tc_wgrad(const float* x, int n, int h, int w, const __nv_bfloat16* dy, int dyld, float* dw, float* dbias,
                   int accumulate, float* workspace, cudaStream_t stream);
 

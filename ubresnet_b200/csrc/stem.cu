@@ -223,6 +223,16 @@ int ubr_stem_conv_fwd(const float* x, int n, int h, int w, const float* wgt, con
   return 0;
 }
 
+int ubr_stem_conv_fwd_relu(const float* x, int n, int h, int w, const float* wgt, const float* bias, int out_ch,
+                           ubr_view y, void* stream) {
+  if (int rc = ensure_device()) return rc;
+  UBR_REQUIRE(x && wgt && y.ptr, "stem_conv_fwd_relu: null pointer");
+  UBR_REQUIRE(y.n == n && y.h == h && y.w == w && y.c == out_ch && y.ld >= out_ch && y.ld % 8 == 0,
+              "stem_conv_fwd_relu: output view mismatch");
+  if (!stem_tc_eligible(n, h, w, out_ch)) return 1;          // caller runs conv + bn_act instead
+  return stem_tc_fwd(x, n, h, w, wgt, bias, (__nv_bfloat16*)y.ptr, y.ld, (cudaStream_t)stream, 1);
+}
+
 uint64_t ubr_stem_wgrad_workspace_bytes(int n, int h, int w, int out_ch) {
   (void)n; (void)h; (void)w;
   const uint64_t cc = (uint64_t)kWgBlocks * (out_ch / 16) * 800 * sizeof(float);

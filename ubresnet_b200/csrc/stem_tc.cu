@@ -35,6 +35,7 @@ struct StemTcParams {
   const float* bias;                         // fwd: [16] or null
   __nv_bfloat16* y;                          // fwd: NHWC view
   int yld;
+  int relu;                                  // fwd: y = max(y, 0) (inference with BatchNorm folded into wgt / bias)
   const __nv_bfloat16* dy;                   // wgrad: NHWC view (16 channels)
   int dyld;
   float* partials;                           // wgrad: [gridDim.x][128][16]
@@ -150,8 +151,12 @@ __device__ __forceinline__ void stem_fwd_store(const StemTcParams& p, uint32_t t
   uint32_t pk[8];
 #pragma unroll
   for (int j = 0; j < 8; ++j)
-    pk[j] = pack_bf16x2(__uint_as_float(v[2 * j]) + __uint_as_float(u[2 * j]) + bias_r[2 * j],
-                        __uint_as_float(v[2 * j + 1]) + __uint_as_float(u[2 * j + 1]) + bias_r[2 * j + 1]);
+  {
+    float a = __uint_as_float(v[2 * j]) + __uint_as_float(u[2 * j]) + bias_r[2 * j];
+    float b = __uint_as_float(v[2 * j + 1]) + __uint_as_float(u[2 * j + 1]) + bias_r[2 * j + 1];
+    if (p.relu) { a = fmaxf(a, 0.f); b = fmaxf(b, 0.f); }
+    pk[j] = pack_bf16x2(a, b);
+  }
   __nv_bfloat16* dst = p.y + pixel * (size_t)p.yld;
   *reinterpret_cast<uint4*>(dst) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
   *reinterpret_cast<uint4*>(dst + 8) = make_uint4(pk[4], pk[5], pk[6], pk[7]);
@@ -402,10 +407,10 @@ bool stem_tc_eligible(int n, int h, int w, int out_ch) {
 }
 
 int stem_tc_fwd(const float* x, int n, int h, int w, const float* wgt, const float* bias, __nv_bfloat16* y, int yld,
-                cudaStream_t st) {
+                cudaStream_t st, int relu) {
   StemTcParams p{};
   UBR_REQUIRE(stem_tc_plan(n, h, w, p), "stem_tc_fwd: shape %dx%dx%d not eligible", n, h, w);
-  p.x = x; p.wgt = wgt; p.bias = bias; p.y = y; p.yld = yld;
+  p.x = x; p.wgt = wgt; p.bias = bias; p.y = y; p.yld = yld; p.relu = relu;
   UBR_CUDA_OK(cudaFuncSetAttribute(stem_tc_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kStemSmemBytes));
   const int grid = p.nstrips < kStemTcMaxBlocks ? p.nstrips : kStemTcMaxBlocks;
   stem_tc_fwd_kernel<<<grid, kSTThreads, kStemSmemBytes, st>>>(p);

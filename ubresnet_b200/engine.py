@@ -30,7 +30,8 @@ class _FoldedConv:
     def __init__(self):
         self.w = self.b = self._key = None
 
-    def refresh(self, conv, bn):
+    def refresh(self, conv, bn, packed=True):
+        """packed=False keeps W' as fp32 OIHW (the stem kernel reads fp32 weights)"""
         srcs = [conv.weight, conv.bias, bn.weight, bn.bias, bn.running_mean, bn.running_var]
         key = tuple((t.data_ptr(), t._version) if t is not None else None for t in srcs) + (bn.eps,)
         if key == self._key:
@@ -44,7 +45,8 @@ class _FoldedConv:
                 shift = shift + bn.bias.float()
             if conv.bias is not None:
                 shift = shift + conv.bias.float() * scale
-            self.w = ops.pack_weights((conv.weight.float() * scale.view(-1, 1, 1, 1)).contiguous(), False, True)
+            wf = (conv.weight.float() * scale.view(-1, 1, 1, 1)).contiguous()
+            self.w = ops.pack_weights(wf, False, True) if packed else wf
             self.b = shift.contiguous()
         self._key = key
         return self
@@ -287,9 +289,15 @@ class Engine:
     def _stem_fwd(self, x, x0_out, training, need_grad, bn_ws):
         """conv1 -> bn1 -> relu1 -> pool1 (ub_uresnet.py:94-97); x0 lands in `x0_out` (the dec1 skip slice)."""
         m = self.model
-        y0 = ops.stem_conv_fwd(x, m.conv1.weight, m.conv1.bias)
-        st0 = self._bn(y0, m.bn1, training, bn_ws)
-        x0 = ops.bn_act(y0, st0, True, out=x0_out)
+        x0 = None
+        if FOLD_EVAL_BN and not training and not need_grad:
+            f0 = self._folded(m.conv1, m.bn1, packed=False)
+            x0 = ops.stem_conv_fwd_relu(x, f0.w, f0.b, y=x0_out)
+            y0 = st0 = None
+        if x0 is None:
+            y0 = ops.stem_conv_fwd(x, m.conv1.weight, m.conv1.bias)
+            st0 = self._bn(y0, m.bn1, training, bn_ws)
+            x0 = ops.bn_act(y0, st0, True, out=x0_out)
         if need_grad:
             h0, pool_idx = ops.maxpool_fwd_idx(x0)
         else:
@@ -373,11 +381,11 @@ class Engine:
         return ops.deconv_dgrad(dy, wd.dgrad, in_ch)
 
     # ------------------------------------------------------------------ forward pieces
-    def _folded(self, conv, bn):
+    def _folded(self, conv, bn, packed=True):
         ent = self._folds.get(id(conv))
         if ent is None:
             ent = self._folds[id(conv)] = _FoldedConv()
-        return ent.refresh(conv, bn)
+        return ent.refresh(conv, bn, packed)
 
     def _block_fwd_folded(self, blk, x, out):
         """eval-mode BasicBlock (common_layers.py:39-58) in three launches: BatchNorm folded into the conv operands,

@@ -291,6 +291,22 @@ def stem_conv_fwd(x, w, b, y=None):
     return y
 
 
+def stem_conv_fwd_relu(x, w, b, y=None):
+    """relu(conv(x) + b) for folded inference weights; returns None when the shape has no fused path."""
+    lib = _lib.load()
+    require_cuda(x, "input")
+    n, cin, h, wd = x.shape
+    assert cin == 1 and x.dtype == torch.float32 and x.is_contiguous()
+    oc = w.shape[0]
+    if y is None:
+        y = Act.empty(n, h, wd, oc, x.device)
+    rc = lib.ubr_stem_conv_fwd_relu(x.data_ptr(), n, h, wd, w.data_ptr(), _ptr(b), oc, y.view(), _stream())
+    if rc == 1:
+        return None
+    _lib.check(rc, "stem_conv_fwd_relu")
+    return y
+
+
 def stem_wgrad_workspace_bytes(n, h, w, oc):
     return int(_lib.load().ubr_stem_wgrad_workspace_bytes(n, h, w, oc))
 
