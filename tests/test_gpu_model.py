@@ -54,3 +54,44 @@ def test_wholeview_deploy_bitexact_tiling():
     tiles = torch.randn(len(plan), 3, 128, 128)
     st = wholeview.stitch(tiles.cuda(), plan, 256, 448)
     assert (st.cpu().numpy() == port.stitch_scatter_np(tiles.numpy(), plan, 256, 448)).all()
+
+
+def test_wholeview_run_event_matches_per_crop_pipeline():
+    """deploy/wholeview.run_event (all planes' crops in one forward) == gather -> per-chunk forward -> stitch, bit for bit,
+    for any crops-per-forward setting"""
+    from ubresnet_b200 import synthetic
+    from ubresnet_b200.deploy import wholeview
+    from ubresnet_b200.models import UResNet
+    torch.manual_seed(7)
+    model = UResNet(num_classes=3, input_channels=1, inplanes=16).cuda().eval()
+    ev = synthetic.make_wholeview(rows=256, cols=448, planes=2)
+    plan = wholeview.tile_plan(256, 448, 128)
+    with torch.no_grad():
+        ref = []
+        for p in range(2):
+            crops = wholeview.gather(ev[p].cuda(), plan, 128)
+            outs = torch.cat([model(crops[i:i + 3]) for i in range(0, crops.shape[0], 3)], 0)
+            ref.append(wholeview.stitch(outs, plan, 256, 448))
+        ref = torch.stack(ref, 0)
+    full = wholeview.run_event(model, ev, crop=128)
+    chunked = wholeview.run_event(model, ev, crop=128, batch=5)
+    assert full.shape == (2, 3, 256, 448)
+    assert torch.equal(full, ref) and torch.equal(chunked, ref)
+
+
+def test_wholeview_run_events_pipeline_matches_run_event():
+    """the overlapped deploy loop yields, in order, exactly argmax(run_event) of each event"""
+    from ubresnet_b200 import synthetic
+    from ubresnet_b200.deploy import wholeview
+    from ubresnet_b200.models import UResNet
+    torch.manual_seed(11)
+    model = UResNet(num_classes=3, input_channels=1, inplanes=16).cuda().eval()
+    events = [synthetic.make_wholeview(seed=100 + i, rows=256, cols=448, planes=2).pin_memory() for i in range(5)]
+    refs = [wholeview.run_event(model, e, crop=128).argmax(1).to(torch.uint8).cpu() for e in events]
+    got = [m.clone() for m in wholeview.run_events(model, events, crop=128)]
+    assert len(got) == len(refs)
+    for g, r in zip(got, refs):
+        assert g.shape == (2, 256, 448) and torch.equal(g, r)
+    assert list(wholeview.run_events(model, [], crop=128)) == []
+    one = [m.clone() for m in wholeview.run_events(model, events[:1], crop=128)]
+    assert len(one) == 1 and torch.equal(one[0], refs[0])
