@@ -1,5 +1,5 @@
 """Summarise an `ncu --metrics gpu__time_duration.sum --csv` launch list: per kernel name (and optionally grid) totals
-over ONE training step (launch window selected by --first/--count or the first stem_fwd_kernel..next stem_fwd_kernel)."""
+over ONE training step (launch window = one stem forward kernel to the next, after the warm-up step)."""
 import csv
 import re
 import sys
@@ -18,7 +18,9 @@ def load(path):
 
 
 def one_step(rows):
-    idx = [i for i, r in enumerate(rows) if r[0].startswith("stem_fwd_kernel")]
+    idx = [i for i, r in enumerate(rows) if r[0].startswith(("stem_fwd_kernel", "stem_tc_fwd_kernel"))]
+    if len(idx) >= 3:
+        return rows[idx[1]:idx[2]]          # the first window is the warm-up step (weight packing, allocations)
     if len(idx) >= 2:
         return rows[idx[0]:idx[1]]
     return rows

@@ -23,8 +23,10 @@ PY
 echo "conv kernel launches per step: $PER"
 timeout 900 ncu --metrics $M --clock-control none -k regex:"conv_gemm_kernel|wgrad_gemm_kernel|halo_kernel" --launch-skip $((2*PER)) -c $PER --csv --log-file $OUT/${TAG}_conv_traffic.csv $CMD > $OUT/${TAG}_ncu_traffic.log 2>&1
 echo "traffic pass rc=$?"
+if [ -z "${SKIP_FULL:-}" ]; then
 timeout 600 ncu --set full --clock-control none --import-source on -k regex:"conv_gemm_kernel|wgrad_gemm_kernel" --launch-skip 290 -c 10 -o /tmp/${TAG}_gemm_full $CMD > $OUT/${TAG}_ncu_full.log 2>&1
 echo "set full rc=$?"
 ncu -i /tmp/${TAG}_gemm_full.ncu-rep --page raw --csv > $OUT/${TAG}_gemm_full_raw.csv 2>/dev/null
 ncu -i /tmp/${TAG}_gemm_full.ncu-rep --page details --csv > $OUT/${TAG}_gemm_full_details.csv 2>/dev/null
+fi
 ls -la $OUT
