@@ -166,14 +166,18 @@ int ubr_bn_act_bwd_apply(ubr_view dout, ubr_view y, const float* scale, const fl
                          const float* invstd, const float* gamma, int relu, const void* workspace, double count,
                          ubr_view dy, float* dgamma, float* dbeta, int accumulate, void* stream);
 /* backward of the block tail.  du = dout*(out>0); main branch dz2 = du*(bn2(y2)>0); residual branch gets du.
- * res_is_bn=1: residual is bnpass(bypass conv) -> dres = BN backward of du wrt `res` (pre-BN conv output)
- * res_is_bn=0: identity residual -> dres = du */
+ * res_is_bn=1: residual is bnpass(bypass conv) -> dres = BN backward of du wrt `res` (pre-BN conv output); the mask
+ *              (out>0) is recomputed from y2 and res with the forward arithmetic and the residual affine
+ *              (scaler, shiftr) -- `out` is not read and may be a null view
+ * res_is_bn=0: identity residual -> dres = du (scaler / shiftr unused) */
 int ubr_block_tail_bwd_reduce(ubr_view dout, ubr_view out, ubr_view y2, const float* s2, const float* b2,
                               const float* mean2, const float* invstd2, ubr_view res, const float* meanr,
-                              const float* invstdr, int res_is_bn, void* workspace, void* stream);
+                              const float* invstdr, const float* scaler, const float* shiftr, int res_is_bn,
+                              void* workspace, void* stream);
 int ubr_block_tail_bwd_apply(ubr_view dout, ubr_view out, ubr_view y2, const float* s2, const float* b2,
                              const float* mean2, const float* invstd2, const float* gamma2,
                              ubr_view res, const float* meanr, const float* invstdr, const float* gammar,
+                             const float* scaler, const float* shiftr,
                              int res_is_bn, const void* workspace, double count, ubr_view dy2, ubr_view dres,
                              float* dgamma2, float* dbeta2, float* dgammar, float* dbetar, int accumulate,
                              void* stream);

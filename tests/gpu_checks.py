@@ -434,10 +434,11 @@ def check_block_tail(c, n, h, w, bypass, seed=0):
     out = ops.block_tail(y2a, st2, ra, str_)
     torch.cuda.synchronize()
     res = [(name + "_fwd", relerr(out.nchw_float(), ref), 8e-3)]
-    # backward uses the STORED (bf16) out for the outer mask, like the engine does
+    # identity residual: the STORED (bf16) out gives the outer mask; BatchNorm'd residual: the kernels recompute it from
+    # y2 and res with the forward arithmetic and never read `out` (None here)
     dg2, db2 = torch.zeros(c, device=DEV), torch.zeros(c, device=DEV)
     dgr, dbr = torch.zeros(c, device=DEV), torch.zeros(c, device=DEV)
-    dy2, dres = ops.block_tail_bwd(act_from(dout), out, y2a, st2, ra, str_, gr.to(DEV) if bypass else None, ws, dg2, db2,
+    dy2, dres = ops.block_tail_bwd(act_from(dout), None if bypass else out, y2a, st2, ra, str_, gr.to(DEV) if bypass else None, ws, dg2, db2,
                                    dgr if bypass else None, dbr if bypass else None)
     torch.cuda.synchronize()
     res += [(name + "_dy2", relerr(dy2.nchw_float(), t[0].grad), 1.5e-2),

@@ -157,22 +157,33 @@ def train_parity(batch=2, size=128, num_classes=3, dense=False, seed=1234, arch=
     return res, detail
 
 
-def eval_parity(batch=2, size=128, num_classes=3, seed=77, arch="uresnet"):
-    model, sd = build_pair(num_classes=num_classes, seed=seed, arch=arch)
+def eval_parity(batch=2, size=128, num_classes=3, seed=77, arch="uresnet", inplanes=16):
+    """eval() forward under no_grad: the BatchNorm-folded inference path (engine._block_fwd_folded) against the oracle,
+    and against the unfolded kernel schedule of the same weights"""
+    from ubresnet_b200 import engine as _engine
+    model, sd = build_pair(num_classes=num_classes, inplanes=inplanes, seed=seed, arch=arch)
     port = aspp_port if arch == "aspp" else globals()["port"]
-    img, _, _ = synthetic.make_batch(batch, size, size)
+    hh, ww = size if isinstance(size, tuple) else (size, size)
+    img, _, _ = synthetic.make_batch(batch, hh, ww)
     with torch.no_grad():
         logp_ref = port.forward(port.clone_state_dict(sd), img, training=False)
         logp_emu = port.forward(port.clone_state_dict(sd), img, training=False, quant=True)
         model.eval()
         logp = model(img.to(DEV))
+        _engine.FOLD_EVAL_BN = False
+        try:
+            logp_unfolded = model(img.to(DEV))
+        finally:
+            _engine.FOLD_EVAL_BN = True
     torch.cuda.synchronize()
     nz = img[:, 0] != 0
     e_emu = _rel(logp_emu, logp_ref)
     a_emu = _argmax_disagree(logp_emu, logp_ref, nz)
     return [("eval_logp_rel (emulated-bf16 oracle: %.2e)" % e_emu, _rel(logp, logp_ref), max(TOL_LOGP, SLACK * e_emu)),
             ("eval_argmax_disagree_nonzero (emulated: %.2e)" % a_emu, _argmax_disagree(logp, logp_ref, nz),
-             max(1.0 - TOL_ARGMAX, SLACK * a_emu))], {}
+             max(1.0 - TOL_ARGMAX, SLACK * a_emu)),
+            ("eval_unfolded_logp_rel", _rel(logp_unfolded, logp_ref), max(TOL_LOGP, SLACK * e_emu)),
+            ("eval_folded_vs_unfolded_rel", _rel(logp, logp_unfolded), max(TOL_LOGP, SLACK * e_emu))], {}
 
 
 def golden_parity(path=None, arch="uresnet"):
@@ -225,6 +236,9 @@ CHECKS = {
     "train_odd_3x96x160": lambda: train_parity(3, (96, 160), dense=True, seed=31),      # partial tiles, odd batch
     "train_inplanes32_128": lambda: train_parity(2, 128, inplanes=32, seed=41),   # train_ubresnet2018_wlarcv2.py:88
     "eval_128": lambda: eval_parity(2, 128),
+    "eval_odd_3x96x160": lambda: eval_parity(3, (96, 160), seed=78),                # implicit-GEMM epilogues, partial tiles
+    "eval_256_c4": lambda: eval_parity(1, 256, num_classes=4, seed=79),            # deploy/ubresnet_funcs.py:41-68 shape
+    "eval_inplanes32_128": lambda: eval_parity(2, 128, inplanes=32, seed=80),
     "golden": lambda: golden_parity(),
     # ASPP_ResNet (BASELINE.json configs[4]; reference models/ASPP_ResNet.py)
     "aspp_train_256": lambda: train_parity(2, 256, arch="aspp", seed=321),

@@ -59,8 +59,8 @@ SIGNATURES = {
     "ubr_block_tail": (_i, [View, _vp, _vp, View, _vp, _vp, View, _vp]),
     "ubr_bn_act_bwd_reduce": (_i, [View, View, _vp, _vp, _vp, _vp, _i, _vp, _vp]),
     "ubr_bn_act_bwd_apply": (_i, [View, View, _vp, _vp, _vp, _vp, _vp, _i, _vp, _d, View, _vp, _vp, _i, _vp]),
-    "ubr_block_tail_bwd_reduce": (_i, [View, View, View, _vp, _vp, _vp, _vp, View, _vp, _vp, _i, _vp, _vp]),
-    "ubr_block_tail_bwd_apply": (_i, [View, View, View, _vp, _vp, _vp, _vp, _vp, View, _vp, _vp, _vp, _i, _vp, _d,
+    "ubr_block_tail_bwd_reduce": (_i, [View, View, View, _vp, _vp, _vp, _vp, View, _vp, _vp, _vp, _vp, _i, _vp, _vp]),
+    "ubr_block_tail_bwd_apply": (_i, [View, View, View, _vp, _vp, _vp, _vp, _vp, View, _vp, _vp, _vp, _vp, _vp, _i, _vp, _d,
                                       View, View, _vp, _vp, _vp, _vp, _i, _vp]),
     "ubr_maxpool3s2_fwd": (_i, [View, View, _vp]),
     "ubr_maxpool3s2_bwd": (_i, [View, View, View, _i, _vp]),

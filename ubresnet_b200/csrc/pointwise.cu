@@ -364,7 +364,10 @@ __global__ void __launch_bounds__(kRedThreads, 2) tail_bwd_reduce_kernel(DView d
                                                                       const float* b2, const float* mean2,
                                                                       const float* invstd2, DView res,
                                                                       const float* meanr, const float* invstdr,
+                                                                      const float* sr, const float* br,
                                                                       float* partials) {
+  // RES_BN: the mask of the block's final ReLU is recomputed from y2 and the bypass output with the forward pass's own
+  // arithmetic (block_tail_kernel) instead of reading `out` back
   constexpr int NS = RES_BN ? 4 : 2;
   constexpr int U = RES_BN ? 1 : 2;      // 4 tensors in flight per pixel group with the residual BN: no unroll (registers)
   const int cgs = y2.c >> 3, lanes = blockDim.x / cgs;
@@ -372,7 +375,8 @@ __global__ void __launch_bounds__(kRedThreads, 2) tail_bwd_reduce_kernel(DView d
   float sc[8], sh[8], mu[8], is[8], mur[8], isr[8];
   ldparam8(s2, cg * 8, sc); ldparam8(b2, cg * 8, sh);
   ldparam8(mean2, cg * 8, mu); ldparam8(invstd2, cg * 8, is);
-  if (RES_BN) { ldparam8(meanr, cg * 8, mur); ldparam8(invstdr, cg * 8, isr); }
+  float ar[8], cr[8];
+  if (RES_BN) { ldparam8(meanr, cg * 8, mur); ldparam8(invstdr, cg * 8, isr); ldparam8(sr, cg * 8, ar); ldparam8(br, cg * 8, cr); }
   float acc[NS][8];
 #pragma unroll
   for (int s = 0; s < NS; ++s)
@@ -386,7 +390,7 @@ __global__ void __launch_bounds__(kRedThreads, 2) tail_bwd_reduce_kernel(DView d
       const long q = p + u * ps;
       if (q < y2.npix) {
         rg[u] = ldraw(dout.ptr + q * dout.ld + cg * 8);
-        ro[u] = ldraw(out.ptr + q * out.ld + cg * 8);
+        ro[u] = RES_BN ? make_uint4(0u, 0u, 0u, 0u) : ldraw(out.ptr + q * out.ld + cg * 8);
         rv[u] = ldraw(y2.ptr + q * y2.ld + cg * 8);
         rr4[u] = RES_BN ? ldraw(res.ptr + q * res.ld + cg * 8) : make_uint4(0u, 0u, 0u, 0u);
       } else {
@@ -402,8 +406,9 @@ __global__ void __launch_bounds__(kRedThreads, 2) tail_bwd_reduce_kernel(DView d
       unpack8(rr4[u], r);
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
-        const float du = o[j] > 0.f ? g[j] : 0.f;
         const float z = fmaf(v[j], sc[j], sh[j]);
+        const bool on = RES_BN ? (fmaxf(z, 0.f) + fmaf(r[j], ar[j], cr[j]) > 0.f) : (o[j] > 0.f);
+        const float du = on ? g[j] : 0.f;
         const float dz = z > 0.f ? du : 0.f;
         acc[0][j] += dz;
         acc[1][j] = fmaf(dz, (v[j] - mu[j]) * is[j], acc[1][j]);
@@ -424,11 +429,13 @@ __global__ void __launch_bounds__(256, 2) tail_bwd_apply_kernel(DView dout, DVie
                                                                 const float* b2, const float* mean2,
                                                                 const float* invstd2, DView res, const float* meanr,
                                                                 const float* invstdr, const float* gammar,
+                                                                const float* sr, const float* br,
                                                                 const float* sums, float inv_count, DViewW dy2,
                                                                 DViewW dres) {
   const int c = y2.c;
   const EwIdx ix = ew_index(c >> 3);
-  float sc[8], sh[8], ca[8], cb[8], gr[8], ra[8], rb[8];
+  float sc[8], sh[8], ca[8], cb[8], gr[8], ra[8], rb[8], ar[8], cr[8];
+  if (RES_BN) { ldparam8(sr, ix.cg * 8, ar); ldparam8(br, ix.cg * 8, cr); }
   {
     float mu[8], is[8], t0[8], t1[8];
     ldparam8(s2, ix.cg * 8, sc); ldparam8(b2, ix.cg * 8, sh);
@@ -457,7 +464,7 @@ __global__ void __launch_bounds__(256, 2) tail_bwd_apply_kernel(DView dout, DVie
       const long q = p + u * ix.ps;
       if (q < y2.npix) {
         rg[u] = ldraw(dout.ptr + q * dout.ld + ix.cg * 8);
-        ro[u] = ldraw(out.ptr + q * out.ld + ix.cg * 8);
+        if (!RES_BN) ro[u] = ldraw(out.ptr + q * out.ld + ix.cg * 8);
         rv[u] = ldraw(y2.ptr + q * y2.ld + ix.cg * 8);
         if (RES_BN) rr4[u] = ldraw(res.ptr + q * res.ld + ix.cg * 8);
       }
@@ -466,21 +473,21 @@ __global__ void __launch_bounds__(256, 2) tail_bwd_apply_kernel(DView dout, DVie
     for (int u = 0; u < 2; ++u) {
       const long q = p + u * ix.ps;
       if (q < y2.npix) {
-        float du[8], d2[8], g[8], o[8], v[8];
+        float du[8], d2[8], g[8], o[8], v[8], r[8];
         unpack8(rg[u], g);
-        unpack8(ro[u], o);
+        if (!RES_BN) unpack8(ro[u], o);
         unpack8(rv[u], v);
+        if (RES_BN) unpack8(rr4[u], r);
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
-          du[j] = o[j] > 0.f ? g[j] : 0.f;
           const float z = fmaf(v[j], sc[j], sh[j]);
+          const bool on = RES_BN ? (fmaxf(z, 0.f) + fmaf(r[j], ar[j], cr[j]) > 0.f) : (o[j] > 0.f);
+          du[j] = on ? g[j] : 0.f;
           const float dz = z > 0.f ? du[j] : 0.f;
           d2[j] = fmaf(sc[j], dz, fmaf(ca[j], v[j], cb[j]));
         }
         store8(dy2.ptr + q * dy2.ld + ix.cg * 8, d2);
         if (RES_BN) {
-          float r[8];
-          unpack8(rr4[u], r);
 #pragma unroll
           for (int j = 0; j < 8; ++j) du[j] = fmaf(gr[j], du[j], fmaf(ra[j], r[j], rb[j]));
         }
@@ -982,13 +989,16 @@ int ubr_bn_act_bwd_apply(ubr_view dout, ubr_view y, const float* scale, const fl
 
 int ubr_block_tail_bwd_reduce(ubr_view dout, ubr_view out, ubr_view y2, const float* s2, const float* b2,
                               const float* mean2, const float* invstd2, ubr_view res, const float* meanr,
-                              const float* invstdr, int res_is_bn, void* workspace, void* stream) {
+                              const float* invstdr, const float* scaler, const float* shiftr, int res_is_bn,
+                              void* workspace, void* stream) {
   if (int rc = ensure_device()) return rc;
   if (int rc = chk_red(y2, "block_tail_bwd_reduce.y2")) return rc;
   if (int rc = chk(dout, "block_tail_bwd_reduce.dout")) return rc;
-  if (int rc = chk(out, "block_tail_bwd_reduce.out")) return rc;
+  if (!res_is_bn) {                                 // with a BatchNorm'd residual `out` is not read (mask recomputed)
+    if (int rc = chk(out, "block_tail_bwd_reduce.out")) return rc;
+    if (int rc = same_shape(y2, out, "block_tail_bwd_reduce(out)")) return rc;
+  }
   if (int rc = same_shape(y2, dout, "block_tail_bwd_reduce(dout)")) return rc;
-  if (int rc = same_shape(y2, out, "block_tail_bwd_reduce(out)")) return rc;
   UBR_REQUIRE(s2 && b2 && mean2 && invstd2 && workspace, "block_tail_bwd_reduce: null pointer");
   DView v = dv(y2);
   const int nb = red_blocks(v.npix, v.c, kBwdRedBlocks);
@@ -996,12 +1006,12 @@ int ubr_block_tail_bwd_reduce(ubr_view dout, ubr_view out, ubr_view y2, const fl
   if (res_is_bn) {
     if (int rc = chk(res, "block_tail_bwd_reduce.res")) return rc;
     if (int rc = same_shape(y2, res, "block_tail_bwd_reduce(res)")) return rc;
-    UBR_REQUIRE(meanr && invstdr, "block_tail_bwd_reduce: null residual stats");
+    UBR_REQUIRE(meanr && invstdr && scaler && shiftr, "block_tail_bwd_reduce: null residual stats / affine");
     tail_bwd_reduce_kernel<true><<<nb, kRedThreads, kRedThreads * 32 * sizeof(float), st>>>(
-        dv(dout), dv(out), v, s2, b2, mean2, invstd2, dv(res), meanr, invstdr, (float*)workspace);
+        dv(dout), v, v, s2, b2, mean2, invstd2, dv(res), meanr, invstdr, scaler, shiftr, (float*)workspace);
   } else {
     tail_bwd_reduce_kernel<false><<<nb, kRedThreads, kRedThreads * 16 * sizeof(float), st>>>(
-        dv(dout), dv(out), v, s2, b2, mean2, invstd2, v, nullptr, nullptr, (float*)workspace);
+        dv(dout), dv(out), v, s2, b2, mean2, invstd2, v, nullptr, nullptr, nullptr, nullptr, (float*)workspace);
   }
   UBR_LAUNCH_CHECK("tail_bwd_reduce_kernel");
   return 0;
@@ -1009,17 +1019,20 @@ int ubr_block_tail_bwd_reduce(ubr_view dout, ubr_view out, ubr_view y2, const fl
 
 int ubr_block_tail_bwd_apply(ubr_view dout, ubr_view out, ubr_view y2, const float* s2, const float* b2,
                              const float* mean2, const float* invstd2, const float* gamma2, ubr_view res,
-                             const float* meanr, const float* invstdr, const float* gammar, int res_is_bn,
+                             const float* meanr, const float* invstdr, const float* gammar, const float* scaler,
+                             const float* shiftr, int res_is_bn,
                              const void* workspace, double count, ubr_view dy2, ubr_view dres, float* dgamma2,
                              float* dbeta2, float* dgammar, float* dbetar, int accumulate, void* stream) {
   if (int rc = ensure_device()) return rc;
   if (int rc = chk_red(y2, "block_tail_bwd_apply.y2")) return rc;
   if (int rc = chk(dout, "block_tail_bwd_apply.dout")) return rc;
-  if (int rc = chk(out, "block_tail_bwd_apply.out")) return rc;
+  if (!res_is_bn) {
+    if (int rc = chk(out, "block_tail_bwd_apply.out")) return rc;
+    if (int rc = same_shape(y2, out, "block_tail_bwd_apply(out)")) return rc;
+  }
   if (int rc = chk(dy2, "block_tail_bwd_apply.dy2")) return rc;
   if (int rc = chk(dres, "block_tail_bwd_apply.dres")) return rc;
   if (int rc = same_shape(y2, dout, "block_tail_bwd_apply(dout)")) return rc;
-  if (int rc = same_shape(y2, out, "block_tail_bwd_apply(out)")) return rc;
   if (int rc = same_shape(y2, dy2, "block_tail_bwd_apply(dy2)")) return rc;
   if (int rc = same_shape(y2, dres, "block_tail_bwd_apply(dres)")) return rc;
   UBR_REQUIRE(s2 && b2 && mean2 && invstd2 && workspace, "block_tail_bwd_apply: null pointer");
@@ -1037,14 +1050,14 @@ int ubr_block_tail_bwd_apply(ubr_view dout, ubr_view out, ubr_view y2, const flo
   const unsigned blocks = ew_grid(v.npix, v.c >> 3, 2);
   if (res_is_bn) {
     if (int rc = chk(res, "block_tail_bwd_apply.res")) return rc;
-    UBR_REQUIRE(meanr && invstdr && gammar, "block_tail_bwd_apply: null residual stats");
-    tail_bwd_apply_kernel<true><<<blocks, 256, 0, st>>>(dv(dout), dv(out), v, s2, b2, mean2, invstd2, dv(res), meanr,
-                                                        invstdr, gammar, sums, (float)(1.0 / count), dvw(dy2),
-                                                        dvw(dres));
+    UBR_REQUIRE(meanr && invstdr && gammar && scaler && shiftr, "block_tail_bwd_apply: null residual stats / affine");
+    tail_bwd_apply_kernel<true><<<blocks, 256, 0, st>>>(dv(dout), v, v, s2, b2, mean2, invstd2, dv(res), meanr,
+                                                        invstdr, gammar, scaler, shiftr, sums, (float)(1.0 / count),
+                                                        dvw(dy2), dvw(dres));
   } else {
     tail_bwd_apply_kernel<false><<<blocks, 256, 0, st>>>(dv(dout), dv(out), v, s2, b2, mean2, invstd2, v, nullptr,
-                                                         nullptr, nullptr, sums, (float)(1.0 / count), dvw(dy2),
-                                                         dvw(dres));
+                                                         nullptr, nullptr, nullptr, nullptr, sums, (float)(1.0 / count),
+                                                         dvw(dy2), dvw(dres));
   }
   UBR_LAUNCH_CHECK("tail_bwd_apply_kernel");
   return 0;

@@ -390,7 +390,8 @@ def bn_act_bwd(dout, y, st, relu, ws, dgamma=None, dbeta=None, accumulate=False,
 
 def block_tail_bwd(dout, out, y2, st2, res, st_res, gamma_res, ws, dgamma2=None, dbeta2=None, dgamma_res=None,
                    dbeta_res=None, accumulate=False, dy2=None, dres=None):
-    """Backward of the ReLU-add-ReLU block tail.  Returns (dy2, dres)."""
+    """Backward of the ReLU-add-ReLU block tail.  Returns (dy2, dres).  With a BatchNorm'd residual (`st_res`) the
+    kernels recompute the final ReLU's mask from y2 and res, so `out` is not read and may be None."""
     lib = _lib.load()
     dev = y2.buf.device
     if dy2 is None:
@@ -402,12 +403,15 @@ def block_tail_bwd(dout, out, y2, st2, res, st_res, gamma_res, ws, dgamma2=None,
     rv = res.view() if res_bn else _NULLVIEW
     mr = st_res.mean.data_ptr() if res_bn else 0
     ir = st_res.invstd.data_ptr() if res_bn else 0
-    _lib.check(lib.ubr_block_tail_bwd_reduce(dout.view(), out.view(), y2.view(), st2.scale.data_ptr(),
+    sr = st_res.scale.data_ptr() if res_bn else 0
+    br = st_res.shift.data_ptr() if res_bn else 0
+    ov = out.view() if (out is not None and not res_bn) else _NULLVIEW
+    _lib.check(lib.ubr_block_tail_bwd_reduce(dout.view(), ov, y2.view(), st2.scale.data_ptr(),
                                              st2.shift.data_ptr(), st2.mean.data_ptr(), st2.invstd.data_ptr(), rv, mr,
-                                             ir, int(res_bn), ws.data_ptr(), s), "block_tail_bwd_reduce")
-    _lib.check(lib.ubr_block_tail_bwd_apply(dout.view(), out.view(), y2.view(), st2.scale.data_ptr(),
+                                             ir, sr, br, int(res_bn), ws.data_ptr(), s), "block_tail_bwd_reduce")
+    _lib.check(lib.ubr_block_tail_bwd_apply(dout.view(), ov, y2.view(), st2.scale.data_ptr(),
                                             st2.shift.data_ptr(), st2.mean.data_ptr(), st2.invstd.data_ptr(), 0, rv, mr,
-                                            ir, _ptr(gamma_res), int(res_bn), ws.data_ptr(), st2.count, dy2.view(),
+                                            ir, _ptr(gamma_res), sr, br, int(res_bn), ws.data_ptr(), st2.count, dy2.view(),
                                             dres.view(), _ptr(dgamma2), _ptr(dbeta2), _ptr(dgamma_res), _ptr(dbeta_res),
                                             int(accumulate), s), "block_tail_bwd_apply")
     return dy2, dres
