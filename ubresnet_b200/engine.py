@@ -549,11 +549,14 @@ class Engine:
         self._wgrad_begin(dev)
 
         def done(name):
+            self._wgrad_stage()
             if sink is not None and sink.wants(name):
-                self._wgrad_join()             # the bucket's weight gradients must be complete before its all-reduce
+                # the bucket's all-reduce waits (on the communication stream) for the weight gradients queued on the
+                # side stream up to here; the main stream itself does not stop
+                side = [self._w_prev[0]] if (self._w_on and self._w_prev is not None) else []
+                sink.stage_done(name, side)
+            elif sink is not None:
                 sink.stage_done(name)
-            else:
-                self._wgrad_stage()
         # ---- head
         dcur = self._head_bwd(saved, dlogp, grads, bn_ws, wg_ws)
         done("head")

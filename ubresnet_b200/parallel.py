@@ -13,8 +13,13 @@ one process per GPU:
 
 The path has exactly one exchange step (the gradient all-reduce); activations never leave the GPU.
 """
+import os
+
 import torch
 import torch.distributed as dist
+
+# UBR_DP_OVERLAP=0: launch every bucket's all-reduce at the end of backward instead of as soon as the bucket is complete
+DP_OVERLAP = os.environ.get("UBR_DP_OVERLAP", "1") != "0"
 
 STAGE_ORDER = ["head", "dec1", "dec2", "dec3", "dec4", "dec5", "enc5", "enc4", "enc3", "enc2", "enc1", "stem"]
 ASPP_STAGE_ORDER = STAGE_ORDER[:6] + ["aspp"] + STAGE_ORDER[6:]          # backward order of engine_aspp.ASPPEngine
@@ -67,24 +72,32 @@ class GradBuckets:
         self.is_cuda = device.type == "cuda"
         self.comm_stream = torch.cuda.Stream(device=device) if self.is_cuda else None
         self._pending = []
+        self._deferred = []
         self.nbytes = sum(t.numel() * 4 for t in self.flat.values())
 
     # ---- Engine sink protocol
     def grad_buffer(self, param):
-        return self.views[param]
+        # a FRESH tensor object over the bucket storage: autograd's AccumulateGrad adopts a gradient it holds the only
+        # reference to, but clones one that something else (our `views` table) also references -- 165 copy kernels/step
+        return self.views[param].view(param.shape)
 
     def wants(self, stage):
         """True when `stage` closes a bucket (its all-reduce is launched by stage_done)."""
         b = BUCKET_OF_STAGE[stage]
         return LAST_STAGE_OF_BUCKET[b] == stage and b in self.flat
 
-    def stage_done(self, stage):
+    def stage_done(self, stage, wait_events=()):
+        """`wait_events`: CUDA events of other streams (the engine's weight-gradient side stream) that the bucket's
+        all-reduce must also wait for."""
         b = BUCKET_OF_STAGE[stage]
         if LAST_STAGE_OF_BUCKET[b] != stage or b not in self.flat:
             return
-        self._launch(b)
+        if not DP_OVERLAP:
+            self._deferred.append(b)
+            return
+        self._launch(b, wait_events)
 
-    def _launch(self, b):
+    def _launch(self, b, wait_events=()):
         flat = self.flat[b]
         if self.world == 1:
             return
@@ -92,6 +105,8 @@ class GradBuckets:
             ready = torch.cuda.Event()
             ready.record()                              # on the compute (current) stream
             self.comm_stream.wait_event(ready)
+            for ev in wait_events:
+                self.comm_stream.wait_event(ev)
             with torch.cuda.stream(self.comm_stream):
                 work = dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=self.group, async_op=True)
             self._pending.append((b, work))
@@ -100,6 +115,9 @@ class GradBuckets:
             self._pending.append((b, work))
 
     def finish(self):
+        for b in self._deferred:          # UBR_DP_OVERLAP=0: backward (incl. the weight-gradient stream) is complete here
+            self._launch(b)
+        self._deferred = []
         for b, work in self._pending:
             if self.is_cuda:
                 with torch.cuda.stream(self.comm_stream):
