@@ -88,7 +88,7 @@ int ubr_conv2d_fwd_fused(ubr_view x, const void* wpk, const float* bias, int out
 /* data gradient of the same conv: dx = conv_transpose(dy, W).  wpk = pack(..., n_is_out=0). */
 int ubr_conv2d_dgrad(ubr_view dy, const void* wpk, int in_ch, int ksize, int stride, ubr_view dx, void* stream);
 /* dx += conv_transpose(dy, W), fused into the epilogue (fp32 add of the stored bf16 value, one rounding).
- * Returns 1 (and does nothing) when the shape has no fused path: the caller then adds with ubr_add. */
+ * Returns 1 (and does nothing) when the shape has no fused path (stride 2): the caller then adds with ubr_add. */
 int ubr_conv2d_dgrad_acc(ubr_view dy, const void* wpk, int in_ch, int ksize, int stride, ubr_view dx, void* stream);
 /* weight gradient: dw[o,i,r,s] (+)= sum_pixels dy[.,o] * x[shifted,i]; fp32 OIHW.  accumulate: 0 overwrite, 1 add */
 int ubr_conv2d_wgrad(ubr_view x, ubr_view dy, int out_ch /* true rows of dw; dy.c may be padded */, int ksize,

@@ -671,8 +671,10 @@ CHECKS = {
     "gemm_fwd_bn": lambda: (check_conv_fwd_bn(128, 256, 3, 2, 16, 16, seed=67) + check_conv_fwd_bn(512, 512, 1, 4, 8, 8, seed=68, bias=True)
                             + check_conv_fwd_bn(64, 128, 3, 8, 32, 32, seed=69) + check_conv_fwd_bn(256, 16, 3, 1, 24, 40, seed=70)),
     "halo_dgrad_acc": lambda: (check_conv_dgrad_acc(16, 16, 3, 2, 64, 128, seed=51) + check_conv_dgrad_acc(32, 16, 3, 1, 32, 256, seed=52)
-                               + check_conv_dgrad_acc(64, 64, 3, 1, 32, 128, seed=53, expect_fused=False)
-                               + check_conv_dgrad_acc(16, 16, 3, 1, 32, 32, seed=54, expect_fused=False)),
+                               + check_conv_dgrad_acc(64, 64, 3, 1, 32, 128, seed=53)          # halo, TMA-store path
+                               + check_conv_dgrad_acc(16, 16, 3, 1, 32, 32, seed=54)           # implicit GEMM
+                               + check_conv_dgrad_acc(128, 256, 3, 3, 12, 20, seed=55)         # GEMM, partial tiles
+                               + check_conv_dgrad_acc(256, 128, 1, 2, 16, 16, seed=56)),
     "halo_wgrad_3x3": lambda: (check_conv_wgrad(16, 16, 3, 1, 2, 64, 128, seed=41) + check_conv_wgrad(32, 32, 3, 1, 1, 32, 256, seed=42)
                                + check_conv_wgrad(64, 64, 3, 1, 1, 32, 128, seed=43) + check_conv_wgrad(16, 32, 3, 1, 1, 32, 128, seed=44)
                                + check_conv_wgrad(64, 32, 3, 1, 1, 32, 128, seed=45)),

@@ -502,10 +502,16 @@ static int conv2d_dgrad_impl(ubr_view dy, const void* wpk, int in_ch, int ksize,
                                     (cudaStream_t)stream, accumulate);
       if (hrc <= 0) return hrc;
     }
-    if (accumulate) return 1;      // not fused for this shape: caller adds separately
     p.out_mode = 0;
     p.o_box_c = out_box_c(pick_nt(in_ch));
     if (int rc = make_act_map(&p.o_map, dx, p.o_box_c, t)) return rc;
+    if (accumulate) {
+      // dx += dgrad: the old dx is the residual of the fused epilogue (in place: every tile reads its own pixels
+      // before its TMA store, tiles are disjoint)
+      p.fused = 1; p.relu_pre = 0; p.relu_post = 0;
+      p.res = (const __nv_bfloat16*)dx.ptr; p.res_ld = dx.ld;
+      p.out_n = dx.n; p.out_h = dx.h; p.out_w = dx.w;
+    }
     return launch_conv_gemm(p, dy.n, dy.h, dy.w, t, dy.c, in_ch, wpk, ksize * ksize, taps, nt, (cudaStream_t)stream);
   }
   if (accumulate) return 1;

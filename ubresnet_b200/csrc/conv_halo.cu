@@ -507,7 +507,7 @@ int conv_halo_try(const ubr_view& x, const void* wpk, int nslabs, int n_pad, con
     break;
   }
   if (nt == 0) return 1;
-  if (accumulate && out_mode != 2) return 1;                 // in-epilogue accumulation: direct-store path only
+  if (accumulate && out_mode != 2 && out_mode != 0) return 1;  // in-epilogue accumulation: bf16 outputs only
   if (stats && out_mode != 2) return 1;                      // fused BN statistics: direct-store path only
 
   HaloParams p;
@@ -556,8 +556,15 @@ int conv_halo_try(const ubr_view& x, const void* wpk, int nslabs, int n_pad, con
     p.acc_stride = (uint32_t)nt;
   }
   p.bias = bias;
-  p.accumulate = accumulate;
+  p.accumulate = accumulate && out_mode == 2;
   p.stats = stats; p.stats_c = n_pad;
+  if (accumulate && out_mode == 0) {
+    // TMA-store path: the old value of the output is the "residual" of the fused epilogue (read by the thread that
+    // owns the pixel before the tile is stored -- in place is safe, tiles are disjoint)
+    UBR_REQUIRE(epi == nullptr && y != nullptr, "conv_halo: accumulate and a fused epilogue are exclusive");
+    p.fused = 1; p.relu_pre = 0; p.relu_post = 0;
+    p.res = (const __nv_bfloat16*)y->ptr; p.res_ld = y->ld;
+  }
   if (epi) {
     UBR_REQUIRE(p.out_mode == 0 || p.out_mode == 2, "conv_halo: the fused epilogue needs a bf16 output");
     p.fused = 1; p.relu_pre = epi->relu_pre; p.relu_post = epi->relu_post;
