@@ -347,6 +347,8 @@ def check_optim(seed=0):
             oa.step()
             ob.step()
         torch.cuda.synchronize()
+        # every step must bump the parameters' version counters (the engine's packed-weight cache is keyed on them)
+        res.append((name + "_versions_bumped", float(sum(1 for a in pa if a._version < 4)), 0.0))
         res.append((name + "_params", max(relerr(a, b) for a, b in zip(pa, pb)), 2e-6))
         sa, sb = oa.state_dict()["state"], ob.state_dict()["state"]
         worst = 0.0

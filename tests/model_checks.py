@@ -157,6 +157,33 @@ def train_parity(batch=2, size=128, num_classes=3, dense=False, seed=1234, arch=
     return res, detail
 
 
+def fused_optimizer_training(steps=3, size=128, seed=55):
+    """three training steps with training/optim.SGD against the same steps with torch.optim.SGD: identical kernels on
+    both sides, so the loss trajectories must agree to rounding -- in particular the engine must re-pack its bf16 weight
+    operands after every fused optimizer step (the kernel writes parameters through raw pointers)"""
+    from ubresnet_b200.training.optim import SGD
+    img, lab, wgt = (t.to(DEV) for t in synthetic.make_batch(2, size, size))
+    crit = PixelWiseNLLLoss()
+    traj = []
+    for which in ("torch", "fused"):
+        model, _ = build_pair(seed=seed)
+        model.train()
+        kw = dict(lr=1e-2, momentum=0.9, weight_decay=1e-3)
+        opt = torch.optim.SGD(model.parameters(), **kw) if which == "torch" else SGD(model.parameters(), **kw)
+        losses = []
+        for _ in range(steps):
+            opt.zero_grad(set_to_none=True)
+            loss = crit(model(img), lab, wgt)
+            loss.backward()
+            opt.step()
+            losses.append(loss.item())
+        traj.append(losses)
+    a, b = traj
+    res = [("fused_sgd_loss_step%d_vs_torch_sgd" % i, abs(a[i] - b[i]) / abs(a[i]), 1e-4) for i in range(steps)]
+    res.append(("loss_changes_between_steps (weights really update)", 0.0 if abs(b[-1] - b[0]) > 1e-6 * abs(b[0]) else 1.0, 0.0))
+    return res, {}
+
+
 def eval_parity(batch=2, size=128, num_classes=3, seed=77, arch="uresnet", inplanes=16):
     """eval() forward under no_grad: the BatchNorm-folded inference path (engine._block_fwd_folded) against the oracle,
     and against the unfolded kernel schedule of the same weights"""
@@ -235,6 +262,7 @@ CHECKS = {
     "train_256_c4": lambda: train_parity(1, 256, num_classes=4, seed=5),
     "train_odd_3x96x160": lambda: train_parity(3, (96, 160), dense=True, seed=31),      # partial tiles, odd batch
     "train_inplanes32_128": lambda: train_parity(2, 128, inplanes=32, seed=41),   # train_ubresnet2018_wlarcv2.py:88
+    "fused_optimizer_training": lambda: fused_optimizer_training(),
     "eval_128": lambda: eval_parity(2, 128),
     "eval_odd_3x96x160": lambda: eval_parity(3, (96, 160), seed=78),                # implicit-GEMM epilogues, partial tiles
     "eval_256_c4": lambda: eval_parity(1, 256, num_classes=4, seed=79),            # deploy/ubresnet_funcs.py:41-68 shape

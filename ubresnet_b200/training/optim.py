@@ -58,6 +58,13 @@ class _Tables:
         self.slots, self.chunks, self.nchunks, self.key = upload(slots), upload(carr), len(chunks), key
 
 
+def _mark_modified(tensors):
+    """The kernels write parameters and state through raw pointers: bump the tensors' version counters like an
+    in-place torch op would, so that everything keyed on `_version` (the engine's packed bf16 weight cache, autograd's
+    saved-tensor checks) sees the update."""
+    torch.autograd.graph.increment_version(list(tensors))
+
+
 class _FusedBase(torch.optim.Optimizer):
     def _collect(self, group, state_names):
         """[(param, grad, state tensors...)] of the parameters that have a gradient"""
@@ -114,6 +121,9 @@ class SGD(_FusedBase):
                 _lib.check(lib.ubr_sgd_step(tab.slots.data_ptr(), tab.chunks.data_ptr(), tab.nchunks, float(group["lr"]),
                                             mom, float(group["dampening"]), float(group["weight_decay"]),
                                             int(bool(group["nesterov"])), int(first and mom != 0), _stream()), "sgd_step")
+                _mark_modified([p for p, _, _, _ in sub])
+                if mom != 0:
+                    _mark_modified([st["momentum_buffer"] for _, _, _, st in sub])
         return loss
 
 
@@ -150,4 +160,6 @@ class Adam(_FusedBase):
                 _lib.check(lib.ubr_adam_step(tab.slots.data_ptr(), tab.chunks.data_ptr(), tab.nchunks, float(group["lr"]),
                                              float(b1), float(b2), float(group["eps"]), float(group["weight_decay"]),
                                              step, _stream()), "adam_step")
+                _mark_modified([p for p, _, _ in sub])
+                _mark_modified([t for _, _, st in sub for t in (st["exp_avg"], st["exp_avg_sq"])])
         return loss
