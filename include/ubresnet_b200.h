@@ -102,6 +102,9 @@ uint64_t ubr_wgrad_workspace_bytes(int grid_n, int grid_h, int grid_w, int m_ch,
  * The wgrad workspace is sized with ubr_wgrad_workspace_bytes(n, h, w, pad16(out_ch), in_ch, 9). */
 int ubr_conv2d_dilated_fwd(ubr_view x, const void* wpk, const float* bias, int out_ch, int dilation, ubr_view y,
                            void* stream);
+/* y = relu(conv(x) + bias): inference form of an ASPP atrous branch with its BatchNorm folded into (wpk, bias) */
+int ubr_conv2d_dilated_fwd_relu(ubr_view x, const void* wpk, const float* bias, int out_ch, int dilation, ubr_view y,
+                                void* stream);
 int ubr_conv2d_dilated_dgrad(ubr_view dy, const void* wpk, int in_ch, int dilation, ubr_view dx, void* stream);
 int ubr_conv2d_dilated_wgrad(ubr_view x, ubr_view dy, int out_ch, int dilation, float* dw, int accumulate,
                              void* workspace, uint64_t workspace_bytes, void* stream);

@@ -490,8 +490,11 @@ def check_dilated(cin, cout, dil, n, h, w, in_ld=None, seed=0):
     ws = torch.empty(ops.wgrad_workspace_bytes(n, h, w, cout, cin, 9) // 4 + 4, dtype=torch.float32, device=DEV)
     dw = torch.full((cout, cin, 3, 3), 9.0, dtype=torch.float32, device=DEV)
     ops.conv2d_dilated_wgrad(xa, act_from(dy), cout, dil, dw, False, ws)
+    yr = act_out(n, h, w, cout, 2 * cout, cout)
+    ops.conv2d_dilated_fwd(xa, ops.pack_weights(wt.to(DEV), False, True), b.to(DEV), cout, dil, y=yr, relu=True)
     torch.cuda.synchronize()
     return [(name + "_fwd", relerr(ya.nchw_float(), F.conv2d(x, wt, b, 1, dil, dil)), 1e-2),
+            (name + "_fwd_relu", relerr(yr.nchw_float(), F.relu(F.conv2d(x, wt, b, 1, dil, dil))), 1e-2),
             (name + "_fwd_slice_untouched", (ya.buf[..., :cout].float() - 3.0).abs().max().item(), 0.0),
             (name + "_dgrad", relerr(dxa.nchw_float(), torch.nn.grad.conv2d_input((n, cin, h, w), wt, dy, 1, dil, dil)), 1e-2),
             (name + "_wgrad", relerr(dw, torch.nn.grad.conv2d_weight(x, (cout, cin, 3, 3), dy, 1, dil, dil)), 2e-3)]

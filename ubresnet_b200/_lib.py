@@ -37,6 +37,7 @@ SIGNATURES = {
     "ubr_wgrad_workspace_bytes": (_u64, [_i, _i, _i, _i, _i, _i]),
     "ubr_deconv4s2_fwd": (_i, [View, _vp, _i, View, _vp]),
     "ubr_conv2d_dilated_fwd": (_i, [View, _vp, _vp, _i, _i, View, _vp]),
+    "ubr_conv2d_dilated_fwd_relu": (_i, [View, _vp, _vp, _i, _i, View, _vp]),
     "ubr_conv2d_dilated_dgrad": (_i, [View, _vp, _i, _i, View, _vp]),
     "ubr_conv2d_dilated_wgrad": (_i, [View, View, _i, _i, _vp, _i, _vp, _u64, _vp]),
     "ubr_maxpool3s1_fwd": (_i, [View, View, _vp, _vp]),

@@ -547,8 +547,21 @@ static int conv2d_dgrad_impl(ubr_view dy, const void* wpk, int in_ch, int ksize,
 
 // 3x3 stride-1 DILATED conv (padding == dilation): the ASPP branches of models/ASPP_ResNet.py:207-214.  Taps are the
 // dense 3x3 taps scaled by the dilation; the TMA zero-fill provides the (dilation-wide) padding.
+static int conv2d_dilated_fwd_impl(ubr_view x, const void* wpk, const float* bias, int out_ch, int dilation, ubr_view y,
+                                   int relu, void* stream);
+
 int ubr_conv2d_dilated_fwd(ubr_view x, const void* wpk, const float* bias, int out_ch, int dilation, ubr_view y,
                            void* stream) {
+  return conv2d_dilated_fwd_impl(x, wpk, bias, out_ch, dilation, y, 0, stream);
+}
+
+int ubr_conv2d_dilated_fwd_relu(ubr_view x, const void* wpk, const float* bias, int out_ch, int dilation, ubr_view y,
+                                void* stream) {
+  return conv2d_dilated_fwd_impl(x, wpk, bias, out_ch, dilation, y, 1, stream);
+}
+
+static int conv2d_dilated_fwd_impl(ubr_view x, const void* wpk, const float* bias, int out_ch, int dilation, ubr_view y,
+                                   int relu, void* stream) {
   if (int rc = ensure_device()) return rc;
   if (int rc = check_view(x, "conv2d_dilated_fwd.x")) return rc;
   if (int rc = check_view(y, "conv2d_dilated_fwd.y")) return rc;
@@ -569,6 +582,7 @@ int ubr_conv2d_dilated_fwd(ubr_view x, const void* wpk, const float* bias, int o
   p.out_mode = 0;
   p.o_box_c = out_box_c(pick_nt(out_ch));
   if (int rc = make_act_map(&p.o_map, y, p.o_box_c, t)) return rc;
+  if (relu) { p.fused = 1; p.relu_pre = 1; }               // inference form: BatchNorm folded into (wpk, bias)
   return launch_conv_gemm(p, x.n, x.h, x.w, t, x.c, out_ch, wpk, 9, taps, nt, (cudaStream_t)stream);
 }
 

@@ -15,6 +15,7 @@ slices of the (64 + Cin)-channel ASPP buffer, and `aspp` / `e` into slices of th
 """
 import torch
 
+from . import engine as _engine
 from . import ops
 from .engine import Engine, _UResNetFn, _channel_sum  # noqa: F401
 from .ops import Act
@@ -59,6 +60,20 @@ class ASPPEngine(Engine):
         rec = _AsppRec()
         cin = e.c
         acat = torch.empty((e.n, e.h, e.w, 64 + cin), dtype=torch.bfloat16, device=e.buf.device)
+        if _engine.FOLD_EVAL_BN and not training and not need_grad:
+            # inference: BatchNorm folded into every branch conv and into ASPP_conv, ReLU in the conv epilogues, branch
+            # outputs written straight into their channel slices of the concat buffer
+            for j, (pre, k, dil) in enumerate(_BRANCHES):
+                f = self._folded(getattr(layer, pre + "_conv"), getattr(layer, pre + "_bn"))
+                dst = Act(acat, 16 * j, 16)
+                if dil == 1:
+                    ops.conv2d_fwd_fused(e, f.w, f.b, 16, k, 1, True, y=dst)
+                else:
+                    ops.conv2d_dilated_fwd(e, f.w, f.b, 16, dil, y=dst, relu=True)
+            ops.maxpool3s1_fwd(e, y=Act(acat, 64, cin), want_idx=False)
+            fc = self._folded(post.ASPP_conv, post.ASPP_bn)
+            ops.conv2d_fwd_fused(Act(acat), fc.w, fc.b, cin, 1, 1, True, y=out)
+            return rec
         ys, sts = [], []
         for j, (pre, k, dil) in enumerate(_BRANCHES):
             conv = getattr(layer, pre + "_conv")

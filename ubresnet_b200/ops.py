@@ -182,13 +182,14 @@ def conv2d_wgrad(x, dy, out_ch, ksize, stride, dw, accumulate, ws):
     return dw
 
 
-def conv2d_dilated_fwd(x, wpk, bias, out_ch, dilation, y=None):
-    """3x3 stride-1 conv with padding == dilation (ASPP branches, reference models/ASPP_ResNet.py:203-214)."""
+def conv2d_dilated_fwd(x, wpk, bias, out_ch, dilation, y=None, relu=False):
+    """3x3 stride-1 conv with padding == dilation (ASPP branches, reference models/ASPP_ResNet.py:203-214).
+    relu=True: the inference form relu(conv + bias) for weights with the BatchNorm folded in."""
     lib = _lib.load()
     if y is None:
         y = Act.empty(x.n, x.h, x.w, out_ch, x.buf.device)
-    _lib.check(lib.ubr_conv2d_dilated_fwd(x.view(), wpk.data_ptr(), _ptr(bias), out_ch, dilation, y.view(), _stream()),
-               "conv2d_dilated_fwd")
+    fn = lib.ubr_conv2d_dilated_fwd_relu if relu else lib.ubr_conv2d_dilated_fwd
+    _lib.check(fn(x.view(), wpk.data_ptr(), _ptr(bias), out_ch, dilation, y.view(), _stream()), "conv2d_dilated_fwd")
     return y
 
 
