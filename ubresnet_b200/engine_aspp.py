@@ -100,7 +100,7 @@ class ASPPEngine(Engine):
         g = grads
         cin = rec.e.c
         dyc = ops.bn_act_bwd(d_aspp, rec.yc, rec.stc, True, bn_ws, g[post.ASPP_bn.weight], g[post.ASPP_bn.bias])
-        ops.conv2d_wgrad(rec.acat, dyc, cin, 1, 1, g[post.ASPP_conv.weight], False, wg_ws)
+        self._wgrad(lambda d=dyc: ops.conv2d_wgrad(rec.acat, d, cin, 1, 1, g[post.ASPP_conv.weight], False, wg_ws), dyc)
         g[post.ASPP_conv.bias].copy_(_channel_sum(dyc, cin))
         wc = self._pack(post.ASPP_conv, True)
         dacat = ops.conv2d_dgrad(dyc, wc.dgrad, 64 + cin, 1, 1)
@@ -113,10 +113,11 @@ class ASPPEngine(Engine):
             dyb = ops.bn_act_bwd(dacat.slice(16 * j, 16), rec.ys[j], rec.sts[j], True, bn_ws, g[bn.weight], g[bn.bias])
             wpk = self._pack(conv, True)
             if k == 1:
-                ops.conv2d_wgrad(rec.e, dyb, 16, 1, 1, g[conv.weight], False, wg_ws)
+                self._wgrad(lambda d=dyb, c=conv: ops.conv2d_wgrad(rec.e, d, 16, 1, 1, g[c.weight], False, wg_ws), dyb)
                 parts.append(ops.conv2d_dgrad(dyb, wpk.dgrad, cin, 1, 1))
             else:
-                ops.conv2d_dilated_wgrad(rec.e, dyb, 16, dil, g[conv.weight], False, wg_ws)
+                self._wgrad(lambda d=dyb, c=conv, dl=dil: ops.conv2d_dilated_wgrad(rec.e, d, 16, dl, g[c.weight], False,
+                                                                                 wg_ws), dyb)
                 parts.append(ops.conv2d_dilated_dgrad(dyb, wpk.dgrad, cin, dil))
             g[conv.bias].copy_(_channel_sum(dyb, 16))
             if len(parts) == 2:
@@ -182,11 +183,13 @@ class ASPPEngine(Engine):
             grads = {prm: sink.grad_buffer(prm) for prm in m.parameters()}
         else:
             grads = {prm: torch.empty_like(prm, dtype=torch.float32) for prm in m.parameters()}
-        self._w_on = False         # all weight gradients in stream order (the ASPP ones share the wgrad workspace)
+        self._wgrad_begin(dlogp.device)     # every weight gradient (ASPP layers included) goes to the side stream
 
         def done(name):
+            self._wgrad_stage()
             if sink is not None:
-                sink.stage_done(name)
+                side = [self._w_prev[0]] if (self._w_on and self._w_prev is not None) else []
+                sink.stage_done(name, side)
         recs = saved["recs"]
         dcur = self._head_bwd(saved, dlogp, grads, bn_ws, wg_ws)
         done("head")
@@ -216,6 +219,7 @@ class ASPPEngine(Engine):
             done("enc%d" % i)
         self._stem_bwd(saved, dcur, dskip[1], grads, bn_ws, stem_ws)
         done("stem")
+        self._wgrad_join()
         if sink is not None:
             sink.finish()
         return grads
