@@ -95,3 +95,16 @@ def test_wholeview_run_events_pipeline_matches_run_event():
     assert list(wholeview.run_events(model, [], crop=128)) == []
     one = [m.clone() for m in wholeview.run_events(model, events[:1], crop=128)]
     assert len(one) == 1 and torch.equal(one[0], refs[0])
+
+
+@pytest.mark.parametrize("arch", ["uresnet", "aspp"])
+def test_training_step_is_bit_deterministic(arch):
+    """tools/determinism_check.py: repeated steps under allocator perturbation give bit-identical losses and gradients
+    (fixed-order reductions; catches lifetime bugs of the weight-gradient side stream)"""
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, os.path.join(root, "tools", "determinism_check.py"), arch, "4"],
+                       capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout[-500:] + r.stderr[-500:]
