@@ -165,29 +165,34 @@ __global__ void __launch_bounds__(256) pack_weights_kernel(const float* __restri
                                                            int out_ch, int in_ch, int kh, int kw, int n_pad, int k_pad,
                                                            __nv_bfloat16* __restrict__ dst) {
   const int taps = kh * kw;
-  const long total = (long)(taps + 1) * n_pad * k_pad;
-  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
-    const int k = (int)(i % k_pad);
-    const int nn = (int)((i / k_pad) % n_pad);
-    const int t = (int)(i / ((long)k_pad * n_pad));
-    const float v = t < taps ? pack_value(src, src_layout, n_is_out, out_ch, in_ch, taps, t, nn, k) : 0.f;
+  // 32-bit index arithmetic (the host checks total < 2^31); the grid is wide enough that a thread of the largest
+  // conv (512x512x3x3) handles a few tens of elements -- the strided source reads are latency bound
+  const unsigned total = (unsigned)(taps + 1) * (unsigned)n_pad * (unsigned)k_pad;
+  const unsigned plane = (unsigned)k_pad * (unsigned)n_pad;
+  for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const unsigned t = i / plane, rem = i - t * plane;
+    const unsigned nn = rem / (unsigned)k_pad, k = rem - nn * (unsigned)k_pad;
+    const float v = (int)t < taps ? pack_value(src, src_layout, n_is_out, out_ch, in_ch, taps, (int)t, (int)nn, (int)k) : 0.f;
     dst[i] = __float2bfloat16_rn(v);
   }
 }
 
 // batched variant: one launch packs every job of a device-resident table (blockIdx.y = job)
+constexpr unsigned kPackBlocksPerJob = 384;
 __global__ void __launch_bounds__(256) pack_weights_batch_kernel(const long long* __restrict__ jobs) {
   const long long* j = jobs + (size_t)blockIdx.y * 10;
   const float* src = reinterpret_cast<const float*>(j[0]);
   __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(j[1]);
   const int src_layout = (int)j[2], n_is_out = (int)j[3], out_ch = (int)j[4], in_ch = (int)j[5];
   const int taps = (int)(j[6] * j[7]), n_pad = (int)j[8], k_pad = (int)j[9];
-  const long total = (long)(taps + 1) * n_pad * k_pad;
-  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
-    const int k = (int)(i % k_pad);
-    const int nn = (int)((i / k_pad) % n_pad);
-    const int t = (int)(i / ((long)k_pad * n_pad));
-    const float v = t < taps ? pack_value(src, src_layout, n_is_out, out_ch, in_ch, taps, t, nn, k) : 0.f;
+  // 32-bit index arithmetic (the host checks total < 2^31); the grid is wide enough that a thread of the largest
+  // conv (512x512x3x3) handles a few tens of elements -- the strided source reads are latency bound
+  const unsigned total = (unsigned)(taps + 1) * (unsigned)n_pad * (unsigned)k_pad;
+  const unsigned plane = (unsigned)k_pad * (unsigned)n_pad;
+  for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const unsigned t = i / plane, rem = i - t * plane;
+    const unsigned nn = rem / (unsigned)k_pad, k = rem - nn * (unsigned)k_pad;
+    const float v = (int)t < taps ? pack_value(src, src_layout, n_is_out, out_ch, in_ch, taps, (int)t, (int)nn, (int)k) : 0.f;
     dst[i] = __float2bfloat16_rn(v);
   }
 }
@@ -256,7 +261,8 @@ int ubr_pack_weights(const float* src, int src_layout, int n_is_out, int out_ch,
 int ubr_pack_weights_batch(const int64_t* jobs_device, int njobs, void* stream) {
   if (int rc = ensure_device()) return rc;
   UBR_REQUIRE(jobs_device != nullptr && njobs >= 1 && njobs <= 65535, "pack_weights_batch: bad job table");
-  pack_weights_batch_kernel<<<dim3(48, (unsigned)njobs), 256, 0, (cudaStream_t)stream>>>((const long long*)jobs_device);
+  pack_weights_batch_kernel<<<dim3(kPackBlocksPerJob, (unsigned)njobs), 256, 0, (cudaStream_t)stream>>>(
+      (const long long*)jobs_device);
   UBR_LAUNCH_CHECK("pack_weights_batch_kernel");
   return 0;
 }
