@@ -159,14 +159,17 @@ class Engine:
         """Re-derive the bf16 GEMM operands of every conv whose fp32 parameter changed (optimizer step,
         load_state_dict) with ONE kernel launch; the device job table is cached while pointers are stable."""
         m = self.model
-        convs = []
-        for mod in m.modules():
-            if mod is m.conv1:
-                continue
-            if isinstance(mod, torch.nn.ConvTranspose2d):
-                convs.append((mod, True))
-            elif isinstance(mod, torch.nn.Conv2d):
-                convs.append((mod, False))
+        convs = getattr(self, "_conv_list", None)
+        if convs is None:                       # the module tree is fixed after construction: walk it once
+            convs = []
+            for mod in m.modules():
+                if mod is m.conv1:
+                    continue
+                if isinstance(mod, torch.nn.ConvTranspose2d):
+                    convs.append((mod, True))
+                elif isinstance(mod, torch.nn.Conv2d):
+                    convs.append((mod, False))
+            self._conv_list = convs
         jobs = []
         for conv, transposed in convs:
             ent = self._packs.get(id(conv))
@@ -458,7 +461,6 @@ class Engine:
         dev = x.device
         p = m.inplanes
         bn_ws, _, _ = self._workspaces(n, h, w, dev)
-        self._refresh_packs(need_grad)
         saved = {}
         # concat buffers: cat[i] feeds dec_layer{i}; channels [0,Cd) deconv output, [Cd,2Cd) skip x_{i-1}
         cat = {}
@@ -468,6 +470,9 @@ class Engine:
             cat[i] = torch.empty((n, hh, ww, 2 * cd), dtype=torch.bfloat16, device=dev)
         # ---- stem (ub_uresnet.py:94-97)
         y0, st0, x0, h0, pool_idx = self._stem_fwd(x, Act(cat[1], p, p), training, need_grad, bn_ws)
+        # the stem reads the fp32 conv1 parameter directly: the (host-side) bookkeeping of the bf16 operand refresh
+        # runs while its kernels are already executing
+        self._refresh_packs(need_grad)
         # ---- encoder (:103-107)
         recs = {}
         cur = h0

@@ -136,13 +136,13 @@ class ASPPEngine(Engine):
             raise RuntimeError("ASPP_ResNet: the reference head (conv11 in_channels == inplanes, nkernels == 16, "
                                "models/ASPP_ResNet.py:376-386) is only consistent at inplanes=16")
         bn_ws, _, _ = self._workspaces(n, h, w, dev)
-        self._refresh_packs(need_grad)
         new = lambda hh, ww, c: torch.empty((n, hh, ww, c), dtype=torch.bfloat16, device=dev)
         # decoder concat buffers [deconv | skip]; skip of dec5 / dec4 is itself [aspp | e]
         cat = {1: new(h, w, 2 * p), 2: new(h // 2, w // 2, 4 * p), 3: new(h // 4, w // 4, 8 * p),
                4: new(h // 8, w // 8, 24 * p), 5: new(h // 16, w // 16, 48 * p)}
         e5skip = new(h // 32, w // 32, 64 * p)
         y0, st0, x0, h0, pool_idx = self._stem_fwd(x, Act(cat[1], p, p), training, need_grad, bn_ws)
+        self._refresh_packs(need_grad)          # after the stem launches (they do not use packed operands)
         # ---- encoder: e_i lands in the slice of the buffer that consumes it as a skip
         e_out = {1: Act(cat[2], 2 * p, 2 * p), 2: Act(cat[3], 4 * p, 4 * p), 3: Act(cat[4], 16 * p, 8 * p),
                  4: Act(cat[5], 32 * p, 16 * p), 5: Act(e5skip, 32 * p, 32 * p)}
