@@ -445,10 +445,10 @@ class Engine:
             raise RuntimeError("UResNet: H and W must be multiples of 32 (5 stride-2 stages), got %dx%d" % tuple(x.shape[2:]))
         if m.conv1.weight.device != x.device:
             raise RuntimeError("UResNet: parameters on %s but input on %s" % (m.conv1.weight.device, x.device))
-        need_grad = torch.is_grad_enabled() and m.training and any(p.requires_grad for p in m.parameters())
+        params = list(m.parameters())                    # ONE walk of the module tree per call (host time before
+        need_grad = torch.is_grad_enabled() and m.training and any(p.requires_grad for p in params)   # the first launch)
         with torch.cuda.device(x.device):
             if need_grad:
-                params = [p for p in m.parameters()]
                 return _UResNetFn.apply(self, x, *params)
             with torch.no_grad():
                 logp, _ = self._forward_impl(x.detach(), m.training, False)
@@ -614,6 +614,7 @@ class _UResNetFn(torch.autograd.Function):
         ctx.engine = engine
         ctx.saved = saved
         ctx.nparams = len(params)
+        ctx.param_list = params            # model.parameters() order, as passed by Engine.forward
         return logp
 
     @staticmethod
@@ -623,7 +624,7 @@ class _UResNetFn(torch.autograd.Function):
         ctx.saved = None
         with torch.cuda.device(dlogp.device):
             grads = engine.backward(saved, dlogp.contiguous())
-        out = [grads[p] if p.requires_grad else None for p in engine.model.parameters()]
+        out = [grads[p] if p.requires_grad else None for p in ctx.param_list]
         return (None, None) + tuple(out)
 
 
