@@ -611,31 +611,47 @@ __global__ void __launch_bounds__(256) maxpool_bwd_idx_kernel(const uint8_t* __r
     const int iw = (int)(p % w); p /= w;
     const int ih = (int)(p % h);
     const int b = (int)(p / h);
+    // the <= 4 covering windows: every index load is issued before any of them is inspected, then the dy loads of
+    // the windows that hit -- independent loads instead of a load -> test -> load chain per window
+    const int oh_lo = ih / 2, ow_lo = iw / 2;
+    long q[4];
+    uint2 u[4];
+    uint32_t hit[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const int oh = oh_lo + (k >> 1), ow = ow_lo + (k & 1);
+      const bool valid = oh <= (ih + 1) / 2 && ow <= (iw + 1) / 2 && oh < ho && ow < wo;
+      q[k] = valid ? ((long)b * ho + oh) * wo + ow : -1;
+      u[k] = valid ? *reinterpret_cast<const uint2*>(idx + (q[k] * cgs + cg) * 8) : make_uint2(0xffffffffu, 0xffffffffu);
+    }
     float acc[8];
     if (accumulate) load8(dx + (((long)b * h + ih) * w + iw) * dxld + cg * 8, acc);
     else {
 #pragma unroll
       for (int j = 0; j < 8; ++j) acc[j] = 0.f;
     }
-    const int oh_lo = ih / 2, oh_hi = (ih + 1) / 2;
-    const int ow_lo = iw / 2, ow_hi = (iw + 1) / 2;
-    for (int oh = oh_lo; oh <= oh_hi; ++oh) {
-      if (oh >= ho) continue;
-      for (int ow = ow_lo; ow <= ow_hi; ++ow) {
-        if (ow >= wo) continue;
-        const long q = ((long)b * ho + oh) * wo + ow;
-        const uint2 u = *reinterpret_cast<const uint2*>(idx + (q * cgs + cg) * 8);
-        const uint32_t me = (uint32_t)((ih - (2 * oh - 1)) * 3 + (iw - (2 * ow - 1)));
-        const uint32_t m4 = me * 0x01010101u;
-        const uint32_t e0 = u.x ^ m4, e1 = u.y ^ m4;       // a zero byte <=> this input is that channel's argmax
-        if (((e0 - 0x01010101u) & ~e0 & 0x80808080u) | ((e1 - 0x01010101u) & ~e1 & 0x80808080u)) {
-          float g[8];
-          load8(dy + q * dyld + cg * 8, g);
+    uint32_t e0[4], e1[4];
 #pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            if (((e0 >> (8 * j)) & 0xffu) == 0u) acc[j] += g[j];
-            if (((e1 >> (8 * j)) & 0xffu) == 0u) acc[4 + j] += g[4 + j];
-          }
+    for (int k = 0; k < 4; ++k) {
+      const int oh = oh_lo + (k >> 1), ow = ow_lo + (k & 1);
+      const uint32_t me = (uint32_t)((ih - (2 * oh - 1)) * 3 + (iw - (2 * ow - 1))) & 0xffu;
+      const uint32_t m4 = me * 0x01010101u;
+      e0[k] = u[k].x ^ m4; e1[k] = u[k].y ^ m4;            // a zero byte <=> this input is that channel's argmax
+      hit[k] = q[k] >= 0 ? (((e0[k] - 0x01010101u) & ~e0[k] & 0x80808080u) | ((e1[k] - 0x01010101u) & ~e1[k] & 0x80808080u)) : 0u;
+    }
+    uint4 graw[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+      graw[k] = hit[k] ? ldraw(dy + q[k] * dyld + cg * 8) : make_uint4(0u, 0u, 0u, 0u);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      if (hit[k]) {
+        float g[8];
+        unpack8(graw[k], g);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          if (((e0[k] >> (8 * j)) & 0xffu) == 0u) acc[j] += g[j];
+          if (((e1[k] >> (8 * j)) & 0xffu) == 0u) acc[4 + j] += g[4 + j];
         }
       }
     }
