@@ -82,11 +82,19 @@ class ClockSampler(threading.Thread):
 # ------------------------------------------------------------------------------------------------
 # CPU arm: the oracle port (reference algorithm) on the host cores
 # ------------------------------------------------------------------------------------------------
+def host_cores():
+    """cores this process may use (torchrun exports OMP_NUM_THREADS=1; the CPU arm runs alone on rank 0 and takes
+    every core of the box)"""
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
 def cpu_train_rate(batch, size, steps, warmup, threads=None):
     from oracle import uresnet_port as port
     from ubresnet_b200 import synthetic
-    if threads:
-        torch.set_num_threads(threads)
+    torch.set_num_threads(threads or host_cores())
     sd = port.init_state_dict(3, 1, 16, seed=1)
     params = port.clone_state_dict(sd, requires_grad=True)
     leaves = [v for v in params.values() if v.requires_grad]
@@ -153,20 +161,68 @@ def library_train_rate(batch, size, steps, warmup, mode, dev):
                     "batch %d" % (torch.__version__, batch)}
 
 
+def aspp_rates(batch, size, steps, host_batch, dev, lib):
+    """BASELINE.json configs[4]: ASPP_ResNet(3,1,16) train step (fwd + loss + bwd + fused SGD) and eval forward, bf16
+    storage, same batch shape as the headline workload."""
+    from ubresnet_b200.models import ASPP_ResNet
+    from ubresnet_b200.training.optim import SGD
+    from ubresnet_b200.training.pixelwise_nllloss import PixelWiseNLLLoss
+    torch.manual_seed(5)
+    model = ASPP_ResNet(3, 1, 16, showsizes=False).to(dev).train()
+    crit = PixelWiseNLLLoss()
+    opt = SGD(model.parameters(), lr=1e-4, momentum=0.9, weight_decay=1e-3)
+    img, lab, wgt = (t.to(dev) for t in host_batch)
+
+    def train():
+        opt.zero_grad(set_to_none=True)
+        crit(model(img), lab, wgt).backward()
+        opt.step()
+
+    def timed(fn, n, warm=3):
+        for _ in range(warm):
+            fn()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        n0 = lib.ubr_launch_count()
+        e0.record()
+        for _ in range(n):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / n, (lib.ubr_launch_count() - n0) // n
+
+    ms_t, l_t = timed(train, steps)
+    model.eval()
+    with torch.no_grad():
+        ms_i, l_i = timed(lambda: model(img), steps)
+    gf_train, gf_fwd = 310.5, 103.65           # algorithmic conv GFLOP per 512x512 crop (SURVEY.md 8d)
+    return {"model": "ASPP_ResNet(3,1,16)", "per_gpu_batch": batch, "crop": size,
+            "train": {"value": batch / (ms_t * 1e-3), "unit": UNIT, "ms_per_step": ms_t, "gpu_launches": int(l_t),
+                      "conv_tflops": gf_train * batch / ms_t},
+            "infer": {"value": batch / (ms_i * 1e-3), "unit": UNIT, "ms_per_step": ms_i, "gpu_launches": int(l_i),
+                      "conv_tflops": gf_fwd * batch / ms_i}}
+
+
 def run_reference(args, rank):
     if rank != 0:
         return
     batch = args.cpu_batch
-    rate, ms, threads = cpu_train_rate(batch, args.size, max(1, args.steps), max(0, min(args.warmup, 1)))
+    nsteps = max(5, args.steps)                      # bounded sample: >= 5 timed steps of `batch` crops
+    rate, ms, threads = cpu_train_rate(batch, args.size, nsteps, max(1, min(args.warmup, 2)))
     line = {
         "impl": "reference", "metric": METRIC, "value": rate, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
         "config": {"workload": "ub_uresnet(inplanes=16,1ch,3cls) train step fwd+weighted-NLL+bwd+SGD, 512x512 crops",
-                   "per_gpu_batch": args.batch, "l2": "working set >> 126 MB L2 (no flush needed)"},
+                   "per_gpu_batch": batch, "crop": args.size,
+                   "note": "bounded sample of the %d-crop batch of the CUDA arm: %d crops per CPU step (BASELINE.json "
+                           "configs[0], the reference's own CPU-runnable case); rank 0 only, all host cores" %
+                           (args.batch, batch),
+                   "l2": "working set >> L2 (no flush needed)"},
         "cpu_baseline": {"value": rate, "unit": UNIT, "cores": threads, "kind": "port",
                          "sample": "oracle/uresnet_port.py (CPU fp32 restatement of the reference), batch %d of %dx%d "
-                                   "crops per step, %d timed steps" % (batch, args.size, args.size, max(1, args.steps))},
+                                   "crops per step, %d timed steps, %d threads" %
+                                   (batch, args.size, args.size, nsteps, threads)},
         "e2e": {"value": rate, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -398,6 +454,20 @@ def run_own(args, rank, world, local_rank):
         kernels = {k: {"calls_per_step": c / nprof, "ms_per_step": t / nprof} for k, (c, t) in
                    sorted(summ.items(), key=lambda kv: -kv[1][1])}
 
+    # ---- multi-GPU correctness riding along with the speed number: after all steps every rank must hold bit-identical
+    # parameters (same seed, same all-reduced gradients) -- the spread of a float64 checksum over ranks must be 0
+    dp_check = None
+    if world > 1:
+        with torch.no_grad():
+            chk = torch.stack([torch.stack([p.double().sum(), p.double().abs().sum()]) for p in model.parameters()]).sum(0)
+        allc = [torch.zeros_like(chk) for _ in range(world)]
+        dist.all_gather(allc, chk)
+        allc = torch.stack(allc)
+        dp_check = {"param_checksum_spread": float((allc.max(0).values - allc.min(0).values).abs().max().item()),
+                    "param_abs_sum": float(allc[0, 1].item()), "ranks": world,
+                    "what": "max over {sum, abs-sum} of (max - min over ranks) of the float64 parameter checksums after "
+                            "every timed step; must be 0"}
+
     # ---- inference (eval-mode forward; BASELINE metric is "train+infer") and whole-view deploy (configs[3])
     infer = None
     wholeview = None
@@ -457,22 +527,34 @@ def run_own(args, rank, world, local_rank):
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
-        rate, cms, threads = cpu_train_rate(args.cpu_batch, S, 2, 1)
+        rate, cms, threads = cpu_train_rate(args.cpu_batch, S, 6, 1)
         cpu = {"value": rate, "unit": UNIT, "cores": threads, "kind": "port",
-               "sample": "oracle/uresnet_port.py train step, batch %d of %dx%d crops, best-effort mean of 2 steps after 1 "
+               "sample": "oracle/uresnet_port.py train step, batch %d of %dx%d crops, mean of 6 steps after 1 "
                          "warm-up (%.0f ms/step)" % (args.cpu_batch, S, S, cms)}
 
     library = None
-    if rank == 0 and world == 1 and args.library_baseline:
+    if rank == 0 and world == 1 and not args.no_library:
         resident.clear()
         torch.cuda.empty_cache()
         library = []
-        for mode in ("bf16", "tf32", "fp32"):
+        # default: the bf16-autocast + channels_last leg (the fastest library configuration, "the bar" of SURVEY 2b);
+        # --library-baseline adds tf32 and fp32
+        for mode in (("bf16", "tf32", "fp32") if args.library_baseline else ("bf16",)):
             try:
                 library.append(library_train_rate(B, S, 5, 3, mode, dev))
             except Exception as exc:                               # e.g. out of memory in fp32
                 library.append({"mode": mode, "error": str(exc)[:200]})
             torch.cuda.empty_cache()
+
+    aspp = None
+    if rank == 0 and world == 1 and not args.no_aspp and S == 512:
+        try:
+            resident.clear()
+            del model, net, opt
+            torch.cuda.empty_cache()
+            aspp = aspp_rates(B, S, max(3, args.steps // 2), host[0], dev, lib)
+        except Exception as exc:
+            aspp = {"error": str(exc)[:300]}
 
     if rank == 0:
         line = {
@@ -496,6 +578,10 @@ def run_own(args, rank, world, local_rank):
             line["cpu_baseline"] = cpu
         if library:
             line["library_baseline"] = library
+        if dp_check:
+            line["dp_check"] = dp_check
+        if aspp:
+            line["aspp"] = aspp
         if infer:
             line["infer"] = infer
         if wholeview:
@@ -522,6 +608,8 @@ def main():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--library-baseline", action="store_true",
                     help="also time the oracle port through PyTorch/cuDNN on the same GPU (bf16 autocast, tf32, fp32)")
+    ap.add_argument("--no-library", action="store_true", help="skip the PyTorch/cuDNN bf16 comparison leg (N=1)")
+    ap.add_argument("--no-aspp", action="store_true", help="skip the ASPP_ResNet (configs[4]) extra measurement (N=1)")
     ap.add_argument("--no-infer", action="store_true", help="skip the eval-forward and whole-view measurements")
     ap.add_argument("--verbose", action="store_true")
     ap.add_argument("--kernel-log", default="")

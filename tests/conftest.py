@@ -31,3 +31,18 @@ def pytest_collection_modifyitems(config, items):
     for item in items:
         if "gpu" in item.keywords:
             item.add_marker(skip)
+
+
+def pytest_terminal_summary(terminalreporter):
+    """print every measured parity error of the run (GPUTEST records carry the numbers, not only a pass count)"""
+    try:
+        from tests import model_checks
+    except Exception:
+        return
+    if not model_checks.MEASURED:
+        return
+    tr = terminalreporter
+    tr.write_line("")
+    tr.write_line("measured parity errors (check:label err / bound):")
+    for name, label, err, tol in model_checks.MEASURED:
+        tr.write_line("  %-4s %s:%s  %.3e / %.1e" % ("ok" if err <= tol else "FAIL", name, label, err, tol))

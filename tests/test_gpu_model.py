@@ -9,7 +9,7 @@ pytestmark = pytest.mark.gpu
 
 @pytest.mark.parametrize("name", list(model_checks.CHECKS))
 def test_model(name):
-    results, _ = model_checks.CHECKS[name]()
+    results, _ = model_checks.run_check(name)
     bad = [(lbl, err, tol) for lbl, err, tol in results if not err <= tol]
     assert not bad, "parity failures: %s" % bad
 
@@ -54,6 +54,25 @@ def test_wholeview_deploy_bitexact_tiling():
     tiles = torch.randn(len(plan), 3, 128, 128)
     st = wholeview.stitch(tiles.cuda(), plan, 256, 448)
     assert (st.cpu().numpy() == port.stitch_scatter_np(tiles.numpy(), plan, 256, 448)).all()
+
+
+def test_wholeview_1008x3456_crop512_bitexact():
+    """BASELINE.json configs[3] geometry: 3 planes 1008x3456 -> 42 crops of 512^2 (SURVEY 8c tile plan), gather and
+    stitch bit-exact against the numpy restatement"""
+    from oracle import uresnet_port as port
+    from ubresnet_b200 import synthetic
+    from ubresnet_b200.deploy import wholeview
+    ev = synthetic.make_wholeview(rows=1008, cols=3456, planes=3)
+    plan = wholeview.tile_plan(1008, 3456, 512)
+    assert plan == port.tile_plan(1008, 3456, 512) and len(plan) == 14
+    assert [r for r, _ in plan[::7]] == [0, 496] and [c for _, c in plan[:7]] == [0, 491, 981, 1472, 1963, 2453, 2944]
+    g = torch.Generator().manual_seed(5)
+    for p in range(3):
+        crops = wholeview.gather(ev[p].cuda(), plan, 512)
+        assert (crops[:, 0].cpu().numpy() == port.tile_gather_np(ev[p].numpy(), plan, 512)).all()
+        tiles = torch.randn(len(plan), 3, 512, 512, generator=g)
+        st = wholeview.stitch(tiles.cuda(), plan, 1008, 3456)
+        assert (st.cpu().numpy() == port.stitch_scatter_np(tiles.numpy(), plan, 1008, 3456)).all()
 
 
 def test_wholeview_run_event_matches_per_crop_pipeline():

@@ -216,3 +216,28 @@ def test_accuracy_port_matches_reference(script, nonzero):
     tgt2 = tgt.clamp(max=1)
     a2 = ref_acc(out, tgt2.clone(), None) if nonzero else ref_acc(out, tgt2.clone())
     assert float(a2[2]) == port.accuracy(out, tgt2, nonzero=nonzero)[2] == 0.0
+
+
+def test_port_matches_trained_fixture():
+    """the oracle port on the reference-TRAINED weights reproduces the outputs the reference itself produced on them
+    (tests/golden/uresnet_trained.pt, oracle/make_golden.py::trained_fixture): eval + train log-probs, raw conv11
+    logits, losses and gradients"""
+    fx = torch.load(os.path.join(GOLD, "uresnet_trained.pt"), weights_only=False)
+    sd = OrderedDict((k, (v.float() if v.is_floating_point() else v.clone()))
+                     for k, v in fx["checkpoint"]["state_dict"].items())
+    assert set(fx["checkpoint"]) == {"iter", "epoch", "state_dict", "best_prec1", "optimizer"}
+    img, lab, wgt = fx["image"], fx["label"], fx["weight"]
+    with torch.no_grad():
+        logp, logits = port.forward(port.clone_state_dict(sd), img, training=False, return_logits=True)
+    assert _rel(logp, fx["logp_eval"]) < 1e-5 and _rel(logits, fx["logits_eval"]) < 1e-5
+    assert abs(port.pixelwise_nll(logp, lab, wgt).item() - fx["loss_eval"]) / fx["loss_eval"] < 1e-5
+    nz = img[:, 0] != 0
+    acc = (logp.argmax(1)[nz] == lab[nz]).float().mean().item()
+    assert acc > 0.95, "fixture is not trained-like: accuracy on non-zero pixels %.3f" % acc
+    loss, logp_t, grads, _ = port.train_step_grads(sd, img, lab, wgt)
+    assert _rel(logp_t, fx["logp_train"]) < 1e-5
+    assert abs(loss.item() - fx["loss_train"]) / fx["loss_train"] < 1e-5
+    for k, g in fx["grads"].items():
+        if k in ("conv1.bias", "conv10.bias"):
+            continue
+        assert _rel(grads[k], g) < 5e-4, k

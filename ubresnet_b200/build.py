@@ -19,12 +19,28 @@ def _nvcc():
     return "nvcc"
 
 
+HASHPATH = os.path.join(LIBDIR, "source.sha256")
+
+
+def source_hash():
+    """sha256 over every file of csrc/, the public header and the compiler flags: the library is rebuilt when (and only
+    when) this changes -- file times do not survive a checkout or the copy to the GPU box"""
+    import hashlib
+    h = hashlib.sha256()
+    deps = sorted(os.path.join(CSRC, f) for f in os.listdir(CSRC)) + [os.path.join(HERE, "..", "include", "ubresnet_b200.h")]
+    for d in deps:
+        h.update(os.path.basename(d).encode())
+        with open(d, "rb") as fh:
+            h.update(fh.read())
+    h.update(" ".join(NVCC_FLAGS + SOURCES).encode())
+    return h.hexdigest()
+
+
 def _stale():
-    if not os.path.isfile(LIBPATH):
+    if not os.path.isfile(LIBPATH) or not os.path.isfile(HASHPATH):
         return True
-    t = os.path.getmtime(LIBPATH)
-    deps = [os.path.join(CSRC, f) for f in os.listdir(CSRC)] + [os.path.join(HERE, "..", "include", "ubresnet_b200.h")]
-    return any(os.path.getmtime(d) > t for d in deps)
+    with open(HASHPATH) as fh:
+        return fh.read().strip() != source_hash()
 
 
 def build(force=False, verbose=False):
@@ -52,6 +68,8 @@ def build(force=False, verbose=False):
         raise RuntimeError("link failed:\n%s" % r.stdout)
     with open(os.path.join(LIBDIR, "build.log"), "w") as fh:
         fh.write("\n".join(logs))
+    with open(HASHPATH, "w") as fh:
+        fh.write(source_hash() + "\n")
     if verbose:
         print("\n".join(logs))
     return LIBPATH

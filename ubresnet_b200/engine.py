@@ -145,6 +145,8 @@ class Engine:
         self._w_on = False
         self.grad_sink = None      # optional data-parallel gradient sink (ubresnet_b200.parallel.GradBuckets)
         self._wstream = None       # side stream of the weight-gradient kernels (backward only)
+        self.keep_logits = False   # parity aid: keep the raw conv11 output of the last forward (what a forward hook on
+        self.last_logits = None    # the reference's conv11 sees, ub_uresnet.py:141) as (N,C,H,W) fp32
 
     # ------------------------------------------------------------------ helpers
     def _pack(self, conv, need_dgrad, transposed=False):
@@ -325,6 +327,8 @@ class Engine:
         logits = torch.empty((n * h * w, ld), dtype=torch.float32, device=cur.buf.device)
         ops.conv2d_fwd(a10, w11.fwd, m.conv11.bias, ncls, 7, 1, y_f32=logits)
         logp = ops.logsoftmax_fwd(logits, n, ncls, h, w)
+        if self.keep_logits:
+            self.last_logits = logits.view(n, h, w, ld)[..., :ncls].permute(0, 3, 1, 2).contiguous()
         if training:
             with torch.no_grad():
                 bns = [mod.num_batches_tracked for mod in m.modules()
