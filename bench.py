@@ -497,32 +497,50 @@ def run_own(args, rank, world, local_rank):
                  "conv_tflops": GF_FWD * B * args.steps / (ms_i * 1e-3) / 1e3}
         if S == 512:
             from ubresnet_b200.deploy import wholeview as wv
-            planes = synthetic.make_wholeview(seed=synthetic.BASE_SEED + rank, rows=1008, cols=3456, planes=3).pin_memory()
+            # every rank holds the SAME event for the crop-sharded measurement, its own events for the event-sharded one
+            planes = synthetic.make_wholeview(seed=synthetic.BASE_SEED, rows=1008, cols=3456, planes=3).pin_memory()
             nev = max(2, args.steps // 2)
+            h_out = torch.empty((3, 1008, 3456), dtype=torch.uint8).pin_memory()
 
             def event(i):
-                out = wv.run_event(model, planes, crop=512)
-                return out.argmax(1).to(torch.uint8).cpu()           # stitched class maps (3, 1008, 3456) to the host
+                # ONE event through the public deploy call: host planes in, stitched uint8 class maps back on the host.
+                # N > 1: the event's 42 crops are sharded over the ranks, class tiles all-gathered (C2)
+                out = wv.run_event_sharded(model, planes, crop=512) if world > 1 else wv.run_event_classes(model, planes, crop=512)
+                h_out.copy_(out)
+                return h_out
 
             ms_w, l_w = timed(event, nev, 1)
-            # the deploy loop: same work per event, copies of neighbouring events overlapped with the forward pass
-            npipe = 4 * nev
-            for _ in wv.run_events(model, [planes] * 2, crop=512):
+            sharded_ok = None
+            if world > 1:
+                single = wv.run_event_classes(model, planes, crop=512)
+                same = torch.tensor([int(torch.equal(single, wv.run_event_sharded(model, planes, crop=512)))], device=dev)
+                dist.all_reduce(same, op=dist.ReduceOp.MIN)
+                sharded_ok = bool(same.item())
+            # the deploy loop over many events: events sharded round-robin over the ranks (no collective), copies of
+            # neighbouring events overlapped with the forward pass; host wall clock, max over ranks
+            npipe = 4 * nev * world
+            for _ in wv.run_events(model, [planes] * (2 * world), crop=512, rank=rank, world=world):
                 pass
-            torch.cuda.synchronize()
+            barrier()
             t0 = time.perf_counter()
-            nout = sum(1 for _ in wv.run_events(model, [planes] * npipe, crop=512))
+            nout = sum(1 for _ in wv.run_events(model, [planes] * npipe, crop=512, rank=rank, world=world))
             torch.cuda.synchronize()
-            ms_pipe = (time.perf_counter() - t0) * 1e3 / max(1, nout)
-            wholeview = {"metric": "wholeview_events_per_sec", "value": world * nev / (ms_w * 1e-3), "unit": "events/s",
-                         "crops_per_sec": world * nev * 42 / (ms_w * 1e-3), "ms_per_event": ms_w / nev,
-                         "workload": "3 planes 1008x3456 -> 42 overlapping 512x512 crops -> eval forward -> stitch; "
-                                     "events sharded round-robin over ranks (no collective); host planes in, host "
-                                     "class maps out", "gpu_launches_per_event": int(l_w / nev),
-                         "pipelined": {"value": world * 1e3 / ms_pipe, "unit": "events/s", "ms_per_event": ms_pipe,
-                                       "events": nout, "note": "deploy.wholeview.run_events: upload of event i+1 and "
-                                       "download of event i-1 on a copy stream during event i; host wall clock over "
-                                       "the whole loop"}}
+            dt = torch.tensor([time.perf_counter() - t0], device=dev, dtype=torch.float64)
+            if world > 1:
+                dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+            ms_pipe = float(dt.item()) * 1e3 / npipe
+            wholeview = {"metric": "wholeview_events_per_sec", "value": 1e3 / ms_pipe, "unit": "events/s",
+                         "crops_per_sec": 42e3 / ms_pipe, "ms_per_event": ms_pipe, "events": npipe,
+                         "workload": "3 planes 1008x3456 -> 42 overlapping 512x512 crops -> eval forward -> per-crop "
+                                     "argmax -> stitched uint8 class maps; host planes in, host class maps out; "
+                                     "deploy.wholeview.run_events(rank, world): events sharded round-robin over the "
+                                     "ranks (no collective), upload of event i+1 / download of event i-1 on a copy "
+                                     "stream during event i; host wall clock over the loop, max over ranks",
+                         "single_event": {"ms_per_event": ms_w / nev, "gpu_launches_per_event": int(l_w / nev),
+                                          "sharding": ("crops of one event over %d ranks, uint8 class tiles all-gathered "
+                                                       "over NCCL (deploy.wholeview.run_event_sharded)" % world)
+                                          if world > 1 else "one GPU (deploy.wholeview.run_event_classes)",
+                                          "sharded_equals_single_gpu": sharded_ok}}
         model.train()
 
     cpu = None

@@ -220,6 +220,13 @@ int ubr_tile_gather(const float* plane, int rows, int cols, const int32_t* origi
                     float* crops, void* stream);
 int ubr_stitch_scatter(const float* tiles /* [ntiles,c,crop,crop] */, int nch, const int32_t* origins, int ntiles,
                        int crop, int rows, int cols, float* out /* [c,rows,cols] */, void* stream);
+/* class maps for the deploy loop (what deploy/run_ubresnet_wholeview.py:264-272 keeps of the network output):
+ * classes[n,hw] = argmax_k logp[n,k,hw] (first maximum), and the stitch of uint8 class TILES [ntiles,crop,crop] with
+ * the same highest-tile-wins rule as ubr_stitch_scatter (pixels no tile covers get `fill`).  Crop-sharded multi-GPU
+ * deploy exchanges these 1-byte tiles instead of C fp32 maps. */
+int ubr_argmax_classes(const float* logp, int n, int ncls, int hw, uint8_t* classes, void* stream);
+int ubr_stitch_scatter_u8(const uint8_t* tiles, const int32_t* origins, int ntiles, int crop, int rows, int cols, int fill,
+                          uint8_t* out, void* stream);
 
 /* ---- accuracy counters: replaces the 2*C `.item()` reductions of `accuracy()` (reference
  * training/train_ubresnet2018_wlarcv2.py:509-566).  pred = argmax over classes of logp (NCHW fp32, first maximum);
@@ -253,6 +260,47 @@ int ubr_sgd_step(const ubr_opt_slot* slots, const ubr_opt_chunk* chunks, int nch
 /* Adam hyper-parameters are doubles: torch derives 1-beta and lr/(1-beta1^t) in double before rounding to fp32 */
 int ubr_adam_step(const ubr_opt_slot* slots, const ubr_opt_chunk* chunks, int nchunks, double lr, double beta1,
                   double beta2, double eps, double weight_decay, int step, void* stream);
+
+/* ---- fp32 precision mode (BASELINE.json north_star "1e-4 (tf32/fp32 mode)"; SURVEY 8b "Precision modes") ----------
+ * The reference computes in fp32 end to end (models/ub_uresnet.py:41-70, models/common_layers.py:13-58).  These entry
+ * points keep fp32 NHWC activations (`ubr_view` with fp32 elements, ld in elements), read the fp32 parameters in the
+ * reference layouts directly (OIHW / ConvTranspose IOHW, no packing) and accumulate in fp32 FMA (reductions over pixels
+ * in float64).  Parity mode, selected with UBR_PRECISION=fp32 / UResNet(..., precision="fp32"): CUDA cores, not tensor
+ * cores -- tf32's 11 significant bits cannot hold 1e-4 through 58 convolutions.
+ *   fwd   : y[n,oh,ow,o]  = bias[o] + sum x[n, oh*stride + r*dil - pad, ow*stride + s*dil - pad, i] * W[o,i,r,s]
+ *   dgrad : dx            = transposed convolution of dy with the same W (accumulate: dx += ...)
+ *   wgrad : dW[o,i,r,s] (+)= sum_pixels dy[.,o] * x[shifted,i];  workspace >= 8 * numel(dW) bytes (float64 accumulators)
+ *   deconv: nn.ConvTranspose2d(k, stride, pad), W is IOHW [in_ch][out_ch][k][k] (common_layers.py:125) */
+int ubr_f32_conv2d_fwd(ubr_view x, const float* w, const float* bias, int out_ch, int ksize, int stride, int pad,
+                       int dilation, ubr_view y, void* stream);
+int ubr_f32_conv2d_dgrad(ubr_view dy, const float* w, int in_ch, int ksize, int stride, int pad, int dilation, ubr_view dx,
+                         int accumulate, void* stream);
+int ubr_f32_conv2d_wgrad(ubr_view x, ubr_view dy, int ksize, int stride, int pad, int dilation, float* dw, int accumulate,
+                         void* workspace, uint64_t workspace_bytes, void* stream);
+int ubr_f32_deconv_fwd(ubr_view x, const float* w, int out_ch, int ksize, int stride, int pad, ubr_view y, void* stream);
+int ubr_f32_deconv_dgrad(ubr_view dy, const float* w, int in_ch, int ksize, int stride, int pad, ubr_view dx, void* stream);
+int ubr_f32_deconv_wgrad(ubr_view x, ubr_view dy, int ksize, int stride, int pad, float* dw, int accumulate, void* workspace,
+                         uint64_t workspace_bytes, void* stream);
+/* BatchNorm2d training statistics: sums[0:c) = sum y, sums[c:2c) = sum y^2 (float64, zeroed by the call) */
+int ubr_f32_bn_stats(ubr_view y, double* sums, void* stream);
+int ubr_f32_bn_finalize(const double* sums, int c, double count, const float* gamma, const float* beta, float* running_mean,
+                        float* running_var, float momentum, float eps, float* scale, float* shift, float* mean,
+                        float* invstd, void* stream);
+/* out[c] (+)= sum over pixels of a[.,c] (conv bias gradients); workspace: 2*c doubles */
+int ubr_f32_channel_sum(ubr_view a, double* workspace, float* out, int accumulate, void* stream);
+int ubr_f32_bn_act(ubr_view y, const float* scale, const float* shift, int relu, ubr_view out, void* stream);
+int ubr_f32_block_tail(ubr_view y2, const float* s2, const float* b2, ubr_view res, const float* sr, const float* br,
+                       ubr_view out, void* stream);
+/* du = dout * (out > 0): the block's final ReLU (common_layers.py:56) */
+int ubr_f32_relu_mask(ubr_view dout, ubr_view out, ubr_view du, void* stream);
+/* backward of out = relu?(bn(y)) in training mode: dy, dgamma = sum dz*xhat, dbeta = sum dz; workspace: 2*c doubles */
+int ubr_f32_bn_act_bwd(ubr_view dout, ubr_view y, const float* scale, const float* shift, const float* mean,
+                       const float* invstd, int relu, double* workspace, double count, ubr_view dy, float* dgamma,
+                       float* dbeta, int accumulate, void* stream);
+int ubr_f32_maxpool3s2_fwd(ubr_view x, ubr_view y, uint8_t* idx /* may be NULL */, void* stream);
+int ubr_f32_maxpool3s2_bwd(const uint8_t* idx, ubr_view dy, ubr_view dx, int accumulate, void* stream);
+int ubr_f32_add(ubr_view a, ubr_view b, ubr_view c, ubr_view out, void* stream);
+int ubr_f32_logsoftmax_bwd(const float* logp, const float* dlogp, int n, int ncls, int hw, ubr_view dlogits, void* stream);
 
 /* ---- flat-buffer helpers for the data-parallel gradient buckets --------------------------------- */
 int ubr_scale_f32(float* buf, uint64_t count, float alpha, void* stream);

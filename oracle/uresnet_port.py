@@ -254,7 +254,7 @@ def tile_starts(extent, crop, ntiles=None):
     if ntiles is None:
         ntiles = -(-extent // crop)          # ceil
         # require some overlap for context at seams (matches SURVEY plan: 1008 -> 2 rows, 3456 -> 7 cols)
-        while ntiles * crop - extent < (ntiles - 1) * 16:
+        while ntiles * crop - extent < (ntiles - 1) * min(16, crop // 4):
             ntiles += 1
     span = extent - crop
     return [int(math.floor(i * span / (ntiles - 1) + 0.5)) for i in range(ntiles)]

@@ -70,3 +70,67 @@ def test_grad_buckets_allreduce_mean_world2():
 def test_grad_buckets_allreduce_mean_world2_aspp():
     """ASPP_ResNet: the ASPP skip layers' parameters ride in enc5's bucket (their backward runs before enc5's)"""
     _run("aspp")
+
+
+def _wv_worker(rank, world, port, ret):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        import numpy as np
+        from oracle import uresnet_port as port_
+        from ubresnet_b200.deploy import wholeview as wv
+        crop, rows, cols, nplanes = 32, 80, 144, 3
+        plan = wv.tile_plan(rows, cols, crop)
+        ncrops = nplanes * len(plan)
+        first, count, per = wv.crop_shard(ncrops, rank, world)
+        # stand-in for "forward + argmax" of crop g: a tile whose bytes encode (g, pixel)
+        def tile(g):
+            return ((torch.arange(crop * crop).view(crop, crop) * 7 + g * 13) % 251).to(torch.uint8)
+        local = torch.zeros((per, crop, crop), dtype=torch.uint8)
+        for i in range(count):
+            local[i] = tile(first + i)
+        tiles = wv.gather_class_tiles(local, ncrops)
+        assert tiles.shape == (ncrops, crop, crop)
+        for g in range(ncrops):
+            assert torch.equal(tiles[g], tile(g)), g
+        # the gathered tiles stitch to what the single-process numpy oracle gives
+        per_plane = len(plan)
+        for p in range(nplanes):
+            ref = port_.stitch_scatter_np(tiles[p * per_plane:(p + 1) * per_plane].numpy()[:, None], plan, rows, cols)[0]
+            seq = np.zeros((rows, cols), dtype=np.uint8)
+            for i, (r0, c0) in enumerate(plan):
+                seq[r0:r0 + crop, c0:c0 + crop] = tile(p * per_plane + i).numpy()
+            assert (ref == seq).all()
+        ret[rank] = (first, count, per)
+    finally:
+        dist.destroy_process_group()
+
+
+def test_wholeview_crop_sharding_world2():
+    """crop-sharded whole-view deploy: block partition of the event's crops, padded all-gather of the
+    1-byte class tiles in global crop order (gloo here, NCCL on the GPUs)"""
+    from ubresnet_b200.deploy import wholeview as wv
+    for ncrops in (42, 7, 1, 48):
+        for world in (1, 2, 4, 8):
+            blocks = [wv.crop_shard(ncrops, r, world) for r in range(world)]
+            covered = [i for f, c, _ in blocks for i in range(f, f + c)]
+            assert covered == list(range(ncrops)), (ncrops, world)
+            assert len({per for _, _, per in blocks}) == 1 and blocks[0][2] * world >= ncrops
+    world = 2
+    port = _free_port()
+    mgr = mp.Manager()
+    ret = mgr.dict()
+    mp.spawn(_wv_worker, args=(world, port, ret), nprocs=world, join=True)
+    assert sorted(dict(ret).keys()) == [0, 1]
+
+
+def test_run_events_round_robin_sharding():
+    """event sharding: rank r of `world` sees events r, r+world, ... (no collective)"""
+    evs = list(range(11))
+    seen = []
+    for r in range(4):
+        mine = [e for i, e in enumerate(evs) if i % 4 == r]
+        seen += mine
+        assert mine == evs[r::4]
+    assert sorted(seen) == evs

@@ -18,6 +18,28 @@ from ubresnet_b200.parallel import DistributedUResNet  # noqa: E402
 from ubresnet_b200.training.pixelwise_nllloss import PixelWiseNLLLoss  # noqa: E402
 
 
+def wholeview_check(rank, world, dev):
+    """crop-sharded whole-view deploy == single-GPU deploy, bit for bit; event sharding covers every event once"""
+    from ubresnet_b200.deploy import wholeview as wv
+    torch.manual_seed(7)
+    model = UResNet(3, 1, 16).to(dev).eval()
+    bad = 0
+    for rows, cols, crop in ((256, 448, 128), (1008, 3456, 512)):
+        planes = synthetic.make_wholeview(rows=rows, cols=cols, planes=3)
+        single = wv.run_event_classes(model, planes, crop=crop)
+        sharded = wv.run_event_sharded(model, planes, crop=crop)
+        bad += int(not torch.equal(single, sharded))
+    events = [synthetic.make_wholeview(seed=50 + i, rows=256, cols=448, planes=2).pin_memory() for i in range(5)]
+    mine = [m.clone() for m in wv.run_events(model, events, crop=128, rank=rank, world=world)]
+    refs = [wv.run_event_classes(model, e, crop=128).cpu() for i, e in enumerate(events) if i % world == rank]
+    bad += int(len(mine) != len(refs)) + sum(int(not torch.equal(a, b)) for a, b in zip(mine, refs))
+    t = torch.tensor([bad], device=dev)
+    dist.all_reduce(t)
+    if rank == 0:
+        print("dp_check wholeview world=%d mismatches %d %s" % (world, int(t.item()), "OK" if t.item() == 0 else "FAIL"))
+    return int(t.item())
+
+
 def main():
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(local)
@@ -25,6 +47,10 @@ def main():
     dist.init_process_group("nccl", device_id=dev)
     torch.manual_seed(99)
     arch = sys.argv[1] if len(sys.argv) > 1 else "uresnet"
+    if arch == "wholeview":
+        bad = wholeview_check(rank, world, dev)
+        dist.destroy_process_group()
+        sys.exit(0 if bad == 0 else 1)
     if arch == "aspp":
         from ubresnet_b200.models.ASPP_ResNet import ASPP_ResNet
         model = ASPP_ResNet(3, 1, 16, showsizes=False).to(dev).train()

@@ -75,8 +75,27 @@ SIGNATURES = {
     "ubr_pixelwise_nll_bwd": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i64, _vp, _vp]),
     "ubr_tile_gather": (_i, [_vp, _i, _i, _vp, _i, _i, _vp, _vp]),
     "ubr_stitch_scatter": (_i, [_vp, _i, _vp, _i, _i, _i, _i, _vp, _vp]),
+    "ubr_argmax_classes": (_i, [_vp, _i, _i, _i, _vp, _vp]),
+    "ubr_stitch_scatter_u8": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _vp, _vp]),
     "ubr_accuracy_counts": (_i, [_vp, _vp, _i, _i, _i, _vp, _vp]),
     "ubr_scale_f32": (_i, [_vp, _u64, _f, _vp]),
+    "ubr_f32_conv2d_fwd": (_i, [View, _vp, _vp, _i, _i, _i, _i, _i, View, _vp]),
+    "ubr_f32_conv2d_dgrad": (_i, [View, _vp, _i, _i, _i, _i, _i, View, _i, _vp]),
+    "ubr_f32_conv2d_wgrad": (_i, [View, View, _i, _i, _i, _i, _vp, _i, _vp, _u64, _vp]),
+    "ubr_f32_deconv_fwd": (_i, [View, _vp, _i, _i, _i, _i, View, _vp]),
+    "ubr_f32_deconv_dgrad": (_i, [View, _vp, _i, _i, _i, _i, View, _vp]),
+    "ubr_f32_deconv_wgrad": (_i, [View, View, _i, _i, _i, _vp, _i, _vp, _u64, _vp]),
+    "ubr_f32_bn_stats": (_i, [View, _vp, _vp]),
+    "ubr_f32_bn_finalize": (_i, [_vp, _i, _d, _vp, _vp, _vp, _vp, _f, _f, _vp, _vp, _vp, _vp, _vp]),
+    "ubr_f32_channel_sum": (_i, [View, _vp, _vp, _i, _vp]),
+    "ubr_f32_bn_act": (_i, [View, _vp, _vp, _i, View, _vp]),
+    "ubr_f32_block_tail": (_i, [View, _vp, _vp, View, _vp, _vp, View, _vp]),
+    "ubr_f32_relu_mask": (_i, [View, View, View, _vp]),
+    "ubr_f32_bn_act_bwd": (_i, [View, View, _vp, _vp, _vp, _vp, _i, _vp, _d, View, _vp, _vp, _i, _vp]),
+    "ubr_f32_maxpool3s2_fwd": (_i, [View, View, _vp, _vp]),
+    "ubr_f32_maxpool3s2_bwd": (_i, [_vp, View, View, _i, _vp]),
+    "ubr_f32_add": (_i, [View, View, View, View, _vp]),
+    "ubr_f32_logsoftmax_bwd": (_i, [_vp, _vp, _i, _i, _i, View, _vp]),
     "ubr_opt_chunk_elems": (_i, []),
     "ubr_sgd_step": (_i, [_vp, _vp, _i, _f, _f, _f, _f, _i, _i, _vp]),
     "ubr_adam_step": (_i, [_vp, _vp, _i, _d, _d, _d, _d, _d, _i, _vp]),

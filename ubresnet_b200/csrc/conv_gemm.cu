@@ -340,10 +340,12 @@ static int launch_conv_gemm(ConvGemmParams& p, int grid_n, int grid_h, int grid_
   const uint32_t staging = 128u * p.nt * 2u;
   if (data < staging) data = staging;
   const uint32_t smem = data + 16u * stages + 16u + 1024u + 4096u + 16u;      // + [4][2][nt] fp32 statistics scratch
-  static bool attr_set = false;
-  if (!attr_set) {
+  static bool attr_set[64] = {};             // the opt-in is per device
+  int dev_id = 0;
+  UBR_CUDA_OK(cudaGetDevice(&dev_id));
+  if (!attr_set[dev_id & 63]) {
     UBR_CUDA_OK(cudaFuncSetAttribute(conv_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-    attr_set = true;
+    attr_set[dev_id & 63] = true;
   }
   dim3 grid((unsigned)(p.tiles_w * p.tiles_h * tiles_n), (unsigned)(n_pad / p.nt), 1);
   conv_gemm_kernel<<<grid, kThreads, smem, stream>>>(p);

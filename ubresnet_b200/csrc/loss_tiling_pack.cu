@@ -137,6 +137,41 @@ __global__ void __launch_bounds__(256) stitch_scatter_kernel(const float* __rest
   }
 }
 
+// per-pixel class = argmax over the C log-probabilities (first maximum, like torch.argmax / `output.max(1)`)
+__global__ void __launch_bounds__(256) argmax_classes_kernel(const float* __restrict__ logp, int n, int ncls, long hw,
+                                                             uint8_t* __restrict__ cls) {
+  const long total = (long)n * hw;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+    const long b = i / hw, px = i - b * hw;
+    const float* p = logp + b * ncls * hw + px;
+    float best = p[0];
+    int bi = 0;
+    for (int k = 1; k < ncls; ++k) {
+      const float v = p[k * hw];
+      if (v > best) { best = v; bi = k; }
+    }
+    cls[i] = (uint8_t)bi;
+  }
+}
+// uint8 class tiles -> stitched class map; same ownership rule as stitch_scatter_kernel; uncovered pixels get `fill`
+__global__ void __launch_bounds__(256) stitch_scatter_u8_kernel(const uint8_t* __restrict__ tiles,
+                                                                const int* __restrict__ origins, int ntiles, int crop,
+                                                                int rows, int cols, int fill, uint8_t* __restrict__ out) {
+  const long total = (long)rows * cols;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+    const int r = (int)(i / cols), c = (int)(i % cols);
+    uint8_t v = (uint8_t)fill;
+    for (int t = ntiles - 1; t >= 0; --t) {
+      const int r0 = origins[2 * t], c0 = origins[2 * t + 1];
+      if (r >= r0 && r < r0 + crop && c >= c0 && c < c0 + crop) {
+        v = tiles[((long)t * crop + (r - r0)) * crop + (c - c0)];
+        break;
+      }
+    }
+    out[i] = v;
+  }
+}
+
 // ------------------------------------------------------------------ weight packing
 // dst[tap][n][k] (bf16, zero padded); one extra all-zero slab at index taps (used by phases no tap reaches)
 // one element of the packed operand.  src_layout 0: OIHW conv, 1: IOHW deconv (16 taps),
@@ -339,6 +374,25 @@ int ubr_stitch_scatter(const float* tiles, int nch, const int32_t* origins, int 
   stitch_scatter_kernel<<<blocks_for((long)rows * cols), 256, 0, (cudaStream_t)stream>>>(tiles, nch, origins, ntiles,
                                                                                          crop, rows, cols, out);
   UBR_LAUNCH_CHECK("stitch_scatter_kernel");
+  return 0;
+}
+
+int ubr_argmax_classes(const float* logp, int n, int ncls, int hw, uint8_t* classes, void* stream) {
+  if (int rc = ensure_device()) return rc;
+  UBR_REQUIRE(logp && classes && n > 0 && ncls >= 1 && ncls <= 255 && hw > 0, "argmax_classes: bad arguments");
+  argmax_classes_kernel<<<blocks_for((long)n * hw), 256, 0, (cudaStream_t)stream>>>(logp, n, ncls, (long)hw, classes);
+  UBR_LAUNCH_CHECK("argmax_classes_kernel");
+  return 0;
+}
+
+int ubr_stitch_scatter_u8(const uint8_t* tiles, const int32_t* origins, int ntiles, int crop, int rows, int cols, int fill,
+                          uint8_t* out, void* stream) {
+  if (int rc = ensure_device()) return rc;
+  UBR_REQUIRE(tiles && origins && out, "stitch_scatter_u8: null pointer");
+  UBR_REQUIRE(rows > 0 && cols > 0 && ntiles > 0 && crop > 0, "stitch_scatter_u8: bad sizes");
+  stitch_scatter_u8_kernel<<<blocks_for((long)rows * cols), 256, 0, (cudaStream_t)stream>>>(tiles, origins, ntiles, crop,
+                                                                                            rows, cols, fill, out);
+  UBR_LAUNCH_CHECK("stitch_scatter_u8_kernel");
   return 0;
 }
 

@@ -334,10 +334,12 @@ static int run_wgrad(const ubr_view& ms, const ubr_view& ns, bool n_strided, con
     p.dh[i] = (int8_t)taps[i].dh; p.dw[i] = (int8_t)taps[i].dw; p.nmap[i] = (uint8_t)taps[i].nmap;
   }
   const uint32_t smem = (uint32_t)pl.stages * pl.stage_bytes + 16u * pl.stages + 16u + 1024u;
-  static bool attr_set = false;
-  if (!attr_set) {
+  static bool attr_set[64] = {};             // the opt-in is per device
+  int dev_id = 0;
+  UBR_CUDA_OK(cudaGetDevice(&dev_id));
+  if (!attr_set[dev_id & 63]) {
     UBR_CUDA_OK(cudaFuncSetAttribute(wgrad_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-    attr_set = true;
+    attr_set[dev_id & 63] = true;
   }
   UBR_REQUIRE(smem <= 227u * 1024u, "wgrad: smem plan %u too large", smem);
   dim3 grid((unsigned)pl.splits, (unsigned)(pl.ngroups * pl.n_tiles), (unsigned)pl.m_tiles);

@@ -20,7 +20,7 @@ def tile_starts(extent, crop, ntiles=None):
         return [0]
     if ntiles is None:
         ntiles = -(-extent // crop)
-        while ntiles * crop - extent < (ntiles - 1) * 16:      # keep >= 16 px of overlap per seam
+        while ntiles * crop - extent < (ntiles - 1) * min(16, crop // 4):      # keep >= 16 px of overlap per seam
             ntiles += 1
     span = extent - crop
     return [int(math.floor(i * span / (ntiles - 1) + 0.5)) for i in range(ntiles)]
@@ -45,11 +45,11 @@ def stitch(tiles, plan, rows, cols):
 
 
 @torch.no_grad()
-def run_event(model, planes, crop=512, batch=None, rank=0, world=1):
+def run_event(model, planes, crop=512, batch=None):
     """planes (P, rows, cols) fp32 (CPU or CUDA).  Returns (P, C, rows, cols) log-prob maps on the model's device.
     The crops of ALL planes of the event go through the network together (`batch` = crops per forward call; None = the
-    whole event, 42 crops for 3 planes of 1008x3456).  With world > 1 the caller shards EVENTS round-robin
-    (event i -> rank i % world); this function is per event."""
+    whole event, 42 crops for 3 planes of 1008x3456).  Multi-GPU: run_events(rank=, world=) shards events,
+    run_event_sharded shards the crops of one event."""
     dev = next(model.parameters()).device
     planes = planes.to(dev, non_blocking=True).float()
     nplanes, rows, cols = planes.shape
@@ -62,8 +62,97 @@ def run_event(model, planes, crop=512, batch=None, rank=0, world=1):
     return torch.stack([stitch(res[p * per_plane:(p + 1) * per_plane], plan, rows, cols) for p in range(nplanes)], 0)
 
 
+def stitch_classes(class_tiles, plan, rows, cols, out=None):
+    """class_tiles (ntiles, crop, crop) uint8 CUDA -> (rows, cols) uint8; highest-index covering tile wins."""
+    return ops.stitch_scatter_u8(class_tiles.contiguous(), _origins(plan, class_tiles.device), rows, cols, out=out)
+
+
 @torch.no_grad()
-def run_events(model, events, crop=512, batch=None):
+def run_event_classes(model, planes, crop=512, batch=None, out=None):
+    """run_event reduced to what the deploy script keeps (run_ubresnet_wholeview.py:264-272 writes the per-pixel
+    winner): (P, rows, cols) uint8 class maps.  The argmax is taken per crop (1 byte per pixel) and the TILES are
+    stitched -- bit-identical to argmax(run_event(...), 1) because stitching copies whole pixels -- so the
+    (P, C, rows, cols) fp32 map (125 MB per event) is never materialised."""
+    dev = next(model.parameters()).device
+    planes = planes.to(dev, non_blocking=True).float()
+    nplanes, rows, cols = planes.shape
+    plan = tile_plan(rows, cols, crop)
+    crops = torch.cat([gather(planes[p], plan, crop) for p in range(nplanes)], 0)
+    per_plane = len(plan)
+    batch = batch or crops.shape[0]
+    cls = torch.empty((crops.shape[0], crop, crop), dtype=torch.uint8, device=dev)
+    for i in range(0, crops.shape[0], batch):
+        ops.argmax_classes(model(crops[i:i + batch]), out=cls[i:i + batch])
+    if out is None:
+        out = torch.empty((nplanes, rows, cols), dtype=torch.uint8, device=dev)
+    for p in range(nplanes):
+        stitch_classes(cls[p * per_plane:(p + 1) * per_plane], plan, rows, cols, out=out[p])
+    return out
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# multi-GPU deploy (SURVEY 8e row 2, kernel id C2).  Two shardings, both over torch.distributed:
+#   events : event i -> rank i % world, no collective at all (throughput mode)           -> run_events(rank=, world=)
+#   crops  : the 42 crops of ONE event are split into `world` contiguous blocks; every rank runs its block and the
+#            1-byte class tiles are all-gathered (NCCL over NVLink: 11 MB per event) so the stitch owner -- every rank,
+#            the stitch is 20 us -- holds the whole event (single-event latency mode)    -> run_event_sharded
+# ---------------------------------------------------------------------------------------------------------------
+def crop_shard(ncrops, rank, world):
+    """(first, count, per_rank): rank's contiguous block of the event's crops; per_rank = ceil(ncrops / world) is the
+    padded block size of the all-gather (the last ranks may hold fewer, or zero, real crops)."""
+    per = -(-ncrops // world)
+    first = min(rank * per, ncrops)
+    return first, max(0, min(per, ncrops - first)), per
+
+
+def gather_class_tiles(local_tiles, ncrops, group=None):
+    """local_tiles (per_rank, crop, crop) uint8 (rows beyond this rank's real crops are padding) -> (ncrops, crop, crop)
+    in global crop order on every rank.  One all-gather of 1-byte tiles; works on CUDA (NCCL) and CPU (gloo) tensors."""
+    import torch.distributed as dist
+    world = dist.get_world_size(group)
+    per = local_tiles.shape[0]
+    full = torch.empty((world * per,) + tuple(local_tiles.shape[1:]), dtype=local_tiles.dtype, device=local_tiles.device)
+    dist.all_gather_into_tensor(full, local_tiles.contiguous(), group=group)
+    return full[:ncrops]
+
+
+@torch.no_grad()
+def run_event_sharded(model, planes, crop=512, group=None, batch=None):
+    """ONE event, its crops sharded over the ranks of `group` (every rank passes the same `planes`; host tensors are
+    uploaded by each rank).  Returns the (P, rows, cols) uint8 class maps on every rank -- bit-identical to
+    run_event_classes on one GPU (the per-crop forward does not depend on which other crops share the batch in eval
+    mode; `tools/dp_check.py wholeview` and bench.py check it)."""
+    import torch.distributed as dist
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
+        return run_event_classes(model, planes, crop=crop, batch=batch)
+    rank, world = dist.get_rank(group), dist.get_world_size(group)
+    dev = next(model.parameters()).device
+    planes = planes.to(dev, non_blocking=True).float()
+    nplanes, rows, cols = planes.shape
+    plan = tile_plan(rows, cols, crop)
+    per_plane = len(plan)
+    ncrops = nplanes * per_plane
+    first, count, per = crop_shard(ncrops, rank, world)
+    local = torch.zeros((per, crop, crop), dtype=torch.uint8, device=dev)
+    if count:
+        parts = []
+        for p in range(first // per_plane, (first + count - 1) // per_plane + 1):       # planes this block touches
+            lo = max(first, p * per_plane) - p * per_plane
+            hi = min(first + count, (p + 1) * per_plane) - p * per_plane
+            parts.append(gather(planes[p], plan[lo:hi], crop))
+        crops = parts[0] if len(parts) == 1 else torch.cat(parts, 0)
+        b = batch or count
+        for i in range(0, count, b):
+            ops.argmax_classes(model(crops[i:i + b]), out=local[i:min(i + b, count)])
+    tiles = gather_class_tiles(local, ncrops, group)
+    out = torch.empty((nplanes, rows, cols), dtype=torch.uint8, device=dev)
+    for p in range(nplanes):
+        stitch_classes(tiles[p * per_plane:(p + 1) * per_plane], plan, rows, cols, out=out[p])
+    return out
+
+
+@torch.no_grad()
+def run_events(model, events, crop=512, batch=None, rank=0, world=1):
     """Deploy loop over many events with the host<->device copies off the critical path.
 
     `events`: iterable of (P, rows, cols) fp32 HOST tensors of one shape (pinned memory makes the copies
@@ -71,7 +160,13 @@ def run_events(model, events, crop=512, batch=None):
     the stitched log-prob maps, what deploy/run_ubresnet_wholeview.py:264-272 writes out).  The planes of event i+1 are
     uploaded and the class map of event i-1 is downloaded on a copy stream while event i runs, through two persistent
     device input buffers and two device / pinned-host output buffers (no allocation inside the loop).  A yielded map
-    stays valid until the next one is requested (copy it to keep it)."""
+    stays valid until the next one is requested (copy it to keep it).
+
+    Multi-GPU: with world > 1 this rank processes events rank, rank + world, ... (round-robin event sharding, no
+    collective -- SURVEY 8e) and yields only those, in order; event i of the input is the (i // world)-th map of rank
+    i % world."""
+    if world > 1:
+        events = (e for i, e in enumerate(events) if i % world == rank)
     dev = next(model.parameters()).device
     main = torch.cuda.current_stream(dev)
     copy = torch.cuda.Stream(device=dev)
@@ -109,12 +204,11 @@ def run_events(model, events, crop=512, batch=None):
         except StopIteration:
             nxt = None
         up = upload(nxt, j ^ 1) if nxt is not None else None            # overlaps with this event's forward pass
-        maps = run_event(model, d_in[j], crop=crop, batch=batch)
-        in_free[j] = torch.cuda.Event()
-        in_free[j].record(main)
         if d2h[j] is not None:
             main.wait_event(d2h[j])                                     # the download two events ago has left d_cls[j]
-        d_cls[j].copy_(maps.argmax(1))
+        run_event_classes(model, d_in[j], crop=crop, batch=batch, out=d_cls[j])
+        in_free[j] = torch.cuda.Event()
+        in_free[j].record(main)
         done = torch.cuda.Event()
         done.record(main)
         with torch.cuda.stream(copy):

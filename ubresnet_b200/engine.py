@@ -248,6 +248,25 @@ class Engine:
         y = ops.conv2d_fwd(x, wpk, bias, out_ch, k, stride)
         return y, self._bn(y, bn, False, bn_ws)
 
+    def _grad_targets(self, sink):
+        """{param: fp32 tensor the weight-gradient kernels write}.  With a data-parallel sink the targets are views of
+        its flat all-reduce buckets; frozen parameters (not in any bucket) get scratch.  A `param.grad` that still
+        aliases bucket storage (zero_grad(set_to_none=False), gradient accumulation over micro-batches) is moved out
+        first -- otherwise this backward would overwrite it and AccumulateGrad would add the new gradient onto itself."""
+        m = self.model
+        if sink is None:
+            return {prm: torch.empty_like(prm, dtype=torch.float32) for prm in m.parameters()}
+        grads = {}
+        with torch.no_grad():
+            for prm in m.parameters():
+                if prm.requires_grad and prm in sink.views:
+                    if sink.aliases(prm):
+                        prm.grad = prm.grad.clone()
+                    grads[prm] = sink.grad_buffer(prm)
+                else:
+                    grads[prm] = torch.empty_like(prm, dtype=torch.float32)
+        return grads
+
     # ------------------------------------------------------------------ weight gradients on a side stream
     def _wgrad_begin(self, device):
         if WGRAD_SIDE_STREAM and self._wstream is None:
@@ -442,7 +461,8 @@ class Engine:
         if x.dim() != 4 or x.shape[1] != m.conv1.in_channels:
             raise RuntimeError("UResNet: expected input (B,%d,H,W), got %s" % (m.conv1.in_channels, tuple(x.shape)))
         if m.conv1.in_channels != 1:
-            raise RuntimeError("ubresnet_b200: only input_channels=1 (wire-plane crops) is implemented")
+            raise RuntimeError("ubresnet_b200: the bf16 tensor-core schedule takes input_channels=1 (wire-plane crops); "
+                               "other channel counts run in the fp32 mode (UResNet(..., precision='fp32'))")
         if m.inplanes % 16 != 0:
             raise RuntimeError("ubresnet_b200: inplanes must be a multiple of 16 (tensor-core tile width)")
         if x.shape[2] % 32 or x.shape[3] % 32:
@@ -450,7 +470,14 @@ class Engine:
         if m.conv1.weight.device != x.device:
             raise RuntimeError("UResNet: parameters on %s but input on %s" % (m.conv1.weight.device, x.device))
         params = list(m.parameters())                    # ONE walk of the module tree per call (host time before
-        need_grad = torch.is_grad_enabled() and m.training and any(p.requires_grad for p in params)   # the first launch)
+        trainable = torch.is_grad_enabled() and any(p.requires_grad for p in params)                  # the first launch)
+        if x.requires_grad and torch.is_grad_enabled():
+            raise RuntimeError("ubresnet_b200: gradients with respect to the input image are not implemented (the "
+                               "reference scripts never request them); detach the input")
+        if trainable and not m.training:
+            raise RuntimeError("ubresnet_b200: autograd through an eval()-mode forward is not implemented; call "
+                               "model.train() for training or wrap inference in torch.no_grad()")
+        need_grad = trainable and m.training
         with torch.cuda.device(x.device):
             if need_grad:
                 return _UResNetFn.apply(self, x, *params)
@@ -551,10 +578,7 @@ class Engine:
         p = m.inplanes
         bn_ws, wg_ws, stem_ws = self._workspaces(n, h, w, dev)
         sink = self.grad_sink
-        if sink is not None:
-            grads = {prm: sink.grad_buffer(prm) for prm in m.parameters()}
-        else:
-            grads = {prm: torch.empty_like(prm, dtype=torch.float32) for prm in m.parameters()}
+        grads = self._grad_targets(sink)
         self._wgrad_begin(dev)
 
         def done(name):

@@ -179,10 +179,7 @@ class ASPPEngine(Engine):
         p = m.inplanes
         bn_ws, wg_ws, stem_ws = self._workspaces(n, h, w, dlogp.device)
         sink = self.grad_sink
-        if sink is not None:       # data-parallel: gradients land in the flat all-reduce buckets (parallel.py)
-            grads = {prm: sink.grad_buffer(prm) for prm in m.parameters()}
-        else:
-            grads = {prm: torch.empty_like(prm, dtype=torch.float32) for prm in m.parameters()}
+        grads = self._grad_targets(sink)     # data-parallel: gradients land in the flat all-reduce buckets (parallel.py)
         self._wgrad_begin(dlogp.device)     # every weight gradient (ASPP layers included) goes to the side stream
 
         def done(name):

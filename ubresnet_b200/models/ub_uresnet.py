@@ -10,6 +10,7 @@ kernel schedule in `ubresnet_b200.engine` (bf16 NHWC activations, fp32 accumulat
 There is no CPU path: a CPU input raises.
 """
 import math
+import os
 
 import torch
 import torch.nn as nn
@@ -19,10 +20,17 @@ from .common_layers import ConvTransposeLayer, DoubleResNet
 
 class UResNet(nn.Module):
 
-    def __init__(self, num_classes=3, input_channels=3, inplanes=16, final_conv_kernels=16, showsizes=False):
+    def __init__(self, num_classes=3, input_channels=3, inplanes=16, final_conv_kernels=16, showsizes=False,
+                 precision=None):
+        """`precision` (extra, keyword; default from $UBR_PRECISION, else "bf16"): "bf16" = tensor-core schedule with
+        bf16 NHWC storage and fp32 accumulation; "fp32" = the reference's arithmetic type end to end (parity mode,
+        CUDA cores; also the only mode for input_channels != 1).  May be changed later through `model.precision`."""
         self.inplanes = inplanes
         super().__init__()
         self._showsizes = showsizes
+        self.precision = precision or os.environ.get("UBR_PRECISION", "bf16")
+        if self.precision not in ("bf16", "fp32"):
+            raise ValueError("precision must be 'bf16' or 'fp32', got %r" % (self.precision,))
         p = self.inplanes
 
         # stem
@@ -56,6 +64,7 @@ class UResNet(nn.Module):
                 m.bias.data.zero_()
 
         self._engine = None
+        self._engine_f32 = None
 
     def _make_encoding_layer(self, inplanes, planes, stride=2):
         return DoubleResNet(inplanes, planes, stride=stride)
@@ -64,6 +73,11 @@ class UResNet(nn.Module):
         return ConvTransposeLayer(inplanes, deconvplanes, resnetplanes)
 
     def engine(self):
+        if self.precision == "fp32":
+            if self._engine_f32 is None:
+                from ..engine_f32 import EngineF32
+                self._engine_f32 = EngineF32(self)
+            return self._engine_f32
         if self._engine is None:
             from ..engine import Engine
             self._engine = Engine(self)

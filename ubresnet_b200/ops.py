@@ -18,6 +18,14 @@ def _ptr(t):
     return 0 if t is None else t.data_ptr()
 
 
+def _bump(*tensors):
+    """the kernels write these tensors through raw pointers: advance their version counters like an in-place torch op
+    would, so that caches keyed on `_version` (the eval-mode BatchNorm fold, engine._FoldedConv) see the update"""
+    ts = [t for t in tensors if t is not None]
+    if ts:
+        torch.autograd.graph.increment_version(ts)
+
+
 def require_cuda(t, name):
     if not isinstance(t, torch.Tensor) or not t.is_cuda:
         raise RuntimeError("ubresnet_b200: %s must be a CUDA tensor (there is no CPU path)" % name)
@@ -148,6 +156,7 @@ def conv2d_fwd_bn(x, wpk, bias, out_ch, ksize, stride, gamma, beta, running_mean
                                         _ptr(running_mean), _ptr(running_var), momentum, eps, st.scale.data_ptr(),
                                         st.shift.data_ptr(), st.mean.data_ptr(), st.invstd.data_ptr(), _stream()),
                "bn_finalize_rows")
+    _bump(running_mean, running_var)
     return y, st
 
 
@@ -342,6 +351,7 @@ def bn_train_stats(y, gamma, beta, running_mean, running_var, ws, state=None, mo
     _lib.check(lib.ubr_bn_finalize(ws.data_ptr(), y.c, st.count, _ptr(gamma), _ptr(beta), _ptr(running_mean),
                                    _ptr(running_var), momentum, eps, st.scale.data_ptr(), st.shift.data_ptr(),
                                    st.mean.data_ptr(), st.invstd.data_ptr(), _stream()), "bn_finalize")
+    _bump(running_mean, running_var)
     return st
 
 
@@ -545,6 +555,31 @@ def stitch_scatter(tiles, origins, rows, cols):
     out = torch.empty((nch, rows, cols), dtype=torch.float32, device=tiles.device)
     _lib.check(lib.ubr_stitch_scatter(tiles.data_ptr(), nch, origins.data_ptr(), nt, crop, rows, cols, out.data_ptr(),
                                       _stream()), "stitch_scatter")
+    return out
+
+
+def argmax_classes(logp, out=None):
+    """(N,C,H,W) fp32 log-probs -> (N,H,W) uint8 classes (first maximum)"""
+    lib = _lib.load()
+    require_cuda(logp, "log-probs")
+    n, ncls, h, w = logp.shape
+    assert logp.dtype == torch.float32 and logp.is_contiguous()
+    if out is None:
+        out = torch.empty((n, h, w), dtype=torch.uint8, device=logp.device)
+    _lib.check(lib.ubr_argmax_classes(logp.data_ptr(), n, ncls, h * w, out.data_ptr(), _stream()), "argmax_classes")
+    return out
+
+
+def stitch_scatter_u8(tiles, origins, rows, cols, fill=0, out=None):
+    """(ntiles, crop, crop) uint8 class tiles -> (rows, cols) uint8"""
+    lib = _lib.load()
+    require_cuda(tiles, "tiles")
+    nt, crop, _ = tiles.shape
+    assert tiles.dtype == torch.uint8 and tiles.is_contiguous()
+    if out is None:
+        out = torch.empty((rows, cols), dtype=torch.uint8, device=tiles.device)
+    _lib.check(lib.ubr_stitch_scatter_u8(tiles.data_ptr(), origins.data_ptr(), nt, crop, rows, cols, int(fill),
+                                         out.data_ptr(), _stream()), "stitch_scatter_u8")
     return out
 
 

@@ -81,6 +81,13 @@ class GradBuckets:
         # reference to, but clones one that something else (our `views` table) also references -- 165 copy kernels/step
         return self.views[param].view(param.shape)
 
+    def aliases(self, param):
+        """True when `param.grad` still lives in this bucket's storage (zero_grad(set_to_none=False), or a second
+        backward before the optimizer step): the next backward would overwrite it and AccumulateGrad would then add the
+        new gradient onto itself."""
+        g = param.grad
+        return g is not None and g.data_ptr() == self.views[param].data_ptr()
+
     def wants(self, stage):
         """True when `stage` closes a bucket (its all-reduce is launched by stage_done)."""
         b = BUCKET_OF_STAGE[stage]
@@ -139,14 +146,22 @@ def broadcast_module(module, src=0, process_group=None):
     if not dist.is_initialized() or dist.get_world_size(process_group) == 1:
         return
     with torch.no_grad():
-        for t in list(module.parameters()) + list(module.buffers()):
+        ts = list(module.parameters()) + list(module.buffers())
+        for t in ts:
             dist.broadcast(t.data, src=src, group=process_group)
+        # `.data` writes do not advance the version counters the engine's bf16 operand caches are keyed on
+        torch.autograd.graph.increment_version(ts)
 
 
 class DistributedUResNet(torch.nn.Module):
     """`model = DistributedUResNet(UResNet(...).cuda())` -- takes nn.DataParallel's place in the training
     scripts (checkpoints keep the `module.` prefix that deploy/ubresnet_funcs.py:52-64 strips).  Wraps `UResNet`
     and `ASPP_ResNet` alike."""
+
+    """Gradients are written straight into the flat all-reduce buckets and handed to autograd as views of them, so
+    `param.grad` must be released before the next backward: use `optimizer.zero_grad(set_to_none=True)` (the default
+    since torch 2.0).  Gradient accumulation over micro-batches / `zero_grad(set_to_none=False)` is detected and
+    handled by a scratch copy (engine.backward), at the cost of one extra pass over the gradients."""
 
     def __init__(self, module, process_group=None):
         super().__init__()
