@@ -512,6 +512,10 @@ def run_own(args, rank, world, local_rank):
             ms_w, l_w = timed(event, nev, 1)
             sharded_ok = None
             if world > 1:
+                # deploy needs ONE model state on every rank: BatchNorm running statistics are per rank during training
+                # (like nn.DataParallel's replicas) -- rank 0's buffers win, as when a checkpoint is written
+                from ubresnet_b200.parallel import broadcast_module
+                broadcast_module(model, 0)
                 single = wv.run_event_classes(model, planes, crop=512)
                 same = torch.tensor([int(torch.equal(single, wv.run_event_sharded(model, planes, crop=512)))], device=dev)
                 dist.all_reduce(same, op=dist.ReduceOp.MIN)
@@ -643,7 +647,9 @@ def main():
         import torch.distributed as dist
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
-            os.environ["NCCL_DEBUG"] = "WARN"          # keep NCCL's version banner off stdout (one JSON line only)
+            os.environ["NCCL_DEBUG"] = "WARN"
+        # NCCL writes its version banner and warnings to stdout: send them to a file so that stdout is ONE JSON line
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/tmp/ubresnet_b200_nccl_%h_%p.log")
         torch.cuda.set_device(local_rank)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     try:

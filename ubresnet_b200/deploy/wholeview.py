@@ -119,7 +119,9 @@ def gather_class_tiles(local_tiles, ncrops, group=None):
 @torch.no_grad()
 def run_event_sharded(model, planes, crop=512, group=None, batch=None):
     """ONE event, its crops sharded over the ranks of `group` (every rank passes the same `planes`; host tensors are
-    uploaded by each rank).  Returns the (P, rows, cols) uint8 class maps on every rank -- bit-identical to
+    uploaded by each rank; every rank must hold the same model state -- a loaded checkpoint, or
+    parallel.broadcast_module after training, whose BatchNorm running statistics are per rank).  Returns the
+    (P, rows, cols) uint8 class maps on every rank -- bit-identical to
     run_event_classes on one GPU (the per-crop forward does not depend on which other crops share the batch in eval
     mode; `tools/dp_check.py wholeview` and bench.py check it)."""
     import torch.distributed as dist
