@@ -220,13 +220,19 @@ int ubr_tile_gather(const float* plane, int rows, int cols, const int32_t* origi
                     float* crops, void* stream);
 int ubr_stitch_scatter(const float* tiles /* [ntiles,c,crop,crop] */, int nch, const int32_t* origins, int ntiles,
                        int crop, int rows, int cols, float* out /* [c,rows,cols] */, void* stream);
+/* rectangular crops (crop_h x crop_w): the 512 x 832 boxes of the UBSplitDetector configuration
+ * (deploy/run_ubresnet_wholeview.py:33-47).  Gather zero-fills the part of a box that lies outside the plane. */
+int ubr_tile_gather_rect(const float* plane, int rows, int cols, const int32_t* origins, int ntiles, int crop_h, int crop_w,
+                         float* crops, void* stream);
+int ubr_stitch_scatter_rect(const float* tiles, int nch, const int32_t* origins, int ntiles, int crop_h, int crop_w, int rows,
+                            int cols, float* out, void* stream);
 /* class maps for the deploy loop (what deploy/run_ubresnet_wholeview.py:264-272 keeps of the network output):
  * classes[n,hw] = argmax_k logp[n,k,hw] (first maximum), and the stitch of uint8 class TILES [ntiles,crop,crop] with
  * the same highest-tile-wins rule as ubr_stitch_scatter (pixels no tile covers get `fill`).  Crop-sharded multi-GPU
  * deploy exchanges these 1-byte tiles instead of C fp32 maps. */
 int ubr_argmax_classes(const float* logp, int n, int ncls, int hw, uint8_t* classes, void* stream);
-int ubr_stitch_scatter_u8(const uint8_t* tiles, const int32_t* origins, int ntiles, int crop, int rows, int cols, int fill,
-                          uint8_t* out, void* stream);
+int ubr_stitch_scatter_u8(const uint8_t* tiles, const int32_t* origins, int ntiles, int crop_h, int crop_w, int rows, int cols,
+                          int fill, uint8_t* out, void* stream);
 
 /* ---- accuracy counters: replaces the 2*C `.item()` reductions of `accuracy()` (reference
  * training/train_ubresnet2018_wlarcv2.py:509-566).  pred = argmax over classes of logp (NCHW fp32, first maximum);
@@ -301,6 +307,32 @@ int ubr_f32_maxpool3s2_fwd(ubr_view x, ubr_view y, uint8_t* idx /* may be NULL *
 int ubr_f32_maxpool3s2_bwd(const uint8_t* idx, ubr_view dy, ubr_view dx, int accumulate, void* stream);
 int ubr_f32_add(ubr_view a, ubr_view b, ubr_view c, ubr_view out, void* stream);
 int ubr_f32_logsoftmax_bwd(const float* logp, const float* dlogp, int n, int ncls, int hw, ubr_view dlogits, void* stream);
+
+/* ---- device-side batch assembly: the reference's C++ batch fillers as kernels ----------------------
+ * src_dtype: 0 fp32, 1 fp16, 2 uint8 (what travels over PCIe); larcv Image2D pixel order is COLUMN-major
+ * (index = col*rows + row).  mirror: optional per-sample flags (device uint8[batch]) -- the column mirror of
+ * BatchFillerImage2D.cxx:102-112 / SegFiller.cxx `EnableMirror`.
+ *   ubr_fill_image_batch : out[b,0,row,col] (fp32, the network input) = src[b][(mirror ? cols-1-col : col)*rows + row]
+ *                          (larcv/larcv/app/ThreadIO/BatchFillerImage2D.cxx:217-256)
+ *   ubr_fill_label_batch : out[b,row,col] (int64 nll target) = lut[(size_t)src[...]] + shift; lut = the roitype->class
+ *                          table of SegFiller.cxx:49-63 (0xFF = invalid), shift = -1 in the training scripts
+ *                          (grid_scripts/train_ubresnet_wlarcv1_tuftsgrid.py:132); *invalid_count (device int) receives
+ *                          the number of pixels with an invalid ROI type (the host code throws larbys on the first)
+ *   ubr_seg_weights      : SegWeightTrackShower (caffe/larcv/app/ImageMod/SegWeightTrackShower.cxx:109-272) without the
+ *                          optional keypoint term: cat_lut maps a label code to 0 none / 1 shower / 2 track;
+ *                          w = pool(weight_in | 1.0, {(int)(N/n_shower), (int)(N/n_track), (int)(N/n_surrounding)}),
+ *                          clipped at weight_max.  pool_type: 0 sum, 1 max, 2 average, 3 overwrite (SegWeightTrackShower.h
+ *                          PoolType_t).  label_dtype: 0 fp32, 2 uint8, 3 int64; column_major describes the label only,
+ *                          weight_in (may be NULL) and weight_out are row-major fp32 [batch][rows][cols]. */
+int ubr_fill_image_batch(const void* src, int src_dtype, int batch, int rows, int cols, const uint8_t* mirror, float* out,
+                         void* stream);
+int ubr_fill_label_batch(const void* src, int src_dtype, int batch, int rows, int cols, const uint8_t* mirror,
+                         const uint8_t* lut, int lut_size, int shift, int64_t* out, int* invalid_count, void* stream);
+uint64_t ubr_seg_weights_workspace_bytes(int batch, int rows, int cols);
+int ubr_seg_weights(const void* label, int label_dtype, int column_major, int batch, int rows, int cols,
+                    const uint8_t* cat_lut, int lut_size, int dist_surrounding, int weight_surrounding, int pool_type,
+                    float weight_max, const float* weight_in, float* weight_out, void* workspace, uint64_t workspace_bytes,
+                    void* stream);
 
 /* ---- flat-buffer helpers for the data-parallel gradient buckets --------------------------------- */
 int ubr_scale_f32(float* buf, uint64_t count, float alpha, void* stream);

@@ -76,9 +76,15 @@ SIGNATURES = {
     "ubr_tile_gather": (_i, [_vp, _i, _i, _vp, _i, _i, _vp, _vp]),
     "ubr_stitch_scatter": (_i, [_vp, _i, _vp, _i, _i, _i, _i, _vp, _vp]),
     "ubr_argmax_classes": (_i, [_vp, _i, _i, _i, _vp, _vp]),
-    "ubr_stitch_scatter_u8": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _vp, _vp]),
+    "ubr_stitch_scatter_u8": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _i, _vp, _vp]),
+    "ubr_tile_gather_rect": (_i, [_vp, _i, _i, _vp, _i, _i, _i, _vp, _vp]),
+    "ubr_stitch_scatter_rect": (_i, [_vp, _i, _vp, _i, _i, _i, _i, _i, _vp, _vp]),
     "ubr_accuracy_counts": (_i, [_vp, _vp, _i, _i, _i, _vp, _vp]),
     "ubr_scale_f32": (_i, [_vp, _u64, _f, _vp]),
+    "ubr_fill_image_batch": (_i, [_vp, _i, _i, _i, _i, _vp, _vp, _vp]),
+    "ubr_fill_label_batch": (_i, [_vp, _i, _i, _i, _i, _vp, _vp, _i, _i, _vp, _vp, _vp]),
+    "ubr_seg_weights_workspace_bytes": (_u64, [_i, _i, _i]),
+    "ubr_seg_weights": (_i, [_vp, _i, _i, _i, _i, _i, _vp, _i, _i, _i, _i, _f, _vp, _vp, _vp, _u64, _vp]),
     "ubr_f32_conv2d_fwd": (_i, [View, _vp, _vp, _i, _i, _i, _i, _i, View, _vp]),
     "ubr_f32_conv2d_dgrad": (_i, [View, _vp, _i, _i, _i, _i, _i, View, _i, _vp]),
     "ubr_f32_conv2d_wgrad": (_i, [View, View, _i, _i, _i, _i, _vp, _i, _vp, _u64, _vp]),

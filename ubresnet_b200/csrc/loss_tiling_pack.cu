@@ -103,9 +103,9 @@ __global__ void __launch_bounds__(256) nll_bwd_kernel(const long long* __restric
 
 // ------------------------------------------------------------------ tiling
 __global__ void __launch_bounds__(256) tile_gather_kernel(const float* __restrict__ plane, int rows, int cols,
-                                                          const int* __restrict__ origins, int ntiles, int crop,
-                                                          float* __restrict__ crops) {
-  const long per = (long)crop * crop;
+                                                          const int* __restrict__ origins, int ntiles, int crop_h,
+                                                          int crop, float* __restrict__ crops) {
+  const long per = (long)crop_h * crop;
   const long total = per * ntiles;
   for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
     const int t = (int)(i / per);
@@ -116,21 +116,21 @@ __global__ void __launch_bounds__(256) tile_gather_kernel(const float* __restric
 }
 // every output pixel takes the value of the highest-index tile that covers it (== sequential overwrite)
 __global__ void __launch_bounds__(256) stitch_scatter_kernel(const float* __restrict__ tiles, int nch,
-                                                             const int* __restrict__ origins, int ntiles, int crop,
-                                                             int rows, int cols, float* __restrict__ out) {
+                                                             const int* __restrict__ origins, int ntiles, int crop_h,
+                                                             int crop, int rows, int cols, float* __restrict__ out) {
   const long total = (long)rows * cols;
   for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
     const int r = (int)(i / cols), c = (int)(i % cols);
     int owner = -1;
     for (int t = ntiles - 1; t >= 0; --t) {
       const int r0 = origins[2 * t], c0 = origins[2 * t + 1];
-      if (r >= r0 && r < r0 + crop && c >= c0 && c < c0 + crop) { owner = t; break; }
+      if (r >= r0 && r < r0 + crop_h && c >= c0 && c < c0 + crop) { owner = t; break; }
     }
     for (int k = 0; k < nch; ++k) {
       float v = 0.f;
       if (owner >= 0) {
         const int r0 = origins[2 * owner], c0 = origins[2 * owner + 1];
-        v = tiles[(((long)owner * nch + k) * crop + (r - r0)) * crop + (c - c0)];
+        v = tiles[(((long)owner * nch + k) * crop_h + (r - r0)) * crop + (c - c0)];
       }
       out[(long)k * total + i] = v;
     }
@@ -155,16 +155,17 @@ __global__ void __launch_bounds__(256) argmax_classes_kernel(const float* __rest
 }
 // uint8 class tiles -> stitched class map; same ownership rule as stitch_scatter_kernel; uncovered pixels get `fill`
 __global__ void __launch_bounds__(256) stitch_scatter_u8_kernel(const uint8_t* __restrict__ tiles,
-                                                                const int* __restrict__ origins, int ntiles, int crop,
-                                                                int rows, int cols, int fill, uint8_t* __restrict__ out) {
+                                                                const int* __restrict__ origins, int ntiles, int crop_h,
+                                                                int crop, int rows, int cols, int fill,
+                                                                uint8_t* __restrict__ out) {
   const long total = (long)rows * cols;
   for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
     const int r = (int)(i / cols), c = (int)(i % cols);
     uint8_t v = (uint8_t)fill;
     for (int t = ntiles - 1; t >= 0; --t) {
       const int r0 = origins[2 * t], c0 = origins[2 * t + 1];
-      if (r >= r0 && r < r0 + crop && c >= c0 && c < c0 + crop) {
-        v = tiles[((long)t * crop + (r - r0)) * crop + (c - c0)];
+      if (r >= r0 && r < r0 + crop_h && c >= c0 && c < c0 + crop) {
+        v = tiles[((long)t * crop_h + (r - r0)) * crop + (c - c0)];
         break;
       }
     }
@@ -355,26 +356,34 @@ int ubr_pixelwise_nll_bwd(const int64_t* target, const float* pixw, const float*
   return 0;
 }
 
-int ubr_tile_gather(const float* plane, int rows, int cols, const int32_t* origins, int ntiles, int crop, float* crops,
-                    void* stream) {
+int ubr_tile_gather_rect(const float* plane, int rows, int cols, const int32_t* origins, int ntiles, int crop_h, int crop_w,
+                         float* crops, void* stream) {
   if (int rc = ensure_device()) return rc;
   UBR_REQUIRE(plane && origins && crops, "tile_gather: null pointer");
-  UBR_REQUIRE(rows > 0 && cols > 0 && ntiles > 0 && crop > 0, "tile_gather: bad sizes");
-  tile_gather_kernel<<<blocks_for((long)ntiles * crop * crop), 256, 0, (cudaStream_t)stream>>>(plane, rows, cols, origins,
-                                                                                               ntiles, crop, crops);
+  UBR_REQUIRE(rows > 0 && cols > 0 && ntiles > 0 && crop_h > 0 && crop_w > 0, "tile_gather: bad sizes");
+  tile_gather_kernel<<<blocks_for((long)ntiles * crop_h * crop_w), 256, 0, (cudaStream_t)stream>>>(
+      plane, rows, cols, origins, ntiles, crop_h, crop_w, crops);
   UBR_LAUNCH_CHECK("tile_gather_kernel");
   return 0;
 }
+int ubr_tile_gather(const float* plane, int rows, int cols, const int32_t* origins, int ntiles, int crop, float* crops,
+                    void* stream) {
+  return ubr_tile_gather_rect(plane, rows, cols, origins, ntiles, crop, crop, crops, stream);
+}
 
-int ubr_stitch_scatter(const float* tiles, int nch, const int32_t* origins, int ntiles, int crop, int rows, int cols,
-                       float* out, void* stream) {
+int ubr_stitch_scatter_rect(const float* tiles, int nch, const int32_t* origins, int ntiles, int crop_h, int crop_w, int rows,
+                            int cols, float* out, void* stream) {
   if (int rc = ensure_device()) return rc;
   UBR_REQUIRE(tiles && origins && out, "stitch_scatter: null pointer");
-  UBR_REQUIRE(rows > 0 && cols > 0 && ntiles > 0 && crop > 0 && nch > 0, "stitch_scatter: bad sizes");
+  UBR_REQUIRE(rows > 0 && cols > 0 && ntiles > 0 && crop_h > 0 && crop_w > 0 && nch > 0, "stitch_scatter: bad sizes");
   stitch_scatter_kernel<<<blocks_for((long)rows * cols), 256, 0, (cudaStream_t)stream>>>(tiles, nch, origins, ntiles,
-                                                                                         crop, rows, cols, out);
+                                                                                         crop_h, crop_w, rows, cols, out);
   UBR_LAUNCH_CHECK("stitch_scatter_kernel");
   return 0;
+}
+int ubr_stitch_scatter(const float* tiles, int nch, const int32_t* origins, int ntiles, int crop, int rows, int cols,
+                       float* out, void* stream) {
+  return ubr_stitch_scatter_rect(tiles, nch, origins, ntiles, crop, crop, rows, cols, out, stream);
 }
 
 int ubr_argmax_classes(const float* logp, int n, int ncls, int hw, uint8_t* classes, void* stream) {
@@ -385,13 +394,13 @@ int ubr_argmax_classes(const float* logp, int n, int ncls, int hw, uint8_t* clas
   return 0;
 }
 
-int ubr_stitch_scatter_u8(const uint8_t* tiles, const int32_t* origins, int ntiles, int crop, int rows, int cols, int fill,
-                          uint8_t* out, void* stream) {
+int ubr_stitch_scatter_u8(const uint8_t* tiles, const int32_t* origins, int ntiles, int crop_h, int crop_w, int rows, int cols,
+                          int fill, uint8_t* out, void* stream) {
   if (int rc = ensure_device()) return rc;
   UBR_REQUIRE(tiles && origins && out, "stitch_scatter_u8: null pointer");
-  UBR_REQUIRE(rows > 0 && cols > 0 && ntiles > 0 && crop > 0, "stitch_scatter_u8: bad sizes");
-  stitch_scatter_u8_kernel<<<blocks_for((long)rows * cols), 256, 0, (cudaStream_t)stream>>>(tiles, origins, ntiles, crop,
-                                                                                            rows, cols, fill, out);
+  UBR_REQUIRE(rows > 0 && cols > 0 && ntiles > 0 && crop_h > 0 && crop_w > 0, "stitch_scatter_u8: bad sizes");
+  stitch_scatter_u8_kernel<<<blocks_for((long)rows * cols), 256, 0, (cudaStream_t)stream>>>(tiles, origins, ntiles, crop_h,
+                                                                                            crop_w, rows, cols, fill, out);
   UBR_LAUNCH_CHECK("stitch_scatter_u8_kernel");
   return 0;
 }

@@ -35,7 +35,7 @@ def _origins(plan, device):
 
 
 def gather(plane, plan, crop=512):
-    """plane (rows, cols) fp32 CUDA -> (ntiles, 1, crop, crop)."""
+    """plane (rows, cols) fp32 CUDA -> (ntiles, 1, crop, crop); crop may be (crop_h, crop_w)."""
     return ops.tile_gather(plane.contiguous(), _origins(plan, plane.device), crop)
 
 
@@ -87,6 +87,28 @@ def run_event_classes(model, planes, crop=512, batch=None, out=None):
         out = torch.empty((nplanes, rows, cols), dtype=torch.uint8, device=dev)
     for p in range(nplanes):
         stitch_classes(cls[p * per_plane:(p + 1) * per_plane], plan, rows, cols, out=out[p])
+    return out
+
+
+@torch.no_grad()
+def run_event_classes_3d(model, planes, box=(512, 832), covered_z=310, batch=None):
+    """Whole-view deploy on the 3D-consistent crop sets of deploy/run_ubresnet_wholeview.py:33-47 (512 x 832 boxes, one
+    per plane and z slab, `crop_geometry.split_detector`): planes (3, rows, cols) in U, V, Y order -> (3, rows, cols)
+    uint8 class maps.  Pixels no box covers (U/V wires beyond the planes' 2400) stay 0."""
+    from . import crop_geometry
+    dev = next(model.parameters()).device
+    planes = planes.to(dev, non_blocking=True).float()
+    nplanes, rows, cols = planes.shape
+    plans = crop_geometry.plane_plans(crop_geometry.split_detector(rows, cols, box[0], box[1], covered_z))[:nplanes]
+    crops = torch.cat([gather(planes[p], plans[p], box) for p in range(nplanes)], 0)
+    per_plane = len(plans[0])
+    batch = batch or crops.shape[0]
+    cls = torch.empty((crops.shape[0], box[0], box[1]), dtype=torch.uint8, device=dev)
+    for i in range(0, crops.shape[0], batch):
+        ops.argmax_classes(model(crops[i:i + batch]), out=cls[i:i + batch])
+    out = torch.empty((nplanes, rows, cols), dtype=torch.uint8, device=dev)
+    for p in range(nplanes):
+        stitch_classes(cls[p * per_plane:(p + 1) * per_plane], plans[p], rows, cols, out=out[p])
     return out
 
 

@@ -538,23 +538,25 @@ def accuracy_counts(logp, target):
 
 
 def tile_gather(plane, origins, crop):
+    """crop: int (square) or (crop_h, crop_w)"""
     lib = _lib.load()
     require_cuda(plane, "plane")
     rows, cols = plane.shape
     nt = origins.shape[0]
-    crops = torch.empty((nt, 1, crop, crop), dtype=torch.float32, device=plane.device)
-    _lib.check(lib.ubr_tile_gather(plane.data_ptr(), rows, cols, origins.data_ptr(), nt, crop, crops.data_ptr(),
-                                   _stream()), "tile_gather")
+    ch, cw = (crop, crop) if isinstance(crop, int) else crop
+    crops = torch.empty((nt, 1, ch, cw), dtype=torch.float32, device=plane.device)
+    _lib.check(lib.ubr_tile_gather_rect(plane.data_ptr(), rows, cols, origins.data_ptr(), nt, ch, cw, crops.data_ptr(),
+                                        _stream()), "tile_gather")
     return crops
 
 
 def stitch_scatter(tiles, origins, rows, cols):
     lib = _lib.load()
     require_cuda(tiles, "tiles")
-    nt, nch, crop, _ = tiles.shape
+    nt, nch, ch, cw = tiles.shape
     out = torch.empty((nch, rows, cols), dtype=torch.float32, device=tiles.device)
-    _lib.check(lib.ubr_stitch_scatter(tiles.data_ptr(), nch, origins.data_ptr(), nt, crop, rows, cols, out.data_ptr(),
-                                      _stream()), "stitch_scatter")
+    _lib.check(lib.ubr_stitch_scatter_rect(tiles.data_ptr(), nch, origins.data_ptr(), nt, ch, cw, rows, cols, out.data_ptr(),
+                                           _stream()), "stitch_scatter")
     return out
 
 
@@ -574,11 +576,11 @@ def stitch_scatter_u8(tiles, origins, rows, cols, fill=0, out=None):
     """(ntiles, crop, crop) uint8 class tiles -> (rows, cols) uint8"""
     lib = _lib.load()
     require_cuda(tiles, "tiles")
-    nt, crop, _ = tiles.shape
+    nt, ch, cw = tiles.shape
     assert tiles.dtype == torch.uint8 and tiles.is_contiguous()
     if out is None:
         out = torch.empty((rows, cols), dtype=torch.uint8, device=tiles.device)
-    _lib.check(lib.ubr_stitch_scatter_u8(tiles.data_ptr(), origins.data_ptr(), nt, crop, rows, cols, int(fill),
+    _lib.check(lib.ubr_stitch_scatter_u8(tiles.data_ptr(), origins.data_ptr(), nt, ch, cw, rows, cols, int(fill),
                                          out.data_ptr(), _stream()), "stitch_scatter_u8")
     return out
 
