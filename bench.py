@@ -361,7 +361,32 @@ def run_own(args, rank, world, local_rank):
         img, lab, wgt = synthetic.make_batch(B, S, S, rank=rank, step=i)
         host.append((img.pin_memory(), lab.pin_memory(), wgt.pin_memory()))
     resident = [(a.to(dev), b.to(dev), c.to(dev)) for a, b, c in host]
-    h2d_bytes = sum(t.numel() * t.element_size() for t in host[0])
+    # e2e wire format (ubresnet_b200/fill.py): what the reference's fillers read from the larcv file --
+    # column-major fp32 ADC planes and 1-byte ROI-type label planes; the transpose, the ROI->class table with the -1
+    # shift and the SegWeightTrackShower pixel weights are computed on the device
+    from ubresnet_b200.fill import DeviceBatchFiller
+    filler = DeviceBatchFiller(dev)
+    wire = []
+    for img, lab, _ in host:
+        roi = torch.zeros_like(lab, dtype=torch.uint8)
+        roi[lab == 1] = 6                        # kROIMuminus (track)
+        roi[lab == 2] = 3                        # kROIEminus  (shower)
+        wire.append((img[:, 0].transpose(1, 2).contiguous().view(B, -1).pin_memory(),
+                     roi.transpose(1, 2).contiguous().view(B, -1).pin_memory()))
+    h2d_bytes = sum(t.numel() * t.element_size() for t in wire[0])
+    fi, fl, fw = filler.fill(wire[0][0], wire[0][1], S, S, check=True)
+    fill_ok = bool(torch.equal(fi, resident[0][0]) and torch.equal(fl, resident[0][1]) and torch.equal(fw, resident[0][2]))
+    del fi, fl, fw
+    dw0 = tuple(t.to(dev) for t in wire[0])
+    torch.cuda.synchronize()
+    ef0, ef1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ef0.record()
+    for _ in range(5):
+        filler.fill(dw0[0], dw0[1], S, S)
+    ef1.record()
+    torch.cuda.synchronize()
+    fill_ms = ef0.elapsed_time(ef1) / 5
+    del dw0
 
     def step_resident(i):
         img, lab, wgt = resident[i % nbuf]
@@ -381,17 +406,36 @@ def run_own(args, rank, world, local_rank):
             yield host[i % nbuf]
             i += 1
 
+    def wire_batches():
+        i = 0
+        while True:
+            yield wire[i % nbuf]
+            i += 1
+
     feed = {}
+    # the loss of EVERY step is copied device -> host inside the timed region, asynchronously into pinned memory, and
+    # read by the host one step later (the last one after the final synchronize): the copy never drains the GPU queue
+    loss_host = [torch.zeros((), dtype=torch.float32).pin_memory() for _ in range(2)]
+    loss_ready = [None, None]
+    losses_seen = []
 
     def step_e2e(i):
         if "it" not in feed:
-            feed["it"] = DevicePrefetcher(host_batches(), dev)
-        img, lab, wgt = next(feed["it"])
+            feed["it"] = DevicePrefetcher(wire_batches(), dev)
+        planes, rois = next(feed["it"])
+        img, lab, wgt = filler.fill(planes, rois, S, S)
         opt.zero_grad(set_to_none=True)
         loss = crit(net(img), lab, wgt)
         loss.backward()
         opt.step()
-        return float(loss.item())            # device -> host read of the step's result
+        j = i & 1
+        loss_host[j].copy_(loss.detach(), non_blocking=True)          # device -> host read of the step's result
+        loss_ready[j] = torch.cuda.Event()
+        loss_ready[j].record()
+        if loss_ready[j ^ 1] is not None:
+            loss_ready[j ^ 1].synchronize()                           # previous step's loss: already on the host
+            losses_seen.append(float(loss_host[j ^ 1]))
+        return None
 
     def barrier():
         if world > 1:
@@ -589,7 +633,13 @@ def run_own(args, rank, world, local_rank):
                        "l2": "per-step working set (>8 GB) >> 126 MB L2; no flush needed"},
             "clocks": clocks,
             "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": h2d_bytes * world, "d2h_bytes_per_step": 4 * world,
-                    "ms_per_step": ms_e2e / args.steps},
+                    "ms_per_step": ms_e2e / args.steps,
+                    "input": "pinned host larcv-style planes (column-major fp32 ADC + uint8 ROI-type labels) -> device "
+                             "batch assembly (ubresnet_b200.fill: transpose, ROI->class LUT -1, SegWeightTrackShower "
+                             "weights) -> train step -> loss.item()",
+                    "loss_readback": "every step's loss copied D2H (pinned, non_blocking) and consumed by the host one step "
+                                     "later; %d losses read inside the timed loop" % len(losses_seen),
+                    "device_fill_equals_host_batch": fill_ok, "device_fill_ms_per_batch": fill_ms},
             "gpu_launches": int(launches),
             "utilisation": {"conv_tflops_whole_step": GF_TRAIN * B * world * args.steps / (ms * 1e-3) / 1e3 / world,
                             "note": "algorithmic conv FLOPs (199.41 GF/crop) / step time, per GPU"},

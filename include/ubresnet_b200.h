@@ -327,7 +327,9 @@ int ubr_f32_logsoftmax_bwd(const float* logp, const float* dlogp, int n, int ncl
 int ubr_fill_image_batch(const void* src, int src_dtype, int batch, int rows, int cols, const uint8_t* mirror, float* out,
                          void* stream);
 int ubr_fill_label_batch(const void* src, int src_dtype, int batch, int rows, int cols, const uint8_t* mirror,
-                         const uint8_t* lut, int lut_size, int shift, int64_t* out, int* invalid_count, void* stream);
+                         const uint8_t* lut, int lut_size, int shift, int64_t* out, uint8_t* out_class_u8 /* optional:
+                         the pre-shift class per pixel, row-major, 1 byte -- the cheap input of ubr_seg_weights */,
+                         int* invalid_count, void* stream);
 uint64_t ubr_seg_weights_workspace_bytes(int batch, int rows, int cols);
 int ubr_seg_weights(const void* label, int label_dtype, int column_major, int batch, int rows, int cols,
                     const uint8_t* cat_lut, int lut_size, int dist_surrounding, int weight_surrounding, int pool_type,

@@ -82,7 +82,7 @@ SIGNATURES = {
     "ubr_accuracy_counts": (_i, [_vp, _vp, _i, _i, _i, _vp, _vp]),
     "ubr_scale_f32": (_i, [_vp, _u64, _f, _vp]),
     "ubr_fill_image_batch": (_i, [_vp, _i, _i, _i, _i, _vp, _vp, _vp]),
-    "ubr_fill_label_batch": (_i, [_vp, _i, _i, _i, _i, _vp, _vp, _i, _i, _vp, _vp, _vp]),
+    "ubr_fill_label_batch": (_i, [_vp, _i, _i, _i, _i, _vp, _vp, _i, _i, _vp, _vp, _vp, _vp]),
     "ubr_seg_weights_workspace_bytes": (_u64, [_i, _i, _i]),
     "ubr_seg_weights": (_i, [_vp, _i, _i, _i, _i, _i, _vp, _i, _i, _i, _i, _f, _vp, _vp, _vp, _u64, _vp]),
     "ubr_f32_conv2d_fwd": (_i, [View, _vp, _vp, _i, _i, _i, _i, _i, View, _vp]),

@@ -51,13 +51,14 @@ template <typename T>
 __global__ void __launch_bounds__(256) fill_label_kernel(const T* __restrict__ in, int rows, int cols,
                                                          const uint8_t* __restrict__ mirror, const uint8_t* __restrict__ lut,
                                                          int lut_size, int shift, long long* __restrict__ out,
-                                                         int* __restrict__ bad) {
+                                                         uint8_t* __restrict__ out_cls, int* __restrict__ bad) {
   __shared__ long long tile[32][33];
   const int b = blockIdx.z;
   const bool mir = mirror && mirror[b];
   const int r0 = blockIdx.x * 32, c0 = blockIdx.y * 32;
   const T* src = in + (size_t)b * rows * cols;
   long long* dst = out + (size_t)b * rows * cols;
+  uint8_t* dst8 = out_cls ? out_cls + (size_t)b * rows * cols : nullptr;
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
   for (int j = ty; j < 32; j += 8) {
     const int row = r0 + tx, col = c0 + j;
@@ -68,13 +69,17 @@ __global__ void __launch_bounds__(256) fill_label_kernel(const T* __restrict__ i
       uint8_t cls = 0xFF;
       if (t >= 0 && t < lut_size) cls = lut[t];
       if (cls == 0xFF) { atomicAdd(bad, 1); cls = 0; }
-      tile[j][tx] = (long long)cls + shift;
+      tile[j][tx] = (long long)cls;
     }
   }
   __syncthreads();
   for (int j = ty; j < 32; j += 8) {
     const int row = r0 + j, col = c0 + tx;
-    if (row < rows && col < cols) dst[(size_t)row * cols + col] = tile[tx][j];
+    if (row < rows && col < cols) {
+      const long long cls = tile[tx][j];
+      dst[(size_t)row * cols + col] = cls + shift;
+      if (dst8) dst8[(size_t)row * cols + col] = (uint8_t)cls;    // pre-shift class, 1 byte: input of the weight maker
+    }
   }
 }
 
@@ -176,7 +181,8 @@ int ubr_fill_image_batch(const void* src, int src_dtype, int batch, int rows, in
 }
 
 int ubr_fill_label_batch(const void* src, int src_dtype, int batch, int rows, int cols, const uint8_t* mirror,
-                         const uint8_t* lut, int lut_size, int shift, int64_t* out, int* invalid_count, void* stream) {
+                         const uint8_t* lut, int lut_size, int shift, int64_t* out, uint8_t* out_class_u8, int* invalid_count,
+                         void* stream) {
   if (int rc = ensure_device()) return rc;
   UBR_REQUIRE(src && out && lut && invalid_count && batch > 0 && rows > 0 && cols > 0 && lut_size > 0,
               "fill_label_batch: bad arguments");
@@ -185,10 +191,10 @@ int ubr_fill_label_batch(const void* src, int src_dtype, int batch, int rows, in
   dim3 grid((unsigned)ceil_div(rows, 32), (unsigned)ceil_div(cols, 32), (unsigned)batch);
   if (src_dtype == 0)
     fill_label_kernel<float><<<grid, 256, 0, st>>>((const float*)src, rows, cols, mirror, lut, lut_size, shift,
-                                                   (long long*)out, invalid_count);
+                                                   (long long*)out, out_class_u8, invalid_count);
   else if (src_dtype == 2)
     fill_label_kernel<uint8_t><<<grid, 256, 0, st>>>((const uint8_t*)src, rows, cols, mirror, lut, lut_size, shift,
-                                                     (long long*)out, invalid_count);
+                                                     (long long*)out, out_class_u8, invalid_count);
   else { set_error("fill_label_batch: src_dtype %d (0 f32, 2 u8)", src_dtype); return UBR_E_BADARG; }
   UBR_LAUNCH_CHECK("fill_label_kernel");
   return 0;

@@ -28,6 +28,7 @@ struct ConvGemmParams {
   CUtensorMap b_map;
   CUtensorMap o_map;
   int ntaps, nkc, kc, nt, stages;
+  int mt, ntiles;               // pixel sub-tiles per CTA (1 or 2, sharing every weight stage) / total 128-pixel tiles
   int tiles_w, tiles_h, bw, bh, bn;
   uint32_t a_bytes, b_bytes, a_stride, b_stride;
   uint32_t idesc, tmem_cols;
@@ -49,8 +50,8 @@ __global__ void __launch_bounds__(kThreads, 1) conv_gemm_kernel(const __grid_con
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   // dynamic smem base is not guaranteed 1024-aligned: align by hand (host adds 1024 slack)
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
-  const uint32_t stage_bytes = p.a_stride + p.b_stride;
-  const uint32_t staging_bytes = 128u * (uint32_t)p.nt * 2u;
+  const uint32_t stage_bytes = (uint32_t)p.mt * p.a_stride + p.b_stride;
+  const uint32_t staging_bytes = (uint32_t)p.mt * 128u * (uint32_t)p.nt * 2u;
   uint32_t data_bytes = (uint32_t)p.stages * stage_bytes;
   if (data_bytes < staging_bytes) data_bytes = staging_bytes;
   const uint32_t bar_base = smem_base + data_bytes;        // full[stages], empty[stages], accum, tmem ptr
@@ -63,12 +64,17 @@ __global__ void __launch_bounds__(kThreads, 1) conv_gemm_kernel(const __grid_con
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
 
-  // tile coordinates
-  const int tile = blockIdx.x;
-  const int tw = tile % p.tiles_w;
-  const int th = (tile / p.tiles_w) % p.tiles_h;
-  const int tn = tile / (p.tiles_w * p.tiles_h);
-  const int w0 = tw * p.bw, h0 = th * p.bh, n0 = tn * p.bn;
+  // tile coordinates: this CTA owns the 128-pixel tiles blockIdx.x*mt .. +mt-1 (the last CTA may own one only)
+  const int tile0 = blockIdx.x * p.mt;
+  const int nsub = (tile0 + p.mt <= p.ntiles) ? p.mt : (p.ntiles - tile0);
+  int w0s[2], h0s[2], n0s[2];
+#pragma unroll
+  for (int s = 0; s < 2; ++s) {
+    const int tile = tile0 + (s < nsub ? s : 0);
+    w0s[s] = (tile % p.tiles_w) * p.bw;
+    h0s[s] = ((tile / p.tiles_w) % p.tiles_h) * p.bh;
+    n0s[s] = (tile / (p.tiles_w * p.tiles_h)) * p.bn;
+  }
   const int co0 = blockIdx.y * p.nt;
 
   if (threadIdx.x == 0) {
@@ -100,15 +106,16 @@ __global__ void __launch_bounds__(kThreads, 1) conv_gemm_kernel(const __grid_con
       int it = 0;
       for (int t = 0; t < p.ntaps; ++t) {
         const CUtensorMap* am = &p.a_map[p.amap[t]];
-        const int cw = w0 + p.dw[t], ch = h0 + p.dh[t];
         for (int kc = 0; kc < p.nkc; ++kc, ++it) {
           const int s = it % p.stages;
           const uint32_t ph = (uint32_t)(it / p.stages) & 1u;
           mbar_wait(empty0 + 8u * s, ph ^ 1u);
           const uint32_t a_dst = smem_base + (uint32_t)s * stage_bytes;
-          const uint32_t b_dst = a_dst + p.a_stride;
-          mbar_arrive_expect_tx(full0 + 8u * s, p.a_bytes + p.b_bytes);
-          tma_load_4d(a_dst, am, full0 + 8u * s, kc * p.kc, cw, ch, n0);
+          const uint32_t b_dst = a_dst + (uint32_t)p.mt * p.a_stride;
+          mbar_arrive_expect_tx(full0 + 8u * s, (uint32_t)nsub * p.a_bytes + p.b_bytes);
+          for (int u = 0; u < nsub; ++u)
+            tma_load_4d(a_dst + (uint32_t)u * p.a_stride, am, full0 + 8u * s, kc * p.kc, w0s[u] + p.dw[t],
+                        h0s[u] + p.dh[t], n0s[u]);
           tma_load_3d(b_dst, &p.b_map, full0 + 8u * s, kc * p.kc, co0, (int)p.slab[t]);
         }
       }
@@ -126,13 +133,16 @@ __global__ void __launch_bounds__(kThreads, 1) conv_gemm_kernel(const __grid_con
         mbar_wait(full0 + 8u * s, ph);
         tc_fence_after();
         const uint32_t a_src = smem_base + (uint32_t)s * stage_bytes;
-        const uint32_t b_src = a_src + p.a_stride;
-        const uint64_t adesc = make_smem_desc(a_src, 0, sbo, layout);
+        const uint32_t b_src = a_src + (uint32_t)p.mt * p.a_stride;
         const uint64_t bdesc = make_smem_desc(b_src, 0, sbo, layout);
-        for (int k = 0; k < ksteps; ++k) {
-          // advance 16 bf16 = 32 bytes along K inside the swizzle row: +2 in the (addr>>4) field
-          tc_mma_bf16(tmem_base, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), p.idesc,
-                      (it > 0 || k > 0) ? 1u : 0u);
+        for (int u = 0; u < nsub; ++u) {
+          // every pixel sub-tile multiplies the SAME weight stage (halves the weight bytes pulled through L2 per FLOP)
+          const uint64_t adesc = make_smem_desc(a_src + (uint32_t)u * p.a_stride, 0, sbo, layout);
+          for (int k = 0; k < ksteps; ++k) {
+            // advance 16 bf16 = 32 bytes along K inside the swizzle row: +2 in the (addr>>4) field
+            tc_mma_bf16(tmem_base + (uint32_t)(u * p.nt), adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), p.idesc,
+                        (it > 0 || k > 0) ? 1u : 0u);
+          }
         }
         tc_commit(empty0 + 8u * s);          // frees the smem stage when these MMAs retire
       }
@@ -144,7 +154,10 @@ __global__ void __launch_bounds__(kThreads, 1) conv_gemm_kernel(const __grid_con
     const int row = quad * 32 + lane;        // tile-local pixel
     mbar_wait(accum_bar, 0);
     tc_fence_after();
-    const uint32_t t_row = tmem_base + ((uint32_t)(quad * 32) << 16);
+    for (int u = 0; u < nsub; ++u) {
+    const int w0 = w0s[u], h0 = h0s[u], n0 = n0s[u];
+    const uint32_t t_row = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(u * p.nt);
+    const uint32_t stage_base = smem_base + (uint32_t)u * 128u * (uint32_t)p.nt * 2u;   // own staging per sub-tile
     if (p.out_mode == 0) {
       const int bc = p.o_box_c;                         // channels per staging block
       const uint32_t rb = (uint32_t)bc * 2u;            // staging row bytes (32/64/128)
@@ -174,7 +187,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_gemm_kernel(const __grid_con
         for (int j = 0; j < 8; ++j) pk[j] = pack_bf16x2(f[2 * j], f[2 * j + 1]);
         const int blk = c / bc;
         const uint32_t q = (uint32_t)((c % bc) >> 3);   // 16-byte chunk index inside the row
-        const uint32_t base = smem_base + (uint32_t)blk * 128u * rb + (uint32_t)row * rb;
+        const uint32_t base = stage_base + (uint32_t)blk * 128u * rb + (uint32_t)row * rb;
         const uint32_t a0 = base + ((q ^ xr) << 4);
         const uint32_t a1 = base + (((q + 1u) ^ xr) << 4);
         asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a0), "r"(pk[0]), "r"(pk[1]), "r"(pk[2]), "r"(pk[3]) : "memory");
@@ -204,15 +217,16 @@ __global__ void __launch_bounds__(kThreads, 1) conv_gemm_kernel(const __grid_con
           const int k = i / p.nt, ch = i % p.nt;
           const float v = s_part[(0 * 2 + k) * p.nt + ch] + s_part[(1 * 2 + k) * p.nt + ch] +
                           s_part[(2 * 2 + k) * p.nt + ch] + s_part[(3 * 2 + k) * p.nt + ch];
-          p.stats[((size_t)blockIdx.x * 2 + k) * (size_t)p.stats_c + co0 + ch] = v;
+          p.stats[((size_t)(tile0 + u) * 2 + k) * (size_t)p.stats_c + co0 + ch] = v;
         }
+        asm volatile("bar.sync 1, 128;" ::: "memory");       // s_part is reused by the next sub-tile
       }
       if (warp == 2 && lane == 0) {
         const int nblk = p.nt / bc;
         for (int b = 0; b < nblk; ++b)
-          tma_store_4d(&p.o_map, smem_base + (uint32_t)b * 128u * rb, co0 + b * bc, w0, h0, n0);
+          tma_store_4d(&p.o_map, stage_base + (uint32_t)b * 128u * rb, co0 + b * bc, w0, h0, n0);
         tma_store_commit();
-        tma_store_wait_all();
+        if (u == nsub - 1) tma_store_wait_all();
       }
     } else {
       // fp32 direct store (network logits): few valid columns, pixel-major rows
@@ -233,6 +247,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_gemm_kernel(const __grid_con
         }
       }
     }
+    }   // sub-tiles
   }
 
   tc_fence_before();
@@ -293,6 +308,11 @@ static int make_phase_map(CUtensorMap* m, const ubr_view& v, int ph, int pw, int
 // output-channel tile: 128 where it divides N, else 64 (192/320/576-channel ASPP concat gradients), else all of N
 static int pick_nt(int n_pad) { return (n_pad % 128 == 0) ? 128 : ((n_pad % 64 == 0) ? 64 : n_pad); }
 
+static int env_int(const char* name, int dflt) {
+  const char* v = getenv(name);
+  return (v && *v) ? atoi(v) : dflt;
+}
+
 // generic launcher. `grid_view` = (n, h, w) of the output tile grid; a_maps built by caller.
 static int launch_conv_gemm(ConvGemmParams& p, int grid_n, int grid_h, int grid_w, TileShape t, int k_ch,
                             int n_pad, const void* wpk, int nslabs, const TapSpec* taps, int ntaps,
@@ -305,6 +325,16 @@ static int launch_conv_gemm(ConvGemmParams& p, int grid_n, int grid_h, int grid_
   p.nkc = k_ch / p.kc;
   p.nt = pick_nt(n_pad);
   UBR_REQUIRE(p.nt <= 128 && n_pad % p.nt == 0, "conv_gemm: N=%d not a multiple of tile %d", n_pad, p.nt);
+  // Tile shape per CTA: mt pixel sub-tiles of 128 x nt channels.  The kernel is bound by the bytes it pulls through L2
+  // per FLOP (a 128x128 tile streams 32 KB per 2.1 MFLOP k-step = 64 FLOP/B); two pixel sub-tiles sharing one weight
+  // stage give 87 FLOP/B.  Used when it still leaves a full wave of CTAs.
+  const int tiles_total = ceil_div(grid_w, t.bw) * ceil_div(grid_h, t.bh) * ceil_div(grid_n, t.bn);
+  const int sms = sm_count();
+  static const int force_mt = env_int("UBR_GEMM_MT", 0);
+  p.mt = 1;
+  if (p.out_mode == 0 && (tiles_total / 2) * (n_pad / p.nt) >= sms) p.mt = 2;
+  if (force_mt == 1 || force_mt == 2) p.mt = force_mt;
+  p.ntiles = tiles_total;
   p.ntaps = ntaps;
   for (int i = 0; i < ntaps; ++i) {
     p.dh[i] = (int8_t)taps[i].dh; p.dw[i] = (int8_t)taps[i].dw;
@@ -318,15 +348,16 @@ static int launch_conv_gemm(ConvGemmParams& p, int grid_n, int grid_h, int grid_
   p.b_bytes = (uint32_t)p.nt * p.kc * 2u;
   p.a_stride = (p.a_bytes + 1023u) & ~1023u;
   p.b_stride = (p.b_bytes + 1023u) & ~1023u;
-  const uint32_t stage = p.a_stride + p.b_stride;
-  int stages = (int)(98304u / stage);
+  const uint32_t stage = (uint32_t)p.mt * p.a_stride + p.b_stride;
+  static const uint32_t smem_budget = (uint32_t)env_int("UBR_GEMM_SMEM_KB", 96) * 1024u;
+  int stages = (int)(smem_budget / stage);
   if (stages > 8) stages = 8;
   if (stages < 2) stages = 2;
   if (stages > ntaps * p.nkc) stages = ntaps * p.nkc;
   p.stages = stages;
   p.idesc = make_idesc_bf16(128, p.nt, 0, 0);
   uint32_t cols = 32;
-  while ((int)cols < p.nt) cols <<= 1;
+  while ((int)cols < p.mt * p.nt) cols <<= 1;
   p.tmem_cols = cols;
   // weights: (K, N, slab) 3-D map, box {kc, nt, 1}
   {
@@ -337,7 +368,7 @@ static int launch_conv_gemm(ConvGemmParams& p, int grid_n, int grid_h, int grid_
     if (rc) return rc;
   }
   uint32_t data = (uint32_t)stages * stage;
-  const uint32_t staging = 128u * p.nt * 2u;
+  const uint32_t staging = (uint32_t)p.mt * 128u * p.nt * 2u;
   if (data < staging) data = staging;
   const uint32_t smem = data + 16u * stages + 16u + 1024u + 4096u + 16u;      // + [4][2][nt] fp32 statistics scratch
   static bool attr_set[64] = {};             // the opt-in is per device
@@ -347,7 +378,7 @@ static int launch_conv_gemm(ConvGemmParams& p, int grid_n, int grid_h, int grid_
     UBR_CUDA_OK(cudaFuncSetAttribute(conv_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     attr_set[dev_id & 63] = true;
   }
-  dim3 grid((unsigned)(p.tiles_w * p.tiles_h * tiles_n), (unsigned)(n_pad / p.nt), 1);
+  dim3 grid((unsigned)ceil_div(p.tiles_w * p.tiles_h * tiles_n, p.mt), (unsigned)(n_pad / p.nt), 1);
   conv_gemm_kernel<<<grid, kThreads, smem, stream>>>(p);
   UBR_LAUNCH_CHECK("conv_gemm_kernel");
   return 0;

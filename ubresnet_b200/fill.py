@@ -41,14 +41,14 @@ class DeviceBatchFiller:
         self.device = torch.device(device)
         self.lut = torch.tensor(roitype_to_class(class_type_list, class_type_def), dtype=torch.uint8, device=self.device)
         self.shift = int(label_shift)
-        # weights are made from the FILLED labels (classes after the shift: 1 track, 2 shower -- ClassTypeDef's groups)
+        # weights are made from the FILLED class image (1 byte per pixel, mirrored like the image): class -> 1 shower /
+        # 2 track for the classes the shower / track ROI types map to (ClassTypeDef's groups)
         cat = [0] * 16
         for roi, cls in enumerate(roitype_to_class(class_type_list, class_type_def)):
-            c = cls + self.shift
-            if roi in (3, 4, 5) and 0 <= c < 16:
-                cat[c] = 1
-            if roi in (6, 7, 8, 9) and 0 <= c < 16:
-                cat[c] = 2
+            if roi in (3, 4, 5) and cls < 16:
+                cat[cls] = 1
+            if roi in (6, 7, 8, 9) and cls < 16:
+                cat[cls] = 2
         self.cat_lut = torch.tensor(cat, dtype=torch.uint8, device=self.device)
         self.dist, self.wsurr, self.pool, self.wmax = int(dist_surrounding), int(bool(weight_surrounding)), int(pool_type), float(weight_max)
         self._bad = torch.zeros(1, dtype=torch.int32, device=self.device)
@@ -67,15 +67,16 @@ class DeviceBatchFiller:
         out_img = torch.empty((b, 1, rows, cols), dtype=torch.float32, device=self.device)
         out_lab = torch.empty((b, rows, cols), dtype=torch.int64, device=self.device)
         out_w = torch.empty((b, rows, cols), dtype=torch.float32, device=self.device)
+        cls8 = torch.empty((b, rows, cols), dtype=torch.uint8, device=self.device)
         _lib.check(lib.ubr_fill_image_batch(img.contiguous().data_ptr(), _DTYPE_CODE[img.dtype], b, rows, cols, _ptr(mir),
                                             out_img.data_ptr(), _stream()), "fill_image_batch")
         _lib.check(lib.ubr_fill_label_batch(lab.contiguous().data_ptr(), _DTYPE_CODE[lab.dtype], b, rows, cols, _ptr(mir),
                                             self.lut.data_ptr(), self.lut.numel(), self.shift, out_lab.data_ptr(),
-                                            self._bad.data_ptr(), _stream()), "fill_label_batch")
+                                            cls8.data_ptr(), self._bad.data_ptr(), _stream()), "fill_label_batch")
         need = int(lib.ubr_seg_weights_workspace_bytes(b, rows, cols))
         if self._ws is None or self._ws.numel() < need:
             self._ws = torch.empty(need, dtype=torch.uint8, device=self.device)
-        _lib.check(lib.ubr_seg_weights(out_lab.data_ptr(), 3, 0, b, rows, cols, self.cat_lut.data_ptr(), self.cat_lut.numel(),
+        _lib.check(lib.ubr_seg_weights(cls8.data_ptr(), 2, 0, b, rows, cols, self.cat_lut.data_ptr(), self.cat_lut.numel(),
                                        self.dist, self.wsurr, self.pool, self.wmax, 0, out_w.data_ptr(), self._ws.data_ptr(),
                                        self._ws.numel(), _stream()), "seg_weights")
         if check and int(self._bad.item()):          # one host sync; the C++ filler throws on the first bad pixel
