@@ -442,6 +442,8 @@ def run_own(args, rank, world, local_rank):
             dist.barrier()
         torch.cuda.synchronize()
 
+    host_ms = [0.0]
+
     def timed(fn, steps, warmup):
         for i in range(warmup):
             fn(i)
@@ -449,8 +451,10 @@ def run_own(args, rank, world, local_rank):
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         n0 = lib.ubr_launch_count()
         e0.record()
+        t_host = time.perf_counter()
         for i in range(steps):
             fn(warmup + i)
+        host_ms[0] = (time.perf_counter() - t_host) * 1e3 / steps      # host time to ENQUEUE one step (no sync inside)
         e1.record()
         barrier()
         ms = e0.elapsed_time(e1)
@@ -465,6 +469,7 @@ def run_own(args, rank, world, local_rank):
     if sampler:
         sampler.start()
     ms, launches = timed(step_resident, args.steps, args.warmup)
+    host_enqueue_ms = host_ms[0]
     clocks = sampler.stop() if sampler else None
     ms_e2e, _ = timed(step_e2e, args.steps, 1)
     value = world * B * args.steps / (ms * 1e-3)
@@ -641,6 +646,7 @@ def run_own(args, rank, world, local_rank):
                                      "later; %d losses read inside the timed loop" % len(losses_seen),
                     "device_fill_equals_host_batch": fill_ok, "device_fill_ms_per_batch": fill_ms},
             "gpu_launches": int(launches),
+            "host_enqueue_ms_per_step": host_enqueue_ms,
             "utilisation": {"conv_tflops_whole_step": GF_TRAIN * B * world * args.steps / (ms * 1e-3) / 1e3 / world,
                             "note": "algorithmic conv FLOPs (199.41 GF/crop) / step time, per GPU"},
         }

@@ -90,6 +90,15 @@ int ubr_conv2d_dgrad(ubr_view dy, const void* wpk, int in_ch, int ksize, int str
 /* dx += conv_transpose(dy, W), fused into the epilogue (fp32 add of the stored bf16 value, one rounding).
  * Returns 1 (and does nothing) when the shape has no fused path (stride 2): the caller then adds with ubr_add. */
 int ubr_conv2d_dgrad_acc(ubr_view dy, const void* wpk, int in_ch, int ksize, int stride, ubr_view dx, void* stream);
+/* data gradient that ALSO emits the reduction pass of the BatchNorm(+ReLU) backward that consumes it
+ * (common_layers.py:41-44 in reverse: dx is the gradient wrt a = relu?(bn(y_pre))): while the epilogue holds the stored
+ * dx tile it reads y_pre and accumulates sum dz and sum dz*xhat per channel (dz = dx * [y_pre*scale+shift > 0]) into
+ * *rows partial rows of bn_workspace -- feed them to ubr_bn_act_bwd_apply_rows instead of running
+ * ubr_bn_act_bwd_reduce (one full read of dx and y_pre saved).  Returns 1 (nothing launched) when the shape has no
+ * fused path (stride 2, in_ch > 32, W %% 128 != 0): run ubr_conv2d_dgrad + ubr_bn_act_bwd_reduce/apply. */
+int ubr_conv2d_dgrad_bnreduce(ubr_view dy, const void* wpk, int in_ch, int ksize, int stride, ubr_view dx, ubr_view y_pre,
+                              const float* scale, const float* shift, const float* mean, const float* invstd, int relu,
+                              void* bn_workspace, int* rows, void* stream);
 /* weight gradient: dw[o,i,r,s] (+)= sum_pixels dy[.,o] * x[shifted,i]; fp32 OIHW.  accumulate: 0 overwrite, 1 add */
 int ubr_conv2d_wgrad(ubr_view x, ubr_view dy, int out_ch /* true rows of dw; dy.c may be padded */, int ksize,
                      int stride, float* dw, int accumulate, void* workspace, uint64_t workspace_bytes, void* stream);
@@ -168,6 +177,10 @@ int ubr_bn_act_bwd_reduce(ubr_view dout, ubr_view y, const float* scale, const f
 int ubr_bn_act_bwd_apply(ubr_view dout, ubr_view y, const float* scale, const float* shift, const float* mean,
                          const float* invstd, const float* gamma, int relu, const void* workspace, double count,
                          ubr_view dy, float* dgamma, float* dbeta, int accumulate, void* stream);
+/* pass 2 for `rows` partial rows written by a fused producer (ubr_conv2d_dgrad_bnreduce) */
+int ubr_bn_act_bwd_apply_rows(ubr_view dout, ubr_view y, const float* scale, const float* shift, const float* mean,
+                              const float* invstd, const float* gamma, int relu, const void* workspace, int rows,
+                              double count, ubr_view dy, float* dgamma, float* dbeta, int accumulate, void* stream);
 /* backward of the block tail.  du = dout*(out>0); main branch dz2 = du*(bn2(y2)>0); residual branch gets du.
  * res_is_bn=1: residual is bnpass(bypass conv) -> dres = BN backward of du wrt `res` (pre-BN conv output); the mask
  *              (out>0) is recomputed from y2 and res with the forward arithmetic and the residual affine

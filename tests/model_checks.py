@@ -608,6 +608,41 @@ def fp32_parity(batch=2, size=128, trained=True, train=True, seed=1234, num_clas
     return res, {}
 
 
+def fused_bn_reduce():
+    """ubr_conv2d_dgrad_bnreduce (BatchNorm-backward reduction in the data-gradient epilogue) against the unfused
+    sequence dgrad -> bn_act_bwd_reduce -> bn_act_bwd_apply: same da (bit-identical), same sums up to summation order"""
+    from ubresnet_b200 import ops
+    from ubresnet_b200.ops import Act
+    res = []
+    g = torch.Generator(device=DEV).manual_seed(11)
+    for (cin, cout, k, n, h, w, relu) in [(16, 16, 3, 2, 64, 128, True), (32, 32, 3, 1, 32, 256, True),
+                                          (16, 16, 7, 2, 40, 128, True), (32, 16, 3, 3, 16, 128, False)]:
+        # forward conv cin -> cout produced y_pre... here only the backward: dy has `cout` channels, da / y_pre `cin`
+        dy = Act(torch.randn(n, h, w, cout, device=DEV, generator=g).to(torch.bfloat16))
+        ypre = Act(torch.randn(n, h, w, cin, device=DEV, generator=g).to(torch.bfloat16))
+        wt = torch.randn(cout, cin, k, k, device=DEV, generator=g) * 0.1
+        wpk = ops.pack_weights(wt, False, False)
+        ws = ops.bn_workspace(max(cin, 16), DEV)
+        ws2 = ops.bn_workspace(max(cin, 16), DEV)
+        gamma = torch.rand(cin, device=DEV, generator=g) + 0.5
+        beta = torch.randn(cin, device=DEV, generator=g) * 0.3
+        st = ops.bn_train_stats(ypre, gamma, beta, None, None, ws)
+        dg_a, db_a = torch.empty(cin, device=DEV), torch.empty(cin, device=DEV)
+        dg_b, db_b = torch.empty(cin, device=DEV), torch.empty(cin, device=DEV)
+        n0 = ops._lib.load().ubr_launch_count()
+        fused = ops.conv2d_dgrad_bn_bwd(dy, wpk, cin, k, 1, ypre, st, relu, ws, dg_a, db_a)
+        launches = ops._lib.load().ubr_launch_count() - n0
+        da = ops.conv2d_dgrad(dy, wpk, cin, k, 1)
+        ref = ops.bn_act_bwd(da, ypre, st, relu, ws2, dg_b, db_b)
+        torch.cuda.synchronize()
+        tag = "k%d %d->%d %dx%dx%d relu=%d" % (k, cout, cin, n, h, w, relu)
+        res.append((tag + " fused path taken (3 launches)", 0.0 if launches == 3 else 1.0, 0.0))
+        res.append((tag + " dy_pre", _rel(fused.torch(), ref.torch()), 1e-2))
+        res.append((tag + " dgamma", _rel(dg_a, dg_b), 1e-4))
+        res.append((tag + " dbeta", _rel(db_a, db_b), 1e-4))
+    return res, {}
+
+
 CHECKS = {
     "train_128": lambda: train_parity(2, 128),
     "train_dense_64": lambda: train_parity(4, 64, dense=True, seed=99),
@@ -621,6 +656,7 @@ CHECKS = {
     "eval_inplanes32_128": lambda: eval_parity(2, 128, inplanes=32, seed=80),
     "golden": lambda: golden_parity(),
     "advice_regressions": lambda: advice_regressions(),
+    "fused_bn_reduce": lambda: fused_bn_reduce(),
     # fp32 precision mode: 1e-4 against the fp32 oracle
     "fp32_ops": lambda: fp32_ops(),
     "fp32_train_128_trained": lambda: fp32_parity(2, 128, trained=True, train=True),

@@ -32,6 +32,8 @@ SIGNATURES = {
     "ubr_conv2d_fwd_fused": (_i, [View, _vp, _vp, _i, _i, _i, _i, View, _i, View, _vp]),
     "ubr_conv2d_fwd_stats": (_i, [View, _vp, _vp, _i, _i, _i, View, _vp, _vp, _vp]),
     "ubr_conv2d_dgrad": (_i, [View, _vp, _i, _i, _i, View, _vp]),
+    "ubr_conv2d_dgrad_bnreduce": (_i, [View, _vp, _i, _i, _i, View, View, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp]),
+    "ubr_bn_act_bwd_apply_rows": (_i, [View, View, _vp, _vp, _vp, _vp, _vp, _i, _vp, _i, _d, View, _vp, _vp, _i, _vp]),
     "ubr_conv2d_dgrad_acc": (_i, [View, _vp, _i, _i, _i, View, _vp]),
     "ubr_conv2d_wgrad": (_i, [View, View, _i, _i, _i, _vp, _i, _vp, _u64, _vp]),
     "ubr_wgrad_workspace_bytes": (_u64, [_i, _i, _i, _i, _i, _i]),

@@ -19,8 +19,37 @@ int cuda_fail(cudaError_t e, const char* what);      // records + returns UBR_E_
   do { if (!(cond)) { ::ubr::set_error(__VA_ARGS__); return UBR_E_BADARG; } } while (0)
 #define UBR_LAUNCH_CHECK(name)                                         \
   do { ::ubr::count_launch(name); cudaError_t _e = cudaGetLastError();     \
+       if (_e == cudaSuccess) _e = ::ubr::take_launch_error();             \
        if (_e != cudaSuccess) return ::ubr::cuda_fail(_e, name); } while (0)
 void count_launch(const char* name);          // every kernel launch of this library is counted (ubr_launch_count)
+
+// ------------------------------------------------------------------ kernel launches (programmatic dependent launch)
+// Every hot kernel of the library is launched with the programmatic-stream-serialization attribute and starts with
+//   griddepcontrol.launch_dependents   (the NEXT kernel of the stream may be scheduled as soon as every CTA of this one
+//                                       has started: its launch latency, barrier / TMEM set-up and tensor-map prefetch
+//                                       overlap this kernel's tail)
+//   griddepcontrol.wait                (placed before the first access to global memory: blocks until the previous
+//                                       kernel has completed and flushed, i.e. plain stream order for all data)
+// The ~500 launches of a training step are each a few tens of microseconds long; UBR_PDL=0 restores plain launches.
+bool pdl_enabled();
+cudaError_t take_launch_error();
+void note_launch_error(cudaError_t e);
+struct Launch {
+  cudaLaunchConfig_t cfg;
+  Launch(dim3 grid, dim3 block, size_t smem = 0, cudaStream_t stream = 0) {
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = stream;
+    cfg.attrs = nullptr; cfg.numAttrs = 0;
+  }
+  template <typename... P, typename... A>
+  void operator()(void (*kernel)(P...), A&&... args) {
+    cudaLaunchAttribute at;
+    at.id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at.val.programmaticStreamSerializationAllowed = 1;
+    if (pdl_enabled()) { cfg.attrs = &at; cfg.numAttrs = 1; }
+    const cudaError_t e = cudaLaunchKernelEx(&cfg, kernel, static_cast<P>(args)...);
+    if (e != cudaSuccess) note_launch_error(e);
+  }
+};
 
 int ensure_device();            // 0 if current device is sm_100; else UBR_E_UNSUPPORTED
 int sm_count();
@@ -34,6 +63,11 @@ static inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 
 // ------------------------------------------------------------------ device helpers
 #ifdef __CUDACC__
+
+// programmatic dependent launch (see ubr::Launch): both are no-ops for a kernel launched without the attribute
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_prologue() { pdl_launch_dependents(); pdl_wait(); }
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return static_cast<uint32_t>(__cvta_generic_to_shared(p));

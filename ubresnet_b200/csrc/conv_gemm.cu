@@ -47,6 +47,7 @@ struct ConvGemmParams {
 };
 
 __global__ void __launch_bounds__(kThreads, 1) conv_gemm_kernel(const __grid_constant__ ConvGemmParams p) {
+  pdl_launch_dependents();
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   // dynamic smem base is not guaranteed 1024-aligned: align by hand (host adds 1024 slack)
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -97,6 +98,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_gemm_kernel(const __grid_con
   tc_fence_after();
   uint32_t tmem_base;
   asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
+  pdl_wait();                    // barriers, TMEM and tensor maps are set up; the operands belong to earlier kernels
 
   const int total_iters = p.ntaps * p.nkc;
 
@@ -379,7 +381,7 @@ static int launch_conv_gemm(ConvGemmParams& p, int grid_n, int grid_h, int grid_
     attr_set[dev_id & 63] = true;
   }
   dim3 grid((unsigned)ceil_div(p.tiles_w * p.tiles_h * tiles_n, p.mt), (unsigned)(n_pad / p.nt), 1);
-  conv_gemm_kernel<<<grid, kThreads, smem, stream>>>(p);
+  ::ubr::Launch(grid, kThreads, smem, stream)(conv_gemm_kernel, p);
   UBR_LAUNCH_CHECK("conv_gemm_kernel");
   return 0;
 }
@@ -498,7 +500,19 @@ static int conv2d_fwd_impl(ubr_view x, const void* wpk, const float* bias, int o
 }
 
 static int conv2d_dgrad_impl(ubr_view dy, const void* wpk, int in_ch, int ksize, int stride, ubr_view dx, int accumulate,
-                             void* stream);
+                             void* stream, const BnReduce* bnr = nullptr, float* stats = nullptr, int* stats_rows = nullptr);
+
+int ubr_conv2d_dgrad_bnreduce(ubr_view dy, const void* wpk, int in_ch, int ksize, int stride, ubr_view dx, ubr_view y_pre,
+                              const float* scale, const float* shift, const float* mean, const float* invstd, int relu,
+                              void* bn_workspace, int* rows, void* stream) {
+  UBR_REQUIRE(bn_workspace && rows && scale && shift && mean && invstd, "conv2d_dgrad_bnreduce: null pointer");
+  if (stride != 1) return 1;
+  UBR_REQUIRE(y_pre.ptr && y_pre.n == dx.n && y_pre.h == dx.h && y_pre.w == dx.w && y_pre.c == in_ch && y_pre.ld % 8 == 0 &&
+                  ((uintptr_t)y_pre.ptr & 15) == 0,
+              "conv2d_dgrad_bnreduce: y_pre must match dx (n,h,w,c) with 16-byte aligned pixels");
+  BnReduce b{y_pre.ptr, y_pre.ld, relu, scale, shift, mean, invstd};
+  return conv2d_dgrad_impl(dy, wpk, in_ch, ksize, stride, dx, 0, stream, &b, (float*)bn_workspace, rows);
+}
 
 int ubr_conv2d_dgrad(ubr_view dy, const void* wpk, int in_ch, int ksize, int stride, ubr_view dx, void* stream) {
   return conv2d_dgrad_impl(dy, wpk, in_ch, ksize, stride, dx, 0, stream);
@@ -509,7 +523,7 @@ int ubr_conv2d_dgrad_acc(ubr_view dy, const void* wpk, int in_ch, int ksize, int
 }
 
 static int conv2d_dgrad_impl(ubr_view dy, const void* wpk, int in_ch, int ksize, int stride, ubr_view dx, int accumulate,
-                             void* stream) {
+                             void* stream, const BnReduce* bnr, float* stats, int* stats_rows) {
   if (int rc = ensure_device()) return rc;
   if (int rc = check_view(dy, "conv2d_dgrad.dy")) return rc;
   if (int rc = check_view(dx, "conv2d_dgrad.dx")) return rc;
@@ -532,8 +546,9 @@ static int conv2d_dgrad_impl(ubr_view dy, const void* wpk, int in_ch, int ksize,
       for (int s = 0; s < ksize; ++s) taps[nt++] = TapSpec{pad - r, pad - s, 0, r * ksize + s};
     {
       const int hrc = conv_halo_try(dy, wpk, ksize * ksize, in_ch, taps, nt, nullptr, &dx, nullptr, 0, in_ch,
-                                    (cudaStream_t)stream, accumulate);
+                                    (cudaStream_t)stream, accumulate, stats, stats_rows, 0, nullptr, bnr);
       if (hrc <= 0) return hrc;
+      if (bnr) return 1;                     // the fused reduction lives in the halo-resident epilogue only
     }
     p.out_mode = 0;
     p.o_box_c = out_box_c(pick_nt(in_ch));

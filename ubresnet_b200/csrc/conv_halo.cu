@@ -51,6 +51,10 @@ struct HaloParams {
   int fused, relu_pre, relu_post;   // out_mode 0 / 2: fused inference epilogue (FusedEpi)
   const __nv_bfloat16* res;
   int res_ld;
+  // out_mode 2 + stats: fused BatchNorm-backward reduction (BnReduce) instead of the forward statistics
+  const __nv_bfloat16* bnr_y;
+  int bnr_ld, bnr_relu;
+  const float *bnr_scale, *bnr_shift, *bnr_mean, *bnr_invstd;
 };
 
 template <int N>
@@ -82,7 +86,8 @@ __device__ __forceinline__ void mma_lohi(uint32_t d_tmem, uint32_t alo, uint32_t
 }
 
 template <int KS, int KSTEPS>
-__global__ void __launch_bounds__(kHThreads, 1) conv_halo_kernel(const __grid_constant__ HaloParams p) {
+__global__ void __launch_bounds__(kHThreads, 2) conv_halo_kernel(const __grid_constant__ HaloParams p) {
+  pdl_launch_dependents();
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t w_base = smem_base;
@@ -133,6 +138,18 @@ __global__ void __launch_bounds__(kHThreads, 1) conv_halo_kernel(const __grid_co
     const uint32_t t_q = tmem_base + ((uint32_t)((warp & 3) * 32) << 16);
     for (uint32_t c = 0; c < p.tmem_cols; c += 16) tmem_st16_zero(t_q + c);
     tmem_st_wait();
+  }
+  pdl_wait();                    // everything above touched only this CTA's shared memory / TMEM
+  // per-channel constants of the fused BatchNorm-backward reduction: [scale | shift | invstd | -mean*invstd][32]
+  float* bnr_cst = reinterpret_cast<float*>(smem_raw + (tmem_slot + 16u + 4096u - smem_u32(smem_raw)));
+  if (p.bnr_y && threadIdx.x >= 64 && threadIdx.x < 192) {
+    const int k = (threadIdx.x - 64) >> 5, ch = (threadIdx.x - 64) & 31;
+    float v = 0.f;
+    if (ch < p.nt) {
+      const int gc = co0 + ch;
+      v = k == 0 ? p.bnr_scale[gc] : k == 1 ? p.bnr_shift[gc] : k == 2 ? p.bnr_invstd[gc] : -p.bnr_mean[gc] * p.bnr_invstd[gc];
+    }
+    bnr_cst[k * 32 + ch] = v;
   }
   tc_fence_before();
   __syncthreads();
@@ -241,6 +258,21 @@ __global__ void __launch_bounds__(kHThreads, 1) conv_halo_kernel(const __grid_co
         const uint32_t r = r0 + (uint32_t)i;
         const int h = band * p.bh + i;
         const uint32_t b = r & ((uint32_t)p.nb - 1u);
+        if (p.out_mode == 2 && (p.bnr_y || p.accumulate) && i + 2 < p.bh) {
+          // the epilogue's own global reads (y of the fused BatchNorm-backward reduction, the old value of an
+          // accumulating store) sit on its serial per-row chain: pull the NEXT row of this group towards L2 now
+          const size_t npx = (size_t)((size_t)n * p.out_h + h + 2) * p.out_w + (c0 + row);
+          if (p.bnr_y) {
+            const char* a = reinterpret_cast<const char*>(p.bnr_y + npx * (size_t)p.bnr_ld + co0);
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(a));
+            if (p.nt > 16) asm volatile("prefetch.global.L2 [%0];" ::"l"(a + 32));
+          }
+          if (p.accumulate) {
+            const char* a = reinterpret_cast<const char*>(p.out_bf16 + npx * (size_t)p.out_ld + co0);
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(a));
+            if (p.nt > 16) asm volatile("prefetch.global.L2 [%0];" ::"l"(a + 32));
+          }
+        }
         mbar_wait(accf0 + 8u * b, (r >> ((uint32_t)__ffs(p.nb) - 1u)) & 1u);
         tc_fence_after();
         const uint32_t t_row = tmem_base + b * (uint32_t)p.nt + ((uint32_t)(quad * 32) << 16);
@@ -283,11 +315,35 @@ __global__ void __launch_bounds__(kHThreads, 1) conv_halo_kernel(const __grid_co
               // statistics of the STORED (bf16-rounded) values, like the stand-alone bn_stats kernel
               const uint32_t uw[8] = {u0.x, u0.y, u0.z, u0.w, u1.x, u1.y, u1.z, u1.w};
               float g[16], q[16];
+              if (p.bnr_y) {
+                // BatchNorm(+ReLU) backward sums of the stored gradient: dz = da * [y*scale+shift > 0], dz * xhat
+                const __nv_bfloat16* yp = p.bnr_y + pix * (size_t)p.bnr_ld + co0 + c;
+                const uint4 y0 = __ldg(reinterpret_cast<const uint4*>(yp));
+                const uint4 y1 = __ldg(reinterpret_cast<const uint4*>(yp + 8));
+                const uint32_t yw[8] = {y0.x, y0.y, y0.z, y0.w, y1.x, y1.y, y1.z, y1.w};
+                // constants are read pair by pair from shared memory (warp-uniform addresses: broadcast), keeping
+                // the register footprint of the epilogue below the two-CTAs-per-SM limit
 #pragma unroll
-              for (int j = 0; j < 8; ++j) {
-                const float2 t = unpack_bf16x2(uw[j]);
-                g[2 * j] = t.x; g[2 * j + 1] = t.y;
-                q[2 * j] = t.x * t.x; q[2 * j + 1] = t.y * t.y;
+                for (int j = 0; j < 8; ++j) {
+                  const float2 t = unpack_bf16x2(uw[j]);
+                  const float2 v = unpack_bf16x2(yw[j]);
+                  const float2 ksc = *reinterpret_cast<const float2*>(bnr_cst + c + 2 * j);
+                  const float2 ksh = *reinterpret_cast<const float2*>(bnr_cst + 32 + c + 2 * j);
+                  const float2 kis = *reinterpret_cast<const float2*>(bnr_cst + 64 + c + 2 * j);
+                  const float2 knb = *reinterpret_cast<const float2*>(bnr_cst + 96 + c + 2 * j);
+                  const float d0 = (!p.bnr_relu || fmaf(v.x, ksc.x, ksh.x) > 0.f) ? t.x : 0.f;
+                  const float d1 = (!p.bnr_relu || fmaf(v.y, ksc.y, ksh.y) > 0.f) ? t.y : 0.f;
+                  g[2 * j] = d0; g[2 * j + 1] = d1;
+                  q[2 * j] = d0 * fmaf(v.x, kis.x, knb.x);
+                  q[2 * j + 1] = d1 * fmaf(v.y, kis.y, knb.y);
+                }
+              } else {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                  const float2 t = unpack_bf16x2(uw[j]);
+                  g[2 * j] = t.x; g[2 * j + 1] = t.y;
+                  q[2 * j] = t.x * t.x; q[2 * j + 1] = t.y * t.y;
+                }
               }
               const float rs = warp_reduce_scatter16(g, lane), rq = warp_reduce_scatter16(q, lane);
               if (c == 0) { st_sum0 += rs; st_sq0 += rq; } else { st_sum1 += rs; st_sq1 += rq; }
@@ -453,7 +509,7 @@ static halo_kernel_t pick_halo_kernel(int ks, int ksteps) {
 int conv_halo_try(const ubr_view& x, const void* wpk, int nslabs, int n_pad, const TapSpec* taps, int ntaps,
                   const float* bias, const ubr_view* y, float* y_f32, int y_f32_ld, int out_cols,
                   cudaStream_t stream, int accumulate, float* stats, int* stats_rows, int shuffle_cout,
-                  const FusedEpi* epi) {
+                  const FusedEpi* epi, const BnReduce* bnr) {
   if (halo_disabled()) return 1;
   const int cin = x.c;
   if (!(cin == 16 || cin == 32 || cin == 64)) return 1;
@@ -497,7 +553,7 @@ int conv_halo_try(const ubr_view& x, const void* wpk, int nslabs, int n_pad, con
     if (s > 16) s = 16;
     // two CTAs per SM (two issuing threads) beat one deep ring: shrink the ring if that makes a second CTA fit
     {
-      const uint32_t half = 110u * 1024u - 1024u - 1024u - 4096u;
+      const uint32_t half = 110u * 1024u - 1024u - 1024u - 4096u - 512u;
       if (wr + 2u * st + 6u * slot_bytes <= half && (ks + 3 <= 8 ? 8 : 16) * cand <= 256) {
         const int s2 = (int)((half - wr - 2u * st) / slot_bytes);
         if (s2 < s) s = s2;
@@ -509,6 +565,7 @@ int conv_halo_try(const ubr_view& x, const void* wpk, int nslabs, int n_pad, con
   if (nt == 0) return 1;
   if (accumulate && out_mode != 2 && out_mode != 0) return 1;  // in-epilogue accumulation: bf16 outputs only
   if (stats && out_mode != 2) return 1;                      // fused BN statistics: direct-store path only
+  if (bnr && (!stats || out_mode != 2 || nt > 32 || accumulate)) return 1;
 
   HaloParams p;
   memset(&p, 0, sizeof(p));
@@ -558,6 +615,10 @@ int conv_halo_try(const ubr_view& x, const void* wpk, int nslabs, int n_pad, con
   p.bias = bias;
   p.accumulate = accumulate && out_mode == 2;
   p.stats = stats; p.stats_c = n_pad;
+  if (bnr) {
+    p.bnr_y = (const __nv_bfloat16*)bnr->y; p.bnr_ld = bnr->y_ld; p.bnr_relu = bnr->relu;
+    p.bnr_scale = bnr->scale; p.bnr_shift = bnr->shift; p.bnr_mean = bnr->mean; p.bnr_invstd = bnr->invstd;
+  }
   if (accumulate && out_mode == 0) {
     // TMA-store path: the old value of the output is the "residual" of the fused epilogue (read by the thread that
     // owns the pixel before the tile is stored -- in place is safe, tiles are disjoint)
@@ -570,7 +631,7 @@ int conv_halo_try(const ubr_view& x, const void* wpk, int nslabs, int n_pad, con
     p.fused = 1; p.relu_pre = epi->relu_pre; p.relu_post = epi->relu_post;
     p.res = (const __nv_bfloat16*)epi->res; p.res_ld = epi->res_ld;
   }
-  const uint32_t smem = w_region + (uint32_t)nslots * slot_bytes + 2u * stage_bytes + 16u * nslots + 640u + 4096u + 1024u;
+  const uint32_t smem = w_region + (uint32_t)nslots * slot_bytes + 2u * stage_bytes + 16u * nslots + 640u + 4096u + 512u + 1024u;
   UBR_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
   const int n_tiles = n_pad / nt;
   int per_sm = (smem <= 110u * 1024u && p.tmem_cols <= 256u) ? 2 : 1;
@@ -581,7 +642,7 @@ int conv_halo_try(const ubr_view& x, const void* wpk, int nslabs, int n_pad, con
   p.stats_rows = ctas;
   if (stats_rows) *stats_rows = ctas;
   dim3 grid((unsigned)ctas, (unsigned)n_tiles, 1);
-  kern<<<grid, kHThreads, smem, stream>>>(p);
+  ::ubr::Launch(grid, kHThreads, smem, stream)(kern, p);
   UBR_LAUNCH_CHECK("conv_halo_kernel");
   return 0;
 }

@@ -64,12 +64,23 @@ int stem_tc_fwd(const float* x, int n, int h, int w, const float* wgt, const flo
 int stem_tc_wgrad(const float* x, int n, int h, int w, const __nv_bfloat16* dy, int dyld, float* dw, float* dbias,
                   int accumulate, float* workspace, cudaStream_t stream);
 
+// Fused BatchNorm(+ReLU)-backward REDUCTION in a data-gradient epilogue: the conv output `da` feeds the backward of
+// a = relu?(bn(y)); while the epilogue still holds the (bf16-rounded) da tile it reads the matching y pixels and
+// accumulates  sum dz  and  sum dz*xhat  (dz = da * [bn(y) > 0], xhat = (y - mean) * invstd) per channel, replacing the
+// stand-alone bn_act_bwd_reduce pass (one full read of da and y).  Partial rows [cta][2][c] land in `stats`.
+struct BnReduce {
+  const void* y;                // bf16 NHWC pre-BatchNorm conv output on the da grid
+  int y_ld, relu;
+  const float *scale, *shift, *mean, *invstd;
+};
+
 // Halo-resident kernel (conv_halo.cu).  Returns 0 = launched, 1 = shape not eligible (caller falls back to the
 // tap-by-tap kernel), <0 = error.  `y` (bf16 view) or `y_f32` (fp32 [pixel][ld]) selects the output mode.
 int conv_halo_try(const ubr_view& x, const void* wpk, int nslabs, int n_pad, const TapSpec* taps, int ntaps,
                   const float* bias, const ubr_view* y, float* y_f32, int y_f32_ld, int out_cols,
                   cudaStream_t stream, int accumulate = 0, float* stats = nullptr,
-                  int* stats_rows = nullptr, int shuffle_cout = 0, const FusedEpi* epi = nullptr);
+                  int* stats_rows = nullptr, int shuffle_cout = 0, const FusedEpi* epi = nullptr,
+                  const BnReduce* bnr = nullptr);
 
 // Halo-resident weight gradient (wgrad_halo.cu).  Same return convention.
 int wgrad_halo_try(const ubr_view& x, const ubr_view& dy, int out_ch, int ksize, float* dw, int accumulate,

@@ -10,6 +10,7 @@ constexpr int kMaxCls = 16;
 // logits [pixel][ld] fp32 -> logp NCHW fp32
 __global__ void __launch_bounds__(256) logsoftmax_fwd_kernel(const float* __restrict__ logits, int ld, int n, int ncls,
                                                              int hw, float* __restrict__ logp) {
+  pdl_prologue();
   const long total = (long)n * hw;
   for (long p = (long)blockIdx.x * blockDim.x + threadIdx.x; p < total; p += (long)gridDim.x * blockDim.x) {
     const float* src = logits + p * ld;
@@ -34,6 +35,7 @@ __global__ void __launch_bounds__(256) logsoftmax_fwd_kernel(const float* __rest
 __global__ void __launch_bounds__(256) logsoftmax_bwd_kernel(const float* __restrict__ logp,
                                                              const float* __restrict__ dlogp, int n, int ncls, int hw,
                                                              __nv_bfloat16* __restrict__ dl, int dl_c, int dl_ld) {
+  pdl_prologue();
   const long total = (long)n * hw;
   for (long p = (long)blockIdx.x * blockDim.x + threadIdx.x; p < total; p += (long)gridDim.x * blockDim.x) {
     const long b = p / hw, i = p % hw;
@@ -58,6 +60,7 @@ __global__ void __launch_bounds__(256) nll_fwd_kernel(const float* __restrict__ 
                                                       const float* __restrict__ pixw, const float* __restrict__ classw,
                                                       int n, int ncls, int hw, long long ignore_index,
                                                       float* __restrict__ partials) {
+  pdl_prologue();
   const long total = (long)n * hw;
   float acc = 0.f;
   for (long p = (long)blockIdx.x * blockDim.x + threadIdx.x; p < total; p += (long)gridDim.x * blockDim.x) {
@@ -80,6 +83,7 @@ __global__ void __launch_bounds__(256) nll_fwd_kernel(const float* __restrict__ 
   }
 }
 __global__ void nll_finalize_kernel(const float* partials, int nb, double inv_count, float* loss) {
+  pdl_prologue();
   if (threadIdx.x == 0 && blockIdx.x == 0) {
     double s = 0.0;
     for (int i = 0; i < nb; ++i) s += (double)partials[i];
@@ -90,6 +94,7 @@ __global__ void __launch_bounds__(256) nll_bwd_kernel(const long long* __restric
                                                       const float* __restrict__ classw, const float* __restrict__ gout,
                                                       int n, int ncls, int hw, long long ignore_index, float inv_count,
                                                       float* __restrict__ dlogp) {
+  pdl_prologue();
   const long total = (long)n * hw;
   const float go = gout ? *gout : 1.f;
   for (long p = (long)blockIdx.x * blockDim.x + threadIdx.x; p < total; p += (long)gridDim.x * blockDim.x) {
@@ -105,6 +110,7 @@ __global__ void __launch_bounds__(256) nll_bwd_kernel(const long long* __restric
 __global__ void __launch_bounds__(256) tile_gather_kernel(const float* __restrict__ plane, int rows, int cols,
                                                           const int* __restrict__ origins, int ntiles, int crop_h,
                                                           int crop, float* __restrict__ crops) {
+  pdl_prologue();
   const long per = (long)crop_h * crop;
   const long total = per * ntiles;
   for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
@@ -118,6 +124,7 @@ __global__ void __launch_bounds__(256) tile_gather_kernel(const float* __restric
 __global__ void __launch_bounds__(256) stitch_scatter_kernel(const float* __restrict__ tiles, int nch,
                                                              const int* __restrict__ origins, int ntiles, int crop_h,
                                                              int crop, int rows, int cols, float* __restrict__ out) {
+  pdl_prologue();
   const long total = (long)rows * cols;
   for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
     const int r = (int)(i / cols), c = (int)(i % cols);
@@ -140,6 +147,7 @@ __global__ void __launch_bounds__(256) stitch_scatter_kernel(const float* __rest
 // per-pixel class = argmax over the C log-probabilities (first maximum, like torch.argmax / `output.max(1)`)
 __global__ void __launch_bounds__(256) argmax_classes_kernel(const float* __restrict__ logp, int n, int ncls, long hw,
                                                              uint8_t* __restrict__ cls) {
+  pdl_prologue();
   const long total = (long)n * hw;
   for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
     const long b = i / hw, px = i - b * hw;
@@ -158,6 +166,7 @@ __global__ void __launch_bounds__(256) stitch_scatter_u8_kernel(const uint8_t* _
                                                                 const int* __restrict__ origins, int ntiles, int crop_h,
                                                                 int crop, int rows, int cols, int fill,
                                                                 uint8_t* __restrict__ out) {
+  pdl_prologue();
   const long total = (long)rows * cols;
   for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
     const int r = (int)(i / cols), c = (int)(i % cols);
@@ -200,6 +209,7 @@ __device__ __forceinline__ float pack_value(const float* __restrict__ src, int s
 __global__ void __launch_bounds__(256) pack_weights_kernel(const float* __restrict__ src, int src_layout, int n_is_out,
                                                            int out_ch, int in_ch, int kh, int kw, int n_pad, int k_pad,
                                                            __nv_bfloat16* __restrict__ dst) {
+  pdl_prologue();
   const int taps = kh * kw;
   // 32-bit index arithmetic (the host checks total < 2^31); the grid is wide enough that a thread of the largest
   // conv (512x512x3x3) handles a few tens of elements -- the strided source reads are latency bound
@@ -216,6 +226,7 @@ __global__ void __launch_bounds__(256) pack_weights_kernel(const float* __restri
 // batched variant: one launch packs every job of a device-resident table (blockIdx.y = job)
 constexpr unsigned kPackBlocksPerJob = 384;
 __global__ void __launch_bounds__(256) pack_weights_batch_kernel(const long long* __restrict__ jobs) {
+  pdl_prologue();
   const long long* j = jobs + (size_t)blockIdx.y * 10;
   const float* src = reinterpret_cast<const float*>(j[0]);
   __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(j[1]);
@@ -248,6 +259,7 @@ constexpr int kAccMaxCls = 16;
 __global__ void __launch_bounds__(256) accuracy_counts_kernel(const float* __restrict__ logp,
                                                               const long long* __restrict__ target, int n, int ncls,
                                                               int hw, unsigned long long* __restrict__ counts) {
+  pdl_prologue();
   __shared__ unsigned int s_cnt[2 * kAccMaxCls];
   if (threadIdx.x < 2 * kAccMaxCls) s_cnt[threadIdx.x] = 0u;
   __syncthreads();
@@ -288,7 +300,7 @@ int ubr_pack_weights(const float* src, int src_layout, int n_is_out, int out_ch,
   UBR_REQUIRE(n_pad >= nn && k_pad >= kk, "pack_weights: pads too small");
   UBR_REQUIRE(src_layout != 2 || (kh == 3 && kw == 3), "pack_weights: sub-pixel deconv pack is 3x3");
   const long total = (long)(kh * kw + 1) * n_pad * k_pad;
-  pack_weights_kernel<<<blocks_for(total), 256, 0, (cudaStream_t)stream>>>(src, src_layout, n_is_out, out_ch, in_ch, kh,
+  ::ubr::Launch(blocks_for(total), 256, 0, (cudaStream_t)stream)(pack_weights_kernel, src, src_layout, n_is_out, out_ch, in_ch, kh,
                                                                            kw, n_pad, k_pad, (__nv_bfloat16*)dst_bf16);
   UBR_LAUNCH_CHECK("pack_weights_kernel");
   return 0;
@@ -297,8 +309,7 @@ int ubr_pack_weights(const float* src, int src_layout, int n_is_out, int out_ch,
 int ubr_pack_weights_batch(const int64_t* jobs_device, int njobs, void* stream) {
   if (int rc = ensure_device()) return rc;
   UBR_REQUIRE(jobs_device != nullptr && njobs >= 1 && njobs <= 65535, "pack_weights_batch: bad job table");
-  pack_weights_batch_kernel<<<dim3(kPackBlocksPerJob, (unsigned)njobs), 256, 0, (cudaStream_t)stream>>>(
-      (const long long*)jobs_device);
+  ::ubr::Launch(dim3(kPackBlocksPerJob, (unsigned)njobs), 256, 0, (cudaStream_t)stream)(pack_weights_batch_kernel, (const long long*)jobs_device);
   UBR_LAUNCH_CHECK("pack_weights_batch_kernel");
   return 0;
 }
@@ -307,7 +318,7 @@ int ubr_logsoftmax_fwd(const float* logits, int ld, int n, int ncls, int hw, flo
   if (int rc = ensure_device()) return rc;
   UBR_REQUIRE(logits && logp, "logsoftmax_fwd: null pointer");
   UBR_REQUIRE(ncls >= 1 && ncls <= kMaxCls && ld >= ncls, "logsoftmax_fwd: ncls=%d ld=%d unsupported", ncls, ld);
-  logsoftmax_fwd_kernel<<<blocks_for((long)n * hw), 256, 0, (cudaStream_t)stream>>>(logits, ld, n, ncls, hw, logp);
+  ::ubr::Launch(blocks_for((long)n * hw), 256, 0, (cudaStream_t)stream)(logsoftmax_fwd_kernel, logits, ld, n, ncls, hw, logp);
   UBR_LAUNCH_CHECK("logsoftmax_fwd_kernel");
   return 0;
 }
@@ -318,8 +329,7 @@ int ubr_logsoftmax_bwd(const float* logp, const float* dlogp, int n, int ncls, i
   UBR_REQUIRE(ncls >= 1 && ncls <= kMaxCls && dlogits.c >= ncls && dlogits.c % 8 == 0 && dlogits.ld % 8 == 0,
               "logsoftmax_bwd: bad dlogits view");
   UBR_REQUIRE((long)dlogits.n * dlogits.h * dlogits.w == (long)n * hw, "logsoftmax_bwd: pixel count mismatch");
-  logsoftmax_bwd_kernel<<<blocks_for((long)n * hw), 256, 0, (cudaStream_t)stream>>>(
-      logp, dlogp, n, ncls, hw, (__nv_bfloat16*)dlogits.ptr, dlogits.c, dlogits.ld);
+  ::ubr::Launch(blocks_for((long)n * hw), 256, 0, (cudaStream_t)stream)(logsoftmax_bwd_kernel, logp, dlogp, n, ncls, hw, (__nv_bfloat16*)dlogits.ptr, dlogits.c, dlogits.ld);
   UBR_LAUNCH_CHECK("logsoftmax_bwd_kernel");
   return 0;
 }
@@ -337,10 +347,10 @@ int ubr_pixelwise_nll_fwd(const float* logp, const int64_t* target, const float*
   cudaStream_t st = (cudaStream_t)stream;
   long nb = ((long)n * hw + 255) / 256;
   if (nb > kNllBlocks) nb = kNllBlocks;
-  nll_fwd_kernel<<<(unsigned)nb, 256, 0, st>>>(logp, (const long long*)target, pixw, classw, n, ncls, hw,
+  ::ubr::Launch((unsigned)nb, 256, 0, st)(nll_fwd_kernel, logp, (const long long*)target, pixw, classw, n, ncls, hw,
                                                (long long)ignore_index, (float*)workspace);
   UBR_LAUNCH_CHECK("nll_fwd_kernel");
-  nll_finalize_kernel<<<1, 32, 0, st>>>((const float*)workspace, (int)nb, 1.0 / ((double)n * hw), loss);
+  ::ubr::Launch(1, 32, 0, st)(nll_finalize_kernel, (const float*)workspace, (int)nb, 1.0 / ((double)n * hw), loss);
   UBR_LAUNCH_CHECK("nll_finalize_kernel");
   return 0;
 }
@@ -349,8 +359,7 @@ int ubr_pixelwise_nll_bwd(const int64_t* target, const float* pixw, const float*
                           int ncls, int hw, int64_t ignore_index, float* dlogp, void* stream) {
   if (int rc = ensure_device()) return rc;
   UBR_REQUIRE(target && pixw && dlogp, "pixelwise_nll_bwd: null pointer");
-  nll_bwd_kernel<<<blocks_for((long)n * hw), 256, 0, (cudaStream_t)stream>>>(
-      (const long long*)target, pixw, classw, gout, n, ncls, hw, (long long)ignore_index,
+  ::ubr::Launch(blocks_for((long)n * hw), 256, 0, (cudaStream_t)stream)(nll_bwd_kernel, (const long long*)target, pixw, classw, gout, n, ncls, hw, (long long)ignore_index,
       (float)(1.0 / ((double)n * hw)), dlogp);
   UBR_LAUNCH_CHECK("nll_bwd_kernel");
   return 0;
@@ -361,8 +370,7 @@ int ubr_tile_gather_rect(const float* plane, int rows, int cols, const int32_t* 
   if (int rc = ensure_device()) return rc;
   UBR_REQUIRE(plane && origins && crops, "tile_gather: null pointer");
   UBR_REQUIRE(rows > 0 && cols > 0 && ntiles > 0 && crop_h > 0 && crop_w > 0, "tile_gather: bad sizes");
-  tile_gather_kernel<<<blocks_for((long)ntiles * crop_h * crop_w), 256, 0, (cudaStream_t)stream>>>(
-      plane, rows, cols, origins, ntiles, crop_h, crop_w, crops);
+  ::ubr::Launch(blocks_for((long)ntiles * crop_h * crop_w), 256, 0, (cudaStream_t)stream)(tile_gather_kernel, plane, rows, cols, origins, ntiles, crop_h, crop_w, crops);
   UBR_LAUNCH_CHECK("tile_gather_kernel");
   return 0;
 }
@@ -376,7 +384,7 @@ int ubr_stitch_scatter_rect(const float* tiles, int nch, const int32_t* origins,
   if (int rc = ensure_device()) return rc;
   UBR_REQUIRE(tiles && origins && out, "stitch_scatter: null pointer");
   UBR_REQUIRE(rows > 0 && cols > 0 && ntiles > 0 && crop_h > 0 && crop_w > 0 && nch > 0, "stitch_scatter: bad sizes");
-  stitch_scatter_kernel<<<blocks_for((long)rows * cols), 256, 0, (cudaStream_t)stream>>>(tiles, nch, origins, ntiles,
+  ::ubr::Launch(blocks_for((long)rows * cols), 256, 0, (cudaStream_t)stream)(stitch_scatter_kernel, tiles, nch, origins, ntiles,
                                                                                          crop_h, crop_w, rows, cols, out);
   UBR_LAUNCH_CHECK("stitch_scatter_kernel");
   return 0;
@@ -389,7 +397,7 @@ int ubr_stitch_scatter(const float* tiles, int nch, const int32_t* origins, int 
 int ubr_argmax_classes(const float* logp, int n, int ncls, int hw, uint8_t* classes, void* stream) {
   if (int rc = ensure_device()) return rc;
   UBR_REQUIRE(logp && classes && n > 0 && ncls >= 1 && ncls <= 255 && hw > 0, "argmax_classes: bad arguments");
-  argmax_classes_kernel<<<blocks_for((long)n * hw), 256, 0, (cudaStream_t)stream>>>(logp, n, ncls, (long)hw, classes);
+  ::ubr::Launch(blocks_for((long)n * hw), 256, 0, (cudaStream_t)stream)(argmax_classes_kernel, logp, n, ncls, (long)hw, classes);
   UBR_LAUNCH_CHECK("argmax_classes_kernel");
   return 0;
 }
@@ -399,7 +407,7 @@ int ubr_stitch_scatter_u8(const uint8_t* tiles, const int32_t* origins, int ntil
   if (int rc = ensure_device()) return rc;
   UBR_REQUIRE(tiles && origins && out, "stitch_scatter_u8: null pointer");
   UBR_REQUIRE(rows > 0 && cols > 0 && ntiles > 0 && crop_h > 0 && crop_w > 0, "stitch_scatter_u8: bad sizes");
-  stitch_scatter_u8_kernel<<<blocks_for((long)rows * cols), 256, 0, (cudaStream_t)stream>>>(tiles, origins, ntiles, crop_h,
+  ::ubr::Launch(blocks_for((long)rows * cols), 256, 0, (cudaStream_t)stream)(stitch_scatter_u8_kernel, tiles, origins, ntiles, crop_h,
                                                                                             crop_w, rows, cols, fill, out);
   UBR_LAUNCH_CHECK("stitch_scatter_u8_kernel");
   return 0;
@@ -413,7 +421,7 @@ int ubr_accuracy_counts(const float* logp, const int64_t* target, int n, int ncl
   const long total = (long)n * hw;
   long nb = (total + 255) / 256;
   if (nb > 148 * 8) nb = 148 * 8;
-  accuracy_counts_kernel<<<(unsigned)nb, 256, 0, (cudaStream_t)stream>>>(logp, (const long long*)target, n, ncls, hw,
+  ::ubr::Launch((unsigned)nb, 256, 0, (cudaStream_t)stream)(accuracy_counts_kernel, logp, (const long long*)target, n, ncls, hw,
                                                                        (unsigned long long*)counts);
   UBR_LAUNCH_CHECK("accuracy_counts_kernel");
   return 0;

@@ -22,6 +22,7 @@ template <bool ADAM>
 __global__ void __launch_bounds__(kOptThreads) opt_step_kernel(const ubr_opt_slot* __restrict__ slots,
                                                                const ubr_opt_chunk* __restrict__ chunks,
                                                                const OptHyper hp) {
+  pdl_prologue();
   const ubr_opt_chunk ck = chunks[blockIdx.x];
   const ubr_opt_slot sl = slots[ck.slot];
   const long long end = (sl.numel - ck.offset) < kOptChunk ? sl.numel : ck.offset + kOptChunk;
@@ -96,7 +97,7 @@ int ubr_sgd_step(const ubr_opt_slot* slots, const ubr_opt_chunk* chunks, int nch
   hp.lr = lr; hp.momentum = momentum; hp.dampening = dampening; hp.weight_decay = weight_decay;
   hp.one_m_damp = (float)(1.0 - (double)dampening);
   hp.nesterov = nesterov; hp.first_step = first_step;
-  opt_step_kernel<false><<<nchunks, kOptThreads, 0, (cudaStream_t)stream>>>(slots, chunks, hp);
+  ::ubr::Launch(nchunks, kOptThreads, 0, (cudaStream_t)stream)(opt_step_kernel<false>, slots, chunks, hp);
   UBR_LAUNCH_CHECK("opt_step_kernel<sgd>");
   return 0;
 }
@@ -111,7 +112,7 @@ int ubr_adam_step(const ubr_opt_slot* slots, const ubr_opt_chunk* chunks, int nc
   hp.one_m_beta2 = (float)(1.0 - beta2);
   hp.step_size = (float)(lr / (1.0 - pow(beta1, (double)step)));
   hp.bc2_sqrt = (float)sqrt(1.0 - pow(beta2, (double)step));
-  opt_step_kernel<true><<<nchunks, kOptThreads, 0, (cudaStream_t)stream>>>(slots, chunks, hp);
+  ::ubr::Launch(nchunks, kOptThreads, 0, (cudaStream_t)stream)(opt_step_kernel<true>, slots, chunks, hp);
   UBR_LAUNCH_CHECK("opt_step_kernel<adam>");
   return 0;
 }

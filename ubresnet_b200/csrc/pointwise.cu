@@ -94,6 +94,7 @@ static inline int red_blocks(long npix, int c, int cap = kRedBlocks) {
 
 // ------------------------------------------------------------------ BN forward statistics
 __global__ void __launch_bounds__(kRedThreads) bn_stats_kernel(DView y, float* partials) {
+  pdl_prologue();
   const int cgs = y.c >> 3, lanes = blockDim.x / cgs;
   const int cg = threadIdx.x % cgs, pl = threadIdx.x / cgs;
   const long ps = (long)gridDim.x * lanes;
@@ -149,6 +150,7 @@ __device__ __forceinline__ double col_sum_32x8(const float* partials, int nb, in
 __global__ void bn_finalize_kernel(const float* partials, int nb, int c, double count, const float* gamma,
                                    const float* beta, float* running_mean, float* running_var, float momentum,
                                    float eps, float* scale, float* shift, float* mean_out, float* invstd_out) {
+  pdl_prologue();
   const int ch = blockIdx.x * 32 + threadIdx.x;
   const bool act = ch < c;
   const double s = col_sum_32x8(partials, nb, 2 * c, ch, act);
@@ -172,6 +174,7 @@ __global__ void bn_finalize_kernel(const float* partials, int nb, int c, double 
 
 __global__ void bn_eval_affine_kernel(int c, const float* gamma, const float* beta, const float* rm, const float* rv,
                                       float eps, float* scale, float* shift) {
+  pdl_prologue();
   const int ch = blockIdx.x * blockDim.x + threadIdx.x;
   if (ch >= c) return;
   const float invstd = rsqrtf(rv[ch] + eps);
@@ -183,6 +186,7 @@ __global__ void bn_eval_affine_kernel(int c, const float* gamma, const float* be
 // ------------------------------------------------------------------ BN apply (+ReLU), block tail
 __global__ void __launch_bounds__(256, 2) bn_act_kernel(DView y, const float* scale, const float* shift, int relu,
                                                         DViewW out) {
+  pdl_prologue();
   const EwIdx ix = ew_index(y.c >> 3);
   float sc[8], sh[8];
   ldparam8(scale, ix.cg * 8, sc);
@@ -212,6 +216,7 @@ __global__ void __launch_bounds__(256, 2) bn_act_kernel(DView y, const float* sc
 // out = relu( relu(y2*s2+b2) + (res*sr+br | res) )
 __global__ void __launch_bounds__(256, 2) block_tail_kernel(DView y2, const float* s2, const float* b2, DView res,
                                                             const float* sr, const float* br, DViewW out) {
+  pdl_prologue();
   const EwIdx ix = ew_index(y2.c >> 3);
   float a2[8], c2[8], ar[8], cr[8];
   ldparam8(s2, ix.cg * 8, a2);
@@ -255,6 +260,7 @@ __global__ void __launch_bounds__(256, 2) block_tail_kernel(DView y2, const floa
 __global__ void __launch_bounds__(kRedThreads, 2) bn_act_bwd_reduce_kernel(DView dout, DView y, const float* scale,
                                                                            const float* shift, const float* mean,
                                                                            const float* invstd, int relu, float* partials) {
+  pdl_prologue();
   const int cgs = y.c >> 3, lanes = blockDim.x / cgs;
   const int cg = threadIdx.x % cgs, pl = threadIdx.x / cgs;
   const long ps = (long)gridDim.x * lanes;
@@ -298,6 +304,7 @@ __global__ void __launch_bounds__(kRedThreads, 2) bn_act_bwd_reduce_kernel(DView
 struct ParamGradOut { float* p[4]; };    // per sum row: optional fp32 parameter-gradient vector of c entries (dbeta / dgamma)
 __global__ void sums_finalize_kernel(const float* partials, int nb, int nsc, float* sums, int c, ParamGradOut out,
                                      int accumulate) {
+  pdl_prologue();
   const int i = blockIdx.x * 32 + threadIdx.x;
   const double s = col_sum_32x8(partials, nb, nsc, i, i < nsc);
   if (i < nsc && threadIdx.y == 0) {
@@ -313,6 +320,7 @@ __global__ void __launch_bounds__(256, 2) bn_act_bwd_apply_kernel(DView dout, DV
                                                                   const float* shift, const float* mean,
                                                                   const float* invstd, const float* gamma, int relu,
                                                                   const float* sums, float inv_count, DViewW dy) {
+  pdl_prologue();
   const EwIdx ix = ew_index(y.c >> 3);
   float sc[8], sh[8], ca[8], cb[8];
   {
@@ -366,6 +374,7 @@ __global__ void __launch_bounds__(kRedThreads, 2) tail_bwd_reduce_kernel(DView d
                                                                       const float* meanr, const float* invstdr,
                                                                       const float* sr, const float* br,
                                                                       float* partials) {
+  pdl_prologue();
   // RES_BN: the mask of the block's final ReLU is recomputed from y2 and the bypass output with the forward pass's own
   // arithmetic (block_tail_kernel) instead of reading `out` back
   constexpr int NS = RES_BN ? 4 : 2;
@@ -432,6 +441,7 @@ __global__ void __launch_bounds__(256, 2) tail_bwd_apply_kernel(DView dout, DVie
                                                                 const float* sr, const float* br,
                                                                 const float* sums, float inv_count, DViewW dy2,
                                                                 DViewW dres) {
+  pdl_prologue();
   const int c = y2.c;
   const EwIdx ix = ew_index(c >> 3);
   float sc[8], sh[8], ca[8], cb[8], gr[8], ra[8], rb[8], ar[8], cr[8];
@@ -499,6 +509,7 @@ __global__ void __launch_bounds__(256, 2) tail_bwd_apply_kernel(DView dout, DVie
 
 // ------------------------------------------------------------------ pointwise sum
 __global__ void __launch_bounds__(256, 2) add_kernel(DView a, DView b, DView c, DViewW out) {
+  pdl_prologue();
   const EwIdx ix = ew_index(a.c >> 3);
   for (long p = ix.p0; p < a.npix; p += 4 * ix.ps) {
     uint4 rx[4], ry[4], rz[4];
@@ -536,6 +547,7 @@ __global__ void __launch_bounds__(256, 2) add_kernel(DView a, DView b, DView c, 
 // ------------------------------------------------------------------ MaxPool 3x3 / stride 2 / pad 1
 __global__ void __launch_bounds__(256) maxpool_fwd_kernel(const __nv_bfloat16* x, int xld, int n, int h, int w, int c,
                                                           __nv_bfloat16* y, int yld) {
+  pdl_prologue();
   const int cgs = c >> 3, ho = h / 2, wo = w / 2;
   const long total = (long)n * ho * wo * cgs;
   for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
@@ -566,6 +578,7 @@ __global__ void __launch_bounds__(256) maxpool_fwd_kernel(const __nv_bfloat16* x
 // forward that also records the argmax tap (kh*3+kw of the FIRST maximum in scan order, as ATen) per element
 __global__ void __launch_bounds__(256) maxpool_fwd_idx_kernel(const __nv_bfloat16* x, int xld, int n, int h, int w, int c,
                                                               __nv_bfloat16* y, int yld, uint8_t* __restrict__ idx) {
+  pdl_prologue();
   const int cgs = c >> 3, ho = h / 2, wo = w / 2;
   const long total = (long)n * ho * wo * cgs;
   for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
@@ -603,6 +616,7 @@ __global__ void __launch_bounds__(256) maxpool_fwd_idx_kernel(const __nv_bfloat1
 __global__ void __launch_bounds__(256) maxpool_bwd_idx_kernel(const uint8_t* __restrict__ idx, int n, int h, int w, int c,
                                                               const __nv_bfloat16* dy, int dyld, __nv_bfloat16* dx,
                                                               int dxld, int accumulate) {
+  pdl_prologue();
   const int cgs = c >> 3, ho = h / 2, wo = w / 2;
   const long total = (long)n * h * w * cgs;
   for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
@@ -664,6 +678,7 @@ __global__ void __launch_bounds__(256) maxpool_bwd_idx_kernel(const uint8_t* __r
 // stride-2 kernel so the backward is a gather over the <= 9 windows that cover an input pixel.
 __global__ void __launch_bounds__(256) maxpool3s1_fwd_kernel(const __nv_bfloat16* x, int xld, int n, int h, int w, int c,
                                                              __nv_bfloat16* y, int yld, uint8_t* __restrict__ idx) {
+  pdl_prologue();
   const int cgs = c >> 3;
   const long total = (long)n * h * w * cgs;
   for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
@@ -702,6 +717,7 @@ __global__ void __launch_bounds__(256) maxpool3s1_fwd_kernel(const __nv_bfloat16
 __global__ void __launch_bounds__(256) maxpool3s1_bwd_idx_kernel(const uint8_t* __restrict__ idx, int n, int h, int w, int c,
                                                                  const __nv_bfloat16* dy, int dyld, __nv_bfloat16* dx,
                                                                  int dxld, int accumulate) {
+  pdl_prologue();
   const int cgs = c >> 3;
   const long total = (long)n * h * w * cgs;
   for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
@@ -746,6 +762,7 @@ __global__ void __launch_bounds__(256) maxpool3s1_bwd_idx_kernel(const uint8_t* 
 // (the transpose of the sub-pixel forward, ubr_deconv4s2_fwd_subpixel).
 __global__ void __launch_bounds__(256) pixel_unshuffle2_kernel(const __nv_bfloat16* __restrict__ y, int yld, int n, int h,
                                                                int w, int c, __nv_bfloat16* __restrict__ y4, int y4ld) {
+  pdl_prologue();
   const int cgs = c >> 3;                       // 16-byte groups per source pixel
   const long total = (long)n * (2 * h) * (2 * w) * cgs;
   for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
@@ -764,6 +781,7 @@ __global__ void __launch_bounds__(256) pixel_unshuffle2_kernel(const __nv_bfloat
 // (the inverse of pack src_layout 2: every 4x4 tap is exactly one (phase, 3x3 tap) pair)
 __global__ void deconv_wgrad_gather_kernel(const float* __restrict__ dw3, int in_ch, int out_ch, float* __restrict__ dw,
                                            int accumulate) {
+  pdl_prologue();
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= in_ch * out_ch * 16) return;
   const int kw = i & 3, kh = (i >> 2) & 3, co = (i >> 4) % out_ch, ci = (i >> 4) / out_ch;
@@ -778,6 +796,7 @@ __global__ void deconv_wgrad_gather_kernel(const float* __restrict__ dw3, int in
 __global__ void __launch_bounds__(256) maxpool_bwd_kernel(const __nv_bfloat16* x, int xld, int n, int h, int w, int c,
                                                           const __nv_bfloat16* dy, int dyld, __nv_bfloat16* dx,
                                                           int dxld, int accumulate) {
+  pdl_prologue();
   const int cgs = c >> 3, ho = h / 2, wo = w / 2;
   const long total = (long)n * h * w * cgs;
   for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
@@ -829,6 +848,7 @@ __global__ void __launch_bounds__(256) maxpool_bwd_kernel(const __nv_bfloat16* x
 }
 
 __global__ void scale_f32_kernel(float* buf, unsigned long long count, float alpha) {
+  pdl_prologue();
   for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < count;
        i += (unsigned long long)gridDim.x * blockDim.x)
     buf[i] *= alpha;
@@ -892,7 +912,7 @@ int ubr_bn_stats(ubr_view y, void* workspace, void* stream) {
   UBR_REQUIRE(workspace != nullptr, "bn_stats: null workspace");
   DView v = dv(y);
   const int nb = red_blocks(v.npix, v.c);
-  bn_stats_kernel<<<nb, kRedThreads, kRedThreads * 16 * sizeof(float), (cudaStream_t)stream>>>(v, (float*)workspace);
+  ::ubr::Launch(nb, kRedThreads, kRedThreads * 16 * sizeof(float), (cudaStream_t)stream)(bn_stats_kernel, v, (float*)workspace);
   UBR_LAUNCH_CHECK("bn_stats_kernel");
   return 0;
 }
@@ -904,7 +924,7 @@ int ubr_bn_finalize(const void* workspace, int c, double count, const float* gam
   UBR_REQUIRE(workspace && scale && shift, "bn_finalize: null pointer");
   UBR_REQUIRE(c > 0 && c % 8 == 0 && count >= 1.0, "bn_finalize: bad c/count");
   const int nb = red_blocks((long)count, c);
-  bn_finalize_kernel<<<ceil_div(c, 32), dim3(32, kColLanes), 0, (cudaStream_t)stream>>>((const float*)workspace, nb, c, count, gamma,
+  ::ubr::Launch(ceil_div(c, 32), dim3(32, kColLanes), 0, (cudaStream_t)stream)(bn_finalize_kernel, (const float*)workspace, nb, c, count, gamma,
                                                                          beta, running_mean, running_var, momentum,
                                                                          eps, scale, shift, mean, invstd);
   UBR_LAUNCH_CHECK("bn_finalize_kernel");
@@ -917,7 +937,7 @@ int ubr_bn_finalize_rows(const void* workspace, int rows, int c, double count, c
   if (int rc = ensure_device()) return rc;
   UBR_REQUIRE(workspace && scale && shift, "bn_finalize_rows: null pointer");
   UBR_REQUIRE(c > 0 && c % 8 == 0 && count >= 1.0 && rows >= 1 && rows <= 2 * kRedBlocks, "bn_finalize_rows: bad c/count/rows");
-  bn_finalize_kernel<<<ceil_div(c, 32), dim3(32, kColLanes), 0, (cudaStream_t)stream>>>((const float*)workspace, rows, c, count,
+  ::ubr::Launch(ceil_div(c, 32), dim3(32, kColLanes), 0, (cudaStream_t)stream)(bn_finalize_kernel, (const float*)workspace, rows, c, count,
                                                                                       gamma, beta, running_mean, running_var,
                                                                                       momentum, eps, scale, shift, mean, invstd);
   UBR_LAUNCH_CHECK("bn_finalize_kernel");
@@ -928,7 +948,7 @@ int ubr_bn_eval_affine(int c, const float* gamma, const float* beta, const float
                        const float* running_var, float eps, float* scale, float* shift, void* stream) {
   if (int rc = ensure_device()) return rc;
   UBR_REQUIRE(running_mean && running_var && scale && shift && c > 0, "bn_eval_affine: bad args");
-  bn_eval_affine_kernel<<<ceil_div(c, 128), 128, 0, (cudaStream_t)stream>>>(c, gamma, beta, running_mean, running_var,
+  ::ubr::Launch(ceil_div(c, 128), 128, 0, (cudaStream_t)stream)(bn_eval_affine_kernel, c, gamma, beta, running_mean, running_var,
                                                                             eps, scale, shift);
   UBR_LAUNCH_CHECK("bn_eval_affine_kernel");
   return 0;
@@ -941,7 +961,7 @@ int ubr_bn_act(ubr_view y, const float* scale, const float* shift, int relu, ubr
   if (int rc = same_shape(y, out, "bn_act")) return rc;
   UBR_REQUIRE(scale && shift, "bn_act: null affine");
   DView v = dv(y);
-  bn_act_kernel<<<ew_grid(v.npix, v.c >> 3, 4), 256, 0, (cudaStream_t)stream>>>(v, scale, shift, relu, dvw(out));
+  ::ubr::Launch(ew_grid(v.npix, v.c >> 3, 4), 256, 0, (cudaStream_t)stream)(bn_act_kernel, v, scale, shift, relu, dvw(out));
   UBR_LAUNCH_CHECK("bn_act_kernel");
   return 0;
 }
@@ -956,7 +976,7 @@ int ubr_block_tail(ubr_view y2, const float* s2, const float* b2, ubr_view res, 
   if (int rc = same_shape(y2, out, "block_tail(out)")) return rc;
   UBR_REQUIRE(s2 && b2 && ((sr == nullptr) == (br == nullptr)), "block_tail: bad affine pointers");
   DView v = dv(y2);
-  block_tail_kernel<<<ew_grid(v.npix, v.c >> 3, 4), 256, 0, (cudaStream_t)stream>>>(v, s2, b2, dv(res), sr, br,
+  ::ubr::Launch(ew_grid(v.npix, v.c >> 3, 4), 256, 0, (cudaStream_t)stream)(block_tail_kernel, v, s2, b2, dv(res), sr, br,
                                                                                       dvw(out));
   UBR_LAUNCH_CHECK("block_tail_kernel");
   return 0;
@@ -971,8 +991,7 @@ int ubr_bn_act_bwd_reduce(ubr_view dout, ubr_view y, const float* scale, const f
   UBR_REQUIRE(scale && shift && mean && invstd && workspace, "bn_act_bwd_reduce: null pointer");
   DView v = dv(y);
   const int nb = red_blocks(v.npix, v.c, kBwdRedBlocks);
-  bn_act_bwd_reduce_kernel<<<nb, kRedThreads, kRedThreads * 16 * sizeof(float), (cudaStream_t)stream>>>(
-      dv(dout), v, scale, shift, mean, invstd, relu, (float*)workspace);
+  ::ubr::Launch(nb, kRedThreads, kRedThreads * 16 * sizeof(float), (cudaStream_t)stream)(bn_act_bwd_reduce_kernel, dv(dout), v, scale, shift, mean, invstd, relu, (float*)workspace);
   UBR_LAUNCH_CHECK("bn_act_bwd_reduce_kernel");
   return 0;
 }
@@ -993,10 +1012,33 @@ int ubr_bn_act_bwd_apply(ubr_view dout, ubr_view y, const float* scale, const fl
   float* sums = (float*)workspace + (size_t)kRedBlocks * 4 * v.c;
   cudaStream_t st = (cudaStream_t)stream;
   // sums row 0 = sum dz (-> dbeta), row 1 = sum dz*xhat (-> dgamma): parameter gradients written by the finalize
-  sums_finalize_kernel<<<ceil_div(2 * v.c, 32), dim3(32, kColLanes), 0, st>>>(
-      partials, nb, 2 * v.c, sums, v.c, ParamGradOut{{dbeta, dgamma, nullptr, nullptr}}, accumulate);
+  ::ubr::Launch(ceil_div(2 * v.c, 32), dim3(32, kColLanes), 0, st)(sums_finalize_kernel, partials, nb, 2 * v.c, sums, v.c, ParamGradOut{{dbeta, dgamma, nullptr, nullptr}}, accumulate);
   UBR_LAUNCH_CHECK("sums_finalize_kernel");
-  bn_act_bwd_apply_kernel<<<ew_grid(v.npix, v.c >> 3, 4), 256, 0, st>>>(dv(dout), v, scale, shift, mean, invstd,
+  ::ubr::Launch(ew_grid(v.npix, v.c >> 3, 4), 256, 0, st)(bn_act_bwd_apply_kernel, dv(dout), v, scale, shift, mean, invstd,
+                                                                          gamma, relu, sums, (float)(1.0 / count),
+                                                                          dvw(dy));
+  UBR_LAUNCH_CHECK("bn_act_bwd_apply_kernel");
+  return 0;
+}
+
+int ubr_bn_act_bwd_apply_rows(ubr_view dout, ubr_view y, const float* scale, const float* shift, const float* mean,
+                              const float* invstd, const float* gamma, int relu, const void* workspace, int rows,
+                              double count, ubr_view dy, float* dgamma, float* dbeta, int accumulate, void* stream) {
+  if (int rc = ensure_device()) return rc;
+  if (int rc = chk_red(y, "bn_act_bwd_apply_rows.y")) return rc;
+  if (int rc = chk(dout, "bn_act_bwd_apply_rows.dout")) return rc;
+  if (int rc = chk(dy, "bn_act_bwd_apply_rows.dy")) return rc;
+  if (int rc = same_shape(y, dout, "bn_act_bwd_apply_rows(dout)")) return rc;
+  if (int rc = same_shape(y, dy, "bn_act_bwd_apply_rows(dy)")) return rc;
+  UBR_REQUIRE(scale && shift && mean && invstd && workspace && rows >= 1 && rows <= kRedBlocks,
+              "bn_act_bwd_apply_rows: null pointer / bad row count %d", rows);
+  DView v = dv(y);
+  const float* partials = (const float*)workspace;
+  float* sums = (float*)workspace + (size_t)kRedBlocks * 4 * v.c;
+  cudaStream_t st = (cudaStream_t)stream;
+  ::ubr::Launch(ceil_div(2 * v.c, 32), dim3(32, kColLanes), 0, st)(sums_finalize_kernel, partials, rows, 2 * v.c, sums, v.c, ParamGradOut{{dbeta, dgamma, nullptr, nullptr}}, accumulate);
+  UBR_LAUNCH_CHECK("sums_finalize_kernel");
+  ::ubr::Launch(ew_grid(v.npix, v.c >> 3, 4), 256, 0, st)(bn_act_bwd_apply_kernel, dv(dout), v, scale, shift, mean, invstd,
                                                                           gamma, relu, sums, (float)(1.0 / count),
                                                                           dvw(dy));
   UBR_LAUNCH_CHECK("bn_act_bwd_apply_kernel");
@@ -1023,11 +1065,9 @@ int ubr_block_tail_bwd_reduce(ubr_view dout, ubr_view out, ubr_view y2, const fl
     if (int rc = chk(res, "block_tail_bwd_reduce.res")) return rc;
     if (int rc = same_shape(y2, res, "block_tail_bwd_reduce(res)")) return rc;
     UBR_REQUIRE(meanr && invstdr && scaler && shiftr, "block_tail_bwd_reduce: null residual stats / affine");
-    tail_bwd_reduce_kernel<true><<<nb, kRedThreads, kRedThreads * 32 * sizeof(float), st>>>(
-        dv(dout), v, v, s2, b2, mean2, invstd2, dv(res), meanr, invstdr, scaler, shiftr, (float*)workspace);
+    ::ubr::Launch(nb, kRedThreads, kRedThreads * 32 * sizeof(float), st)(tail_bwd_reduce_kernel<true>, dv(dout), v, v, s2, b2, mean2, invstd2, dv(res), meanr, invstdr, scaler, shiftr, (float*)workspace);
   } else {
-    tail_bwd_reduce_kernel<false><<<nb, kRedThreads, kRedThreads * 16 * sizeof(float), st>>>(
-        dv(dout), dv(out), v, s2, b2, mean2, invstd2, v, nullptr, nullptr, nullptr, nullptr, (float*)workspace);
+    ::ubr::Launch(nb, kRedThreads, kRedThreads * 16 * sizeof(float), st)(tail_bwd_reduce_kernel<false>, dv(dout), dv(out), v, s2, b2, mean2, invstd2, v, nullptr, nullptr, nullptr, nullptr, (float*)workspace);
   }
   UBR_LAUNCH_CHECK("tail_bwd_reduce_kernel");
   return 0;
@@ -1059,19 +1099,18 @@ int ubr_block_tail_bwd_apply(ubr_view dout, ubr_view out, ubr_view y2, const flo
   const float* partials = (const float*)workspace;
   float* sums = (float*)workspace + (size_t)kRedBlocks * 4 * v.c;
   cudaStream_t st = (cudaStream_t)stream;
-  sums_finalize_kernel<<<ceil_div(ns * v.c, 32), dim3(32, kColLanes), 0, st>>>(
-      partials, nb, ns * v.c, sums, v.c,
+  ::ubr::Launch(ceil_div(ns * v.c, 32), dim3(32, kColLanes), 0, st)(sums_finalize_kernel, partials, nb, ns * v.c, sums, v.c,
       ParamGradOut{{dbeta2, dgamma2, res_is_bn ? dbetar : nullptr, res_is_bn ? dgammar : nullptr}}, accumulate);
   UBR_LAUNCH_CHECK("sums_finalize_kernel");
   const unsigned blocks = ew_grid(v.npix, v.c >> 3, 2);
   if (res_is_bn) {
     if (int rc = chk(res, "block_tail_bwd_apply.res")) return rc;
     UBR_REQUIRE(meanr && invstdr && gammar && scaler && shiftr, "block_tail_bwd_apply: null residual stats / affine");
-    tail_bwd_apply_kernel<true><<<blocks, 256, 0, st>>>(dv(dout), v, v, s2, b2, mean2, invstd2, dv(res), meanr,
+    ::ubr::Launch(blocks, 256, 0, st)(tail_bwd_apply_kernel<true>, dv(dout), v, v, s2, b2, mean2, invstd2, dv(res), meanr,
                                                         invstdr, gammar, scaler, shiftr, sums, (float)(1.0 / count),
                                                         dvw(dy2), dvw(dres));
   } else {
-    tail_bwd_apply_kernel<false><<<blocks, 256, 0, st>>>(dv(dout), dv(out), v, s2, b2, mean2, invstd2, v, nullptr,
+    ::ubr::Launch(blocks, 256, 0, st)(tail_bwd_apply_kernel<false>, dv(dout), dv(out), v, s2, b2, mean2, invstd2, v, nullptr,
                                                          nullptr, nullptr, nullptr, nullptr, sums, (float)(1.0 / count),
                                                          dvw(dy2), dvw(dres));
   }
@@ -1086,7 +1125,7 @@ int ubr_maxpool3s2_fwd(ubr_view x, ubr_view y, void* stream) {
   UBR_REQUIRE(x.h % 2 == 0 && x.w % 2 == 0, "maxpool_fwd: H,W must be even");
   UBR_REQUIRE(y.n == x.n && y.c == x.c && y.h == x.h / 2 && y.w == x.w / 2, "maxpool_fwd: output view mismatch");
   const long total = (long)y.n * y.h * y.w * (y.c >> 3);
-  maxpool_fwd_kernel<<<ew_blocks(total), 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)x.ptr, x.ld, x.n, x.h,
+  ::ubr::Launch(ew_blocks(total), 256, 0, (cudaStream_t)stream)(maxpool_fwd_kernel, (const __nv_bfloat16*)x.ptr, x.ld, x.n, x.h,
                                                                          x.w, x.c, (__nv_bfloat16*)y.ptr, y.ld);
   UBR_LAUNCH_CHECK("maxpool_fwd_kernel");
   return 0;
@@ -1100,8 +1139,7 @@ int ubr_maxpool3s2_bwd(ubr_view x, ubr_view dy, ubr_view dx_accum, int accumulat
   if (int rc = same_shape(x, dx_accum, "maxpool_bwd(dx)")) return rc;
   UBR_REQUIRE(dy.n == x.n && dy.c == x.c && dy.h == x.h / 2 && dy.w == x.w / 2, "maxpool_bwd: dy view mismatch");
   const long total = (long)x.n * x.h * x.w * (x.c >> 3);
-  maxpool_bwd_kernel<<<ew_blocks(total), 256, 0, (cudaStream_t)stream>>>(
-      (const __nv_bfloat16*)x.ptr, x.ld, x.n, x.h, x.w, x.c, (const __nv_bfloat16*)dy.ptr, dy.ld,
+  ::ubr::Launch(ew_blocks(total), 256, 0, (cudaStream_t)stream)(maxpool_bwd_kernel, (const __nv_bfloat16*)x.ptr, x.ld, x.n, x.h, x.w, x.c, (const __nv_bfloat16*)dy.ptr, dy.ld,
       (__nv_bfloat16*)dx_accum.ptr, dx_accum.ld, accumulate);
   UBR_LAUNCH_CHECK("maxpool_bwd_kernel");
   return 0;
@@ -1114,7 +1152,7 @@ int ubr_maxpool3s1_fwd(ubr_view x, ubr_view y, uint8_t* idx, void* stream) {
   UBR_REQUIRE(idx == nullptr || ((uintptr_t)idx & 7) == 0, "maxpool3s1_fwd: idx must be 8-byte aligned");
   if (int rc = same_shape(x, y, "maxpool3s1_fwd(y)")) return rc;
   const long total = (long)x.n * x.h * x.w * (x.c / 8);
-  maxpool3s1_fwd_kernel<<<ew_blocks(total), 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)x.ptr, x.ld, x.n, x.h, x.w,
+  ::ubr::Launch(ew_blocks(total), 256, 0, (cudaStream_t)stream)(maxpool3s1_fwd_kernel, (const __nv_bfloat16*)x.ptr, x.ld, x.n, x.h, x.w,
                                                                             x.c, (__nv_bfloat16*)y.ptr, y.ld, idx);
   UBR_LAUNCH_CHECK("maxpool3s1_fwd_kernel");
   return 0;
@@ -1127,8 +1165,7 @@ int ubr_maxpool3s1_bwd_idx(const uint8_t* idx, ubr_view dy, ubr_view dx_accum, i
   UBR_REQUIRE(idx != nullptr, "maxpool3s1_bwd_idx: null idx");
   if (int rc = same_shape(dy, dx_accum, "maxpool3s1_bwd_idx(dx)")) return rc;
   const long total = (long)dy.n * dy.h * dy.w * (dy.c / 8);
-  maxpool3s1_bwd_idx_kernel<<<ew_blocks(total), 256, 0, (cudaStream_t)stream>>>(
-      idx, dy.n, dy.h, dy.w, dy.c, (const __nv_bfloat16*)dy.ptr, dy.ld, (__nv_bfloat16*)dx_accum.ptr, dx_accum.ld, accumulate);
+  ::ubr::Launch(ew_blocks(total), 256, 0, (cudaStream_t)stream)(maxpool3s1_bwd_idx_kernel, idx, dy.n, dy.h, dy.w, dy.c, (const __nv_bfloat16*)dy.ptr, dy.ld, (__nv_bfloat16*)dx_accum.ptr, dx_accum.ld, accumulate);
   UBR_LAUNCH_CHECK("maxpool3s1_bwd_idx_kernel");
   return 0;
 }
@@ -1140,7 +1177,7 @@ int ubr_pixel_unshuffle2(ubr_view y, ubr_view y4, void* stream) {
   UBR_REQUIRE(y.h % 2 == 0 && y.w % 2 == 0 && y4.n == y.n && y4.h * 2 == y.h && y4.w * 2 == y.w && y4.c == 4 * y.c,
               "pixel_unshuffle2: shape mismatch");
   const long total = (long)y.n * y.h * y.w * (y.c / 8);
-  pixel_unshuffle2_kernel<<<ew_blocks(total), 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)y.ptr, y.ld, y4.n, y4.h,
+  ::ubr::Launch(ew_blocks(total), 256, 0, (cudaStream_t)stream)(pixel_unshuffle2_kernel, (const __nv_bfloat16*)y.ptr, y.ld, y4.n, y4.h,
                                                                               y4.w, y.c, (__nv_bfloat16*)y4.ptr, y4.ld);
   UBR_LAUNCH_CHECK("pixel_unshuffle2_kernel");
   return 0;
@@ -1150,7 +1187,7 @@ int ubr_deconv4s2_wgrad_gather(const float* dw3, int in_ch, int out_ch, float* d
   if (int rc = ensure_device()) return rc;
   UBR_REQUIRE(dw3 != nullptr && dw != nullptr && in_ch > 0 && out_ch > 0, "deconv4s2_wgrad_gather: bad arguments");
   const int total = in_ch * out_ch * 16;
-  deconv_wgrad_gather_kernel<<<(total + 255) / 256, 256, 0, (cudaStream_t)stream>>>(dw3, in_ch, out_ch, dw, accumulate);
+  ::ubr::Launch((total + 255) / 256, 256, 0, (cudaStream_t)stream)(deconv_wgrad_gather_kernel, dw3, in_ch, out_ch, dw, accumulate);
   UBR_LAUNCH_CHECK("deconv_wgrad_gather_kernel");
   return 0;
 }
@@ -1163,7 +1200,7 @@ int ubr_maxpool3s2_fwd_idx(ubr_view x, ubr_view y, uint8_t* idx, void* stream) {
   UBR_REQUIRE(x.h % 2 == 0 && x.w % 2 == 0 && y.n == x.n && y.h == x.h / 2 && y.w == x.w / 2 && y.c == x.c,
               "maxpool_fwd_idx: shape mismatch");
   const long total = (long)y.n * y.h * y.w * (x.c >> 3);
-  maxpool_fwd_idx_kernel<<<ew_blocks(total), 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)x.ptr, x.ld, x.n, x.h, x.w,
+  ::ubr::Launch(ew_blocks(total), 256, 0, (cudaStream_t)stream)(maxpool_fwd_idx_kernel, (const __nv_bfloat16*)x.ptr, x.ld, x.n, x.h, x.w,
                                                                              x.c, (__nv_bfloat16*)y.ptr, y.ld, idx);
   UBR_LAUNCH_CHECK("maxpool_fwd_idx_kernel");
   return 0;
@@ -1177,7 +1214,7 @@ int ubr_maxpool3s2_bwd_idx(const uint8_t* idx, ubr_view dy, ubr_view dx_accum, i
   UBR_REQUIRE(dx_accum.n == dy.n && dx_accum.h == 2 * dy.h && dx_accum.w == 2 * dy.w && dx_accum.c == dy.c,
               "maxpool_bwd_idx: shape mismatch");
   const long total = (long)dx_accum.n * dx_accum.h * dx_accum.w * (dy.c >> 3);
-  maxpool_bwd_idx_kernel<<<ew_blocks(total), 256, 0, (cudaStream_t)stream>>>(idx, dx_accum.n, dx_accum.h, dx_accum.w, dy.c,
+  ::ubr::Launch(ew_blocks(total), 256, 0, (cudaStream_t)stream)(maxpool_bwd_idx_kernel, idx, dx_accum.n, dx_accum.h, dx_accum.w, dy.c,
                                                                              (const __nv_bfloat16*)dy.ptr, dy.ld,
                                                                              (__nv_bfloat16*)dx_accum.ptr, dx_accum.ld,
                                                                              accumulate);
@@ -1202,7 +1239,7 @@ int ubr_add(ubr_view a, ubr_view b, ubr_view c, ubr_view out, void* stream) {
     vc = dv(c);
   }
   DView va = dv(a);
-  add_kernel<<<ew_grid(va.npix, va.c >> 3, 4), 256, 0, (cudaStream_t)stream>>>(va, vb, vc, dvw(out));
+  ::ubr::Launch(ew_grid(va.npix, va.c >> 3, 4), 256, 0, (cudaStream_t)stream)(add_kernel, va, vb, vc, dvw(out));
   UBR_LAUNCH_CHECK("add_kernel");
   return 0;
 }
@@ -1211,7 +1248,7 @@ int ubr_scale_f32(float* buf, uint64_t count, float alpha, void* stream) {
   if (int rc = ensure_device()) return rc;
   UBR_REQUIRE(buf != nullptr || count == 0, "scale_f32: null buffer");
   if (count == 0) return 0;
-  scale_f32_kernel<<<ew_blocks((long)count), 256, 0, (cudaStream_t)stream>>>(buf, (unsigned long long)count, alpha);
+  ::ubr::Launch(ew_blocks((long)count), 256, 0, (cudaStream_t)stream)(scale_f32_kernel, buf, (unsigned long long)count, alpha);
   UBR_LAUNCH_CHECK("scale_f32_kernel");
   return 0;
 }

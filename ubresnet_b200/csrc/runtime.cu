@@ -1,6 +1,7 @@
 // Library plumbing: error reporting, device gating, TMA descriptor encoding.
 #include <stdarg.h>
 #include <string.h>
+#include <stdlib.h>
 #include <atomic>
 #include <mutex>
 #include "common.cuh"
@@ -38,6 +39,15 @@ void count_launch(const char* name) {
       g_names[g_names_len] = 0;
     }
   }
+}
+
+static thread_local cudaError_t g_launch_err = cudaSuccess;
+void note_launch_error(cudaError_t e) { g_launch_err = e; }
+cudaError_t take_launch_error() { const cudaError_t e = g_launch_err; g_launch_err = cudaSuccess; return e; }
+bool pdl_enabled() {
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("UBR_PDL"); v = (e && e[0] == '0') ? 0 : 1; }
+  return v == 1;
 }
 
 static int g_dev_ok[64];       // 0 unknown, 1 ok, -1 unsupported

@@ -18,6 +18,7 @@ constexpr int kFHW = kFTW + 8, kFHH = kFTH + 6;      // tile columns start at w0
 __global__ void __launch_bounds__(256) stem_fwd_kernel(const float* __restrict__ x, int n, int h, int w,
                                                        const float* __restrict__ wgt, const float* __restrict__ bias,
                                                        int oc, __nv_bfloat16* __restrict__ y, int yld) {
+  pdl_prologue();
   __shared__ __align__(16) float tile[kFHH][kFHW];
   __shared__ __align__(16) float wsm[49][16];
   __shared__ float bsm[16];
@@ -91,6 +92,7 @@ constexpr int kWgBlocks = 296;
 __global__ void __launch_bounds__(256) stem_wgrad_kernel(const float* __restrict__ x, int n, int h, int w,
                                                          const __nv_bfloat16* __restrict__ dy, int dyld, int oc,
                                                          float* __restrict__ partials /* [blocks][ocg][50][16] */) {
+  pdl_prologue();
   __shared__ float tile[kHH][kHW + 2];
   __shared__ __align__(16) float dys[kTH * kTW][16];
   __shared__ float red[50][16];
@@ -188,6 +190,7 @@ __global__ void __launch_bounds__(256) stem_wgrad_kernel(const float* __restrict
 
 __global__ void stem_wgrad_reduce_kernel(const float* partials, int nblocks, int oc, float* dw, float* db,
                                          int accumulate) {
+  pdl_prologue();
   const int ocg = oc / 16;
   const int i = blockIdx.x * blockDim.x + threadIdx.x;      // over ocg*50*16
   if (i >= ocg * 800) return;
@@ -218,7 +221,7 @@ int ubr_stem_conv_fwd(const float* x, int n, int h, int w, const float* wgt, con
   if (stem_tc_eligible(n, h, w, out_ch))
     return stem_tc_fwd(x, n, h, w, wgt, bias, (__nv_bfloat16*)y.ptr, y.ld, (cudaStream_t)stream);
   dim3 grid(ceil_div(w, kFTW), ceil_div(h, kFTH), n * (out_ch / 16));
-  stem_fwd_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(x, n, h, w, wgt, bias, out_ch, (__nv_bfloat16*)y.ptr, y.ld);
+  ::ubr::Launch(grid, 256, 0, (cudaStream_t)stream)(stem_fwd_kernel, x, n, h, w, wgt, bias, out_ch, (__nv_bfloat16*)y.ptr, y.ld);
   UBR_LAUNCH_CHECK("stem_fwd_kernel");
   return 0;
 }
@@ -249,10 +252,10 @@ int ubr_stem_conv_wgrad(const float* x, int n, int h, int w, ubr_view dy, float*
   cudaStream_t st = (cudaStream_t)stream;
   if (stem_tc_eligible(n, h, w, dy.c) && dy.ld % 8 == 0)
     return stem_tc_wgrad(x, n, h, w, (const __nv_bfloat16*)dy.ptr, dy.ld, dw, dbias, accumulate, (float*)workspace, st);
-  stem_wgrad_kernel<<<kWgBlocks, 256, 0, st>>>(x, n, h, w, (const __nv_bfloat16*)dy.ptr, dy.ld, dy.c, (float*)workspace);
+  ::ubr::Launch(kWgBlocks, 256, 0, st)(stem_wgrad_kernel, x, n, h, w, (const __nv_bfloat16*)dy.ptr, dy.ld, dy.c, (float*)workspace);
   UBR_LAUNCH_CHECK("stem_wgrad_kernel");
   const int total = (dy.c / 16) * 800;
-  stem_wgrad_reduce_kernel<<<ceil_div(total, 128), 128, 0, st>>>((const float*)workspace, kWgBlocks, dy.c, dw, dbias,
+  ::ubr::Launch(ceil_div(total, 128), 128, 0, st)(stem_wgrad_reduce_kernel, (const float*)workspace, kWgBlocks, dy.c, dw, dbias,
                                                                  accumulate);
   UBR_LAUNCH_CHECK("stem_wgrad_reduce_kernel");
   return 0;

@@ -163,6 +163,7 @@ __device__ __forceinline__ void stem_fwd_store(const StemTcParams& p, uint32_t t
 }
 
 __global__ void __launch_bounds__(kSTThreads, 4) stem_tc_fwd_kernel(const StemTcParams p) {
+  pdl_launch_dependents();
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const StemSmem s = stem_smem_layout(base);
@@ -176,6 +177,7 @@ __global__ void __launch_bounds__(kSTThreads, 4) stem_tc_fwd_kernel(const StemTc
     tmem_alloc_dyn(s.tslot, 64);
     tmem_relinquish();
   }
+  pdl_wait();                     // the weights below are written by the optimizer step of the previous kernel chain
   // weight tiles W_hi / W_lo [16 co][64 k], K-major SW128 (slot 7 of every filter row and k >= 56 are zero)
   if (threadIdx.x < 128) {
     const int co = threadIdx.x >> 3, j = threadIdx.x & 7;
@@ -269,6 +271,7 @@ __global__ void __launch_bounds__(kSTThreads, 4) stem_tc_fwd_kernel(const StemTc
 // two im2col tiles are the two 64-channel blocks of one MN-major A operand, LBO = 16 KB apart).  One fp32
 // accumulator [128][16] per CTA lives in TMEM over all its tiles; hi + lo rows are added by the reduce kernel.
 __global__ void __launch_bounds__(kSTThreads, 4) stem_tc_wgrad_kernel(const StemTcParams p) {
+  pdl_launch_dependents();
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const StemSmem s = stem_smem_layout(base);
@@ -287,6 +290,7 @@ __global__ void __launch_bounds__(kSTThreads, 4) stem_tc_wgrad_kernel(const Stem
   tc_fence_after();
   uint32_t tmem_base;
   asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(s.tslot));
+  pdl_wait();
 
   const uint32_t idesc = make_idesc_bf16(128, 16, 1, 1);
   const int dpx = threadIdx.x >> 1, dj = threadIdx.x & 1;                 // dy tile: thread <-> (pixel, 16-byte half)
@@ -362,6 +366,7 @@ __global__ void __launch_bounds__(kSTThreads, 4) stem_tc_wgrad_kernel(const Stem
 // dbias[co] = the same for k = 56.  One block per k; 16 slices of the CTA partials per output, combined in fixed order.
 __global__ void __launch_bounds__(256) stem_tc_wgrad_reduce_kernel(const float* __restrict__ partials, int nblocks,
                                                                    float* dw, float* db, int accumulate) {
+  pdl_prologue();
   __shared__ double red[16][16];
   const int k = blockIdx.x, r = k >> 3, sl = k & 7;
   const bool is_w = r < 7 && sl < 7, is_b = k == 56;
@@ -413,7 +418,7 @@ int stem_tc_fwd(const float* x, int n, int h, int w, const float* wgt, const flo
   p.x = x; p.wgt = wgt; p.bias = bias; p.y = y; p.yld = yld; p.relu = relu;
   UBR_CUDA_OK(cudaFuncSetAttribute(stem_tc_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kStemSmemBytes));
   const int grid = p.nstrips < kStemTcMaxBlocks ? p.nstrips : kStemTcMaxBlocks;
-  stem_tc_fwd_kernel<<<grid, kSTThreads, kStemSmemBytes, st>>>(p);
+  ::ubr::Launch(grid, kSTThreads, kStemSmemBytes, st)(stem_tc_fwd_kernel, p);
   UBR_LAUNCH_CHECK("stem_tc_fwd_kernel");
   return 0;
 }
@@ -425,9 +430,9 @@ int stem_tc_wgrad(const float* x, int n, int h, int w, const __nv_bfloat16* dy, 
   p.x = x; p.dy = dy; p.dyld = dyld; p.partials = workspace;
   UBR_CUDA_OK(cudaFuncSetAttribute(stem_tc_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kStemSmemBytes));
   const int grid = p.nstrips < kStemTcMaxBlocks ? p.nstrips : kStemTcMaxBlocks;
-  stem_tc_wgrad_kernel<<<grid, kSTThreads, kStemSmemBytes, st>>>(p);
+  ::ubr::Launch(grid, kSTThreads, kStemSmemBytes, st)(stem_tc_wgrad_kernel, p);
   UBR_LAUNCH_CHECK("stem_tc_wgrad_kernel");
-  stem_tc_wgrad_reduce_kernel<<<64, 256, 0, st>>>(workspace, grid, dw, dbias, accumulate);
+  ::ubr::Launch(64, 256, 0, st)(stem_tc_wgrad_reduce_kernel, workspace, grid, dw, dbias, accumulate);
   UBR_LAUNCH_CHECK("stem_tc_wgrad_reduce_kernel");
   return 0;
 }

@@ -34,6 +34,7 @@ struct WgradParams {
 };
 
 __global__ void __launch_bounds__(kWThreads, 1) wgrad_gemm_kernel(const __grid_constant__ WgradParams p) {
+  pdl_launch_dependents();
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t bar_base = smem_base + (uint32_t)p.stages * p.stage_bytes;
@@ -76,6 +77,7 @@ __global__ void __launch_bounds__(kWThreads, 1) wgrad_gemm_kernel(const __grid_c
   tc_fence_after();
   uint32_t tmem_base;
   asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
+  pdl_wait();
 
   const uint32_t rbm = (uint32_t)p.mbox_c * 2u;     // bytes per pixel-row of an M box
   const uint32_t rbn = (uint32_t)p.nbox_c * 2u;
@@ -175,6 +177,7 @@ __global__ void __launch_bounds__(kWThreads, 1) wgrad_gemm_kernel(const __grid_c
 __global__ void wgrad_reduce_kernel(const float* __restrict__ partials, int splits, int m_ch, int m_valid, int ntaps,
                                     int n_ch, int n_valid, long sm, long st, long sn, float* __restrict__ dw,
                                     int accumulate) {
+  pdl_prologue();
   const long total = (long)m_ch * ntaps * n_ch;
   const long idx = (long)blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= total) return;
@@ -343,10 +346,10 @@ static int run_wgrad(const ubr_view& ms, const ubr_view& ns, bool n_strided, con
   }
   UBR_REQUIRE(smem <= 227u * 1024u, "wgrad: smem plan %u too large", smem);
   dim3 grid((unsigned)pl.splits, (unsigned)(pl.ngroups * pl.n_tiles), (unsigned)pl.m_tiles);
-  wgrad_gemm_kernel<<<grid, kWThreads, smem, stream>>>(p);
+  ::ubr::Launch(grid, kWThreads, smem, stream)(wgrad_gemm_kernel, p);
   UBR_LAUNCH_CHECK("wgrad_gemm_kernel");
   const long total = (long)ms.c * ntaps * ns.c;
-  wgrad_reduce_kernel<<<(unsigned)((total + 255) / 256), 256, 0, stream>>>(p.partials, pl.splits, ms.c, m_valid, ntaps,
+  ::ubr::Launch((unsigned)((total + 255) / 256), 256, 0, stream)(wgrad_reduce_kernel, p.partials, pl.splits, ms.c, m_valid, ntaps,
                                                                            ns.c, n_valid, sm, st, sn, dw, accumulate);
   UBR_LAUNCH_CHECK("wgrad_reduce_kernel");
   return 0;

@@ -50,6 +50,7 @@ __device__ __forceinline__ void mma_wg(uint32_t d_tmem, uint32_t alo, uint32_t a
 
 template <int KS, int NMMA>
 __global__ void __launch_bounds__(kWHThreads, 1) wgrad_halo_kernel(const __grid_constant__ WgradHaloParams p) {
+  pdl_launch_dependents();
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   constexpr int P2 = KS - 1;
   constexpr int PAD = (KS - 1) / 2;
@@ -84,6 +85,7 @@ __global__ void __launch_bounds__(kWHThreads, 1) wgrad_halo_kernel(const __grid_
   tc_fence_after();
   uint32_t tmem_base;
   asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
+  pdl_wait();
   if (warp >= 2) {                                   // accumulators start at zero: every MMA accumulates
     const uint32_t t_q = tmem_base + ((uint32_t)((warp & 3) * 32) << 16);
     for (uint32_t c = 0; c < p.tmem_cols; c += 16) tmem_st16_zero(t_q + c);
@@ -209,6 +211,7 @@ __global__ void __launch_bounds__(kWHThreads, 1) wgrad_halo_kernel(const __grid_
 // partials [ncta][r][s][cout][cin] -> dw OIHW [out_ch][cin][k][k]  (fixed summation order)
 __global__ void wgrad_halo_reduce_kernel(const float* __restrict__ partials, int ncta, int ksize, int cout, int cin,
                                          int out_ch, float* __restrict__ dw, int accumulate) {
+  pdl_prologue();
   const int total = ksize * ksize * cout * cin;
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= total) return;
@@ -335,10 +338,10 @@ int wgrad_halo_try(const ubr_view& x, const ubr_view& dy, int out_ch, int ksize,
   }
   UBR_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
   UBR_REQUIRE(smem <= 227u * 1024u, "wgrad(halo): smem plan %u too large", smem);
-  kern<<<ctas, kWHThreads, smem, stream>>>(p);
+  ::ubr::Launch(ctas, kWHThreads, smem, stream)(kern, p);
   UBR_LAUNCH_CHECK("wgrad_halo_kernel");
   const int total = ksize * ksize * cout * cin;
-  wgrad_halo_reduce_kernel<<<(total + 255) / 256, 256, 0, stream>>>(p.partials, ctas, ksize, cout, cin, out_ch, dw,
+  ::ubr::Launch((total + 255) / 256, 256, 0, stream)(wgrad_halo_reduce_kernel, p.partials, ctas, ksize, cout, cin, out_ch, dw,
                                                                     accumulate);
   UBR_LAUNCH_CHECK("wgrad_halo_reduce_kernel");
   return 0;

@@ -365,10 +365,9 @@ class Engine:
         self._wgrad(lambda: ops.conv2d_wgrad(saved["a10"], dl, ncls, 7, 1, grads[m.conv11.weight], False, wg_ws), dl)
         grads[m.conv11.bias].copy_(_channel_sum(dl, ncls))
         w11 = self._pack(m.conv11, True)
-        da10 = ops.conv2d_dgrad(dl, w11.dgrad, m.nkernels, 7, 1)
+        dy10 = ops.conv2d_dgrad_bn_bwd(dl, w11.dgrad, m.nkernels, 7, 1, saved["y10"], saved["st10"], True, bn_ws,
+                                       grads[m.bn10.weight], grads[m.bn10.bias])
         del dl
-        dy10 = ops.bn_act_bwd(da10, saved["y10"], saved["st10"], True, bn_ws, grads[m.bn10.weight], grads[m.bn10.bias])
-        del da10
         self._wgrad(lambda: ops.conv2d_wgrad(saved["d1"], dy10, m.nkernels, 7, 1, grads[m.conv10.weight], False, wg_ws),
                     dy10)
         grads[m.conv10.bias].copy_(_channel_sum(dy10, m.nkernels))
@@ -541,10 +540,10 @@ class Engine:
             g[blk.bnpass.bias] if has_bp else None)
         w2 = self._pack(blk.conv2, True)
         self._wgrad(lambda: ops.conv2d_wgrad(rec.a1, dy2, cout, 3, 1, g[blk.conv2.weight], False, wg_ws), dy2)
-        da1 = ops.conv2d_dgrad(dy2, w2.dgrad, cout, 3, 1)
+        # conv2 data gradient -> bn1/relu1 backward (the reduction pass rides in the conv epilogue where it can)
+        dy1 = ops.conv2d_dgrad_bn_bwd(dy2, w2.dgrad, cout, 3, 1, rec.y1, rec.st1, True, bn_ws, g[blk.bn1.weight],
+                                      g[blk.bn1.bias])
         del dy2
-        dy1 = ops.bn_act_bwd(da1, rec.y1, rec.st1, True, bn_ws, g[blk.bn1.weight], g[blk.bn1.bias])
-        del da1
         def wg1():
             ops.conv2d_wgrad(rec.x, dy1, cout, 3, s, g[blk.conv1.weight], False, wg_ws)
             if has_bp:

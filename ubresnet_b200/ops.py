@@ -169,6 +169,28 @@ def conv2d_dgrad(dy, wpk, in_ch, ksize, stride, dx=None):
     return dx
 
 
+def conv2d_dgrad_bn_bwd(dy, wpk, in_ch, ksize, stride, y_pre, st, relu, ws, dgamma=None, dbeta=None):
+    """da = dgrad(dy) followed by the backward of a = relu?(bn(y_pre)): returns the gradient wrt y_pre.  Where the conv
+    kernel has the fused reduction epilogue the stand-alone bn_act_bwd_reduce pass is skipped."""
+    import ctypes
+    lib = _lib.load()
+    da = Act.empty(dy.n, dy.h * stride, dy.w * stride, in_ch, dy.buf.device)
+    rows = ctypes.c_int(0)
+    rc = lib.ubr_conv2d_dgrad_bnreduce(dy.view(), wpk.data_ptr(), in_ch, ksize, stride, da.view(), y_pre.view(),
+                                       st.scale.data_ptr(), st.shift.data_ptr(), st.mean.data_ptr(), st.invstd.data_ptr(),
+                                       int(relu), ws.data_ptr(), ctypes.addressof(rows), _stream())
+    if rc == 1:
+        conv2d_dgrad(dy, wpk, in_ch, ksize, stride, dx=da)
+        return bn_act_bwd(da, y_pre, st, relu, ws, dgamma, dbeta)
+    _lib.check(rc, "conv2d_dgrad_bnreduce")
+    dyp = Act.empty(y_pre.n, y_pre.h, y_pre.w, y_pre.c, y_pre.buf.device)
+    _lib.check(lib.ubr_bn_act_bwd_apply_rows(da.view(), y_pre.view(), st.scale.data_ptr(), st.shift.data_ptr(),
+                                             st.mean.data_ptr(), st.invstd.data_ptr(), 0, int(relu), ws.data_ptr(),
+                                             rows.value, st.count, dyp.view(), _ptr(dgamma), _ptr(dbeta), 0, _stream()),
+               "bn_act_bwd_apply_rows")
+    return dyp
+
+
 def conv2d_dgrad_acc(dy, wpk, in_ch, ksize, stride, dx):
     """dx += dgrad(dy) fused in the conv epilogue.  Returns False (nothing done) if the shape has no fused path."""
     lib = _lib.load()
