@@ -465,13 +465,57 @@ def run_own(args, rank, world, local_rank):
             ms = float(t.item())
         return ms, launches
 
+    # ---- the loop body as ONE CUDA graph (ubresnet_b200.graphs.GraphedTrainStep): what a user who cares about
+    # throughput runs.  Eager launches (the ~520 ctypes calls per step) are measured too and reported next to it.
+    graphed = None
+    graph_note = None
+    if not args.no_graph:
+        try:
+            from ubresnet_b200.graphs import GraphedTrainStep
+            n0 = lib.ubr_launch_count()
+            graphed = GraphedTrainStep(net, crit, opt, *resident[0], warmup=3)
+            graphed.launches_per_step = int((lib.ubr_launch_count() - n0) // 4)        # 3 warm-up steps + the capture
+        except Exception as exc:                                    # capture is an optimisation: fall back loudly
+            graph_note = "CUDA-graph capture failed, eager launches timed instead: %s" % str(exc)[:300]
+            graphed = None
+            torch.cuda.synchronize()
+
+    def step_graphed(i):
+        img, lab, wgt = resident[i % nbuf]
+        return graphed(img, lab, wgt)
+
+    def step_e2e_graphed(i):
+        if "it" not in feed:
+            feed["it"] = DevicePrefetcher(wire_batches(), dev)
+        planes, rois = next(feed["it"])
+        filler.fill(planes, rois, S, S, out=graphed.inputs)          # assembled straight into the graph's static inputs
+        loss = graphed.replay()
+        j = i & 1
+        loss_host[j].copy_(loss, non_blocking=True)                   # device -> host read of the step's result
+        loss_ready[j] = torch.cuda.Event()
+        loss_ready[j].record()
+        if loss_ready[j ^ 1] is not None:
+            loss_ready[j ^ 1].synchronize()
+            losses_seen.append(float(loss_host[j ^ 1]))
+        return None
+
     sampler = ClockSampler(local_rank) if rank == 0 else None
     if sampler:
         sampler.start()
-    ms, launches = timed(step_resident, args.steps, args.warmup)
+    eager = None
+    if graphed is not None:
+        ms_eager, launches = timed(step_resident, max(3, args.steps // 2), args.warmup)
+        eager = {"value": world * B * max(3, args.steps // 2) / (ms_eager * 1e-3), "unit": UNIT,
+                 "ms_per_step": ms_eager / max(3, args.steps // 2), "host_enqueue_ms_per_step": host_ms[0],
+                 "what": "the same step issued kernel by kernel from Python (no CUDA graph)"}
+        launches_per_step = graphed.launches_per_step
+        ms, _ = timed(step_graphed, args.steps, args.warmup)
+        launches = launches_per_step * args.steps
+    else:
+        ms, launches = timed(step_resident, args.steps, args.warmup)
     host_enqueue_ms = host_ms[0]
     clocks = sampler.stop() if sampler else None
-    ms_e2e, _ = timed(step_e2e, args.steps, 1)
+    ms_e2e, _ = timed(step_e2e_graphed if graphed is not None else step_e2e, args.steps, max(3, args.warmup))
     value = world * B * args.steps / (ms * 1e-3)
     e2e = world * B * args.steps / (ms_e2e * 1e-3)
 
@@ -647,6 +691,9 @@ def run_own(args, rank, world, local_rank):
                     "device_fill_equals_host_batch": fill_ok, "device_fill_ms_per_batch": fill_ms},
             "gpu_launches": int(launches),
             "host_enqueue_ms_per_step": host_enqueue_ms,
+            "launch_mode": ("one CUDA graph per step (ubresnet_b200.graphs.GraphedTrainStep: forward + loss + backward "
+                            "+ all-reduce + optimizer captured once, %d kernels per replay)" % (launches // max(1, args.steps)))
+                           if graphed is not None else (graph_note or "eager: one ctypes call per kernel"),
             "utilisation": {"conv_tflops_whole_step": GF_TRAIN * B * world * args.steps / (ms * 1e-3) / 1e3 / world,
                             "note": "algorithmic conv FLOPs (199.41 GF/crop) / step time, per GPU"},
         }
@@ -656,6 +703,8 @@ def run_own(args, rank, world, local_rank):
             line["cpu_baseline"] = cpu
         if library:
             line["library_baseline"] = library
+        if eager:
+            line["eager"] = eager
         if dp_check:
             line["dp_check"] = dp_check
         if aspp:
@@ -688,6 +737,7 @@ def main():
                     help="also time the oracle port through PyTorch/cuDNN on the same GPU (bf16 autocast, tf32, fp32)")
     ap.add_argument("--no-library", action="store_true", help="skip the PyTorch/cuDNN bf16 comparison leg (N=1)")
     ap.add_argument("--no-aspp", action="store_true", help="skip the ASPP_ResNet (configs[4]) extra measurement (N=1)")
+    ap.add_argument("--no-graph", action="store_true", help="time eager kernel-by-kernel launches only")
     ap.add_argument("--no-infer", action="store_true", help="skip the eval-forward and whole-view measurements")
     ap.add_argument("--verbose", action="store_true")
     ap.add_argument("--kernel-log", default="")

@@ -643,6 +643,41 @@ def fused_bn_reduce():
     return res, {}
 
 
+def graphed_step():
+    """ubresnet_b200.graphs.GraphedTrainStep: the captured loop body replays to the same losses and weights as the eager
+    loop from the same start (same kernels, same order)"""
+    from ubresnet_b200.graphs import GraphedTrainStep
+    from ubresnet_b200.training.optim import SGD
+    crit = PixelWiseNLLLoss()
+    batches = [tuple(t.to(DEV) for t in synthetic.make_batch(2, 128, 128, step=s)) for s in range(6)]
+    kw = dict(lr=1e-2, momentum=0.9, weight_decay=1e-3)
+    # eager: 3 warm-up steps on batch 0 (what GraphedTrainStep does internally), then batches 1..5
+    model, _ = build_pair(seed=61)
+    model.train()
+    opt = SGD(model.parameters(), **kw)
+    ref = []
+    for b in [batches[0]] * 3 + batches[1:]:
+        opt.zero_grad(set_to_none=True)
+        loss = crit(model(b[0]), b[1], b[2])
+        loss.backward()
+        opt.step()
+        ref.append(loss.item())
+    ref = ref[3:]
+    model2, _ = build_pair(seed=61)
+    model2.train()
+    opt2 = SGD(model2.parameters(), **kw)
+    step = GraphedTrainStep(model2, crit, opt2, *batches[0], warmup=3)
+    got = [step(*b).item() for b in batches[1:]]
+    res = [("graph_replay_loss_step%d_vs_eager" % i, abs(got[i] - ref[i]) / abs(ref[i]), 1e-6) for i in range(len(ref))]
+    worst = max(_rel(p2, p1) for p1, p2 in zip(model.parameters(), model2.parameters()))
+    res.append(("weights_after_5_replays_vs_eager", worst, 1e-6))
+    # an eager eval forward after the replays sees the replayed weights (version counters advanced by replay())
+    with torch.no_grad():
+        model.eval(); model2.eval()
+        res.append(("eval_after_replays_matches_eager_model", _rel(model2(batches[0][0]), model(batches[0][0])), 1e-6))
+    return res, {}
+
+
 CHECKS = {
     "train_128": lambda: train_parity(2, 128),
     "train_dense_64": lambda: train_parity(4, 64, dense=True, seed=99),
@@ -657,6 +692,7 @@ CHECKS = {
     "golden": lambda: golden_parity(),
     "advice_regressions": lambda: advice_regressions(),
     "fused_bn_reduce": lambda: fused_bn_reduce(),
+    "graphed_step": lambda: graphed_step(),
     # fp32 precision mode: 1e-4 against the fp32 oracle
     "fp32_ops": lambda: fp32_ops(),
     "fp32_train_128_trained": lambda: fp32_parity(2, 128, trained=True, train=True),

@@ -187,8 +187,9 @@ class Engine:
         key = tuple(jobs)
         cache = getattr(self, "_job_cache", None)
         if cache is None or cache[0] != key:
-            table = torch.tensor(jobs, dtype=torch.int64).to(m.conv1.weight.device)
-            self._job_cache = cache = (key, table)
+            host = torch.tensor(jobs, dtype=torch.int64).pin_memory()       # pinned + async: legal under graph capture
+            table = host.to(m.conv1.weight.device, non_blocking=True)
+            self._job_cache = cache = (key, table, host)
         ops.pack_weights_batch(cache[1], len(jobs))
 
     def _workspaces(self, n, h, w, device):

@@ -54,7 +54,8 @@ class DeviceBatchFiller:
         self._bad = torch.zeros(1, dtype=torch.int32, device=self.device)
         self._ws = None
 
-    def fill(self, image_planes, label_planes, rows, cols, mirror=None, check=False):
+    def fill(self, image_planes, label_planes, rows, cols, mirror=None, check=False, out=None):
+        """out: optional (image, label, weight) device tensors to fill in place (e.g. the static inputs of a CUDA graph)"""
         lib = _lib.load()
         img = image_planes.to(self.device, non_blocking=True)
         lab = label_planes.to(self.device, non_blocking=True)
@@ -64,10 +65,18 @@ class DeviceBatchFiller:
         mir = None
         if mirror is not None:
             mir = torch.as_tensor(mirror, dtype=torch.uint8).to(self.device, non_blocking=True)
-        out_img = torch.empty((b, 1, rows, cols), dtype=torch.float32, device=self.device)
-        out_lab = torch.empty((b, rows, cols), dtype=torch.int64, device=self.device)
-        out_w = torch.empty((b, rows, cols), dtype=torch.float32, device=self.device)
-        cls8 = torch.empty((b, rows, cols), dtype=torch.uint8, device=self.device)
+        if out is not None:
+            out_img, out_lab, out_w = out
+            assert out_img.shape == (b, 1, rows, cols) and out_img.dtype == torch.float32 and out_img.is_contiguous()
+            assert out_lab.shape == (b, rows, cols) and out_lab.dtype == torch.int64 and out_lab.is_contiguous()
+            assert out_w.shape == (b, rows, cols) and out_w.dtype == torch.float32 and out_w.is_contiguous()
+        else:
+            out_img = torch.empty((b, 1, rows, cols), dtype=torch.float32, device=self.device)
+            out_lab = torch.empty((b, rows, cols), dtype=torch.int64, device=self.device)
+            out_w = torch.empty((b, rows, cols), dtype=torch.float32, device=self.device)
+        if getattr(self, "_cls8", None) is None or self._cls8.shape != (b, rows, cols):
+            self._cls8 = torch.empty((b, rows, cols), dtype=torch.uint8, device=self.device)
+        cls8 = self._cls8
         _lib.check(lib.ubr_fill_image_batch(img.contiguous().data_ptr(), _DTYPE_CODE[img.dtype], b, rows, cols, _ptr(mir),
                                             out_img.data_ptr(), _stream()), "fill_image_batch")
         _lib.check(lib.ubr_fill_label_batch(lab.contiguous().data_ptr(), _DTYPE_CODE[lab.dtype], b, rows, cols, _ptr(mir),

@@ -51,11 +51,17 @@ class _Tables:
             chunks.extend((i, 0, off) for off in range(0, n, chunk))
         carr = (_Chunk * len(chunks))(*[_Chunk(*c) for c in chunks])
 
+        keep = []
+
         def upload(arr):
-            host = torch.frombuffer(bytearray(bytes(arr)), dtype=torch.uint8)
-            return host.to(device)
+            # pinned staging + asynchronous copy: legal inside CUDA-graph capture (ubresnet_b200.graphs), where the
+            # gradient pointers of the captured step differ from the warm-up ones; the pinned source stays alive
+            host = torch.frombuffer(bytearray(bytes(arr)), dtype=torch.uint8).pin_memory()
+            keep.append(host)
+            return host.to(device, non_blocking=True)
 
         self.slots, self.chunks, self.nchunks, self.key = upload(slots), upload(carr), len(chunks), key
+        self._host = keep
 
 
 def _mark_modified(tensors):
