@@ -7,7 +7,7 @@
 set -u
 TAG=${1:-prof}
 OUT=gpurun_out
-CMD="env UBR_WGRAD_STREAM=0 python bench.py --steps 1 --warmup 1 --no-cpu --no-infer"
+CMD="env UBR_WGRAD_STREAM=0 python bench.py --steps 1 --warmup 1 --no-cpu --no-infer --no-graph --no-library --no-aspp"
 mkdir -p $OUT
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 6000 --csv --log-file $OUT/${TAG}_launches.csv $CMD > $OUT/${TAG}_ncu_list.log 2>&1
 echo "launch list rc=$?"
@@ -25,8 +25,10 @@ timeout 900 ncu --metrics $M --clock-control none -k regex:"conv_gemm_kernel|wgr
 echo "traffic pass rc=$?"
 if [ -z "${SKIP_FULL:-}" ]; then
 timeout 600 ncu --set full --clock-control none --import-source on -k regex:"conv_gemm_kernel|wgrad_gemm_kernel" --launch-skip 290 -c 10 -o /tmp/${TAG}_gemm_full $CMD > $OUT/${TAG}_ncu_full.log 2>&1
-echo "set full rc=$?"
+echo "set full (gemm) rc=$?"
 ncu -i /tmp/${TAG}_gemm_full.ncu-rep --page raw --csv > $OUT/${TAG}_gemm_full_raw.csv 2>/dev/null
-ncu -i /tmp/${TAG}_gemm_full.ncu-rep --page details --csv > $OUT/${TAG}_gemm_full_details.csv 2>/dev/null
+timeout 600 ncu --set full --clock-control none --import-source on -k regex:"conv_halo_kernel" --launch-skip 100 -c 12 -o /tmp/${TAG}_halo_full $CMD > $OUT/${TAG}_ncu_full_halo.log 2>&1
+echo "set full (halo) rc=$?"
+ncu -i /tmp/${TAG}_halo_full.ncu-rep --page raw --csv > $OUT/${TAG}_halo_full_raw.csv 2>/dev/null
 fi
 ls -la $OUT
