@@ -17,7 +17,7 @@ PER=$(python - <<PY
 import csv,re
 rows=[l for l in open("$OUT/${TAG}_launches.csv") if l.startswith('"')]
 n=sum(1 for r in csv.DictReader(rows) if re.search(r"conv_gemm_kernel|wgrad_gemm_kernel|halo_kernel", r["Kernel Name"]))
-print(n//6)
+print(n//8)      # steps in the run: 1 warm-up + 1 timed, e2e 3 + 1, 2 profiling steps
 PY
 )
 echo "conv kernel launches per step: $PER"

@@ -9,13 +9,16 @@ import sys
 
 def main():
     path, tag = sys.argv[1], sys.argv[2]
-    rows = list(csv.DictReader([l for l in open(path) if l.startswith('"')]))
+    per_step = int(sys.argv[3]) if len(sys.argv) > 3 else 0     # conv-kernel launches of ONE step: trim the capture to
+    rows = list(csv.DictReader([l for l in open(path) if l.startswith('"')]))   # one period (any cyclic window is one step)
     by = collections.OrderedDict()
     mult = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "ns": 1.0, "us": 1e3, "ms": 1e6}
     for r in rows:
         e = by.setdefault(r["ID"], {"name": re.sub(r"\(.*", "", r["Kernel Name"]).replace("void ", "").replace("ubr::", ""),
                                     "grid": r["Grid Size"]})
         e[r["Metric Name"]] = float(r["Metric Value"].replace(",", "")) * mult.get(r["Metric Unit"], 1.0)
+    if per_step and len(by) > per_step:
+        by = collections.OrderedDict(list(by.items())[:per_step])
     out_csv = "profiles/%s_conv_traffic_one_step.csv" % tag
     agg = collections.OrderedDict()
     with open(out_csv, "w", newline="") as fh:

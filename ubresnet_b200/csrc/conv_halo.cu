@@ -534,6 +534,14 @@ int conv_halo_try(const ubr_view& x, const void* wpk, int nslabs, int n_pad, con
   int bh = 32;
   while (bh > 1 && x.h % bh != 0) bh >>= 1;
   if (bh < 8) return 1;
+  {
+    // small images (128^2 layers at batch 32: 128 tiles of 32 rows for 148-296 resident CTAs) leave SMs idle and every
+    // CTA pays its pipeline fill once for a single tile: shorter bands give each CTA >= 2 tiles (UBR_HALO_MIN_TILES per
+    // SM; the extra halo rows cost 2*pad/bh more reads)
+    static const int min_tiles = [] { const char* e = getenv("UBR_HALO_MIN_TILES"); return e ? atoi(e) : 0; }();
+    if (min_tiles > 0)
+      while (bh > 8 && (x.h / bh) * (x.w / 128) * x.n < min_tiles * sm_count() && x.h % (bh / 2) == 0) bh >>= 1;
+  }
   const uint32_t span = (uint32_t)cin * 2u;
   const uint32_t row_bytes = (uint32_t)(128 + 2 * pad) * span;
   const uint32_t slot_bytes = (row_bytes + 1023u) & ~1023u;
