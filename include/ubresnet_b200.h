@@ -349,6 +349,12 @@ int ubr_seg_weights(const void* label, int label_dtype, int column_major, int ba
                     float weight_max, const float* weight_in, float* weight_out, void* workspace, uint64_t workspace_bytes,
                     void* stream);
 
+/* out[0:nvalid) (+)= sum over pixels of a[., 0:nvalid): the bias gradient of a biased conv (ub_uresnet.py:41,60,64);
+ * workspace: ubr_bn_workspace_bytes(a.c).  ubr_increment_i64: *ptrs[i] += 1 for a DEVICE table of int64 scalars
+ * (BatchNorm2d.num_batches_tracked of all 52 layers in one launch). */
+int ubr_channel_sum(ubr_view a, int nvalid, void* workspace, float* out, int accumulate, void* stream);
+int ubr_increment_i64(int64_t* const* ptrs_device, int n, void* stream);
+
 /* ---- flat-buffer helpers for the data-parallel gradient buckets --------------------------------- */
 int ubr_scale_f32(float* buf, uint64_t count, float alpha, void* stream);
 

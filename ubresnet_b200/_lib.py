@@ -83,6 +83,8 @@ SIGNATURES = {
     "ubr_stitch_scatter_rect": (_i, [_vp, _i, _vp, _i, _i, _i, _i, _i, _vp, _vp]),
     "ubr_accuracy_counts": (_i, [_vp, _vp, _i, _i, _i, _vp, _vp]),
     "ubr_scale_f32": (_i, [_vp, _u64, _f, _vp]),
+    "ubr_channel_sum": (_i, [View, _i, _vp, _vp, _i, _vp]),
+    "ubr_increment_i64": (_i, [_vp, _i, _vp]),
     "ubr_fill_image_batch": (_i, [_vp, _i, _i, _i, _i, _vp, _vp, _vp]),
     "ubr_fill_label_batch": (_i, [_vp, _i, _i, _i, _i, _vp, _vp, _i, _i, _vp, _vp, _vp, _vp]),
     "ubr_seg_weights_workspace_bytes": (_u64, [_i, _i, _i]),

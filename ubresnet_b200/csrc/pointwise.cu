@@ -300,6 +300,21 @@ __global__ void __launch_bounds__(kRedThreads, 2) bn_act_bwd_reduce_kernel(DView
   block_reduce_store<2>(acc, y.c, partials);
 }
 
+// per-channel pixel sums (conv bias gradients): partials[nb][2][c] of bn_stats -> out[0:nvalid) (fixed order, double)
+__global__ void channel_sum_finish_kernel(const float* partials, int nb, int c, int nvalid, float* out, int accumulate) {
+  pdl_prologue();
+  const int i = blockIdx.x * 32 + threadIdx.x;
+  const double s = col_sum_32x8(partials, nb, 2 * c, i, i < c);
+  if (i < nvalid && threadIdx.y == 0) out[i] = (accumulate ? out[i] : 0.f) + (float)s;
+}
+
+// bumps a list of int64 scalars (BatchNorm2d.num_batches_tracked of every layer) by one
+__global__ void increment_i64_kernel(long long* const* ptrs, int n) {
+  pdl_prologue();
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) *ptrs[i] += 1;
+}
+
 // sums partials[nb][NS][C] -> sums[NS][C] (fixed order, double); grid = ceil(nsc/32), block = (32, 8)
 struct ParamGradOut { float* p[4]; };    // per sum row: optional fp32 parameter-gradient vector of c entries (dbeta / dgamma)
 __global__ void sums_finalize_kernel(const float* partials, int nb, int nsc, float* sums, int c, ParamGradOut out,
@@ -1241,6 +1256,29 @@ int ubr_add(ubr_view a, ubr_view b, ubr_view c, ubr_view out, void* stream) {
   DView va = dv(a);
   ::ubr::Launch(ew_grid(va.npix, va.c >> 3, 4), 256, 0, (cudaStream_t)stream)(add_kernel, va, vb, vc, dvw(out));
   UBR_LAUNCH_CHECK("add_kernel");
+  return 0;
+}
+
+int ubr_channel_sum(ubr_view a, int nvalid, void* workspace, float* out, int accumulate, void* stream) {
+  if (int rc = ensure_device()) return rc;
+  if (int rc = chk_red(a, "channel_sum.a")) return rc;
+  UBR_REQUIRE(workspace && out && nvalid >= 1 && nvalid <= a.c, "channel_sum: bad arguments");
+  DView v = dv(a);
+  const int nb = red_blocks(v.npix, v.c);
+  cudaStream_t st = (cudaStream_t)stream;
+  ::ubr::Launch(nb, kRedThreads, kRedThreads * 16 * sizeof(float), st)(bn_stats_kernel, v, (float*)workspace);
+  UBR_LAUNCH_CHECK("bn_stats_kernel");
+  ::ubr::Launch(ceil_div(v.c, 32), dim3(32, kColLanes), 0, st)(channel_sum_finish_kernel, (const float*)workspace, nb, v.c,
+                                                               nvalid, out, accumulate);
+  UBR_LAUNCH_CHECK("channel_sum_finish_kernel");
+  return 0;
+}
+
+int ubr_increment_i64(int64_t* const* ptrs_device, int n, void* stream) {
+  if (int rc = ensure_device()) return rc;
+  UBR_REQUIRE(ptrs_device != nullptr && n >= 1, "increment_i64: bad arguments");
+  ::ubr::Launch(ceil_div(n, 128), 128, 0, (cudaStream_t)stream)(increment_i64_kernel, (long long* const*)ptrs_device, n);
+  UBR_LAUNCH_CHECK("increment_i64_kernel");
   return 0;
 }
 

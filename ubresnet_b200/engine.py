@@ -350,12 +350,23 @@ class Engine:
         if self.keep_logits:
             self.last_logits = logits.view(n, h, w, ld)[..., :ncls].permute(0, 3, 1, 2).contiguous()
         if training:
-            with torch.no_grad():
-                bns = [mod.num_batches_tracked for mod in m.modules()
-                       if isinstance(mod, torch.nn.BatchNorm2d) and mod.num_batches_tracked is not None]
-                if bns:
-                    torch._foreach_add_(bns, 1)
+            self._bump_batches_tracked()
         return y10, st10, a10, logp
+
+    def _bump_batches_tracked(self):
+        """num_batches_tracked += 1 for every BatchNorm2d of the model: one launch over a device pointer table"""
+        m = self.model
+        bns = [mod.num_batches_tracked for mod in m.modules()
+               if isinstance(mod, torch.nn.BatchNorm2d) and mod.num_batches_tracked is not None]
+        if not bns:
+            return
+        key = tuple(t.data_ptr() for t in bns)
+        cache = getattr(self, "_nbt_cache", None)
+        if cache is None or cache[0] != key:
+            host = torch.tensor(key, dtype=torch.int64).pin_memory()
+            cache = self._nbt_cache = (key, host.to(bns[0].device, non_blocking=True), host)
+        ops._lib.check(ops._lib.load().ubr_increment_i64(cache[1].data_ptr(), len(bns), ops._stream()), "increment_i64")
+        torch.autograd.graph.increment_version(bns)
 
     def _head_bwd(self, saved, dlogp, grads, bn_ws, wg_ws):
         """backward of the head; returns the gradient wrt the last decoder output."""
@@ -364,14 +375,14 @@ class Engine:
         ncls = m.conv11.out_channels
         dl = ops.logsoftmax_bwd(saved["logp"], dlogp.float())
         self._wgrad(lambda: ops.conv2d_wgrad(saved["a10"], dl, ncls, 7, 1, grads[m.conv11.weight], False, wg_ws), dl)
-        grads[m.conv11.bias].copy_(_channel_sum(dl, ncls))
+        _bias_grad(dl, grads[m.conv11.bias], bn_ws)
         w11 = self._pack(m.conv11, True)
         dy10 = ops.conv2d_dgrad_bn_bwd(dl, w11.dgrad, m.nkernels, 7, 1, saved["y10"], saved["st10"], True, bn_ws,
                                        grads[m.bn10.weight], grads[m.bn10.bias])
         del dl
         self._wgrad(lambda: ops.conv2d_wgrad(saved["d1"], dy10, m.nkernels, 7, 1, grads[m.conv10.weight], False, wg_ws),
                     dy10)
-        grads[m.conv10.bias].copy_(_channel_sum(dy10, m.nkernels))
+        _bias_grad(dy10, grads[m.conv10.bias], bn_ws)
         w10 = self._pack(m.conv10, True)
         return ops.conv2d_dgrad(dy10, w10.dgrad, p, 7, 1)
 
@@ -621,18 +632,11 @@ class Engine:
         return grads
 
 
-def _channel_sum(a, nvalid):
-    """per-channel sum over pixels of an Act (bias gradients): tiny, done with the BN statistics kernels."""
-    dev = a.buf.device
-    ws = ops.bn_workspace(a.c, dev)
-    st = ops.BNState(a.c, dev)
-    lib = ops._lib.load()
-    ops._lib.check(lib.ubr_bn_stats(a.view(), ws.data_ptr(), ops._stream()), "bn_stats")
-    # finalize with gamma = beta = NULL: mean = sum / count
-    ops._lib.check(lib.ubr_bn_finalize(ws.data_ptr(), a.c, float(a.npix), 0, 0, 0, 0, 0.0, 1e-5, st.scale.data_ptr(),
-                                       st.shift.data_ptr(), st.mean.data_ptr(), st.invstd.data_ptr(), ops._stream()),
-                   "bn_finalize")
-    return (st.mean * float(a.npix))[:nvalid]
+def _bias_grad(a, out, ws):
+    """out[:] = per-channel sum over pixels of the first out.numel() channels of `a` (the bias gradient of a biased
+    conv), written by the library into the gradient tensor: two launches, no torch op"""
+    ops._lib.check(ops._lib.load().ubr_channel_sum(a.view(), out.numel(), ws.data_ptr(), out.data_ptr(), 0, ops._stream()),
+                   "channel_sum")
 
 
 class _UResNetFn(torch.autograd.Function):

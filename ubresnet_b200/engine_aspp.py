@@ -17,7 +17,7 @@ import torch
 
 from . import engine as _engine
 from . import ops
-from .engine import Engine, _UResNetFn, _channel_sum  # noqa: F401
+from .engine import Engine, _UResNetFn, _bias_grad  # noqa: F401
 from .ops import Act
 
 _BRANCHES = (("B1", 1, 1), ("B2", 3, 1), ("B3", 3, 3), ("B4", 3, 5))      # (prefix, ksize, dilation)
@@ -101,7 +101,7 @@ class ASPPEngine(Engine):
         cin = rec.e.c
         dyc = ops.bn_act_bwd(d_aspp, rec.yc, rec.stc, True, bn_ws, g[post.ASPP_bn.weight], g[post.ASPP_bn.bias])
         self._wgrad(lambda d=dyc: ops.conv2d_wgrad(rec.acat, d, cin, 1, 1, g[post.ASPP_conv.weight], False, wg_ws), dyc)
-        g[post.ASPP_conv.bias].copy_(_channel_sum(dyc, cin))
+        _bias_grad(dyc, g[post.ASPP_conv.bias], bn_ws)
         wc = self._pack(post.ASPP_conv, True)
         dacat = ops.conv2d_dgrad(dyc, wc.dgrad, 64 + cin, 1, 1)
         del dyc
@@ -119,7 +119,7 @@ class ASPPEngine(Engine):
                 self._wgrad(lambda d=dyb, c=conv, dl=dil: ops.conv2d_dilated_wgrad(rec.e, d, 16, dl, g[c.weight], False,
                                                                                  wg_ws), dyb)
                 parts.append(ops.conv2d_dilated_dgrad(dyb, wpk.dgrad, cin, dil))
-            g[conv.bias].copy_(_channel_sum(dyb, 16))
+            _bias_grad(dyb, g[conv.bias], bn_ws)
             if len(parts) == 2:
                 ops.add(acc, parts[0], parts[1], out=acc)
                 parts = []

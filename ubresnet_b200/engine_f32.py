@@ -246,11 +246,8 @@ class EngineF32:
         if self.keep_logits:
             self.last_logits = logits.buf.permute(0, 3, 1, 2).contiguous()
         if training:
-            with torch.no_grad():
-                bns = [mod.num_batches_tracked for mod in m.modules()
-                       if isinstance(mod, torch.nn.BatchNorm2d) and mod.num_batches_tracked is not None]
-                if bns:
-                    torch._foreach_add_(bns, 1)
+            from .engine import Engine
+            Engine._bump_batches_tracked(self)
         saved = None
         if need_grad:
             saved = dict(xin=xin, y0=y0, st0=st0, x0=x0, pool_idx=pool_idx, recs=recs, dec_in=dec_in, d1=cur, y10=y10,

@@ -51,17 +51,41 @@ class _Tables:
             chunks.extend((i, 0, off) for off in range(0, n, chunk))
         carr = (_Chunk * len(chunks))(*[_Chunk(*c) for c in chunks])
 
+        capturing = torch.cuda.is_current_stream_capturing()
+        # pinned staging + asynchronous copy (legal inside CUDA-graph capture, ubresnet_b200.graphs).  Outside capture a
+        # ring of 4 staging sets is REUSED -- gradient pointers may change every step (pinning memory costs
+        # milliseconds) and the host must not wait for the step that is still running; under capture the source must
+        # stay untouched for the life of the graph, so it gets buffers of its own
+        ring = getattr(self, "_ring", None)
+        if ring is None:
+            ring = self._ring = {"i": 0, "sets": [dict() for _ in range(4)], "done": [None] * 4}
         keep = []
+        k = ring["i"] % 4
+        if not capturing:
+            ring["i"] += 1
+            if ring["done"][k] is not None:
+                ring["done"][k].synchronize()       # the upload issued 4 updates ago has left this set
 
-        def upload(arr):
-            # pinned staging + asynchronous copy: legal inside CUDA-graph capture (ubresnet_b200.graphs), where the
-            # gradient pointers of the captured step differ from the warm-up ones; the pinned source stays alive
-            host = torch.frombuffer(bytearray(bytes(arr)), dtype=torch.uint8).pin_memory()
-            keep.append(host)
+        def upload(arr, slot):
+            raw = torch.frombuffer(bytearray(bytes(arr)), dtype=torch.uint8)
+            if capturing:
+                host = raw.pin_memory()
+                keep.append(host)
+            else:
+                stage = ring["sets"][k]
+                host = stage.get(slot)
+                if host is None or host.numel() < raw.numel():
+                    host = stage[slot] = torch.empty(max(raw.numel(), 1 << 16), dtype=torch.uint8).pin_memory()
+                host = host[:raw.numel()]
+                host.copy_(raw)
             return host.to(device, non_blocking=True)
 
-        self.slots, self.chunks, self.nchunks, self.key = upload(slots), upload(carr), len(chunks), key
-        self._host = keep
+        self.slots, self.chunks, self.nchunks, self.key = upload(slots, 0), upload(carr, 1), len(chunks), key
+        if capturing:
+            self._host = getattr(self, "_host", []) + keep
+        else:
+            ring["done"][k] = torch.cuda.Event()
+            ring["done"][k].record()
 
 
 def _mark_modified(tensors):
