@@ -257,6 +257,10 @@ def _conv_call_work(fn, a):
         dy, in_ch, k, st = a[0], a[2], a[3], a[4]
         b = 2.0 * (npx(dy) * dy[3] + npx(dy) * st * st * in_ch * (2 if fn.endswith("_acc") else 1))
         return 2.0 * npx(dy) * dy[3] * in_ch * k * k, b
+    if fn == "ubr_conv2d_dgrad_bnreduce":
+        # data gradient + the BatchNorm-backward reduction it carries: reads dy and y_pre, writes dx
+        dy, in_ch, k = a[0], a[2], a[3]
+        return 2.0 * npx(dy) * dy[3] * in_ch * k * k, 2.0 * (npx(dy) * dy[3] + 2 * npx(dy) * in_ch)
     if fn == "ubr_conv2d_wgrad":
         x, dy, out_ch, k = a[0], a[1], a[2], a[3]
         return 2.0 * npx(dy) * x[3] * out_ch * k * k, 2.0 * (npx(x) * x[3] + npx(dy) * dy[3])
