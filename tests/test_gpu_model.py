@@ -116,6 +116,19 @@ def test_wholeview_run_events_pipeline_matches_run_event():
     assert len(one) == 1 and torch.equal(one[0], refs[0])
 
 
+def test_nn_dataparallel_wrapping():
+    """`nn.DataParallel(model)` (train_ubresnet2018_wlarcv2.py:99,103): needs >= 2 GPUs in one process"""
+    import os
+    import subprocess
+    import sys
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs >= 2 GPUs")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, os.path.join(root, "tools", "dataparallel_check.py")], capture_output=True, text=True,
+                       timeout=300)
+    assert r.returncode == 0, r.stdout[-500:] + r.stderr[-500:]
+
+
 @pytest.mark.parametrize("arch", ["uresnet", "aspp"])
 def test_training_step_is_bit_deterministic(arch):
     """tools/determinism_check.py: repeated steps under allocator perturbation give bit-identical losses and gradients

@@ -22,6 +22,18 @@ from .ops import Act
 WGRAD_SIDE_STREAM = os.environ.get("UBR_WGRAD_STREAM", "1") != "0"
 
 
+def model_params(m):
+    """`list(m.parameters())`, also for an `nn.DataParallel` replica: replicate() leaves a replica's `_parameters` empty
+    and keeps the broadcast copies (non-leaf tensors) as plain attributes + `_former_parameters`"""
+    ps = list(m.parameters())
+    if ps:
+        return ps
+    out = []
+    for mod in m.modules():
+        out.extend(v for v in getattr(mod, "_former_parameters", {}).values() if v is not None)
+    return out
+
+
 class _FoldedConv:
     """Inference operands of conv -> BatchNorm(eval): W' = W * gamma/sqrt(var+eps) per output channel (packed bf16),
     b' = beta - mean*scale (+ conv bias*scale), fp32.  Re-derived when any of the six tensors changes."""
@@ -256,10 +268,10 @@ class Engine:
         first -- otherwise this backward would overwrite it and AccumulateGrad would add the new gradient onto itself."""
         m = self.model
         if sink is None:
-            return {prm: torch.empty_like(prm, dtype=torch.float32) for prm in m.parameters()}
+            return {prm: torch.empty_like(prm, dtype=torch.float32) for prm in model_params(m)}
         grads = {}
         with torch.no_grad():
-            for prm in m.parameters():
+            for prm in model_params(m):
                 if prm.requires_grad and prm in sink.views:
                     if sink.aliases(prm):
                         prm.grad = prm.grad.clone()
@@ -480,7 +492,7 @@ class Engine:
             raise RuntimeError("UResNet: H and W must be multiples of 32 (5 stride-2 stages), got %dx%d" % tuple(x.shape[2:]))
         if m.conv1.weight.device != x.device:
             raise RuntimeError("UResNet: parameters on %s but input on %s" % (m.conv1.weight.device, x.device))
-        params = list(m.parameters())                    # ONE walk of the module tree per call (host time before
+        params = model_params(m)                         # ONE walk of the module tree per call (host time before
         trainable = torch.is_grad_enabled() and any(p.requires_grad for p in params)                  # the first launch)
         if x.requires_grad and torch.is_grad_enabled():
             raise RuntimeError("ubresnet_b200: gradients with respect to the input image are not implemented (the "

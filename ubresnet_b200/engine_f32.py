@@ -191,7 +191,8 @@ class EngineF32:
         if m.conv1.weight.device != x.device:
             raise RuntimeError("UResNet: parameters on %s but input on %s" % (m.conv1.weight.device, x.device))
         self.lib = _lib.load()
-        params = list(m.parameters())
+        from .engine import model_params
+        params = model_params(m)
         trainable = torch.is_grad_enabled() and any(p.requires_grad for p in params)
         if x.requires_grad and torch.is_grad_enabled():
             raise RuntimeError("ubresnet_b200: gradients with respect to the input image are not implemented")
@@ -260,7 +261,8 @@ class EngineF32:
         n, h, w = saved["shape"]
         dev = dlogp.device
         ws = self._workspace(dev)
-        grads = {prm: torch.empty_like(prm, dtype=torch.float32) for prm in m.parameters()}
+        from .engine import model_params
+        grads = {prm: torch.empty_like(prm, dtype=torch.float32) for prm in model_params(m)}
         ncls = m.conv11.out_channels
         dl = ActF.empty(n, h, w, ncls, dev)
         _ck(self.lib.ubr_f32_logsoftmax_bwd(saved["logp"].data_ptr(), dlogp.contiguous().float().data_ptr(), n, ncls, h * w,

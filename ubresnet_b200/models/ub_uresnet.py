@@ -73,12 +73,15 @@ class UResNet(nn.Module):
         return ConvTransposeLayer(inplanes, deconvplanes, resnetplanes)
 
     def engine(self):
+        # `nn.DataParallel` (training/train_ubresnet2018_wlarcv2.py:99,103) shallow-copies the module per device on every
+        # forward: a replica must not run through the original's engine (its caches belong to the original's parameters
+        # on another device), so an engine whose `.model` is not this object is replaced
         if self.precision == "fp32":
-            if self._engine_f32 is None:
+            if self._engine_f32 is None or self._engine_f32.model is not self:
                 from ..engine_f32 import EngineF32
                 self._engine_f32 = EngineF32(self)
             return self._engine_f32
-        if self._engine is None:
+        if self._engine is None or self._engine.model is not self:
             from ..engine import Engine
             self._engine = Engine(self)
         return self._engine
