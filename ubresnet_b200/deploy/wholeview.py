@@ -30,8 +30,19 @@ def tile_plan(rows=1008, cols=3456, crop=512):
     return [(r, c) for r in tile_starts(rows, crop) for c in tile_starts(cols, crop)]
 
 
+_ORIGINS = {}
+
+
 def _origins(plan, device):
-    return torch.tensor(plan, dtype=torch.int32, device=device).contiguous()
+    """int32 [ntiles][2] device table of a tile plan, cached per (plan, device): building it with torch.tensor(...,
+    device=cuda) is a SYNCHRONOUS host-to-device copy, six of which per event serialised the deploy loop with the host"""
+    key = (tuple(map(tuple, plan)), str(device))
+    t = _ORIGINS.get(key)
+    if t is None:
+        if len(_ORIGINS) > 256:
+            _ORIGINS.clear()
+        t = _ORIGINS[key] = torch.tensor(plan, dtype=torch.int32).to(device).contiguous()
+    return t
 
 
 def gather(plane, plan, crop=512):
