@@ -26,7 +26,8 @@ constexpr int kThreads = 192;
 struct ConvGemmParams {
   CUtensorMap a_map[4];
   CUtensorMap b_map;
-  CUtensorMap o_map;
+  CUtensorMap o_map[4];         // one store map per output phase (blockIdx.z): parity-phase launches are merged
+  int nphase, tap_begin[5];     // phase z owns taps [tap_begin[z], tap_begin[z+1]) (nphase == 1: all ntaps)
   int ntaps, nkc, kc, nt, stages;
   int mt, ntiles;               // pixel sub-tiles per CTA (1 or 2, sharing every weight stage) / total 128-pixel tiles
   int tiles_w, tiles_h, bw, bh, bn;
@@ -87,7 +88,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_gemm_kernel(const __grid_con
     fence_mbar_init();
     prefetch_tmap(&p.a_map[0]);
     prefetch_tmap(&p.b_map);
-    if (p.out_mode == 0) prefetch_tmap(&p.o_map);
+    if (p.out_mode == 0) prefetch_tmap(&p.o_map[blockIdx.z]);
   }
   if (warp == 1) {
     tmem_alloc_dyn(tmem_slot, p.tmem_cols);
@@ -100,13 +101,14 @@ __global__ void __launch_bounds__(kThreads, 1) conv_gemm_kernel(const __grid_con
   asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
   pdl_wait();                    // barriers, TMEM and tensor maps are set up; the operands belong to earlier kernels
 
-  const int total_iters = p.ntaps * p.nkc;
+  const int tap_lo = p.tap_begin[blockIdx.z], tap_hi = p.tap_begin[blockIdx.z + 1];
+  const int total_iters = (tap_hi - tap_lo) * p.nkc;
 
   if (warp == 0) {
     if (lane == 0) {
       // ================= TMA producer =================
       int it = 0;
-      for (int t = 0; t < p.ntaps; ++t) {
+      for (int t = tap_lo; t < tap_hi; ++t) {
         const CUtensorMap* am = &p.a_map[p.amap[t]];
         for (int kc = 0; kc < p.nkc; ++kc, ++it) {
           const int s = it % p.stages;
@@ -226,7 +228,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_gemm_kernel(const __grid_con
       if (warp == 2 && lane == 0) {
         const int nblk = p.nt / bc;
         for (int b = 0; b < nblk; ++b)
-          tma_store_4d(&p.o_map, stage_base + (uint32_t)b * 128u * rb, co0 + b * bc, w0, h0, n0);
+          tma_store_4d(&p.o_map[blockIdx.z], stage_base + (uint32_t)b * 128u * rb, co0 + b * bc, w0, h0, n0);
         tma_store_commit();
         if (u == nsub - 1) tma_store_wait_all();
       }
@@ -338,6 +340,7 @@ static int launch_conv_gemm(ConvGemmParams& p, int grid_n, int grid_h, int grid_
   if (force_mt == 1 || force_mt == 2) p.mt = force_mt;
   p.ntiles = tiles_total;
   p.ntaps = ntaps;
+  if (p.nphase <= 1) { p.nphase = 1; p.tap_begin[0] = 0; p.tap_begin[1] = ntaps; }
   for (int i = 0; i < ntaps; ++i) {
     p.dh[i] = (int8_t)taps[i].dh; p.dw[i] = (int8_t)taps[i].dw;
     p.amap[i] = (uint8_t)taps[i].amap; p.slab[i] = (uint8_t)taps[i].slab;
@@ -380,7 +383,7 @@ static int launch_conv_gemm(ConvGemmParams& p, int grid_n, int grid_h, int grid_
     UBR_CUDA_OK(cudaFuncSetAttribute(conv_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     attr_set[dev_id & 63] = true;
   }
-  dim3 grid((unsigned)ceil_div(p.tiles_w * p.tiles_h * tiles_n, p.mt), (unsigned)(n_pad / p.nt), 1);
+  dim3 grid((unsigned)ceil_div(p.tiles_w * p.tiles_h * tiles_n, p.mt), (unsigned)(n_pad / p.nt), (unsigned)p.nphase);
   ::ubr::Launch(grid, kThreads, smem, stream)(conv_gemm_kernel, p);
   UBR_LAUNCH_CHECK("conv_gemm_kernel");
   return 0;
@@ -489,7 +492,7 @@ static int conv2d_fwd_impl(ubr_view x, const void* wpk, const float* bias, int o
     UBR_REQUIRE(out_ch % 16 == 0, "conv2d_fwd: bf16 output needs out_ch %% 16 == 0");
     p.out_mode = 0;
     p.o_box_c = out_box_c(pick_nt(n_pad));
-    if (int rc = make_act_map(&p.o_map, y, p.o_box_c, t)) return rc;
+    if (int rc = make_act_map(&p.o_map[0], y, p.o_box_c, t)) return rc;
     if (epi) {
       p.fused = 1; p.relu_pre = epi->relu_pre; p.relu_post = epi->relu_post;
       p.res = (const __nv_bfloat16*)epi->res; p.res_ld = epi->res_ld;
@@ -552,7 +555,7 @@ static int conv2d_dgrad_impl(ubr_view dy, const void* wpk, int in_ch, int ksize,
     }
     p.out_mode = 0;
     p.o_box_c = out_box_c(pick_nt(in_ch));
-    if (int rc = make_act_map(&p.o_map, dx, p.o_box_c, t)) return rc;
+    if (int rc = make_act_map(&p.o_map[0], dx, p.o_box_c, t)) return rc;
     if (accumulate) {
       // dx += dgrad: the old dx is the residual of the fused epilogue (in place: every tile reads its own pixels
       // before its TMA store, tiles are disjoint)
@@ -564,33 +567,35 @@ static int conv2d_dgrad_impl(ubr_view dy, const void* wpk, int in_ch, int ksize,
   }
   if (accumulate) return 1;
   // stride 2: input row x = 2*o + r - pad.  For output parity (ph,pw) only taps with (r-pad)&1 == ph contribute,
-  // from dy row o = (x - (r-pad))/2 = i + (ph - (r-pad))/2.
+  // from dy row o = (x - (r-pad))/2 = i + (ph - (r-pad))/2.  The four parity phases are ONE launch (blockIdx.z = phase,
+  // each with its own tap range and strided store map): 4x the CTAs for the small deep layers, 3 launches less.
+  ConvGemmParams p;
+  memset(&p, 0, sizeof(p));
+  if (int rc = make_act_map(&p.a_map[0], dy, kc, t)) return rc;
+  TapSpec taps[kMaxTaps];
+  int nt = 0;
+  p.out_mode = 0;
+  p.o_box_c = out_box_c(pick_nt(in_ch));
+  p.nphase = 4;
   for (int ph = 0; ph < 2; ++ph)
     for (int pw = 0; pw < 2; ++pw) {
-      ConvGemmParams p;
-      memset(&p, 0, sizeof(p));
-      if (int rc = make_act_map(&p.a_map[0], dy, kc, t)) return rc;
-      TapSpec taps[kMaxTaps];
-      int nt = 0;
+      const int z = ph * 2 + pw;
+      p.tap_begin[z] = nt;
       for (int r = 0; r < ksize; ++r)
         for (int s = 0; s < ksize; ++s) {
           const int oh = r - pad, ow = s - pad;
           if ((oh & 1) != ph || (ow & 1) != pw) continue;
           taps[nt++] = TapSpec{(ph - oh) / 2, (pw - ow) / 2, 0, r * ksize + s};
         }
-      p.out_mode = 0;
-      p.o_box_c = out_box_c(pick_nt(in_ch));
-      if (int rc = make_phase_map(&p.o_map, dx, ph, pw, p.o_box_c, t)) return rc;
-      if (nt == 0) {
+      if (nt == p.tap_begin[z]) {
         // no tap reaches this phase (1x1 stride 2, odd pixels): gradient is zero there.
         // Handled by a zero weight slab: use tap 0 with slab index == ksize*ksize (caller packs +1 zero slab)
         taps[nt++] = TapSpec{0, 0, 0, ksize * ksize};
       }
-      if (int rc = launch_conv_gemm(p, dy.n, dy.h, dy.w, t, dy.c, in_ch, wpk, ksize * ksize + 1, taps, nt,
-                                    (cudaStream_t)stream))
-        return rc;
+      if (int rc = make_phase_map(&p.o_map[z], dx, ph, pw, p.o_box_c, t)) return rc;
     }
-  return 0;
+  p.tap_begin[4] = nt;
+  return launch_conv_gemm(p, dy.n, dy.h, dy.w, t, dy.c, in_ch, wpk, ksize * ksize + 1, taps, nt, (cudaStream_t)stream);
 }
 
 // 3x3 stride-1 DILATED conv (padding == dilation): the ASPP branches of models/ASPP_ResNet.py:207-214.  Taps are the
@@ -629,7 +634,7 @@ static int conv2d_dilated_fwd_impl(ubr_view x, const void* wpk, const float* bia
   p.bias = bias;
   p.out_mode = 0;
   p.o_box_c = out_box_c(pick_nt(out_ch));
-  if (int rc = make_act_map(&p.o_map, y, p.o_box_c, t)) return rc;
+  if (int rc = make_act_map(&p.o_map[0], y, p.o_box_c, t)) return rc;
   if (relu) { p.fused = 1; p.relu_pre = 1; }               // inference form: BatchNorm folded into (wpk, bias)
   return launch_conv_gemm(p, x.n, x.h, x.w, t, x.c, out_ch, wpk, 9, taps, nt, (cudaStream_t)stream);
 }
@@ -653,7 +658,7 @@ int ubr_conv2d_dilated_dgrad(ubr_view dy, const void* wpk, int in_ch, int dilati
     for (int s = 0; s < 3; ++s) taps[nt++] = TapSpec{(1 - r) * dilation, (1 - s) * dilation, 0, r * 3 + s};
   p.out_mode = 0;
   p.o_box_c = out_box_c(pick_nt(in_ch));
-  if (int rc = make_act_map(&p.o_map, dx, p.o_box_c, t)) return rc;
+  if (int rc = make_act_map(&p.o_map[0], dx, p.o_box_c, t)) return rc;
   return launch_conv_gemm(p, dy.n, dy.h, dy.w, t, dy.c, in_ch, wpk, 9, taps, nt, (cudaStream_t)stream);
 }
 
@@ -665,26 +670,29 @@ int ubr_deconv4s2_fwd(ubr_view x, const void* wpk, int out_ch, ubr_view y, void*
   UBR_REQUIRE(y.c == out_ch && y.n == x.n && y.h == 2 * x.h && y.w == 2 * x.w, "deconv_fwd: output view mismatch");
   const int kc = x.c >= 64 ? 64 : x.c;
   TileShape t = pick_tile(x.n, x.h, x.w);
-  // out row o = 2*i - 1 + kh  =>  for o = 2*j + ph: i = j + (ph + 1 - kh)/2, kh == (ph+1) mod 2
+  // out row o = 2*i - 1 + kh  =>  for o = 2*j + ph: i = j + (ph + 1 - kh)/2, kh == (ph+1) mod 2.
+  // The four sub-pixel phases (2x2 taps each) are ONE launch: blockIdx.z = phase.
+  ConvGemmParams p;
+  memset(&p, 0, sizeof(p));
+  if (int rc = make_act_map(&p.a_map[0], x, kc, t)) return rc;
+  TapSpec taps[16];
+  int nt = 0;
+  p.out_mode = 0;
+  p.o_box_c = out_box_c(pick_nt(out_ch));
+  p.nphase = 4;
   for (int ph = 0; ph < 2; ++ph)
     for (int pw = 0; pw < 2; ++pw) {
-      ConvGemmParams p;
-      memset(&p, 0, sizeof(p));
-      if (int rc = make_act_map(&p.a_map[0], x, kc, t)) return rc;
-      TapSpec taps[4];
-      int nt = 0;
+      const int z = ph * 2 + pw;
+      p.tap_begin[z] = nt;
       for (int kh = 0; kh < 4; ++kh)
         for (int kw = 0; kw < 4; ++kw) {
           if (((ph + 1 - kh) & 1) || ((pw + 1 - kw) & 1)) continue;
           taps[nt++] = TapSpec{(ph + 1 - kh) / 2, (pw + 1 - kw) / 2, 0, kh * 4 + kw};
         }
-      p.out_mode = 0;
-      p.o_box_c = out_box_c(pick_nt(out_ch));
-      if (int rc = make_phase_map(&p.o_map, y, ph, pw, p.o_box_c, t)) return rc;
-      if (int rc = launch_conv_gemm(p, x.n, x.h, x.w, t, x.c, out_ch, wpk, 16, taps, nt, (cudaStream_t)stream))
-        return rc;
+      if (int rc = make_phase_map(&p.o_map[z], y, ph, pw, p.o_box_c, t)) return rc;
     }
-  return 0;
+  p.tap_begin[4] = nt;
+  return launch_conv_gemm(p, x.n, x.h, x.w, t, x.c, out_ch, wpk, 16, taps, nt, (cudaStream_t)stream);
 }
 
 int ubr_deconv4s2_fwd_subpixel(ubr_view x, const void* wpk3, int out_ch, ubr_view y, void* stream) {
@@ -727,7 +735,7 @@ int ubr_deconv4s2_dgrad(ubr_view dy, const void* wpk, int in_ch, ubr_view dx, vo
     }
   p.out_mode = 0;
   p.o_box_c = out_box_c(pick_nt(in_ch));
-  if (int rc = make_act_map(&p.o_map, dx, p.o_box_c, t)) return rc;
+  if (int rc = make_act_map(&p.o_map[0], dx, p.o_box_c, t)) return rc;
   return launch_conv_gemm(p, dx.n, dx.h, dx.w, t, dy.c, in_ch, wpk, 16, taps, nt, (cudaStream_t)stream);
 }
 
