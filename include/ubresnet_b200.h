@@ -43,6 +43,7 @@ int ubr_abi_version(void);
 const char* ubr_last_error(void);
 int ubr_device_check(void);               /* 0 iff the current CUDA device is sm_100 (B200) */
 int ubr_sync_check(void* stream);         /* cudaStreamSynchronize + surface async errors */
+int ubr_shutdown(void);                   /* teardown: the library owns no device memory; clears trace / error state */
 uint64_t ubr_launch_count(void);          /* kernels launched by this library so far (process wide) */
 /* profiling aid (bench.py): when enabled, ubr_take_kernel_names() returns "k1+k2" = the kernels the calling thread
  * launched since the previous take (thread-local buffer, valid until the next take) */

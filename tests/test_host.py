@@ -108,3 +108,19 @@ def test_fused_optimizers_refuse_cpu_parameters():
         with pytest.raises(RuntimeError):
             opt.step()
         assert isinstance(opt, torch.optim.Optimizer) and opt.state_dict()["param_groups"][0]["lr"] == 0.1
+
+
+def test_default_ctor_three_input_channels_selects_fp32():
+    """the reference's default ctor (input_channels=3, models/ub_uresnet.py:31) constructs and gets the fp32 schedule;
+    an explicit bf16 request for it is refused at construction, not at the first forward"""
+    import warnings
+    import pytest
+    from ubresnet_b200.models import UResNet
+    with warnings.catch_warnings(record=True) as w:
+        warnings.simplefilter("always")
+        m = UResNet()
+    assert m.conv1.in_channels == 3 and m.precision == "fp32" and any("fp32" in str(x.message) for x in w)
+    assert len(m.state_dict()) == 321
+    with pytest.raises(ValueError):
+        UResNet(3, 3, 16, precision="bf16")
+    assert UResNet(3, 1, 16).precision == "bf16"

@@ -23,6 +23,7 @@ SIGNATURES = {
     "ubr_last_error": (C.c_char_p, []),
     "ubr_device_check": (_i, []),
     "ubr_sync_check": (_i, [_vp]),
+    "ubr_shutdown": (_i, []),
     "ubr_launch_count": (_u64, []),
     "ubr_trace_kernels": (None, [_i]),
     "ubr_take_kernel_names": (C.c_char_p, []),

@@ -142,6 +142,17 @@ const char* ubr_take_kernel_names(void) {
   return ubr::g_names_out;
 }
 
+/* The library keeps no device allocations and no cached tensor maps (every descriptor is encoded per call): shutdown
+ * only clears the per-thread trace / error state.  Present so that a binding has a symmetric teardown call. */
+int ubr_shutdown(void) {
+  ubr::g_trace.store(0);
+  ubr::g_names_len = 0;
+  ubr::g_names[0] = 0;
+  ubr::g_err[0] = 0;
+  ubr::take_launch_error();
+  return 0;
+}
+
 int ubr_sync_check(void* stream) {
   cudaError_t e = cudaStreamSynchronize((cudaStream_t)stream);
   if (e != cudaSuccess) return ubr::cuda_fail(e, "cudaStreamSynchronize");

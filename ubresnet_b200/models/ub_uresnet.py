@@ -31,6 +31,16 @@ class UResNet(nn.Module):
         self.precision = precision or os.environ.get("UBR_PRECISION", "bf16")
         if self.precision not in ("bf16", "fp32"):
             raise ValueError("precision must be 'bf16' or 'fp32', got %r" % (self.precision,))
+        if input_channels != 1 and self.precision == "bf16":
+            # the tensor-core stem kernels are single-channel (wire-plane crops); the reference's default ctor
+            # (input_channels=3, models/ub_uresnet.py:31) still has to construct and run
+            if precision == "bf16":
+                raise ValueError("UResNet: precision='bf16' takes input_channels=1; other channel counts run in "
+                                 "precision='fp32'")
+            import warnings
+            warnings.warn("ubresnet_b200: input_channels=%d -> precision='fp32' (the bf16 tensor-core schedule is "
+                          "single-channel)" % input_channels)
+            self.precision = "fp32"
         p = self.inplanes
 
         # stem
