@@ -185,8 +185,14 @@ __global__ void wgrad_reduce_kernel(const float* __restrict__ partials, int spli
   const int t = (int)((idx / n_ch) % ntaps);
   const int m = (int)(idx / ((long)n_ch * ntaps));
   if (m >= m_valid || n >= n_valid) return;
-  float acc = 0.f;
-  for (int s = 0; s < splits; ++s) acc += partials[(long)s * total + idx];
+  float a8[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};      // see wgrad_halo_reduce_kernel: same fixed-order scheme
+  int s = 0;
+  for (; s + 8 <= splits; s += 8) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) a8[j] += partials[(long)(s + j) * total + idx];
+  }
+  for (int j = 0; s < splits; ++s, ++j) a8[j] += partials[(long)s * total + idx];
+  const float acc = ((a8[0] + a8[1]) + (a8[2] + a8[3])) + ((a8[4] + a8[5]) + (a8[6] + a8[7]));
   float* d = dw + m * sm + t * st + n * sn;
   *d = accumulate ? (*d + acc) : acc;
 }

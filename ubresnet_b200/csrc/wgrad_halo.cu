@@ -219,8 +219,16 @@ __global__ void wgrad_halo_reduce_kernel(const float* __restrict__ partials, int
   const int co = (idx / cin) % cout;
   const int rs = idx / (cin * cout);
   if (co >= out_ch) return;
-  float acc = 0.f;
-  for (int c = 0; c < ncta; ++c) acc += partials[(size_t)c * total + idx];
+  // eight independent partial sums (fixed assignment c mod 8, fixed combination order: deterministic) keep eight loads
+  // in flight instead of one dependent add chain over up to 296 partials
+  float a8[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  int c = 0;
+  for (; c + 8 <= ncta; c += 8) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) a8[j] += partials[(size_t)(c + j) * total + idx];
+  }
+  for (int j = 0; c < ncta; ++c, ++j) a8[j] += partials[(size_t)c * total + idx];
+  const float acc = ((a8[0] + a8[1]) + (a8[2] + a8[3])) + ((a8[4] + a8[5]) + (a8[6] + a8[7]));
   float* d = dw + ((size_t)co * cin + ci) * ksize * ksize + rs;
   *d = accumulate ? (*d + acc) : acc;
 }
