@@ -354,6 +354,13 @@ int ubr_seg_weights(const void* label, int label_dtype, int column_major, int ba
  * workspace: ubr_bn_workspace_bytes(a.c).  ubr_increment_i64: *ptrs[i] += 1 for a DEVICE table of int64 scalars
  * (BatchNorm2d.num_batches_tracked of all 52 layers in one launch). */
 int ubr_channel_sum(ubr_view a, int nvalid, void* workspace, float* out, int accumulate, void* stream);
+/* Allocation-free variant of ubr_channel_sum.  It has NO counterpart in the reference: it was added
+ * for callers that cannot allocate a workspace (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid cudaMalloc).  The partial sums go to a file-scope device array inside the library
+ * (2.3 MiB per GPU that loads it, held until exit) instead of a caller workspace; the call itself performs no
+ * cudaMalloc / cudaFree.  Limit: a.c <= 512 channels, larger views return UBR_E_BADARG.  All calls share the array:
+ * calls that overlap on the GPU (different streams) race -- keep them on one stream or order them with events. */
+int ubr_channel_sum_static(ubr_view a, int nvalid, float* out, int accumulate, void* stream);
 int ubr_increment_i64(int64_t* const* ptrs_device, int n, void* stream);
 
 /* ---- flat-buffer helpers for the data-parallel gradient buckets --------------------------------- */

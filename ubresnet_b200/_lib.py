@@ -85,6 +85,7 @@ SIGNATURES = {
     "ubr_accuracy_counts": (_i, [_vp, _vp, _i, _i, _i, _vp, _vp]),
     "ubr_scale_f32": (_i, [_vp, _u64, _f, _vp]),
     "ubr_channel_sum": (_i, [View, _i, _vp, _vp, _i, _vp]),
+    "ubr_channel_sum_static": (_i, [View, _i, _vp, _i, _vp]),
     "ubr_increment_i64": (_i, [_vp, _i, _vp]),
     "ubr_fill_image_batch": (_i, [_vp, _i, _i, _i, _i, _vp, _vp, _vp]),
     "ubr_fill_label_batch": (_i, [_vp, _i, _i, _i, _i, _vp, _vp, _i, _i, _vp, _vp, _vp, _vp]),

@@ -1274,6 +1274,42 @@ int ubr_channel_sum(ubr_view a, int nvalid, void* workspace, float* out, int acc
   return 0;
 }
 
+// ---- allocation-free variant (no counterpart in the reference) -----------
+// Same two kernels as ubr_channel_sum, but the partial rows live in a file-scope device array instead of a caller
+// workspace, for callers that cannot allocate (graph capture, serving loops).  Every GPU that loads the library holds
+// the array (kStaticMaxC * kRedBlocks * 2 floats = 2.3 MiB) until exit.  The array's name is only a host-side handle:
+// its device address is looked up once per device with cudaGetSymbolAddress (with that device current) and cached.
+// bn_stats_kernel overwrites every partial row the finish kernel reads, so nothing has to be cleared between calls;
+// all calls share the array, so two calls that overlap on the GPU (different streams) race.
+constexpr int kStaticMaxC = 512;
+static __device__ __align__(256) float g_static_partials[(size_t)kRedBlocks * 2 * kStaticMaxC];
+static float* g_static_partials_ptr[64] = {};
+
+int ubr_channel_sum_static(ubr_view a, int nvalid, float* out, int accumulate, void* stream) {
+  if (int rc = ensure_device()) return rc;
+  if (int rc = chk_red(a, "channel_sum_static.a")) return rc;
+  UBR_REQUIRE(out && nvalid >= 1 && nvalid <= a.c, "channel_sum_static: bad arguments");
+  UBR_REQUIRE(a.c <= kStaticMaxC, "channel_sum_static: c=%d exceeds the built-in scratch (max %d channels); use "
+              "ubr_channel_sum with a caller workspace", a.c, kStaticMaxC);
+  int dev = 0;
+  UBR_CUDA_OK(cudaGetDevice(&dev));
+  if (g_static_partials_ptr[dev] == nullptr) {
+    float* p = nullptr;
+    UBR_CUDA_OK(cudaGetSymbolAddress((void**)&p, g_static_partials));
+    g_static_partials_ptr[dev] = p;
+  }
+  float* scratch = g_static_partials_ptr[dev];
+  DView v = dv(a);
+  const int nb = red_blocks(v.npix, v.c);
+  cudaStream_t st = (cudaStream_t)stream;
+  ::ubr::Launch(nb, kRedThreads, kRedThreads * 16 * sizeof(float), st)(bn_stats_kernel, v, scratch);
+  UBR_LAUNCH_CHECK("bn_stats_kernel");
+  ::ubr::Launch(ceil_div(v.c, 32), dim3(32, kColLanes), 0, st)(channel_sum_finish_kernel, (const float*)scratch, nb, v.c,
+                                                               nvalid, out, accumulate);
+  UBR_LAUNCH_CHECK("channel_sum_finish_kernel");
+  return 0;
+}
+
 int ubr_increment_i64(int64_t* const* ptrs_device, int n, void* stream) {
   if (int rc = ensure_device()) return rc;
   UBR_REQUIRE(ptrs_device != nullptr && n >= 1, "increment_i64: bad arguments");
