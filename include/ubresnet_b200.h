@@ -86,6 +86,15 @@ int ubr_conv2d_fwd_stats(ubr_view x, const void* wpk, const float* bias, int out
  * is a bf16 view on the output grid.  bf16 output only. */
 int ubr_conv2d_fwd_fused(ubr_view x, const void* wpk, const float* bias, int out_ch, int ksize, int stride, int relu_pre,
                          ubr_view res, int relu_post, ubr_view y, void* stream);
+/* Eval-mode residual block chain (models/common_layers.py:39-58 with BatchNorm folded):
+ *   y = relu( relu( conv3x3(relu(conv3x3(x, w1) + b1), w2) + b2 ) + res )
+ * in ONE launch: the intermediate activation stays in shared memory (row bands with one recomputed halo row on either
+ * side).  w1pk / w2pk: ubr_pack_weights forward layouts of [planes, x.c, 3, 3] and [planes, planes, 3, 3]; b1 / b2:
+ * fp32 [planes]; res: bf16 view like y (x itself for an identity block, the projected bypass otherwise).
+ * Returns 1 (nothing launched) when the shape is not eligible -- x.w % 128 != 0, channels outside {16,32,64},
+ * (x.w/128)*(planes/16) > 4 -- and the caller runs two ubr_conv2d_fwd_fused calls instead. */
+int ubr_block_chain_fwd(ubr_view x, const void* w1pk, const float* b1, const void* w2pk, const float* b2, int planes,
+                        ubr_view res, ubr_view y, void* stream);
 /* data gradient of the same conv: dx = conv_transpose(dy, W).  wpk = pack(..., n_is_out=0). */
 int ubr_conv2d_dgrad(ubr_view dy, const void* wpk, int in_ch, int ksize, int stride, ubr_view dx, void* stream);
 /* dx += conv_transpose(dy, W), fused into the epilogue (fp32 add of the stored bf16 value, one rounding).

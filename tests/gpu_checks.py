@@ -119,6 +119,40 @@ def check_conv_fwd_fused(cin, cout, k, stride, n, h, w, relu_pre=True, with_res=
     return res
 
 
+def check_block_chain(cin, planes, n, h, w, in_ld=None, out_ld=None, seed=0):
+    """eval residual-block chain (ubr_block_chain_fwd) against torch AND against the two-launch path it replaces
+    (same accumulation order: bit-identical)."""
+    name = "block_chain_ci%d_p%d_n%d_%dx%d" % (cin, planes, n, h, w)
+    x = bf(gen(n, cin, h, w, seed=seed))
+    w1 = bf(gen(planes, cin, 3, 3, seed=seed + 1, scale=(2.0 / (9 * cin)) ** 0.5))
+    w2 = bf(gen(planes, planes, 3, 3, seed=seed + 2, scale=(2.0 / (9 * planes)) ** 0.5))
+    b1 = gen(planes, seed=seed + 3, scale=0.3)
+    b2 = gen(planes, seed=seed + 4, scale=0.3)
+    identity = cin == planes
+    r = x if identity else bf(gen(n, planes, h, w, seed=seed + 5))
+    a1 = bf(F.relu(F.conv2d(x, w1, b1, 1, 1)))
+    ref = F.relu(F.relu(F.conv2d(a1, w2, b2, 1, 1)) + r)
+    w1pk = ops.pack_weights(w1.to(DEV), False, True)
+    w2pk = ops.pack_weights(w2.to(DEV), False, True)
+    xa = act_from(x, in_ld, 0)
+    ra = xa if identity else act_from(r)
+    ya = act_out(n, h, w, planes, out_ld, 0)
+    got = ops.block_chain_fwd(xa, w1pk, b1.to(DEV), w2pk, b2.to(DEV), planes, ra, y=ya)
+    torch.cuda.synchronize()
+    res = [(name + "_eligible", 0.0 if got is not None else 1.0, 0.0)]
+    if got is None:
+        return res
+    out = ya.nchw_float()
+    res.append((name, relerr(out, ref), 1e-2))
+    a1d = ops.conv2d_fwd_fused(xa, w1pk, b1.to(DEV), planes, 3, 1, True)
+    y2 = ops.conv2d_fwd_fused(a1d, w2pk, b2.to(DEV), planes, 3, 1, True, ra, True)
+    torch.cuda.synchronize()
+    res.append((name + "_vs_two_launches", (out - y2.nchw_float()).abs().max().item(), 0.0))
+    if out_ld and out_ld != planes:
+        res.append((name + "_slice_untouched", (ya.buf[..., planes:].float() - 3.0).abs().max().item(), 0.0))
+    return res
+
+
 def check_conv_fwd_bn(cin, cout, k, n, h, w, seed=0, bias=False, expect_rows=True):
     """conv + fused BatchNorm statistics (ubr_conv2d_fwd_stats) against F.conv2d + batch statistics."""
     name = "conv_fwd_bn_ci%d_co%d_k%d_n%d_%dx%d" % (cin, cout, k, n, h, w)
@@ -691,6 +725,15 @@ CHECKS = {
 
 # ASPP_ResNet operators (reference models/ASPP_ResNet.py:188-286): dilated branches, stride-1 max-pool, and the
 # 192/320/576/384/768-channel concat operands (64-wide N tiles in conv_gemm / wgrad_gemm)
+CHECKS.update({
+    # eval conv->ReLU->conv chains, one launch (N1): the three resolutions / channel widths of the U-ResNet and odd bands
+    "block_chain_512": lambda: (check_block_chain(32, 16, 2, 64, 512, seed=201) + check_block_chain(16, 16, 1, 96, 512, seed=202)),
+    "block_chain_256": lambda: (check_block_chain(16, 32, 2, 64, 256, seed=203) + check_block_chain(32, 32, 3, 40, 256, seed=204)
+                                + check_block_chain(64, 32, 2, 32, 256, in_ld=128, out_ld=64, seed=205)),
+    "block_chain_128": lambda: (check_block_chain(64, 64, 2, 64, 128, seed=206) + check_block_chain(16, 16, 1, 8, 128, seed=207)
+                                + check_block_chain(32, 64, 5, 16, 128, seed=208)),
+})
+
 CHECKS.update({
     "aspp_dilated_d3": lambda: check_dilated(128, 16, 3, 2, 16, 16, seed=81) + check_dilated(256, 16, 3, 1, 8, 8, in_ld=512, seed=82),
     "aspp_dilated_d5": lambda: check_dilated(128, 16, 5, 2, 16, 16, seed=83) + check_dilated(512, 16, 5, 3, 4, 4, seed=84),

@@ -31,6 +31,7 @@ SIGNATURES = {
     "ubr_pack_weights_batch": (_i, [_vp, _i, _vp]),
     "ubr_conv2d_fwd": (_i, [View, _vp, _vp, _i, _i, _i, View, _vp, _i, _vp]),
     "ubr_conv2d_fwd_fused": (_i, [View, _vp, _vp, _i, _i, _i, _i, View, _i, View, _vp]),
+    "ubr_block_chain_fwd": (_i, [View, _vp, _vp, _vp, _vp, _i, View, View, _vp]),
     "ubr_conv2d_fwd_stats": (_i, [View, _vp, _vp, _i, _i, _i, View, _vp, _vp, _vp]),
     "ubr_conv2d_dgrad": (_i, [View, _vp, _i, _i, _i, View, _vp]),
     "ubr_conv2d_dgrad_bnreduce": (_i, [View, _vp, _i, _i, _i, View, View, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp]),

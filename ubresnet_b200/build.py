@@ -7,7 +7,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIBDIR = os.path.join(HERE, "lib")
 LIBPATH = os.path.join(LIBDIR, "libubresnet_b200.so")
-SOURCES = ["runtime.cu", "fp32_path.cu", "batch_fill.cu", "conv_gemm.cu", "conv_halo.cu", "wgrad_gemm.cu", "wgrad_halo.cu", "pointwise.cu", "stem.cu", "stem_tc.cu", "optim.cu", "loss_tiling_pack.cu"]
+SOURCES = ["runtime.cu", "fp32_path.cu", "batch_fill.cu", "conv_gemm.cu", "conv_halo.cu", "chain_halo.cu", "wgrad_gemm.cu", "wgrad_halo.cu", "pointwise.cu", "stem.cu", "stem_tc.cu", "optim.cu", "loss_tiling_pack.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-Xcompiler", "-fPIC", "--use_fast_math", "-Xptxas", "-v"]
 

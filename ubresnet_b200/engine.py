@@ -65,6 +65,7 @@ class _FoldedConv:
 
 
 FOLD_EVAL_BN = os.environ.get("UBR_FOLD_EVAL_BN", "1") != "0"
+CHAIN_EVAL_BLOCKS = os.environ.get("UBR_NO_CHAIN", "0") in ("", "0")    # eval: conv->ReLU->conv chains in one kernel
 
 
 class _ConvW:
@@ -437,18 +438,23 @@ class Engine:
         return ent.refresh(conv, bn, packed)
 
     def _block_fwd_folded(self, blk, x, out):
-        """eval-mode BasicBlock (common_layers.py:39-58) in three launches: BatchNorm folded into the conv operands,
+        """eval-mode BasicBlock (common_layers.py:39-58) in at most three launches: BatchNorm folded into the conv operands,
         ReLU / residual add / ReLU in the conv epilogues -- no stand-alone pointwise pass."""
         cout = blk.conv1.out_channels
         s = blk.stride
         f1 = self._folded(blk.conv1, blk.bn1)
-        a1 = ops.conv2d_fwd_fused(x, f1.w, f1.b, cout, 3, s, True)
+        f2 = self._folded(blk.conv2, blk.bn2)
         if blk.bypass is not None:
             fb = self._folded(blk.bypass, blk.bnpass)
             res = ops.conv2d_fwd_fused(x, fb.w, fb.b, cout, 1, s, False)
         else:
             res = x
-        f2 = self._folded(blk.conv2, blk.bn2)
+        if s == 1 and CHAIN_EVAL_BLOCKS:
+            # conv1 -> ReLU -> conv2 with the intermediate activation kept in shared memory (512^2 .. 128^2 layers)
+            y = ops.block_chain_fwd(x, f1.w, f1.b, f2.w, f2.b, cout, res, y=out)
+            if y is not None:
+                return y
+        a1 = ops.conv2d_fwd_fused(x, f1.w, f1.b, cout, 3, s, True)
         return ops.conv2d_fwd_fused(a1, f2.w, f2.b, cout, 3, 1, True, res, True, y=out)
 
     def _block_fwd(self, blk, x, out, training, need_grad, bn_ws):

@@ -135,6 +135,20 @@ def conv2d_fwd_fused(x, wpk, bias, out_ch, ksize, stride, relu_pre, res=None, re
     return y
 
 
+def block_chain_fwd(x, w1pk, b1, w2pk, b2, planes, res, y=None):
+    """eval-mode residual block conv3x3 -> ReLU -> conv3x3 -> ReLU -> (+res) -> ReLU in one launch, the intermediate
+    activation kept on chip (csrc/chain_halo.cu).  Returns None when the shape is not eligible (nothing launched)."""
+    lib = _lib.load()
+    if y is None:
+        y = Act.empty(x.n, x.h, x.w, planes, x.buf.device)
+    rc = lib.ubr_block_chain_fwd(x.view(), w1pk.data_ptr(), b1.data_ptr(), w2pk.data_ptr(), b2.data_ptr(), planes,
+                                 res.view(), y.view(), _stream())
+    if rc == 1:
+        return None
+    _lib.check(rc, "block_chain_fwd")
+    return y
+
+
 def conv2d_fwd_bn(x, wpk, bias, out_ch, ksize, stride, gamma, beta, running_mean, running_var, ws, y=None,
                   momentum=BN_MOMENTUM, eps=BN_EPS):
     """conv forward + training-mode BatchNorm statistics.  Where the conv kernel has a fused-statistics epilogue the
