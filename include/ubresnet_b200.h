@@ -81,6 +81,16 @@ int ubr_conv2d_fwd(ubr_view x, const void* wpk, const float* bias, int out_ch, i
  * Returns 1 (and does nothing) when the shape has no fused path: run ubr_conv2d_fwd + ubr_bn_stats instead. */
 int ubr_conv2d_fwd_stats(ubr_view x, const void* wpk, const float* bias, int out_ch, int ksize, int stride, ubr_view y,
                          void* bn_workspace, int* stats_rows, void* stream);
+/* conv + training-mode BatchNorm statistics + their finalize in ONE launch: the epilogue's partial rows are summed, in
+ * a fixed order, by the last CTAs to arrive (a two-level ticket tree in `tree`), and the last of them writes scale /
+ * shift / mean / invstd and updates the running statistics -- what ubr_conv2d_fwd_stats + ubr_bn_finalize_rows do in
+ * two launches (models/common_layers.py:41-42,47-48: conv -> bn in training mode).  `tree`: ubr_bn_tree_bytes(c) bytes of
+ * device memory, zero-filled ONCE after allocation (the library leaves it zeroed); launches sharing a tree or workspace
+ * must be stream-ordered.  Returns 1 (nothing launched) when the shape has no fused-statistics epilogue. */
+int ubr_conv2d_fwd_bn(ubr_view x, const void* wpk, const float* bias, int out_ch, int ksize, int stride, ubr_view y,
+                      void* bn_workspace, void* tree, const float* gamma, const float* beta, float* running_mean,
+                      float* running_var, float momentum, float eps, float* scale, float* shift, float* mean,
+                      float* invstd, void* stream);
 /* Inference form of a residual-block conv with BatchNorm folded into (wpk, bias) by the caller (SURVEY 8f N1;
  * common_layers.py:39-58 in eval mode):  y = relu_post?( relu_pre?(conv(x) + bias) + res ).  `res` (ptr NULL = none)
  * is a bf16 view on the output grid.  bf16 output only. */
@@ -109,6 +119,13 @@ int ubr_conv2d_dgrad_acc(ubr_view dy, const void* wpk, int in_ch, int ksize, int
 int ubr_conv2d_dgrad_bnreduce(ubr_view dy, const void* wpk, int in_ch, int ksize, int stride, ubr_view dx, ubr_view y_pre,
                               const float* scale, const float* shift, const float* mean, const float* invstd, int relu,
                               void* bn_workspace, int* rows, void* stream);
+/* ubr_conv2d_dgrad_bnreduce whose launch also finishes the two sums (kept behind the partial rows of bn_workspace, where
+ * the apply passes read them) and writes dbeta / dgamma (common_layers.py:41-44 reversed): follow it with
+ * ubr_bn_act_bwd_apply_final.  `tree` as for ubr_conv2d_fwd_bn.  Returns 1 (nothing launched) without a fused path. */
+int ubr_conv2d_dgrad_bnreduce_final(ubr_view dy, const void* wpk, int in_ch, int ksize, int stride, ubr_view dx,
+                                    ubr_view y_pre, const float* scale, const float* shift, const float* mean,
+                                    const float* invstd, int relu, void* bn_workspace, void* tree, float* dgamma,
+                                    float* dbeta, int accumulate, void* stream);
 /* weight gradient: dw[o,i,r,s] (+)= sum_pixels dy[.,o] * x[shifted,i]; fp32 OIHW.  accumulate: 0 overwrite, 1 add */
 int ubr_conv2d_wgrad(ubr_view x, ubr_view dy, int out_ch /* true rows of dw; dy.c may be padded */, int ksize,
                      int stride, float* dw, int accumulate, void* workspace, uint64_t workspace_bytes, void* stream);
@@ -170,6 +187,13 @@ int ubr_bn_finalize(const void* workspace, int c, double count, const float* gam
 int ubr_bn_finalize_rows(const void* workspace, int rows, int c, double count, const float* gamma, const float* beta,
                          float* running_mean, float* running_var, float momentum, float eps,
                          float* scale, float* shift, float* mean, float* invstd, void* stream);
+/* ubr_bn_stats + ubr_bn_finalize in ONE launch (nn.BatchNorm2d in training mode, common_layers.py:24,27,35): the last
+ * CTAs to arrive reduce the partial rows in a fixed order (`tree`: ubr_bn_tree_bytes(c) bytes, zero-filled once after
+ * allocation, see ubr_conv2d_fwd_bn) */
+uint64_t ubr_bn_tree_bytes(int c);
+int ubr_bn_stats_final(ubr_view y, void* workspace, void* tree, const float* gamma, const float* beta, float* running_mean,
+                       float* running_var, float momentum, float eps, float* scale, float* shift, float* mean,
+                       float* invstd, void* stream);
 /* eval mode: scale/shift from running statistics */
 int ubr_bn_eval_affine(int c, const float* gamma, const float* beta, const float* running_mean,
                        const float* running_var, float eps, float* scale, float* shift, void* stream);
@@ -191,6 +215,14 @@ int ubr_bn_act_bwd_apply(ubr_view dout, ubr_view y, const float* scale, const fl
 int ubr_bn_act_bwd_apply_rows(ubr_view dout, ubr_view y, const float* scale, const float* shift, const float* mean,
                               const float* invstd, const float* gamma, int relu, const void* workspace, int rows,
                               double count, ubr_view dy, float* dgamma, float* dbeta, int accumulate, void* stream);
+/* the same two passes with the reduction FINISHED inside pass 1 (sums and dgamma / dbeta written by the last CTA to
+ * arrive; `tree` as for ubr_conv2d_fwd_bn), so pass 2 is a single launch */
+int ubr_bn_act_bwd_reduce_final(ubr_view dout, ubr_view y, const float* scale, const float* shift, const float* mean,
+                                const float* invstd, int relu, void* workspace, void* tree, float* dgamma, float* dbeta,
+                                int accumulate, void* stream);
+int ubr_bn_act_bwd_apply_final(ubr_view dout, ubr_view y, const float* scale, const float* shift, const float* mean,
+                               const float* invstd, int relu, const void* workspace, double count, ubr_view dy,
+                               void* stream);
 /* backward of the block tail.  du = dout*(out>0); main branch dz2 = du*(bn2(y2)>0); residual branch gets du.
  * res_is_bn=1: residual is bnpass(bypass conv) -> dres = BN backward of du wrt `res` (pre-BN conv output); the mask
  *              (out>0) is recomputed from y2 and res with the forward arithmetic and the residual affine
@@ -207,6 +239,18 @@ int ubr_block_tail_bwd_apply(ubr_view dout, ubr_view out, ubr_view y2, const flo
                              int res_is_bn, const void* workspace, double count, ubr_view dy2, ubr_view dres,
                              float* dgamma2, float* dbeta2, float* dgammar, float* dbetar, int accumulate,
                              void* stream);
+
+/* block-tail backward with the reduction finished inside pass 1 (see ubr_bn_act_bwd_reduce_final) */
+int ubr_block_tail_bwd_reduce_final(ubr_view dout, ubr_view out, ubr_view y2, const float* s2, const float* b2,
+                                    const float* mean2, const float* invstd2, ubr_view res, const float* meanr,
+                                    const float* invstdr, const float* scaler, const float* shiftr, int res_is_bn,
+                                    void* workspace, void* tree, float* dgamma2, float* dbeta2, float* dgammar,
+                                    float* dbetar, int accumulate, void* stream);
+int ubr_block_tail_bwd_apply_final(ubr_view dout, ubr_view out, ubr_view y2, const float* s2, const float* b2,
+                                   const float* mean2, const float* invstd2, ubr_view res, const float* meanr,
+                                   const float* invstdr, const float* gammar, const float* scaler, const float* shiftr,
+                                   int res_is_bn, const void* workspace, double count, ubr_view dy2, ubr_view dres,
+                                   void* stream);
 
 /* ---- MaxPool2d(3, stride 2, pad 1) (ub_uresnet.py:44,97) and pointwise sums ---------------------- */
 int ubr_maxpool3s2_fwd(ubr_view x, ubr_view y, void* stream);

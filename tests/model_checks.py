@@ -636,7 +636,8 @@ def fused_bn_reduce():
         ref = ops.bn_act_bwd(da, ypre, st, relu, ws2, dg_b, db_b)
         torch.cuda.synchronize()
         tag = "k%d %d->%d %dx%dx%d relu=%d" % (k, cout, cin, n, h, w, relu)
-        res.append((tag + " fused path taken (3 launches)", 0.0 if launches == 3 else 1.0, 0.0))
+        want = 2 if ops.TREE_FINALIZE else 3       # dgrad (+ in-launch finalize) + apply | dgrad + sums finalize + apply
+        res.append((tag + " fused path taken (%d launches)" % want, 0.0 if launches == want else 1.0, 0.0))
         res.append((tag + " dy_pre", _rel(fused.torch(), ref.torch()), 1e-2))
         res.append((tag + " dgamma", _rel(dg_a, dg_b), 1e-4))
         res.append((tag + " dbeta", _rel(db_a, db_b), 1e-4))

@@ -33,7 +33,10 @@ SIGNATURES = {
     "ubr_conv2d_fwd_fused": (_i, [View, _vp, _vp, _i, _i, _i, _i, View, _i, View, _vp]),
     "ubr_block_chain_fwd": (_i, [View, _vp, _vp, _vp, _vp, _i, View, View, _vp]),
     "ubr_conv2d_fwd_stats": (_i, [View, _vp, _vp, _i, _i, _i, View, _vp, _vp, _vp]),
+    "ubr_conv2d_fwd_bn": (_i, [View, _vp, _vp, _i, _i, _i, View, _vp, _vp, _vp, _vp, _vp, _vp, _f, _f, _vp, _vp, _vp, _vp, _vp]),
     "ubr_conv2d_dgrad": (_i, [View, _vp, _i, _i, _i, View, _vp]),
+    "ubr_conv2d_dgrad_bnreduce_final": (_i, [View, _vp, _i, _i, _i, View, View, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _vp,
+                                             _i, _vp]),
     "ubr_conv2d_dgrad_bnreduce": (_i, [View, _vp, _i, _i, _i, View, View, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp]),
     "ubr_bn_act_bwd_apply_rows": (_i, [View, View, _vp, _vp, _vp, _vp, _vp, _i, _vp, _i, _d, View, _vp, _vp, _i, _vp]),
     "ubr_conv2d_dgrad_acc": (_i, [View, _vp, _i, _i, _i, View, _vp]),
@@ -57,6 +60,8 @@ SIGNATURES = {
     "ubr_stem_wgrad_workspace_bytes": (_u64, [_i, _i, _i, _i]),
     "ubr_bn_workspace_bytes": (_u64, [_i]),
     "ubr_bn_stats": (_i, [View, _vp, _vp]),
+    "ubr_bn_tree_bytes": (_u64, [_i]),
+    "ubr_bn_stats_final": (_i, [View, _vp, _vp, _vp, _vp, _vp, _vp, _f, _f, _vp, _vp, _vp, _vp, _vp]),
     "ubr_bn_finalize": (_i, [_vp, _i, _d, _vp, _vp, _vp, _vp, _f, _f, _vp, _vp, _vp, _vp, _vp]),
     "ubr_bn_finalize_rows": (_i, [_vp, _i, _i, _d, _vp, _vp, _vp, _vp, _f, _f, _vp, _vp, _vp, _vp, _vp]),
     "ubr_bn_eval_affine": (_i, [_i, _vp, _vp, _vp, _vp, _f, _vp, _vp, _vp]),
@@ -64,6 +69,12 @@ SIGNATURES = {
     "ubr_block_tail": (_i, [View, _vp, _vp, View, _vp, _vp, View, _vp]),
     "ubr_bn_act_bwd_reduce": (_i, [View, View, _vp, _vp, _vp, _vp, _i, _vp, _vp]),
     "ubr_bn_act_bwd_apply": (_i, [View, View, _vp, _vp, _vp, _vp, _vp, _i, _vp, _d, View, _vp, _vp, _i, _vp]),
+    "ubr_bn_act_bwd_reduce_final": (_i, [View, View, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _vp, _i, _vp]),
+    "ubr_bn_act_bwd_apply_final": (_i, [View, View, _vp, _vp, _vp, _vp, _i, _vp, _d, View, _vp]),
+    "ubr_block_tail_bwd_reduce_final": (_i, [View, View, View, _vp, _vp, _vp, _vp, View, _vp, _vp, _vp, _vp, _i, _vp, _vp,
+                                             _vp, _vp, _vp, _vp, _i, _vp]),
+    "ubr_block_tail_bwd_apply_final": (_i, [View, View, View, _vp, _vp, _vp, _vp, View, _vp, _vp, _vp, _vp, _vp, _i, _vp, _d,
+                                            View, View, _vp]),
     "ubr_block_tail_bwd_reduce": (_i, [View, View, View, _vp, _vp, _vp, _vp, View, _vp, _vp, _vp, _vp, _i, _vp, _vp]),
     "ubr_block_tail_bwd_apply": (_i, [View, View, View, _vp, _vp, _vp, _vp, _vp, View, _vp, _vp, _vp, _vp, _vp, _i, _vp, _d,
                                       View, View, _vp, _vp, _vp, _vp, _i, _vp]),

@@ -45,6 +45,10 @@ struct ConvGemmParams {
   int res_ld;
   int8_t dh[kMaxTaps], dw[kMaxTaps];
   uint8_t amap[kMaxTaps], slab[kMaxTaps];
+  // stats: reduction over the per-tile partial rows + BatchNorm finalize inside this launch (tree_reduce.cuh)
+  int fin_kind;
+  TreeRed tr;
+  BnFinal bnf;
 };
 
 __global__ void __launch_bounds__(kThreads, 1) conv_gemm_kernel(const __grid_constant__ ConvGemmParams p) {
@@ -261,6 +265,11 @@ __global__ void __launch_bounds__(kThreads, 1) conv_gemm_kernel(const __grid_con
     tc_fence_after();
     tmem_dealloc_dyn(tmem_base, p.tmem_cols);
   }
+  if (p.fin_kind) {
+    // this CTA wrote the partial rows tile0 .. tile0+mt-1 of its channel tile blockIdx.y
+    double* ts = reinterpret_cast<double*>(smem_raw + (smem_base - smem_u32(smem_raw)));     // the idle stage buffers
+    if (tree_arrive(p.tr, tile0, p.mt, (int)gridDim.y, ts)) tree_finish_bn(ts, p.bnf);
+  }
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -398,7 +407,7 @@ extern "C" {
 
 static int conv2d_fwd_impl(ubr_view x, const void* wpk, const float* bias, int out_ch, int ksize, int stride, ubr_view y,
                            float* y_f32, int y_f32_ld, void* stream, float* stats, int* stats_rows,
-                           const FusedEpi* epi = nullptr);
+                           const FusedEpi* epi = nullptr, const FusedFinal* fin = nullptr);
 
 int ubr_conv2d_fwd_fused(ubr_view x, const void* wpk, const float* bias, int out_ch, int ksize, int stride, int relu_pre,
                          ubr_view res, int relu_post, ubr_view y, void* stream) {
@@ -422,8 +431,26 @@ int ubr_conv2d_fwd_stats(ubr_view x, const void* wpk, const float* bias, int out
   return conv2d_fwd_impl(x, wpk, bias, out_ch, ksize, stride, y, nullptr, 0, stream, (float*)bn_workspace, stats_rows);
 }
 
+// conv + BatchNorm statistics + finalize in ONE launch (the partial rows are reduced by the last CTAs to arrive).
+// Returns 1 (nothing launched) where the conv kernel has no fused-statistics epilogue.
+int ubr_conv2d_fwd_bn(ubr_view x, const void* wpk, const float* bias, int out_ch, int ksize, int stride, ubr_view y,
+                      void* bn_workspace, void* tree, const float* gamma, const float* beta, float* running_mean,
+                      float* running_var, float momentum, float eps, float* scale, float* shift, float* mean,
+                      float* invstd, void* stream) {
+  UBR_REQUIRE(bn_workspace && tree && scale && shift, "conv2d_fwd_bn: null pointer");
+  FusedFinal f;
+  memset(&f, 0, sizeof(f));
+  f.tree = tree;
+  f.kind = 1;
+  f.bn = BnFinal{gamma, beta, running_mean, running_var, momentum, eps, (double)y.n * y.h * y.w, scale, shift, mean, invstd,
+                 out_ch, out_ch};
+  int rows = 0;
+  return conv2d_fwd_impl(x, wpk, bias, out_ch, ksize, stride, y, nullptr, 0, stream, (float*)bn_workspace, &rows, nullptr, &f);
+}
+
 static int conv2d_fwd_impl(ubr_view x, const void* wpk, const float* bias, int out_ch, int ksize, int stride, ubr_view y,
-                           float* y_f32, int y_f32_ld, void* stream, float* stats, int* stats_rows, const FusedEpi* epi) {
+                           float* y_f32, int y_f32_ld, void* stream, float* stats, int* stats_rows, const FusedEpi* epi,
+                           const FusedFinal* fin) {
   if (int rc = ensure_device()) return rc;
   UBR_REQUIRE(!(epi && (y_f32 || stats)), "conv2d_fwd: the fused epilogue writes bf16 and emits no statistics");
   if (int rc = check_view(x, "conv2d_fwd.x")) return rc;
@@ -470,7 +497,7 @@ static int conv2d_fwd_impl(ubr_view x, const void* wpk, const float* bias, int o
       UBR_REQUIRE(y_f32_ld >= out_ch, "conv2d_fwd: y_f32_ld too small");
     }
     const int hrc = conv_halo_try(x, wpk, ksize * ksize, n_pad, taps, nt, bias, y_f32 ? nullptr : &y, y_f32, y_f32_ld,
-                                  out_ch, (cudaStream_t)stream, 0, stats, stats_rows, 0, epi);
+                                  out_ch, (cudaStream_t)stream, 0, stats, stats_rows, 0, epi, nullptr, fin);
     if (hrc <= 0) return hrc;
   }
   if (stats) {
@@ -480,6 +507,11 @@ static int conv2d_fwd_impl(ubr_view x, const void* wpk, const float* bias, int o
     p.stats = stats;
     p.stats_c = out_ch;
     *stats_rows = tiles;
+    if (fin) {
+      p.fin_kind = 1;
+      p.tr = make_tree(fin->tree, stats, tiles, 2 * out_ch);
+      p.bnf = fin->bn;
+    }
   }
   p.bias = bias;
   if (y_f32) {
@@ -503,7 +535,30 @@ static int conv2d_fwd_impl(ubr_view x, const void* wpk, const float* bias, int o
 }
 
 static int conv2d_dgrad_impl(ubr_view dy, const void* wpk, int in_ch, int ksize, int stride, ubr_view dx, int accumulate,
-                             void* stream, const BnReduce* bnr = nullptr, float* stats = nullptr, int* stats_rows = nullptr);
+                             void* stream, const BnReduce* bnr = nullptr, float* stats = nullptr, int* stats_rows = nullptr,
+                             const FusedFinal* fin = nullptr);
+
+// ubr_conv2d_dgrad_bnreduce whose launch also finishes the two sums (sums[2][in_ch] behind the partial rows of
+// bn_workspace, dbeta / dgamma): follow it with ubr_bn_act_bwd_apply_final
+int ubr_conv2d_dgrad_bnreduce_final(ubr_view dy, const void* wpk, int in_ch, int ksize, int stride, ubr_view dx,
+                                    ubr_view y_pre, const float* scale, const float* shift, const float* mean,
+                                    const float* invstd, int relu, void* bn_workspace, void* tree, float* dgamma,
+                                    float* dbeta, int accumulate, void* stream) {
+  UBR_REQUIRE(bn_workspace && tree && scale && shift && mean && invstd, "conv2d_dgrad_bnreduce_final: null pointer");
+  if (stride != 1) return 1;
+  UBR_REQUIRE(y_pre.ptr && y_pre.n == dx.n && y_pre.h == dx.h && y_pre.w == dx.w && y_pre.c == in_ch && y_pre.ld % 8 == 0 &&
+                  ((uintptr_t)y_pre.ptr & 15) == 0,
+              "conv2d_dgrad_bnreduce_final: y_pre must match dx (n,h,w,c) with 16-byte aligned pixels");
+  BnReduce b{y_pre.ptr, y_pre.ld, relu, scale, shift, mean, invstd};
+  FusedFinal f;
+  memset(&f, 0, sizeof(f));
+  f.tree = tree;
+  f.kind = 2;
+  // same place as the stand-alone reduce passes keep their final sums
+  f.sums = SumsFinal{(float*)bn_workspace + (size_t)kRedBlocks * 4 * in_ch, {dbeta, dgamma, nullptr, nullptr}, in_ch, 2, in_ch, accumulate};
+  int rows = 0;
+  return conv2d_dgrad_impl(dy, wpk, in_ch, ksize, stride, dx, 0, stream, &b, (float*)bn_workspace, &rows, &f);
+}
 
 int ubr_conv2d_dgrad_bnreduce(ubr_view dy, const void* wpk, int in_ch, int ksize, int stride, ubr_view dx, ubr_view y_pre,
                               const float* scale, const float* shift, const float* mean, const float* invstd, int relu,
@@ -526,7 +581,7 @@ int ubr_conv2d_dgrad_acc(ubr_view dy, const void* wpk, int in_ch, int ksize, int
 }
 
 static int conv2d_dgrad_impl(ubr_view dy, const void* wpk, int in_ch, int ksize, int stride, ubr_view dx, int accumulate,
-                             void* stream, const BnReduce* bnr, float* stats, int* stats_rows) {
+                             void* stream, const BnReduce* bnr, float* stats, int* stats_rows, const FusedFinal* fin) {
   if (int rc = ensure_device()) return rc;
   if (int rc = check_view(dy, "conv2d_dgrad.dy")) return rc;
   if (int rc = check_view(dx, "conv2d_dgrad.dx")) return rc;
@@ -549,7 +604,7 @@ static int conv2d_dgrad_impl(ubr_view dy, const void* wpk, int in_ch, int ksize,
       for (int s = 0; s < ksize; ++s) taps[nt++] = TapSpec{pad - r, pad - s, 0, r * ksize + s};
     {
       const int hrc = conv_halo_try(dy, wpk, ksize * ksize, in_ch, taps, nt, nullptr, &dx, nullptr, 0, in_ch,
-                                    (cudaStream_t)stream, accumulate, stats, stats_rows, 0, nullptr, bnr);
+                                    (cudaStream_t)stream, accumulate, stats, stats_rows, 0, nullptr, bnr, fin);
       if (hrc <= 0) return hrc;
       if (bnr) return 1;                     // the fused reduction lives in the halo-resident epilogue only
     }

@@ -55,6 +55,11 @@ struct HaloParams {
   const __nv_bfloat16* bnr_y;
   int bnr_ld, bnr_relu;
   const float *bnr_scale, *bnr_shift, *bnr_mean, *bnr_invstd;
+  // stats: the reduction over the partial rows and its finalize run inside this launch (tree_reduce.cuh)
+  int fin_kind;                 // 0: none (rows are left for a finalize launch), 1: BnFinal, 2: SumsFinal
+  TreeRed tr;
+  BnFinal bnf;
+  SumsFinal sf;
 };
 
 template <int N>
@@ -480,6 +485,14 @@ __global__ void __launch_bounds__(kHThreads, 2) conv_halo_kernel(const __grid_co
     tc_fence_after();
     tmem_dealloc_dyn(tmem_base, p.tmem_cols);
   }
+  if (p.fin_kind) {
+    // partial row blockIdx.x is shared by the gridDim.y channel tiles; the last CTA of the grid finishes the reduction
+    double* ts = reinterpret_cast<double*>(smem_raw + (smem_base - smem_u32(smem_raw)));     // the idle weight / ring region
+    if (tree_arrive(p.tr, (int)blockIdx.x, 1, (int)gridDim.y, ts)) {
+      if (p.fin_kind == 1) tree_finish_bn(ts, p.bnf);
+      else tree_finish_sums(ts, p.sf);
+    }
+  }
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -509,7 +522,7 @@ static halo_kernel_t pick_halo_kernel(int ks, int ksteps) {
 int conv_halo_try(const ubr_view& x, const void* wpk, int nslabs, int n_pad, const TapSpec* taps, int ntaps,
                   const float* bias, const ubr_view* y, float* y_f32, int y_f32_ld, int out_cols,
                   cudaStream_t stream, int accumulate, float* stats, int* stats_rows, int shuffle_cout,
-                  const FusedEpi* epi, const BnReduce* bnr) {
+                  const FusedEpi* epi, const BnReduce* bnr, const FusedFinal* fin) {
   if (halo_disabled()) return 1;
   const int cin = x.c;
   if (!(cin == 16 || cin == 32 || cin == 64)) return 1;
@@ -649,6 +662,13 @@ int conv_halo_try(const ubr_view& x, const void* wpk, int nslabs, int n_pad, con
   if (ctas > p.ntiles) ctas = p.ntiles;
   p.stats_rows = ctas;
   if (stats_rows) *stats_rows = ctas;
+  if (fin && stats) {
+    UBR_REQUIRE(fin->tree != nullptr && ctas <= kTreeGroupCtas * kTreeMaxGroups, "conv_halo: bad fused-finalize state");
+    p.fin_kind = fin->kind;
+    p.tr = make_tree(fin->tree, stats, ctas, 2 * n_pad);
+    p.bnf = fin->bn; p.bnf.sq_off = n_pad;
+    p.sf = fin->sums; p.sf.row_stride = n_pad;
+  }
   dim3 grid((unsigned)ctas, (unsigned)n_tiles, 1);
   ::ubr::Launch(grid, kHThreads, smem, stream)(kern, p);
   UBR_LAUNCH_CHECK("conv_halo_kernel");

@@ -1,6 +1,7 @@
 // internal (non-ABI) declarations shared by the convolution translation units
 #pragma once
 #include "common.cuh"
+#include "tree_reduce.cuh"
 
 namespace ubr {
 
@@ -74,13 +75,22 @@ struct BnReduce {
   const float *scale, *shift, *mean, *invstd;
 };
 
+// Finalize folded into the producing conv launch (tree_reduce.cuh): the partial rows the epilogue emits are summed by the
+// last CTAs to arrive and turned into the BatchNorm affine (kind 1, forward statistics) or the backward sums (kind 2).
+struct FusedFinal {
+  void* tree;                   // ubr_bn_tree_bytes() of zero-initialised device memory
+  int kind;                     // 1: BnFinal, 2: SumsFinal
+  BnFinal bn;
+  SumsFinal sums;
+};
+
 // Halo-resident kernel (conv_halo.cu).  Returns 0 = launched, 1 = shape not eligible (caller falls back to the
 // tap-by-tap kernel), <0 = error.  `y` (bf16 view) or `y_f32` (fp32 [pixel][ld]) selects the output mode.
 int conv_halo_try(const ubr_view& x, const void* wpk, int nslabs, int n_pad, const TapSpec* taps, int ntaps,
                   const float* bias, const ubr_view* y, float* y_f32, int y_f32_ld, int out_cols,
                   cudaStream_t stream, int accumulate = 0, float* stats = nullptr,
                   int* stats_rows = nullptr, int shuffle_cout = 0, const FusedEpi* epi = nullptr,
-                  const BnReduce* bnr = nullptr);
+                  const BnReduce* bnr = nullptr, const FusedFinal* fin = nullptr);
 
 // Halo-resident weight gradient (wgrad_halo.cu).  Same return convention.
 int wgrad_halo_try(const ubr_view& x, const ubr_view& dy, int out_ch, int ksize, float* dw, int accumulate,

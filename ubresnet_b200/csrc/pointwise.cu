@@ -2,10 +2,10 @@
 // max-pool, pointwise sums.  All are HBM-roofline kernels: 16-byte vector accesses (8 bf16 channels per
 // thread), fp32 math, deterministic two-level reductions (per-block partials, fixed-order finalize).
 #include "common.cuh"
+#include "tree_reduce.cuh"
 
 namespace ubr {
 
-constexpr int kRedBlocks = 592;      // 4 x 148 SMs: partial rows of every reduction workspace
 constexpr int kRedThreads = 256;
 constexpr int kBwdRedBlocks = 296;   // 2 x 148: the backward reduce kernels keep 2 CTAs (x4 / x2 pixels in flight) per SM
 
@@ -84,6 +84,13 @@ __device__ __forceinline__ EwIdx ew_index(int cgs) {
   return EwIdx{(int)(g % cgs), g / cgs, t / cgs};
 }
 
+// dynamic shared memory of a reduce kernel: the block_reduce_store scratch, reused by the in-launch finalize tail
+static inline size_t red_smem(int ns, int c, bool tree) {
+  const size_t a = (size_t)kRedThreads * ns * 8 * sizeof(float);
+  const size_t b = tree ? tree_smem_bytes(ns * c, kRedThreads) : 0;
+  return a > b ? a : b;
+}
+
 static inline int red_blocks(long npix, int c, int cap = kRedBlocks) {
   const int lanes = kRedThreads / (c >> 3);
   long nb = (npix + (long)lanes * 8 - 1) / ((long)lanes * 8);
@@ -93,7 +100,8 @@ static inline int red_blocks(long npix, int c, int cap = kRedBlocks) {
 }
 
 // ------------------------------------------------------------------ BN forward statistics
-__global__ void __launch_bounds__(kRedThreads) bn_stats_kernel(DView y, float* partials) {
+// tr.tickets != null: the last CTA to arrive finishes the reduction and the BatchNorm finalize (tree_reduce.cuh)
+__global__ void __launch_bounds__(kRedThreads) bn_stats_kernel(DView y, float* partials, TreeRed tr, BnFinal fin) {
   pdl_prologue();
   const int cgs = y.c >> 3, lanes = blockDim.x / cgs;
   const int cg = threadIdx.x % cgs, pl = threadIdx.x / cgs;
@@ -117,6 +125,10 @@ __global__ void __launch_bounds__(kRedThreads) bn_stats_kernel(DView y, float* p
     }
   }
   block_reduce_store<2>(acc, y.c, partials);
+  if (tr.tickets) {
+    extern __shared__ __align__(16) double tree_smem[];       // the reduction scratch of block_reduce_store, now idle
+    if (tree_arrive(tr, blockIdx.x, 1, 1, tree_smem)) tree_finish_bn(tree_smem, fin);
+  }
 }
 
 // column sums of partials[nb][stride] for 32 consecutive columns starting at col0, by a (32 x 32) thread block:
@@ -259,7 +271,8 @@ __global__ void __launch_bounds__(256, 2) block_tail_kernel(DView y2, const floa
 // reduce: sums[0] = sum dz, sums[1] = sum dz*xhat
 __global__ void __launch_bounds__(kRedThreads, 2) bn_act_bwd_reduce_kernel(DView dout, DView y, const float* scale,
                                                                            const float* shift, const float* mean,
-                                                                           const float* invstd, int relu, float* partials) {
+                                                                           const float* invstd, int relu, float* partials,
+                                                                           TreeRed tr, SumsFinal fin) {
   pdl_prologue();
   const int cgs = y.c >> 3, lanes = blockDim.x / cgs;
   const int cg = threadIdx.x % cgs, pl = threadIdx.x / cgs;
@@ -298,6 +311,10 @@ __global__ void __launch_bounds__(kRedThreads, 2) bn_act_bwd_reduce_kernel(DView
     }
   }
   block_reduce_store<2>(acc, y.c, partials);
+  if (tr.tickets) {
+    extern __shared__ __align__(16) double tree_smem[];       // the reduction scratch of block_reduce_store, now idle
+    if (tree_arrive(tr, blockIdx.x, 1, 1, tree_smem)) tree_finish_sums(tree_smem, fin);
+  }
 }
 
 // per-channel pixel sums (conv bias gradients): partials[nb][2][c] of bn_stats -> out[0:nvalid) (fixed order, double)
@@ -388,7 +405,7 @@ __global__ void __launch_bounds__(kRedThreads, 2) tail_bwd_reduce_kernel(DView d
                                                                       const float* invstd2, DView res,
                                                                       const float* meanr, const float* invstdr,
                                                                       const float* sr, const float* br,
-                                                                      float* partials) {
+                                                                      float* partials, TreeRed tr, SumsFinal fin) {
   pdl_prologue();
   // RES_BN: the mask of the block's final ReLU is recomputed from y2 and the bypass output with the forward pass's own
   // arithmetic (block_tail_kernel) instead of reading `out` back
@@ -444,6 +461,10 @@ __global__ void __launch_bounds__(kRedThreads, 2) tail_bwd_reduce_kernel(DView d
     }
   }
   block_reduce_store<NS>(acc, y2.c, partials);
+  if (tr.tickets) {
+    extern __shared__ __align__(16) double tree_smem[];       // the reduction scratch of block_reduce_store, now idle
+    if (tree_arrive(tr, blockIdx.x, 1, 1, tree_smem)) tree_finish_sums(tree_smem, fin);
+  }
 }
 
 // dy2 = s2 * dz2 + A2 * y2 + B2 (see bn_act_bwd_apply_kernel);  dres = du | Gr * du + Ar * res + Br with
@@ -927,10 +948,29 @@ int ubr_bn_stats(ubr_view y, void* workspace, void* stream) {
   UBR_REQUIRE(workspace != nullptr, "bn_stats: null workspace");
   DView v = dv(y);
   const int nb = red_blocks(v.npix, v.c);
-  ::ubr::Launch(nb, kRedThreads, kRedThreads * 16 * sizeof(float), (cudaStream_t)stream)(bn_stats_kernel, v, (float*)workspace);
+  ::ubr::Launch(nb, kRedThreads, kRedThreads * 16 * sizeof(float), (cudaStream_t)stream)(bn_stats_kernel, v, (float*)workspace, TreeRed{}, BnFinal{});
   UBR_LAUNCH_CHECK("bn_stats_kernel");
   return 0;
 }
+
+// bn_stats + finalize in ONE launch: the last CTA to arrive finishes the reduction (tree_reduce.cuh)
+int ubr_bn_stats_final(ubr_view y, void* workspace, void* tree, const float* gamma, const float* beta, float* running_mean,
+                       float* running_var, float momentum, float eps, float* scale, float* shift, float* mean,
+                       float* invstd, void* stream) {
+  if (int rc = ensure_device()) return rc;
+  if (int rc = chk_red(y, "bn_stats_final.y")) return rc;
+  UBR_REQUIRE(workspace && tree && scale && shift, "bn_stats_final: null pointer");
+  UBR_REQUIRE(red_smem(2, y.c, true) <= 48 * 1024, "bn_stats_final: c=%d too wide for the in-launch finalize", y.c);
+  DView v = dv(y);
+  const int nb = red_blocks(v.npix, v.c);
+  BnFinal f{gamma, beta, running_mean, running_var, momentum, eps, (double)v.npix, scale, shift, mean, invstd, v.c, v.c};
+  ::ubr::Launch(nb, kRedThreads, red_smem(2, v.c, true), (cudaStream_t)stream)(
+      bn_stats_kernel, v, (float*)workspace, make_tree(tree, (const float*)workspace, nb, 2 * v.c), f);
+  UBR_LAUNCH_CHECK("bn_stats_kernel");
+  return 0;
+}
+
+uint64_t ubr_bn_tree_bytes(int c) { return (uint64_t)tree_bytes(c); }
 
 int ubr_bn_finalize(const void* workspace, int c, double count, const float* gamma, const float* beta,
                     float* running_mean, float* running_var, float momentum, float eps, float* scale, float* shift,
@@ -1006,8 +1046,49 @@ int ubr_bn_act_bwd_reduce(ubr_view dout, ubr_view y, const float* scale, const f
   UBR_REQUIRE(scale && shift && mean && invstd && workspace, "bn_act_bwd_reduce: null pointer");
   DView v = dv(y);
   const int nb = red_blocks(v.npix, v.c, kBwdRedBlocks);
-  ::ubr::Launch(nb, kRedThreads, kRedThreads * 16 * sizeof(float), (cudaStream_t)stream)(bn_act_bwd_reduce_kernel, dv(dout), v, scale, shift, mean, invstd, relu, (float*)workspace);
+  ::ubr::Launch(nb, kRedThreads, kRedThreads * 16 * sizeof(float), (cudaStream_t)stream)(bn_act_bwd_reduce_kernel, dv(dout), v, scale, shift, mean, invstd, relu, (float*)workspace, TreeRed{}, SumsFinal{});
   UBR_LAUNCH_CHECK("bn_act_bwd_reduce_kernel");
+  return 0;
+}
+
+// reduce pass that also finishes its sums (sums[2][c] behind the partial rows, dbeta / dgamma) in the same launch
+int ubr_bn_act_bwd_reduce_final(ubr_view dout, ubr_view y, const float* scale, const float* shift, const float* mean,
+                                const float* invstd, int relu, void* workspace, void* tree, float* dgamma, float* dbeta,
+                                int accumulate, void* stream) {
+  if (int rc = ensure_device()) return rc;
+  if (int rc = chk_red(y, "bn_act_bwd_reduce_final.y")) return rc;
+  if (int rc = chk(dout, "bn_act_bwd_reduce_final.dout")) return rc;
+  if (int rc = same_shape(y, dout, "bn_act_bwd_reduce_final")) return rc;
+  UBR_REQUIRE(scale && shift && mean && invstd && workspace && tree, "bn_act_bwd_reduce_final: null pointer");
+  UBR_REQUIRE(red_smem(2, y.c, true) <= 48 * 1024, "bn_act_bwd_reduce_final: c=%d too wide for the in-launch finalize", y.c);
+  DView v = dv(y);
+  const int nb = red_blocks(v.npix, v.c, kBwdRedBlocks);
+  float* sums = (float*)workspace + (size_t)kRedBlocks * 4 * v.c;
+  SumsFinal f{sums, {dbeta, dgamma, nullptr, nullptr}, v.c, 2, v.c, accumulate};
+  ::ubr::Launch(nb, kRedThreads, red_smem(2, v.c, true), (cudaStream_t)stream)(
+      bn_act_bwd_reduce_kernel, dv(dout), v, scale, shift, mean, invstd, relu, (float*)workspace,
+      make_tree(tree, (const float*)workspace, nb, 2 * v.c), f);
+  UBR_LAUNCH_CHECK("bn_act_bwd_reduce_kernel");
+  return 0;
+}
+
+// apply pass for sums that are already final (ubr_bn_act_bwd_reduce_final / ubr_conv2d_dgrad_bnreduce_final)
+int ubr_bn_act_bwd_apply_final(ubr_view dout, ubr_view y, const float* scale, const float* shift, const float* mean,
+                               const float* invstd, int relu, const void* workspace, double count, ubr_view dy,
+                               void* stream) {
+  if (int rc = ensure_device()) return rc;
+  if (int rc = chk_red(y, "bn_act_bwd_apply_final.y")) return rc;
+  if (int rc = chk(dout, "bn_act_bwd_apply_final.dout")) return rc;
+  if (int rc = chk(dy, "bn_act_bwd_apply_final.dy")) return rc;
+  if (int rc = same_shape(y, dout, "bn_act_bwd_apply_final(dout)")) return rc;
+  if (int rc = same_shape(y, dy, "bn_act_bwd_apply_final(dy)")) return rc;
+  UBR_REQUIRE(scale && shift && mean && invstd && workspace && count >= 1.0, "bn_act_bwd_apply_final: null pointer");
+  DView v = dv(y);
+  const float* sums = (const float*)workspace + (size_t)kRedBlocks * 4 * v.c;
+  ::ubr::Launch(ew_grid(v.npix, v.c >> 3, 4), 256, 0, (cudaStream_t)stream)(bn_act_bwd_apply_kernel, dv(dout), v, scale, shift, mean,
+                                                                             invstd, (const float*)nullptr, relu, sums,
+                                                                             (float)(1.0 / count), dvw(dy));
+  UBR_LAUNCH_CHECK("bn_act_bwd_apply_kernel");
   return 0;
 }
 
@@ -1080,9 +1161,44 @@ int ubr_block_tail_bwd_reduce(ubr_view dout, ubr_view out, ubr_view y2, const fl
     if (int rc = chk(res, "block_tail_bwd_reduce.res")) return rc;
     if (int rc = same_shape(y2, res, "block_tail_bwd_reduce(res)")) return rc;
     UBR_REQUIRE(meanr && invstdr && scaler && shiftr, "block_tail_bwd_reduce: null residual stats / affine");
-    ::ubr::Launch(nb, kRedThreads, kRedThreads * 32 * sizeof(float), st)(tail_bwd_reduce_kernel<true>, dv(dout), v, v, s2, b2, mean2, invstd2, dv(res), meanr, invstdr, scaler, shiftr, (float*)workspace);
+    ::ubr::Launch(nb, kRedThreads, kRedThreads * 32 * sizeof(float), st)(tail_bwd_reduce_kernel<true>, dv(dout), v, v, s2, b2, mean2, invstd2, dv(res), meanr, invstdr, scaler, shiftr, (float*)workspace, TreeRed{}, SumsFinal{});
   } else {
-    ::ubr::Launch(nb, kRedThreads, kRedThreads * 16 * sizeof(float), st)(tail_bwd_reduce_kernel<false>, dv(dout), dv(out), v, s2, b2, mean2, invstd2, v, nullptr, nullptr, nullptr, nullptr, (float*)workspace);
+    ::ubr::Launch(nb, kRedThreads, kRedThreads * 16 * sizeof(float), st)(tail_bwd_reduce_kernel<false>, dv(dout), dv(out), v, s2, b2, mean2, invstd2, v, nullptr, nullptr, nullptr, nullptr, (float*)workspace, TreeRed{}, SumsFinal{});
+  }
+  UBR_LAUNCH_CHECK("tail_bwd_reduce_kernel");
+  return 0;
+}
+
+// reduce pass of the block-tail backward that finishes its 2 / 4 sums and the BatchNorm parameter gradients itself
+int ubr_block_tail_bwd_reduce_final(ubr_view dout, ubr_view out, ubr_view y2, const float* s2, const float* b2,
+                                    const float* mean2, const float* invstd2, ubr_view res, const float* meanr,
+                                    const float* invstdr, const float* scaler, const float* shiftr, int res_is_bn,
+                                    void* workspace, void* tree, float* dgamma2, float* dbeta2, float* dgammar,
+                                    float* dbetar, int accumulate, void* stream) {
+  if (int rc = ensure_device()) return rc;
+  if (int rc = chk_red(y2, "block_tail_bwd_reduce_final.y2")) return rc;
+  if (int rc = chk(dout, "block_tail_bwd_reduce_final.dout")) return rc;
+  if (!res_is_bn) {
+    if (int rc = chk(out, "block_tail_bwd_reduce_final.out")) return rc;
+    if (int rc = same_shape(y2, out, "block_tail_bwd_reduce_final(out)")) return rc;
+  }
+  if (int rc = same_shape(y2, dout, "block_tail_bwd_reduce_final(dout)")) return rc;
+  UBR_REQUIRE(s2 && b2 && mean2 && invstd2 && workspace && tree, "block_tail_bwd_reduce_final: null pointer");
+  UBR_REQUIRE(red_smem(4, y2.c, true) <= 48 * 1024, "block_tail_bwd_reduce_final: c=%d too wide for the in-launch finalize", y2.c);
+  DView v = dv(y2);
+  const int nb = red_blocks(v.npix, v.c, kBwdRedBlocks);
+  const int ns = res_is_bn ? 4 : 2;
+  float* sums = (float*)workspace + (size_t)kRedBlocks * 4 * v.c;
+  SumsFinal f{sums, {dbeta2, dgamma2, res_is_bn ? dbetar : nullptr, res_is_bn ? dgammar : nullptr}, v.c, ns, v.c, accumulate};
+  const TreeRed tr = make_tree(tree, (const float*)workspace, nb, ns * v.c);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (res_is_bn) {
+    if (int rc = chk(res, "block_tail_bwd_reduce_final.res")) return rc;
+    if (int rc = same_shape(y2, res, "block_tail_bwd_reduce_final(res)")) return rc;
+    UBR_REQUIRE(meanr && invstdr && scaler && shiftr, "block_tail_bwd_reduce_final: null residual stats / affine");
+    ::ubr::Launch(nb, kRedThreads, red_smem(4, v.c, true), st)(tail_bwd_reduce_kernel<true>, dv(dout), v, v, s2, b2, mean2, invstd2, dv(res), meanr, invstdr, scaler, shiftr, (float*)workspace, tr, f);
+  } else {
+    ::ubr::Launch(nb, kRedThreads, red_smem(2, v.c, true), st)(tail_bwd_reduce_kernel<false>, dv(dout), dv(out), v, s2, b2, mean2, invstd2, v, nullptr, nullptr, nullptr, nullptr, (float*)workspace, tr, f);
   }
   UBR_LAUNCH_CHECK("tail_bwd_reduce_kernel");
   return 0;
@@ -1121,6 +1237,44 @@ int ubr_block_tail_bwd_apply(ubr_view dout, ubr_view out, ubr_view y2, const flo
   if (res_is_bn) {
     if (int rc = chk(res, "block_tail_bwd_apply.res")) return rc;
     UBR_REQUIRE(meanr && invstdr && gammar && scaler && shiftr, "block_tail_bwd_apply: null residual stats / affine");
+    ::ubr::Launch(blocks, 256, 0, st)(tail_bwd_apply_kernel<true>, dv(dout), v, v, s2, b2, mean2, invstd2, dv(res), meanr,
+                                                        invstdr, gammar, scaler, shiftr, sums, (float)(1.0 / count),
+                                                        dvw(dy2), dvw(dres));
+  } else {
+    ::ubr::Launch(blocks, 256, 0, st)(tail_bwd_apply_kernel<false>, dv(dout), dv(out), v, s2, b2, mean2, invstd2, v, nullptr,
+                                                         nullptr, nullptr, nullptr, nullptr, sums, (float)(1.0 / count),
+                                                         dvw(dy2), dvw(dres));
+  }
+  UBR_LAUNCH_CHECK("tail_bwd_apply_kernel");
+  return 0;
+}
+
+// apply pass of the block-tail backward for sums that are already final (ubr_block_tail_bwd_reduce_final)
+int ubr_block_tail_bwd_apply_final(ubr_view dout, ubr_view out, ubr_view y2, const float* s2, const float* b2,
+                                   const float* mean2, const float* invstd2, ubr_view res, const float* meanr,
+                                   const float* invstdr, const float* gammar, const float* scaler, const float* shiftr,
+                                   int res_is_bn, const void* workspace, double count, ubr_view dy2, ubr_view dres,
+                                   void* stream) {
+  if (int rc = ensure_device()) return rc;
+  if (int rc = chk_red(y2, "block_tail_bwd_apply_final.y2")) return rc;
+  if (int rc = chk(dout, "block_tail_bwd_apply_final.dout")) return rc;
+  if (!res_is_bn) {
+    if (int rc = chk(out, "block_tail_bwd_apply_final.out")) return rc;
+    if (int rc = same_shape(y2, out, "block_tail_bwd_apply_final(out)")) return rc;
+  }
+  if (int rc = chk(dy2, "block_tail_bwd_apply_final.dy2")) return rc;
+  if (int rc = chk(dres, "block_tail_bwd_apply_final.dres")) return rc;
+  if (int rc = same_shape(y2, dout, "block_tail_bwd_apply_final(dout)")) return rc;
+  if (int rc = same_shape(y2, dy2, "block_tail_bwd_apply_final(dy2)")) return rc;
+  if (int rc = same_shape(y2, dres, "block_tail_bwd_apply_final(dres)")) return rc;
+  UBR_REQUIRE(s2 && b2 && mean2 && invstd2 && workspace && count >= 1.0, "block_tail_bwd_apply_final: null pointer");
+  DView v = dv(y2);
+  const float* sums = (const float*)workspace + (size_t)kRedBlocks * 4 * v.c;
+  cudaStream_t st = (cudaStream_t)stream;
+  const unsigned blocks = ew_grid(v.npix, v.c >> 3, 2);
+  if (res_is_bn) {
+    if (int rc = chk(res, "block_tail_bwd_apply_final.res")) return rc;
+    UBR_REQUIRE(meanr && invstdr && gammar && scaler && shiftr, "block_tail_bwd_apply_final: null residual stats / affine");
     ::ubr::Launch(blocks, 256, 0, st)(tail_bwd_apply_kernel<true>, dv(dout), v, v, s2, b2, mean2, invstd2, dv(res), meanr,
                                                         invstdr, gammar, scaler, shiftr, sums, (float)(1.0 / count),
                                                         dvw(dy2), dvw(dres));
@@ -1266,7 +1420,7 @@ int ubr_channel_sum(ubr_view a, int nvalid, void* workspace, float* out, int acc
   DView v = dv(a);
   const int nb = red_blocks(v.npix, v.c);
   cudaStream_t st = (cudaStream_t)stream;
-  ::ubr::Launch(nb, kRedThreads, kRedThreads * 16 * sizeof(float), st)(bn_stats_kernel, v, (float*)workspace);
+  ::ubr::Launch(nb, kRedThreads, kRedThreads * 16 * sizeof(float), st)(bn_stats_kernel, v, (float*)workspace, TreeRed{}, BnFinal{});
   UBR_LAUNCH_CHECK("bn_stats_kernel");
   ::ubr::Launch(ceil_div(v.c, 32), dim3(32, kColLanes), 0, st)(channel_sum_finish_kernel, (const float*)workspace, nb, v.c,
                                                                nvalid, out, accumulate);
@@ -1302,7 +1456,7 @@ int ubr_channel_sum_static(ubr_view a, int nvalid, float* out, int accumulate, v
   DView v = dv(a);
   const int nb = red_blocks(v.npix, v.c);
   cudaStream_t st = (cudaStream_t)stream;
-  ::ubr::Launch(nb, kRedThreads, kRedThreads * 16 * sizeof(float), st)(bn_stats_kernel, v, scratch);
+  ::ubr::Launch(nb, kRedThreads, kRedThreads * 16 * sizeof(float), st)(bn_stats_kernel, v, scratch, TreeRed{}, BnFinal{});
   UBR_LAUNCH_CHECK("bn_stats_kernel");
   ::ubr::Launch(ceil_div(v.c, 32), dim3(32, kColLanes), 0, st)(channel_sum_finish_kernel, (const float*)scratch, nb, v.c,
                                                                nvalid, out, accumulate);

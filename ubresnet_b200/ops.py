@@ -1,6 +1,8 @@
 """Thin torch-tensor wrappers over the C ABI.  Device memory, streams and allocation are PyTorch's;
 every byte of arithmetic happens in libubresnet_b200.so.  No fallback paths.
 """
+import os
+
 import torch
 
 from . import _lib
@@ -8,6 +10,15 @@ from ._lib import View
 
 BN_EPS = 1e-5
 BN_MOMENTUM = 0.1
+# Reductions (BatchNorm statistics, BatchNorm-backward sums) are finished inside the producing launch by the last CTAs
+# to arrive (csrc/tree_reduce.cuh) instead of by a separate finalize launch; UBR_TREE_FINALIZE=0 keeps the two-launch form.
+TREE_FINALIZE = os.environ.get("UBR_TREE_FINALIZE", "1") != "0"
+
+
+def _tree(ws):
+    """device pointer of the arrival-ticket tree that rides on a workspace made by bn_workspace(), or 0"""
+    t = getattr(ws, "tree", None) if TREE_FINALIZE else None
+    return 0 if t is None else t.data_ptr()
 
 
 def _stream():
@@ -150,21 +161,35 @@ def block_chain_fwd(x, w1pk, b1, w2pk, b2, planes, res, y=None):
 
 
 def conv2d_fwd_bn(x, wpk, bias, out_ch, ksize, stride, gamma, beta, running_mean, running_var, ws, y=None,
-                  momentum=BN_MOMENTUM, eps=BN_EPS):
+                  momentum=BN_MOMENTUM, eps=BN_EPS, state=None):
     """conv forward + training-mode BatchNorm statistics.  Where the conv kernel has a fused-statistics epilogue the
     stand-alone bn_stats pass over y is skipped.  Returns (y, BNState)."""
     import ctypes
     lib = _lib.load()
     if y is None:
         y = Act.empty(x.n, x.h // stride, x.w // stride, out_ch, x.buf.device)
+    tree = _tree(ws)
+    if tree:
+        st = state or BNState(y.c, y.buf.device)
+        st.count = float(y.npix)
+        rc = lib.ubr_conv2d_fwd_bn(x.view(), wpk.data_ptr(), _ptr(bias), out_ch, ksize, stride, y.view(), ws.data_ptr(), tree,
+                                   _ptr(gamma), _ptr(beta), _ptr(running_mean), _ptr(running_var), momentum, eps,
+                                   st.scale.data_ptr(), st.shift.data_ptr(), st.mean.data_ptr(), st.invstd.data_ptr(),
+                                   _stream())
+        if rc == 1:
+            conv2d_fwd(x, wpk, bias, out_ch, ksize, stride, y=y)
+            return y, bn_train_stats(y, gamma, beta, running_mean, running_var, ws, state=st, momentum=momentum, eps=eps)
+        _lib.check(rc, "conv2d_fwd_bn")
+        _bump(running_mean, running_var)
+        return y, st
     rows = ctypes.c_int(0)
     rc = lib.ubr_conv2d_fwd_stats(x.view(), wpk.data_ptr(), _ptr(bias), out_ch, ksize, stride, y.view(), ws.data_ptr(),
                                   ctypes.addressof(rows), _stream())
     if rc == 1:
         conv2d_fwd(x, wpk, bias, out_ch, ksize, stride, y=y)
-        return y, bn_train_stats(y, gamma, beta, running_mean, running_var, ws, momentum=momentum, eps=eps)
+        return y, bn_train_stats(y, gamma, beta, running_mean, running_var, ws, state=state, momentum=momentum, eps=eps)
     _lib.check(rc, "conv2d_fwd_stats")
-    st = BNState(y.c, y.buf.device)
+    st = state or BNState(y.c, y.buf.device)
     st.count = float(y.npix)
     _lib.check(lib.ubr_bn_finalize_rows(ws.data_ptr(), rows.value, y.c, st.count, _ptr(gamma), _ptr(beta),
                                         _ptr(running_mean), _ptr(running_var), momentum, eps, st.scale.data_ptr(),
@@ -189,6 +214,21 @@ def conv2d_dgrad_bn_bwd(dy, wpk, in_ch, ksize, stride, y_pre, st, relu, ws, dgam
     import ctypes
     lib = _lib.load()
     da = Act.empty(dy.n, dy.h * stride, dy.w * stride, in_ch, dy.buf.device)
+    tree = _tree(ws)
+    if tree:
+        rc = lib.ubr_conv2d_dgrad_bnreduce_final(dy.view(), wpk.data_ptr(), in_ch, ksize, stride, da.view(), y_pre.view(),
+                                                 st.scale.data_ptr(), st.shift.data_ptr(), st.mean.data_ptr(),
+                                                 st.invstd.data_ptr(), int(relu), ws.data_ptr(), tree, _ptr(dgamma),
+                                                 _ptr(dbeta), 0, _stream())
+        if rc == 1:
+            conv2d_dgrad(dy, wpk, in_ch, ksize, stride, dx=da)
+            return bn_act_bwd(da, y_pre, st, relu, ws, dgamma, dbeta)
+        _lib.check(rc, "conv2d_dgrad_bnreduce_final")
+        dyp = Act.empty(y_pre.n, y_pre.h, y_pre.w, y_pre.c, y_pre.buf.device)
+        _lib.check(lib.ubr_bn_act_bwd_apply_final(da.view(), y_pre.view(), st.scale.data_ptr(), st.shift.data_ptr(),
+                                                  st.mean.data_ptr(), st.invstd.data_ptr(), int(relu), ws.data_ptr(),
+                                                  st.count, dyp.view(), _stream()), "bn_act_bwd_apply_final")
+        return dyp
     rows = ctypes.c_int(0)
     rc = lib.ubr_conv2d_dgrad_bnreduce(dy.view(), wpk.data_ptr(), in_ch, ksize, stride, da.view(), y_pre.view(),
                                        st.scale.data_ptr(), st.shift.data_ptr(), st.mean.data_ptr(), st.invstd.data_ptr(),
@@ -365,8 +405,12 @@ def stem_conv_wgrad(x, dy, dw, db, accumulate, ws):
 
 
 def bn_workspace(c, device):
-    nbytes = int(_lib.load().ubr_bn_workspace_bytes(c))
-    return torch.empty(nbytes // 4, dtype=torch.float32, device=device)
+    """reduction workspace for layers of up to `c` channels: partial rows + final sums, and riding on it as `.tree` the
+    zero-initialised arrival tickets / second-level rows of the in-launch finalize (csrc/tree_reduce.cuh)"""
+    lib = _lib.load()
+    ws = torch.empty(int(lib.ubr_bn_workspace_bytes(c)) // 4, dtype=torch.float32, device=device)
+    ws.tree = torch.zeros(int(lib.ubr_bn_tree_bytes(c)) // 4, dtype=torch.float32, device=device)
+    return ws
 
 
 class BNState:
@@ -383,6 +427,13 @@ def bn_train_stats(y, gamma, beta, running_mean, running_var, ws, state=None, mo
     lib = _lib.load()
     st = state or BNState(y.c, y.buf.device)
     st.count = float(y.npix)
+    tree = _tree(ws)
+    if tree:
+        _lib.check(lib.ubr_bn_stats_final(y.view(), ws.data_ptr(), tree, _ptr(gamma), _ptr(beta), _ptr(running_mean),
+                                          _ptr(running_var), momentum, eps, st.scale.data_ptr(), st.shift.data_ptr(),
+                                          st.mean.data_ptr(), st.invstd.data_ptr(), _stream()), "bn_stats_final")
+        _bump(running_mean, running_var)
+        return st
     _lib.check(lib.ubr_bn_stats(y.view(), ws.data_ptr(), _stream()), "bn_stats")
     _lib.check(lib.ubr_bn_finalize(ws.data_ptr(), y.c, st.count, _ptr(gamma), _ptr(beta), _ptr(running_mean),
                                    _ptr(running_var), momentum, eps, st.scale.data_ptr(), st.shift.data_ptr(),
@@ -426,6 +477,15 @@ def bn_act_bwd(dout, y, st, relu, ws, dgamma=None, dbeta=None, accumulate=False,
     if dy is None:
         dy = Act.empty(y.n, y.h, y.w, y.c, y.buf.device)
     s = _stream()
+    tree = _tree(ws)
+    if tree:
+        _lib.check(lib.ubr_bn_act_bwd_reduce_final(dout.view(), y.view(), st.scale.data_ptr(), st.shift.data_ptr(),
+                                                   st.mean.data_ptr(), st.invstd.data_ptr(), int(relu), ws.data_ptr(), tree,
+                                                   _ptr(dgamma), _ptr(dbeta), int(accumulate), s), "bn_act_bwd_reduce_final")
+        _lib.check(lib.ubr_bn_act_bwd_apply_final(dout.view(), y.view(), st.scale.data_ptr(), st.shift.data_ptr(),
+                                                  st.mean.data_ptr(), st.invstd.data_ptr(), int(relu), ws.data_ptr(),
+                                                  st.count, dy.view(), s), "bn_act_bwd_apply_final")
+        return dy
     _lib.check(lib.ubr_bn_act_bwd_reduce(dout.view(), y.view(), st.scale.data_ptr(), st.shift.data_ptr(),
                                          st.mean.data_ptr(), st.invstd.data_ptr(), int(relu), ws.data_ptr(), s),
                "bn_act_bwd_reduce")
@@ -453,6 +513,18 @@ def block_tail_bwd(dout, out, y2, st2, res, st_res, gamma_res, ws, dgamma2=None,
     sr = st_res.scale.data_ptr() if res_bn else 0
     br = st_res.shift.data_ptr() if res_bn else 0
     ov = out.view() if (out is not None and not res_bn) else _NULLVIEW
+    tree = _tree(ws)
+    if tree:
+        _lib.check(lib.ubr_block_tail_bwd_reduce_final(dout.view(), ov, y2.view(), st2.scale.data_ptr(),
+                                                       st2.shift.data_ptr(), st2.mean.data_ptr(), st2.invstd.data_ptr(),
+                                                       rv, mr, ir, sr, br, int(res_bn), ws.data_ptr(), tree, _ptr(dgamma2),
+                                                       _ptr(dbeta2), _ptr(dgamma_res), _ptr(dbeta_res), int(accumulate), s),
+                   "block_tail_bwd_reduce_final")
+        _lib.check(lib.ubr_block_tail_bwd_apply_final(dout.view(), ov, y2.view(), st2.scale.data_ptr(),
+                                                      st2.shift.data_ptr(), st2.mean.data_ptr(), st2.invstd.data_ptr(), rv,
+                                                      mr, ir, _ptr(gamma_res), sr, br, int(res_bn), ws.data_ptr(), st2.count,
+                                                      dy2.view(), dres.view(), s), "block_tail_bwd_apply_final")
+        return dy2, dres
     _lib.check(lib.ubr_block_tail_bwd_reduce(dout.view(), ov, y2.view(), st2.scale.data_ptr(),
                                              st2.shift.data_ptr(), st2.mean.data_ptr(), st2.invstd.data_ptr(), rv, mr,
                                              ir, sr, br, int(res_bn), ws.data_ptr(), s), "block_tail_bwd_reduce")
