@@ -249,7 +249,7 @@ def _conv_call_work(fn, a):
     """(algorithmic FLOPs, algorithmic HBM bytes) of one conv C-ABI call from its raw arguments (Views are (n,h,w,c)).
     FLOPs = 2*M*N*K of the contraction; bytes = each operand / result tensor once (bf16), the DESIGN.md figure."""
     npx = lambda v: v[0] * v[1] * v[2]
-    if fn in ("ubr_conv2d_fwd", "ubr_conv2d_fwd_stats"):
+    if fn in ("ubr_conv2d_fwd", "ubr_conv2d_fwd_stats", "ubr_conv2d_fwd_bn", "ubr_conv2d_fwd_fused"):
         x, out_ch, k, st = a[0], a[3], a[4], a[5]
         m = npx(x) // (st * st)
         return 2.0 * m * x[3] * out_ch * k * k, 2.0 * (npx(x) * x[3] + m * max(out_ch, 16))
@@ -257,7 +257,7 @@ def _conv_call_work(fn, a):
         dy, in_ch, k, st = a[0], a[2], a[3], a[4]
         b = 2.0 * (npx(dy) * dy[3] + npx(dy) * st * st * in_ch * (2 if fn.endswith("_acc") else 1))
         return 2.0 * npx(dy) * dy[3] * in_ch * k * k, b
-    if fn == "ubr_conv2d_dgrad_bnreduce":
+    if fn in ("ubr_conv2d_dgrad_bnreduce", "ubr_conv2d_dgrad_bnreduce_final"):
         # data gradient + the BatchNorm-backward reduction it carries: reads dy and y_pre, writes dx
         dy, in_ch, k = a[0], a[2], a[3]
         return 2.0 * npx(dy) * dy[3] * in_ch * k * k, 2.0 * (npx(dy) * dy[3] + 2 * npx(dy) * in_ch)
@@ -296,6 +296,44 @@ def conv_kernel_classes(groups, nsteps):
     for ent in out.values():
         ent["tflops"] = ent["gflop"] / ent["ms"] if ent["ms"] else None
         ent["gbs"] = ent["gbytes"] / ent["ms"] * 1e3 if ent["ms"] else None
+    return out
+
+
+def conv_bound_split(groups, nsteps, peaks):
+    """Every conv launch against ITS OWN roofline: a launch is tensor bound when its algorithmic FLOPs / sustained bf16
+    peak exceed its algorithmic bytes / HBM peak (arithmetic intensity above the ridge), HBM bound otherwise -- one kernel
+    template serves both kinds (3x3 at 16 channels: 72 FLOP/B, 7x7: 392 FLOP/B, ridge ~210).  Returns per bound the
+    launches, time, achieved rate and fraction of that peak, the FLOP-weighted tensor fraction and
+    `mixed_frac` = sum of the launches' roofline times / sum of their measured times."""
+    tf, bw = peaks["tf_sustained"] * 1e12, peaks["hbm_gbs"] * 1e9
+    acc = {"tensor": [0, 0.0, 0.0, 0.0, 0.0], "hbm": [0, 0.0, 0.0, 0.0, 0.0]}     # launches, ms, flop, bytes, flop*frac
+    roof_ms = 0.0
+    for kern, calls in groups.items():
+        names = kern.split("+") if kern else []
+        if not names or names[0] not in ("conv_halo_kernel", "conv_gemm_kernel", "wgrad_halo_kernel", "wgrad_gemm_kernel"):
+            continue
+        for fn, a, ms in calls:
+            work = _conv_call_work(fn, a)
+            if work is None or ms <= 0:
+                continue
+            t_tensor, t_hbm = work[0] / tf * 1e3, work[1] / bw * 1e3
+            e = acc["tensor" if t_tensor >= t_hbm else "hbm"]
+            e[0] += 1; e[1] += ms; e[2] += work[0]; e[3] += work[1]; e[4] += work[0] * (t_tensor / ms)
+            roof_ms += max(t_tensor, t_hbm)
+    tot_ms = acc["tensor"][1] + acc["hbm"][1]
+    if tot_ms <= 0:
+        return None
+    t, h = acc["tensor"], acc["hbm"]
+    out = {"ridge_flop_per_byte": tf / bw, "mixed_frac": roof_ms / tot_ms,
+           "what": "per-launch roofline: tensor bound if FLOPs/peak >= bytes/peak, else HBM bound; mixed_frac = sum(roofline "
+                   "time) / sum(measured time) over all conv launches of a step"}
+    if t[1] > 0:
+        out["tensor_bound"] = {"launches_per_step": t[0] / nsteps, "ms_per_step": t[1] / nsteps,
+                               "achieved_tflops": t[2] / t[1] / 1e9, "frac_of_bf16_sustained": t[2] / t[1] / 1e9 / peaks["tf_sustained"],
+                               "frac_flop_weighted": t[4] / t[2] if t[2] else None}
+    if h[1] > 0:
+        out["hbm_bound"] = {"launches_per_step": h[0] / nsteps, "ms_per_step": h[1] / nsteps,
+                            "achieved_gbs": h[3] / h[1] / 1e6, "frac_of_hbm_peak": h[3] / h[1] / 1e6 / peaks["hbm_gbs"]}
     return out
 
 
@@ -544,15 +582,16 @@ def run_own(args, rank, world, local_rank):
     nprof = 2
     prof = None
     from ubresnet_b200 import engine as _engine
-    side = _engine.WGRAD_SIDE_STREAM
-    _engine.WGRAD_SIDE_STREAM = False          # per-kernel durations are taken with every kernel alone on the GPU
+    side, branch = _engine.WGRAD_SIDE_STREAM, _engine.BRANCH_MAX_RES
+    _engine.WGRAD_SIDE_STREAM = False          # per-kernel durations are taken with every kernel alone on the GPU:
+    _engine.BRANCH_MAX_RES = 0                 # no weight-gradient side stream, no bypass branch stream
     if rank == 0:
         prof = _lib.enable_profiling()
         prof.records.clear()
     for i in range(nprof):
         step_resident(i)
     barrier()
-    _engine.WGRAD_SIDE_STREAM = side
+    _engine.WGRAD_SIDE_STREAM, _engine.BRANCH_MAX_RES = side, branch
     if rank == 0:
         summ = prof.summary()
         groups = prof.by_kernel()
@@ -561,6 +600,8 @@ def run_own(args, rank, world, local_rank):
         peaks = load_peaks()
         klass = conv_kernel_classes(groups, nprof)
         roof = make_roofline(klass, peaks, tot / nprof)
+        if roof is not None:
+            roof["by_bound"] = conv_bound_split(groups, nprof, peaks)
         kernels = {k: {"calls_per_step": c / nprof, "ms_per_step": t / nprof} for k, (c, t) in
                    sorted(summ.items(), key=lambda kv: -kv[1][1])}
 

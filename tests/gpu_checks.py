@@ -723,6 +723,25 @@ CHECKS = {
 }
 
 
+def _with_conv_tails(fn):
+    """run a check with the in-launch finalize of the conv epilogues switched on (ops.TREE_FINALIZE_CONV, off by default)"""
+    def run():
+        old = ops.TREE_FINALIZE_CONV
+        ops.TREE_FINALIZE_CONV = ops.TREE_FINALIZE
+        try:
+            return [(lbl + " [in-launch finalize]", err, tol) for lbl, err, tol in fn()]
+        finally:
+            ops.TREE_FINALIZE_CONV = old
+    return run
+
+
+# the same statistics checks with the reduction finished inside the conv launch (ubr_conv2d_fwd_bn, tree_reduce.cuh)
+CHECKS.update({
+    "halo_fwd_bn_tail": _with_conv_tails(CHECKS["halo_fwd_bn"]),
+    "gemm_fwd_bn_tail": _with_conv_tails(CHECKS["gemm_fwd_bn"]),
+})
+
+
 # ASPP_ResNet operators (reference models/ASPP_ResNet.py:188-286): dilated branches, stride-1 max-pool, and the
 # 192/320/576/384/768-channel concat operands (64-wide N tiles in conv_gemm / wgrad_gemm)
 CHECKS.update({

@@ -608,6 +608,18 @@ def fp32_parity(batch=2, size=128, trained=True, train=True, seed=1234, num_clas
     return res, {}
 
 
+def _fused_bn_reduce_tail():
+    """fused_bn_reduce with the sums finished inside the data-gradient launch (ops.TREE_FINALIZE_CONV, off by default)"""
+    from ubresnet_b200 import ops
+    old = ops.TREE_FINALIZE_CONV
+    ops.TREE_FINALIZE_CONV = ops.TREE_FINALIZE
+    try:
+        res, extra = fused_bn_reduce()
+        return [(lbl + " [in-launch finalize]", err, tol) for lbl, err, tol in res], extra
+    finally:
+        ops.TREE_FINALIZE_CONV = old
+
+
 def fused_bn_reduce():
     """ubr_conv2d_dgrad_bnreduce (BatchNorm-backward reduction in the data-gradient epilogue) against the unfused
     sequence dgrad -> bn_act_bwd_reduce -> bn_act_bwd_apply: same da (bit-identical), same sums up to summation order"""
@@ -636,7 +648,7 @@ def fused_bn_reduce():
         ref = ops.bn_act_bwd(da, ypre, st, relu, ws2, dg_b, db_b)
         torch.cuda.synchronize()
         tag = "k%d %d->%d %dx%dx%d relu=%d" % (k, cout, cin, n, h, w, relu)
-        want = 2 if ops.TREE_FINALIZE else 3       # dgrad (+ in-launch finalize) + apply | dgrad + sums finalize + apply
+        want = 2 if ops.TREE_FINALIZE_CONV else 3       # dgrad (+ in-launch finalize) + apply | dgrad + sums finalize + apply
         res.append((tag + " fused path taken (%d launches)" % want, 0.0 if launches == want else 1.0, 0.0))
         res.append((tag + " dy_pre", _rel(fused.torch(), ref.torch()), 1e-2))
         res.append((tag + " dgamma", _rel(dg_a, dg_b), 1e-4))
@@ -693,6 +705,7 @@ CHECKS = {
     "golden": lambda: golden_parity(),
     "advice_regressions": lambda: advice_regressions(),
     "fused_bn_reduce": lambda: fused_bn_reduce(),
+    "fused_bn_reduce_tail": lambda: _fused_bn_reduce_tail(),
     "graphed_step": lambda: graphed_step(),
     # fp32 precision mode: 1e-4 against the fp32 oracle
     "fp32_ops": lambda: fp32_ops(),

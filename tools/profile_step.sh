@@ -7,7 +7,7 @@
 set -u
 TAG=${1:-prof}
 OUT=gpurun_out
-CMD="env UBR_WGRAD_STREAM=0 python bench.py --steps 1 --warmup 1 --no-cpu --no-infer --no-graph --no-library --no-aspp"
+CMD="env UBR_WGRAD_STREAM=0 UBR_BRANCH_MAX_RES=0 python bench.py --steps 1 --warmup 1 --no-cpu --no-infer --no-graph --no-library --no-aspp"
 mkdir -p $OUT
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 6000 --csv --log-file $OUT/${TAG}_launches.csv $CMD > $OUT/${TAG}_ncu_list.log 2>&1
 echo "launch list rc=$?"

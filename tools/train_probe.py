@@ -1,5 +1,5 @@
 """per C-ABI-call timing of one training step (batch 32, 512x512, side stream off): where the step goes, by entry point AND
-by resolution of the tensor the call works on.  usage: python tools/train_probe.py [--calls]"""
+by resolution of the tensor the call works on.  usage: python tools/train_probe.py [--calls] [--aspp]"""
 import collections
 import os
 import sys
@@ -8,12 +8,14 @@ import torch
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 os.environ.setdefault("UBR_WGRAD_STREAM", "0")
+os.environ.setdefault("UBR_BRANCH_MAX_RES", "0")
 from ubresnet_b200 import _lib, synthetic                                   # noqa: E402
 from ubresnet_b200.models import UResNet                                    # noqa: E402
+from ubresnet_b200.models.ASPP_ResNet import ASPP_ResNet                    # noqa: E402
 from ubresnet_b200.training.pixelwise_nllloss import PixelWiseNLLLoss       # noqa: E402
 
 torch.manual_seed(1)
-m = UResNet(3, 1, 16).cuda().train()
+m = (ASPP_ResNet(3, 1, 16, showsizes=False) if "--aspp" in sys.argv else UResNet(3, 1, 16)).cuda().train()
 img, lab, wgt = [t.cuda() for t in synthetic.make_batch(32, 512, 512)]
 crit = PixelWiseNLLLoss()
 

@@ -13,6 +13,11 @@ BN_MOMENTUM = 0.1
 # Reductions (BatchNorm statistics, BatchNorm-backward sums) are finished inside the producing launch by the last CTAs
 # to arrive (csrc/tree_reduce.cuh) instead of by a separate finalize launch; UBR_TREE_FINALIZE=0 keeps the two-launch form.
 TREE_FINALIZE = os.environ.get("UBR_TREE_FINALIZE", "1") != "0"
+# ... and the same inside the CONV launches that emit statistics from their epilogue (ubr_conv2d_fwd_bn,
+# ubr_conv2d_dgrad_bnreduce_final).  Off by default: the step time is the same either way (the finalize launch is hidden
+# by programmatic dependent launch, the in-launch tail is a ~5-10 us single-CTA epilogue), and with the tail inside, a
+# conv kernel's measured duration -- the denominator of its roofline fraction -- would carry the finalize as well.
+TREE_FINALIZE_CONV = TREE_FINALIZE and os.environ.get("UBR_TREE_FINALIZE_CONV", "0") != "0"
 
 
 def _tree(ws):
@@ -168,7 +173,7 @@ def conv2d_fwd_bn(x, wpk, bias, out_ch, ksize, stride, gamma, beta, running_mean
     lib = _lib.load()
     if y is None:
         y = Act.empty(x.n, x.h // stride, x.w // stride, out_ch, x.buf.device)
-    tree = _tree(ws)
+    tree = _tree(ws) if TREE_FINALIZE_CONV else 0
     if tree:
         st = state or BNState(y.c, y.buf.device)
         st.count = float(y.npix)
@@ -214,7 +219,7 @@ def conv2d_dgrad_bn_bwd(dy, wpk, in_ch, ksize, stride, y_pre, st, relu, ws, dgam
     import ctypes
     lib = _lib.load()
     da = Act.empty(dy.n, dy.h * stride, dy.w * stride, in_ch, dy.buf.device)
-    tree = _tree(ws)
+    tree = _tree(ws) if TREE_FINALIZE_CONV else 0
     if tree:
         rc = lib.ubr_conv2d_dgrad_bnreduce_final(dy.view(), wpk.data_ptr(), in_ch, ksize, stride, da.view(), y_pre.view(),
                                                  st.scale.data_ptr(), st.shift.data_ptr(), st.mean.data_ptr(),
