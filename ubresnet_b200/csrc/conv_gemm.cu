@@ -28,6 +28,8 @@ struct ConvGemmParams {
   CUtensorMap b_map;
   CUtensorMap o_map[4];         // one store map per output phase (blockIdx.z): parity-phase launches are merged
   int nphase, tap_begin[5];     // phase z owns taps [tap_begin[z], tap_begin[z+1]) (nphase == 1: all ntaps)
+  int zin;                      // 1: ONE CTA walks all nphase phases of its tile (own TMEM accumulator per phase, the
+                                // operand tile stays in L2, set-up paid once); 0: one CTA per phase (blockIdx.z)
   int ntaps, nkc, kc, nt, stages;
   int mt, ntiles;               // pixel sub-tiles per CTA (1 or 2, sharing every weight stage) / total 128-pixel tiles
   int tiles_w, tiles_h, bw, bh, bn;
@@ -82,6 +84,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_gemm_kernel(const __grid_con
     n0s[s] = (tile / (p.tiles_w * p.tiles_h)) * p.bn;
   }
   const int co0 = blockIdx.y * p.nt;
+  const int z_lo_early = p.zin ? 0 : (int)blockIdx.z;
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < p.stages; ++s) {
@@ -92,7 +95,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_gemm_kernel(const __grid_con
     fence_mbar_init();
     prefetch_tmap(&p.a_map[0]);
     prefetch_tmap(&p.b_map);
-    if (p.out_mode == 0) prefetch_tmap(&p.o_map[blockIdx.z]);
+    if (p.out_mode == 0) prefetch_tmap(&p.o_map[z_lo_early]);
   }
   if (warp == 1) {
     tmem_alloc_dyn(tmem_slot, p.tmem_cols);
@@ -105,8 +108,8 @@ __global__ void __launch_bounds__(kThreads, 1) conv_gemm_kernel(const __grid_con
   asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
   pdl_wait();                    // barriers, TMEM and tensor maps are set up; the operands belong to earlier kernels
 
-  const int tap_lo = p.tap_begin[blockIdx.z], tap_hi = p.tap_begin[blockIdx.z + 1];
-  const int total_iters = (tap_hi - tap_lo) * p.nkc;
+  const int z_lo = p.zin ? 0 : (int)blockIdx.z, z_hi = p.zin ? p.nphase : (int)blockIdx.z + 1;
+  const int tap_lo = p.tap_begin[z_lo], tap_hi = p.tap_begin[z_hi];
 
   if (warp == 0) {
     if (lane == 0) {
@@ -135,24 +138,29 @@ __global__ void __launch_bounds__(kThreads, 1) conv_gemm_kernel(const __grid_con
       const uint32_t layout = swizzle_layout_code((int)row_bytes);
       const uint32_t sbo = 8u * row_bytes;
       const int ksteps = p.kc / 16;
-      for (int it = 0; it < total_iters; ++it) {
-        const int s = it % p.stages;
-        const uint32_t ph = (uint32_t)(it / p.stages) & 1u;
-        mbar_wait(full0 + 8u * s, ph);
-        tc_fence_after();
-        const uint32_t a_src = smem_base + (uint32_t)s * stage_bytes;
-        const uint32_t b_src = a_src + (uint32_t)p.mt * p.a_stride;
-        const uint64_t bdesc = make_smem_desc(b_src, 0, sbo, layout);
-        for (int u = 0; u < nsub; ++u) {
-          // every pixel sub-tile multiplies the SAME weight stage (halves the weight bytes pulled through L2 per FLOP)
-          const uint64_t adesc = make_smem_desc(a_src + (uint32_t)u * p.a_stride, 0, sbo, layout);
-          for (int k = 0; k < ksteps; ++k) {
-            // advance 16 bf16 = 32 bytes along K inside the swizzle row: +2 in the (addr>>4) field
-            tc_mma_bf16(tmem_base + (uint32_t)(u * p.nt), adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), p.idesc,
-                        (it > 0 || k > 0) ? 1u : 0u);
+      int it = 0;
+      for (int z = z_lo; z < z_hi; ++z) {
+        const uint32_t acc_z = (uint32_t)((z - z_lo) * p.mt * p.nt);      // this phase's accumulator columns
+        const int iters_z = (p.tap_begin[z + 1] - p.tap_begin[z]) * p.nkc;
+        for (int iz = 0; iz < iters_z; ++iz, ++it) {
+          const int s = it % p.stages;
+          const uint32_t ph = (uint32_t)(it / p.stages) & 1u;
+          mbar_wait(full0 + 8u * s, ph);
+          tc_fence_after();
+          const uint32_t a_src = smem_base + (uint32_t)s * stage_bytes;
+          const uint32_t b_src = a_src + (uint32_t)p.mt * p.a_stride;
+          const uint64_t bdesc = make_smem_desc(b_src, 0, sbo, layout);
+          for (int u = 0; u < nsub; ++u) {
+            // every pixel sub-tile multiplies the SAME weight stage (halves the weight bytes pulled through L2 per FLOP)
+            const uint64_t adesc = make_smem_desc(a_src + (uint32_t)u * p.a_stride, 0, sbo, layout);
+            for (int k = 0; k < ksteps; ++k) {
+              // advance 16 bf16 = 32 bytes along K inside the swizzle row: +2 in the (addr>>4) field
+              tc_mma_bf16(tmem_base + acc_z + (uint32_t)(u * p.nt), adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k),
+                          p.idesc, (iz > 0 || k > 0) ? 1u : 0u);
+            }
           }
+          tc_commit(empty0 + 8u * s);          // frees the smem stage when these MMAs retire
         }
-        tc_commit(empty0 + 8u * s);          // frees the smem stage when these MMAs retire
       }
       tc_commit(accum_bar);                  // accumulator complete
     }
@@ -162,9 +170,15 @@ __global__ void __launch_bounds__(kThreads, 1) conv_gemm_kernel(const __grid_con
     const int row = quad * 32 + lane;        // tile-local pixel
     mbar_wait(accum_bar, 0);
     tc_fence_after();
+    for (int z = z_lo; z < z_hi; ++z) {
+    if (z > z_lo) {
+      // the staging tiles are reused by the next phase: its TMA stores must have read them first
+      if (warp == 2 && lane == 0) tma_store_wait_read();
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+    }
     for (int u = 0; u < nsub; ++u) {
     const int w0 = w0s[u], h0 = h0s[u], n0 = n0s[u];
-    const uint32_t t_row = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(u * p.nt);
+    const uint32_t t_row = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(((z - z_lo) * p.mt + u) * p.nt);
     const uint32_t stage_base = smem_base + (uint32_t)u * 128u * (uint32_t)p.nt * 2u;   // own staging per sub-tile
     if (p.out_mode == 0) {
       const int bc = p.o_box_c;                         // channels per staging block
@@ -232,9 +246,9 @@ __global__ void __launch_bounds__(kThreads, 1) conv_gemm_kernel(const __grid_con
       if (warp == 2 && lane == 0) {
         const int nblk = p.nt / bc;
         for (int b = 0; b < nblk; ++b)
-          tma_store_4d(&p.o_map[blockIdx.z], stage_base + (uint32_t)b * 128u * rb, co0 + b * bc, w0, h0, n0);
+          tma_store_4d(&p.o_map[z], stage_base + (uint32_t)b * 128u * rb, co0 + b * bc, w0, h0, n0);
         tma_store_commit();
-        if (u == nsub - 1) tma_store_wait_all();
+        if (u == nsub - 1 && z == z_hi - 1) tma_store_wait_all();
       }
     } else {
       // fp32 direct store (network logits): few valid columns, pixel-major rows
@@ -256,6 +270,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_gemm_kernel(const __grid_con
       }
     }
     }   // sub-tiles
+    }   // phases
   }
 
   tc_fence_before();
@@ -347,6 +362,16 @@ static int launch_conv_gemm(ConvGemmParams& p, int grid_n, int grid_h, int grid_
   p.mt = 1;
   if (p.out_mode == 0 && (tiles_total / 2) * (n_pad / p.nt) >= sms) p.mt = 2;
   if (force_mt == 1 || force_mt == 2) p.mt = force_mt;
+  // parity-phase launches (stride-2 data gradients, ConvTranspose forwards: 1-4 taps per phase): one CTA walks all
+  // phases of its tile -- barrier / TMEM / tensor-map set-up paid once per 9-16 taps instead of once per 1-4 -- when the
+  // accumulators of all phases fit beside a second CTA (<= 256 TMEM columns, i.e. N tiles of <= 32 channels) and a full
+  // wave of CTAs remains.  Measured (batch 32): enc_layer2.res1 data gradients (64 -> 32 channels, 128^2 -> 256^2) 0.177
+  // -> 0.120 ms; with 64-channel N tiles the single pixel sub-tile and the serial four-phase epilogue lose more than
+  // the set-up saves (0.065 -> 0.076 ms, ConvTranspose 128 -> 64: 0.085 -> 0.106 ms), so those keep one CTA per phase.
+  p.zin = 0;
+  static const int zin_on = env_int("UBR_GEMM_ZIN", 1);
+  if (p.nphase > 1 && zin_on && p.nphase * p.mt * p.nt <= 256 && ceil_div(tiles_total, p.mt) * (n_pad / p.nt) >= sms)
+    p.zin = 1;
   p.ntiles = tiles_total;
   p.ntaps = ntaps;
   if (p.nphase <= 1) { p.nphase = 1; p.tap_begin[0] = 0; p.tap_begin[1] = ntaps; }
@@ -371,7 +396,7 @@ static int launch_conv_gemm(ConvGemmParams& p, int grid_n, int grid_h, int grid_
   p.stages = stages;
   p.idesc = make_idesc_bf16(128, p.nt, 0, 0);
   uint32_t cols = 32;
-  while ((int)cols < p.mt * p.nt) cols <<= 1;
+  while ((int)cols < (p.zin ? p.nphase : 1) * p.mt * p.nt) cols <<= 1;
   p.tmem_cols = cols;
   // weights: (K, N, slab) 3-D map, box {kc, nt, 1}
   {
@@ -392,7 +417,7 @@ static int launch_conv_gemm(ConvGemmParams& p, int grid_n, int grid_h, int grid_
     UBR_CUDA_OK(cudaFuncSetAttribute(conv_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     attr_set[dev_id & 63] = true;
   }
-  dim3 grid((unsigned)ceil_div(p.tiles_w * p.tiles_h * tiles_n, p.mt), (unsigned)(n_pad / p.nt), (unsigned)p.nphase);
+  dim3 grid((unsigned)ceil_div(p.tiles_w * p.tiles_h * tiles_n, p.mt), (unsigned)(n_pad / p.nt), (unsigned)(p.zin ? 1 : p.nphase));
   ::ubr::Launch(grid, kThreads, smem, stream)(conv_gemm_kernel, p);
   UBR_LAUNCH_CHECK("conv_gemm_kernel");
   return 0;
