@@ -566,10 +566,23 @@ class Engine:
             hh, ww = (h, w) if i == 1 else (h // 2 ** (i - 1), w // 2 ** (i - 1))
             cat[i] = torch.empty((n, hh, ww, 2 * cd), dtype=torch.bfloat16, device=dev)
         # ---- stem (ub_uresnet.py:94-97)
+        ev0 = None
+        if BRANCH_MAX_RES > 0 and self._bn_ws_b is not None and os.environ.get("UBR_PACK_BRANCH", "1") != "0":
+            ev0 = torch.cuda.Event()
+            ev0.record()
         y0, st0, x0, h0, pool_idx = self._stem_fwd(x, Act(cat[1], p, p), training, need_grad, bn_ws)
         # the stem reads the fp32 conv1 parameter directly: the (host-side) bookkeeping of the bf16 operand refresh
-        # runs while its kernels are already executing
-        self._refresh_packs(need_grad)
+        # runs while its kernels are already executing -- and the re-pack launch itself goes to the branch stream, ordered
+        # after everything BEFORE the stem (the optimizer step), so that it overlaps the stem's HBM-bound kernels
+        if ev0 is not None:
+            if self._bstream is None:
+                self._bstream = torch.cuda.Stream(device=dev)
+            self._bstream.wait_event(ev0)
+            with torch.cuda.stream(self._bstream):
+                self._refresh_packs(need_grad)
+            self._branch_join()
+        else:
+            self._refresh_packs(need_grad)
         # ---- encoder (:103-107)
         recs = {}
         cur = h0
