@@ -189,7 +189,8 @@ int ubr_bn_finalize_rows(const void* workspace, int rows, int c, double count, c
                          float* scale, float* shift, float* mean, float* invstd, void* stream);
 /* ubr_bn_stats + ubr_bn_finalize in ONE launch (nn.BatchNorm2d in training mode, common_layers.py:24,27,35): the last
  * CTAs to arrive reduce the partial rows in a fixed order (`tree`: ubr_bn_tree_bytes(c) bytes, zero-filled once after
- * allocation, see ubr_conv2d_fwd_bn) */
+ * allocation, see ubr_conv2d_fwd_bn).  The *_final reduce entry points return 1 (nothing launched) for channel counts whose
+ * totals do not fit the tail's shared memory (c > 1024 / 2048): run the two-launch form instead. */
 uint64_t ubr_bn_tree_bytes(int c);
 int ubr_bn_stats_final(ubr_view y, void* workspace, void* tree, const float* gamma, const float* beta, float* running_mean,
                        float* running_var, float momentum, float eps, float* scale, float* shift, float* mean,

@@ -737,6 +737,10 @@ def _with_conv_tails(fn):
 
 # the same statistics checks with the reduction finished inside the conv launch (ubr_conv2d_fwd_bn, tree_reduce.cuh)
 CHECKS.update({
+    # channel counts beyond the in-launch tail's shared memory (c = 2048: the *_final entry points answer 1 and the
+    # two-launch form runs) and at its edge (c = 1024), many partial rows (two ticket levels)
+    "pointwise_wide": lambda: (check_bn(2048, 2, 4, 4, seed=21) + check_bn(1024, 2, 8, 8, seed=22) + check_bn(16, 4, 128, 128, seed=23)
+                               + check_block_tail(1024, 2, 4, 4, True, seed=24) + check_block_tail(2048, 1, 4, 4, False, seed=25)),
     "halo_fwd_bn_tail": _with_conv_tails(CHECKS["halo_fwd_bn"]),
     "gemm_fwd_bn_tail": _with_conv_tails(CHECKS["gemm_fwd_bn"]),
 })

@@ -960,7 +960,7 @@ int ubr_bn_stats_final(ubr_view y, void* workspace, void* tree, const float* gam
   if (int rc = ensure_device()) return rc;
   if (int rc = chk_red(y, "bn_stats_final.y")) return rc;
   UBR_REQUIRE(workspace && tree && scale && shift, "bn_stats_final: null pointer");
-  UBR_REQUIRE(red_smem(2, y.c, true) <= 48 * 1024, "bn_stats_final: c=%d too wide for the in-launch finalize", y.c);
+  if (red_smem(2, y.c, true) > 48 * 1024) return 1;      // too wide for the in-launch tail: ubr_bn_stats + ubr_bn_finalize
   DView v = dv(y);
   const int nb = red_blocks(v.npix, v.c);
   BnFinal f{gamma, beta, running_mean, running_var, momentum, eps, (double)v.npix, scale, shift, mean, invstd, v.c, v.c};
@@ -1060,7 +1060,7 @@ int ubr_bn_act_bwd_reduce_final(ubr_view dout, ubr_view y, const float* scale, c
   if (int rc = chk(dout, "bn_act_bwd_reduce_final.dout")) return rc;
   if (int rc = same_shape(y, dout, "bn_act_bwd_reduce_final")) return rc;
   UBR_REQUIRE(scale && shift && mean && invstd && workspace && tree, "bn_act_bwd_reduce_final: null pointer");
-  UBR_REQUIRE(red_smem(2, y.c, true) <= 48 * 1024, "bn_act_bwd_reduce_final: c=%d too wide for the in-launch finalize", y.c);
+  if (red_smem(2, y.c, true) > 48 * 1024) return 1;      // too wide: ubr_bn_act_bwd_reduce + ubr_bn_act_bwd_apply
   DView v = dv(y);
   const int nb = red_blocks(v.npix, v.c, kBwdRedBlocks);
   float* sums = (float*)workspace + (size_t)kRedBlocks * 4 * v.c;
@@ -1184,7 +1184,7 @@ int ubr_block_tail_bwd_reduce_final(ubr_view dout, ubr_view out, ubr_view y2, co
   }
   if (int rc = same_shape(y2, dout, "block_tail_bwd_reduce_final(dout)")) return rc;
   UBR_REQUIRE(s2 && b2 && mean2 && invstd2 && workspace && tree, "block_tail_bwd_reduce_final: null pointer");
-  UBR_REQUIRE(red_smem(4, y2.c, true) <= 48 * 1024, "block_tail_bwd_reduce_final: c=%d too wide for the in-launch finalize", y2.c);
+  if (red_smem(4, y2.c, true) > 48 * 1024) return 1;     // too wide: ubr_block_tail_bwd_reduce + ubr_block_tail_bwd_apply
   DView v = dv(y2);
   const int nb = red_blocks(v.npix, v.c, kBwdRedBlocks);
   const int ns = res_is_bn ? 4 : 2;

@@ -434,11 +434,13 @@ def bn_train_stats(y, gamma, beta, running_mean, running_var, ws, state=None, mo
     st.count = float(y.npix)
     tree = _tree(ws)
     if tree:
-        _lib.check(lib.ubr_bn_stats_final(y.view(), ws.data_ptr(), tree, _ptr(gamma), _ptr(beta), _ptr(running_mean),
-                                          _ptr(running_var), momentum, eps, st.scale.data_ptr(), st.shift.data_ptr(),
-                                          st.mean.data_ptr(), st.invstd.data_ptr(), _stream()), "bn_stats_final")
-        _bump(running_mean, running_var)
-        return st
+        rc = lib.ubr_bn_stats_final(y.view(), ws.data_ptr(), tree, _ptr(gamma), _ptr(beta), _ptr(running_mean),
+                                    _ptr(running_var), momentum, eps, st.scale.data_ptr(), st.shift.data_ptr(),
+                                    st.mean.data_ptr(), st.invstd.data_ptr(), _stream())
+        if rc != 1:                                        # 1: too many channels for the in-launch tail
+            _lib.check(rc, "bn_stats_final")
+            _bump(running_mean, running_var)
+            return st
     _lib.check(lib.ubr_bn_stats(y.view(), ws.data_ptr(), _stream()), "bn_stats")
     _lib.check(lib.ubr_bn_finalize(ws.data_ptr(), y.c, st.count, _ptr(gamma), _ptr(beta), _ptr(running_mean),
                                    _ptr(running_var), momentum, eps, st.scale.data_ptr(), st.shift.data_ptr(),
@@ -484,13 +486,15 @@ def bn_act_bwd(dout, y, st, relu, ws, dgamma=None, dbeta=None, accumulate=False,
     s = _stream()
     tree = _tree(ws)
     if tree:
-        _lib.check(lib.ubr_bn_act_bwd_reduce_final(dout.view(), y.view(), st.scale.data_ptr(), st.shift.data_ptr(),
-                                                   st.mean.data_ptr(), st.invstd.data_ptr(), int(relu), ws.data_ptr(), tree,
-                                                   _ptr(dgamma), _ptr(dbeta), int(accumulate), s), "bn_act_bwd_reduce_final")
-        _lib.check(lib.ubr_bn_act_bwd_apply_final(dout.view(), y.view(), st.scale.data_ptr(), st.shift.data_ptr(),
-                                                  st.mean.data_ptr(), st.invstd.data_ptr(), int(relu), ws.data_ptr(),
-                                                  st.count, dy.view(), s), "bn_act_bwd_apply_final")
-        return dy
+        rc = lib.ubr_bn_act_bwd_reduce_final(dout.view(), y.view(), st.scale.data_ptr(), st.shift.data_ptr(),
+                                             st.mean.data_ptr(), st.invstd.data_ptr(), int(relu), ws.data_ptr(), tree,
+                                             _ptr(dgamma), _ptr(dbeta), int(accumulate), s)
+        if rc != 1:
+            _lib.check(rc, "bn_act_bwd_reduce_final")
+            _lib.check(lib.ubr_bn_act_bwd_apply_final(dout.view(), y.view(), st.scale.data_ptr(), st.shift.data_ptr(),
+                                                      st.mean.data_ptr(), st.invstd.data_ptr(), int(relu), ws.data_ptr(),
+                                                      st.count, dy.view(), s), "bn_act_bwd_apply_final")
+            return dy
     _lib.check(lib.ubr_bn_act_bwd_reduce(dout.view(), y.view(), st.scale.data_ptr(), st.shift.data_ptr(),
                                          st.mean.data_ptr(), st.invstd.data_ptr(), int(relu), ws.data_ptr(), s),
                "bn_act_bwd_reduce")
@@ -520,16 +524,17 @@ def block_tail_bwd(dout, out, y2, st2, res, st_res, gamma_res, ws, dgamma2=None,
     ov = out.view() if (out is not None and not res_bn) else _NULLVIEW
     tree = _tree(ws)
     if tree:
-        _lib.check(lib.ubr_block_tail_bwd_reduce_final(dout.view(), ov, y2.view(), st2.scale.data_ptr(),
-                                                       st2.shift.data_ptr(), st2.mean.data_ptr(), st2.invstd.data_ptr(),
-                                                       rv, mr, ir, sr, br, int(res_bn), ws.data_ptr(), tree, _ptr(dgamma2),
-                                                       _ptr(dbeta2), _ptr(dgamma_res), _ptr(dbeta_res), int(accumulate), s),
-                   "block_tail_bwd_reduce_final")
-        _lib.check(lib.ubr_block_tail_bwd_apply_final(dout.view(), ov, y2.view(), st2.scale.data_ptr(),
-                                                      st2.shift.data_ptr(), st2.mean.data_ptr(), st2.invstd.data_ptr(), rv,
-                                                      mr, ir, _ptr(gamma_res), sr, br, int(res_bn), ws.data_ptr(), st2.count,
-                                                      dy2.view(), dres.view(), s), "block_tail_bwd_apply_final")
-        return dy2, dres
+        rc = lib.ubr_block_tail_bwd_reduce_final(dout.view(), ov, y2.view(), st2.scale.data_ptr(),
+                                                 st2.shift.data_ptr(), st2.mean.data_ptr(), st2.invstd.data_ptr(),
+                                                 rv, mr, ir, sr, br, int(res_bn), ws.data_ptr(), tree, _ptr(dgamma2),
+                                                 _ptr(dbeta2), _ptr(dgamma_res), _ptr(dbeta_res), int(accumulate), s)
+        if rc != 1:
+            _lib.check(rc, "block_tail_bwd_reduce_final")
+            _lib.check(lib.ubr_block_tail_bwd_apply_final(dout.view(), ov, y2.view(), st2.scale.data_ptr(),
+                                                          st2.shift.data_ptr(), st2.mean.data_ptr(), st2.invstd.data_ptr(), rv,
+                                                          mr, ir, _ptr(gamma_res), sr, br, int(res_bn), ws.data_ptr(),
+                                                          st2.count, dy2.view(), dres.view(), s), "block_tail_bwd_apply_final")
+            return dy2, dres
     _lib.check(lib.ubr_block_tail_bwd_reduce(dout.view(), ov, y2.view(), st2.scale.data_ptr(),
                                              st2.shift.data_ptr(), st2.mean.data_ptr(), st2.invstd.data_ptr(), rv, mr,
                                              ir, sr, br, int(res_bn), ws.data_ptr(), s), "block_tail_bwd_reduce")
