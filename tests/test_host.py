@@ -124,3 +124,27 @@ def test_default_ctor_three_input_channels_selects_fp32():
     with pytest.raises(ValueError):
         UResNet(3, 3, 16, precision="bf16")
     assert UResNet(3, 1, 16).precision == "bf16"
+
+
+def test_bench_per_launch_roofline_split():
+    """bench.conv_bound_split: a launch is tensor bound when FLOPs / peak >= bytes / peak (arithmetic intensity above the
+    ridge); fractions are achieved / peak per class, FLOP-weighted for the tensor class"""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("bench_mod", os.path.join(ROOT, "bench.py"))
+    bench = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(bench)
+    peaks = dict(hbm_gbs=6500.0, tf_sustained=1300.0, tf_burst=1600.0, source="test")
+    x16 = (32, 512, 512, 16)
+    # 3x3 16->16 at 512^2: 72 FLOP/B (HBM bound); 7x7 16->16: 392 FLOP/B (tensor bound); ridge = 200
+    calls = [("ubr_conv2d_fwd_bn", (x16, 0, 0, 16, 3, 1, x16), 0.10), ("ubr_conv2d_fwd", (x16, 0, 0, 16, 7, 1, x16), 0.20)]
+    out = bench.conv_bound_split({"conv_halo_kernel": calls, "bn_act_kernel": [("ubr_bn_act", (x16,), 1.0)]}, 1, peaks)
+    assert abs(out["ridge_flop_per_byte"] - 200.0) < 1e-9
+    assert out["hbm_bound"]["launches_per_step"] == 1 and out["tensor_bound"]["launches_per_step"] == 1
+    npx = 32 * 512 * 512
+    gbs = 2.0 * npx * 32 / 0.10e-3 / 1e9
+    tfl = 2.0 * npx * 16 * 16 * 49 / 0.20e-3 / 1e12
+    assert abs(out["hbm_bound"]["achieved_gbs"] - gbs) < 1e-6 * gbs
+    assert abs(out["tensor_bound"]["achieved_tflops"] - tfl) < 1e-6 * tfl
+    assert abs(out["tensor_bound"]["frac_flop_weighted"] - tfl / 1300.0) < 1e-9       # one launch: weighted == plain
+    roof_ms = 2.0 * npx * 32 / 6500e9 * 1e3 + 2.0 * npx * 16 * 16 * 49 / 1300e12 * 1e3
+    assert abs(out["mixed_frac"] - roof_ms / 0.30) < 1e-9
