@@ -253,6 +253,7 @@ __global__ void __launch_bounds__(kHThreads, 2) conv_halo_kernel(const __grid_co
     const uint32_t sbase = stage_base + (uint32_t)grp * p.stage_bytes;
     const int bar_id = 1 + grp;
     float st_sum0 = 0.f, st_sq0 = 0.f, st_sum1 = 0.f, st_sq1 = 0.f;   // fused BN statistics: this lane's channel, per 16-channel chunk
+    float st_sum2 = 0.f, st_sq2 = 0.f, st_sum3 = 0.f, st_sq3 = 0.f;   // chunks 2, 3: the 64-channel tiles of the TMA-store path
     uint32_t r0 = 0;                           // global output-row counter at the start of the tile
     for (int tile = blockIdx.x; tile < p.ntiles; tile += gridDim.x, r0 += (uint32_t)p.bh) {
       const int band = tile % p.bands;
@@ -405,6 +406,22 @@ __global__ void __launch_bounds__(kHThreads, 2) conv_halo_kernel(const __grid_co
             uint32_t pk[8];
 #pragma unroll
             for (int j = 0; j < 8; ++j) pk[j] = pack_bf16x2(f[2 * j], f[2 * j + 1]);
+            if (p.stats) {
+              // statistics of the STORED (bf16-rounded) values (TMA-store path: no BatchNorm-backward variant here)
+              float g[16], q2[16];
+#pragma unroll
+              for (int j = 0; j < 8; ++j) {
+                const float2 t = unpack_bf16x2(pk[j]);
+                g[2 * j] = t.x; g[2 * j + 1] = t.y;
+                q2[2 * j] = t.x * t.x; q2[2 * j + 1] = t.y * t.y;
+              }
+              const float rs = warp_reduce_scatter16(g, lane), rq = warp_reduce_scatter16(q2, lane);
+              const int ci = c >> 4;
+              if (ci == 0) { st_sum0 += rs; st_sq0 += rq; }
+              else if (ci == 1) { st_sum1 += rs; st_sq1 += rq; }
+              else if (ci == 2) { st_sum2 += rs; st_sq2 += rq; }
+              else { st_sum3 += rs; st_sq3 += rq; }
+            }
             const int blk = c / bc;
             const uint32_t q = (uint32_t)((c % bc) >> 3);
             const uint32_t base = sbase + (uint32_t)blk * 128u * rb + (uint32_t)row * rb;
@@ -456,6 +473,29 @@ __global__ void __launch_bounds__(kHThreads, 2) conv_halo_kernel(const __grid_co
       }
     }
     if (p.out_mode == 0 && leader) tma_store_wait_all();
+    if (p.out_mode == 0 && p.stats) {
+      // same fixed-order combine as below, for up to four 16-channel chunks; the scratch is the first staging tile, idle
+      // once every TMA store of the CTA has completed
+      asm volatile("bar.sync 3, 256;" ::: "memory");
+      float* scr8 = reinterpret_cast<float*>(smem_raw + (stage_base - smem_u32(smem_raw)));        // [8 warps][32 lanes][8]
+      const int we = warp - 2;
+      float* mine = scr8 + (we * 32 + lane) * 8;
+      mine[0] = st_sum0; mine[1] = st_sq0; mine[2] = st_sum1; mine[3] = st_sq1;
+      mine[4] = st_sum2; mine[5] = st_sq2; mine[6] = st_sum3; mine[7] = st_sq3;
+      asm volatile("bar.sync 3, 256;" ::: "memory");
+      if (we == 0 && (lane & 1) == 0) {
+        const int ch = (lane >> 1) & 15;
+        float tot[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+        for (int k = 0; k < 8; ++k)
+#pragma unroll
+          for (int j = 0; j < 8; ++j) tot[j] += scr8[(k * 32 + lane) * 8 + j];
+        float* rowp = p.stats + (size_t)blockIdx.x * 2 * p.stats_c;
+        for (int cc = 0; cc < p.nt; cc += 16) {
+          rowp[co0 + cc + ch] = tot[(cc >> 4) * 2];
+          rowp[p.stats_c + co0 + cc + ch] = tot[(cc >> 4) * 2 + 1];
+        }
+      }
+    }
     if (p.out_mode == 2 && p.stats) {
       // combine the 8 epilogue warps in a fixed order (deterministic) and publish this CTA's partial row
       float* scr = reinterpret_cast<float*>(smem_raw + (tmem_slot + 16u - smem_u32(smem_raw)));   // [8 warps][32 lanes][4]
@@ -585,7 +625,10 @@ int conv_halo_try(const ubr_view& x, const void* wpk, int nslabs, int n_pad, con
   }
   if (nt == 0) return 1;
   if (accumulate && out_mode != 2 && out_mode != 0) return 1;  // in-epilogue accumulation: bf16 outputs only
-  if (stats && out_mode != 2) return 1;                      // fused BN statistics: direct-store path only
+  // fused BN statistics: the direct-store epilogue, and (forward statistics only) the TMA-store epilogue of the 64-channel
+  // tiles (UBR_HALO_STATS_M0=0 leaves those to the stand-alone bn_stats pass)
+  static const bool stats_m0 = [] { const char* e = getenv("UBR_HALO_STATS_M0"); return !(e && e[0] == '0'); }();
+  if (stats && out_mode != 2 && !(stats_m0 && out_mode == 0 && !bnr && !accumulate && !epi && nt <= 64)) return 1;
   if (bnr && (!stats || out_mode != 2 || nt > 32 || accumulate)) return 1;
 
   HaloParams p;
