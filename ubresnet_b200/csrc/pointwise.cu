@@ -612,17 +612,18 @@ __global__ void __launch_bounds__(256) maxpool_fwd_kernel(const __nv_bfloat16* x
 }
 
 // forward that also records the argmax tap (kh*3+kw of the FIRST maximum in scan order, as ATen) per element
+template <typename I>                  // I: index type of the flat element loop (see maxpool_bwd_idx_kernel)
 __global__ void __launch_bounds__(256) maxpool_fwd_idx_kernel(const __nv_bfloat16* x, int xld, int n, int h, int w, int c,
                                                               __nv_bfloat16* y, int yld, uint8_t* __restrict__ idx) {
   pdl_prologue();
   const int cgs = c >> 3, ho = h / 2, wo = w / 2;
-  const long total = (long)n * ho * wo * cgs;
-  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
-    const int cg = (int)(i % cgs);
-    long p = i / cgs;
-    const int ow = (int)(p % wo); p /= wo;
-    const int oh = (int)(p % ho);
-    const int b = (int)(p / ho);
+  const I total = (I)n * (I)ho * (I)wo * (I)cgs;
+  for (I i = (I)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (I)gridDim.x * blockDim.x) {
+    const int cg = (int)(i % (I)cgs);
+    I p = i / (I)cgs;
+    const int ow = (int)(p % (I)wo); p /= (I)wo;
+    const int oh = (int)(p % (I)ho);
+    const int b = (int)(p / (I)ho);
     float m[8];
     uint32_t arg[8];
 #pragma unroll
@@ -644,23 +645,26 @@ __global__ void __launch_bounds__(256) maxpool_fwd_idx_kernel(const __nv_bfloat1
     uint2 u;
     u.x = arg[0] | (arg[1] << 8) | (arg[2] << 16) | (arg[3] << 24);
     u.y = arg[4] | (arg[5] << 8) | (arg[6] << 16) | (arg[7] << 24);
-    *reinterpret_cast<uint2*>(idx + i * 8) = u;          // idx layout [n][ho][wo][c], c contiguous
+    *reinterpret_cast<uint2*>(idx + (size_t)i * 8) = u;  // idx layout [n][ho][wo][c], c contiguous
   }
 }
 
 // backward from the recorded argmax: each input pixel gathers from the <= 4 windows covering it (no atomics)
+// I: index type of the flat element loop (unsigned 32-bit where the tensor allows it: the three div/mod pairs per element
+// are a third of the cost of their 64-bit forms)
+template <typename I>
 __global__ void __launch_bounds__(256) maxpool_bwd_idx_kernel(const uint8_t* __restrict__ idx, int n, int h, int w, int c,
                                                               const __nv_bfloat16* dy, int dyld, __nv_bfloat16* dx,
                                                               int dxld, int accumulate) {
   pdl_prologue();
   const int cgs = c >> 3, ho = h / 2, wo = w / 2;
-  const long total = (long)n * h * w * cgs;
-  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
-    const int cg = (int)(i % cgs);
-    long p = i / cgs;
-    const int iw = (int)(p % w); p /= w;
-    const int ih = (int)(p % h);
-    const int b = (int)(p / h);
+  const I total = (I)n * (I)h * (I)w * (I)cgs;
+  for (I i = (I)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (I)gridDim.x * blockDim.x) {
+    const int cg = (int)(i % (I)cgs);
+    I p = i / (I)cgs;
+    const int iw = (int)(p % (I)w); p /= (I)w;
+    const int ih = (int)(p % (I)h);
+    const int b = (int)(p / (I)h);
     // the <= 4 covering windows: every index load is issued before any of them is inspected, then the dy loads of
     // the windows that hit -- independent loads instead of a load -> test -> load chain per window
     const int oh_lo = ih / 2, ow_lo = iw / 2;
@@ -1369,8 +1373,12 @@ int ubr_maxpool3s2_fwd_idx(ubr_view x, ubr_view y, uint8_t* idx, void* stream) {
   UBR_REQUIRE(x.h % 2 == 0 && x.w % 2 == 0 && y.n == x.n && y.h == x.h / 2 && y.w == x.w / 2 && y.c == x.c,
               "maxpool_fwd_idx: shape mismatch");
   const long total = (long)y.n * y.h * y.w * (x.c >> 3);
-  ::ubr::Launch(ew_blocks(total), 256, 0, (cudaStream_t)stream)(maxpool_fwd_idx_kernel, (const __nv_bfloat16*)x.ptr, x.ld, x.n, x.h, x.w,
-                                                                             x.c, (__nv_bfloat16*)y.ptr, y.ld, idx);
+  if (total < (1L << 31) - (1L << 26))
+    ::ubr::Launch(ew_blocks(total), 256, 0, (cudaStream_t)stream)(maxpool_fwd_idx_kernel<unsigned>, (const __nv_bfloat16*)x.ptr, x.ld, x.n, x.h,
+                                                                               x.w, x.c, (__nv_bfloat16*)y.ptr, y.ld, idx);
+  else
+    ::ubr::Launch(ew_blocks(total), 256, 0, (cudaStream_t)stream)(maxpool_fwd_idx_kernel<long>, (const __nv_bfloat16*)x.ptr, x.ld, x.n, x.h,
+                                                                               x.w, x.c, (__nv_bfloat16*)y.ptr, y.ld, idx);
   UBR_LAUNCH_CHECK("maxpool_fwd_idx_kernel");
   return 0;
 }
@@ -1383,10 +1391,17 @@ int ubr_maxpool3s2_bwd_idx(const uint8_t* idx, ubr_view dy, ubr_view dx_accum, i
   UBR_REQUIRE(dx_accum.n == dy.n && dx_accum.h == 2 * dy.h && dx_accum.w == 2 * dy.w && dx_accum.c == dy.c,
               "maxpool_bwd_idx: shape mismatch");
   const long total = (long)dx_accum.n * dx_accum.h * dx_accum.w * (dy.c >> 3);
-  ::ubr::Launch(ew_blocks(total), 256, 0, (cudaStream_t)stream)(maxpool_bwd_idx_kernel, idx, dx_accum.n, dx_accum.h, dx_accum.w, dy.c,
-                                                                             (const __nv_bfloat16*)dy.ptr, dy.ld,
-                                                                             (__nv_bfloat16*)dx_accum.ptr, dx_accum.ld,
-                                                                             accumulate);
+  // grid-stride loop: i + gridDim * blockDim must not wrap either
+  if (total < (1L << 31) - (1L << 26))
+    ::ubr::Launch(ew_blocks(total), 256, 0, (cudaStream_t)stream)(maxpool_bwd_idx_kernel<unsigned>, idx, dx_accum.n, dx_accum.h, dx_accum.w, dy.c,
+                                                                               (const __nv_bfloat16*)dy.ptr, dy.ld,
+                                                                               (__nv_bfloat16*)dx_accum.ptr, dx_accum.ld,
+                                                                               accumulate);
+  else
+    ::ubr::Launch(ew_blocks(total), 256, 0, (cudaStream_t)stream)(maxpool_bwd_idx_kernel<long>, idx, dx_accum.n, dx_accum.h, dx_accum.w, dy.c,
+                                                                               (const __nv_bfloat16*)dy.ptr, dy.ld,
+                                                                               (__nv_bfloat16*)dx_accum.ptr, dx_accum.ld,
+                                                                               accumulate);
   UBR_LAUNCH_CHECK("maxpool_bwd_idx_kernel");
   return 0;
 }
