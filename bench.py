@@ -453,7 +453,7 @@ def run_own(args, rank, world, local_rank):
 
     # e2e: every step's batch is copied host -> device from pinned memory inside the timed region; the copy of batch
     # i+1 runs on the prefetcher's side stream while step i computes (ubresnet_b200/prefetch.py)
-    from ubresnet_b200.prefetch import DevicePrefetcher
+    from ubresnet_b200.prefetch import AssembledPrefetcher, DevicePrefetcher
 
     def host_batches():
         i = 0
@@ -476,9 +476,8 @@ def run_own(args, rank, world, local_rank):
 
     def step_e2e(i):
         if "it" not in feed:
-            feed["it"] = DevicePrefetcher(wire_batches(), dev)
-        planes, rois = next(feed["it"])
-        img, lab, wgt = filler.fill(planes, rois, S, S)
+            feed["it"] = AssembledPrefetcher(wire_batches(), filler, S, S, B, dev)
+        img, lab, wgt = next(feed["it"])                              # copied + assembled one step ahead
         opt.zero_grad(set_to_none=True)
         loss = crit(net(img), lab, wgt)
         loss.backward()
@@ -541,10 +540,9 @@ def run_own(args, rank, world, local_rank):
 
     def step_e2e_graphed(i):
         if "it" not in feed:
-            feed["it"] = DevicePrefetcher(wire_batches(), dev)
-        planes, rois = next(feed["it"])
-        filler.fill(planes, rois, S, S, out=graphed.inputs)          # assembled straight into the graph's static inputs
-        loss = graphed.replay()
+            feed["it"] = AssembledPrefetcher(wire_batches(), filler, S, S, B, dev)
+        img, lab, wgt = next(feed["it"])                              # copied + assembled one step ahead
+        loss = graphed(img, lab, wgt)                                 # 3 device copies into the graph's static inputs + replay
         j = i & 1
         loss_host[j].copy_(loss, non_blocking=True)                   # device -> host read of the step's result
         loss_ready[j] = torch.cuda.Event()
@@ -765,9 +763,10 @@ def run_own(args, rank, world, local_rank):
             "clocks": clocks,
             "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": h2d_bytes * world, "d2h_bytes_per_step": 4 * world,
                     "ms_per_step": ms_e2e / args.steps,
-                    "input": "pinned host larcv-style planes (column-major fp32 ADC + uint8 ROI-type labels) -> device "
-                             "batch assembly (ubresnet_b200.fill: transpose, ROI->class LUT -1, SegWeightTrackShower "
-                             "weights) -> train step -> loss.item()",
+                    "input": "pinned host larcv-style planes (column-major fp32 ADC + uint8 ROI-type labels) -> H2D copy and "
+                             "device batch assembly (ubresnet_b200.fill: transpose, ROI->class LUT -1, SegWeightTrackShower "
+                             "weights) on the prefetch stream one step ahead (prefetch.AssembledPrefetcher) -> train step "
+                             "-> loss read back",
                     "loss_readback": "every step's loss copied D2H (pinned, non_blocking) and consumed by the host one step "
                                      "later; %d losses read inside the timed loop" % len(losses_seen),
                     "device_fill_equals_host_batch": fill_ok, "device_fill_ms_per_batch": fill_ms,

@@ -100,3 +100,30 @@ def test_seg_weights_options_and_invalid_roi():
     imgs = np.zeros((2, rows * cols), dtype=np.float32)
     with pytest.raises(RuntimeError):
         filler.fill(torch.from_numpy(imgs), torch.from_numpy(bad), rows, cols, check=True)
+
+
+@pytest.mark.gpu
+def test_assembled_prefetcher_yields_the_batches_in_order():
+    """prefetch.AssembledPrefetcher: copy + assembly one step ahead on its own stream into two alternating staging sets.
+    Every yielded (image, label, weight) must equal the synchronous fill of the same host batch, also when the consumer
+    keeps the main stream busy between calls (a staging set may only be refilled after its consumer's work)."""
+    from ubresnet_b200.prefetch import AssembledPrefetcher
+    rows, cols, batch, nb = 64, 128, 2, 5
+    host = []
+    for i in range(nb):
+        imgs, labs = _roi_planes(batch, rows, cols, seed=100 + i)
+        host.append((torch.from_numpy(imgs).pin_memory(), torch.from_numpy(labs).pin_memory()))
+    filler = fill.DeviceBatchFiller("cuda:0")
+    want = [tuple(t.clone() for t in filler.fill(p, r, rows, cols)) for p, r in host]
+    torch.cuda.synchronize()
+    pf = AssembledPrefetcher(iter(host), fill.DeviceBatchFiller("cuda:0"), rows, cols, batch, "cuda:0")
+    busy = torch.zeros(1 << 22, device="cuda:0")
+    got = []
+    for img, lab, wgt in pf:
+        got.append((img.clone(), lab.clone(), wgt.clone()))     # the consumer's work on this set (main stream)
+        for _ in range(20):
+            busy.add_(1.0)                                       # keep the main stream behind the prefetch stream
+    torch.cuda.synchronize()
+    assert len(got) == nb
+    for (a, b, c), (x, y, z) in zip(got, want):
+        assert torch.equal(a, x) and torch.equal(b, y) and torch.equal(c, z)
