@@ -272,11 +272,6 @@ int ubr_add(ubr_view a, ubr_view b, ubr_view c, ubr_view out, void* stream);
 int ubr_logsoftmax_fwd(const float* logits, int ld, int n, int ncls, int hw, float* logp, void* stream);
 /* dlogits (bf16 view, c >= ncls; pad channels zeroed) = dlogp - softmax * sum_k dlogp_k */
 int ubr_logsoftmax_bwd(const float* logp, const float* dlogp, int n, int ncls, int hw, ubr_view dlogits, void* stream);
-/* the same, also writing dbias[0:ncls) = sum over pixels of the stored dlogits, i.e. the bias gradient of conv11
- * (ub_uresnet.py:64,141-143: conv11 has a bias and feeds the log-softmax) -- saves a full pass over dlogits.  ncls <= 4;
- * workspace >= (592 + 1) * 4 floats (a ubr_bn_workspace_bytes buffer will do), tree as for ubr_conv2d_fwd_bn. */
-int ubr_logsoftmax_bwd_bias(const float* logp, const float* dlogp, int n, int ncls, int hw, ubr_view dlogits, void* workspace,
-                            void* tree, float* dbias, int accumulate, void* stream);
 /* loss = mean_{pixels}( pw * cw[t] * -logp[t] ), t == ignore_index contributes 0 (stays in the mean) */
 uint64_t ubr_nll_workspace_bytes(int n, int hw);
 int ubr_pixelwise_nll_fwd(const float* logp, const int64_t* target, const float* pixw, const float* classw,

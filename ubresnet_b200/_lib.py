@@ -85,7 +85,6 @@ SIGNATURES = {
     "ubr_add": (_i, [View, View, View, View, _vp]),
     "ubr_logsoftmax_fwd": (_i, [_vp, _i, _i, _i, _i, _vp, _vp]),
     "ubr_logsoftmax_bwd": (_i, [_vp, _vp, _i, _i, _i, View, _vp]),
-    "ubr_logsoftmax_bwd_bias": (_i, [_vp, _vp, _i, _i, _i, View, _vp, _vp, _vp, _i, _vp]),
     "ubr_nll_workspace_bytes": (_u64, [_i, _i]),
     "ubr_pixelwise_nll_fwd": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i64, _vp, _vp, _vp]),
     "ubr_pixelwise_nll_bwd": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i64, _vp, _vp]),

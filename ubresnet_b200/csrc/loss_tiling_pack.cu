@@ -2,7 +2,6 @@
 // whole-view tile gather / stitch scatter (deploy/run_ubresnet_wholeview.py:238-239; larcv Image2D.cxx:362-367),
 // and weight packing.  All coalesced, fp32 math, deterministic reductions.
 #include "common.cuh"
-#include "tree_reduce.cuh"
 
 namespace ubr {
 
@@ -33,15 +32,11 @@ __global__ void __launch_bounds__(256) logsoftmax_fwd_kernel(const float* __rest
 }
 
 // dlogits[p][k] = dlogp[k] - exp(logp[k]) * sum_j dlogp[j]   (bf16, channels >= ncls zeroed)
-// partials != null: the per-class pixel sums of the STORED (bf16-rounded) gradient -- the bias gradient of the conv that
-// produced the logits -- ride along: one partial row [4] per block, finished by the last blocks to arrive (tree_reduce.cuh)
 __global__ void __launch_bounds__(256) logsoftmax_bwd_kernel(const float* __restrict__ logp,
                                                              const float* __restrict__ dlogp, int n, int ncls, int hw,
-                                                             __nv_bfloat16* __restrict__ dl, int dl_c, int dl_ld,
-                                                             float* __restrict__ partials, TreeRed tr, SumsFinal fin) {
+                                                             __nv_bfloat16* __restrict__ dl, int dl_c, int dl_ld) {
   pdl_prologue();
   const long total = (long)n * hw;
-  float bsum[4] = {0.f, 0.f, 0.f, 0.f};
   for (long p = (long)blockIdx.x * blockDim.x + threadIdx.x; p < total; p += (long)gridDim.x * blockDim.x) {
     const long b = p / hw, i = p % hw;
     float g[kMaxCls], s = 0.f;
@@ -56,28 +51,7 @@ __global__ void __launch_bounds__(256) logsoftmax_bwd_kernel(const float* __rest
       u.x = pack_bf16x2(f[0], f[1]); u.y = pack_bf16x2(f[2], f[3]);
       u.z = pack_bf16x2(f[4], f[5]); u.w = pack_bf16x2(f[6], f[7]);
       *reinterpret_cast<uint4*>(dst + c0) = u;
-      if (partials && c0 == 0) {
-        const float2 a = unpack_bf16x2(u.x), c = unpack_bf16x2(u.y);
-        bsum[0] += a.x; bsum[1] += a.y; bsum[2] += c.x; bsum[3] += c.y;
-      }
     }
-  }
-  if (partials) {
-    extern __shared__ __align__(16) double lsm_smem[];         // block partials, then the tree tail's scratch
-    float* red = reinterpret_cast<float*>(lsm_smem);            // [8 warps][4]
-#pragma unroll
-    for (int k = 0; k < 4; ++k) bsum[k] = warp_sum(bsum[k]);
-    if ((threadIdx.x & 31) == 0) {
-#pragma unroll
-      for (int k = 0; k < 4; ++k) red[(threadIdx.x >> 5) * 4 + k] = bsum[k];
-    }
-    __syncthreads();
-    if (threadIdx.x < 4) {
-      float t = 0.f;
-      for (int w = 0; w < 8; ++w) t += red[w * 4 + threadIdx.x];
-      partials[(size_t)blockIdx.x * 4 + threadIdx.x] = t;
-    }
-    if (tree_arrive(tr, (int)blockIdx.x, 1, 1, lsm_smem)) tree_finish_sums(lsm_smem, fin);
   }
 }
 
@@ -355,28 +329,7 @@ int ubr_logsoftmax_bwd(const float* logp, const float* dlogp, int n, int ncls, i
   UBR_REQUIRE(ncls >= 1 && ncls <= kMaxCls && dlogits.c >= ncls && dlogits.c % 8 == 0 && dlogits.ld % 8 == 0,
               "logsoftmax_bwd: bad dlogits view");
   UBR_REQUIRE((long)dlogits.n * dlogits.h * dlogits.w == (long)n * hw, "logsoftmax_bwd: pixel count mismatch");
-  ::ubr::Launch(blocks_for((long)n * hw), 256, 0, (cudaStream_t)stream)(logsoftmax_bwd_kernel, logp, dlogp, n, ncls, hw, (__nv_bfloat16*)dlogits.ptr, dlogits.c, dlogits.ld,
-                                                                        (float*)nullptr, TreeRed{}, SumsFinal{});
-  UBR_LAUNCH_CHECK("logsoftmax_bwd_kernel");
-  return 0;
-}
-
-// ubr_logsoftmax_bwd that also writes dbias[0:ncls) = per-class sum over pixels of the stored dlogits: the bias gradient
-// of the conv that produced the logits (ncls <= 4).  workspace: >= (592 + 1) * 4 floats; tree: see ubr_conv2d_fwd_bn.
-int ubr_logsoftmax_bwd_bias(const float* logp, const float* dlogp, int n, int ncls, int hw, ubr_view dlogits, void* workspace,
-                            void* tree, float* dbias, int accumulate, void* stream) {
-  if (int rc = ensure_device()) return rc;
-  UBR_REQUIRE(logp && dlogp && dlogits.ptr && workspace && tree && dbias, "logsoftmax_bwd_bias: null pointer");
-  UBR_REQUIRE(ncls >= 1 && ncls <= 4 && dlogits.c >= 8 && dlogits.c % 8 == 0 && dlogits.ld % 8 == 0,
-              "logsoftmax_bwd_bias: ncls=%d (<= 4) / dlogits view unsupported", ncls);
-  UBR_REQUIRE((long)dlogits.n * dlogits.h * dlogits.w == (long)n * hw, "logsoftmax_bwd_bias: pixel count mismatch");
-  unsigned nb = blocks_for((long)n * hw);
-  if (nb > 592u) nb = 592u;
-  float* partials = (float*)workspace;
-  SumsFinal f{partials + (size_t)592 * 4, {dbias, nullptr, nullptr, nullptr}, ncls, 1, 4, accumulate};
-  ::ubr::Launch(nb, 256, tree_smem_bytes(4, 256), (cudaStream_t)stream)(
-      logsoftmax_bwd_kernel, logp, dlogp, n, ncls, hw, (__nv_bfloat16*)dlogits.ptr, dlogits.c, dlogits.ld, partials,
-      make_tree(tree, partials, (int)nb, 4), f);
+  ::ubr::Launch(blocks_for((long)n * hw), 256, 0, (cudaStream_t)stream)(logsoftmax_bwd_kernel, logp, dlogp, n, ncls, hw, (__nv_bfloat16*)dlogits.ptr, dlogits.c, dlogits.ld);
   UBR_LAUNCH_CHECK("logsoftmax_bwd_kernel");
   return 0;
 }

@@ -411,11 +411,9 @@ class Engine:
         m = self.model
         p = m.inplanes
         ncls = m.conv11.out_channels
-        # the conv11 bias gradient (per-class pixel sum of dl) rides in the log-softmax backward launch
-        dl, have_db = ops.logsoftmax_bwd(saved["logp"], dlogp.float(), dbias=grads[m.conv11.bias], ws=bn_ws)
+        dl = ops.logsoftmax_bwd(saved["logp"], dlogp.float())
         self._wgrad(lambda: ops.conv2d_wgrad(saved["a10"], dl, ncls, 7, 1, grads[m.conv11.weight], False, wg_ws), dl)
-        if not have_db:
-            _bias_grad(dl, grads[m.conv11.bias], bn_ws)
+        _bias_grad(dl, grads[m.conv11.bias], bn_ws)
         w11 = self._pack(m.conv11, True)
         dy10 = ops.conv2d_dgrad_bn_bwd(dl, w11.dgrad, m.nkernels, 7, 1, saved["y10"], saved["st10"], True, bn_ws,
                                        grads[m.bn10.weight], grads[m.bn10.bias])

@@ -612,24 +612,12 @@ def logsoftmax_fwd(logits, n, ncls, h, w):
     return logp
 
 
-def logsoftmax_bwd(logp, dlogp, dl=None, dbias=None, ws=None):
-    """dlogits (bf16, 16 channels, classes first).  With `dbias` (fp32 [ncls], ncls <= 4) and a bn_workspace `ws` the
-    bias gradient of the conv that produced the logits -- the per-class pixel sum of dlogits -- is written by the same
-    launch; returns (dl, True) then, (dl, False) if the caller still has to sum."""
+def logsoftmax_bwd(logp, dlogp, dl=None):
     lib = _lib.load()
     n, ncls, h, w = logp.shape
     if dl is None:
         dl = Act.empty(n, h, w, 16, logp.device)
     dlogp = dlogp.contiguous()
-    if dbias is not None:
-        tree = _tree(ws) if (ws is not None and ncls <= 4) else 0
-        if tree:
-            _lib.check(lib.ubr_logsoftmax_bwd_bias(logp.data_ptr(), dlogp.data_ptr(), n, ncls, h * w, dl.view(), ws.data_ptr(),
-                                                   tree, dbias.data_ptr(), 0, _stream()), "logsoftmax_bwd_bias")
-            return dl, True
-        _lib.check(lib.ubr_logsoftmax_bwd(logp.data_ptr(), dlogp.data_ptr(), n, ncls, h * w, dl.view(), _stream()),
-                   "logsoftmax_bwd")
-        return dl, False
     _lib.check(lib.ubr_logsoftmax_bwd(logp.data_ptr(), dlogp.data_ptr(), n, ncls, h * w, dl.view(), _stream()),
                "logsoftmax_bwd")
     return dl
